@@ -1,0 +1,230 @@
+/*
+ * stoat_gpu.h — C ABI of the B200 (sm_100a) implementation of STOAT's per-snarl
+ * association-testing hot path (`stoat vcf`).
+ *
+ * The reference (Pa-Tou/stoat) has no plugin / FFI interface: its hot loop is the body of
+ *   SnarlAnalyzer::process_snarls_by_chromosome_chunk   (src/snarl_analyzer.cpp:161-172)
+ * which calls the virtual analyze_and_write_snarl (src/snarl_analyzer.hpp:66) once per snarl.
+ * This ABI replaces that loop body for a whole chromosome chunk with ONE batched call per
+ * analyzer type.  Everything is plain pointers and sizes; the caller owns every buffer;
+ * the context owns device memory only.  There is no CPU fallback: every entry point fails
+ * with STOAT_GPU_ERR_CUDA when no sm_100 device is usable.
+ *
+ * Data contract (all host pointers unless a name ends in _dev):
+ *
+ *  presence matrix   the reference's EdgeBySampleMatrix bytes (src/matrix.hpp:51-55,
+ *                    src/matrix.cpp:67-84): bit index = row * n_cols + col, LSB-first inside
+ *                    each byte, rows NOT byte aligned.  rows = graph edges, cols = haplotypes
+ *                    (2 per sample, haplotype h belongs to sample h/2).
+ *  snarl paths       CSR produced by the host shim from Snarl_data_t::snarl_paths with the
+ *                    reference's decompose_path_to_edges + identify_path front half
+ *                    (src/snarl_analyzer.cpp:263-274, 321-337):
+ *                      snarl_path_off[S+1]  first path of each snarl
+ *                      path_edge_off[P+1]   first checked edge of each path
+ *                      edge_row[sum R]      matrix row of each checked edge; edges touching
+ *                                           node id 0 are already dropped (:328-330);
+ *                                           STOAT_GPU_MISSING_EDGE marks an edge absent from
+ *                                           the matrix => the path matches nobody (:334-336).
+ *                    A path with zero checked edges matches every haplotype (:343-354).
+ *  results           one entry per snarl (or per path), in input order.  P-values come back
+ *                    as (double, code) pairs; the code selects the reference's literal strings
+ *                    ("NA", "0", "1", set_precision(DBL_MAX)), otherwise the double is
+ *                    formatted with set_precision (src/utils.cpp:5-15) by the host shim.
+ */
+#ifndef STOAT_GPU_H
+#define STOAT_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define STOAT_GPU_ABI_VERSION 1
+#define STOAT_GPU_MISSING_EDGE 0xFFFFFFFFu
+/* hard limits of the device kernels (a snarl above them is reported, never silently mangled) */
+#define STOAT_GPU_MAX_PATHS_PER_SNARL 64   /* paths (table columns) in one snarl            */
+#define STOAT_GPU_MAX_OLS_FEATURES 16      /* 1 + dosage columns + covariates              */
+
+/* return codes */
+enum {
+    STOAT_GPU_OK = 0,
+    STOAT_GPU_ERR_ARG = -1,     /* null pointer / inconsistent sizes / limits exceeded      */
+    STOAT_GPU_ERR_CUDA = -2,    /* CUDA runtime failure or no sm_100 device                 */
+    STOAT_GPU_ERR_STATE = -3,   /* call order (e.g. batch before set_matrix)                */
+    STOAT_GPU_ERR_OOM = -4      /* device or pinned-host allocation failed                  */
+};
+
+/* how a p-value (or statistic) must be printed; mirrors the string returns of
+ * FisherKhi2 (src/stats_test.cpp:189,197,230-234,269,313,323)                              */
+enum {
+    STOAT_P_VALUE = 0,   /* print set_precision(value)                                      */
+    STOAT_P_NA = 1,      /* "NA"                                                            */
+    STOAT_P_ZERO = 2,    /* "0"   (Fisher recurrence overflowed, stats_test.cpp:312-314)    */
+    STOAT_P_ONE = 3,     /* "1"   (Fisher centre mass is zero, stats_test.cpp:322-324)      */
+    STOAT_P_DBLMAX = 4,  /* set_precision(DBL_MAX) (an expected count is zero, :196-197)    */
+    STOAT_P_UNDEF = 5    /* the reference reads out of bounds here (zero dosage columns
+                            reach linear_regression, stats_test.cpp:487-489): value is NaN  */
+};
+
+/* filtering thresholds, defaults of `stoat vcf` (src/subcommand/vcf.cpp:61-73)             */
+typedef struct stoat_gpu_thresholds {
+    uint64_t min_individuals; /* default 3   */
+    uint64_t min_haplotypes;  /* default 5   */
+    double maf_threshold;     /* default 0.05 */
+} stoat_gpu_thresholds;
+
+/* flattened snarl paths of one batch (see "snarl paths" above)                             */
+typedef struct stoat_gpu_paths {
+    uint64_t n_snarls;
+    const uint64_t* snarl_path_off; /* [n_snarls + 1]                 */
+    const uint64_t* path_edge_off;  /* [n_paths + 1], n_paths = snarl_path_off[n_snarls]   */
+    const uint32_t* edge_row;       /* [path_edge_off[n_paths]]       */
+} stoat_gpu_paths;
+
+/* outputs of the binary analyzer: BinarySnarlAnalyzer::analyze_and_write_snarl
+ * (src/snarl_analyzer.cpp:358-390)                                                          */
+typedef struct stoat_gpu_binary_out {
+    uint32_t* g0;          /* [n_paths] controls on path, BEFORE empty-column removal
+                              (create_binary_table, src/binary_table.cpp:19-44)             */
+    uint32_t* g1;          /* [n_paths] cases on path                                       */
+    uint64_t* total_sum;   /* [n_snarls] sum over paths of matching haplotypes              */
+    uint8_t* filtered;     /* [n_snarls] 1 = filtration_binary_table said "filter"
+                              (src/snarl_analyzer.cpp:705-732); p-values are then unset     */
+    double* p_chi2;        /* [n_snarls] chi2_2x2 / chi2_2xN (src/stats_test.cpp:181-257)   */
+    double* p_fisher;      /* [n_snarls] fastFishersExactTest (:264-360), 2 columns only    */
+    uint8_t* chi2_code;    /* [n_snarls] STOAT_P_*                                           */
+    uint8_t* fisher_code;  /* [n_snarls] STOAT_P_*                                           */
+} stoat_gpu_binary_out;
+
+/* outputs of the quantitative analyzer: QuantitativeSnarlAnalyzer::analyze_and_write_snarl
+ * (src/snarl_analyzer.cpp:431-467) -> LinearRegression::linear_regression
+ * (src/stats_test.cpp:424-506)                                                              */
+typedef struct stoat_gpu_quant_out {
+    uint32_t* allele_paths; /* [n_paths] haplotypes on each path (0 for empty paths)
+                               (process_table_quantitative, src/quantitative_table.cpp:57-58) */
+    uint8_t* filtered;      /* [n_snarls] filtration_quantitative_table (:542-579)          */
+    uint32_t* n_used;       /* [n_snarls] rows of the regression table (samples with a hit) */
+    double* p_value;        /* [n_snarls] two-sided Student-t p of the FIRST dosage column  */
+    double* r2;             /* [n_snarls]                                                    */
+    double* beta;           /* [n_snarls]                                                    */
+    double* se;             /* [n_snarls]                                                    */
+    uint8_t* code;          /* [n_snarls] STOAT_P_VALUE or STOAT_P_UNDEF                     */
+} stoat_gpu_quant_out;
+
+/* eQTL: EQTLSnarlAnalyzer::analyze_and_write_snarl (src/snarl_analyzer.cpp:493-539): one OLS
+ * per (snarl, gene in window).  Gene windows are resolved on the host (found_gene_snarl,
+ * :471-491) into a CSR of gene indices per snarl; pair k of the output is
+ * (snarl s, gene gene_idx[k]) for snarl_gene_off[s] <= k < snarl_gene_off[s+1].             */
+typedef struct stoat_gpu_eqtl_genes {
+    uint64_t n_genes;
+    const double* expression;        /* [n_genes * n_samples] row-major, gene major         */
+    const uint64_t* snarl_gene_off;  /* [n_snarls + 1]; NULL = dense (every gene, every snarl) */
+    const uint32_t* gene_idx;        /* [snarl_gene_off[n_snarls]]; NULL when dense          */
+} stoat_gpu_eqtl_genes;
+
+typedef struct stoat_gpu_eqtl_out {
+    uint32_t* allele_paths; /* [n_paths]                                                     */
+    uint8_t* filtered;      /* [n_snarls]                                                    */
+    uint32_t* n_used;       /* [n_snarls]                                                    */
+    double* p_value;        /* [n_pairs]                                                     */
+    double* r2;             /* [n_pairs]                                                     */
+    double* beta;           /* [n_pairs]                                                     */
+    double* se;             /* [n_pairs]                                                     */
+    uint8_t* code;          /* [n_pairs]                                                     */
+} stoat_gpu_eqtl_out;
+
+/* device-side reduction of a dense eQTL scan whose pair table cannot be returned whole
+ * (200k snarls x 20k genes = 4e9 rows); mirrors the reference's --table-threshold idea
+ * (src/snarl_analyzer.cpp:524-527): per snarl the best gene and the number of significant ones */
+typedef struct stoat_gpu_eqtl_summary {
+    double* min_p;          /* [n_snarls] smallest p over genes (NaN if filtered)            */
+    uint32_t* argmin_gene;  /* [n_snarls]                                                    */
+    uint32_t* n_below;      /* [n_snarls] genes with p < p_threshold                         */
+} stoat_gpu_eqtl_summary;
+
+typedef struct stoat_gpu_ctx stoat_gpu_ctx;
+
+/* timing of the last batch call, measured with CUDA events on the context's stream          */
+typedef struct stoat_gpu_timing {
+    float h2d_ms;      /* host -> device copies of the batch inputs                          */
+    float repack_ms;   /* K0 repack_rows (only when the matrix was (re)uploaded)              */
+    float table_ms;    /* K1 path_and_popc / K3 dosage pass                                  */
+    float stats_ms;    /* K2 binary_stats / K4 ols_solve                                     */
+    float d2h_ms;      /* device -> host copies of the results                               */
+    uint32_t launches; /* kernels launched by the call                                       */
+} stoat_gpu_timing;
+
+/* ---- lifetime -------------------------------------------------------------------------- */
+int stoat_gpu_abi_version(void);
+/* one context per host thread and per device (the reference calls the analyzer from OpenMP
+ * threads, src/snarl_analyzer.cpp:165; a context is NOT thread safe)                        */
+int stoat_gpu_create(stoat_gpu_ctx** out, int device);
+void stoat_gpu_destroy(stoat_gpu_ctx* ctx);
+/* message of the last failure on this context ("" if none); ctx may be NULL for create()    */
+const char* stoat_gpu_last_error(const stoat_gpu_ctx* ctx);
+
+/* ---- per-chromosome state (replaces the const-refs held by SnarlAnalyzer,
+ *      src/snarl_analyzer.hpp:75-92) ------------------------------------------------------ */
+/* Upload the reference-layout bit matrix and repack it on the device (K0) into 16-byte
+ * aligned rows.  n_cols must be even (2 haplotypes per sample).                             */
+int stoat_gpu_set_matrix(stoat_gpu_ctx* ctx, const uint8_t* bits, uint64_t n_rows, uint64_t n_cols);
+/* Same, but the reference-layout bytes already live in device memory (bench "resident" leg,
+ * and the upstream make_edge_matrix-on-GPU row of SURVEY §8f).                              */
+int stoat_gpu_set_matrix_dev(stoat_gpu_ctx* ctx, const uint8_t* bits_dev, uint64_t n_rows, uint64_t n_cols);
+/* binary phenotype per sample: 0 = control (g0), 1 = case (g1)
+ * (parse_binary_pheno, src/arg_parser.cpp:20-95)                                            */
+int stoat_gpu_set_binary_phenotype(stoat_gpu_ctx* ctx, const uint8_t* is_case, uint64_t n_samples);
+int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, uint64_t n_samples);
+/* covariates row-major [n_samples][n_covar]; n_covar = 0 clears them.  NOTE the reference
+ * indexes covariate rows by position in the FILTERED table (src/stats_test.cpp:450-452); the
+ * device code reproduces that.                                                              */
+int stoat_gpu_set_covariates(stoat_gpu_ctx* ctx, const double* covar, uint64_t n_samples, uint64_t n_covar);
+
+/* ---- batched analyzers: host buffers in, host buffers out (the drop-in call) ----------- */
+int stoat_gpu_binary_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
+                           const stoat_gpu_thresholds* thr, stoat_gpu_binary_out* out);
+int stoat_gpu_quantitative_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
+                                 const stoat_gpu_thresholds* thr, stoat_gpu_quant_out* out);
+int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
+                         const stoat_gpu_eqtl_genes* genes, const stoat_gpu_thresholds* thr,
+                         stoat_gpu_eqtl_out* out);
+int stoat_gpu_eqtl_dense_summary(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
+                                 const stoat_gpu_eqtl_genes* genes, const stoat_gpu_thresholds* thr,
+                                 double p_threshold, stoat_gpu_eqtl_summary* out);
+
+/* ---- resident mode: inputs staged once, kernels re-run without host traffic ------------ */
+/* Copy the CSR to the device and keep it (and result buffers) resident in the context.     */
+int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths);
+/* Run K1+K2 (binary) / K3+K4 (quantitative) on the staged batch; results stay on the device */
+int stoat_gpu_binary_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
+int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
+/* Sample-sharded mode: run only the count pass, expose the device buffer that an
+ * NCCL all-reduce(sum) must be applied to, then finish with the statistics pass.
+ * counts layout: uint32 [2 * n_paths] = g0[0..P) then g1[0..P).                              */
+int stoat_gpu_binary_counts_staged(stoat_gpu_ctx* ctx);
+int stoat_gpu_binary_counts_dev(stoat_gpu_ctx* ctx, uint32_t** counts_dev, uint64_t* n_words);
+int stoat_gpu_binary_stats_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
+/* Fetch the staged results into host buffers.                                               */
+int stoat_gpu_binary_fetch(stoat_gpu_ctx* ctx, stoat_gpu_binary_out* out);
+int stoat_gpu_quantitative_fetch(stoat_gpu_ctx* ctx, stoat_gpu_quant_out* out);
+
+/* ---- introspection --------------------------------------------------------------------- */
+int stoat_gpu_last_timing(const stoat_gpu_ctx* ctx, stoat_gpu_timing* out);
+/* cudaStream_t of the context as an integer (so the caller can record its own events)       */
+uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx);
+/* bytes per repacked row on the device: ceil(n_cols / 128) * 16                             */
+uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx);
+/* read back one repacked row (tests of K0)                                                  */
+int stoat_gpu_read_row(stoat_gpu_ctx* ctx, uint64_t row, uint8_t* out, uint64_t out_bytes);
+
+/* ---- host formatting helper (pure C, no device): reference strings -------------------- */
+/* set_precision (src/utils.cpp:5-15) + the literal strings selected by `code`.  Returns the
+ * number of characters written (excluding the NUL), or -1 if buf is too small.             */
+int stoat_gpu_format_value(double value, uint8_t code, char* buf, size_t buf_len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STOAT_GPU_H */
