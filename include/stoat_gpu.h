@@ -42,6 +42,11 @@ extern "C" {
 #endif
 
 #define STOAT_GPU_ABI_VERSION 1
+#if defined(__GNUC__)
+#define STOAT_GPU_API __attribute__((visibility("default")))
+#else
+#define STOAT_GPU_API
+#endif
 #define STOAT_GPU_MISSING_EDGE 0xFFFFFFFFu
 /* hard limits of the device kernels (a snarl above them is reported, never silently mangled) */
 #define STOAT_GPU_MAX_PATHS_PER_SNARL 64   /* paths (table columns) in one snarl            */
@@ -64,8 +69,10 @@ enum {
     STOAT_P_ZERO = 2,    /* "0"   (Fisher recurrence overflowed, stats_test.cpp:312-314)    */
     STOAT_P_ONE = 3,     /* "1"   (Fisher centre mass is zero, stats_test.cpp:322-324)      */
     STOAT_P_DBLMAX = 4,  /* set_precision(DBL_MAX) (an expected count is zero, :196-197)    */
-    STOAT_P_UNDEF = 5    /* the reference reads out of bounds here (zero dosage columns
+    STOAT_P_UNDEF = 5,   /* the reference reads out of bounds here (zero dosage columns
                             reach linear_regression, stats_test.cpp:487-489): value is NaN  */
+    STOAT_P_OVERLIMIT = 6 /* snarl exceeds STOAT_GPU_MAX_*: not computed (value NaN); the host
+                            must run its own per-snarl analyzer for it                      */
 };
 
 /* filtering thresholds, defaults of `stoat vcf` (src/subcommand/vcf.cpp:61-73)             */
@@ -157,72 +164,72 @@ typedef struct stoat_gpu_timing {
 } stoat_gpu_timing;
 
 /* ---- lifetime -------------------------------------------------------------------------- */
-int stoat_gpu_abi_version(void);
+STOAT_GPU_API int stoat_gpu_abi_version(void);
 /* one context per host thread and per device (the reference calls the analyzer from OpenMP
  * threads, src/snarl_analyzer.cpp:165; a context is NOT thread safe)                        */
-int stoat_gpu_create(stoat_gpu_ctx** out, int device);
-void stoat_gpu_destroy(stoat_gpu_ctx* ctx);
+STOAT_GPU_API int stoat_gpu_create(stoat_gpu_ctx** out, int device);
+STOAT_GPU_API void stoat_gpu_destroy(stoat_gpu_ctx* ctx);
 /* message of the last failure on this context ("" if none); ctx may be NULL for create()    */
-const char* stoat_gpu_last_error(const stoat_gpu_ctx* ctx);
+STOAT_GPU_API const char* stoat_gpu_last_error(const stoat_gpu_ctx* ctx);
 
 /* ---- per-chromosome state (replaces the const-refs held by SnarlAnalyzer,
  *      src/snarl_analyzer.hpp:75-92) ------------------------------------------------------ */
 /* Upload the reference-layout bit matrix and repack it on the device (K0) into 16-byte
  * aligned rows.  n_cols must be even (2 haplotypes per sample).                             */
-int stoat_gpu_set_matrix(stoat_gpu_ctx* ctx, const uint8_t* bits, uint64_t n_rows, uint64_t n_cols);
+STOAT_GPU_API int stoat_gpu_set_matrix(stoat_gpu_ctx* ctx, const uint8_t* bits, uint64_t n_rows, uint64_t n_cols);
 /* Same, but the reference-layout bytes already live in device memory (bench "resident" leg,
  * and the upstream make_edge_matrix-on-GPU row of SURVEY §8f).                              */
-int stoat_gpu_set_matrix_dev(stoat_gpu_ctx* ctx, const uint8_t* bits_dev, uint64_t n_rows, uint64_t n_cols);
+STOAT_GPU_API int stoat_gpu_set_matrix_dev(stoat_gpu_ctx* ctx, const uint8_t* bits_dev, uint64_t n_rows, uint64_t n_cols);
 /* binary phenotype per sample: 0 = control (g0), 1 = case (g1)
  * (parse_binary_pheno, src/arg_parser.cpp:20-95)                                            */
-int stoat_gpu_set_binary_phenotype(stoat_gpu_ctx* ctx, const uint8_t* is_case, uint64_t n_samples);
-int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, uint64_t n_samples);
+STOAT_GPU_API int stoat_gpu_set_binary_phenotype(stoat_gpu_ctx* ctx, const uint8_t* is_case, uint64_t n_samples);
+STOAT_GPU_API int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, uint64_t n_samples);
 /* covariates row-major [n_samples][n_covar]; n_covar = 0 clears them.  NOTE the reference
  * indexes covariate rows by position in the FILTERED table (src/stats_test.cpp:450-452); the
  * device code reproduces that.                                                              */
-int stoat_gpu_set_covariates(stoat_gpu_ctx* ctx, const double* covar, uint64_t n_samples, uint64_t n_covar);
+STOAT_GPU_API int stoat_gpu_set_covariates(stoat_gpu_ctx* ctx, const double* covar, uint64_t n_samples, uint64_t n_covar);
 
 /* ---- batched analyzers: host buffers in, host buffers out (the drop-in call) ----------- */
-int stoat_gpu_binary_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
+STOAT_GPU_API int stoat_gpu_binary_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
                            const stoat_gpu_thresholds* thr, stoat_gpu_binary_out* out);
-int stoat_gpu_quantitative_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
+STOAT_GPU_API int stoat_gpu_quantitative_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
                                  const stoat_gpu_thresholds* thr, stoat_gpu_quant_out* out);
-int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
+STOAT_GPU_API int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
                          const stoat_gpu_eqtl_genes* genes, const stoat_gpu_thresholds* thr,
                          stoat_gpu_eqtl_out* out);
-int stoat_gpu_eqtl_dense_summary(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
+STOAT_GPU_API int stoat_gpu_eqtl_dense_summary(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
                                  const stoat_gpu_eqtl_genes* genes, const stoat_gpu_thresholds* thr,
                                  double p_threshold, stoat_gpu_eqtl_summary* out);
 
 /* ---- resident mode: inputs staged once, kernels re-run without host traffic ------------ */
 /* Copy the CSR to the device and keep it (and result buffers) resident in the context.     */
-int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths);
+STOAT_GPU_API int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths);
 /* Run K1+K2 (binary) / K3+K4 (quantitative) on the staged batch; results stay on the device */
-int stoat_gpu_binary_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
-int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
+STOAT_GPU_API int stoat_gpu_binary_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
+STOAT_GPU_API int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
 /* Sample-sharded mode: run only the count pass, expose the device buffer that an
  * NCCL all-reduce(sum) must be applied to, then finish with the statistics pass.
  * counts layout: uint32 [2 * n_paths] = g0[0..P) then g1[0..P).                              */
-int stoat_gpu_binary_counts_staged(stoat_gpu_ctx* ctx);
-int stoat_gpu_binary_counts_dev(stoat_gpu_ctx* ctx, uint32_t** counts_dev, uint64_t* n_words);
-int stoat_gpu_binary_stats_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
+STOAT_GPU_API int stoat_gpu_binary_counts_staged(stoat_gpu_ctx* ctx);
+STOAT_GPU_API int stoat_gpu_binary_counts_dev(stoat_gpu_ctx* ctx, uint32_t** counts_dev, uint64_t* n_words);
+STOAT_GPU_API int stoat_gpu_binary_stats_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
 /* Fetch the staged results into host buffers.                                               */
-int stoat_gpu_binary_fetch(stoat_gpu_ctx* ctx, stoat_gpu_binary_out* out);
-int stoat_gpu_quantitative_fetch(stoat_gpu_ctx* ctx, stoat_gpu_quant_out* out);
+STOAT_GPU_API int stoat_gpu_binary_fetch(stoat_gpu_ctx* ctx, stoat_gpu_binary_out* out);
+STOAT_GPU_API int stoat_gpu_quantitative_fetch(stoat_gpu_ctx* ctx, stoat_gpu_quant_out* out);
 
 /* ---- introspection --------------------------------------------------------------------- */
-int stoat_gpu_last_timing(const stoat_gpu_ctx* ctx, stoat_gpu_timing* out);
+STOAT_GPU_API int stoat_gpu_last_timing(const stoat_gpu_ctx* ctx, stoat_gpu_timing* out);
 /* cudaStream_t of the context as an integer (so the caller can record its own events)       */
-uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx);
+STOAT_GPU_API uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx);
 /* bytes per repacked row on the device: ceil(n_cols / 128) * 16                             */
-uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx);
+STOAT_GPU_API uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx);
 /* read back one repacked row (tests of K0)                                                  */
-int stoat_gpu_read_row(stoat_gpu_ctx* ctx, uint64_t row, uint8_t* out, uint64_t out_bytes);
+STOAT_GPU_API int stoat_gpu_read_row(stoat_gpu_ctx* ctx, uint64_t row, uint8_t* out, uint64_t out_bytes);
 
 /* ---- host formatting helper (pure C, no device): reference strings -------------------- */
 /* set_precision (src/utils.cpp:5-15) + the literal strings selected by `code`.  Returns the
  * number of characters written (excluding the NUL), or -1 if buf is too small.             */
-int stoat_gpu_format_value(double value, uint8_t code, char* buf, size_t buf_len);
+STOAT_GPU_API int stoat_gpu_format_value(double value, uint8_t code, char* buf, size_t buf_len);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,231 @@
+"""NumPy front end of the C ABI (include/stoat_gpu.h): one `Context` per GPU.
+
+Every call goes through libstoat_gpu.so; nothing here computes statistics.  Arrays follow the ABI:
+the presence matrix is the reference's `EdgeBySampleMatrix` byte layout (src/matrix.cpp:67-84), snarl
+paths are the CSR of include/stoat_gpu.h.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _lib as L
+
+
+class StoatGpuError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"stoat_gpu error {code}: {msg}")
+        self.code = code
+
+
+@dataclass
+class SnarlPaths:
+    """Flattened snarl paths of one batch (`stoat_gpu_paths`)."""
+    snarl_path_off: np.ndarray  # uint64 [S+1]
+    path_edge_off: np.ndarray   # uint64 [P+1]
+    edge_row: np.ndarray        # uint32 [sum R]
+
+    def __post_init__(self):
+        self.snarl_path_off = np.ascontiguousarray(self.snarl_path_off, dtype=np.uint64)
+        self.path_edge_off = np.ascontiguousarray(self.path_edge_off, dtype=np.uint64)
+        self.edge_row = np.ascontiguousarray(self.edge_row, dtype=np.uint32)
+
+    @property
+    def n_snarls(self) -> int:
+        return len(self.snarl_path_off) - 1
+
+    @property
+    def n_paths(self) -> int:
+        return int(self.snarl_path_off[-1]) if len(self.snarl_path_off) else 0
+
+    def as_c(self) -> L.PathsC:
+        er = self.edge_row if self.edge_row.size else np.zeros(1, np.uint32)
+        self._keep = er
+        return L.PathsC(self.n_snarls, self.snarl_path_off.ctypes.data_as(L.u64p),
+                        self.path_edge_off.ctypes.data_as(L.u64p), er.ctypes.data_as(L.u32p))
+
+
+def _ptr(a: np.ndarray):
+    return C.c_void_p(a.ctypes.data)
+
+
+class Context:
+    """`stoat_gpu_ctx`: device state for one chromosome chunk on one GPU."""
+
+    def __init__(self, device: int = 0):
+        self._lib = L.load()
+        self._ctx = L.CTX()
+        rc = self._lib.stoat_gpu_create(C.byref(self._ctx), device)
+        if rc != L.OK:
+            msg = self._lib.stoat_gpu_last_error(None).decode()
+            self._ctx = None
+            raise StoatGpuError(rc, msg)
+        self.device = device
+        self.n_rows = self.n_cols = 0
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._lib.stoat_gpu_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc: int):
+        if rc != L.OK:
+            raise StoatGpuError(rc, self._lib.stoat_gpu_last_error(self._ctx).decode())
+
+    # ---- state --------------------------------------------------------------------------------------
+    def set_matrix(self, bits: np.ndarray, n_rows: int, n_cols: int):
+        bits = np.ascontiguousarray(bits, dtype=np.uint8)
+        need = (n_rows * n_cols + 7) // 8
+        if bits.size < need:
+            raise ValueError(f"matrix needs {need} bytes, got {bits.size}")
+        self._check(self._lib.stoat_gpu_set_matrix(self._ctx, _ptr(bits), n_rows, n_cols))
+        self.n_rows, self.n_cols = n_rows, n_cols
+
+    def set_matrix_ptr(self, host_ptr: int, n_rows: int, n_cols: int):
+        """Same, from a raw host pointer (e.g. a pinned torch tensor's data_ptr())."""
+        self._check(self._lib.stoat_gpu_set_matrix(self._ctx, C.c_void_p(host_ptr), n_rows, n_cols))
+        self.n_rows, self.n_cols = n_rows, n_cols
+
+    def set_matrix_dev(self, dev_ptr: int, n_rows: int, n_cols: int):
+        self._check(self._lib.stoat_gpu_set_matrix_dev(self._ctx, C.c_void_p(dev_ptr), n_rows, n_cols))
+        self.n_rows, self.n_cols = n_rows, n_cols
+
+    def set_binary_phenotype(self, is_case: np.ndarray):
+        a = np.ascontiguousarray(is_case, dtype=np.uint8)
+        self._check(self._lib.stoat_gpu_set_binary_phenotype(self._ctx, _ptr(a), a.size))
+
+    def set_quantitative_phenotype(self, y: np.ndarray):
+        a = np.ascontiguousarray(y, dtype=np.float64)
+        self._check(self._lib.stoat_gpu_set_quantitative_phenotype(self._ctx, _ptr(a), a.size))
+
+    def set_covariates(self, covar):
+        if covar is None or np.size(covar) == 0:
+            self._check(self._lib.stoat_gpu_set_covariates(self._ctx, None, 0, 0))
+            return
+        a = np.ascontiguousarray(covar, dtype=np.float64)
+        self._check(self._lib.stoat_gpu_set_covariates(self._ctx, _ptr(a), a.shape[0], a.shape[1]))
+
+    @property
+    def row_pitch(self) -> int:
+        return int(self._lib.stoat_gpu_row_pitch(self._ctx))
+
+    @property
+    def stream(self) -> int:
+        return int(self._lib.stoat_gpu_stream(self._ctx))
+
+    def read_row(self, row: int) -> np.ndarray:
+        out = np.zeros(self.row_pitch, np.uint8)
+        self._check(self._lib.stoat_gpu_read_row(self._ctx, row, _ptr(out), out.size))
+        return out
+
+    def timing(self) -> dict:
+        t = L.Timing()
+        self._check(self._lib.stoat_gpu_last_timing(self._ctx, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in L.Timing._fields_}
+
+    # ---- output holders -----------------------------------------------------------------------------
+    @staticmethod
+    def _binary_arrays(S: int, P: int) -> dict:
+        return dict(g0=np.zeros(P, np.uint32), g1=np.zeros(P, np.uint32), total_sum=np.zeros(S, np.uint64),
+                    filtered=np.zeros(S, np.uint8), p_chi2=np.zeros(S), p_fisher=np.zeros(S),
+                    chi2_code=np.zeros(S, np.uint8), fisher_code=np.zeros(S, np.uint8))
+
+    @staticmethod
+    def _binary_c(o: dict) -> L.BinaryOut:
+        return L.BinaryOut(o["g0"].ctypes.data_as(L.u32p), o["g1"].ctypes.data_as(L.u32p),
+                           o["total_sum"].ctypes.data_as(L.u64p), o["filtered"].ctypes.data_as(L.u8p),
+                           o["p_chi2"].ctypes.data_as(L.f64p), o["p_fisher"].ctypes.data_as(L.f64p),
+                           o["chi2_code"].ctypes.data_as(L.u8p), o["fisher_code"].ctypes.data_as(L.u8p))
+
+    @staticmethod
+    def _quant_arrays(S: int, P: int) -> dict:
+        return dict(allele_paths=np.zeros(P, np.uint32), filtered=np.zeros(S, np.uint8),
+                    n_used=np.zeros(S, np.uint32), p_value=np.zeros(S), r2=np.zeros(S), beta=np.zeros(S),
+                    se=np.zeros(S), code=np.zeros(S, np.uint8))
+
+    @staticmethod
+    def _quant_c(o: dict) -> L.QuantOut:
+        return L.QuantOut(o["allele_paths"].ctypes.data_as(L.u32p), o["filtered"].ctypes.data_as(L.u8p),
+                          o["n_used"].ctypes.data_as(L.u32p), o["p_value"].ctypes.data_as(L.f64p),
+                          o["r2"].ctypes.data_as(L.f64p), o["beta"].ctypes.data_as(L.f64p),
+                          o["se"].ctypes.data_as(L.f64p), o["code"].ctypes.data_as(L.u8p))
+
+    @staticmethod
+    def _thr(min_ind, min_hap, maf) -> L.Thresholds:
+        return L.Thresholds(int(min_ind), int(min_hap), float(maf))
+
+    # ---- the drop-in calls: host buffers in, host buffers out -----------------------------------------
+    def binary_batch(self, paths: SnarlPaths, min_ind=3, min_hap=5, maf=0.05, out: dict | None = None) -> dict:
+        o = out if out is not None else self._binary_arrays(paths.n_snarls, paths.n_paths)
+        pc, thr, oc = paths.as_c(), self._thr(min_ind, min_hap, maf), self._binary_c(o)
+        self._check(self._lib.stoat_gpu_binary_batch(self._ctx, C.byref(pc), C.byref(thr), C.byref(oc)))
+        return o
+
+    def quantitative_batch(self, paths: SnarlPaths, min_ind=3, min_hap=5, maf=0.05, out: dict | None = None) -> dict:
+        o = out if out is not None else self._quant_arrays(paths.n_snarls, paths.n_paths)
+        pc, thr, oc = paths.as_c(), self._thr(min_ind, min_hap, maf), self._quant_c(o)
+        self._check(self._lib.stoat_gpu_quantitative_batch(self._ctx, C.byref(pc), C.byref(thr), C.byref(oc)))
+        return o
+
+    # ---- resident mode ------------------------------------------------------------------------------
+    def stage_paths(self, paths: SnarlPaths):
+        pc = paths.as_c()
+        self._check(self._lib.stoat_gpu_stage_paths(self._ctx, C.byref(pc)))
+        self._staged = (paths.n_snarls, paths.n_paths)
+
+    def binary_run_staged(self, min_ind=3, min_hap=5, maf=0.05):
+        thr = self._thr(min_ind, min_hap, maf)
+        self._check(self._lib.stoat_gpu_binary_run_staged(self._ctx, C.byref(thr)))
+
+    def binary_counts_staged(self):
+        self._check(self._lib.stoat_gpu_binary_counts_staged(self._ctx))
+
+    def binary_counts_dev(self) -> tuple[int, int]:
+        p, n = C.c_void_p(), C.c_uint64()
+        self._check(self._lib.stoat_gpu_binary_counts_dev(self._ctx, C.byref(p), C.byref(n)))
+        return int(p.value), int(n.value)
+
+    def binary_stats_staged(self, min_ind=3, min_hap=5, maf=0.05):
+        thr = self._thr(min_ind, min_hap, maf)
+        self._check(self._lib.stoat_gpu_binary_stats_staged(self._ctx, C.byref(thr)))
+
+    def binary_fetch(self, out: dict | None = None) -> dict:
+        S, P = self._staged
+        o = out if out is not None else self._binary_arrays(S, P)
+        oc = self._binary_c(o)
+        self._check(self._lib.stoat_gpu_binary_fetch(self._ctx, C.byref(oc)))
+        return o
+
+    def quantitative_run_staged(self, min_ind=3, min_hap=5, maf=0.05):
+        thr = self._thr(min_ind, min_hap, maf)
+        self._check(self._lib.stoat_gpu_quantitative_run_staged(self._ctx, C.byref(thr)))
+
+    def quantitative_fetch(self, out: dict | None = None) -> dict:
+        S, P = self._staged
+        o = out if out is not None else self._quant_arrays(S, P)
+        oc = self._quant_c(o)
+        self._check(self._lib.stoat_gpu_quantitative_fetch(self._ctx, C.byref(oc)))
+        return o
+
+
+def format_value(value: float, code: int) -> str:
+    """The reference's output strings: set_precision (src/utils.cpp:5-15) + "NA"/"0"/"1"."""
+    buf = C.create_string_buffer(64)
+    n = L.load().stoat_gpu_format_value(float(value), int(code), buf, 64)
+    if n < 0:
+        raise ValueError("format_value: buffer too small")
+    return buf.value.decode()

@@ -1,0 +1,563 @@
+// abi.cu — implementation of the C ABI declared in include/stoat_gpu.h.
+//
+// Host side only: argument checks, device buffers, copies, kernel launches, timing with CUDA events
+// on the context's stream.  No statistics are computed on the host: if the device is not a usable
+// sm_100 GPU every entry point fails (there is no CPU fallback).
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "ctx.hpp"
+
+using namespace stoat;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+int fail(stoat_gpu_ctx* ctx, int code, const std::string& msg) {
+    if (ctx)
+        ctx->err = msg;
+    else
+        g_create_error = msg;
+    return code;
+}
+int fail_cuda(stoat_gpu_ctx* ctx, cudaError_t e, const char* where) {
+    const int code = (e == cudaErrorMemoryAllocation) ? STOAT_GPU_ERR_OOM : STOAT_GPU_ERR_CUDA;
+    return fail(ctx, code, std::string(where) + ": " + cudaGetErrorString(e));
+}
+#define CK(expr)                                                  \
+    do {                                                          \
+        cudaError_t e__ = (expr);                                 \
+        if (e__ != cudaSuccess) return fail_cuda(ctx, e__, #expr); \
+    } while (0)
+
+uint64_t pitch_for(uint64_t n_cols) { return ((n_cols + 127) / 128) * 16; }
+
+MatrixDev matrix_view(const stoat_gpu_ctx* ctx) {
+    MatrixDev m;
+    m.rows = ctx->rows.as<uint8_t>();
+    m.n_rows = ctx->n_rows;
+    m.n_cols = ctx->n_cols;
+    m.pitch = ctx->pitch;
+    return m;
+}
+
+struct QuantState {
+    DevBuf yc, ys, mom;
+    double sy_all = 0.0, syy_all = 0.0;
+};
+
+}  // namespace
+
+// extra per-context state that does not need to be visible to the kernel translation units
+struct CtxExtra {
+    QuantState q;
+    uint32_t max_stage_rows = 0;
+    uint32_t counters_host[4] = {0, 0, 0, 0};
+};
+static CtxExtra* extra_of(stoat_gpu_ctx* ctx);
+
+struct stoat_gpu_ctx_full : stoat_gpu_ctx {
+    CtxExtra extra;
+};
+static CtxExtra* extra_of(stoat_gpu_ctx* ctx) { return &static_cast<stoat_gpu_ctx_full*>(ctx)->extra; }
+
+extern "C" {
+
+int stoat_gpu_abi_version(void) { return STOAT_GPU_ABI_VERSION; }
+
+const char* stoat_gpu_last_error(const stoat_gpu_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int stoat_gpu_create(stoat_gpu_ctx** out, int device) {
+    stoat_gpu_ctx* ctx = nullptr;
+    if (!out) return fail(nullptr, STOAT_GPU_ERR_ARG, "stoat_gpu_create: out is NULL");
+    *out = nullptr;
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0)
+        return fail(nullptr, STOAT_GPU_ERR_CUDA,
+                    std::string("stoat_gpu_create: no CUDA device (") + cudaGetErrorString(e) +
+                        "); this library has no CPU fallback");
+    if (device < 0 || device >= n_dev) return fail(nullptr, STOAT_GPU_ERR_ARG, "stoat_gpu_create: bad device index");
+    cudaDeviceProp prop{};
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail_cuda(nullptr, e, "cudaGetDeviceProperties");
+    if (prop.major != 10)
+        return fail(nullptr, STOAT_GPU_ERR_CUDA,
+                    "stoat_gpu_create: device is sm_" + std::to_string(prop.major) + std::to_string(prop.minor) +
+                        ", this library is built for sm_100a (B200) only");
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail_cuda(nullptr, e, "cudaSetDevice");
+    stoat_gpu_ctx_full* full = new (std::nothrow) stoat_gpu_ctx_full();
+    if (!full) return fail(nullptr, STOAT_GPU_ERR_OOM, "stoat_gpu_create: host allocation failed");
+    ctx = full;
+    ctx->device = device;
+    ctx->num_sms = prop.multiProcessorCount;
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        delete full;
+        return fail_cuda(nullptr, e, "cudaStreamCreate");
+    }
+    for (auto& ev : ctx->ev)
+        if ((e = cudaEventCreate(&ev)) != cudaSuccess) {
+            delete full;
+            return fail_cuda(nullptr, e, "cudaEventCreate");
+        }
+    const char* k1 = std::getenv("STOAT_GPU_K1");
+    ctx->k1_variant = (k1 && std::strcmp(k1, "ldg") == 0) ? 1 : 0;
+    *out = ctx;
+    return STOAT_GPU_OK;
+}
+
+void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    DevBuf* bufs[] = {&ctx->rows, &ctx->raw_stage[0], &ctx->raw_stage[1], &ctx->case_mask, &ctx->is_case_dev, &ctx->y,
+                      &ctx->covar, &ctx->d_snarl_path_off, &ctx->d_path_edge_off, &ctx->d_edge_row, &ctx->d_rec,
+                      &ctx->d_blob, &ctx->d_big, &ctx->d_counters, &ctx->counts, &ctx->total_sum, &ctx->filtered,
+                      &ctx->p_a, &ctx->p_b, &ctx->code_a, &ctx->code_b, &ctx->q_allele, &ctx->q_nused, &ctx->q_p,
+                      &ctx->q_r2, &ctx->q_beta, &ctx->q_se, &ctx->q_code};
+    for (DevBuf* b : bufs) b->release();
+    CtxExtra* x = extra_of(ctx);
+    x->q.yc.release();
+    x->q.ys.release();
+    x->q.mom.release();
+    for (auto& ev : ctx->ev)
+        if (ev) cudaEventDestroy(ev);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete static_cast<stoat_gpu_ctx_full*>(ctx);
+}
+
+// ---- matrix ----------------------------------------------------------------------------------------
+static int set_matrix_common(stoat_gpu_ctx* ctx, const uint8_t* bits, bool on_device, uint64_t n_rows,
+                             uint64_t n_cols) {
+    if (!ctx) return STOAT_GPU_ERR_ARG;
+    if (n_cols == 0 || (n_cols & 1)) return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix: n_cols must be even and > 0");
+    if (n_cols >= (1ull << 32) || n_rows >= 0xFFFFFFFFull)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix: dimensions exceed 32-bit row / column indices");
+    if (n_rows && !bits) return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix: bits is NULL");
+    if (on_device && (reinterpret_cast<uintptr_t>(bits) & 3))
+        return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_dev: device pointer must be 4-byte aligned");
+    CK(cudaSetDevice(ctx->device));
+    const uint64_t pitch = pitch_for(n_cols);
+    const uint64_t raw_bytes = (n_rows * n_cols + 7) / 8;
+    CK(ctx->rows.reserve(std::max<uint64_t>(n_rows * pitch, 16)));
+    ctx->timing = stoat_gpu_timing{};
+    const uint8_t* raw_dev = bits;
+    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    if (!on_device) {
+        CK(ctx->raw_stage[0].reserve(raw_bytes + 16));
+        if (raw_bytes) CK(cudaMemcpyAsync(ctx->raw_stage[0].p, bits, raw_bytes, cudaMemcpyHostToDevice, ctx->stream));
+        raw_dev = ctx->raw_stage[0].as<uint8_t>();
+    }
+    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    CK(launch_repack_rows(raw_dev, raw_bytes, 0, n_rows, n_cols, pitch, ctx->rows.as<uint8_t>(), ctx->stream));
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&ctx->timing.h2d_ms, ctx->ev[0], ctx->ev[1]));
+    CK(cudaEventElapsedTime(&ctx->timing.repack_ms, ctx->ev[1], ctx->ev[2]));
+    ctx->timing.launches = n_rows ? 1 : 0;
+    ctx->n_rows = n_rows;
+    ctx->n_cols = n_cols;
+    ctx->pitch = pitch;
+    ctx->have_matrix = true;
+    // phenotype masks depend on the pitch: they must be set again after a matrix of another width
+    if (ctx->have_binary && ctx->n_samples_binary * 2 != n_cols) ctx->have_binary = false;
+    if (ctx->have_quant && ctx->n_samples_quant * 2 != n_cols) ctx->have_quant = false;
+    ctx->have_batch = false;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_set_matrix(stoat_gpu_ctx* ctx, const uint8_t* bits, uint64_t n_rows, uint64_t n_cols) {
+    return set_matrix_common(ctx, bits, false, n_rows, n_cols);
+}
+int stoat_gpu_set_matrix_dev(stoat_gpu_ctx* ctx, const uint8_t* bits_dev, uint64_t n_rows, uint64_t n_cols) {
+    return set_matrix_common(ctx, bits_dev, true, n_rows, n_cols);
+}
+
+uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx) { return ctx ? ctx->pitch : 0; }
+uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx) { return ctx ? reinterpret_cast<uint64_t>(ctx->stream) : 0; }
+
+int stoat_gpu_read_row(stoat_gpu_ctx* ctx, uint64_t row, uint8_t* out, uint64_t out_bytes) {
+    if (!ctx || !out) return STOAT_GPU_ERR_ARG;
+    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, "read_row: no matrix");
+    if (row >= ctx->n_rows || out_bytes < ctx->pitch) return fail(ctx, STOAT_GPU_ERR_ARG, "read_row: bad row / size");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(out, ctx->rows.as<uint8_t>() + row * ctx->pitch, ctx->pitch, cudaMemcpyDeviceToHost,
+                       ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return STOAT_GPU_OK;
+}
+
+// ---- phenotypes ------------------------------------------------------------------------------------
+int stoat_gpu_set_binary_phenotype(stoat_gpu_ctx* ctx, const uint8_t* is_case, uint64_t n_samples) {
+    if (!ctx || !is_case) return fail(ctx, STOAT_GPU_ERR_ARG, "set_binary_phenotype: NULL argument");
+    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, "set_binary_phenotype: set the matrix first");
+    if (n_samples * 2 != ctx->n_cols)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "set_binary_phenotype: n_samples must be n_cols / 2");
+    CK(cudaSetDevice(ctx->device));
+    CK(ctx->is_case_dev.reserve(n_samples));
+    CK(ctx->case_mask.reserve(ctx->pitch));
+    CK(cudaMemcpyAsync(ctx->is_case_dev.p, is_case, n_samples, cudaMemcpyHostToDevice, ctx->stream));
+    CK(launch_build_case_mask(ctx->is_case_dev.as<uint8_t>(), n_samples, ctx->pitch, ctx->case_mask.as<uint8_t>(),
+                              ctx->stream));
+    uint64_t cases = 0;
+    for (uint64_t i = 0; i < n_samples; ++i) cases += is_case[i] ? 1 : 0;
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->n_case_hap = uint32_t(cases * 2);
+    ctx->n_samples_binary = n_samples;
+    ctx->have_binary = true;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, uint64_t n_samples) {
+    if (!ctx || !y) return fail(ctx, STOAT_GPU_ERR_ARG, "set_quantitative_phenotype: NULL argument");
+    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, "set_quantitative_phenotype: set the matrix first");
+    if (n_samples * 2 != ctx->n_cols)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "set_quantitative_phenotype: n_samples must be n_cols / 2");
+    CK(cudaSetDevice(ctx->device));
+    CtxExtra* x = extra_of(ctx);
+    // centring constant and the all-sample sums of the centred values (O(n), once per phenotype)
+    long double acc = 0.0L;
+    for (uint64_t i = 0; i < n_samples; ++i) acc += y[i];
+    const double mean = double(acc / (long double)n_samples);
+    long double s1 = 0.0L, s2 = 0.0L;
+    for (uint64_t i = 0; i < n_samples; ++i) {
+        const double v = y[i] - mean;
+        s1 += v;
+        s2 += (long double)v * v;
+    }
+    x->q.sy_all = double(s1);
+    x->q.syy_all = double(s2);
+    const uint32_t n_words = uint32_t(ctx->pitch / 4);
+    CK(ctx->y.reserve(n_samples * 8));
+    CK(x->q.yc.reserve(n_samples * 8));
+    CK(x->q.ys.reserve(size_t(16) * n_words * 8));
+    CK(cudaMemcpyAsync(ctx->y.p, y, n_samples * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CK(launch_centre_permute(ctx->y.as<double>(), uint32_t(n_samples), mean, n_words, x->q.yc.as<double>(),
+                             x->q.ys.as<double>(), ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->n_samples_quant = n_samples;
+    ctx->have_quant = true;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_set_covariates(stoat_gpu_ctx* ctx, const double* covar, uint64_t n_samples, uint64_t n_covar) {
+    if (!ctx) return STOAT_GPU_ERR_ARG;
+    if (n_covar == 0) {
+        ctx->n_covar = 0;
+        ctx->n_samples_covar = 0;
+        return STOAT_GPU_OK;
+    }
+    if (!covar) return fail(ctx, STOAT_GPU_ERR_ARG, "set_covariates: covar is NULL");
+    if (n_covar + 2 > STOAT_GPU_MAX_OLS_FEATURES)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "set_covariates: too many covariates for STOAT_GPU_MAX_OLS_FEATURES");
+    CK(cudaSetDevice(ctx->device));
+    CK(ctx->covar.reserve(n_samples * n_covar * 8));
+    CK(cudaMemcpyAsync(ctx->covar.p, covar, n_samples * n_covar * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->n_covar = n_covar;
+    ctx->n_samples_covar = n_samples;
+    return STOAT_GPU_OK;
+}
+
+// ---- staging of a batch ----------------------------------------------------------------------------
+int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths) {
+    if (!ctx || !paths) return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: NULL argument");
+    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, "stage_paths: set the matrix first");
+    const uint64_t S = paths->n_snarls;
+    if (S && (!paths->snarl_path_off || !paths->path_edge_off))
+        return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: offset arrays are NULL");
+    if (S >= 0xFFFFFFFFull) return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: too many snarls for one batch");
+    const uint64_t P = S ? paths->snarl_path_off[S] : 0;
+    if (S && paths->snarl_path_off[0] != 0) return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: snarl_path_off[0] != 0");
+    const uint64_t E = P ? paths->path_edge_off[P] : 0;
+    if (P && paths->path_edge_off[0] != 0) return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: path_edge_off[0] != 0");
+    if (P >= 0xFFFFFFFFull || E >= 0xFFFFFFFFull)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: more than 2^32 paths / edges in one batch");
+    if (E && !paths->edge_row) return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: edge_row is NULL");
+    for (uint64_t s = 0; s < S; ++s)
+        if (paths->snarl_path_off[s + 1] < paths->snarl_path_off[s])
+            return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: snarl_path_off is not monotone");
+    for (uint64_t p = 0; p < P; ++p)
+        if (paths->path_edge_off[p + 1] < paths->path_edge_off[p])
+            return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: path_edge_off is not monotone");
+    CK(cudaSetDevice(ctx->device));
+    CtxExtra* x = extra_of(ctx);
+    ctx->have_batch = false;
+    ctx->have_binary_counts = ctx->have_binary_result = ctx->have_quant_result = false;
+    CK(ctx->d_snarl_path_off.reserve((S + 1) * 8));
+    CK(ctx->d_path_edge_off.reserve((P + 1) * 8));
+    CK(ctx->d_edge_row.reserve(std::max<uint64_t>(E * 4, 16)));
+    CK(ctx->d_rec.reserve(std::max<uint64_t>(S * sizeof(SnarlRec), 32)));
+    const uint64_t blob_bytes = 16 * (2 * S + ((P + E) >> 4) + 2 + kMaxBlob16);
+    CK(ctx->d_blob.reserve(blob_bytes));
+    CK(ctx->d_big.reserve(std::max<uint64_t>(S * 4, 16)));
+    CK(ctx->d_counters.reserve(16));
+    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    const uint64_t zero = 0;
+    if (S) {
+        CK(cudaMemcpyAsync(ctx->d_snarl_path_off.p, paths->snarl_path_off, (S + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->d_path_edge_off.p, P ? paths->path_edge_off : &zero, (P + 1) * 8, cudaMemcpyHostToDevice,
+                           ctx->stream));
+        if (E) CK(cudaMemcpyAsync(ctx->d_edge_row.p, paths->edge_row, E * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    CK(cudaMemsetAsync(ctx->d_counters.p, 0, 16, ctx->stream));
+    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    BatchDev& b = ctx->batch;
+    b.n_snarls = S;
+    b.n_paths = P;
+    b.n_edges = E;
+    b.snarl_path_off = ctx->d_snarl_path_off.as<uint64_t>();
+    b.path_edge_off = ctx->d_path_edge_off.as<uint64_t>();
+    b.edge_row = ctx->d_edge_row.as<uint32_t>();
+    b.rec = ctx->d_rec.as<SnarlRec>();
+    b.blob = ctx->d_blob.as<uint8_t>();
+    b.big_list = ctx->d_big.as<uint32_t>();
+    b.counters = ctx->d_counters.as<uint32_t>();
+    CK(launch_binary_prep(b, ctx->n_rows, ctx->stream));
+    CK(cudaMemcpyAsync(x->counters_host, ctx->d_counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
+    ctx->timing = stoat_gpu_timing{};
+    ctx->timing.h2d_ms = ms;
+    ctx->timing.launches = S ? 1 : 0;
+    if (x->counters_host[1])
+        return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: edge_row holds a row index >= n_rows (and != MISSING_EDGE)");
+    ctx->n_big = x->counters_host[0];
+    x->max_stage_rows = x->counters_host[2];
+    ctx->have_batch = true;
+    return STOAT_GPU_OK;
+}
+
+// ---- binary ----------------------------------------------------------------------------------------
+static int binary_reserve(stoat_gpu_ctx* ctx) {
+    const BatchDev& b = ctx->batch;
+    CK(ctx->counts.reserve(std::max<uint64_t>(2 * b.n_paths * 4, 16)));
+    CK(ctx->total_sum.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
+    CK(ctx->filtered.reserve(std::max<uint64_t>(b.n_snarls, 16)));
+    CK(ctx->p_a.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
+    CK(ctx->p_b.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
+    CK(ctx->code_a.reserve(std::max<uint64_t>(b.n_snarls, 16)));
+    CK(ctx->code_b.reserve(std::max<uint64_t>(b.n_snarls, 16)));
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_binary_counts_staged(stoat_gpu_ctx* ctx) {
+    if (!ctx) return STOAT_GPU_ERR_ARG;
+    if (!ctx->have_batch) return fail(ctx, STOAT_GPU_ERR_STATE, "binary: no staged batch");
+    if (!ctx->have_binary) return fail(ctx, STOAT_GPU_ERR_STATE, "binary: no binary phenotype");
+    CK(cudaSetDevice(ctx->device));
+    int rc = binary_reserve(ctx);
+    if (rc) return rc;
+    CtxExtra* x = extra_of(ctx);
+    ctx->timing.launches = 0;
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    CK(launch_path_and_popc(matrix_view(ctx), ctx->case_mask.as<uint8_t>(), ctx->n_case_hap, ctx->batch, ctx->n_big,
+                            x->max_stage_rows, ctx->counts.as<uint32_t>(), ctx->num_sms, ctx->k1_variant, ctx->stream,
+                            &ctx->timing.launches));
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    ctx->have_binary_counts = true;
+    ctx->have_binary_result = false;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_binary_counts_dev(stoat_gpu_ctx* ctx, uint32_t** counts_dev, uint64_t* n_words) {
+    if (!ctx || !counts_dev || !n_words) return STOAT_GPU_ERR_ARG;
+    if (!ctx->have_binary_counts) return fail(ctx, STOAT_GPU_ERR_STATE, "binary_counts_dev: run the count pass first");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));  // the caller's collective runs on its own stream
+    *counts_dev = ctx->counts.as<uint32_t>();
+    *n_words = 2 * ctx->batch.n_paths;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_binary_stats_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr) {
+    if (!ctx || !thr) return fail(ctx, STOAT_GPU_ERR_ARG, "binary_stats: NULL argument");
+    if (!ctx->have_binary_counts) return fail(ctx, STOAT_GPU_ERR_STATE, "binary_stats: run the count pass first");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaEventRecord(ctx->ev[4], ctx->stream));
+    CK(launch_binary_stats(ctx->batch, ctx->counts.as<uint32_t>(), *thr, ctx->total_sum.as<uint64_t>(),
+                           ctx->filtered.as<uint8_t>(), ctx->p_a.as<double>(), ctx->p_b.as<double>(),
+                           ctx->code_a.as<uint8_t>(), ctx->code_b.as<uint8_t>(), ctx->stream));
+    CK(cudaEventRecord(ctx->ev[5], ctx->stream));
+    if (ctx->batch.n_snarls) ctx->timing.launches += 1;
+    ctx->have_binary_result = true;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_binary_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr) {
+    int rc = stoat_gpu_binary_counts_staged(ctx);
+    if (rc) return rc;
+    rc = stoat_gpu_binary_stats_staged(ctx, thr);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));
+    CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ctx->ev[4], ctx->ev[5]));
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_binary_fetch(stoat_gpu_ctx* ctx, stoat_gpu_binary_out* out) {
+    if (!ctx || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "binary_fetch: NULL argument");
+    if (!ctx->have_binary_result) return fail(ctx, STOAT_GPU_ERR_STATE, "binary_fetch: nothing to fetch");
+    CK(cudaSetDevice(ctx->device));
+    const uint64_t S = ctx->batch.n_snarls, P = ctx->batch.n_paths;
+    CK(cudaEventRecord(ctx->ev[6], ctx->stream));
+    const cudaMemcpyKind k = cudaMemcpyDeviceToHost;
+    if (P && out->g0) CK(cudaMemcpyAsync(out->g0, ctx->counts.as<uint32_t>(), P * 4, k, ctx->stream));
+    if (P && out->g1) CK(cudaMemcpyAsync(out->g1, ctx->counts.as<uint32_t>() + P, P * 4, k, ctx->stream));
+    if (S && out->total_sum) CK(cudaMemcpyAsync(out->total_sum, ctx->total_sum.p, S * 8, k, ctx->stream));
+    if (S && out->filtered) CK(cudaMemcpyAsync(out->filtered, ctx->filtered.p, S, k, ctx->stream));
+    if (S && out->p_chi2) CK(cudaMemcpyAsync(out->p_chi2, ctx->p_a.p, S * 8, k, ctx->stream));
+    if (S && out->p_fisher) CK(cudaMemcpyAsync(out->p_fisher, ctx->p_b.p, S * 8, k, ctx->stream));
+    if (S && out->chi2_code) CK(cudaMemcpyAsync(out->chi2_code, ctx->code_a.p, S, k, ctx->stream));
+    if (S && out->fisher_code) CK(cudaMemcpyAsync(out->fisher_code, ctx->code_b.p, S, k, ctx->stream));
+    CK(cudaEventRecord(ctx->ev[7], ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&ctx->timing.d2h_ms, ctx->ev[6], ctx->ev[7]));
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_binary_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const stoat_gpu_thresholds* thr,
+                           stoat_gpu_binary_out* out) {
+    if (!ctx || !paths || !thr || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "binary_batch: NULL argument");
+    int rc = stoat_gpu_stage_paths(ctx, paths);
+    if (rc) return rc;
+    const float h2d = ctx->timing.h2d_ms;
+    rc = stoat_gpu_binary_run_staged(ctx, thr);
+    if (rc) return rc;
+    rc = stoat_gpu_binary_fetch(ctx, out);
+    ctx->timing.h2d_ms = h2d;
+    if (ctx->batch.n_snarls) ctx->timing.launches += 1;  // prep
+    return rc;
+}
+
+// ---- quantitative ----------------------------------------------------------------------------------
+static int quant_reserve(stoat_gpu_ctx* ctx) {
+    const BatchDev& b = ctx->batch;
+    CtxExtra* x = extra_of(ctx);
+    CK(ctx->q_allele.reserve(std::max<uint64_t>(b.n_paths * 4, 16)));
+    CK(ctx->filtered.reserve(std::max<uint64_t>(b.n_snarls, 16)));
+    CK(ctx->q_nused.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
+    CK(ctx->q_p.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
+    CK(ctx->q_r2.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
+    CK(ctx->q_beta.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
+    CK(ctx->q_se.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
+    CK(ctx->q_code.reserve(std::max<uint64_t>(b.n_snarls, 16)));
+    CK(x->q.mom.reserve(std::max<size_t>(quant_moments_bytes(b.n_snarls), 16)));
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr) {
+    if (!ctx || !thr) return fail(ctx, STOAT_GPU_ERR_ARG, "quantitative: NULL argument");
+    if (!ctx->have_batch) return fail(ctx, STOAT_GPU_ERR_STATE, "quantitative: no staged batch");
+    if (!ctx->have_quant) return fail(ctx, STOAT_GPU_ERR_STATE, "quantitative: no quantitative phenotype");
+    if (ctx->n_covar && ctx->n_samples_covar * 2 < ctx->n_cols)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "quantitative: fewer covariate rows than samples");
+    CK(cudaSetDevice(ctx->device));
+    int rc = quant_reserve(ctx);
+    if (rc) return rc;
+    CtxExtra* x = extra_of(ctx);
+    const uint64_t S = ctx->batch.n_snarls;
+    // the general-path list grows during the run: reset its length to what prep put there
+    x->counters_host[0] = ctx->n_big;
+    CK(cudaMemcpyAsync(ctx->d_counters.p, x->counters_host, 4, cudaMemcpyHostToDevice, ctx->stream));
+    // filtered snarls keep NaN / NA outputs
+    if (S) {
+        CK(cudaMemsetAsync(ctx->q_p.p, 0xFF, S * 8, ctx->stream));
+        CK(cudaMemsetAsync(ctx->q_r2.p, 0xFF, S * 8, ctx->stream));
+        CK(cudaMemsetAsync(ctx->q_beta.p, 0xFF, S * 8, ctx->stream));
+        CK(cudaMemsetAsync(ctx->q_se.p, 0xFF, S * 8, ctx->stream));
+        CK(cudaMemsetAsync(ctx->q_code.p, STOAT_P_NA, S, ctx->stream));
+    }
+    QuantOut out{ctx->q_allele.as<uint32_t>(), ctx->filtered.as<uint8_t>(), ctx->q_nused.as<uint32_t>(),
+                 ctx->q_p.as<double>(),        ctx->q_r2.as<double>(),      ctx->q_beta.as<double>(),
+                 ctx->q_se.as<double>(),       ctx->q_code.as<uint8_t>()};
+    ctx->timing.launches = 0;
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    CK(launch_quantitative_impl(matrix_view(ctx), x->q.yc.as<double>(), x->q.ys.as<double>(), x->q.sy_all,
+                                x->q.syy_all, ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar),
+                                ctx->batch, x->max_stage_rows, *thr, out,
+                                reinterpret_cast<QuantMoments*>(x->q.mom.p), ctx->num_sms, ctx->k1_variant,
+                                ctx->stream, &ctx->timing.launches));
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));
+    ctx->timing.stats_ms = 0.f;
+    ctx->have_quant_result = true;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_quantitative_fetch(stoat_gpu_ctx* ctx, stoat_gpu_quant_out* out) {
+    if (!ctx || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "quantitative_fetch: NULL argument");
+    if (!ctx->have_quant_result) return fail(ctx, STOAT_GPU_ERR_STATE, "quantitative_fetch: nothing to fetch");
+    CK(cudaSetDevice(ctx->device));
+    const uint64_t S = ctx->batch.n_snarls, P = ctx->batch.n_paths;
+    const cudaMemcpyKind k = cudaMemcpyDeviceToHost;
+    CK(cudaEventRecord(ctx->ev[6], ctx->stream));
+    if (P && out->allele_paths) CK(cudaMemcpyAsync(out->allele_paths, ctx->q_allele.p, P * 4, k, ctx->stream));
+    if (S && out->filtered) CK(cudaMemcpyAsync(out->filtered, ctx->filtered.p, S, k, ctx->stream));
+    if (S && out->n_used) CK(cudaMemcpyAsync(out->n_used, ctx->q_nused.p, S * 4, k, ctx->stream));
+    if (S && out->p_value) CK(cudaMemcpyAsync(out->p_value, ctx->q_p.p, S * 8, k, ctx->stream));
+    if (S && out->r2) CK(cudaMemcpyAsync(out->r2, ctx->q_r2.p, S * 8, k, ctx->stream));
+    if (S && out->beta) CK(cudaMemcpyAsync(out->beta, ctx->q_beta.p, S * 8, k, ctx->stream));
+    if (S && out->se) CK(cudaMemcpyAsync(out->se, ctx->q_se.p, S * 8, k, ctx->stream));
+    if (S && out->code) CK(cudaMemcpyAsync(out->code, ctx->q_code.p, S, k, ctx->stream));
+    CK(cudaEventRecord(ctx->ev[7], ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&ctx->timing.d2h_ms, ctx->ev[6], ctx->ev[7]));
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_quantitative_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const stoat_gpu_thresholds* thr,
+                                 stoat_gpu_quant_out* out) {
+    if (!ctx || !paths || !thr || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "quantitative_batch: NULL argument");
+    int rc = stoat_gpu_stage_paths(ctx, paths);
+    if (rc) return rc;
+    const float h2d = ctx->timing.h2d_ms;
+    rc = stoat_gpu_quantitative_run_staged(ctx, thr);
+    if (rc) return rc;
+    rc = stoat_gpu_quantitative_fetch(ctx, out);
+    ctx->timing.h2d_ms = h2d;
+    if (ctx->batch.n_snarls) ctx->timing.launches += 1;  // prep
+    return rc;
+}
+
+// ---- eQTL ------------------------------------------------------------------------------------------
+int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths*, const stoat_gpu_eqtl_genes*,
+                         const stoat_gpu_thresholds*, stoat_gpu_eqtl_out*) {
+    return fail(ctx, STOAT_GPU_ERR_STATE, "eqtl_batch: not built yet in this revision");
+}
+int stoat_gpu_eqtl_dense_summary(stoat_gpu_ctx* ctx, const stoat_gpu_paths*, const stoat_gpu_eqtl_genes*,
+                                 const stoat_gpu_thresholds*, double, stoat_gpu_eqtl_summary*) {
+    return fail(ctx, STOAT_GPU_ERR_STATE, "eqtl_dense_summary: not built yet in this revision");
+}
+
+// set_precision (src/utils.cpp:5-15): iostream scientific / defaultfloat at precision 4 are "%.4e" / "%.4g"
+int stoat_gpu_format_value(double value, uint8_t code, char* buf, size_t buf_len) {
+    if (!buf || buf_len == 0) return -1;
+    int n;
+    switch (code) {
+        case STOAT_P_NA: n = std::snprintf(buf, buf_len, "NA"); break;
+        case STOAT_P_ZERO: n = std::snprintf(buf, buf_len, "0"); break;
+        case STOAT_P_ONE: n = std::snprintf(buf, buf_len, "1"); break;
+        case STOAT_P_DBLMAX: n = std::snprintf(buf, buf_len, "%.4g", 1.7976931348623157e308); break;
+        default:
+            if (std::fabs(value) < 1e-1 && value != 0.0)
+                n = std::snprintf(buf, buf_len, "%.4e", value);
+            else
+                n = std::snprintf(buf, buf_len, "%.4g", value);
+    }
+    return (n < 0 || size_t(n) >= buf_len) ? -1 : n;
+}
+
+int stoat_gpu_last_timing(const stoat_gpu_ctx* ctx, stoat_gpu_timing* out) {
+    if (!ctx || !out) return STOAT_GPU_ERR_ARG;
+    *out = ctx->timing;
+    return STOAT_GPU_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,145 @@
+// ctx.hpp — the context behind the C ABI (include/stoat_gpu.h) and the launch interfaces of the
+// kernel translation units.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <cuda_runtime.h>
+
+#include "../../include/stoat_gpu.h"
+
+namespace stoat {
+
+// ---- device buffer that only grows --------------------------------------------------------------
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        // grow geometrically a little so repeated batches of similar size do not realloc
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) {
+            e = cudaMalloc(&p, bytes);
+            want = bytes;
+        }
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <typename T>
+    T* as() const {
+        return static_cast<T*>(p);
+    }
+};
+
+// Per-snarl record produced by the prep kernel and consumed by the TMA producer warp (32 bytes,
+// one coalesced 2 x 16-byte load).  rows[] are the snarl's distinct matrix rows.
+constexpr int kMaxStageRows = 6;  // distinct rows a snarl may have on the TMA path (else: LDG path)
+struct __align__(32) SnarlRec {
+    uint32_t rows[kMaxStageRows];  // distinct rows (global row index)
+    uint32_t blob16;               // offset of the path program in the blob array, 16-byte units
+    uint8_t n_rows;                // number of distinct rows (0 when the snarl is on the LDG path)
+    uint8_t blob_len16;            // path-program length in 16-byte units (>= 1)
+    uint16_t n_paths;
+};
+static_assert(sizeof(SnarlRec) == 32, "SnarlRec must be 32 bytes");
+
+constexpr int kMaxBlob16 = 4;  // path programs longer than 64 bytes go to the LDG path
+
+// device view of a staged batch
+struct BatchDev {
+    uint64_t n_snarls = 0, n_paths = 0, n_edges = 0;
+    const uint64_t* snarl_path_off = nullptr;
+    const uint64_t* path_edge_off = nullptr;
+    const uint32_t* edge_row = nullptr;
+    SnarlRec* rec = nullptr;
+    uint8_t* blob = nullptr;      // path programs, see kernels_binary.cu
+    uint32_t* big_list = nullptr;  // snarls that take the LDG path
+    uint32_t* counters = nullptr;  // [0] = number of big snarls, [1] = error flag, [2] = widest stage (rows)
+};
+
+struct MatrixDev {
+    const uint8_t* rows = nullptr;  // repacked, row pitch bytes each, padding bits zero
+    uint64_t n_rows = 0, n_cols = 0, pitch = 0;
+};
+
+// ---- kernel launchers (defined in the kernels_*.cu files) ---------------------------------------
+// K0
+cudaError_t launch_repack_rows(const uint8_t* raw, uint64_t raw_bytes, uint64_t row_begin, uint64_t row_end,
+                               uint64_t n_cols, uint64_t pitch, uint8_t* out, cudaStream_t st);
+cudaError_t launch_build_case_mask(const uint8_t* is_case, uint64_t n_samples, uint64_t pitch, uint8_t* mask,
+                                   cudaStream_t st);
+// binary
+cudaError_t launch_binary_prep(const BatchDev& b, uint64_t n_matrix_rows, cudaStream_t st);
+cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, uint32_t n_case_hap, const BatchDev& b,
+                                 uint32_t n_big, uint32_t max_stage_rows, uint32_t* counts, int num_sms, int variant,
+                                 cudaStream_t st, uint32_t* launches);
+cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const stoat_gpu_thresholds& thr,
+                                uint64_t* total_sum, uint8_t* filtered, double* p_chi2, double* p_fisher,
+                                uint8_t* chi2_code, uint8_t* fisher_code, cudaStream_t st);
+// quantitative
+struct QuantMoments;  // kernels_quant.cu
+struct QuantOut {
+    uint32_t* allele_paths;
+    uint8_t* filtered;
+    uint32_t* n_used;
+    double* p;
+    double* r2;
+    double* beta;
+    double* se;
+    uint8_t* code;
+};
+cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_centred, const double* ys_perm,
+                                     double sy_all, double syy_all, const double* covar, uint32_t n_covar,
+                                     const BatchDev& b, uint32_t max_stage_rows, const stoat_gpu_thresholds& thr,
+                                     QuantOut out, QuantMoments* mom, int num_sms, int variant, cudaStream_t st,
+                                     uint32_t* launches);
+cudaError_t launch_centre_permute(const double* y, uint32_t n, double mean, uint32_t n_words, double* yc, double* ys,
+                                  cudaStream_t st);
+size_t quant_moments_bytes(uint64_t n_snarls);
+
+}  // namespace stoat
+
+// ---- the context ----------------------------------------------------------------------------------
+struct stoat_gpu_ctx {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev[8] = {};
+    cudaEvent_t chunk_ev[2] = {};
+    std::string err;
+    stoat_gpu_timing timing = {};
+    int k1_variant = 0;  // 0 = TMA pipeline (default), 1 = LDG only (STOAT_GPU_K1=ldg)
+
+    // matrix
+    stoat::DevBuf rows;        // repacked
+    stoat::DevBuf raw_stage[2];  // upload staging (chunked H2D of the reference-layout bytes)
+    uint64_t n_rows = 0, n_cols = 0, pitch = 0;
+    bool have_matrix = false;
+
+    // phenotypes
+    stoat::DevBuf case_mask, is_case_dev, y, covar;
+    uint64_t n_samples_binary = 0, n_samples_quant = 0, n_samples_covar = 0, n_covar = 0;
+    uint32_t n_case_hap = 0;
+    bool have_binary = false, have_quant = false;
+
+    // staged batch
+    stoat::DevBuf d_snarl_path_off, d_path_edge_off, d_edge_row, d_rec, d_blob, d_big, d_counters;
+    stoat::BatchDev batch;
+    uint32_t n_big = 0;
+    bool have_batch = false;
+
+    // results (device)
+    stoat::DevBuf counts, total_sum, filtered, p_a, p_b, code_a, code_b;  // binary
+    stoat::DevBuf q_allele, q_nused, q_p, q_r2, q_beta, q_se, q_code;      // quantitative
+    bool have_binary_counts = false, have_binary_result = false, have_quant_result = false;
+};

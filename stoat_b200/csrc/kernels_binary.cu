@@ -1,0 +1,455 @@
+// kernels_binary.cu — the binary-trait hot path on sm_100a.
+//
+//   prep            per snarl: distinct rows + a compact "path program" (which of the snarl's rows each
+//                   path ANDs), so that K1 touches every matrix row of a snarl exactly once.
+//   K1 path_and_popc  identify_path (src/snarl_analyzer.cpp:315-356) + create_binary_table
+//                   (src/binary_table.cpp:19-44): per path AND over its rows, popcount split by the
+//                   case mask.  HBM-bound.  Rows are staged into shared memory by TMA bulk copies
+//                   (cp.async.bulk + mbarrier), each warp running its own multi-stage pipeline.
+//   K1' (LDG)       same arithmetic straight from global memory for snarls that do not fit a stage
+//                   (many distinct rows / long path programs).
+//   K2 binary_stats remove_empty_columns_binary_table + filtration_binary_table
+//                   (src/snarl_analyzer.cpp:686-732) + FisherKhi2::fisher_khi2
+//                   (src/stats_test.cpp:181-380), one thread per snarl, FP64.
+//
+// Path program ("blob") of a snarl, bytes:  [np] [3 reserved] [first path index, u32] [code_0 ..
+// code_{np-1}] [locals of path 0] [locals of path 1] ...   code = 0xFF: an edge of the path is missing from the matrix => nobody matches
+// (:334-336); code = 0: no checked edge => every haplotype matches (:343-354); else the number of
+// checked edges R, followed (in the locals area) by R indices into the snarl's distinct-row list.
+#include "ctx.hpp"
+#include "device_math.cuh"
+#include "ptx.cuh"
+
+namespace stoat {
+
+constexpr uint32_t kMissing = 0xFFFFFFFFu;
+constexpr int kBlobBytes = kMaxBlob16 * 16;
+constexpr uint32_t kBlobHeader = 8;
+
+// =================================================================================================
+// prep
+// =================================================================================================
+__global__ void __launch_bounds__(128) binary_prep_kernel(BatchDev b, uint64_t n_matrix_rows) {
+    const uint64_t s = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (s >= b.n_snarls) return;
+    const uint64_t p0 = b.snarl_path_off[s], p1 = b.snarl_path_off[s + 1];
+    const uint64_t e0 = b.path_edge_off[p0], e1 = b.path_edge_off[p1];
+    const uint64_t np = p1 - p0, ne = e1 - e0;
+    const uint64_t base16 = 2 * s + ((p0 + e0) >> 4);  // room: 2 + floor((np+ne)/16) >= ceil((8+np+ne)/16)
+
+    SnarlRec rec;
+    for (int k = 0; k < kMaxStageRows; ++k) rec.rows[k] = 0;
+    rec.blob16 = uint32_t(base16);
+    rec.n_rows = 0;
+    rec.blob_len16 = 1;
+    rec.n_paths = 0;
+
+    bool big = (np > 250) || (kBlobHeader + np + ne > uint64_t(kBlobBytes));
+    uint32_t urows[kMaxStageRows];
+    int nu = 0;
+    // distinct rows (and validation of the row indices)
+    for (uint64_t e = e0; e < e1; ++e) {
+        const uint32_t r = b.edge_row[e];
+        if (r == kMissing) continue;
+        if (uint64_t(r) >= n_matrix_rows) {
+            atomicExch(&b.counters[1], 1u);  // invalid row index: reported by the ABI call
+            big = true;
+            continue;
+        }
+        if (big) continue;
+        int f = -1;
+        for (int k = 0; k < nu; ++k)
+            if (urows[k] == r) f = k;
+        if (f < 0) {
+            if (nu == kMaxStageRows)
+                big = true;
+            else
+                urows[nu++] = r;
+        }
+    }
+    uint8_t* blob = b.blob + base16 * 16;
+    if (big) {
+        blob[0] = 0;  // "nothing to do here" for the TMA kernel
+        const uint32_t slot = atomicAdd(&b.counters[0], 1u);
+        b.big_list[slot] = uint32_t(s);
+        b.rec[s] = rec;
+        return;
+    }
+    blob[0] = uint8_t(np);
+    blob[1] = blob[2] = blob[3] = 0;
+    *reinterpret_cast<uint32_t*>(blob + 4) = uint32_t(p0);
+    uint32_t off = kBlobHeader + uint32_t(np);
+    for (uint64_t j = 0; j < np; ++j) {
+        const uint64_t a = b.path_edge_off[p0 + j], z = b.path_edge_off[p0 + j + 1];
+        bool missing = false;
+        for (uint64_t e = a; e < z; ++e) missing |= (b.edge_row[e] == kMissing);
+        if (missing) {
+            blob[kBlobHeader + j] = 0xFF;
+            continue;
+        }
+        blob[kBlobHeader + j] = uint8_t(z - a);
+        for (uint64_t e = a; e < z; ++e) {
+            const uint32_t r = b.edge_row[e];
+            int f = 0;
+            for (int k = 0; k < nu; ++k)
+                if (urows[k] == r) f = k;
+            blob[off++] = uint8_t(f);
+        }
+    }
+    for (int k = 0; k < nu; ++k) rec.rows[k] = urows[k];
+    rec.n_rows = uint8_t(nu);
+    rec.blob_len16 = uint8_t((off + 15) / 16);
+    rec.n_paths = uint16_t(np);
+    atomicMax(&b.counters[2], uint32_t(nu));  // widest stage needed
+    b.rec[s] = rec;
+}
+
+cudaError_t launch_binary_prep(const BatchDev& b, uint64_t n_matrix_rows, cudaStream_t st) {
+    if (b.n_snarls == 0) return cudaSuccess;
+    const unsigned blocks = unsigned((b.n_snarls + 127) / 128);
+    binary_prep_kernel<<<blocks, 128, 0, st>>>(b, n_matrix_rows);
+    return cudaGetLastError();
+}
+
+// =================================================================================================
+// K1: TMA-staged AND + popcount
+// =================================================================================================
+struct K1Params {
+    const uint8_t* rows;       // repacked matrix
+    const uint8_t* case_mask;  // pitch bytes
+    const SnarlRec* rec;
+    const uint8_t* blob;
+    uint32_t* g0;  // [P]
+    uint32_t* g1;  // [P]
+    uint64_t n_snarls;
+    uint32_t pitch;        // bytes per row
+    uint32_t n_hap;        // n_cols
+    uint32_t n_case_hap;   // popcount of the case mask
+    uint32_t stage_rows;   // row slots per stage
+    uint32_t n_stages;     // pipeline depth per warp
+};
+
+// AND of R staged rows over the 16-byte chunks owned by this lane, popcounts split by case mask
+template <int R>
+__device__ __forceinline__ void and_popc_rows(const uint8_t* const* rp, const uint8_t* mask, uint32_t chunks,
+                                              uint32_t lane, uint32_t& n_all, uint32_t& n_case) {
+#pragma unroll 2
+    for (uint32_t c = lane; c < chunks; c += 32) {
+        uint4 v = *reinterpret_cast<const uint4*>(rp[0] + c * 16);
+#pragma unroll
+        for (int r = 1; r < R; ++r) v = and4(v, *reinterpret_cast<const uint4*>(rp[r] + c * 16));
+        const uint4 m = *reinterpret_cast<const uint4*>(mask + c * 16);
+        n_all += popc4(v);
+        n_case += popc4(and4(v, m));
+    }
+}
+
+__global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Params p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const uint32_t n_warps = blockDim.x >> 5;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t stage_bytes = kBlobBytes + p.stage_rows * p.pitch;
+    // layout: [full barriers: n_warps * n_stages * 8][pad to 128][case mask: pitch][pad to 128][stages]
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+    const uint32_t bar_bytes = (n_warps * p.n_stages * 8 + 127) & ~127u;
+    uint8_t* mask_s = smem + bar_bytes;
+    const uint32_t mask_bytes = (p.pitch + 127) & ~127u;
+    uint8_t* stages = mask_s + mask_bytes;
+
+    if (threadIdx.x == 0) {
+        for (uint32_t i = 0; i < n_warps * p.n_stages; ++i) mbar_init(&full[i], 1);
+        mbar_fence_init();
+    }
+    for (uint32_t i = threadIdx.x; i < p.pitch / 16; i += blockDim.x)
+        reinterpret_cast<uint4*>(mask_s)[i] = __ldg(reinterpret_cast<const uint4*>(p.case_mask) + i);
+    __syncthreads();
+
+    const uint64_t gw = uint64_t(blockIdx.x) * n_warps + warp;  // adjacent warps take adjacent snarls
+    const uint64_t stride = uint64_t(gridDim.x) * n_warps;
+    uint64_t* my_full = full + warp * p.n_stages;
+    uint8_t* my_stages = stages + size_t(warp) * p.n_stages * stage_bytes;
+    const uint32_t chunks = p.pitch / 16;
+    const uint64_t policy = make_evict_first_policy();
+
+    // issue the TMA bulk copies of one snarl into one stage (lane 0 only)
+    auto issue = [&](const SnarlRec& r, uint32_t stage) {
+        uint8_t* dst = my_stages + size_t(stage) * stage_bytes;
+        const uint32_t blob_bytes = uint32_t(r.blob_len16) * 16;
+        mbar_arrive_expect_tx(&my_full[stage], blob_bytes + uint32_t(r.n_rows) * p.pitch);
+        tma_bulk_g2s(dst, p.blob + size_t(r.blob16) * 16, blob_bytes, &my_full[stage]);
+        for (uint32_t k = 0; k < r.n_rows; ++k)
+            tma_bulk_g2s_hint(dst + kBlobBytes + k * p.pitch, p.rows + size_t(r.rows[k]) * p.pitch, p.pitch,
+                              &my_full[stage], policy);
+    };
+
+    // prologue: fill the pipeline
+    if (lane == 0) {
+        uint64_t s = gw;
+        for (uint32_t st = 0; st < p.n_stages && s < p.n_snarls; ++st, s += stride) issue(p.rec[s], st);
+    }
+    __syncwarp();
+
+    uint32_t it = 0;
+    for (uint64_t s = gw; s < p.n_snarls; s += stride, ++it) {
+        const uint32_t stage = it % p.n_stages;
+        const uint32_t parity = (it / p.n_stages) & 1u;
+        // record of the snarl that will refill this stage: fetched now, needed after the compute
+        const uint64_t s_next = s + uint64_t(p.n_stages) * stride;
+        SnarlRec next_rec;
+        if (lane == 0 && s_next < p.n_snarls) next_rec = p.rec[s_next];
+        mbar_wait(&my_full[stage], parity);
+        const uint8_t* blob = my_stages + size_t(stage) * stage_bytes;
+        const uint8_t* rows_s = blob + kBlobBytes;
+        const uint32_t np = blob[0];
+        if (np) {
+            const uint32_t p0 = *reinterpret_cast<const uint32_t*>(blob + 4);
+            uint32_t off = kBlobHeader + np;
+            for (uint32_t j = 0; j < np; ++j) {
+                const uint32_t code = blob[kBlobHeader + j];
+                uint32_t n_all = 0, n_case = 0;
+                if (code == 0xFF) {
+                    // missing edge: nobody
+                } else if (code == 0) {
+                    n_all = p.n_hap;  // every haplotype (only lane 0's value is written)
+                    n_case = p.n_case_hap;
+                } else {
+                    const uint8_t* rp[4];
+                    if (code <= 4) {
+#pragma unroll
+                        for (int r = 0; r < 4; ++r)
+                            rp[r] = rows_s + uint32_t(blob[off + (r < int(code) ? r : 0)]) * p.pitch;
+                        switch (code) {
+                            case 1: and_popc_rows<1>(rp, mask_s, chunks, lane, n_all, n_case); break;
+                            case 2: and_popc_rows<2>(rp, mask_s, chunks, lane, n_all, n_case); break;
+                            case 3: and_popc_rows<3>(rp, mask_s, chunks, lane, n_all, n_case); break;
+                            default: and_popc_rows<4>(rp, mask_s, chunks, lane, n_all, n_case); break;
+                        }
+                    } else {
+                        for (uint32_t c = lane; c < chunks; c += 32) {
+                            uint4 v = *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[off]) * p.pitch + c * 16);
+                            for (uint32_t r = 1; r < code; ++r)
+                                v = and4(v, *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[off + r]) * p.pitch +
+                                                                            c * 16));
+                            const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
+                            n_all += popc4(v);
+                            n_case += popc4(and4(v, m));
+                        }
+                    }
+                    off += code;
+                    n_all = __reduce_add_sync(0xffffffffu, n_all);
+                    n_case = __reduce_add_sync(0xffffffffu, n_case);
+                }
+                if (lane == 0) {
+                    p.g0[p0 + j] = n_all - n_case;  // controls  (binary_table.cpp:37-39)
+                    p.g1[p0 + j] = n_case;          // cases     (binary_table.cpp:35-36)
+                }
+            }
+        }
+        // all lanes are done reading this stage: refill it with the snarl n_stages ahead
+        __syncwarp();
+        if (lane == 0 && s_next < p.n_snarls) {
+            fence_proxy_async_smem();
+            issue(next_rec, stage);
+        }
+    }
+}
+
+// =================================================================================================
+// K1': straight from global memory (one warp per listed snarl)
+// =================================================================================================
+__global__ void __launch_bounds__(256) path_and_popc_ldg_kernel(const uint8_t* __restrict__ rows,
+                                                                const uint8_t* __restrict__ case_mask, uint32_t pitch,
+                                                                uint32_t n_hap, uint32_t n_case_hap, BatchDev b,
+                                                                const uint32_t* __restrict__ list, uint64_t n_list,
+                                                                uint32_t* __restrict__ g0, uint32_t* __restrict__ g1) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t warp = (uint64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const uint64_t n_warps = (uint64_t(gridDim.x) * blockDim.x) >> 5;
+    const uint32_t chunks = pitch / 16;
+    for (uint64_t i = warp; i < n_list; i += n_warps) {
+        const uint64_t s = list ? list[i] : i;
+        const uint64_t p0 = b.snarl_path_off[s], p1 = b.snarl_path_off[s + 1];
+        for (uint64_t pth = p0; pth < p1; ++pth) {
+            const uint64_t a = b.path_edge_off[pth], z = b.path_edge_off[pth + 1];
+            bool missing = false;
+            for (uint64_t e = a; e < z; ++e) missing |= (b.edge_row[e] == kMissing);
+            uint32_t n_all = 0, n_case = 0;
+            if (missing) {
+            } else if (z == a) {
+                n_all = n_hap;
+                n_case = n_case_hap;
+            } else {
+                for (uint32_t c = lane; c < chunks; c += 32) {
+                    uint4 v = ldg_stream(reinterpret_cast<const uint4*>(rows + size_t(b.edge_row[a]) * pitch) + c);
+                    for (uint64_t e = a + 1; e < z; ++e)
+                        v = and4(v, ldg_stream(reinterpret_cast<const uint4*>(rows + size_t(b.edge_row[e]) * pitch) + c));
+                    const uint4 m = __ldg(reinterpret_cast<const uint4*>(case_mask) + c);
+                    n_all += popc4(v);
+                    n_case += popc4(and4(v, m));
+                }
+                n_all = __reduce_add_sync(0xffffffffu, n_all);
+                n_case = __reduce_add_sync(0xffffffffu, n_case);
+            }
+            if (lane == 0) {
+                g0[pth] = n_all - n_case;
+                g1[pth] = n_case;
+            }
+        }
+    }
+}
+
+// configuration of the TMA kernel for a given pitch / stage width; returns false if a single stage
+// does not fit shared memory (then everything takes the LDG path)
+struct K1Config {
+    uint32_t n_warps, n_stages, stage_rows, smem_bytes;
+};
+static bool choose_k1_config(uint32_t pitch, uint32_t stage_rows, K1Config& cfg) {
+    const uint32_t budget = 200 * 1024;
+    if (stage_rows == 0) stage_rows = 1;
+    const uint32_t stage_bytes = kBlobBytes + stage_rows * pitch;
+    const uint32_t mask_bytes = (pitch + 127) & ~127u;
+    if (mask_bytes + 2 * stage_bytes + 1024 > budget) return false;
+    const uint32_t total_stages = (budget - mask_bytes - 1024) / stage_bytes;
+    uint32_t n_stages = 3;
+    if (total_stages < 3 * 4) n_stages = 2;   // few stages: prefer more warps over depth
+    uint32_t n_warps = total_stages / n_stages;
+    if (n_warps > 16) {
+        n_warps = 16;
+        n_stages = total_stages / 16;
+        if (n_stages > 4) n_stages = 4;
+    }
+    if (n_warps == 0) return false;
+    cfg.n_warps = n_warps;
+    cfg.n_stages = n_stages;
+    cfg.stage_rows = stage_rows;
+    const uint32_t bar_bytes = (n_warps * n_stages * 8 + 127) & ~127u;
+    cfg.smem_bytes = bar_bytes + mask_bytes + n_warps * n_stages * stage_bytes;
+    return true;
+}
+
+cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, uint32_t n_case_hap,
+                                     const BatchDev& b, uint32_t n_big, uint32_t max_stage_rows, uint32_t* counts,
+                                     int num_sms, int variant, cudaStream_t st, uint32_t* launches) {
+    if (b.n_snarls == 0) return cudaSuccess;
+    uint32_t* g0 = counts;
+    uint32_t* g1 = counts + b.n_paths;
+    const uint32_t pitch = uint32_t(m.pitch);
+    K1Config cfg{};
+    const bool use_tma = (variant == 0) && choose_k1_config(pitch, max_stage_rows, cfg) && (n_big < b.n_snarls);
+    if (use_tma) {
+        K1Params p{};
+        p.rows = m.rows;
+        p.case_mask = case_mask;
+        p.rec = b.rec;
+        p.blob = b.blob;
+        p.g0 = g0;
+        p.g1 = g1;
+        p.n_snarls = b.n_snarls;
+        p.pitch = pitch;
+        p.n_hap = uint32_t(m.n_cols);
+        p.n_case_hap = n_case_hap;
+        p.stage_rows = cfg.stage_rows;
+        p.n_stages = cfg.n_stages;
+        cudaError_t e = cudaFuncSetAttribute(path_and_popc_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             int(cfg.smem_bytes));
+        if (e != cudaSuccess) return e;
+        uint64_t want = (b.n_snarls + cfg.n_warps - 1) / cfg.n_warps;
+        const unsigned grid = unsigned(want < uint64_t(num_sms) ? want : uint64_t(num_sms));
+        path_and_popc_tma_kernel<<<grid, cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        if (launches) ++*launches;
+        if (n_big) {
+            const unsigned blocks = unsigned(n_big < 148u * 8 ? (n_big + 7) / 8 : 148u * 8);
+            path_and_popc_ldg_kernel<<<blocks, 256, 0, st>>>(m.rows, case_mask, pitch, uint32_t(m.n_cols), n_case_hap,
+                                                             b, b.big_list, n_big, g0, g1);
+            e = cudaGetLastError();
+            if (e != cudaSuccess) return e;
+            if (launches) ++*launches;
+        }
+        return cudaSuccess;
+    }
+    const uint64_t want = (b.n_snarls + 7) / 8;
+    const unsigned blocks = unsigned(want < 148ull * 16 ? want : 148ull * 16);
+    path_and_popc_ldg_kernel<<<blocks, 256, 0, st>>>(m.rows, case_mask, pitch, uint32_t(m.n_cols), n_case_hap, b,
+                                                     nullptr, b.n_snarls, g0, g1);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+// =================================================================================================
+// K2: per-snarl statistics
+// =================================================================================================
+__global__ void __launch_bounds__(128) binary_stats_kernel(BatchDev b, const uint32_t* __restrict__ g0v,
+                                                           const uint32_t* __restrict__ g1v,
+                                                           stoat_gpu_thresholds thr, uint64_t* __restrict__ total_sum,
+                                                           uint8_t* __restrict__ filtered, double* __restrict__ p_chi2,
+                                                           double* __restrict__ p_fisher,
+                                                           uint8_t* __restrict__ chi2_code,
+                                                           uint8_t* __restrict__ fisher_code) {
+    const uint64_t s = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (s >= b.n_snarls) return;
+    const uint64_t p0 = b.snarl_path_off[s], p1 = b.snarl_path_off[s + 1];
+
+    // pass 1 over the columns: totals, compaction count, MAF count (snarl_analyzer.cpp:686-732)
+    uint64_t tot = 0, row0 = 0, row1 = 0;
+    uint32_t ncol = 0, above = 0;
+    uint64_t c0[2] = {0, 0}, c1[2] = {0, 0};  // first two non-empty columns (the 2x2 case)
+    bool col_low32_zero = false;              // chi2_2xN's any_of takes the column total as int (:233)
+    for (uint64_t p = p0; p < p1; ++p) {
+        const uint64_t a = g0v[p], c = g1v[p];
+        const uint64_t cs = a + c;
+        if (cs == 0) continue;  // remove_empty_columns_binary_table
+        if (ncol < 2) {
+            c0[ncol] = a;
+            c1[ncol] = c;
+        }
+        ++ncol;
+        tot += cs;
+        row0 += a;
+        row1 += c;
+        if (uint32_t(cs) == 0) col_low32_zero = true;
+        const double freq1 = __ddiv_rn(double(c), double(cs));
+        const double maf = fmin(freq1, __dsub_rn(1.0, freq1));
+        if (maf > thr.maf_threshold) ++above;
+    }
+    total_sum[s] = tot;
+    // filtration_binary_table (:714, :731)
+    const bool filt = (tot / 2 < thr.min_individuals) || (tot < thr.min_haplotypes) || (ncol < 2) || (above < 2);
+    filtered[s] = filt ? 1 : 0;
+    PVal chi{0.0, kPNa}, fis{0.0, kPNa};
+    if (!filt) {
+        if (ncol == 2) {  // fisher_khi2 (:369-375): a = g0[0], b = g0[1], c = g1[0], d = g1[1]
+            chi = chi2_2x2(c0[0], c0[1], c1[0], c1[1]);
+            fis = fisher_2x2(c0[0], c0[1], c1[0], c1[1]);
+        } else {  // chi2_2xN (:214-257)
+            if (tot == 0 || row0 == 0 || row1 == 0 || col_low32_zero) {
+                chi = {0.0, kPNa};
+            } else {
+                double stat = 0.0;
+                for (uint64_t p = p0; p < p1; ++p) {
+                    const uint64_t a = g0v[p], c = g1v[p];
+                    if (a + c == 0) continue;
+                    stat = chi2_2xN_column(stat, a, c, row0, row1, tot);
+                }
+                chi = {chi2_pvalue_like_reference(stat, ncol - 1), kPValue};
+            }
+        }
+    }
+    p_chi2[s] = chi.v;
+    chi2_code[s] = chi.code;
+    p_fisher[s] = fis.v;
+    fisher_code[s] = fis.code;
+}
+
+cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const stoat_gpu_thresholds& thr,
+                                uint64_t* total_sum, uint8_t* filtered, double* p_chi2, double* p_fisher,
+                                uint8_t* chi2_code, uint8_t* fisher_code, cudaStream_t st) {
+    if (b.n_snarls == 0) return cudaSuccess;
+    const unsigned blocks = unsigned((b.n_snarls + 127) / 128);
+    binary_stats_kernel<<<blocks, 128, 0, st>>>(b, counts, counts + b.n_paths, thr, total_sum, filtered, p_chi2,
+                                                p_fisher, chi2_code, fisher_code);
+    return cudaGetLastError();
+}
+
+}  // namespace stoat
