@@ -478,7 +478,7 @@ int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresh
                  ctx->q_se.as<double>(),       ctx->q_code.as<uint8_t>()};
     ctx->timing.launches = 0;
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
-    CK(launch_quantitative_impl(matrix_view(ctx), x->q.yc.as<double>(), x->q.ys.as<double>(), x->q.sy_all,
+    CK(launch_quantitative_impl(matrix_view(ctx), ctx->y.as<double>(), x->q.ys.as<double>(), x->q.sy_all,
                                 x->q.syy_all, ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar),
                                 ctx->batch, x->max_stage_rows, *thr, out,
                                 reinterpret_cast<QuantMoments*>(x->q.mom.p), ctx->num_sms, ctx->k1_variant,

@@ -97,7 +97,7 @@ struct QuantOut {
     double* se;
     uint8_t* code;
 };
-cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_centred, const double* ys_perm,
+cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, const double* ys_perm,
                                      double sy_all, double syy_all, const double* covar, uint32_t n_covar,
                                      const BatchDev& b, uint32_t max_stage_rows, const stoat_gpu_thresholds& thr,
                                      QuantOut out, QuantMoments* mom, int num_sms, int variant, cudaStream_t st,

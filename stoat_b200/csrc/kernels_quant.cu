@@ -12,10 +12,11 @@
 //   K3G general path  any snarl (<= 64 paths, <= 16 features, covariates, thirds ...): one warp per snarl,
 //        straight from global memory, lane <-> sample, regression table rebuilt in the reference's own order.
 //
-// The phenotype is centred once (y' = y - mean over all samples) when it is uploaded: OLS with an intercept
-// is invariant under that shift (beta_1, se, t, R^2 unchanged) and it keeps RSS = y'y - 2 b'X'y + b'X'Xb
-// well conditioned.  Snarls where that expansion would still cancel (R^2 > 1 - 1e-6) are re-done by K3G with
-// an explicit residual pass, as the reference does (:460-463).
+// For the moment path the phenotype is centred once (y' = y - mean over all samples) when it is uploaded: a
+// full-rank OLS with an intercept is invariant under that shift (beta_1, se, t, R^2 unchanged) and it keeps
+// RSS = y'y - 2 b'X'y + b'X'Xb well conditioned.  Snarls where that expansion would still cancel
+// (R^2 > 1 - 1e-6), and rank-deficient snarls (pseudo-inverse branch: minimum-norm beta, NOT shift invariant),
+// are re-done by K3G on the raw phenotype with an explicit residual pass, as the reference does (:460-463).
 #include "ctx.hpp"
 #include "ols.cuh"
 #include "ptx.cuh"
@@ -457,7 +458,13 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
             X(i, j) = m.xtx[q];
             X(j, i) = m.xtx[q];
         }
-    xtx_inverse<4>(X, p, inv);
+    if (xtx_inverse<4>(X, p, inv)) {
+        // rank deficient: the pseudo-inverse picks the minimum-norm solution, which is NOT invariant under the
+        // centring of y used by the moment path -> redo on the general path with the raw phenotype
+        const uint32_t slot = atomicAdd(g_count, 1u);
+        g_list[slot] = uint32_t(s);
+        return;
+    }
     double beta[4];
     for (int i = 0; i < p; ++i) {
         double b = 0.0;
@@ -494,7 +501,7 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
 struct GParams {
     const uint8_t* rows;
     uint32_t pitch, n_hap, n_samples;
-    const double* y;      // centred phenotype, natural order
+    const double* y;      // RAW phenotype (not centred: the pseudo-inverse branch is not shift invariant)
     const double* covar;  // [n_samples][n_covar] row-major (indexed by FILTERED row position, see below)
     uint32_t n_covar;
     BatchDev b;
@@ -868,7 +875,7 @@ static bool choose_k3_config(uint32_t pitch, uint32_t stage_rows, K3Config& cfg)
 }
 
 // scratch owned by the caller: mom [n_snarls], ys permuted, sums
-cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_centred, const double* ys_perm,
+cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, const double* ys_perm,
                                      double sy_all, double syy_all, const double* covar, uint32_t n_covar,
                                      const BatchDev& b, uint32_t max_stage_rows, const stoat_gpu_thresholds& thr,
                                      QuantOut out, QuantMoments* mom, int num_sms, int variant, cudaStream_t st,
@@ -885,7 +892,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_centred
     g.pitch = pitch;
     g.n_hap = uint32_t(m.n_cols);
     g.n_samples = n_samples;
-    g.y = y_centred;
+    g.y = y_raw;
     g.covar = covar;
     g.n_covar = n_covar;
     g.b = b;

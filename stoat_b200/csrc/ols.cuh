@@ -128,9 +128,10 @@ __device__ inline void pinv_symmetric(const SmallMat<N>& A, int n, double tol, S
     }
 }
 
-// computeXtXinverse (src/stats_test.cpp:398-421): XtX full symmetric n x n in, inverse out
+// computeXtXinverse (src/stats_test.cpp:398-421): XtX full symmetric n x n in, inverse out.
+// Returns true when the rank-deficient (pseudo-inverse) branch was taken.
 template <int N>
-__device__ inline void xtx_inverse(const SmallMat<N>& XtX, int n, SmallMat<N>& inv) {
+__device__ inline bool xtx_inverse(const SmallMat<N>& XtX, int n, SmallMat<N>& inv) {
     SmallMat<N> f = XtX;
     int tr[N];
     ldlt_factor<N>(f, n, tr);
@@ -139,7 +140,7 @@ __device__ inline void xtx_inverse(const SmallMat<N>& XtX, int n, SmallMat<N>& i
         if (fabs(f(i, i)) < 1e-10) deficient = true;
     if (deficient) {
         pinv_symmetric<N>(XtX, n, 1e-6, inv);
-        return;
+        return true;
     }
     double e[N];
     for (int j = 0; j < n; ++j) {
@@ -147,6 +148,7 @@ __device__ inline void xtx_inverse(const SmallMat<N>& XtX, int n, SmallMat<N>& i
         ldlt_solve<N>(f, n, tr, e);
         for (int i = 0; i < n; ++i) inv(i, j) = e[i];
     }
+    return false;
 }
 
 struct OlsOut {
