@@ -117,7 +117,7 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     DevBuf* bufs[] = {&ctx->rows, &ctx->raw_stage[0], &ctx->raw_stage[1], &ctx->case_mask, &ctx->is_case_dev, &ctx->y,
                       &ctx->covar, &ctx->d_snarl_path_off, &ctx->d_path_edge_off, &ctx->d_edge_row, &ctx->d_rec,
                       &ctx->d_blob, &ctx->d_big, &ctx->d_counters, &ctx->counts, &ctx->total_sum, &ctx->filtered,
-                      &ctx->p_a, &ctx->p_b, &ctx->code_a, &ctx->code_b, &ctx->q_allele, &ctx->q_nused, &ctx->q_p,
+                      &ctx->p_a, &ctx->p_b, &ctx->code_a, &ctx->code_b, &ctx->fisher_tab, &ctx->fisher_idx, &ctx->fisher_cnt, &ctx->q_allele, &ctx->q_nused, &ctx->q_p,
                       &ctx->q_r2, &ctx->q_beta, &ctx->q_se, &ctx->q_code};
     for (DevBuf* b : bufs) b->release();
     CtxExtra* x = extra_of(ctx);
@@ -343,6 +343,9 @@ static int binary_reserve(stoat_gpu_ctx* ctx) {
     CK(ctx->p_b.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
     CK(ctx->code_a.reserve(std::max<uint64_t>(b.n_snarls, 16)));
     CK(ctx->code_b.reserve(std::max<uint64_t>(b.n_snarls, 16)));
+    CK(ctx->fisher_tab.reserve(std::max<uint64_t>(b.n_snarls * 16, 16)));
+    CK(ctx->fisher_idx.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
+    CK(ctx->fisher_cnt.reserve(16));
     return STOAT_GPU_OK;
 }
 
@@ -382,9 +385,10 @@ int stoat_gpu_binary_stats_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds
     CK(cudaEventRecord(ctx->ev[4], ctx->stream));
     CK(launch_binary_stats(ctx->batch, ctx->counts.as<uint32_t>(), *thr, ctx->total_sum.as<uint64_t>(),
                            ctx->filtered.as<uint8_t>(), ctx->p_a.as<double>(), ctx->p_b.as<double>(),
-                           ctx->code_a.as<uint8_t>(), ctx->code_b.as<uint8_t>(), ctx->stream));
+                           ctx->code_a.as<uint8_t>(), ctx->code_b.as<uint8_t>(), ctx->fisher_tab.as<uint4>(),
+                           ctx->fisher_idx.as<uint32_t>(), ctx->fisher_cnt.as<uint32_t>(), ctx->num_sms, ctx->stream));
     CK(cudaEventRecord(ctx->ev[5], ctx->stream));
-    if (ctx->batch.n_snarls) ctx->timing.launches += 1;
+    if (ctx->batch.n_snarls) ctx->timing.launches += 2;
     ctx->have_binary_result = true;
     return STOAT_GPU_OK;
 }

@@ -84,7 +84,8 @@ cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, u
                                  cudaStream_t st, uint32_t* launches);
 cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const stoat_gpu_thresholds& thr,
                                 uint64_t* total_sum, uint8_t* filtered, double* p_chi2, double* p_fisher,
-                                uint8_t* chi2_code, uint8_t* fisher_code, cudaStream_t st);
+                                uint8_t* chi2_code, uint8_t* fisher_code, uint4* fisher_tab, uint32_t* fisher_idx,
+                                uint32_t* fisher_counters, int num_sms, cudaStream_t st);
 // quantitative
 struct QuantMoments;  // kernels_quant.cu
 struct QuantOut {
@@ -140,6 +141,7 @@ struct stoat_gpu_ctx {
 
     // results (device)
     stoat::DevBuf counts, total_sum, filtered, p_a, p_b, code_a, code_b;  // binary
+    stoat::DevBuf fisher_tab, fisher_idx, fisher_cnt;                      // Fisher work list
     stoat::DevBuf q_allele, q_nused, q_p, q_r2, q_beta, q_se, q_code;      // quantitative
     bool have_binary_counts = false, have_binary_result = false, have_quant_result = false;
 };

@@ -174,53 +174,67 @@ __device__ inline double chi2_2xN_column(double stat, uint64_t g0, uint64_t g1, 
 // ------------------------------------------------------------------------------------------------
 // FisherKhi2::fastFishersExactTest — src/stats_test.cpp:264-360
 // ------------------------------------------------------------------------------------------------
+// The reference runs three loops (towards the centre, far tail, near tail).  All three have the same body
+//   d1 += 1; d2 += 1; cur_prob *= (n1 * n2) / (d1 * d2); n1 -= 1; n2 -= 1;
+// with (n, d) = (cur12, cur21 | cur11, cur22) in the first two and (cur11, cur22 | cur12, cur21) in the third.
+// They are fused into ONE loop with a per-thread phase so that the lanes of a warp — each on its own table, in
+// whatever phase — share the expensive instructions (3 DMUL + 1 DDIV) instead of serialising three loops.
+// Every floating-point operation and its order are those of the reference.
 __device__ inline PVal fisher_2x2(uint64_t m11, uint64_t m12, uint64_t m21, uint64_t m22) {
     if ((m11 | m12) == 0 || (m21 | m22) == 0 || (m11 | m21) == 0 || (m12 | m22) == 0) return {0.0, kPNa};
     constexpr double kEps2 = 9.094947017729282e-13;  // stats_test.hpp:59
     constexpr double kBias = 1.0339757656912846e-25;  // stats_test.hpp:60
     constexpr double kStart = (1 - kEps2) * kBias;    // folded in IEEE double, as on the host
-    double tprob = kStart, cur_prob = kStart, cprob = 0.0, preaddp;
     uint64_t u;
-    if (m12 > m21) { u = m12; m12 = m21; m21 = u; }
-    if (m11 > m22) { u = m11; m11 = m22; m22 = u; }
-    if (m11 * m22 > m12 * m21) {
+    if (m12 > m21) { u = m12; m12 = m21; m21 = u; }  // :280-284
+    if (m11 > m22) { u = m11; m11 = m22; m22 = u; }  // :286-290
+    if (m11 * m22 > m12 * m21) {                      // :292-299
         u = m11; m11 = m12; m12 = u;
         u = m21; m21 = m22; m22 = u;
     }
-    double cur11 = double(m11), cur12 = double(m12), cur21 = double(m21), cur22 = double(m22);
-    while (cur12 > 0.5) {
-        cur11 += 1; cur22 += 1;  // exact: small integers
-        cur_prob = __dmul_rn(cur_prob, __ddiv_rn(__dmul_rn(cur12, cur21), __dmul_rn(cur11, cur22)));
-        cur12 -= 1; cur21 -= 1;
-        if (cur_prob > DBL_MAX) return {0.0, kPZero};
-        if (cur_prob < kBias) {
-            tprob = __dadd_rn(tprob, cur_prob);
-            break;
+    double tprob = kStart, cur_prob = kStart, cprob = 0.0;
+    double n1 = double(m12), n2 = double(m21), d1 = double(m11), d2 = double(m22);
+    int phase = 1;
+    PVal res{0.0, kPNa};
+    for (;;) {
+        // ---- loop conditions / transitions evaluated before a body execution ----------------------
+        if (phase == 1 && !(n1 > 0.5)) {  // first loop ran out (:306)
+            if (cprob == 0) { res = {1.0, kPOne}; break; }  // :322-324
+            phase = 2;
         }
-        cprob = __dadd_rn(cprob, cur_prob);
-    }
-    if (cprob == 0) return {1.0, kPOne};
-    while (cur12 > 0.5) {
-        cur11 += 1; cur22 += 1;
-        cur_prob = __dmul_rn(cur_prob, __ddiv_rn(__dmul_rn(cur12, cur21), __dmul_rn(cur11, cur22)));
-        cur12 -= 1; cur21 -= 1;
-        preaddp = tprob;
-        tprob = __dadd_rn(tprob, cur_prob);
-        if (tprob <= preaddp) break;
-    }
-    if (m11) {
-        cur11 = double(m11); cur12 = double(m12); cur21 = double(m21); cur22 = double(m22);
-        cur_prob = kStart;
-        do {
-            cur12 += 1; cur21 += 1;
-            cur_prob = __dmul_rn(cur_prob, __ddiv_rn(__dmul_rn(cur11, cur22), __dmul_rn(cur12, cur21)));
-            cur11 -= 1; cur22 -= 1;
-            preaddp = tprob;
+        if (phase == 2 && !(n1 > 0.5)) phase = 4;  // second loop's condition (:326)
+        if (phase == 4) {                          // set up the third loop (:339-344)
+            if (m11 == 0) { res = {__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue}; break; }  // :359
+            n1 = double(m11); n2 = double(m22); d1 = double(m12); d2 = double(m21);
+            cur_prob = kStart;
+            phase = 3;
+        }
+        // ---- common body ----------------------------------------------------------------------------
+        d1 += 1; d2 += 1;  // exact: small integers
+        cur_prob = __dmul_rn(cur_prob, __ddiv_rn(__dmul_rn(n1, n2), __dmul_rn(d1, d2)));
+        n1 -= 1; n2 -= 1;
+        // ---- per-phase bookkeeping ---------------------------------------------------------------------
+        if (phase == 1) {
+            if (cur_prob > DBL_MAX) { res = {0.0, kPZero}; break; }  // :312-314
+            if (cur_prob < kBias) {                                   // :315-318
+                tprob = __dadd_rn(tprob, cur_prob);
+                if (cprob == 0) { res = {1.0, kPOne}; break; }
+                phase = 2;
+            } else {
+                cprob = __dadd_rn(cprob, cur_prob);
+            }
+        } else {
+            const double preaddp = tprob;
             tprob = __dadd_rn(tprob, cur_prob);
-            if (tprob <= preaddp) return {__ddiv_rn(preaddp, __dadd_rn(cprob, preaddp)), kPValue};
-        } while (cur11 > 0.5);
+            if (phase == 2) {
+                if (tprob <= preaddp) phase = 4;  // :334-336
+            } else {
+                if (tprob <= preaddp) { res = {__ddiv_rn(preaddp, __dadd_rn(cprob, preaddp)), kPValue}; break; }  // :352-354
+                if (!(n1 > 0.5)) { res = {__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue}; break; }           // :356, :359
+            }
+        }
     }
-    return {__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue};
+    return res;
 }
 
 }  // namespace stoat

@@ -16,6 +16,8 @@
 // code_{np-1}] [locals of path 0] [locals of path 1] ...   code = 0xFF: an edge of the path is missing from the matrix => nobody matches
 // (:334-336); code = 0: no checked edge => every haplotype matches (:343-354); else the number of
 // checked edges R, followed (in the locals area) by R indices into the snarl's distinct-row list.
+#include <cstdlib>
+
 #include "ctx.hpp"
 #include "device_math.cuh"
 #include "ptx.cuh"
@@ -129,20 +131,31 @@ struct K1Params {
     uint32_t n_stages;     // pipeline depth per warp
 };
 
-// AND of R staged rows over the 16-byte chunks owned by this lane, popcounts split by case mask
-template <int R>
-__device__ __forceinline__ void and_popc_rows(const uint8_t* const* rp, const uint8_t* mask, uint32_t chunks,
-                                              uint32_t lane, uint32_t& n_all, uint32_t& n_case) {
-#pragma unroll 2
-    for (uint32_t c = lane; c < chunks; c += 32) {
-        uint4 v = *reinterpret_cast<const uint4*>(rp[0] + c * 16);
-#pragma unroll
-        for (int r = 1; r < R; ++r) v = and4(v, *reinterpret_cast<const uint4*>(rp[r] + c * 16));
-        const uint4 m = *reinterpret_cast<const uint4*>(mask + c * 16);
-        n_all += popc4(v);
-        n_case += popc4(and4(v, m));
-    }
+// Record of a snarl as the 8 words lanes 0..7 of a warp hold: words 0..5 = rows, 6 = blob16,
+// 7 = n_rows | blob_len16 << 8 | n_paths << 16.  Lane k < 6 later issues the copy of row k straight from its own
+// register, lane 6 the path program, lane 7 arms the barrier: the refill costs ~10 warp instructions.
+__device__ __forceinline__ uint32_t load_rec_word(const SnarlRec* rec, uint64_t s, uint32_t lane) {
+    return (lane < 8) ? __ldg(reinterpret_cast<const uint32_t*>(rec + s) + lane) : 0u;
 }
+
+__device__ __forceinline__ void issue_stage(uint32_t rec_word, uint32_t lane, uint8_t* dst, uint64_t* bar,
+                                            const uint8_t* rows, const uint8_t* blob, uint32_t pitch,
+                                            uint64_t policy) {
+    const uint32_t packed = __shfl_sync(0xffffffffu, rec_word, 7);
+    const uint32_t n_rows = packed & 0xFFu, blob_bytes = ((packed >> 8) & 0xFFu) * 16u;
+    // No proxy fence: the stage was only READ through the generic proxy, and those reads have completed (their
+    // values were consumed, then __syncwarp) before the async proxy overwrites it — the same write-after-read
+    // hand-over a consumer-release / producer-acquire mbarrier pair gives in a TMA pipeline.  (A
+    // fence.proxy.async here was measured to serialise every iteration on the in-flight bulk copies.)
+    if (lane == 7) mbar_arrive_expect_tx(bar, blob_bytes + n_rows * pitch);
+    __syncwarp();
+    if (lane < n_rows)
+        tma_bulk_g2s_hint(dst + kBlobBytes + lane * pitch, rows + size_t(rec_word) * pitch, pitch, bar, policy);
+    else if (lane == 6)
+        tma_bulk_g2s(dst, blob + size_t(rec_word) * 16, blob_bytes, bar);
+}
+
+constexpr int kGroup = 4;  // paths processed together (shared mask load, independent chains)
 
 __global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Params p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -171,86 +184,106 @@ __global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Param
     const uint32_t chunks = p.pitch / 16;
     const uint64_t policy = make_evict_first_policy();
 
-    // issue the TMA bulk copies of one snarl into one stage (lane 0 only)
-    auto issue = [&](const SnarlRec& r, uint32_t stage) {
-        uint8_t* dst = my_stages + size_t(stage) * stage_bytes;
-        const uint32_t blob_bytes = uint32_t(r.blob_len16) * 16;
-        mbar_arrive_expect_tx(&my_full[stage], blob_bytes + uint32_t(r.n_rows) * p.pitch);
-        tma_bulk_g2s(dst, p.blob + size_t(r.blob16) * 16, blob_bytes, &my_full[stage]);
-        for (uint32_t k = 0; k < r.n_rows; ++k)
-            tma_bulk_g2s_hint(dst + kBlobBytes + k * p.pitch, p.rows + size_t(r.rows[k]) * p.pitch, p.pitch,
-                              &my_full[stage], policy);
-    };
-
     // prologue: fill the pipeline
-    if (lane == 0) {
+    {
         uint64_t s = gw;
-        for (uint32_t st = 0; st < p.n_stages && s < p.n_snarls; ++st, s += stride) issue(p.rec[s], st);
+        for (uint32_t st = 0; st < p.n_stages && s < p.n_snarls; ++st, s += stride)
+            issue_stage(load_rec_word(p.rec, s, lane), lane, my_stages + size_t(st) * stage_bytes, &my_full[st], p.rows,
+                        p.blob, p.pitch, policy);
     }
-    __syncwarp();
 
     uint32_t it = 0;
     for (uint64_t s = gw; s < p.n_snarls; s += stride, ++it) {
         const uint32_t stage = it % p.n_stages;
         const uint32_t parity = (it / p.n_stages) & 1u;
-        // record of the snarl that will refill this stage: fetched now, needed after the compute
+        // record of the snarl that will refill this stage: requested now, consumed after the compute
         const uint64_t s_next = s + uint64_t(p.n_stages) * stride;
-        SnarlRec next_rec;
-        if (lane == 0 && s_next < p.n_snarls) next_rec = p.rec[s_next];
+        uint32_t next_word = (s_next < p.n_snarls) ? load_rec_word(p.rec, s_next, lane) : 0u;
         mbar_wait(&my_full[stage], parity);
         const uint8_t* blob = my_stages + size_t(stage) * stage_bytes;
         const uint8_t* rows_s = blob + kBlobBytes;
         const uint32_t np = blob[0];
-        if (np) {
-            const uint32_t p0 = *reinterpret_cast<const uint32_t*>(blob + 4);
-            uint32_t off = kBlobHeader + np;
-            for (uint32_t j = 0; j < np; ++j) {
-                const uint32_t code = blob[kBlobHeader + j];
-                uint32_t n_all = 0, n_case = 0;
-                if (code == 0xFF) {
-                    // missing edge: nobody
-                } else if (code == 0) {
-                    n_all = p.n_hap;  // every haplotype (only lane 0's value is written)
-                    n_case = p.n_case_hap;
-                } else {
-                    const uint8_t* rp[4];
-                    if (code <= 4) {
+        const uint32_t p0 = *reinterpret_cast<const uint32_t*>(blob + 4);
+        uint32_t off = kBlobHeader + np;
+        for (uint32_t j0 = 0; j0 < np; j0 += kGroup) {
+            // ---- decode up to kGroup path programs (warp uniform) ------------------------------------
+            uint32_t code[kGroup], roff[kGroup][4];
 #pragma unroll
-                        for (int r = 0; r < 4; ++r)
-                            rp[r] = rows_s + uint32_t(blob[off + (r < int(code) ? r : 0)]) * p.pitch;
-                        switch (code) {
-                            case 1: and_popc_rows<1>(rp, mask_s, chunks, lane, n_all, n_case); break;
-                            case 2: and_popc_rows<2>(rp, mask_s, chunks, lane, n_all, n_case); break;
-                            case 3: and_popc_rows<3>(rp, mask_s, chunks, lane, n_all, n_case); break;
-                            default: and_popc_rows<4>(rp, mask_s, chunks, lane, n_all, n_case); break;
-                        }
-                    } else {
-                        for (uint32_t c = lane; c < chunks; c += 32) {
-                            uint4 v = *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[off]) * p.pitch + c * 16);
-                            for (uint32_t r = 1; r < code; ++r)
-                                v = and4(v, *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[off + r]) * p.pitch +
-                                                                            c * 16));
-                            const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
-                            n_all += popc4(v);
-                            n_case += popc4(and4(v, m));
-                        }
+            for (int g = 0; g < kGroup; ++g) {
+                code[g] = (j0 + g < np) ? uint32_t(blob[kBlobHeader + j0 + g]) : 0xFFu;
+                const bool live = code[g] != 0xFFu && code[g] != 0u;
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+                    roff[g][r] = (live && uint32_t(r) < code[g]) ? uint32_t(blob[off + r]) * p.pitch : 0u;
+                if (live) off += code[g];
+            }
+            uint32_t n_all[kGroup], n_case[kGroup];
+#pragma unroll
+            for (int g = 0; g < kGroup; ++g) n_all[g] = n_case[g] = 0;
+            bool longp = false;
+#pragma unroll
+            for (int g = 0; g < kGroup; ++g) longp |= (code[g] != 0xFFu && code[g] > 4u);
+            if (!longp) {
+#pragma unroll 3
+                for (uint32_t c = lane; c < chunks; c += 32) {
+                    const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
+#pragma unroll
+                    for (int g = 0; g < kGroup; ++g) {
+                        if (code[g] == 0xFFu || code[g] == 0u) continue;  // warp uniform
+                        uint4 v = *reinterpret_cast<const uint4*>(rows_s + roff[g][0] + c * 16);
+#pragma unroll
+                        for (int r = 1; r < 4; ++r)
+                            if (uint32_t(r) < code[g])
+                                v = and4(v, *reinterpret_cast<const uint4*>(rows_s + roff[g][r] + c * 16));
+                        n_all[g] += popc4(v);
+                        n_case[g] += popc4(and4(v, m));
                     }
-                    off += code;
-                    n_all = __reduce_add_sync(0xffffffffu, n_all);
-                    n_case = __reduce_add_sync(0xffffffffu, n_case);
                 }
-                if (lane == 0) {
-                    p.g0[p0 + j] = n_all - n_case;  // controls  (binary_table.cpp:37-39)
-                    p.g1[p0 + j] = n_case;          // cases     (binary_table.cpp:35-36)
+            } else {
+                // a path with more than 4 checked edges in this group: plain loops over the program
+                uint32_t o2 = off;
+#pragma unroll
+                for (int g = kGroup - 1; g >= 0; --g)
+                    if (code[g] != 0xFFu) o2 -= code[g];
+#pragma unroll
+                for (int g = 0; g < kGroup; ++g) {
+                    if (code[g] == 0xFFu || code[g] == 0u) continue;
+                    for (uint32_t c = lane; c < chunks; c += 32) {
+                        uint4 v = *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[o2]) * p.pitch + c * 16);
+                        for (uint32_t r = 1; r < code[g]; ++r)
+                            v = and4(v, *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[o2 + r]) * p.pitch + c * 16));
+                        const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
+                        n_all[g] += popc4(v);
+                        n_case[g] += popc4(and4(v, m));
+                    }
+                    o2 += code[g];
                 }
+            }
+            uint32_t my_all = 0, my_case = 0;
+#pragma unroll
+            for (int g = 0; g < kGroup; ++g) {
+                uint32_t a = __reduce_add_sync(0xffffffffu, n_all[g]);
+                uint32_t c1 = __reduce_add_sync(0xffffffffu, n_case[g]);
+                if (code[g] == 0u) {  // no checked edge: every haplotype (snarl_analyzer.cpp:343-354)
+                    a = p.n_hap;
+                    c1 = p.n_case_hap;
+                }
+                if (lane == uint32_t(g)) {
+                    my_all = a;
+                    my_case = c1;
+                }
+            }
+            if (lane < kGroup && j0 + lane < np) {
+                p.g0[p0 + j0 + lane] = my_all - my_case;  // controls  (binary_table.cpp:37-39)
+                p.g1[p0 + j0 + lane] = my_case;           // cases     (binary_table.cpp:35-36)
             }
         }
         // all lanes are done reading this stage: refill it with the snarl n_stages ahead
         __syncwarp();
-        if (lane == 0 && s_next < p.n_snarls) {
-            fence_proxy_async_smem();
-            issue(next_rec, stage);
-        }
+        asm volatile("" : "+r"(next_word));  // keep the record's consumers below the compute
+        if (s_next < p.n_snarls)
+            issue_stage(next_word, lane, my_stages + size_t(stage) * stage_bytes, &my_full[stage], p.rows, p.blob,
+                        p.pitch, policy);
     }
 }
 
@@ -312,6 +345,10 @@ static bool choose_k1_config(uint32_t pitch, uint32_t stage_rows, K1Config& cfg)
     const uint32_t total_stages = (budget - mask_bytes - 1024) / stage_bytes;
     uint32_t n_stages = 3;
     if (total_stages < 3 * 4) n_stages = 2;   // few stages: prefer more warps over depth
+    if (const char* e = std::getenv("STOAT_GPU_K1_STAGES")) {
+        const int v = std::atoi(e);
+        if (v >= 2 && v <= 8 && uint32_t(v) <= total_stages) n_stages = uint32_t(v);
+    }
     uint32_t n_warps = total_stages / n_stages;
     if (n_warps > 16) {
         n_warps = 16;
@@ -379,6 +416,11 @@ cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, u
 
 // =================================================================================================
 // K2: per-snarl statistics
+//   K2a binary_stats   one thread per snarl: column compaction, filter, chi2 (cheap, uniform work); 2x2 tables
+//                      that need Fisher's test are appended to a work list
+//   K2b fisher_exact   persistent lanes pull tables from that list: the recurrence runs 10^2..10^4 iterations
+//                      depending on the table, so a static thread-per-snarl mapping leaves most lanes of a warp idle
+//                      (measured: 8.3 of 32 lanes active); with dynamic refill every lane stays in the shared loop body
 // =================================================================================================
 __global__ void __launch_bounds__(128) binary_stats_kernel(BatchDev b, const uint32_t* __restrict__ g0v,
                                                            const uint32_t* __restrict__ g1v,
@@ -386,69 +428,198 @@ __global__ void __launch_bounds__(128) binary_stats_kernel(BatchDev b, const uin
                                                            uint8_t* __restrict__ filtered, double* __restrict__ p_chi2,
                                                            double* __restrict__ p_fisher,
                                                            uint8_t* __restrict__ chi2_code,
-                                                           uint8_t* __restrict__ fisher_code) {
+                                                           uint8_t* __restrict__ fisher_code,
+                                                           uint4* __restrict__ fisher_tab,
+                                                           uint32_t* __restrict__ fisher_idx,
+                                                           uint32_t* __restrict__ fisher_cnt) {
     const uint64_t s = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (s >= b.n_snarls) return;
-    const uint64_t p0 = b.snarl_path_off[s], p1 = b.snarl_path_off[s + 1];
-
-    // pass 1 over the columns: totals, compaction count, MAF count (snarl_analyzer.cpp:686-732)
-    uint64_t tot = 0, row0 = 0, row1 = 0;
-    uint32_t ncol = 0, above = 0;
+    const uint32_t lane = threadIdx.x & 31;
+    bool want_fisher = false;
     uint64_t c0[2] = {0, 0}, c1[2] = {0, 0};  // first two non-empty columns (the 2x2 case)
-    bool col_low32_zero = false;              // chi2_2xN's any_of takes the column total as int (:233)
-    for (uint64_t p = p0; p < p1; ++p) {
-        const uint64_t a = g0v[p], c = g1v[p];
-        const uint64_t cs = a + c;
-        if (cs == 0) continue;  // remove_empty_columns_binary_table
-        if (ncol < 2) {
-            c0[ncol] = a;
-            c1[ncol] = c;
+    if (s < b.n_snarls) {
+        const uint64_t p0 = b.snarl_path_off[s], p1 = b.snarl_path_off[s + 1];
+        // pass 1 over the columns: totals, compaction count, MAF count (snarl_analyzer.cpp:686-732)
+        uint64_t tot = 0, row0 = 0, row1 = 0;
+        uint32_t ncol = 0, above = 0;
+        bool col_low32_zero = false;  // chi2_2xN's any_of takes the column total as int (:233)
+        for (uint64_t p = p0; p < p1; ++p) {
+            const uint64_t a = g0v[p], c = g1v[p];
+            const uint64_t cs = a + c;
+            if (cs == 0) continue;  // remove_empty_columns_binary_table
+            if (ncol < 2) {
+                c0[ncol] = a;
+                c1[ncol] = c;
+            }
+            ++ncol;
+            tot += cs;
+            row0 += a;
+            row1 += c;
+            if (uint32_t(cs) == 0) col_low32_zero = true;
+            const double freq1 = __ddiv_rn(double(c), double(cs));
+            const double maf = fmin(freq1, __dsub_rn(1.0, freq1));
+            if (maf > thr.maf_threshold) ++above;
         }
-        ++ncol;
-        tot += cs;
-        row0 += a;
-        row1 += c;
-        if (uint32_t(cs) == 0) col_low32_zero = true;
-        const double freq1 = __ddiv_rn(double(c), double(cs));
-        const double maf = fmin(freq1, __dsub_rn(1.0, freq1));
-        if (maf > thr.maf_threshold) ++above;
-    }
-    total_sum[s] = tot;
-    // filtration_binary_table (:714, :731)
-    const bool filt = (tot / 2 < thr.min_individuals) || (tot < thr.min_haplotypes) || (ncol < 2) || (above < 2);
-    filtered[s] = filt ? 1 : 0;
-    PVal chi{0.0, kPNa}, fis{0.0, kPNa};
-    if (!filt) {
-        if (ncol == 2) {  // fisher_khi2 (:369-375): a = g0[0], b = g0[1], c = g1[0], d = g1[1]
-            chi = chi2_2x2(c0[0], c0[1], c1[0], c1[1]);
-            fis = fisher_2x2(c0[0], c0[1], c1[0], c1[1]);
-        } else {  // chi2_2xN (:214-257)
-            if (tot == 0 || row0 == 0 || row1 == 0 || col_low32_zero) {
-                chi = {0.0, kPNa};
-            } else {
-                double stat = 0.0;
-                for (uint64_t p = p0; p < p1; ++p) {
-                    const uint64_t a = g0v[p], c = g1v[p];
-                    if (a + c == 0) continue;
-                    stat = chi2_2xN_column(stat, a, c, row0, row1, tot);
+        total_sum[s] = tot;
+        // filtration_binary_table (:714, :731)
+        const bool filt = (tot / 2 < thr.min_individuals) || (tot < thr.min_haplotypes) || (ncol < 2) || (above < 2);
+        filtered[s] = filt ? 1 : 0;
+        PVal chi{0.0, kPNa};
+        if (!filt) {
+            if (ncol == 2) {  // fisher_khi2 (:369-375): a = g0[0], b = g0[1], c = g1[0], d = g1[1]
+                chi = chi2_2x2(c0[0], c0[1], c1[0], c1[1]);
+                // fastFishersExactTest's own NA rule (:268-270); everything else goes to the work list
+                const uint64_t m11 = c0[0], m12 = c0[1], m21 = c1[0], m22 = c1[1];
+                want_fisher = !((m11 | m12) == 0 || (m21 | m22) == 0 || (m11 | m21) == 0 || (m12 | m22) == 0);
+            } else {  // chi2_2xN (:214-257)
+                if (!(tot == 0 || row0 == 0 || row1 == 0 || col_low32_zero)) {
+                    double stat = 0.0;
+                    for (uint64_t p = p0; p < p1; ++p) {
+                        const uint64_t a = g0v[p], c = g1v[p];
+                        if (a + c == 0) continue;
+                        stat = chi2_2xN_column(stat, a, c, row0, row1, tot);
+                    }
+                    chi = {chi2_pvalue_like_reference(stat, ncol - 1), kPValue};
                 }
-                chi = {chi2_pvalue_like_reference(stat, ncol - 1), kPValue};
+            }
+        }
+        p_chi2[s] = chi.v;
+        chi2_code[s] = chi.code;
+        p_fisher[s] = 0.0;
+        fisher_code[s] = kPNa;
+    }
+    // warp-aggregated append to the Fisher work list
+    const uint32_t need = __ballot_sync(0xffffffffu, want_fisher);
+    if (need) {
+        const int leader = __ffs(need) - 1;
+        uint32_t base = 0;
+        if (int(lane) == leader) base = atomicAdd(fisher_cnt, uint32_t(__popc(need)));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (want_fisher) {
+            const uint32_t slot = base + __popc(need & ((1u << lane) - 1u));
+            fisher_tab[slot] = make_uint4(uint32_t(c0[0]), uint32_t(c0[1]), uint32_t(c1[0]), uint32_t(c1[1]));
+            fisher_idx[slot] = uint32_t(s);
+        }
+    }
+}
+
+// per-lane state of one running recurrence (see fisher_2x2 in device_math.cuh for the single-table form; this
+// is the same arithmetic, operation for operation, split at the loop body so that lanes can be refilled)
+__global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restrict__ tab,
+                                                           const uint32_t* __restrict__ idx,
+                                                           uint32_t* __restrict__ counters,  // [0] n_work, [1] next
+                                                           double* __restrict__ p_fisher,
+                                                           uint8_t* __restrict__ fisher_code) {
+    constexpr double kEps2 = 9.094947017729282e-13;
+    constexpr double kBias = 1.0339757656912846e-25;
+    constexpr double kStart = (1 - kEps2) * kBias;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t n_work = counters[0];
+    bool active = false, drained = false;
+    uint32_t snarl = 0;
+    double m11 = 0, m12 = 0, m21 = 0, m22 = 0;  // (swapped) table as doubles: exact, counts < 2^32
+    double tprob = 0, cur_prob = 0, cprob = 0, n1 = 0, n2 = 0, d1 = 0, d2 = 0;
+    int phase = 0;
+    for (;;) {
+        const uint32_t need = __ballot_sync(0xffffffffu, !active && !drained);
+        if (need) {
+            const int leader = __ffs(need) - 1;
+            uint32_t base = 0;
+            if (int(lane) == leader) base = atomicAdd(&counters[1], uint32_t(__popc(need)));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!active && !drained) {
+                const uint32_t w = base + __popc(need & ((1u << lane) - 1u));
+                if (w < n_work) {
+                    const uint4 t = tab[w];
+                    snarl = idx[w];
+                    uint64_t a11 = t.x, a12 = t.y, a21 = t.z, a22 = t.w, u;
+                    if (a12 > a21) { u = a12; a12 = a21; a21 = u; }  // stats_test.cpp:280-284
+                    if (a11 > a22) { u = a11; a11 = a22; a22 = u; }  // :286-290
+                    if (a11 * a22 > a12 * a21) {                      // :292-299
+                        u = a11; a11 = a12; a12 = u;
+                        u = a21; a21 = a22; a22 = u;
+                    }
+                    m11 = double(a11); m12 = double(a12); m21 = double(a21); m22 = double(a22);
+                    tprob = kStart; cur_prob = kStart; cprob = 0.0;
+                    n1 = m12; n2 = m21; d1 = m11; d2 = m22;
+                    phase = 1;
+                    active = true;
+                } else {
+                    drained = true;
+                }
+            }
+        }
+        if (!__any_sync(0xffffffffu, active)) break;
+        if (active) {
+            bool done = false;
+            double res = 0.0;
+            uint8_t code = kPValue;
+            // loop conditions / transitions before a body execution
+            if (phase == 1 && !(n1 > 0.5)) {
+                if (cprob == 0) { done = true; res = 1.0; code = kPOne; }  // :322-324
+                phase = 2;
+            }
+            if (!done && phase == 2 && !(n1 > 0.5)) phase = 4;
+            if (!done && phase == 4) {
+                if (m11 == 0) {
+                    done = true;
+                    res = __ddiv_rn(tprob, __dadd_rn(cprob, tprob));  // :359
+                } else {
+                    n1 = m11; n2 = m22; d1 = m12; d2 = m21;
+                    cur_prob = kStart;
+                    phase = 3;
+                }
+            }
+            if (!done) {
+                d1 += 1; d2 += 1;
+                cur_prob = __dmul_rn(cur_prob, __ddiv_rn(__dmul_rn(n1, n2), __dmul_rn(d1, d2)));
+                n1 -= 1; n2 -= 1;
+                if (phase == 1) {
+                    if (cur_prob > DBL_MAX) { done = true; res = 0.0; code = kPZero; }  // :312-314
+                    else if (cur_prob < kBias) {                                          // :315-318
+                        tprob = __dadd_rn(tprob, cur_prob);
+                        if (cprob == 0) { done = true; res = 1.0; code = kPOne; }
+                        phase = 2;
+                    } else {
+                        cprob = __dadd_rn(cprob, cur_prob);
+                    }
+                } else {
+                    const double preaddp = tprob;
+                    tprob = __dadd_rn(tprob, cur_prob);
+                    if (phase == 2) {
+                        if (tprob <= preaddp) phase = 4;  // :334-336
+                    } else if (tprob <= preaddp) {
+                        done = true;
+                        res = __ddiv_rn(preaddp, __dadd_rn(cprob, preaddp));  // :352-354
+                    } else if (!(n1 > 0.5)) {
+                        done = true;
+                        res = __ddiv_rn(tprob, __dadd_rn(cprob, tprob));  // :356, :359
+                    }
+                }
+            }
+            if (done) {
+                p_fisher[snarl] = res;
+                fisher_code[snarl] = code;
+                active = false;
             }
         }
     }
-    p_chi2[s] = chi.v;
-    chi2_code[s] = chi.code;
-    p_fisher[s] = fis.v;
-    fisher_code[s] = fis.code;
 }
 
 cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const stoat_gpu_thresholds& thr,
                                 uint64_t* total_sum, uint8_t* filtered, double* p_chi2, double* p_fisher,
-                                uint8_t* chi2_code, uint8_t* fisher_code, cudaStream_t st) {
+                                uint8_t* chi2_code, uint8_t* fisher_code, uint4* fisher_tab, uint32_t* fisher_idx,
+                                uint32_t* fisher_counters, int num_sms, cudaStream_t st) {
     if (b.n_snarls == 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(fisher_counters, 0, 8, st);
+    if (e != cudaSuccess) return e;
     const unsigned blocks = unsigned((b.n_snarls + 127) / 128);
     binary_stats_kernel<<<blocks, 128, 0, st>>>(b, counts, counts + b.n_paths, thr, total_sum, filtered, p_chi2,
-                                                p_fisher, chi2_code, fisher_code);
+                                                p_fisher, chi2_code, fisher_code, fisher_tab, fisher_idx,
+                                                fisher_counters);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    const uint64_t want = (b.n_snarls + 127) / 128;
+    const unsigned fblocks = unsigned(want < uint64_t(num_sms) * 8 ? want : uint64_t(num_sms) * 8);
+    fisher_exact_kernel<<<fblocks, 128, 0, st>>>(fisher_tab, fisher_idx, fisher_counters, p_fisher, fisher_code);
     return cudaGetLastError();
 }
 

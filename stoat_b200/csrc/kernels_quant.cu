@@ -428,10 +428,7 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
             p.mom[s].state = 0;
         }
         __syncwarp();
-        if (lane == 0 && s_next < p.n_snarls) {
-            fence_proxy_async_smem();
-            issue(next_rec, stage);
-        }
+        if (lane == 0 && s_next < p.n_snarls) issue(next_rec, stage);  // WAR on a read-only stage: no proxy fence
     }
 }
 
