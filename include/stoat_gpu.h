@@ -161,6 +161,8 @@ typedef struct stoat_gpu_timing {
     float stats_ms;    /* K2 binary_stats / K4 ols_solve                                     */
     float d2h_ms;      /* device -> host copies of the results                               */
     uint32_t launches; /* kernels launched by the call                                       */
+    uint32_t n_general; /* snarls that left the TMA-staged fast path (LDG / general kernels)  */
+    uint32_t n_fisher;  /* 2x2 tables that went through the Fisher work list                  */
 } stoat_gpu_timing;
 
 /* ---- lifetime -------------------------------------------------------------------------- */

@@ -50,7 +50,7 @@ class EqtlSummary(C.Structure):
 
 class Timing(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("repack_ms", C.c_float), ("table_ms", C.c_float), ("stats_ms", C.c_float),
-                ("d2h_ms", C.c_float), ("launches", C.c_uint32)]
+                ("d2h_ms", C.c_float), ("launches", C.c_uint32), ("n_general", C.c_uint32), ("n_fisher", C.c_uint32)]
 
 
 # every symbol include/stoat_gpu.h declares: name -> (restype, argtypes)

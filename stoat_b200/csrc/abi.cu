@@ -58,6 +58,7 @@ struct CtxExtra {
     QuantState q;
     uint32_t max_stage_rows = 0;
     uint32_t counters_host[4] = {0, 0, 0, 0};
+    uint32_t readback[2] = {0, 0};
 };
 static CtxExtra* extra_of(stoat_gpu_ctx* ctx);
 
@@ -398,7 +399,11 @@ int stoat_gpu_binary_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* 
     if (rc) return rc;
     rc = stoat_gpu_binary_stats_staged(ctx, thr);
     if (rc) return rc;
+    CtxExtra* x = extra_of(ctx);
+    CK(cudaMemcpyAsync(x->readback, ctx->fisher_cnt.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    ctx->timing.n_general = ctx->n_big;
+    ctx->timing.n_fisher = ctx->batch.n_snarls ? x->readback[0] : 0;
     CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));
     CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ctx->ev[4], ctx->ev[5]));
     return STOAT_GPU_OK;
@@ -488,7 +493,10 @@ int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresh
                                 reinterpret_cast<QuantMoments*>(x->q.mom.p), ctx->num_sms, ctx->k1_variant,
                                 ctx->stream, &ctx->timing.launches));
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    CK(cudaMemcpyAsync(x->readback, ctx->d_counters.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    ctx->timing.n_general = S ? x->readback[0] : 0;
+    ctx->timing.n_fisher = 0;
     CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));
     ctx->timing.stats_ms = 0.f;
     ctx->have_quant_result = true;

@@ -1,0 +1,210 @@
+"""Multi-GPU sharding of the `stoat vcf` hot path: one process per GPU.
+
+The reference has no multi-process mode; its unit of parallelism is the snarl inside a chromosome chunk
+(`#pragma omp parallel for`, src/snarl_analyzer.cpp:165-172) and nothing is shared between snarls except the
+read-only matrix and the phenotype.  Two shardings follow from that:
+
+snarl-sharded (default)
+    Contiguous snarl ranges per rank, balanced by checked edges.  A rank receives only the matrix rows its
+    snarls reference (row indices are remapped to a compact local matrix) and a replica of the phenotype.
+    There is NO data-path collective: each rank runs the ordinary batch call and the host concatenates the
+    per-rank result arrays in rank order (`merge_snarl_results`).
+
+sample-sharded
+    Every rank holds all rows but only a range of haplotype columns (cut at multiples of 128 columns, so both
+    haplotypes of a sample and every 16-byte chunk stay on one rank) plus its slice of the phenotype.  Counts
+    are sums over haplotypes, so ONE exchange is needed: all-reduce(sum) of the uint32 [2P] count buffer
+    between the count pass (K1) and the statistics pass (K2).  On GPUs that is an NCCL all-reduce over NVLink
+    applied in place to the context's device buffer; on CPU (tests, gloo) the same driver runs with host tensors.
+
+Everything here is host plumbing (numpy + torch.distributed); the statistics come from the CUDA library.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+
+from .api import SnarlPaths
+
+MISSING_EDGE = 0xFFFFFFFF
+
+
+# ---------------------------------------------------------------------------------------------------
+# snarl-sharded
+# ---------------------------------------------------------------------------------------------------
+def plan_snarl_shards(paths: SnarlPaths, world: int) -> list[tuple[int, int]]:
+    """Contiguous snarl ranges [s0, s1) per rank, balanced by work = checked edges + paths (the matrix rows a
+    snarl streams are proportional to its checked edges; a path without edges still costs a table column)."""
+    S = paths.n_snarls
+    if world <= 0:
+        raise ValueError("world must be positive")
+    spo = paths.snarl_path_off.astype(np.int64)
+    peo = paths.path_edge_off.astype(np.int64)
+    # cumulative work at snarl boundaries
+    work = peo[spo] + spo
+    total = int(work[-1]) if S else 0
+    cuts = [0]
+    for r in range(1, world):
+        target = total * r / world
+        s = int(np.searchsorted(work, target, side="left"))
+        cuts.append(min(max(s, cuts[-1]), S))
+    cuts.append(S)
+    return [(cuts[r], cuts[r + 1]) for r in range(world)]
+
+
+@dataclass
+class SnarlShard:
+    s0: int
+    s1: int
+    paths: SnarlPaths        # local CSR, edge_row remapped to local rows
+    rows: np.ndarray         # int64 [n_local_rows]: global row of each local row (ascending)
+    bits: np.ndarray | None  # local matrix in the reference layout (None until `attach_rows`)
+    n_rows: int
+    n_cols: int
+
+
+def slice_paths(paths: SnarlPaths, s0: int, s1: int) -> SnarlPaths:
+    p0, p1 = int(paths.snarl_path_off[s0]), int(paths.snarl_path_off[s1])
+    e0, e1 = int(paths.path_edge_off[p0]), int(paths.path_edge_off[p1])
+    return SnarlPaths(paths.snarl_path_off[s0:s1 + 1] - np.uint64(p0),
+                      paths.path_edge_off[p0:p1 + 1] - np.uint64(e0), paths.edge_row[e0:e1].copy())
+
+
+def gather_rows(bits: np.ndarray, n_cols: int, rows: np.ndarray) -> np.ndarray:
+    """Rows `rows` of a reference-layout bit matrix (bit = row * n_cols + col, LSB first, src/matrix.cpp:67-84)
+    as a new reference-layout matrix with len(rows) rows."""
+    rows = np.asarray(rows, dtype=np.int64)
+    if rows.size == 0:
+        return np.zeros(0, np.uint8)
+    if n_cols % 8 == 0:  # rows are byte aligned
+        rb = n_cols // 8
+        return np.ascontiguousarray(bits[: (int(rows.max()) + 1) * rb].reshape(-1, rb)[rows]).reshape(-1)
+    out = np.zeros((rows.size, n_cols), dtype=np.uint8)
+    for k, r in enumerate(rows):  # unaligned rows: bit-level extraction, row by row
+        b0 = int(r) * n_cols
+        seg = np.unpackbits(bits[b0 // 8:(b0 + n_cols + 7) // 8 + 1], bitorder="little")
+        out[k] = seg[b0 % 8:b0 % 8 + n_cols]
+    return np.packbits(out.reshape(-1), bitorder="little")
+
+
+def extract_snarl_shard(bits: np.ndarray | None, n_rows: int, n_cols: int, paths: SnarlPaths, s0: int,
+                        s1: int) -> SnarlShard:
+    """The self-contained problem of snarls [s0, s1): local CSR + the compact matrix of the rows they use.
+    Rows shared with a neighbouring shard are duplicated (they are read-only)."""
+    local = slice_paths(paths, s0, s1)
+    er = local.edge_row.astype(np.int64)
+    present = er != MISSING_EDGE
+    if np.any(er[present] >= n_rows):
+        raise ValueError("edge_row holds a row index >= n_rows")
+    rows = np.unique(er[present])
+    remap = er.copy()
+    remap[present] = np.searchsorted(rows, er[present])
+    local = SnarlPaths(local.snarl_path_off, local.path_edge_off, remap.astype(np.uint32))
+    local_bits = gather_rows(bits, n_cols, rows) if bits is not None else None
+    return SnarlShard(s0, s1, local, rows, local_bits, int(rows.size), n_cols)
+
+
+PER_PATH_KEYS = ("g0", "g1", "allele_paths")
+
+
+def merge_snarl_results(parts: list[dict]) -> dict:
+    """Concatenate per-rank result dicts (rank order = snarl order).  Per-path and per-snarl arrays are both
+    plain concatenations because shards are contiguous snarl ranges."""
+    if not parts:
+        return {}
+    return {k: np.concatenate([p[k] for p in parts]) for k in parts[0]}
+
+
+def run_snarl_sharded(ctx, trait: str, bits, n_rows: int, n_cols: int, paths: SnarlPaths, phenotype, rank: int,
+                      world: int, group=None, thresholds=(3, 5, 0.05), covariates=None) -> dict | None:
+    """One rank's part of a snarl-sharded run on its own GPU context; rank 0 returns the merged result.
+    No data-path collective: the only communication is the host gather of the result arrays."""
+    import torch.distributed as dist
+
+    s0, s1 = plan_snarl_shards(paths, world)[rank]
+    sh = extract_snarl_shard(bits, n_rows, n_cols, paths, s0, s1)
+    ctx.set_matrix(sh.bits if sh.n_rows else np.zeros(1, np.uint8), sh.n_rows, n_cols)
+    mi, mh, maf = thresholds
+    if trait == "binary":
+        ctx.set_binary_phenotype(phenotype)
+        part = ctx.binary_batch(sh.paths, mi, mh, maf)
+    else:
+        ctx.set_quantitative_phenotype(phenotype)
+        ctx.set_covariates(covariates)
+        part = ctx.quantitative_batch(sh.paths, mi, mh, maf)
+    if world == 1:
+        return part
+    gathered = [None] * world if rank == 0 else None
+    dist.gather_object(part, gathered, dst=0, group=group)
+    return merge_snarl_results(gathered) if rank == 0 else None
+
+
+# ---------------------------------------------------------------------------------------------------
+# sample-sharded
+# ---------------------------------------------------------------------------------------------------
+def plan_column_shards(n_cols: int, world: int, align: int = 128) -> list[tuple[int, int]]:
+    """Haplotype column ranges [c0, c1) per rank, cut at multiples of `align` columns (128 = one 16-byte chunk of
+    a repacked row; even, so both haplotypes of a sample stay together).  Trailing ranks may be empty."""
+    if n_cols % 2:
+        raise ValueError("n_cols must be even")
+    chunks = (n_cols + align - 1) // align
+    cuts = [min(n_cols, align * ((chunks * r) // world)) for r in range(world)] + [n_cols]
+    return [(cuts[r], cuts[r + 1]) for r in range(world)]
+
+
+def split_columns(bits: np.ndarray, n_rows: int, n_cols: int, c0: int, c1: int) -> np.ndarray:
+    """Columns [c0, c1) of every row as a reference-layout matrix with c1 - c0 columns."""
+    w = c1 - c0
+    if w <= 0 or n_rows == 0:
+        return np.zeros(0, np.uint8)
+    if n_cols % 8 == 0 and c0 % 8 == 0 and w % 8 == 0:
+        rb = n_cols // 8
+        return np.ascontiguousarray(bits[: n_rows * rb].reshape(n_rows, rb)[:, c0 // 8:c1 // 8]).reshape(-1)
+    dense = np.unpackbits(bits[: (n_rows * n_cols + 7) // 8], bitorder="little")[: n_rows * n_cols]
+    return np.packbits(dense.reshape(n_rows, n_cols)[:, c0:c1].reshape(-1), bitorder="little")
+
+
+class _DevU32:
+    """__cuda_array_interface__ view of a device uint32 buffer as int32 (two's-complement sums are identical),
+    so that torch / NCCL can all-reduce the context's count buffer in place."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (ptr, False), "version": 3}
+
+
+def allreduce_counts_inplace(ctx, group=None):
+    """NCCL all-reduce(sum) applied to the context's device count buffer [g0 | g1] (uint32 [2P])."""
+    import torch
+    import torch.distributed as dist
+
+    ptr, n = ctx.binary_counts_dev()
+    if n == 0:
+        return
+    t = torch.as_tensor(_DevU32(ptr, n), device=torch.device("cuda", ctx.device))
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    torch.cuda.synchronize(ctx.device)
+
+
+def run_binary_sample_sharded(ctx, bits, n_rows: int, n_cols: int, paths: SnarlPaths, is_case, rank: int, world: int,
+                              group=None, thresholds=(3, 5, 0.05)) -> dict:
+    """One rank's part of a sample-sharded binary run: count pass on the local columns, ONE all-reduce of the
+    counts, statistics on the summed counts (replicated: every rank returns the full result).
+
+    A path without checked edges matches every haplotype (src/snarl_analyzer.cpp:343-354): each rank counts its
+    own columns for it, so the sum is still the global count.  A rank whose column range is empty contributes
+    zeros and takes part in the collective."""
+    c0, c1 = plan_column_shards(n_cols, world)[rank]
+    mi, mh, maf = thresholds
+    if c1 > c0:
+        local = split_columns(bits, n_rows, n_cols, c0, c1)
+        ctx.set_matrix(local, n_rows, c1 - c0)
+        ctx.set_binary_phenotype(np.asarray(is_case, np.uint8)[c0 // 2:c1 // 2])
+        ctx.stage_paths(paths)
+        ctx.binary_counts_staged()
+    else:
+        raise ValueError("sample-sharded run needs at least 128 columns per rank")
+    if world > 1:
+        allreduce_counts_inplace(ctx, group)
+    ctx.binary_stats_staged(mi, mh, maf)
+    return ctx.binary_fetch()
