@@ -181,6 +181,53 @@ class Context:
         self._check(self._lib.stoat_gpu_quantitative_batch(self._ctx, C.byref(pc), C.byref(thr), C.byref(oc)))
         return o
 
+    # ---- eQTL: one OLS per (snarl, gene of its window) ----------------------------------------------
+    def _genes_c(self, expression, snarl_gene_off, gene_idx):
+        expr = np.ascontiguousarray(expression, dtype=np.float64)
+        keep = [expr]
+        if snarl_gene_off is None:
+            off_p, idx_p = None, None
+        else:
+            off = np.ascontiguousarray(snarl_gene_off, dtype=np.uint64)
+            idx = np.ascontiguousarray(gene_idx, dtype=np.uint32)
+            if idx.size == 0:
+                idx = np.zeros(1, np.uint32)
+            keep += [off, idx]
+            off_p, idx_p = off.ctypes.data_as(L.u64p), idx.ctypes.data_as(L.u32p)
+        g = L.EqtlGenes(expr.shape[0], expr.ctypes.data_as(L.f64p), off_p, idx_p)
+        g._keep = keep
+        return g
+
+    def eqtl_batch(self, paths: SnarlPaths, expression, snarl_gene_off=None, gene_idx=None, min_ind=3, min_hap=5,
+                   maf=0.05) -> dict:
+        """expression [n_genes, n_samples]; gene windows as CSR (None = every gene for every snarl).  Per-pair
+        outputs in CSR order (dense: pair = snarl * n_genes + gene)."""
+        S, P = paths.n_snarls, paths.n_paths
+        G = np.shape(expression)[0]
+        n_pairs = S * G if snarl_gene_off is None else int(np.asarray(snarl_gene_off)[-1])
+        o = dict(allele_paths=np.zeros(P, np.uint32), filtered=np.zeros(S, np.uint8), n_used=np.zeros(S, np.uint32),
+                 p_value=np.zeros(n_pairs), r2=np.zeros(n_pairs), beta=np.zeros(n_pairs), se=np.zeros(n_pairs),
+                 code=np.zeros(n_pairs, np.uint8))
+        oc = L.EqtlOut(o["allele_paths"].ctypes.data_as(L.u32p), o["filtered"].ctypes.data_as(L.u8p),
+                       o["n_used"].ctypes.data_as(L.u32p), o["p_value"].ctypes.data_as(L.f64p),
+                       o["r2"].ctypes.data_as(L.f64p), o["beta"].ctypes.data_as(L.f64p),
+                       o["se"].ctypes.data_as(L.f64p), o["code"].ctypes.data_as(L.u8p))
+        pc, thr, gc = paths.as_c(), self._thr(min_ind, min_hap, maf), self._genes_c(expression, snarl_gene_off, gene_idx)
+        self._check(self._lib.stoat_gpu_eqtl_batch(self._ctx, C.byref(pc), C.byref(gc), C.byref(thr), C.byref(oc)))
+        return o
+
+    def eqtl_dense_summary(self, paths: SnarlPaths, expression, p_threshold=1e-5, min_ind=3, min_hap=5,
+                           maf=0.05) -> dict:
+        """Dense (snarl x gene) scan reduced on the device: per snarl min p, its gene, and #genes with p < threshold."""
+        S = paths.n_snarls
+        o = dict(min_p=np.zeros(S), argmin_gene=np.zeros(S, np.uint32), n_below=np.zeros(S, np.uint32))
+        oc = L.EqtlSummary(o["min_p"].ctypes.data_as(L.f64p), o["argmin_gene"].ctypes.data_as(L.u32p),
+                           o["n_below"].ctypes.data_as(L.u32p))
+        pc, thr, gc = paths.as_c(), self._thr(min_ind, min_hap, maf), self._genes_c(expression, None, None)
+        self._check(self._lib.stoat_gpu_eqtl_dense_summary(self._ctx, C.byref(pc), C.byref(gc), C.byref(thr),
+                                                           C.c_double(p_threshold), C.byref(oc)))
+        return o
+
     # ---- resident mode ------------------------------------------------------------------------------
     def stage_paths(self, paths: SnarlPaths):
         pc = paths.as_c()

@@ -119,7 +119,8 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
                       &ctx->covar, &ctx->d_snarl_path_off, &ctx->d_path_edge_off, &ctx->d_edge_row, &ctx->d_rec,
                       &ctx->d_blob, &ctx->d_big, &ctx->d_counters, &ctx->counts, &ctx->total_sum, &ctx->filtered,
                       &ctx->p_a, &ctx->p_b, &ctx->code_a, &ctx->code_b, &ctx->fisher_tab, &ctx->fisher_idx, &ctx->fisher_cnt, &ctx->q_allele, &ctx->q_nused, &ctx->q_p,
-                      &ctx->q_r2, &ctx->q_beta, &ctx->q_se, &ctx->q_code};
+                      &ctx->q_r2, &ctx->q_beta, &ctx->q_se, &ctx->q_code, &ctx->e_expr, &ctx->e_gene_off, &ctx->e_gene_idx,
+                      &ctx->e_min_p, &ctx->e_argmin, &ctx->e_nbelow};
     for (DevBuf* b : bufs) b->release();
     CtxExtra* x = extra_of(ctx);
     x->q.yc.release();
@@ -539,13 +540,139 @@ int stoat_gpu_quantitative_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* path
 }
 
 // ---- eQTL ------------------------------------------------------------------------------------------
-int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths*, const stoat_gpu_eqtl_genes*,
-                         const stoat_gpu_thresholds*, stoat_gpu_eqtl_out*) {
-    return fail(ctx, STOAT_GPU_ERR_STATE, "eqtl_batch: not built yet in this revision");
+// shared front half: stage the paths, upload the expression matrix and the gene lists
+static int eqtl_stage(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const stoat_gpu_eqtl_genes* genes,
+                      uint64_t* n_pairs_out) {
+    if (!genes->expression || genes->n_genes == 0) return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl: no expression matrix");
+    if (genes->n_genes >= 0xFFFFFFFFull) return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl: too many genes");
+    if (genes->snarl_gene_off && !genes->gene_idx && paths->n_snarls && genes->snarl_gene_off[paths->n_snarls] != 0)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl: snarl_gene_off without gene_idx");
+    if (!genes->snarl_gene_off && genes->gene_idx)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl: gene_idx without snarl_gene_off");
+    if (ctx->n_covar && ctx->n_samples_covar * 2 < ctx->n_cols)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl: fewer covariate rows than samples");
+    int rc = stoat_gpu_stage_paths(ctx, paths);
+    if (rc) return rc;
+    const uint64_t S = paths->n_snarls, G = genes->n_genes, n = ctx->n_cols / 2;
+    uint64_t n_pairs = S * G;
+    if (genes->snarl_gene_off) {
+        n_pairs = S ? genes->snarl_gene_off[S] : 0;
+        for (uint64_t s = 0; s < S; ++s)
+            if (genes->snarl_gene_off[s + 1] < genes->snarl_gene_off[s])
+                return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl: snarl_gene_off is not monotone");
+        for (uint64_t k = 0; k < n_pairs; ++k)
+            if (genes->gene_idx[k] >= G) return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl: gene_idx out of range");
+    }
+    CK(ctx->e_expr.reserve(std::max<uint64_t>(G * n * 8, 16)));
+    CK(cudaMemcpyAsync(ctx->e_expr.p, genes->expression, G * n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    if (genes->snarl_gene_off) {
+        CK(ctx->e_gene_off.reserve((S + 1) * 8));
+        CK(ctx->e_gene_idx.reserve(std::max<uint64_t>(n_pairs * 4, 16)));
+        CK(cudaMemcpyAsync(ctx->e_gene_off.p, genes->snarl_gene_off, (S + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+        if (n_pairs)
+            CK(cudaMemcpyAsync(ctx->e_gene_idx.p, genes->gene_idx, n_pairs * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    const BatchDev& b = ctx->batch;
+    CK(ctx->q_allele.reserve(std::max<uint64_t>(b.n_paths * 4, 16)));
+    CK(ctx->filtered.reserve(std::max<uint64_t>(S, 16)));
+    CK(ctx->q_nused.reserve(std::max<uint64_t>(S * 4, 16)));
+    *n_pairs_out = n_pairs;
+    return STOAT_GPU_OK;
 }
-int stoat_gpu_eqtl_dense_summary(stoat_gpu_ctx* ctx, const stoat_gpu_paths*, const stoat_gpu_eqtl_genes*,
-                                 const stoat_gpu_thresholds*, double, stoat_gpu_eqtl_summary*) {
-    return fail(ctx, STOAT_GPU_ERR_STATE, "eqtl_dense_summary: not built yet in this revision");
+
+static int eqtl_reserve_pairs(stoat_gpu_ctx* ctx, uint64_t n) {
+    CK(ctx->q_p.reserve(std::max<uint64_t>(n * 8, 16)));
+    CK(ctx->q_r2.reserve(std::max<uint64_t>(n * 8, 16)));
+    CK(ctx->q_beta.reserve(std::max<uint64_t>(n * 8, 16)));
+    CK(ctx->q_se.reserve(std::max<uint64_t>(n * 8, 16)));
+    CK(ctx->q_code.reserve(std::max<uint64_t>(n, 16)));
+    return STOAT_GPU_OK;
+}
+
+static QuantOut eqtl_out_view(stoat_gpu_ctx* ctx) {
+    return QuantOut{ctx->q_allele.as<uint32_t>(), ctx->filtered.as<uint8_t>(), ctx->q_nused.as<uint32_t>(),
+                    ctx->q_p.as<double>(),        ctx->q_r2.as<double>(),      ctx->q_beta.as<double>(),
+                    ctx->q_se.as<double>(),       ctx->q_code.as<uint8_t>()};
+}
+
+int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const stoat_gpu_eqtl_genes* genes,
+                         const stoat_gpu_thresholds* thr, stoat_gpu_eqtl_out* out) {
+    if (!ctx || !paths || !genes || !thr || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl_batch: NULL argument");
+    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, "eqtl_batch: set the matrix first");
+    CK(cudaSetDevice(ctx->device));
+    uint64_t n_pairs = 0;
+    int rc = eqtl_stage(ctx, paths, genes, &n_pairs);
+    if (rc) return rc;
+    const float h2d = ctx->timing.h2d_ms;
+    if ((rc = eqtl_reserve_pairs(ctx, n_pairs))) return rc;
+    const uint64_t S = ctx->batch.n_snarls, P = ctx->batch.n_paths;
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    CK(launch_eqtl_general(matrix_view(ctx), ctx->e_expr.as<double>(), uint32_t(genes->n_genes),
+                           genes->snarl_gene_off ? ctx->e_gene_off.as<uint64_t>() : nullptr,
+                           genes->snarl_gene_off ? ctx->e_gene_idx.as<uint32_t>() : nullptr,
+                           ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar), ctx->batch, 0, S, 0,
+                           *thr, eqtl_out_view(ctx), ctx->num_sms, ctx->stream));
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    const cudaMemcpyKind k = cudaMemcpyDeviceToHost;
+    CK(cudaEventRecord(ctx->ev[6], ctx->stream));
+    if (P && out->allele_paths) CK(cudaMemcpyAsync(out->allele_paths, ctx->q_allele.p, P * 4, k, ctx->stream));
+    if (S && out->filtered) CK(cudaMemcpyAsync(out->filtered, ctx->filtered.p, S, k, ctx->stream));
+    if (S && out->n_used) CK(cudaMemcpyAsync(out->n_used, ctx->q_nused.p, S * 4, k, ctx->stream));
+    if (n_pairs && out->p_value) CK(cudaMemcpyAsync(out->p_value, ctx->q_p.p, n_pairs * 8, k, ctx->stream));
+    if (n_pairs && out->r2) CK(cudaMemcpyAsync(out->r2, ctx->q_r2.p, n_pairs * 8, k, ctx->stream));
+    if (n_pairs && out->beta) CK(cudaMemcpyAsync(out->beta, ctx->q_beta.p, n_pairs * 8, k, ctx->stream));
+    if (n_pairs && out->se) CK(cudaMemcpyAsync(out->se, ctx->q_se.p, n_pairs * 8, k, ctx->stream));
+    if (n_pairs && out->code) CK(cudaMemcpyAsync(out->code, ctx->q_code.p, n_pairs, k, ctx->stream));
+    CK(cudaEventRecord(ctx->ev[7], ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));
+    CK(cudaEventElapsedTime(&ctx->timing.d2h_ms, ctx->ev[6], ctx->ev[7]));
+    ctx->timing.h2d_ms = h2d;
+    ctx->timing.stats_ms = 0.f;
+    ctx->timing.launches = S ? 2 : 0;
+    ctx->timing.n_general = uint32_t(S);
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_eqtl_dense_summary(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const stoat_gpu_eqtl_genes* genes,
+                                 const stoat_gpu_thresholds* thr, double p_threshold, stoat_gpu_eqtl_summary* out) {
+    if (!ctx || !paths || !genes || !thr || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl_dense_summary: NULL argument");
+    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, "eqtl_dense_summary: set the matrix first");
+    if (genes->snarl_gene_off || genes->gene_idx)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl_dense_summary: dense scan only (snarl_gene_off / gene_idx must be NULL)");
+    CK(cudaSetDevice(ctx->device));
+    uint64_t n_pairs = 0;
+    int rc = eqtl_stage(ctx, paths, genes, &n_pairs);
+    if (rc) return rc;
+    const uint64_t S = ctx->batch.n_snarls, G = genes->n_genes;
+    // the pair table of a chunk of snarls stays on the device: at most ~16M pairs (0.5 GB) at a time
+    const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(S ? S : 1, (uint64_t(1) << 24) / G + 1));
+    if ((rc = eqtl_reserve_pairs(ctx, chunk * G))) return rc;
+    CK(ctx->e_min_p.reserve(std::max<uint64_t>(S * 8, 16)));
+    CK(ctx->e_argmin.reserve(std::max<uint64_t>(S * 4, 16)));
+    CK(ctx->e_nbelow.reserve(std::max<uint64_t>(S * 4, 16)));
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    uint32_t launches = 0;
+    for (uint64_t s0 = 0; s0 < S; s0 += chunk) {
+        const uint64_t ns = std::min(chunk, S - s0);
+        CK(launch_eqtl_general(matrix_view(ctx), ctx->e_expr.as<double>(), uint32_t(G), nullptr, nullptr,
+                               ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar), ctx->batch, s0,
+                               ns, s0 * G, *thr, eqtl_out_view(ctx), ctx->num_sms, ctx->stream));
+        CK(launch_eqtl_summary(ctx->q_p.as<double>(), ctx->q_code.as<uint8_t>(), ctx->filtered.as<uint8_t>(), s0, ns,
+                               uint32_t(G), p_threshold, ctx->e_min_p.as<double>(), ctx->e_argmin.as<uint32_t>(),
+                               ctx->e_nbelow.as<uint32_t>(), ctx->stream));
+        launches += 2;
+    }
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    const cudaMemcpyKind k = cudaMemcpyDeviceToHost;
+    if (S && out->min_p) CK(cudaMemcpyAsync(out->min_p, ctx->e_min_p.p, S * 8, k, ctx->stream));
+    if (S && out->argmin_gene) CK(cudaMemcpyAsync(out->argmin_gene, ctx->e_argmin.p, S * 4, k, ctx->stream));
+    if (S && out->n_below) CK(cudaMemcpyAsync(out->n_below, ctx->e_nbelow.p, S * 4, k, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));
+    ctx->timing.launches = launches + (S ? 1 : 0);
+    ctx->timing.n_general = uint32_t(S);
+    return STOAT_GPU_OK;
 }
 
 // set_precision (src/utils.cpp:5-15): iostream scientific / defaultfloat at precision 4 are "%.4e" / "%.4g"

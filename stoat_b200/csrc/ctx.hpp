@@ -106,6 +106,15 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
 cudaError_t launch_centre_permute(const double* y, uint32_t n, double mean, uint32_t n_words, double* yc, double* ys,
                                   cudaStream_t st);
 size_t quant_moments_bytes(uint64_t n_snarls);
+// eQTL (general path over snarls [s_begin, s_begin + n_snarls); per-pair outputs at pair - item_base)
+cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, uint32_t n_genes,
+                                const uint64_t* snarl_gene_off, const uint32_t* gene_idx, const double* covar,
+                                uint32_t n_covar, const BatchDev& b, uint64_t s_begin, uint64_t n_snarls,
+                                uint64_t item_base, const stoat_gpu_thresholds& thr, QuantOut out, int num_sms,
+                                cudaStream_t st);
+cudaError_t launch_eqtl_summary(const double* p, const uint8_t* code, const uint8_t* filtered, uint64_t s_begin,
+                                uint64_t n_snarls, uint32_t n_genes, double p_threshold, double* min_p,
+                                uint32_t* argmin, uint32_t* n_below, cudaStream_t st);
 
 }  // namespace stoat
 
@@ -142,6 +151,7 @@ struct stoat_gpu_ctx {
     // results (device)
     stoat::DevBuf counts, total_sum, filtered, p_a, p_b, code_a, code_b;  // binary
     stoat::DevBuf fisher_tab, fisher_idx, fisher_cnt;                      // Fisher work list
-    stoat::DevBuf q_allele, q_nused, q_p, q_r2, q_beta, q_se, q_code;      // quantitative
+    stoat::DevBuf q_allele, q_nused, q_p, q_r2, q_beta, q_se, q_code;      // quantitative / eQTL pairs
+    stoat::DevBuf e_expr, e_gene_off, e_gene_idx, e_min_p, e_argmin, e_nbelow;  // eQTL
     bool have_binary_counts = false, have_binary_result = false, have_quant_result = false;
 };

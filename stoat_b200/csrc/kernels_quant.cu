@@ -492,359 +492,8 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
     out.code[s] = kPValue;
 }
 
-// =================================================================================================
-// K3G: general path, one warp per snarl, straight from global memory
-// =================================================================================================
-struct GParams {
-    const uint8_t* rows;
-    uint32_t pitch, n_hap, n_samples;
-    const double* y;      // RAW phenotype (not centred: the pseudo-inverse branch is not shift invariant)
-    const double* covar;  // [n_samples][n_covar] row-major (indexed by FILTERED row position, see below)
-    uint32_t n_covar;
-    BatchDev b;
-    const uint32_t* list;  // nullptr: every snarl
-    const uint32_t* n_list_dev;
-    uint64_t n_list_host;  // used when list == nullptr
-    stoat_gpu_thresholds thr;
-    QuantOut out;
-};
+#include "quant_general.cuh"
 
-constexpr int kGWarps = 4;
-struct GScratch {
-    double tile[32][kMaxFeat + 1];   // X rows of the current 32 samples, last column = y
-    double beta[kMaxFeat];
-    double colsum[kMaxPathsG];
-    uint8_t cnt[32][kMaxPathsG];     // haplotype counts of the current 32 samples per kept column
-    uint8_t rs[32];                  // row sums
-    uint8_t kept[kMaxPathsG];        // kept column -> path
-    uint8_t fcol[kMaxPathsG];        // final column -> kept column
-    uint8_t fmult[kMaxPathsG];
-    uint8_t merged[kMaxPathsG];
-    uint8_t same[kMaxPathsG];
-};
-
-// word `w` (32 haplotypes) of the presence vector of path `pth`
-__device__ __forceinline__ uint32_t g_path_word(const GParams& g, uint64_t pth, uint32_t w) {
-    const uint64_t a = g.b.path_edge_off[pth], z = g.b.path_edge_off[pth + 1];
-    if (z == a) return valid_word(w, g.n_hap);
-    uint32_t v = 0xFFFFFFFFu;
-    for (uint64_t e = a; e < z; ++e) {
-        const uint32_t r = g.b.edge_row[e];
-        if (r == kMissingQ) return 0u;
-        v &= __ldg(reinterpret_cast<const uint32_t*>(g.rows + size_t(r) * g.pitch) + w);
-    }
-    return v;
-}
-
-__device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint32_t lane) {
-    const uint64_t p0 = g.b.snarl_path_off[s], p1 = g.b.snarl_path_off[s + 1];
-    const uint32_t np = uint32_t(p1 - p0);
-    const double nan = __longlong_as_double(0x7ff8000000000000LL);
-    const uint32_t n_words = g.pitch / 4;
-    auto finish_none = [&](bool filtered, uint32_t n_used, uint8_t code) {
-        if (lane == 0) {
-            g.out.filtered[s] = filtered ? 1 : 0;
-            g.out.n_used[s] = n_used;
-            g.out.p[s] = g.out.r2[s] = g.out.beta[s] = g.out.se[s] = nan;
-            g.out.code[s] = code;
-        }
-    };
-    if (np > uint32_t(kMaxPathsG)) {  // over the device limit: reported, never mangled
-        for (uint32_t j = lane; j < np; j += 32) g.out.allele_paths[p0 + j] = 0;
-        finish_none(true, 0, kPOverLimit);
-        return;
-    }
-    // ---- allele_paths and the kept columns (quantitative_table.cpp:37-58) --------------------------
-    uint32_t nk = 0;
-    for (uint32_t j = 0; j < np; ++j) {
-        uint32_t c = 0;
-        for (uint32_t w = lane; w < n_words; w += 32) c += __popc(g_path_word(g, p0 + j, w));
-        c = __reduce_add_sync(0xffffffffu, c);
-        if (lane == 0) g.out.allele_paths[p0 + j] = c;
-        if (c > 0) {
-            if (lane == 0) sc.kept[nk] = uint8_t(j);
-            ++nk;
-        }
-    }
-    __syncwarp();
-    const uint32_t n_blocks = (g.n_samples + 31) / 32;
-    // counts of the 32 samples of block `blk` for every kept column -> sc.cnt / sc.rs (lane = sample)
-    auto load_block = [&](uint32_t blk) -> uint32_t {
-        const uint32_t i = blk * 32 + lane;
-        const uint32_t w = blk * 2 + (lane >> 4);
-        const uint32_t sh = (lane & 15) * 2;
-        uint32_t rs = 0;
-        for (uint32_t c = 0; c < nk; ++c) {
-            const uint32_t v = (w < n_words) ? g_path_word(g, p0 + sc.kept[c], w) : 0u;
-            const uint32_t k = ((v >> sh) & 1u) + ((v >> (sh + 1)) & 1u);
-            sc.cnt[lane][c] = uint8_t(i < g.n_samples ? k : 0);
-            rs += (i < g.n_samples ? k : 0);
-        }
-        sc.rs[lane] = uint8_t(rs > 255 ? 255 : rs);
-        return rs;
-    };
-    // ---- sweep A: used rows, column sums in the reference's accumulation order (:558-563) ----------
-    uint32_t n_used = 0;
-    bool nondyadic = false;
-    double colsum0 = 0.0, colsum1 = 0.0;  // lane <-> column (two columns per lane when nk > 32)
-    for (uint32_t blk = 0; blk < n_blocks; ++blk) {
-        const uint32_t rs = load_block(blk);
-        const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
-        n_used += __popc(used_ballot);
-        nondyadic |= __any_sync(0xffffffffu, rs >= 3 && rs != 4 && rs != 8 && rs != 16 && rs != 32 && rs != 64);
-        __syncwarp();
-        for (uint32_t i = 0; i < 32; ++i) {
-            if (!((used_ballot >> i) & 1u)) continue;
-            const double rsum = double(sc.rs[i]);
-            if (lane < nk) {
-                const uint32_t k = sc.cnt[i][lane];
-                colsum0 += (k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;  // quantitative_table.cpp:93
-            }
-            if (lane + 32 < nk) {
-                const uint32_t k = sc.cnt[i][lane + 32];
-                colsum1 += (k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;
-            }
-        }
-        __syncwarp();
-    }
-    // remove_empty_columns is a no-op here (empty paths were never added); filtration (:549)
-    if (n_used == 0 || nk < 2 || uint64_t(n_used) < g.thr.min_individuals) {
-        finish_none(true, n_used, kPNa);
-        return;
-    }
-    if (lane < nk) sc.colsum[lane] = colsum0;
-    if (lane + 32 < nk) sc.colsum[lane + 32] = colsum1;
-    __syncwarp();
-    double total = 0.0;
-    if (!nondyadic) {
-        for (uint32_t c = 0; c < nk; ++c) total += sc.colsum[c];  // exact: every term is a multiple of 2^-6
-    } else {
-        // thirds etc.: reproduce the reference's single running sum over (row, column) (:558-563)
-        if (lane == 0) {
-            double t = 0.0;
-            for (uint32_t i = 0; i < g.n_samples; ++i) {
-                const uint32_t w = i >> 4, sh = (i & 15) * 2;
-                uint32_t rs = 0;
-                for (uint32_t c = 0; c < nk; ++c) {
-                    const uint32_t v = g_path_word(g, p0 + sc.kept[c], w);
-                    rs += ((v >> sh) & 1u) + ((v >> (sh + 1)) & 1u);
-                }
-                if (rs == 0) continue;
-                for (uint32_t c = 0; c < nk; ++c) {
-                    const uint32_t v = g_path_word(g, p0 + sc.kept[c], w);
-                    const uint32_t k = ((v >> sh) & 1u) + ((v >> (sh + 1)) & 1u);
-                    t = __dadd_rn(t, (k > 0) ? __ddiv_rn(double(k), double(rs)) : 0.0);
-                }
-            }
-            total = t;
-        }
-        total = __shfl_sync(0xffffffffu, total, 0);
-    }
-    bool filtered = total < double(g.thr.min_haplotypes);  // :565
-    if (!filtered) {
-        int above = 0;
-        for (uint32_t c = 0; c < nk; ++c) {  // :570-576
-            const double freq = __ddiv_rn(sc.colsum[c], total);
-            const double maf = fmin(freq, __dsub_rn(1.0, freq));
-            if (maf > g.thr.maf_threshold) ++above;
-        }
-        filtered = above < 2;
-    }
-    if (filtered) {
-        finish_none(true, n_used, kPNa);
-        return;
-    }
-    // ---- combine identical columns (:620-674) ------------------------------------------------------
-    uint32_t nf = 0;
-    if (lane == 0)
-        for (uint32_t c = 0; c < nk; ++c) sc.merged[c] = 0;
-    __syncwarp();
-    for (uint32_t a = 0; a < nk; ++a) {
-        if (sc.merged[a]) continue;
-        uint32_t mult = 1;
-        if (nk >= 3 && a + 1 < nk) {
-            // columns b > a identical to a over every used row (lane <-> candidate column b)
-            bool same0 = (a + 1 + lane < nk) && !sc.merged[a + 1 + lane];
-            bool same1 = (a + 33 + lane < nk) && !sc.merged[a + 33 + lane];
-            if (__any_sync(0xffffffffu, same0 || same1)) {
-                for (uint32_t blk = 0; blk < n_blocks; ++blk) {
-                    load_block(blk);
-                    __syncwarp();
-                    for (uint32_t i = 0; i < 32; ++i) {
-                        const uint8_t ka = sc.cnt[i][a];
-                        if (same0 && sc.cnt[i][a + 1 + lane] != ka) same0 = false;
-                        if (same1 && sc.cnt[i][a + 33 + lane] != ka) same1 = false;
-                    }
-                    __syncwarp();
-                }
-            }
-            if (a + 1 + lane < nk) sc.same[a + 1 + lane] = same0 ? 1 : 0;
-            if (a + 33 + lane < nk) sc.same[a + 33 + lane] = same1 ? 1 : 0;
-            __syncwarp();
-            if (lane == 0)
-                for (uint32_t b2 = a + 1; b2 < nk; ++b2)
-                    if (sc.same[b2]) sc.merged[b2] = 1;
-            __syncwarp();
-            for (uint32_t b2 = a + 1; b2 < nk; ++b2)
-                if (sc.same[b2]) ++mult;
-        }
-        if (lane == 0) {
-            sc.fcol[nf] = uint8_t(a);
-            sc.fmult[nf] = uint8_t(mult);
-        }
-        ++nf;
-        __syncwarp();
-    }
-    const uint32_t k_reg = nf - 1;  // remove_last_columns (:676-684)
-    const uint32_t p = 1 + k_reg + g.n_covar;
-    if (k_reg == 0) {  // the reference indexes past the end here (stats_test.cpp:487-489)
-        finish_none(false, n_used, kPUndef);
-        return;
-    }
-    if (p > uint32_t(kMaxFeat)) {
-        finish_none(false, n_used, kPOverLimit);
-        return;
-    }
-    // ---- sweep B: X^T X, X^T y ---------------------------------------------------------------------
-    // entries e of the packed lower triangle + X^T y + y'y are owned by lanes (e % 32)
-    const uint32_t n_tri = p * (p + 1) / 2;
-    const uint32_t n_ent = n_tri + p + 2;  // + y'y + sum y
-    double accv[6] = {0, 0, 0, 0, 0, 0};    // ceil((136 + 16 + 2) / 32) = 5
-    uint32_t rank_base = 0;
-    auto build_tile = [&](uint32_t blk, uint32_t used_ballot) {
-        // lane = sample: write its X row (zeros when unused)
-        const bool used = (used_ballot >> lane) & 1u;
-        const uint32_t i = blk * 32 + lane;
-        const uint32_t rank = rank_base + __popc(used_ballot & ((1u << lane) - 1u));
-        const double rsum = double(sc.rs[lane]);
-        sc.tile[lane][0] = used ? 1.0 : 0.0;
-        for (uint32_t a = 0; a < k_reg; ++a) {
-            const uint32_t k = sc.cnt[lane][sc.fcol[a]];
-            // merged columns are sums of identical columns (:653-658): mult * (k / row_sum)
-            double d = (used && k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;
-            double v = d;
-            for (uint32_t m = 1; m < sc.fmult[a]; ++m) v = __dadd_rn(v, d);
-            sc.tile[lane][1 + a] = v;
-        }
-        for (uint32_t c = 0; c < g.n_covar; ++c)
-            // covariate rows are taken by position in the FILTERED table (stats_test.cpp:450-452)
-            sc.tile[lane][1 + k_reg + c] = used ? g.covar[size_t(rank) * g.n_covar + c] : 0.0;
-        sc.tile[lane][kMaxFeat] = (used && i < g.n_samples) ? g.y[i] : 0.0;
-    };
-    // (row, col) of the entries this lane owns
-    uint32_t er[6], ec[6];
-#pragma unroll
-    for (int q = 0; q < 6; ++q) {
-        const uint32_t e = lane + 32u * q;
-        uint32_t r = 0;
-        while ((r + 1) * (r + 2) / 2 <= e) ++r;
-        er[q] = r;
-        ec[q] = e - r * (r + 1) / 2;
-    }
-    for (uint32_t blk = 0; blk < n_blocks; ++blk) {
-        const uint32_t rs = load_block(blk);
-        const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
-        __syncwarp();
-        build_tile(blk, used_ballot);
-        rank_base += __popc(used_ballot);
-        __syncwarp();
-#pragma unroll
-        for (int q = 0; q < 6; ++q) {
-            const uint32_t e = lane + 32u * q;
-            if (e >= n_ent) continue;
-            double a2 = 0.0;
-            if (e < n_tri) {
-                for (uint32_t i = 0; i < 32; ++i) a2 = fma(sc.tile[i][er[q]], sc.tile[i][ec[q]], a2);
-            } else if (e < n_tri + p) {
-                const uint32_t r = e - n_tri;
-                for (uint32_t i = 0; i < 32; ++i) a2 = fma(sc.tile[i][r], sc.tile[i][kMaxFeat], a2);
-            } else if (e == n_tri + p) {
-                for (uint32_t i = 0; i < 32; ++i) a2 = fma(sc.tile[i][kMaxFeat], sc.tile[i][kMaxFeat], a2);
-            } else {
-                for (uint32_t i = 0; i < 32; ++i) a2 += sc.tile[i][kMaxFeat];
-            }
-            accv[q] += a2;
-        }
-        __syncwarp();
-    }
-    // ---- solve on lane 0 ----------------------------------------------------------------------------
-    // gather the entries into lane 0 through shared memory (reuse the tile)
-    __syncwarp();
-    double* flat = &sc.tile[0][0];
-#pragma unroll
-    for (int q = 0; q < 6; ++q)
-        if (lane + 32u * q < n_ent) flat[lane + 32u * q] = accv[q];
-    __syncwarp();
-    double inv11 = 0.0, sum_y = 0.0;
-    if (lane == 0) {
-        SmallMat<kMaxFeat> X, inv;
-        uint32_t e = 0;
-        for (uint32_t r = 0; r < p; ++r)
-            for (uint32_t c = 0; c <= r; ++c, ++e) {
-                X(r, c) = flat[e];
-                X(c, r) = flat[e];
-            }
-        double xty[kMaxFeat];
-        for (uint32_t r = 0; r < p; ++r) xty[r] = flat[n_tri + r];
-        sum_y = flat[n_tri + p + 1];
-        xtx_inverse<kMaxFeat>(X, int(p), inv);
-        for (uint32_t r = 0; r < p; ++r) {
-            double b2 = 0.0;
-            for (uint32_t c = 0; c < p; ++c) b2 += inv(r, c) * xty[c];
-            sc.beta[r] = b2;
-        }
-        inv11 = inv(1, 1);
-    }
-    __syncwarp();
-    sum_y = __shfl_sync(0xffffffffu, sum_y, 0);
-    const double y_mean = sum_y / double(n_used);
-    // ---- sweep C: residuals (stats_test.cpp:459-465) -----------------------------------------------
-    double rss = 0.0, tss = 0.0;
-    rank_base = 0;
-    for (uint32_t blk = 0; blk < n_blocks; ++blk) {
-        const uint32_t rs = load_block(blk);
-        const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
-        __syncwarp();
-        build_tile(blk, used_ballot);
-        rank_base += __popc(used_ballot);
-        __syncwarp();
-        if ((used_ballot >> lane) & 1u) {
-            double pred = 0.0;
-            for (uint32_t r = 0; r < p; ++r) pred = fma(sc.tile[lane][r], sc.beta[r], pred);
-            const double yv = sc.tile[lane][kMaxFeat];
-            const double res = yv - pred;
-            rss = fma(res, res, rss);
-            const double dm = yv - y_mean;
-            tss = fma(dm, dm, tss);
-        }
-        __syncwarp();
-    }
-    rss = warp_sum(rss);
-    tss = warp_sum(tss);
-    if (lane == 0) {
-        const OlsOut o = ols_statistics(sc.beta[1], inv11, rss, tss, n_used, int(p));
-        g.out.filtered[s] = 0;
-        g.out.n_used[s] = n_used;
-        g.out.p[s] = o.p;
-        g.out.r2[s] = o.r2;
-        g.out.beta[s] = o.beta;
-        g.out.se[s] = o.se;
-        g.out.code[s] = kPValue;
-    }
-    __syncwarp();
-}
-
-__global__ void __launch_bounds__(kGWarps * 32) quant_general_kernel(const GParams g) {
-    __shared__ GScratch scratch[kGWarps];
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint64_t gw = uint64_t(blockIdx.x) * kGWarps + warp;
-    const uint64_t n_warps = uint64_t(gridDim.x) * kGWarps;
-    const uint64_t n = g.list ? uint64_t(*g.n_list_dev) : g.n_list_host;
-    for (uint64_t i = gw; i < n; i += n_warps) {
-        const uint64_t s = g.list ? g.list[i] : i;
-        quant_general(g, scratch[warp], s, lane);
-    }
-}
 
 // =================================================================================================
 // host side
@@ -926,21 +575,15 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         g.list = b.big_list;
         g.n_list_dev = b.counters;
-        const uint64_t want_g = (b.n_snarls + kGWarps - 1) / kGWarps;
-        const unsigned grid_g = unsigned(want_g < uint64_t(num_sms) * 4 ? want_g : uint64_t(num_sms) * 4);
-        quant_general_kernel<<<grid_g, kGWarps * 32, 0, st>>>(g);
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if ((e = launch_quant_general(g, b.n_snarls, num_sms, st)) != cudaSuccess) return e;
         if (launches) *launches += 3;
         return cudaSuccess;
     }
     g.list = nullptr;
     g.n_list_dev = nullptr;
     g.n_list_host = b.n_snarls;
-    const uint64_t want_g = (b.n_snarls + kGWarps - 1) / kGWarps;
-    const unsigned grid_g = unsigned(want_g < uint64_t(num_sms) * 8 ? want_g : uint64_t(num_sms) * 8);
-    quant_general_kernel<<<grid_g, kGWarps * 32, 0, st>>>(g);
     if (launches) *launches += 1;
-    return cudaGetLastError();
+    return launch_quant_general(g, b.n_snarls, num_sms, st);
 }
 
 // centre + permute the phenotype:  yc[i] = y[i] - mean;  ys[(i % 16) * n_words + i / 16] = yc[i] (0 beyond n)
@@ -962,5 +605,90 @@ cudaError_t launch_centre_permute(const double* y, uint32_t n, double mean, uint
 }
 
 size_t quant_moments_bytes(uint64_t n_snarls) { return size_t(n_snarls) * sizeof(QuantMoments); }
+
+// =================================================================================================
+// eQTL: EQTLSnarlAnalyzer::analyze_and_write_snarl (src/snarl_analyzer.cpp:493-539) on the general path —
+// snarls [s_begin, s_begin + n_snarls), per-pair outputs written at (pair index - item_base)
+// =================================================================================================
+cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, uint32_t n_genes,
+                                const uint64_t* snarl_gene_off, const uint32_t* gene_idx, const double* covar,
+                                uint32_t n_covar, const BatchDev& b, uint64_t s_begin, uint64_t n_snarls,
+                                uint64_t item_base, const stoat_gpu_thresholds& thr, QuantOut out, int num_sms,
+                                cudaStream_t st) {
+    if (n_snarls == 0) return cudaSuccess;
+    GParams g{};
+    g.rows = m.rows;
+    g.pitch = uint32_t(m.pitch);
+    g.n_hap = uint32_t(m.n_cols);
+    g.n_samples = uint32_t(m.n_cols / 2);
+    g.y = expression;
+    g.covar = covar;
+    g.n_covar = n_covar;
+    g.b = b;
+    g.thr = thr;
+    g.out = out;
+    g.n_genes = n_genes;
+    g.snarl_gene_off = snarl_gene_off;
+    g.gene_idx = gene_idx;
+    g.list = nullptr;
+    g.n_list_dev = nullptr;
+    g.n_list_host = n_snarls;
+    g.s_begin = s_begin;
+    g.item_base = item_base;
+    return launch_quant_general(g, n_snarls, num_sms, st);
+}
+
+// per-snarl reduction of a dense chunk: smallest p, its gene, number of genes with p < p_threshold
+// (the device-side stand-in for writing 4e9 TSV rows; mirrors --table-threshold, src/snarl_analyzer.cpp:524-527)
+__global__ void __launch_bounds__(128) eqtl_summary_kernel(const double* __restrict__ p, const uint8_t* __restrict__ code,
+                                                           const uint8_t* __restrict__ filtered, uint64_t s_begin,
+                                                           uint64_t n_snarls, uint32_t n_genes, double p_threshold,
+                                                           double* __restrict__ min_p, uint32_t* __restrict__ argmin,
+                                                           uint32_t* __restrict__ n_below) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t w = (uint64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    if (w >= n_snarls) return;
+    const uint64_t s = s_begin + w;
+    double best = __longlong_as_double(0x7ff0000000000000LL);  // +inf
+    uint32_t best_g = 0xFFFFFFFFu, cnt = 0;
+    if (!filtered[s]) {
+        for (uint32_t gidx = lane; gidx < n_genes; gidx += 32) {
+            const uint64_t k = w * uint64_t(n_genes) + gidx;
+            if (code[k] != kPValue) continue;
+            const double v = p[k];
+            if (v < p_threshold) ++cnt;
+            if (v < best || (v == best && gidx < best_g)) {
+                best = v;
+                best_g = gidx;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const uint32_t og = __shfl_xor_sync(0xffffffffu, best_g, o);
+        if (ob < best || (ob == best && og < best_g)) {
+            best = ob;
+            best_g = og;
+        }
+    }
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if (lane == 0) {
+        const bool none = best_g == 0xFFFFFFFFu;
+        min_p[s] = none ? __longlong_as_double(0x7ff8000000000000LL) : best;
+        argmin[s] = none ? 0u : best_g;
+        n_below[s] = cnt;
+    }
+}
+
+cudaError_t launch_eqtl_summary(const double* p, const uint8_t* code, const uint8_t* filtered, uint64_t s_begin,
+                                uint64_t n_snarls, uint32_t n_genes, double p_threshold, double* min_p,
+                                uint32_t* argmin, uint32_t* n_below, cudaStream_t st) {
+    if (n_snarls == 0) return cudaSuccess;
+    const unsigned blocks = unsigned((n_snarls + 3) / 4);
+    eqtl_summary_kernel<<<blocks, 128, 0, st>>>(p, code, filtered, s_begin, n_snarls, n_genes, p_threshold, min_p,
+                                                argmin, n_below);
+    return cudaGetLastError();
+}
 
 }  // namespace stoat

@@ -1,0 +1,451 @@
+// quant_general.cuh — K3G: the general quantitative / eQTL path (included by kernels_quant.cu, inside namespace stoat).
+//
+// One warp per snarl, any table the reference can build (<= 64 paths, <= 16 features): covariates, samples on three or
+// more path-haplotypes (non-dyadic dosages), rank-deficient designs, and the eQTL gene loop.  Follows
+//   process_table_quantitative / create_quantitative_table / create_eqtl_table   src/quantitative_table.cpp:22-133
+//   remove_empty / filtration / combine_identical / remove_last                  src/snarl_analyzer.cpp:542-684
+//   LinearRegression::linear_regression                                          src/stats_test.cpp:424-506
+//   EQTLSnarlAnalyzer::analyze_and_write_snarl (table once, one OLS per gene)    src/snarl_analyzer.cpp:493-539
+//
+// Work layout: the presence words of every kept path are ANDed once per "superblock" (32 words = 512 samples) with
+// coalesced 128-byte loads and parked in shared memory; the per-sample sweeps (lane = sample, 32 samples per block)
+// then run from shared memory.  Sweep A: used rows + column sums (filters); sweep B: X^T X, X^T y, y'y; sweep C:
+// residuals with the solved beta, as the reference does (:460-463).  For an eQTL snarl sweeps B (X^T y part only) and C
+// repeat per gene; the table, the filters and (X^T X)^-1 are done once.
+//
+// Exactness of the filters: dosages count/row_sum are dyadic unless a sample sits on >= 3 path-haplotypes, and sums of
+// dyadic values are exact in any order.  For non-dyadic snarls the sums are first taken in parallel order; only when a
+// filter comparison is within 1e-9 of its threshold is the reference's own sequential accumulation order replayed.
+#pragma once
+
+struct GParams {
+    const uint8_t* rows;
+    uint32_t pitch, n_hap, n_samples;
+    const double* y;      // quantitative: RAW phenotype [n] (the pseudo-inverse branch is not shift invariant);
+                          // eQTL: expression [n_genes][n_samples]
+    const double* covar;  // [n_samples][n_covar] row-major, indexed by FILTERED row position (stats_test.cpp:450-452)
+    uint32_t n_covar;
+    BatchDev b;
+    const uint32_t* list;  // nullptr: every snarl
+    const uint32_t* n_list_dev;
+    uint64_t n_list_host;  // used when list == nullptr
+    stoat_gpu_thresholds thr;
+    QuantOut out;  // allele_paths [P], filtered / n_used [S]; p / r2 / beta / se / code per snarl or per (snarl, gene)
+    // eQTL addressing; n_genes == 0: quantitative (one item per snarl, item index = snarl)
+    uint32_t n_genes;
+    const uint64_t* snarl_gene_off;  // nullptr with n_genes > 0: dense, item = s * n_genes + g
+    const uint32_t* gene_idx;
+    uint64_t s_begin;    // list == nullptr: snarls [s_begin, s_begin + n_list_host)
+    uint64_t item_base;  // per-item outputs are written at (item - item_base): chunked dense scans
+};
+
+constexpr int kGWarps = 4;
+struct GScratch {
+    double tile[32][kMaxFeat + 1];    // X rows of the current 32 samples, last column = y
+    double inv[kMaxFeat * kMaxFeat];  // (X^T X)^-1 of the snarl, column-major with leading dimension p
+    double beta[kMaxFeat];
+    double colsum[kMaxPathsG];
+    uint32_t pw[kMaxPathsG][32];      // presence words of the kept paths for the current superblock
+    uint8_t cnt[32][kMaxPathsG];      // haplotype counts of the current 32 samples per kept column
+    uint8_t rs[32];                   // row sums
+    uint8_t kept[kMaxPathsG];         // kept column -> path
+    uint8_t fcol[kMaxPathsG];         // final column -> kept column
+    uint8_t fmult[kMaxPathsG];
+    uint8_t merged[kMaxPathsG];
+    uint8_t same[kMaxPathsG];
+};
+
+// word `w` (32 haplotypes) of the presence vector of path `pth` (identify_path, src/snarl_analyzer.cpp:315-356)
+__device__ __forceinline__ uint32_t g_path_word(const GParams& g, uint64_t pth, uint32_t w) {
+    const uint64_t a = g.b.path_edge_off[pth], z = g.b.path_edge_off[pth + 1];
+    if (z == a) return valid_word(w, g.n_hap);
+    uint32_t v = 0xFFFFFFFFu;
+    for (uint64_t e = a; e < z; ++e) {
+        const uint32_t r = g.b.edge_row[e];
+        if (r == kMissingQ) return 0u;
+        v &= __ldg(reinterpret_cast<const uint32_t*>(g.rows + size_t(r) * g.pitch) + w);
+    }
+    return v;
+}
+
+struct GSnarl {  // warp-uniform state of the snarl being processed
+    uint64_t p0;
+    uint32_t np, nk, n_words, n_blocks;
+};
+
+// presence words of every kept column for superblock sb (lane = word)
+__device__ __forceinline__ void g_load_superblock(const GParams& g, GScratch& sc, const GSnarl& sn, uint32_t sb,
+                                                  uint32_t lane) {
+    __syncwarp();
+    const uint32_t w = sb * 32 + lane;
+    for (uint32_t c = 0; c < sn.nk; ++c) sc.pw[c][lane] = (w < sn.n_words) ? g_path_word(g, sn.p0 + sc.kept[c], w) : 0u;
+    __syncwarp();
+}
+
+// counts of the 32 samples of block blk (lane = sample) for every kept column -> sc.cnt / sc.rs; returns the row sum
+__device__ __forceinline__ uint32_t g_load_block(const GParams& g, GScratch& sc, const GSnarl& sn, uint32_t blk,
+                                                 uint32_t lane) {
+    if ((blk & 15u) == 0) g_load_superblock(g, sc, sn, blk >> 4, lane);
+    const uint32_t i = blk * 32 + lane;
+    const uint32_t wl = (blk & 15u) * 2 + (lane >> 4);
+    const uint32_t sh = (lane & 15) * 2;
+    uint32_t rs = 0;
+    for (uint32_t c = 0; c < sn.nk; ++c) {
+        const uint32_t v = sc.pw[c][wl];
+        const uint32_t k = (i < g.n_samples) ? (((v >> sh) & 1u) + ((v >> (sh + 1)) & 1u)) : 0u;
+        sc.cnt[lane][c] = uint8_t(k);
+        rs += k;
+    }
+    sc.rs[lane] = uint8_t(rs > 255 ? 255 : rs);
+    return rs;
+}
+
+// exact replay of filtration_quantitative_table's accumulation order (src/snarl_analyzer.cpp:558-576) for the rare
+// non-dyadic snarl whose filter comparison is within rounding of a threshold: `total` is one running sum over
+// (row, column); column sums accumulate down the rows.  Lane c owns column c (and c + 32); lane 0 owns the total.
+__device__ void g_exact_sums(const GParams& g, GScratch& sc, const GSnarl& sn, uint32_t lane, double& total) {
+    double colsum0 = 0.0, colsum1 = 0.0, t = 0.0;
+    for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+        const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
+        const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+        __syncwarp();
+        for (uint32_t i = 0; i < 32; ++i) {
+            if (!((used_ballot >> i) & 1u)) continue;
+            const double rsum = double(sc.rs[i]);
+            if (lane < sn.nk) {
+                const uint32_t k = sc.cnt[i][lane];
+                colsum0 = __dadd_rn(colsum0, (k > 0) ? __ddiv_rn(double(k), rsum) : 0.0);
+            }
+            if (lane + 32 < sn.nk) {
+                const uint32_t k = sc.cnt[i][lane + 32];
+                colsum1 = __dadd_rn(colsum1, (k > 0) ? __ddiv_rn(double(k), rsum) : 0.0);
+            }
+            if (lane == 0)
+                for (uint32_t c = 0; c < sn.nk; ++c) {
+                    const uint32_t k = sc.cnt[i][c];
+                    t = __dadd_rn(t, (k > 0) ? __ddiv_rn(double(k), rsum) : 0.0);
+                }
+        }
+        __syncwarp();
+    }
+    if (lane < sn.nk) sc.colsum[lane] = colsum0;
+    if (lane + 32 < sn.nk) sc.colsum[lane + 32] = colsum1;
+    total = __shfl_sync(0xffffffffu, t, 0);
+    __syncwarp();
+}
+
+__device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint32_t lane) {
+    GSnarl sn;
+    sn.p0 = g.b.snarl_path_off[s];
+    const uint64_t p1 = g.b.snarl_path_off[s + 1];
+    sn.np = uint32_t(p1 - sn.p0);
+    sn.n_words = g.pitch / 4;
+    sn.n_blocks = (g.n_samples + 31) / 32;
+    sn.nk = 0;
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    // items (regressions) of this snarl: one for the quantitative analyzer, one per gene of the window for eQTL
+    uint64_t k0 = s, k1 = s + 1;
+    if (g.n_genes) {
+        k0 = g.snarl_gene_off ? g.snarl_gene_off[s] : s * uint64_t(g.n_genes);
+        k1 = g.snarl_gene_off ? g.snarl_gene_off[s + 1] : (s + 1) * uint64_t(g.n_genes);
+    }
+    auto finish_none = [&](bool filtered, uint32_t n_used, uint8_t code) {
+        if (lane == 0) {
+            g.out.filtered[s] = filtered ? 1 : 0;
+            g.out.n_used[s] = n_used;
+        }
+        for (uint64_t k = k0 + lane; k < k1; k += 32) {
+            const uint64_t o = k - g.item_base;
+            g.out.p[o] = g.out.r2[o] = g.out.beta[o] = g.out.se[o] = nan;
+            g.out.code[o] = code;
+        }
+    };
+    if (sn.np > uint32_t(kMaxPathsG)) {  // over the device limit: reported, never mangled
+        for (uint32_t j = lane; j < sn.np; j += 32) g.out.allele_paths[sn.p0 + j] = 0;
+        finish_none(true, 0, kPOverLimit);
+        return;
+    }
+    // ---- allele_paths and the kept columns (quantitative_table.cpp:37-58) --------------------------
+    __syncwarp();
+    for (uint32_t j = 0; j < sn.np; ++j) {
+        uint32_t c = 0;
+        for (uint32_t w = lane; w < sn.n_words; w += 32) c += __popc(g_path_word(g, sn.p0 + j, w));
+        c = __reduce_add_sync(0xffffffffu, c);
+        if (lane == 0) g.out.allele_paths[sn.p0 + j] = c;
+        if (c > 0) {
+            if (lane == 0) sc.kept[sn.nk] = uint8_t(j);
+            ++sn.nk;
+        }
+    }
+    __syncwarp();
+    const uint32_t nk = sn.nk;
+    // ---- sweep A: used rows and column sums --------------------------------------------------------
+    uint32_t n_used = 0;
+    bool nondyadic = false;
+    double colsum0 = 0.0, colsum1 = 0.0;  // lane c owns column c (and c + 32)
+    for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+        const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
+        const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+        n_used += __popc(used_ballot);
+        nondyadic |= __any_sync(0xffffffffu, rs >= 3 && (rs & (rs - 1)) != 0);
+        const double rsum = double(rs);
+        for (uint32_t c = 0; c < nk; ++c) {
+            const uint32_t k = sc.cnt[lane][c];
+            const double d = (k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;  // quantitative_table.cpp:93
+            const double sum = warp_sum(d);
+            if (lane == (c & 31u)) {
+                if (c < 32) colsum0 += sum;
+                else colsum1 += sum;
+            }
+        }
+    }
+    // remove_empty_columns is a no-op here (empty paths were never added); filtration (:549)
+    if (n_used == 0 || nk < 2 || uint64_t(n_used) < g.thr.min_individuals) {
+        finish_none(true, n_used, kPNa);
+        return;
+    }
+    __syncwarp();
+    if (lane < nk) sc.colsum[lane] = colsum0;
+    if (lane + 32 < nk) sc.colsum[lane + 32] = colsum1;
+    __syncwarp();
+    double total = 0.0;
+    for (uint32_t c = 0; c < nk; ++c) total += sc.colsum[c];  // exact when every term is dyadic
+    auto run_filters = [&](double tot, bool& borderline) -> bool {
+        borderline = false;
+        const double eps = 1e-9;
+        const double mh = double(g.thr.min_haplotypes);
+        if (fabs(tot - mh) <= eps * fmax(tot, 1.0)) borderline = true;
+        bool filt = tot < mh;  // :565
+        int above = 0;
+        for (uint32_t c = 0; c < nk; ++c) {  // :570-576
+            const double freq = __ddiv_rn(sc.colsum[c], tot);
+            const double maf = fmin(freq, __dsub_rn(1.0, freq));
+            if (fabs(maf - g.thr.maf_threshold) <= eps) borderline = true;
+            if (maf > g.thr.maf_threshold) ++above;
+        }
+        return filt || above < 2;
+    };
+    bool borderline = false;
+    bool filtered = run_filters(total, borderline);
+    if (nondyadic && borderline) {
+        g_exact_sums(g, sc, sn, lane, total);
+        filtered = run_filters(total, borderline);
+    }
+    if (filtered) {
+        finish_none(true, n_used, kPNa);
+        return;
+    }
+    // ---- combine identical columns (:620-674): lane <-> candidate column b > a ----------------------
+    uint32_t nf = 0;
+    if (lane == 0)
+        for (uint32_t c = 0; c < nk; ++c) sc.merged[c] = 0;
+    __syncwarp();
+    for (uint32_t a = 0; a < nk; ++a) {
+        if (sc.merged[a]) continue;
+        uint32_t mult = 1;
+        if (nk >= 3 && a + 1 < nk) {
+            bool same0 = (a + 1 + lane < nk) && !sc.merged[a + 1 + lane];
+            bool same1 = (a + 33 + lane < nk) && !sc.merged[a + 33 + lane];
+            if (__any_sync(0xffffffffu, same0 || same1)) {
+                for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+                    g_load_block(g, sc, sn, blk, lane);
+                    __syncwarp();
+                    for (uint32_t i = 0; i < 32; ++i) {
+                        const uint8_t ka = sc.cnt[i][a];
+                        if (same0 && sc.cnt[i][a + 1 + lane] != ka) same0 = false;
+                        if (same1 && sc.cnt[i][a + 33 + lane] != ka) same1 = false;
+                    }
+                    __syncwarp();
+                    if (!__any_sync(0xffffffffu, same0 || same1)) break;
+                }
+            }
+            if (a + 1 + lane < nk) sc.same[a + 1 + lane] = same0 ? 1 : 0;
+            if (a + 33 + lane < nk) sc.same[a + 33 + lane] = same1 ? 1 : 0;
+            __syncwarp();
+            if (lane == 0)
+                for (uint32_t b2 = a + 1; b2 < nk; ++b2)
+                    if (sc.same[b2]) sc.merged[b2] = 1;
+            __syncwarp();
+            for (uint32_t b2 = a + 1; b2 < nk; ++b2)
+                if (sc.same[b2]) ++mult;
+        }
+        if (lane == 0) {
+            sc.fcol[nf] = uint8_t(a);
+            sc.fmult[nf] = uint8_t(mult);
+        }
+        ++nf;
+        __syncwarp();
+    }
+    const uint32_t k_reg = nf - 1;  // remove_last_columns (:676-684)
+    const uint32_t p = 1 + k_reg + g.n_covar;
+    if (k_reg == 0) {  // the reference indexes past the end here (stats_test.cpp:487-489)
+        finish_none(false, n_used, kPUndef);
+        return;
+    }
+    if (p > uint32_t(kMaxFeat)) {
+        finish_none(false, n_used, kPOverLimit);
+        return;
+    }
+    if (lane == 0) {
+        g.out.filtered[s] = 0;
+        g.out.n_used[s] = n_used;
+    }
+    // ---- regressions ---------------------------------------------------------------------------------
+    // entries e of [packed lower triangle of X^T X | X^T y | y'y | sum y] are owned by lanes (e % 32)
+    const uint32_t n_tri = p * (p + 1) / 2;
+    const uint32_t n_ent = n_tri + p + 2;
+    uint32_t er[6], ec[6];  // ceil((136 + 16 + 2) / 32) = 5
+#pragma unroll
+    for (int q = 0; q < 6; ++q) {
+        const uint32_t e = lane + 32u * q;
+        uint32_t r = 0;
+        while ((r + 1) * (r + 2) / 2 <= e) ++r;
+        er[q] = r;
+        ec[q] = e - r * (r + 1) / 2;
+    }
+    uint32_t rank_base = 0;
+    auto build_tile = [&](uint32_t blk, uint32_t used_ballot, const double* y) {
+        // lane = sample: write its X row (zeros when unused)
+        const bool used = (used_ballot >> lane) & 1u;
+        const uint32_t i = blk * 32 + lane;
+        const uint32_t rank = rank_base + __popc(used_ballot & ((1u << lane) - 1u));
+        const double rsum = double(sc.rs[lane]);
+        sc.tile[lane][0] = used ? 1.0 : 0.0;
+        for (uint32_t a = 0; a < k_reg; ++a) {
+            const uint32_t k = sc.cnt[lane][sc.fcol[a]];
+            // merged columns are sums of identical columns (:653-658): mult * (k / row_sum)
+            const double d = (used && k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;
+            double v = d;
+            for (uint32_t m = 1; m < sc.fmult[a]; ++m) v = __dadd_rn(v, d);
+            sc.tile[lane][1 + a] = v;
+        }
+        for (uint32_t c = 0; c < g.n_covar; ++c)
+            // covariate rows are taken by position in the FILTERED table (stats_test.cpp:450-452)
+            sc.tile[lane][1 + k_reg + c] = used ? g.covar[size_t(rank) * g.n_covar + c] : 0.0;
+        sc.tile[lane][kMaxFeat] = (used && i < g.n_samples) ? y[i] : 0.0;
+    };
+    for (uint64_t item = k0; item < k1; ++item) {
+        const bool first = (item == k0);
+        const double* y = g.y;
+        if (g.n_genes) {
+            const uint64_t gene = g.gene_idx ? uint64_t(g.gene_idx[item]) : (item - k0);
+            y = g.y + gene * uint64_t(g.n_samples);  // retain_indices(expression, index_filtered), :510-511
+        }
+        // ---- sweep B: X^T X (first item only), X^T y, y'y, sum y ------------------------------------
+        double accv[6] = {0, 0, 0, 0, 0, 0};
+        rank_base = 0;
+        for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+            const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
+            const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+            __syncwarp();
+            build_tile(blk, used_ballot, y);
+            rank_base += __popc(used_ballot);
+            __syncwarp();
+#pragma unroll
+            for (int q = 0; q < 6; ++q) {
+                const uint32_t e = lane + 32u * q;
+                if (e >= n_ent || (!first && e < n_tri)) continue;
+                double a2 = 0.0;
+                if (e < n_tri) {
+                    for (uint32_t i = 0; i < 32; ++i) a2 = fma(sc.tile[i][er[q]], sc.tile[i][ec[q]], a2);
+                } else if (e < n_tri + p) {
+                    const uint32_t r = e - n_tri;
+                    for (uint32_t i = 0; i < 32; ++i) a2 = fma(sc.tile[i][r], sc.tile[i][kMaxFeat], a2);
+                } else if (e == n_tri + p) {
+                    for (uint32_t i = 0; i < 32; ++i) a2 = fma(sc.tile[i][kMaxFeat], sc.tile[i][kMaxFeat], a2);
+                } else {
+                    for (uint32_t i = 0; i < 32; ++i) a2 += sc.tile[i][kMaxFeat];
+                }
+                accv[q] += a2;
+            }
+            __syncwarp();
+        }
+        // ---- solve on lane 0: gather the entries through shared memory (reuse the tile) --------------
+        double* flat = &sc.tile[0][0];
+#pragma unroll
+        for (int q = 0; q < 6; ++q)
+            if (lane + 32u * q < n_ent) flat[lane + 32u * q] = accv[q];
+        __syncwarp();
+        double sum_y = 0.0;
+        if (lane == 0) {
+            if (first) {
+                SmallMat<kMaxFeat> X, inv;
+                uint32_t e = 0;
+                for (uint32_t r = 0; r < p; ++r)
+                    for (uint32_t c = 0; c <= r; ++c, ++e) {
+                        X(r, c) = flat[e];
+                        X(c, r) = flat[e];
+                    }
+                xtx_inverse<kMaxFeat>(X, int(p), inv);
+                for (uint32_t r = 0; r < p; ++r)
+                    for (uint32_t c = 0; c < p; ++c) sc.inv[r + c * p] = inv(r, c);
+            }
+            sum_y = flat[n_tri + p + 1];
+            for (uint32_t r = 0; r < p; ++r) {
+                double b2 = 0.0;
+                for (uint32_t c = 0; c < p; ++c) b2 += sc.inv[r + c * p] * flat[n_tri + c];
+                sc.beta[r] = b2;
+            }
+        }
+        __syncwarp();
+        sum_y = __shfl_sync(0xffffffffu, sum_y, 0);
+        const double y_mean = sum_y / double(n_used);
+        // ---- sweep C: residuals (stats_test.cpp:459-465) ----------------------------------------------
+        double rss = 0.0, tss = 0.0;
+        rank_base = 0;
+        for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+            const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
+            const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+            __syncwarp();
+            build_tile(blk, used_ballot, y);
+            rank_base += __popc(used_ballot);
+            __syncwarp();
+            if ((used_ballot >> lane) & 1u) {
+                double pred = 0.0;
+                for (uint32_t r = 0; r < p; ++r) pred = fma(sc.tile[lane][r], sc.beta[r], pred);
+                const double yv = sc.tile[lane][kMaxFeat];
+                const double res = yv - pred;
+                rss = fma(res, res, rss);
+                const double dm = yv - y_mean;
+                tss = fma(dm, dm, tss);
+            }
+            __syncwarp();
+        }
+        rss = warp_sum(rss);
+        tss = warp_sum(tss);
+        if (lane == 0) {
+            const OlsOut o = ols_statistics(sc.beta[1], sc.inv[1 + p], rss, tss, n_used, int(p));
+            const uint64_t oi = item - g.item_base;
+            g.out.p[oi] = o.p;
+            g.out.r2[oi] = o.r2;
+            g.out.beta[oi] = o.beta;
+            g.out.se[oi] = o.se;
+            g.out.code[oi] = kPValue;
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(kGWarps * 32) quant_general_kernel(const GParams g) {
+    extern __shared__ __align__(16) uint8_t g_smem[];
+    GScratch* scratch = reinterpret_cast<GScratch*>(g_smem);
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t gw = uint64_t(blockIdx.x) * kGWarps + warp;
+    const uint64_t n_warps = uint64_t(gridDim.x) * kGWarps;
+    const uint64_t n = g.list ? uint64_t(*g.n_list_dev) : g.n_list_host;
+    for (uint64_t i = gw; i < n; i += n_warps) {
+        const uint64_t s = g.list ? g.list[i] : g.s_begin + i;
+        quant_general(g, scratch[warp], s, lane);
+    }
+}
+
+inline cudaError_t launch_quant_general(const GParams& g, uint64_t max_items, int num_sms, cudaStream_t st) {
+    const int smem = int(sizeof(GScratch) * kGWarps);
+    cudaError_t e = cudaFuncSetAttribute(quant_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    const uint64_t want = (max_items + kGWarps - 1) / kGWarps;
+    const uint64_t cap = uint64_t(num_sms) * 3;  // 3 CTAs of ~70 KB shared memory per SM
+    const unsigned grid = unsigned(want < cap ? (want ? want : 1) : cap);
+    quant_general_kernel<<<grid, kGWarps * 32, smem, st>>>(g);
+    return cudaGetLastError();
+}
