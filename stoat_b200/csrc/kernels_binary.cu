@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(128) binary_prep_kernel(BatchDev b, uint64_t n
         return;
     }
     blob[0] = uint8_t(np);
-    blob[1] = blob[2] = blob[3] = 0;
+    blob[1] = blob[2] = blob[3] = 0;  // blob[1]: shape class, set below
     *reinterpret_cast<uint32_t*>(blob + 4) = uint32_t(p0);
     uint32_t off = kBlobHeader + uint32_t(np);
     for (uint64_t j = 0; j < np; ++j) {
@@ -98,6 +98,8 @@ __global__ void __launch_bounds__(128) binary_prep_kernel(BatchDev b, uint64_t n
             blob[off++] = uint8_t(f);
         }
     }
+    // shape class 1: two paths with two checked edges each (K1's straight-line case)
+    if (np == 2 && blob[kBlobHeader] == 2 && blob[kBlobHeader + 1] == 2) blob[1] = 1;
     for (int k = 0; k < nu; ++k) rec.rows[k] = urows[k];
     rec.n_rows = uint8_t(nu);
     rec.blob_len16 = uint8_t((off + 15) / 16);
@@ -149,13 +151,33 @@ __device__ __forceinline__ void issue_stage(uint32_t rec_word, uint32_t lane, ui
     // fence.proxy.async here was measured to serialise every iteration on the in-flight bulk copies.)
     if (lane == 7) mbar_arrive_expect_tx(bar, blob_bytes + n_rows * pitch);
     __syncwarp();
-    if (lane < n_rows)
-        tma_bulk_g2s_hint(dst + kBlobBytes + lane * pitch, rows + size_t(rec_word) * pitch, pitch, bar, policy);
-    else if (lane == 6)
+    // Runs of consecutive matrix rows land in consecutive row slots of the stage: one bulk copy per run (a snarl's
+    // edges are usually neighbours in the matrix, so the common case is a single copy of n_rows * pitch bytes).
+    const uint32_t prev = __shfl_up_sync(0xffffffffu, rec_word, 1);
+    const bool head = lane < n_rows && (lane == 0 || rec_word != prev + 1u);
+    const uint32_t heads = __ballot_sync(0xffffffffu, head) | (1u << n_rows);
+    if (head) {
+        const uint32_t run = uint32_t(__ffs(int(heads >> (lane + 1))));  // distance to the next run (or the end)
+        tma_bulk_g2s_hint(dst + kBlobBytes + lane * pitch, rows + size_t(rec_word) * pitch, run * pitch, bar, policy);
+    } else if (lane == 6) {
         tma_bulk_g2s(dst, blob + size_t(rec_word) * 16, blob_bytes, bar);
+    }
 }
 
-constexpr int kGroup = 4;  // paths processed together (shared mask load, independent chains)
+// AND of R staged rows for one 16-byte chunk, then the two popcounts, packed as all | case << 16 (n_hap < 65536) or
+// kept apart.  R is a compile-time constant so the loads and ANDs are straight-line code.
+template <int R>
+__device__ __forceinline__ void path_counts(const uint8_t* rows_s, const uint8_t* mask_s, const uint32_t (&roff)[4],
+                                            uint32_t lane, uint32_t chunks, uint32_t& n_all, uint32_t& n_case) {
+    for (uint32_t c = lane; c < chunks; c += 32) {
+        uint4 v = *reinterpret_cast<const uint4*>(rows_s + roff[0] + c * 16);
+#pragma unroll
+        for (int r = 1; r < R; ++r) v = and4(v, *reinterpret_cast<const uint4*>(rows_s + roff[r] + c * 16));
+        const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
+        n_all += popc4(v);
+        n_case += popc4(and4(v, m));
+    }
+}
 
 __global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Params p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -183,6 +205,7 @@ __global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Param
     uint8_t* my_stages = stages + size_t(warp) * p.n_stages * stage_bytes;
     const uint32_t chunks = p.pitch / 16;
     const uint64_t policy = make_evict_first_policy();
+    const bool packable = p.n_hap < 65536u;  // both counts of a path fit one 32-bit warp reduction
 
     // prologue: fill the pipeline
     {
@@ -202,80 +225,85 @@ __global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Param
         mbar_wait(&my_full[stage], parity);
         const uint8_t* blob = my_stages + size_t(stage) * stage_bytes;
         const uint8_t* rows_s = blob + kBlobBytes;
-        const uint32_t np = blob[0];
+        const uint32_t hdr = *reinterpret_cast<const uint32_t*>(blob);
+        const uint32_t np = hdr & 0xFFu;
         const uint32_t p0 = *reinterpret_cast<const uint32_t*>(blob + 4);
-        uint32_t off = kBlobHeader + np;
-        for (uint32_t j0 = 0; j0 < np; j0 += kGroup) {
-            // ---- decode up to kGroup path programs (warp uniform) ------------------------------------
-            uint32_t code[kGroup], roff[kGroup][4];
-#pragma unroll
-            for (int g = 0; g < kGroup; ++g) {
-                code[g] = (j0 + g < np) ? uint32_t(blob[kBlobHeader + j0 + g]) : 0xFFu;
-                const bool live = code[g] != 0xFFu && code[g] != 0u;
-#pragma unroll
-                for (int r = 0; r < 4; ++r)
-                    roff[g][r] = (live && uint32_t(r) < code[g]) ? uint32_t(blob[off + r]) * p.pitch : 0u;
-                if (live) off += code[g];
+        if ((hdr >> 8 & 0xFFu) == 1u) {
+            // ---- the common shape: two paths with two checked edges each (a biallelic snarl) ----------
+            const uint32_t loc = uint32_t(blob[10]) | uint32_t(blob[11]) << 8 | uint32_t(blob[12]) << 16 |
+                                 uint32_t(blob[13]) << 24;
+            const uint32_t o00 = (loc & 0xFFu) * p.pitch, o01 = (loc >> 8 & 0xFFu) * p.pitch;
+            const uint32_t o10 = (loc >> 16 & 0xFFu) * p.pitch, o11 = (loc >> 24) * p.pitch;
+            uint32_t a0 = 0, c0 = 0, a1 = 0, c1 = 0;
+            for (uint32_t c = lane; c < chunks; c += 32) {
+                const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
+                const uint4 v0 = and4(*reinterpret_cast<const uint4*>(rows_s + o00 + c * 16),
+                                      *reinterpret_cast<const uint4*>(rows_s + o01 + c * 16));
+                const uint4 v1 = and4(*reinterpret_cast<const uint4*>(rows_s + o10 + c * 16),
+                                      *reinterpret_cast<const uint4*>(rows_s + o11 + c * 16));
+                a0 += popc4(v0);
+                c0 += popc4(and4(v0, m));
+                a1 += popc4(v1);
+                c1 += popc4(and4(v1, m));
             }
-            uint32_t n_all[kGroup], n_case[kGroup];
-#pragma unroll
-            for (int g = 0; g < kGroup; ++g) n_all[g] = n_case[g] = 0;
-            bool longp = false;
-#pragma unroll
-            for (int g = 0; g < kGroup; ++g) longp |= (code[g] != 0xFFu && code[g] > 4u);
-            if (!longp) {
-#pragma unroll 3
-                for (uint32_t c = lane; c < chunks; c += 32) {
-                    const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
-#pragma unroll
-                    for (int g = 0; g < kGroup; ++g) {
-                        if (code[g] == 0xFFu || code[g] == 0u) continue;  // warp uniform
-                        uint4 v = *reinterpret_cast<const uint4*>(rows_s + roff[g][0] + c * 16);
-#pragma unroll
-                        for (int r = 1; r < 4; ++r)
-                            if (uint32_t(r) < code[g])
-                                v = and4(v, *reinterpret_cast<const uint4*>(rows_s + roff[g][r] + c * 16));
-                        n_all[g] += popc4(v);
-                        n_case[g] += popc4(and4(v, m));
-                    }
-                }
+            if (packable) {
+                const uint32_t r0 = __reduce_add_sync(0xffffffffu, a0 | c0 << 16);
+                const uint32_t r1 = __reduce_add_sync(0xffffffffu, a1 | c1 << 16);
+                a0 = r0 & 0xFFFFu; c0 = r0 >> 16;
+                a1 = r1 & 0xFFFFu; c1 = r1 >> 16;
             } else {
-                // a path with more than 4 checked edges in this group: plain loops over the program
-                uint32_t o2 = off;
+                a0 = __reduce_add_sync(0xffffffffu, a0); c0 = __reduce_add_sync(0xffffffffu, c0);
+                a1 = __reduce_add_sync(0xffffffffu, a1); c1 = __reduce_add_sync(0xffffffffu, c1);
+            }
+            if (lane < 4) {  // lane = path + 2 * (cases ? 1 : 0)
+                const uint32_t a = (lane & 1u) ? a1 : a0, c = (lane & 1u) ? c1 : c0;
+                uint32_t* dst = (lane & 2u) ? p.g1 : p.g0;
+                dst[p0 + (lane & 1u)] = (lane & 2u) ? c : a - c;  // cases / controls (binary_table.cpp:35-39)
+            }
+        } else {
+            // ---- any other staged shape: one path at a time ----------------------------------------------
+            uint32_t off = kBlobHeader + np;
+            for (uint32_t j = 0; j < np; ++j) {
+                const uint32_t code = blob[kBlobHeader + j];
+                uint32_t n_all = 0, n_case = 0;
+                if (code == 0u) {  // no checked edge: every haplotype (snarl_analyzer.cpp:343-354)
+                    n_all = p.n_hap;
+                    n_case = p.n_case_hap;
+                } else if (code != 0xFFu) {
+                    if (code <= 4u) {
+                        uint32_t roff[4];
 #pragma unroll
-                for (int g = kGroup - 1; g >= 0; --g)
-                    if (code[g] != 0xFFu) o2 -= code[g];
-#pragma unroll
-                for (int g = 0; g < kGroup; ++g) {
-                    if (code[g] == 0xFFu || code[g] == 0u) continue;
-                    for (uint32_t c = lane; c < chunks; c += 32) {
-                        uint4 v = *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[o2]) * p.pitch + c * 16);
-                        for (uint32_t r = 1; r < code[g]; ++r)
-                            v = and4(v, *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[o2 + r]) * p.pitch + c * 16));
-                        const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
-                        n_all[g] += popc4(v);
-                        n_case[g] += popc4(and4(v, m));
+                        for (int r = 0; r < 4; ++r) roff[r] = (uint32_t(r) < code) ? uint32_t(blob[off + r]) * p.pitch : 0u;
+                        switch (code) {
+                            case 1: path_counts<1>(rows_s, mask_s, roff, lane, chunks, n_all, n_case); break;
+                            case 2: path_counts<2>(rows_s, mask_s, roff, lane, chunks, n_all, n_case); break;
+                            case 3: path_counts<3>(rows_s, mask_s, roff, lane, chunks, n_all, n_case); break;
+                            default: path_counts<4>(rows_s, mask_s, roff, lane, chunks, n_all, n_case); break;
+                        }
+                    } else {
+                        for (uint32_t c = lane; c < chunks; c += 32) {
+                            uint4 v = *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[off]) * p.pitch + c * 16);
+                            for (uint32_t r = 1; r < code; ++r)
+                                v = and4(v, *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[off + r]) * p.pitch + c * 16));
+                            const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
+                            n_all += popc4(v);
+                            n_case += popc4(and4(v, m));
+                        }
                     }
-                    o2 += code[g];
+                    off += code;
+                    if (packable) {
+                        const uint32_t r = __reduce_add_sync(0xffffffffu, n_all | n_case << 16);
+                        n_all = r & 0xFFFFu;
+                        n_case = r >> 16;
+                    } else {
+                        n_all = __reduce_add_sync(0xffffffffu, n_all);
+                        n_case = __reduce_add_sync(0xffffffffu, n_case);
+                    }
                 }
-            }
-            uint32_t my_all = 0, my_case = 0;
-#pragma unroll
-            for (int g = 0; g < kGroup; ++g) {
-                uint32_t a = __reduce_add_sync(0xffffffffu, n_all[g]);
-                uint32_t c1 = __reduce_add_sync(0xffffffffu, n_case[g]);
-                if (code[g] == 0u) {  // no checked edge: every haplotype (snarl_analyzer.cpp:343-354)
-                    a = p.n_hap;
-                    c1 = p.n_case_hap;
+                if (lane == 0) {
+                    p.g0[p0 + j] = n_all - n_case;  // controls  (binary_table.cpp:37-39)
+                    p.g1[p0 + j] = n_case;          // cases     (binary_table.cpp:35-36)
                 }
-                if (lane == uint32_t(g)) {
-                    my_all = a;
-                    my_case = c1;
-                }
-            }
-            if (lane < kGroup && j0 + lane < np) {
-                p.g0[p0 + j0 + lane] = my_all - my_case;  // controls  (binary_table.cpp:37-39)
-                p.g1[p0 + j0 + lane] = my_case;           // cases     (binary_table.cpp:35-36)
             }
         }
         // all lanes are done reading this stage: refill it with the snarl n_stages ahead
@@ -343,13 +371,18 @@ static bool choose_k1_config(uint32_t pitch, uint32_t stage_rows, K1Config& cfg)
     const uint32_t mask_bytes = (pitch + 127) & ~127u;
     if (mask_bytes + 2 * stage_bytes + 1024 > budget) return false;
     const uint32_t total_stages = (budget - mask_bytes - 1024) / stage_bytes;
-    uint32_t n_stages = 3;
-    if (total_stages < 3 * 4) n_stages = 2;   // few stages: prefer more warps over depth
+    // measured on B200 (C3, profiles/): 13 warps x 2 stages 0.78 ms, 8 x 3 0.92 ms, 6 x 4 1.22 ms — a warp's compute
+    // chain, not the copy depth, limits the rate, so shared memory goes to warps first
+    uint32_t n_stages = 2;
     if (const char* e = std::getenv("STOAT_GPU_K1_STAGES")) {
         const int v = std::atoi(e);
         if (v >= 2 && v <= 8 && uint32_t(v) <= total_stages) n_stages = uint32_t(v);
     }
     uint32_t n_warps = total_stages / n_stages;
+    if (const char* e = std::getenv("STOAT_GPU_K1_WARPS")) {
+        const int v = std::atoi(e);
+        if (v >= 1 && uint32_t(v) <= n_warps) n_warps = uint32_t(v);
+    }
     if (n_warps > 16) {
         n_warps = 16;
         n_stages = total_stages / 16;
@@ -502,8 +535,15 @@ __global__ void __launch_bounds__(128) binary_stats_kernel(BatchDev b, const uin
     }
 }
 
-// per-lane state of one running recurrence (see fisher_2x2 in device_math.cuh for the single-table form; this
-// is the same arithmetic, operation for operation, split at the loop body so that lanes can be refilled)
+// K2b.  One lane = one running recurrence (the same arithmetic as fisher_2x2 in device_math.cuh, operation for
+// operation, split at the loop body so that lanes can be refilled from the work list).  The body of all three loops of
+// fastFishersExactTest (src/stats_test.cpp:306-357) is
+//     d1 += 1; d2 += 1; cur_prob *= (n1 * n2) / (d1 * d2); n1 -= 1; n2 -= 1;
+// The products are carried instead of the factors:  N = n1 * n2 and D = d1 * d2 are integers below 2^53 (every count
+// is below 2^26 here; larger tables take the factor form), so  D' = D + (d1 + d2 + 1)  and  N' = N - (n1 + n2 - 1)
+// are the exactly representable values the reference's two multiplications round to — bit-identical, two DMUL fewer.
+// The quotient, the running product and the tail sums keep the reference's roundings (__ddiv_rn / __dmul_rn /
+// __dadd_rn: no FMA contraction), which the tie tests (cur_prob < kExactTestBias, tprob <= preaddp) depend on.
 __global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restrict__ tab,
                                                            const uint32_t* __restrict__ idx,
                                                            uint32_t* __restrict__ counters,  // [0] n_work, [1] next
@@ -515,10 +555,27 @@ __global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restri
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t n_work = counters[0];
     bool active = false, drained = false;
-    uint32_t snarl = 0;
-    double m11 = 0, m12 = 0, m21 = 0, m22 = 0;  // (swapped) table as doubles: exact, counts < 2^32
-    double tprob = 0, cur_prob = 0, cprob = 0, n1 = 0, n2 = 0, d1 = 0, d2 = 0;
+    uint32_t snarl = 0, a11 = 0, a12 = 0, a21 = 0, a22 = 0, rem = 0;
     int phase = 0;
+    double N = 0, sN = 0, D = 0, sD = 0, cur = 0, tprob = 0, cprob = 0;
+    auto finish = [&](double v, uint8_t code) {
+        p_fisher[snarl] = v;
+        fisher_code[snarl] = code;
+        active = false;
+    };
+    auto start_near_tail = [&]() {  // :339-344, or the final return when m11 == 0 (:359)
+        if (a11 == 0) {
+            finish(__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue);
+            return;
+        }
+        N = __dmul_rn(double(a11), double(a22));
+        sN = double(a11) + double(a22) - 1.0;
+        D = __dmul_rn(double(a12), double(a21));
+        sD = double(a12) + double(a21) + 1.0;
+        cur = kStart;
+        rem = a11;
+        phase = 3;
+    };
     for (;;) {
         const uint32_t need = __ballot_sync(0xffffffffu, !active && !drained);
         if (need) {
@@ -531,75 +588,64 @@ __global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restri
                 if (w < n_work) {
                     const uint4 t = tab[w];
                     snarl = idx[w];
-                    uint64_t a11 = t.x, a12 = t.y, a21 = t.z, a22 = t.w, u;
-                    if (a12 > a21) { u = a12; a12 = a21; a21 = u; }  // stats_test.cpp:280-284
-                    if (a11 > a22) { u = a11; a11 = a22; a22 = u; }  // :286-290
-                    if (a11 * a22 > a12 * a21) {                      // :292-299
-                        u = a11; a11 = a12; a12 = u;
-                        u = a21; a21 = a22; a22 = u;
+                    if ((t.x | t.y | t.z | t.w) >> 26) {  // products would leave the exact-integer range
+                        const PVal r = fisher_2x2(t.x, t.y, t.z, t.w);
+                        p_fisher[snarl] = r.v;
+                        fisher_code[snarl] = r.code;
+                    } else {
+                        a11 = t.x; a12 = t.y; a21 = t.z; a22 = t.w;
+                        uint32_t u;
+                        if (a12 > a21) { u = a12; a12 = a21; a21 = u; }  // stats_test.cpp:280-284
+                        if (a11 > a22) { u = a11; a11 = a22; a22 = u; }  // :286-290
+                        if (uint64_t(a11) * a22 > uint64_t(a12) * a21) {  // :292-299
+                            u = a11; a11 = a12; a12 = u;
+                            u = a21; a21 = a22; a22 = u;
+                        }
+                        N = __dmul_rn(double(a12), double(a21));
+                        sN = double(a12) + double(a21) - 1.0;
+                        D = __dmul_rn(double(a11), double(a22));
+                        sD = double(a11) + double(a22) + 1.0;
+                        tprob = kStart; cur = kStart; cprob = 0.0;
+                        rem = a12;
+                        phase = 1;
+                        active = true;
                     }
-                    m11 = double(a11); m12 = double(a12); m21 = double(a21); m22 = double(a22);
-                    tprob = kStart; cur_prob = kStart; cprob = 0.0;
-                    n1 = m12; n2 = m21; d1 = m11; d2 = m22;
-                    phase = 1;
-                    active = true;
                 } else {
                     drained = true;
                 }
             }
         }
         if (!__any_sync(0xffffffffu, active)) break;
+        if (active && rem == 0) {  // the loop of the current phase ran out before a body execution (:306, :326)
+            if (phase == 1 && cprob == 0) finish(1.0, kPOne);  // :322-324
+            else start_near_tail();
+        }
         if (active) {
-            bool done = false;
-            double res = 0.0;
-            uint8_t code = kPValue;
-            // loop conditions / transitions before a body execution
-            if (phase == 1 && !(n1 > 0.5)) {
-                if (cprob == 0) { done = true; res = 1.0; code = kPOne; }  // :322-324
-                phase = 2;
-            }
-            if (!done && phase == 2 && !(n1 > 0.5)) phase = 4;
-            if (!done && phase == 4) {
-                if (m11 == 0) {
-                    done = true;
-                    res = __ddiv_rn(tprob, __dadd_rn(cprob, tprob));  // :359
+            D = __dadd_rn(D, sD);
+            sD += 2.0;
+            cur = __dmul_rn(cur, __ddiv_rn(N, D));
+            N = __dsub_rn(N, sN);
+            sN -= 2.0;
+            --rem;
+            if (phase == 1) {
+                if (cur > DBL_MAX) {  // :312-314
+                    finish(0.0, kPZero);
+                } else if (cur < kBias) {  // :315-318
+                    tprob = __dadd_rn(tprob, cur);
+                    if (cprob == 0) finish(1.0, kPOne);
+                    else phase = 2;
                 } else {
-                    n1 = m11; n2 = m22; d1 = m12; d2 = m21;
-                    cur_prob = kStart;
-                    phase = 3;
+                    cprob = __dadd_rn(cprob, cur);
                 }
-            }
-            if (!done) {
-                d1 += 1; d2 += 1;
-                cur_prob = __dmul_rn(cur_prob, __ddiv_rn(__dmul_rn(n1, n2), __dmul_rn(d1, d2)));
-                n1 -= 1; n2 -= 1;
-                if (phase == 1) {
-                    if (cur_prob > DBL_MAX) { done = true; res = 0.0; code = kPZero; }  // :312-314
-                    else if (cur_prob < kBias) {                                          // :315-318
-                        tprob = __dadd_rn(tprob, cur_prob);
-                        if (cprob == 0) { done = true; res = 1.0; code = kPOne; }
-                        phase = 2;
-                    } else {
-                        cprob = __dadd_rn(cprob, cur_prob);
-                    }
-                } else {
-                    const double preaddp = tprob;
-                    tprob = __dadd_rn(tprob, cur_prob);
-                    if (phase == 2) {
-                        if (tprob <= preaddp) phase = 4;  // :334-336
-                    } else if (tprob <= preaddp) {
-                        done = true;
-                        res = __ddiv_rn(preaddp, __dadd_rn(cprob, preaddp));  // :352-354
-                    } else if (!(n1 > 0.5)) {
-                        done = true;
-                        res = __ddiv_rn(tprob, __dadd_rn(cprob, tprob));  // :356, :359
-                    }
+            } else {
+                const double preaddp = tprob;
+                tprob = __dadd_rn(tprob, cur);
+                if (tprob <= preaddp) {
+                    if (phase == 2) start_near_tail();  // :334-336
+                    else finish(__ddiv_rn(preaddp, __dadd_rn(cprob, preaddp)), kPValue);  // :352-354
+                } else if (phase == 3 && rem == 0) {
+                    finish(__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue);  // :356, :359
                 }
-            }
-            if (done) {
-                p_fisher[snarl] = res;
-                fisher_code[snarl] = code;
-                active = false;
             }
         }
     }
