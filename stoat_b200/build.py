@@ -59,5 +59,22 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+HOST = os.path.join(os.path.dirname(HERE), "host")
+SHIM_TEST = os.path.join(HOST, "shim_selftest")
+
+
+def build_host(force: bool = False) -> str:
+    """The C++ host shim (host/stoat_gpu_shim.cpp) + its self-test driver, linked against libstoat_gpu.so."""
+    srcs = [os.path.join(HOST, f) for f in ("shim_selftest.cpp", "stoat_gpu_shim.cpp")]
+    deps = srcs + [os.path.join(HOST, "stoat_gpu_shim.hpp"), LIB]
+    if not force and os.path.exists(SHIM_TEST) and all(os.path.getmtime(d) <= os.path.getmtime(SHIM_TEST) for d in deps):
+        return SHIM_TEST
+    cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-Wextra"] + srcs + ["-o", SHIM_TEST, "-L" + HERE, "-lstoat_gpu",
+                                                                      "-Wl,-rpath," + HERE, "-Wl,-rpath,$ORIGIN/../stoat_b200"]
+    subprocess.check_call(cmd)
+    return SHIM_TEST
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_host(force="--force" in sys.argv))

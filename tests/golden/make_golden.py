@@ -121,9 +121,10 @@ def main():
     with open(os.path.join(OUT, "unit_known_answers.json"), "w") as f:
         json.dump(unit, f, indent=1)
 
-    rows = tsv_columns("tests/expected_output/vcf/binary/binary_table_vcf.tsv",
-                       ["SNARL", "P_FISHER", "P_CHI2", "GROUP_PATHS"])
-    write_tsv("binary_table_vcf.golden.tsv", ["SNARL", "P_FISHER", "P_CHI2", "GROUP_PATHS"], rows)
+    # every column: tests/test_gpu_shim.py reproduces the file byte for byte through the C++ host shim
+    bcols = ["CHR", "START_POS", "END_POS", "SNARL", "PATH_LENGTHS", "P_FISHER", "P_CHI2", "GROUP_PATHS", "DEPTH"]
+    rows = tsv_columns("tests/expected_output/vcf/binary/binary_table_vcf.tsv", bcols)
+    write_tsv("binary_table_vcf.golden.tsv", ["#CHR"] + bcols[1:], rows)
 
     for sub in ("quantitative", "quantitative_covar"):
         rows = tsv_columns("tests/expected_output/vcf/%s/quantitative_table_vcf.tsv" % sub,
