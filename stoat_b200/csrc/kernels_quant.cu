@@ -17,9 +17,12 @@
 // RSS = y'y - 2 b'X'y + b'X'Xb well conditioned.  Snarls where that expansion would still cancel
 // (R^2 > 1 - 1e-6), and rank-deficient snarls (pseudo-inverse branch: minimum-norm beta, NOT shift invariant),
 // are re-done by K3G on the raw phenotype with an explicit residual pass, as the reference does (:460-463).
+#include <cstdlib>
+
 #include "ctx.hpp"
 #include "ols.cuh"
 #include "ptx.cuh"
+#include "stage_pipeline.cuh"
 
 namespace stoat {
 
@@ -358,6 +361,8 @@ __device__ bool quant_fast(const K3Params& p, const uint8_t* blob, const uint8_t
     return true;
 }
 
+#include "quant_lean.cuh"
+
 // =================================================================================================
 // K3 kernel: per-warp TMA pipelines (same structure as K1), fast path per snarl
 // =================================================================================================
@@ -386,35 +391,29 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
     uint8_t* my_stages = stages + size_t(warp) * p.n_stages * stage_bytes;
     const uint64_t policy = make_evict_first_policy();
 
-    auto issue = [&](const SnarlRec& r, uint32_t stage) {
-        uint8_t* dst = my_stages + size_t(stage) * stage_bytes;
-        const uint32_t blob_bytes = uint32_t(r.blob_len16) * 16;
-        mbar_arrive_expect_tx(&my_full[stage], blob_bytes + uint32_t(r.n_rows) * p.pitch);
-        tma_bulk_g2s(dst, p.blob + size_t(r.blob16) * 16, blob_bytes, &my_full[stage]);
-        for (uint32_t k = 0; k < r.n_rows; ++k)
-            tma_bulk_g2s_hint(dst + kBlobBytesQ + k * p.pitch, p.rows + size_t(r.rows[k]) * p.pitch, p.pitch,
-                              &my_full[stage], policy);
-    };
-    if (lane == 0) {
+    // prologue: fill the pipeline (lane-distributed issue, consecutive rows merged: stage_pipeline.cuh)
+    {
         uint64_t s = gw;
-        for (uint32_t st = 0; st < p.n_stages && s < p.n_snarls; ++st, s += stride) issue(p.rec[s], st);
+        for (uint32_t st = 0; st < p.n_stages && s < p.n_snarls; ++st, s += stride)
+            issue_stage(load_rec_word(p.rec, s, lane), lane, my_stages + size_t(st) * stage_bytes, &my_full[st], p.rows,
+                        p.blob, p.pitch, policy);
     }
-    __syncwarp();
 
     uint32_t it = 0;
     for (uint64_t s = gw; s < p.n_snarls; s += stride, ++it) {
         const uint32_t stage = it % p.n_stages;
         const uint32_t parity = (it / p.n_stages) & 1u;
         const uint64_t s_next = s + uint64_t(p.n_stages) * stride;
-        SnarlRec next_rec;
-        if (lane == 0 && s_next < p.n_snarls) next_rec = p.rec[s_next];
+        uint32_t next_word = (s_next < p.n_snarls) ? load_rec_word(p.rec, s_next, lane) : 0u;
         mbar_wait(&my_full[stage], parity);
         const uint8_t* blob = my_stages + size_t(stage) * stage_bytes;
         const uint8_t* rows_s = blob + kBlobBytesQ;
         const uint32_t np = blob[0];
         if (np) {  // np == 0: prep already put the snarl on the general list
             bool done = false;
-            if (np <= 2)
+            if (np == 2)
+                done = quant_lean2(p, blob, rows_s, ys_s, s, lane);
+            else if (np == 1)
                 done = quant_fast<2>(p, blob, rows_s, ys_s, np, s, lane);
             else if (np == 3)
                 done = quant_fast<3>(p, blob, rows_s, ys_s, np, s, lane);
@@ -428,7 +427,10 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
             p.mom[s].state = 0;
         }
         __syncwarp();
-        if (lane == 0 && s_next < p.n_snarls) issue(next_rec, stage);  // WAR on a read-only stage: no proxy fence
+        asm volatile("" : "+r"(next_word));
+        if (s_next < p.n_snarls)  // WAR on a read-only stage: no proxy fence (see issue_stage)
+            issue_stage(next_word, lane, my_stages + size_t(stage) * stage_bytes, &my_full[stage], p.rows, p.blob,
+                        p.pitch, policy);
     }
 }
 
@@ -502,13 +504,18 @@ struct K3Config {
     uint32_t n_warps, n_stages, stage_rows, smem_bytes;
 };
 static bool choose_k3_config(uint32_t pitch, uint32_t stage_rows, K3Config& cfg) {
-    const uint32_t budget = 200 * 1024;
+    const uint32_t budget = 220 * 1024;
     if (stage_rows == 0) stage_rows = 1;
     const uint32_t stage_bytes = kBlobBytesQ + stage_rows * pitch;
     const uint32_t ys_bytes = (16u * (pitch / 4) * 8u + 127) & ~127u;
     if (ys_bytes + 2 * stage_bytes + 1024 > budget) return false;
     const uint32_t total_stages = (budget - ys_bytes - 1024) / stage_bytes;
-    uint32_t n_stages = total_stages >= 12 ? 3 : 2;
+    // as in K1: shared memory goes to warps first (2 stages each), the compute chain of a warp limits the rate
+    uint32_t n_stages = 2;
+    if (const char* e = std::getenv("STOAT_GPU_K3_STAGES")) {
+        const int v = std::atoi(e);
+        if (v >= 2 && v <= 4 && uint32_t(v) <= total_stages) n_stages = uint32_t(v);
+    }
     uint32_t n_warps = total_stages / n_stages;
     if (n_warps > 12) n_warps = 12;
     if (n_warps == 0) return false;
