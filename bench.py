@@ -136,16 +136,52 @@ def cpu_sample_dataset(n_snarls, n_samples, seed=42):
     return synth.numpy_dataset(n_snarls, n_samples, seed=seed)
 
 
-def cpu_run(d, trait, threads, passes=1):
-    """`passes` runs of the oracle's snarl loop over the sample; -> (seconds, path tests)."""
+def cpu_kind():
+    """"reference": oracle/_ref (the reference's own analyzer sources, built by oracle/ref_build.py, shipped to the box as a
+    prebuilt .so) when it is there; "port": the oracle restatement otherwise."""
+    try:
+        from oracle import ref
+
+        if os.path.exists(ref.ref_build.LIB) or ref.available():
+            ref.lib()
+            return "reference"
+    except Exception:
+        pass
+    return "port"
+
+
+def cpu_threads(kind):
     import oracle
 
-    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    if kind == "reference":
+        from oracle import ref
+
+        return ref.num_threads()
+    return oracle.num_threads()
+
+
+def cpu_run(d, trait, threads, passes=1, kind="port"):
+    """`passes` runs of the CPU snarl loop (the reference's own analyzers, or the oracle port) over the sample;
+    -> (seconds of the loop as the reference's "Snarl time analysis" timer spans it, path tests)."""
+    import oracle
+
     secs = 0.0
+    tsv = os.path.join("/tmp", f"stoat_cpu_{os.getpid()}.tsv")
+    if kind == "reference":
+        from oracle import ref
+
+        nodes = d.get("_nodes")
+        if nodes is None:
+            nodes = d["_nodes"] = ref.nodes_from_structure(d["structure"])
+        for _ in range(passes):
+            r = ref.run(trait, d["bits"], d["n_rows"], d["n_cols"], d["paths"].snarl_path_off, nodes,
+                        is_case=d["is_case"], y=d["y"], n_threads=threads, tsv_path=tsv, parse=False)
+            secs += r["seconds"]
+        return secs, passes * d["paths"].n_paths
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
     for _ in range(passes):
         if trait == "binary":
-            r = oracle.binary_batch(d["bits"], d["n_cols"], d["is_case"], P, n_threads=threads,
-                                    tsv_path=os.path.join("/tmp", f"stoat_cpu_{os.getpid()}.tsv"))
+            r = oracle.binary_batch(d["bits"], d["n_cols"], d["is_case"], P, n_threads=threads, tsv_path=tsv)
         else:
             r = oracle.quantitative_batch(d["bits"], d["n_cols"], d["y"], P, n_threads=threads)
         secs += r["seconds"]
@@ -165,30 +201,32 @@ def cpu_sample_plan(rate, target_seconds):
     return n, passes
 
 
-def best_threads(probe, trait):
+def best_threads(probe, trait, kind):
     """All host threads unless the box's CPU quota makes one thread faster (cgroup-limited containers)."""
-    import oracle
-
     best = (1, 0.0)
-    for th in sorted({1, oracle.num_threads()}):
-        secs, tests = cpu_run(probe, trait, th)
+    for th in sorted({1, cpu_threads(kind)}):
+        secs, tests = cpu_run(probe, trait, th, kind=kind)
         if tests / max(secs, 1e-9) > best[1]:
             best = (th, tests / max(secs, 1e-9))
     return best
 
 
-def cpu_baseline(args, target_seconds):
-    """Time the oracle on a bounded sample of the same workload (same generator, same shapes)."""
-    import oracle
+CPU_WHAT = {"reference": "the reference's own analyzer sources (oracle/_ref: src/snarl_analyzer.cpp loop, tables, "
+                         "FisherKhi2 / Eigen OLS, writer; Boost tails from stand-ins) incl. per-row TSV write",
+            "port": "oracle port of the reference's OpenMP snarl loop incl. per-row TSV write"}
 
+
+def cpu_baseline(args, target_seconds):
+    """Time the CPU implementation on a bounded sample of the same workload (same generator, same shapes)."""
+    kind = cpu_kind()
     probe = cpu_sample_dataset(200, args.samples)
-    threads, rate = best_threads(probe, args.trait)
+    threads, rate = best_threads(probe, args.trait, kind)
     n, passes = cpu_sample_plan(rate, target_seconds)
     d = cpu_sample_dataset(n, args.samples)
-    secs, tests = cpu_run(d, args.trait, threads, passes)
-    return {"value": tests / secs, "unit": UNIT, "cores": threads, "kind": "port",
+    secs, tests = cpu_run(d, args.trait, threads, passes, kind=kind)
+    return {"value": tests / secs, "unit": UNIT, "cores": threads, "kind": kind,
             "sample": f"{passes} passes over the first {n} snarls ({tests} path tests in all) of the same generator, "
-                      f"{2 * args.samples} haplotypes, oracle OpenMP loop incl. per-row TSV write, {secs:.2f} s"}
+                      f"{2 * args.samples} haplotypes, {CPU_WHAT[kind]}, {secs:.2f} s"}
 
 
 def run_reference_arm(args):
@@ -198,28 +236,30 @@ def run_reference_arm(args):
     import oracle
 
     oracle.build()
+    kind = cpu_kind()
     probe = cpu_sample_dataset(200, args.samples)
-    threads, rate = best_threads(probe, args.trait)
+    threads, rate = best_threads(probe, args.trait, kind)
     # each step ~ 4 s of CPU work so that warmup + steps stay within a few minutes
     n, passes = cpu_sample_plan(rate, 4.0)
     d = cpu_sample_dataset(n, args.samples)
     for _ in range(args.warmup):
-        cpu_run(d, args.trait, threads, passes)
+        cpu_run(d, args.trait, threads, passes, kind=kind)
     total = 0.0
     tests = 0
     for _ in range(args.steps):
-        s, t = cpu_run(d, args.trait, threads, passes)
+        s, t = cpu_run(d, args.trait, threads, passes, kind=kind)
         total += s
         tests += t
     value = tests / total
     sample = (f"{passes} passes over {n} snarls ({passes * d['paths'].n_paths} path tests) per step, same generator "
-              f"and shapes, oracle port of the reference's OpenMP snarl loop incl. per-row TSV write")
+              f"and shapes, {CPU_WHAT[kind]}")
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": METRIC if args.trait == "binary" else "snarl-path tests/sec (quantitative OLS)",
+        "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32 popcounts + f64 statistics", "data": "synthetic",
         "config": config_dict(args, args.gpus),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

@@ -161,3 +161,47 @@ def assert_quant_equal(got: dict, ref: dict, rtol=1e-9):
         ok = both_nan | (err <= rtol * np.abs(b) + atols[k])
         bad = np.flatnonzero(~ok)
         assert bad.size == 0, f"{k}: {bad.size} mismatches, first got {a[bad[:3]]} want {b[bad[:3]]} idx {np.flatnonzero(m)[bad[:3]]}"
+
+
+# ---------------------------------------------------------------------------------------------------
+# result arrays (oracle or CUDA path) against TSV rows written by the reference's own analyzers (oracle/_ref)
+# ---------------------------------------------------------------------------------------------------
+def printed_close(a: str, b: str, rel=2e-4) -> bool:
+    """Printed values carry 5 significant digits; a 1e-12 relative difference may flip the last one."""
+    if a == b:
+        return True
+    try:
+        x, y = float(a), float(b)
+    except ValueError:
+        return False
+    if np.isnan(x) and np.isnan(y):
+        return True
+    return abs(x - y) <= rel * max(abs(x), abs(y))
+
+
+def assert_binary_rows(fmt, res: dict, ref_rows: dict, snarl_path_off) -> int:
+    """fmt(value, code) -> the reference's string.  Tables bit-exact, filter decisions identical, p-values as printed."""
+    spo = np.asarray(snarl_path_off, np.int64)
+    kept = np.flatnonzero(res["filtered"] == 0)
+    assert sorted(ref_rows) == list(kept), "filter decisions differ"
+    for s in kept:
+        (row,) = ref_rows[int(s)]
+        g0, g1 = res["g0"][spo[s]:spo[s + 1]], res["g1"][spo[s]:spo[s + 1]]
+        keep = (g0 + g1) > 0
+        gp = ",".join(f"{a}:{b}" for a, b in zip(g0[keep], g1[keep]))
+        assert row["GROUP_PATHS"] == gp, (s, row, gp)
+        pf, pc = fmt(res["p_fisher"][s], res["fisher_code"][s]), fmt(res["p_chi2"][s], res["chi2_code"][s])
+        assert printed_close(row["P_FISHER"], pf) and printed_close(row["P_CHI2"], pc), (s, row, pf, pc)
+    return kept.size
+
+
+def assert_quant_rows(fmt, res: dict, ref_rows: dict, snarl_path_off) -> int:
+    spo = np.asarray(snarl_path_off, np.int64)
+    kept = np.flatnonzero(res["filtered"] == 0)
+    assert sorted(ref_rows) == list(kept), "filter decisions differ"
+    for s in kept:
+        (row,) = ref_rows[int(s)]
+        assert row["ALLELE_PATHS"] == ",".join(str(v) for v in res["allele_paths"][spo[s]:spo[s + 1]]), (s, row)
+        for col, key in (("P", "p_value"), ("RSQUARE", "r2"), ("BETA", "beta"), ("SE", "se")):
+            assert printed_close(row[col], fmt(res[key][s], 0)), (s, col, row, res[key][s])
+    return kept.size
