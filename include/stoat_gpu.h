@@ -202,6 +202,14 @@ STOAT_GPU_API int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths
 STOAT_GPU_API int stoat_gpu_eqtl_dense_summary(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
                                  const stoat_gpu_eqtl_genes* genes, const stoat_gpu_thresholds* thr,
                                  double p_threshold, stoat_gpu_eqtl_summary* out);
+/* Dense scan, resident mode: the expression matrix [n_genes][n_samples] (gene major, the sampleExpresion vectors of
+ * Qtl_data, src/arg_parser.hpp:49-62) is uploaded and centred once; the scan then runs over the staged paths
+ * (stoat_gpu_stage_paths) without host traffic and its per-snarl summary is fetched separately.  Two-path snarls with
+ * dyadic dosages and no covariates take the FP64 tensor-core contraction, every other snarl the general kernel.   */
+STOAT_GPU_API int stoat_gpu_set_expression(stoat_gpu_ctx* ctx, const double* expression, uint64_t n_genes);
+STOAT_GPU_API int stoat_gpu_set_expression_dev(stoat_gpu_ctx* ctx, const double* expression_dev, uint64_t n_genes);
+STOAT_GPU_API int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, double p_threshold);
+STOAT_GPU_API int stoat_gpu_eqtl_summary_fetch(stoat_gpu_ctx* ctx, stoat_gpu_eqtl_summary* out);
 
 /* ---- resident mode: inputs staged once, kernels re-run without host traffic ------------ */
 /* Copy the CSR to the device and keep it (and result buffers) resident in the context.     */

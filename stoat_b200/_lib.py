@@ -71,6 +71,10 @@ SIGNATURES = {
                                        C.POINTER(EqtlOut)]),
     "stoat_gpu_eqtl_dense_summary": (C.c_int, [CTX, C.POINTER(PathsC), C.POINTER(EqtlGenes), C.POINTER(Thresholds),
                                                C.c_double, C.POINTER(EqtlSummary)]),
+    "stoat_gpu_set_expression": (C.c_int, [CTX, C.c_void_p, C.c_uint64]),
+    "stoat_gpu_set_expression_dev": (C.c_int, [CTX, C.c_void_p, C.c_uint64]),
+    "stoat_gpu_eqtl_dense_run_staged": (C.c_int, [CTX, C.POINTER(Thresholds), C.c_double]),
+    "stoat_gpu_eqtl_summary_fetch": (C.c_int, [CTX, C.POINTER(EqtlSummary)]),
     "stoat_gpu_stage_paths": (C.c_int, [CTX, C.POINTER(PathsC)]),
     "stoat_gpu_binary_run_staged": (C.c_int, [CTX, C.POINTER(Thresholds)]),
     "stoat_gpu_quantitative_run_staged": (C.c_int, [CTX, C.POINTER(Thresholds)]),

@@ -229,6 +229,26 @@ class Context:
         return o
 
     # ---- resident mode ------------------------------------------------------------------------------
+    def set_expression(self, expression):
+        """Upload + centre the expression matrix [n_genes, n_samples] for dense scans (resident)."""
+        a = np.ascontiguousarray(expression, dtype=np.float64)
+        self._check(self._lib.stoat_gpu_set_expression(self._ctx, _ptr(a), a.shape[0]))
+
+    def set_expression_dev(self, dev_ptr: int, n_genes: int):
+        self._check(self._lib.stoat_gpu_set_expression_dev(self._ctx, C.c_void_p(dev_ptr), n_genes))
+
+    def eqtl_dense_run_staged(self, p_threshold=1e-5, min_ind=3, min_hap=5, maf=0.05):
+        thr = self._thr(min_ind, min_hap, maf)
+        self._check(self._lib.stoat_gpu_eqtl_dense_run_staged(self._ctx, C.byref(thr), C.c_double(p_threshold)))
+
+    def eqtl_summary_fetch(self) -> dict:
+        S, _ = self._staged
+        o = dict(min_p=np.zeros(S), argmin_gene=np.zeros(S, np.uint32), n_below=np.zeros(S, np.uint32))
+        oc = L.EqtlSummary(o["min_p"].ctypes.data_as(L.f64p), o["argmin_gene"].ctypes.data_as(L.u32p),
+                           o["n_below"].ctypes.data_as(L.u32p))
+        self._check(self._lib.stoat_gpu_eqtl_summary_fetch(self._ctx, C.byref(oc)))
+        return o
+
     def stage_paths(self, paths: SnarlPaths):
         pc = paths.as_c()
         self._check(self._lib.stoat_gpu_stage_paths(self._ctx, C.byref(pc)))

@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "ctx.hpp"
+#include "eqtl_dense.hpp"
 
 using namespace stoat;
 
@@ -107,6 +108,8 @@ int stoat_gpu_create(stoat_gpu_ctx** out, int device) {
         }
     const char* k1 = std::getenv("STOAT_GPU_K1");
     ctx->k1_variant = (k1 && std::strcmp(k1, "ldg") == 0) ? 1 : 0;
+    const char* eq = std::getenv("STOAT_GPU_EQTL");
+    ctx->eqtl_variant = (eq && std::strcmp(eq, "general") == 0) ? 1 : 0;
     *out = ctx;
     return STOAT_GPU_OK;
 }
@@ -634,6 +637,166 @@ int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const
     return STOAT_GPU_OK;
 }
 
+// ---- dense eQTL scan -------------------------------------------------------------------------------
+// |t| below which the two-sided NORMAL tail is already >= p_threshold; Student's t has the heavier tail for every df,
+// so such a pair can not have p < p_threshold and its exact tail need not be evaluated.
+static double eqtl_z_threshold(double p_threshold) {
+    if (!(p_threshold > 0.0)) return 1e300;  // nothing is below
+    if (p_threshold > 1.0) return -1.0;      // everything is
+    double lo = 0.0, hi = 40.0;              // erfc(40 / sqrt 2) underflows: p below ~1e-350 is never reached
+    for (int i = 0; i < 200; ++i) {
+        const double mid = 0.5 * (lo + hi);
+        if (std::erfc(mid * 0.7071067811865476) > p_threshold) lo = mid; else hi = mid;
+    }
+    return lo * (1.0 - 1e-9);
+}
+
+// centre + pad the expression matrix that already sits in ctx->e_expr
+static int eqtl_prepare_expression(stoat_gpu_ctx* ctx, uint64_t G) {
+    const uint64_t n = ctx->n_cols / 2, n_pad = (ctx->pitch / 16) * uint64_t(kEqKT);
+    CK(ctx->e_yc.reserve(std::max<uint64_t>(G * n_pad * 8, 16)));
+    CK(ctx->e_tot.reserve(std::max<uint64_t>(G * 8, 16)));
+    CK(ctx->e_tot2.reserve(std::max<uint64_t>(G * 8, 16)));
+    CK(launch_eqtl_centre(ctx->e_expr.as<double>(), uint32_t(G), uint32_t(n), uint32_t(n_pad), ctx->e_yc.as<double>(),
+                          ctx->e_tot.as<double>(), ctx->e_tot2.as<double>(), ctx->stream));
+    ctx->e_n_genes = G;
+    ctx->have_expression = true;
+    return STOAT_GPU_OK;
+}
+
+static int eqtl_check_expression_args(stoat_gpu_ctx* ctx, const void* expr, uint64_t n_genes, const char* who) {
+    if (!ctx || !expr || n_genes == 0) return fail(ctx, STOAT_GPU_ERR_ARG, std::string(who) + ": no expression matrix");
+    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, std::string(who) + ": set the matrix first");
+    if (n_genes >= 0xFFFFFFFFull) return fail(ctx, STOAT_GPU_ERR_ARG, std::string(who) + ": too many genes");
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_set_expression(stoat_gpu_ctx* ctx, const double* expression, uint64_t n_genes) {
+    if (int rc = eqtl_check_expression_args(ctx, expression, n_genes, "set_expression")) return rc;
+    CK(cudaSetDevice(ctx->device));
+    const uint64_t n = ctx->n_cols / 2;
+    CK(ctx->e_expr.reserve(std::max<uint64_t>(n_genes * n * 8, 16)));
+    CK(cudaMemcpyAsync(ctx->e_expr.p, expression, n_genes * n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    if (int rc = eqtl_prepare_expression(ctx, n_genes)) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_set_expression_dev(stoat_gpu_ctx* ctx, const double* expression_dev, uint64_t n_genes) {
+    if (int rc = eqtl_check_expression_args(ctx, expression_dev, n_genes, "set_expression_dev")) return rc;
+    CK(cudaSetDevice(ctx->device));
+    const uint64_t n = ctx->n_cols / 2;
+    CK(ctx->e_expr.reserve(std::max<uint64_t>(n_genes * n * 8, 16)));
+    CK(cudaMemcpyAsync(ctx->e_expr.p, expression_dev, n_genes * n * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (int rc = eqtl_prepare_expression(ctx, n_genes)) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return STOAT_GPU_OK;
+}
+
+// the scan over the staged batch and the resident expression matrix; results stay on the device
+int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, double p_threshold) {
+    if (!ctx || !thr) return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl_dense_run_staged: NULL argument");
+    if (!ctx->have_matrix || !ctx->have_batch || !ctx->have_expression)
+        return fail(ctx, STOAT_GPU_ERR_STATE, "eqtl_dense_run_staged: needs the matrix, staged paths and the expression matrix");
+    if (ctx->n_covar && ctx->n_samples_covar * 2 < ctx->n_cols)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl: fewer covariate rows than samples");
+    CK(cudaSetDevice(ctx->device));
+    const BatchDev& b = ctx->batch;
+    const uint64_t S = b.n_snarls, G = ctx->e_n_genes, n = ctx->n_cols / 2;
+    CK(ctx->q_allele.reserve(std::max<uint64_t>(b.n_paths * 4, 16)));
+    CK(ctx->filtered.reserve(std::max<uint64_t>(S, 16)));
+    CK(ctx->q_nused.reserve(std::max<uint64_t>(S * 4, 16)));
+    CK(ctx->e_min_p.reserve(std::max<uint64_t>(S * 8, 16)));
+    CK(ctx->e_argmin.reserve(std::max<uint64_t>(S * 4, 16)));
+    CK(ctx->e_nbelow.reserve(std::max<uint64_t>(S * 4, 16)));
+    EqtlDense e{};
+    e.yc = ctx->e_yc.as<double>();
+    e.tot = ctx->e_tot.as<double>();
+    e.tot2 = ctx->e_tot2.as<double>();
+    e.n_genes = uint32_t(G);
+    e.n_samples = uint32_t(n);
+    e.n_kst = uint32_t(ctx->pitch / 16);
+    e.n_pad = e.n_kst * kEqKT;
+    e.n_snarls = S;
+    e.s_pad = (S + kEqTileS - 1) / kEqTileS * kEqTileS;
+    // a gene group's rows of yc (~48 MB) stay L2 resident while every snarl tile passes over them
+    const uint64_t row_bytes = uint64_t(e.n_pad) * 8;
+    uint64_t gpg = std::max<uint64_t>(1, (uint64_t(48) << 20) / row_bytes / kEqTileG) * kEqTileG;
+    if (const char* v = std::getenv("STOAT_GPU_EQTL_GROUP")) gpg = std::max<uint64_t>(1, uint64_t(std::atoll(v)) / kEqTileG) * kEqTileG;
+    e.genes_per_group = uint32_t(std::min<uint64_t>(gpg, (G + kEqTileG - 1) / kEqTileG * kEqTileG));
+    e.n_groups = uint32_t((G + e.genes_per_group - 1) / e.genes_per_group);
+    CK(ctx->e_dcode.reserve(std::max<uint64_t>(uint64_t(e.n_kst) * e.s_pad * 16, 16)));
+    CK(ctx->e_rec.reserve(std::max<uint64_t>(e.s_pad * sizeof(EqtlRec), 16)));
+    CK(ctx->e_fb_list.reserve(std::max<uint64_t>(e.s_pad * 4, 16)));
+    CK(ctx->e_fb_count.reserve(16));
+    CK(ctx->e_part_key.reserve(std::max<uint64_t>(uint64_t(e.n_groups) * e.s_pad * 8, 16)));
+    CK(ctx->e_part_gene.reserve(std::max<uint64_t>(uint64_t(e.n_groups) * e.s_pad * 4, 16)));
+    CK(ctx->e_part_cnt.reserve(std::max<uint64_t>(uint64_t(e.n_groups) * e.s_pad * 4, 16)));
+    e.dcode = ctx->e_dcode.as<uint8_t>();
+    e.rec = ctx->e_rec.as<EqtlRec>();
+    e.fb_list = ctx->e_fb_list.as<uint32_t>();
+    e.fb_count = ctx->e_fb_count.as<uint32_t>();
+    e.part_key = ctx->e_part_key.as<double>();
+    e.part_gene = ctx->e_part_gene.as<uint32_t>();
+    e.part_cnt = ctx->e_part_cnt.as<uint32_t>();
+    e.p_threshold = p_threshold;
+    e.z_threshold = eqtl_z_threshold(p_threshold);
+    e.min_p = ctx->e_min_p.as<double>();
+    e.argmin = ctx->e_argmin.as<uint32_t>();
+    e.n_below = ctx->e_nbelow.as<uint32_t>();
+    const bool allow_dense = ctx->eqtl_variant == 0 && ctx->n_covar == 0;
+
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    CK(cudaMemsetAsync(e.fb_count, 0, 4, ctx->stream));
+    CK(launch_eqtl_dosage_codes(matrix_view(ctx), b, *thr, allow_dense, e, eqtl_out_view(ctx), ctx->stream));
+    uint32_t launches = 1;
+    if (allow_dense && S) {
+        CK(launch_eqtl_dense(e, ctx->num_sms, ctx->stream));
+        CK(launch_eqtl_dense_finish(e, ctx->stream));
+        launches += 2;
+    }
+    CK(cudaEventRecord(ctx->ev[4], ctx->stream));
+    // snarls the dense path does not take (other shapes, covariates): the general kernel, a chunk of pairs at a time
+    uint32_t n_fb = 0;
+    CK(cudaMemcpyAsync(&n_fb, e.fb_count, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (n_fb) {
+        const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(n_fb, (uint64_t(1) << 24) / G + 1));
+        if (int rc = eqtl_reserve_pairs(ctx, chunk * G)) return rc;
+        for (uint64_t i0 = 0; i0 < n_fb; i0 += chunk) {
+            const uint64_t ns = std::min<uint64_t>(chunk, n_fb - i0);
+            CK(launch_eqtl_general(matrix_view(ctx), ctx->e_expr.as<double>(), uint32_t(G), nullptr, nullptr,
+                                   ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar), b, 0, ns, 0,
+                                   *thr, eqtl_out_view(ctx), ctx->num_sms, ctx->stream, e.fb_list + i0));
+            CK(launch_eqtl_summary(ctx->q_p.as<double>(), ctx->q_code.as<uint8_t>(), ctx->filtered.as<uint8_t>(), 0, ns,
+                                   uint32_t(G), p_threshold, e.min_p, e.argmin, e.n_below, ctx->stream, e.fb_list + i0));
+            launches += 2;
+        }
+    }
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[4]));   // E0 + E1 + E2 (dense path)
+    CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ctx->ev[4], ctx->ev[3]));   // general path for the rest
+    ctx->timing.launches = launches;
+    ctx->timing.n_general = n_fb;
+    ctx->have_eqtl_summary = true;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_eqtl_summary_fetch(stoat_gpu_ctx* ctx, stoat_gpu_eqtl_summary* out) {
+    if (!ctx || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl_summary_fetch: NULL argument");
+    if (!ctx->have_eqtl_summary) return fail(ctx, STOAT_GPU_ERR_STATE, "eqtl_summary_fetch: no scan has run");
+    CK(cudaSetDevice(ctx->device));
+    const uint64_t S = ctx->batch.n_snarls;
+    const cudaMemcpyKind k = cudaMemcpyDeviceToHost;
+    if (S && out->min_p) CK(cudaMemcpyAsync(out->min_p, ctx->e_min_p.p, S * 8, k, ctx->stream));
+    if (S && out->argmin_gene) CK(cudaMemcpyAsync(out->argmin_gene, ctx->e_argmin.p, S * 4, k, ctx->stream));
+    if (S && out->n_below) CK(cudaMemcpyAsync(out->n_below, ctx->e_nbelow.p, S * 4, k, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return STOAT_GPU_OK;
+}
+
+// the drop-in call with host buffers: stage + upload + scan + fetch
 int stoat_gpu_eqtl_dense_summary(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const stoat_gpu_eqtl_genes* genes,
                                  const stoat_gpu_thresholds* thr, double p_threshold, stoat_gpu_eqtl_summary* out) {
     if (!ctx || !paths || !genes || !thr || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl_dense_summary: NULL argument");
@@ -644,35 +807,9 @@ int stoat_gpu_eqtl_dense_summary(stoat_gpu_ctx* ctx, const stoat_gpu_paths* path
     uint64_t n_pairs = 0;
     int rc = eqtl_stage(ctx, paths, genes, &n_pairs);
     if (rc) return rc;
-    const uint64_t S = ctx->batch.n_snarls, G = genes->n_genes;
-    // the pair table of a chunk of snarls stays on the device: at most ~16M pairs (0.5 GB) at a time
-    const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(S ? S : 1, (uint64_t(1) << 24) / G + 1));
-    if ((rc = eqtl_reserve_pairs(ctx, chunk * G))) return rc;
-    CK(ctx->e_min_p.reserve(std::max<uint64_t>(S * 8, 16)));
-    CK(ctx->e_argmin.reserve(std::max<uint64_t>(S * 4, 16)));
-    CK(ctx->e_nbelow.reserve(std::max<uint64_t>(S * 4, 16)));
-    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
-    uint32_t launches = 0;
-    for (uint64_t s0 = 0; s0 < S; s0 += chunk) {
-        const uint64_t ns = std::min(chunk, S - s0);
-        CK(launch_eqtl_general(matrix_view(ctx), ctx->e_expr.as<double>(), uint32_t(G), nullptr, nullptr,
-                               ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar), ctx->batch, s0,
-                               ns, s0 * G, *thr, eqtl_out_view(ctx), ctx->num_sms, ctx->stream));
-        CK(launch_eqtl_summary(ctx->q_p.as<double>(), ctx->q_code.as<uint8_t>(), ctx->filtered.as<uint8_t>(), s0, ns,
-                               uint32_t(G), p_threshold, ctx->e_min_p.as<double>(), ctx->e_argmin.as<uint32_t>(),
-                               ctx->e_nbelow.as<uint32_t>(), ctx->stream));
-        launches += 2;
-    }
-    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
-    const cudaMemcpyKind k = cudaMemcpyDeviceToHost;
-    if (S && out->min_p) CK(cudaMemcpyAsync(out->min_p, ctx->e_min_p.p, S * 8, k, ctx->stream));
-    if (S && out->argmin_gene) CK(cudaMemcpyAsync(out->argmin_gene, ctx->e_argmin.p, S * 4, k, ctx->stream));
-    if (S && out->n_below) CK(cudaMemcpyAsync(out->n_below, ctx->e_nbelow.p, S * 4, k, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));
-    ctx->timing.launches = launches + (S ? 1 : 0);
-    ctx->timing.n_general = uint32_t(S);
-    return STOAT_GPU_OK;
+    if ((rc = eqtl_prepare_expression(ctx, genes->n_genes))) return rc;
+    if ((rc = stoat_gpu_eqtl_dense_run_staged(ctx, thr, p_threshold))) return rc;
+    return stoat_gpu_eqtl_summary_fetch(ctx, out);
 }
 
 // set_precision (src/utils.cpp:5-15): iostream scientific / defaultfloat at precision 4 are "%.4e" / "%.4g"

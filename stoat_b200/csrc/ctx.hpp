@@ -111,10 +111,10 @@ cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, ui
                                 const uint64_t* snarl_gene_off, const uint32_t* gene_idx, const double* covar,
                                 uint32_t n_covar, const BatchDev& b, uint64_t s_begin, uint64_t n_snarls,
                                 uint64_t item_base, const stoat_gpu_thresholds& thr, QuantOut out, int num_sms,
-                                cudaStream_t st);
+                                cudaStream_t st, const uint32_t* list = nullptr);
 cudaError_t launch_eqtl_summary(const double* p, const uint8_t* code, const uint8_t* filtered, uint64_t s_begin,
                                 uint64_t n_snarls, uint32_t n_genes, double p_threshold, double* min_p,
-                                uint32_t* argmin, uint32_t* n_below, cudaStream_t st);
+                                uint32_t* argmin, uint32_t* n_below, cudaStream_t st, const uint32_t* list = nullptr);
 
 }  // namespace stoat
 
@@ -153,5 +153,10 @@ struct stoat_gpu_ctx {
     stoat::DevBuf fisher_tab, fisher_idx, fisher_cnt;                      // Fisher work list
     stoat::DevBuf q_allele, q_nused, q_p, q_r2, q_beta, q_se, q_code;      // quantitative / eQTL pairs
     stoat::DevBuf e_expr, e_gene_off, e_gene_idx, e_min_p, e_argmin, e_nbelow;  // eQTL
+    // dense eQTL scan (kernels_eqtl.cu)
+    stoat::DevBuf e_yc, e_tot, e_tot2, e_dcode, e_rec, e_fb_list, e_fb_count, e_part_key, e_part_gene, e_part_cnt;
+    uint64_t e_n_genes = 0;
+    bool have_expression = false, have_eqtl_summary = false;
+    int eqtl_variant = 0;  // 0 = dense DMMA path where it applies (default), 1 = general kernel only (STOAT_GPU_EQTL=general)
     bool have_binary_counts = false, have_binary_result = false, have_quant_result = false;
 };

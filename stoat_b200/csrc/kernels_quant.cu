@@ -20,6 +20,7 @@
 #include <cstdlib>
 
 #include "ctx.hpp"
+#include "dosage_masks.cuh"
 #include "ols.cuh"
 #include "ptx.cuh"
 #include "stage_pipeline.cuh"
@@ -59,12 +60,6 @@ struct K3Params {
     uint32_t* g_count;
 };
 
-__device__ __forceinline__ uint32_t valid_word(uint32_t w, uint32_t n_hap) {
-    const uint32_t lo = w * 32;
-    if (lo + 32 <= n_hap) return 0xFFFFFFFFu;
-    if (lo >= n_hap) return 0u;
-    return (1u << (n_hap - lo)) - 1u;
-}
 
 template <int NP>
 __device__ __forceinline__ uint32_t pick(const uint32_t (&a)[NP], int j) {
@@ -621,7 +616,7 @@ cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, ui
                                 const uint64_t* snarl_gene_off, const uint32_t* gene_idx, const double* covar,
                                 uint32_t n_covar, const BatchDev& b, uint64_t s_begin, uint64_t n_snarls,
                                 uint64_t item_base, const stoat_gpu_thresholds& thr, QuantOut out, int num_sms,
-                                cudaStream_t st) {
+                                cudaStream_t st, const uint32_t* list) {
     if (n_snarls == 0) return cudaSuccess;
     GParams g{};
     g.rows = m.rows;
@@ -637,11 +632,12 @@ cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, ui
     g.n_genes = n_genes;
     g.snarl_gene_off = snarl_gene_off;
     g.gene_idx = gene_idx;
-    g.list = nullptr;
+    g.list = list;  // list != nullptr: snarls list[0 .. n_snarls), items of entry i at [i * n_genes, (i + 1) * n_genes)
     g.n_list_dev = nullptr;
     g.n_list_host = n_snarls;
     g.s_begin = s_begin;
     g.item_base = item_base;
+    g.items_by_slot = list != nullptr;
     return launch_quant_general(g, n_snarls, num_sms, st);
 }
 
@@ -651,11 +647,11 @@ __global__ void __launch_bounds__(128) eqtl_summary_kernel(const double* __restr
                                                            const uint8_t* __restrict__ filtered, uint64_t s_begin,
                                                            uint64_t n_snarls, uint32_t n_genes, double p_threshold,
                                                            double* __restrict__ min_p, uint32_t* __restrict__ argmin,
-                                                           uint32_t* __restrict__ n_below) {
+                                                           uint32_t* __restrict__ n_below, const uint32_t* __restrict__ list) {
     const uint32_t lane = threadIdx.x & 31;
     const uint64_t w = (uint64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     if (w >= n_snarls) return;
-    const uint64_t s = s_begin + w;
+    const uint64_t s = list ? uint64_t(list[w]) : s_begin + w;  // pair table row w <-> snarl s
     double best = __longlong_as_double(0x7ff0000000000000LL);  // +inf
     uint32_t best_g = 0xFFFFFFFFu, cnt = 0;
     if (!filtered[s]) {
@@ -690,11 +686,11 @@ __global__ void __launch_bounds__(128) eqtl_summary_kernel(const double* __restr
 
 cudaError_t launch_eqtl_summary(const double* p, const uint8_t* code, const uint8_t* filtered, uint64_t s_begin,
                                 uint64_t n_snarls, uint32_t n_genes, double p_threshold, double* min_p,
-                                uint32_t* argmin, uint32_t* n_below, cudaStream_t st) {
+                                uint32_t* argmin, uint32_t* n_below, cudaStream_t st, const uint32_t* list) {
     if (n_snarls == 0) return cudaSuccess;
     const unsigned blocks = unsigned((n_snarls + 3) / 4);
     eqtl_summary_kernel<<<blocks, 128, 0, st>>>(p, code, filtered, s_begin, n_snarls, n_genes, p_threshold, min_p,
-                                                argmin, n_below);
+                                                argmin, n_below, list);
     return cudaGetLastError();
 }
 

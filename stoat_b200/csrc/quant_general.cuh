@@ -28,7 +28,7 @@ struct GParams {
     BatchDev b;
     const uint32_t* list;  // nullptr: every snarl
     const uint32_t* n_list_dev;
-    uint64_t n_list_host;  // used when list == nullptr
+    uint64_t n_list_host;  // used when list == nullptr or n_list_dev == nullptr
     stoat_gpu_thresholds thr;
     QuantOut out;  // allele_paths [P], filtered / n_used [S]; p / r2 / beta / se / code per snarl or per (snarl, gene)
     // eQTL addressing; n_genes == 0: quantitative (one item per snarl, item index = snarl)
@@ -37,6 +37,7 @@ struct GParams {
     const uint32_t* gene_idx;
     uint64_t s_begin;    // list == nullptr: snarls [s_begin, s_begin + n_list_host)
     uint64_t item_base;  // per-item outputs are written at (item - item_base): chunked dense scans
+    bool items_by_slot;  // dense scan over a LIST of snarls: the items of list entry i are [i * n_genes, (i + 1) * n_genes)
 };
 
 constexpr int kGWarps = 4;
@@ -134,7 +135,7 @@ __device__ void g_exact_sums(const GParams& g, GScratch& sc, const GSnarl& sn, u
     __syncwarp();
 }
 
-__device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint32_t lane) {
+__device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64_t slot, uint32_t lane) {
     GSnarl sn;
     sn.p0 = g.b.snarl_path_off[s];
     const uint64_t p1 = g.b.snarl_path_off[s + 1];
@@ -146,8 +147,9 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint32
     // items (regressions) of this snarl: one for the quantitative analyzer, one per gene of the window for eQTL
     uint64_t k0 = s, k1 = s + 1;
     if (g.n_genes) {
-        k0 = g.snarl_gene_off ? g.snarl_gene_off[s] : s * uint64_t(g.n_genes);
-        k1 = g.snarl_gene_off ? g.snarl_gene_off[s + 1] : (s + 1) * uint64_t(g.n_genes);
+        const uint64_t dense_row = g.items_by_slot ? slot : s;
+        k0 = g.snarl_gene_off ? g.snarl_gene_off[s] : dense_row * uint64_t(g.n_genes);
+        k1 = g.snarl_gene_off ? g.snarl_gene_off[s + 1] : (dense_row + 1) * uint64_t(g.n_genes);
     }
     auto finish_none = [&](bool filtered, uint32_t n_used, uint8_t code) {
         if (lane == 0) {
@@ -432,10 +434,10 @@ __global__ void __launch_bounds__(kGWarps * 32) quant_general_kernel(const GPara
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint64_t gw = uint64_t(blockIdx.x) * kGWarps + warp;
     const uint64_t n_warps = uint64_t(gridDim.x) * kGWarps;
-    const uint64_t n = g.list ? uint64_t(*g.n_list_dev) : g.n_list_host;
+    const uint64_t n = (g.list && g.n_list_dev) ? uint64_t(*g.n_list_dev) : g.n_list_host;
     for (uint64_t i = gw; i < n; i += n_warps) {
         const uint64_t s = g.list ? g.list[i] : g.s_begin + i;
-        quant_general(g, scratch[warp], s, lane);
+        quant_general(g, scratch[warp], s, i, lane);
     }
 }
 

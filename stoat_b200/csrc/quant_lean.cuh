@@ -15,25 +15,6 @@
 // within 1e-9 of its threshold the snarl is handed to the general path, which replays the reference's summation order.
 #pragma once
 
-struct LeanMasks {
-    uint32_t used, full0, half, third, tthird;
-};
-
-__device__ __forceinline__ LeanMasks lean_masks(uint32_t v0, uint32_t v1) {
-    const uint32_t M = 0x55555555u;
-    const uint32_t s0 = v0 >> 1, s1 = v1 >> 1;
-    const uint32_t any0 = (v0 | s0) & M, any1 = (v1 | s1) & M;
-    const uint32_t one0 = (v0 ^ s0) & M, one1 = (v1 ^ s1) & M;
-    const uint32_t two0 = v0 & s0 & M, two1 = v1 & s1 & M;
-    LeanMasks m;
-    m.used = any0 | any1;
-    m.full0 = any0 & ~any1;
-    m.half = (one0 & one1) | (two0 & two1);
-    m.third = one0 & two1;
-    m.tthird = two0 & one1;
-    return m;
-}
-
 // one path's presence bits for 16-byte chunk c (code: 0xFF missing edge -> nobody, 0 no checked edge -> everybody,
 // else the number of ANDed rows, <= 4)
 __device__ __forceinline__ uint4 lean_path_chunk(const uint8_t* rows_s, uint32_t code, const uint32_t (&roff)[4],

@@ -99,3 +99,123 @@ def test_dense_summary_matches_reduced_pairs(gpu_ctx, oracle):
         near = np.abs(ps - thr) <= 1e-9 * thr
         lo, hi = int(((ps < thr) & ~near).sum()), int(((ps < thr) | near).sum())
         assert lo <= got["n_below"][s] <= hi
+
+
+# ---------------------------------------------------------------------------------------------------
+# the dense scan on the FP64 tensor cores (kernels_eqtl.cu) — two-path snarls, any number of tiles / gene groups
+# ---------------------------------------------------------------------------------------------------
+def _check_summary(got, ref, S, G, thr, rtol=1e-9, skip=()):
+    p = ref["p_value"].reshape(S, G)
+    ok = ref["code"].reshape(S, G) == 0
+    n_checked = 0
+    for s in range(S):
+        if s in skip:
+            continue
+        if ref["filtered"][s] or not ok[s].any():
+            assert np.isnan(got["min_p"][s]) and got["n_below"][s] == 0, s
+            continue
+        ps = np.where(ok[s], p[s], np.inf)
+        g = int(np.argmin(ps))
+        assert abs(got["min_p"][s] - ps[g]) <= rtol * ps[g] + 1e-300, (s, got["min_p"][s], ps[g])
+        if got["argmin_gene"][s] != g:  # a tie within rounding
+            assert abs(ps[got["argmin_gene"][s]] - ps[g]) <= rtol * ps[g], (s, got["argmin_gene"][s], g)
+        near = np.abs(ps - thr) <= rtol * thr
+        lo, hi = int(((ps < thr) & ~near).sum()), int(((ps < thr) | near).sum())
+        assert lo <= got["n_below"][s] <= hi, (s, got["n_below"][s], lo, hi)
+        n_checked += 1
+    return n_checked
+
+
+def _dense_problem(seed, n_snarls, n_samples, n_genes, **kw):
+    from stoat_b200 import synth
+
+    d = synth.numpy_dataset(n_snarls, n_samples, seed=seed, **kw)
+    rng = np.random.default_rng(seed + 50)
+    base = rng.uniform(0, 8, size=(n_genes, 1))
+    expr = base * (1.0 + rng.uniform(-1, 1, size=(n_genes, n_samples)))
+    dense = d["dense"]
+    st = d["structure"]
+    for g in range(0, n_genes, 4):  # genes driven by a snarl's alt dosage (simulate_test_dataset.py:75-88)
+        s = int(rng.integers(0, n_snarls))
+        if st.kind[s] == 2:
+            continue
+        expr[g] += rng.uniform(0.5, 3.0) * dense[st.row0[s] + 2].reshape(n_samples, 2).sum(1)
+    return d, expr
+
+
+@pytest.mark.parametrize("seed,n_snarls,n_samples,n_genes,group", [
+    (11, 300, 100, 70, None),     # 3 snarl tiles, 2 gene tiles (the second one ragged)
+    (12, 130, 517, 200, "64"),    # ragged sample count (9 stages), 4 gene groups of one tile
+    (13, 64, 33, 5, None),        # less than one tile in every dimension
+])
+def test_dense_dmma_summary(oracle, monkeypatch, seed, n_snarls, n_samples, n_genes, group):
+    import stoat_b200
+
+    if group:
+        monkeypatch.setenv("STOAT_GPU_EQTL_GROUP", group)
+    d, expr = _dense_problem(seed, n_snarls, n_samples, n_genes, frac_missing_edge=0.02, frac_missing_hap=0.08)
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    thr = 1e-3
+    ref = oracle.eqtl_batch(d["bits"], d["n_cols"], expr, P)
+    with stoat_b200.Context(0) as ctx:
+        ctx.set_matrix(d["bits"], d["n_rows"], d["n_cols"])
+        got = ctx.eqtl_dense_summary(d["paths"], expr, p_threshold=thr)
+        t = ctx.timing()
+        # resident mode gives the same answer
+        ctx.stage_paths(d["paths"])
+        ctx.set_expression(expr)
+        ctx.eqtl_dense_run_staged(p_threshold=thr)
+        again = ctx.eqtl_summary_fetch()
+    assert _check_summary(got, ref, P.n_snarls, n_genes, thr) > n_snarls // 3
+    for k in ("argmin_gene", "n_below"):
+        np.testing.assert_array_equal(got[k], again[k])
+    np.testing.assert_array_equal(np.isnan(got["min_p"]), np.isnan(again["min_p"]))
+    # most snarls of the generator are two-path and dyadic: they must have taken the tensor-core path
+    assert t["n_general"] < 0.2 * n_snarls + 8, t
+    # and the general kernel alone (STOAT_GPU_EQTL=general) agrees
+    monkeypatch.setenv("STOAT_GPU_EQTL", "general")
+    with stoat_b200.Context(0) as ctx:
+        ctx.set_matrix(d["bits"], d["n_rows"], d["n_cols"])
+        gen = ctx.eqtl_dense_summary(d["paths"], expr, p_threshold=thr)
+        assert ctx.timing()["n_general"] == n_snarls
+    _check_summary(gen, ref, P.n_snarls, n_genes, thr)
+
+
+def test_dense_dmma_degenerate_genes(oracle):
+    """Near-perfect fits (explicit-residual branch), a constant gene (tss = 0: invalid t -> p = 1), a gene equal to the
+    dosage itself (rss = 0), thresholds above 1."""
+    import stoat_b200
+
+    d, expr = _dense_problem(21, 140, 90, 9, frac_three=0.0, frac_node0=0.0, frac_missing_hap=0.03)
+    st, dense, n = d["structure"], d["dense"], 90
+    dos = dense[st.row0[3]].reshape(n, 2).sum(1) / 2.0
+    dos5 = dense[st.row0[5]].reshape(n, 2).sum(1) / 2.0
+    expr[0] = 2.0 + 3.0 * dos                                                # exact linear function of snarl 3's dosage
+    expr[1] = 1.0 - 2.0 * dos5 + 1e-7 * np.random.default_rng(1).normal(size=n)  # near perfect for snarl 5
+    expr[2] = 4.25                                                            # constant
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    ref = oracle.eqtl_batch(d["bits"], d["n_cols"], expr, P)
+    with stoat_b200.Context(0) as ctx:
+        ctx.set_matrix(d["bits"], d["n_rows"], d["n_cols"])
+        for thr in (1e-4, 0.5, 2.0):
+            got = ctx.eqtl_dense_summary(d["paths"], expr, p_threshold=thr)
+            # the exactly-linear gene has rss ~ 1e-30 in any implementation: compare p only where it is not rounding noise
+            # snarl 3 x gene 0 has rss ~ 1e-30 in any implementation: its p is rounding noise, only its rank is checked
+            _check_summary(got, ref, P.n_snarls, 9, thr, rtol=1e-6, skip={3})
+            if not ref["filtered"][3]:
+                assert got["argmin_gene"][3] == 0 and got["min_p"][3] < 1e-30
+            if not ref["filtered"][5]:
+                assert got["argmin_gene"][5] == 1
+
+
+def test_dense_with_covariates_takes_general_path(gpu_ctx, oracle):
+    d, expr = _dense_problem(31, 60, 80, 6)
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    covar = np.random.default_rng(2).normal(size=(80, 2))
+    gpu_ctx.set_matrix(d["bits"], d["n_rows"], d["n_cols"])
+    gpu_ctx.set_covariates(covar)
+    got = gpu_ctx.eqtl_dense_summary(d["paths"], expr, p_threshold=1e-2)
+    assert gpu_ctx.timing()["n_general"] == 60
+    gpu_ctx.set_covariates(None)
+    ref = oracle.eqtl_batch(d["bits"], d["n_cols"], expr, P, covar=covar)
+    _check_summary(got, ref, P.n_snarls, 6, 1e-2)
