@@ -157,8 +157,8 @@ typedef struct stoat_gpu_ctx stoat_gpu_ctx;
 typedef struct stoat_gpu_timing {
     float h2d_ms;      /* host -> device copies of the batch inputs                          */
     float repack_ms;   /* K0 repack_rows (only when the matrix was (re)uploaded)              */
-    float table_ms;    /* K1 path_and_popc / K3 dosage pass                                  */
-    float stats_ms;    /* K2 binary_stats / K4 ols_solve                                     */
+    float table_ms;    /* K1 path_and_popc / K3 dosage pass / dense eQTL: the DMMA contraction (E1) */
+    float stats_ms;    /* K2 binary_stats / K4 ols_solve / dense eQTL: E0 + E2 + general-path rest  */
     float d2h_ms;      /* device -> host copies of the results                               */
     uint32_t launches; /* kernels launched by the call                                       */
     uint32_t n_general; /* snarls that left the TMA-staged fast path (LDG / general kernels)  */

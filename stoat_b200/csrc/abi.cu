@@ -750,12 +750,15 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     CK(cudaMemsetAsync(e.fb_count, 0, 4, ctx->stream));
     CK(launch_eqtl_dosage_codes(matrix_view(ctx), b, *thr, allow_dense, e, eqtl_out_view(ctx), ctx->stream));
     uint32_t launches = 1;
+    CK(cudaEventRecord(ctx->ev[5], ctx->stream));
     if (allow_dense && S) {
         CK(launch_eqtl_dense(e, ctx->num_sms, ctx->stream));
+        CK(cudaEventRecord(ctx->ev[6], ctx->stream));
         CK(launch_eqtl_dense_finish(e, ctx->stream));
         launches += 2;
+    } else {
+        CK(cudaEventRecord(ctx->ev[6], ctx->stream));
     }
-    CK(cudaEventRecord(ctx->ev[4], ctx->stream));
     // snarls the dense path does not take (other shapes, covariates): the general kernel, a chunk of pairs at a time
     uint32_t n_fb = 0;
     CK(cudaMemcpyAsync(&n_fb, e.fb_count, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -775,8 +778,10 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     }
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[4]));   // E0 + E1 + E2 (dense path)
-    CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ctx->ev[4], ctx->ev[3]));   // general path for the rest
+    float all_ms = 0.f;
+    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[5], ctx->ev[6]));  // E1, the tensor-core contraction + epilogue
+    CK(cudaEventElapsedTime(&all_ms, ctx->ev[2], ctx->ev[3]));
+    ctx->timing.stats_ms = all_ms - ctx->timing.table_ms;                     // E0, E2 and the general path for the rest
     ctx->timing.launches = launches;
     ctx->timing.n_general = n_fb;
     ctx->have_eqtl_summary = true;

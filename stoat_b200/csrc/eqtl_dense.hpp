@@ -10,7 +10,7 @@ namespace stoat {
 constexpr int kEqTileS = 128;     // snarls per CTA tile
 constexpr int kEqTileG = 64;      // genes per gene tile
 constexpr int kEqKT = 64;         // samples per pipeline stage (= one 16-byte chunk of a matrix row)
-constexpr int kEqMaxUnused = 4;   // samples on no path a dense snarl may have (more: general path)
+constexpr int kEqMaxUnused = 8;   // samples on no path a dense snarl may have (more: general path)
 
 // Per-snarl record written by E0 (64 bytes).  state: 0 filtered, 1 dense, 2 general path.
 struct __align__(16) EqtlRec {
@@ -19,7 +19,6 @@ struct __align__(16) EqtlRec {
     uint32_t n_used;
     uint16_t unused[kEqMaxUnused];
     uint8_t n_unused, state, pad[2];
-    uint32_t pad2[2];
 };
 static_assert(sizeof(EqtlRec) == 64, "EqtlRec must be 64 bytes");
 

@@ -72,7 +72,9 @@ __global__ void __launch_bounds__(128) binary_prep_kernel(BatchDev b, uint64_t n
     }
     uint8_t* blob = b.blob + base16 * 16;
     if (big) {
-        blob[0] = 0;  // "nothing to do here" for the TMA kernel
+        // "nothing to do here" for the TMA kernel: the WHOLE header, not just np — the buffer is reused between batches
+        // and a stale shape class (blob[1] == 1) would send the kernel down the biallelic branch with a stale p0
+        *reinterpret_cast<uint2*>(blob) = make_uint2(0u, 0u);
         const uint32_t slot = atomicAdd(&b.counters[0], 1u);
         b.big_list[slot] = uint32_t(s);
         b.rec[s] = rec;

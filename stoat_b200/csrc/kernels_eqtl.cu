@@ -14,7 +14,7 @@
 //                           2 x 2 solve, RSS by the moment expansion (explicit residuals when the fit is near perfect),
 //                           t statistic; reduced on the fly to per-snarl best gene / count below the threshold
 //   E2  eqtl_dense_finish   merge the gene groups, p = 2 * T_df(|t|) of the best gene
-// Snarls of any other shape (three or more kept paths, non-dyadic dosages, rank-deficient designs, > 4 unused samples,
+// Snarls of any other shape (three or more kept paths, non-dyadic dosages, rank-deficient designs, > 8 unused samples,
 // covariates) go to the general kernel (quant_general.cuh), which follows the reference's order of operations.
 #include <cstdint>
 
@@ -357,13 +357,15 @@ __global__ void __launch_bounds__(kEqThreads, 1) eqtl_dense_dmma_kernel(const Eq
                     a_even[mt] = code_to_double((w >> sh) & 3u);
                     a_odd[mt] = code_to_double((w >> (sh + 2)) & 3u);
                 }
+                // 16 independent accumulator tiles between two DMMAs on the same tile (no back-to-back dependency)
 #pragma unroll
                 for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
-                    for (int nt = 0; nt < 4; ++nt) {
-                        dmma884(acc[mt][nt][0], acc[mt][nt][1], a_even[mt], bv[nt].x);
-                        dmma884(acc[mt][nt][0], acc[mt][nt][1], a_odd[mt], bv[nt].y);
-                    }
+                    for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a_even[mt], bv[nt].x);
+#pragma unroll
+                for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                    for (int nt = 0; nt < 4; ++nt) dmma884(acc[mt][nt][0], acc[mt][nt][1], a_odd[mt], bv[nt].y);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.empty[st]);

@@ -17,6 +17,7 @@
 // RSS = y'y - 2 b'X'y + b'X'Xb well conditioned.  Snarls where that expansion would still cancel
 // (R^2 > 1 - 1e-6), and rank-deficient snarls (pseudo-inverse branch: minimum-norm beta, NOT shift invariant),
 // are re-done by K3G on the raw phenotype with an explicit residual pass, as the reference does (:460-463).
+#include <algorithm>
 #include <cstdlib>
 
 #include "ctx.hpp"
@@ -638,7 +639,13 @@ cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, ui
     g.s_begin = s_begin;
     g.item_base = item_base;
     g.items_by_slot = list != nullptr;
-    return launch_quant_general(g, n_snarls, num_sms, st);
+    g.gene_split = 1;
+    if (list) {  // few snarls, many genes each: give every snarl enough warps to fill the machine
+        const uint64_t target = uint64_t(num_sms) * 3 * kGWarps * 2;
+        const uint64_t want = (target + n_snarls - 1) / n_snarls, most = (uint64_t(n_genes) + 7) / 8;
+        g.gene_split = uint32_t(std::max<uint64_t>(1, std::min(want, most)));
+    }
+    return launch_quant_general(g, n_snarls * g.gene_split, num_sms, st);
 }
 
 // per-snarl reduction of a dense chunk: smallest p, its gene, number of genes with p < p_threshold

@@ -38,6 +38,7 @@ struct GParams {
     uint64_t s_begin;    // list == nullptr: snarls [s_begin, s_begin + n_list_host)
     uint64_t item_base;  // per-item outputs are written at (item - item_base): chunked dense scans
     bool items_by_slot;  // dense scan over a LIST of snarls: the items of list entry i are [i * n_genes, (i + 1) * n_genes)
+    uint32_t gene_split;  // items_by_slot: a list entry is worked by gene_split warps, each a contiguous share of the genes
 };
 
 constexpr int kGWarps = 4;
@@ -135,7 +136,7 @@ __device__ void g_exact_sums(const GParams& g, GScratch& sc, const GSnarl& sn, u
     __syncwarp();
 }
 
-__device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64_t slot, uint32_t lane) {
+__device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64_t slot, uint32_t part, uint32_t lane) {
     GSnarl sn;
     sn.p0 = g.b.snarl_path_off[s];
     const uint64_t p1 = g.b.snarl_path_off[s + 1];
@@ -145,11 +146,18 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
     sn.nk = 0;
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
     // items (regressions) of this snarl: one for the quantitative analyzer, one per gene of the window for eQTL
-    uint64_t k0 = s, k1 = s + 1;
+    uint64_t k0 = s, k1 = s + 1, gene_base = 0;
     if (g.n_genes) {
         const uint64_t dense_row = g.items_by_slot ? slot : s;
         k0 = g.snarl_gene_off ? g.snarl_gene_off[s] : dense_row * uint64_t(g.n_genes);
         k1 = g.snarl_gene_off ? g.snarl_gene_off[s + 1] : (dense_row + 1) * uint64_t(g.n_genes);
+        if (g.items_by_slot && g.gene_split > 1) {  // this warp's share of the entry's genes
+            const uint64_t share = (uint64_t(g.n_genes) + g.gene_split - 1) / g.gene_split;
+            const uint64_t lo = k0 + uint64_t(part) * share;
+            k1 = lo + share < k1 ? lo + share : k1;
+            k0 = lo < k1 ? lo : k1;
+        }
+        gene_base = dense_row * uint64_t(g.n_genes);
     }
     auto finish_none = [&](bool filtered, uint32_t n_used, uint8_t code) {
         if (lane == 0) {
@@ -330,7 +338,7 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         const bool first = (item == k0);
         const double* y = g.y;
         if (g.n_genes) {
-            const uint64_t gene = g.gene_idx ? uint64_t(g.gene_idx[item]) : (item - k0);
+            const uint64_t gene = g.gene_idx ? uint64_t(g.gene_idx[item]) : (item - gene_base);
             y = g.y + gene * uint64_t(g.n_samples);  // retain_indices(expression, index_filtered), :510-511
         }
         // ---- sweep B: X^T X (first item only), X^T y, y'y, sum y ------------------------------------
@@ -434,10 +442,12 @@ __global__ void __launch_bounds__(kGWarps * 32) quant_general_kernel(const GPara
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint64_t gw = uint64_t(blockIdx.x) * kGWarps + warp;
     const uint64_t n_warps = uint64_t(gridDim.x) * kGWarps;
-    const uint64_t n = (g.list && g.n_list_dev) ? uint64_t(*g.n_list_dev) : g.n_list_host;
+    const uint64_t split = (g.items_by_slot && g.gene_split > 1) ? g.gene_split : 1;
+    const uint64_t n = ((g.list && g.n_list_dev) ? uint64_t(*g.n_list_dev) : g.n_list_host) * split;
     for (uint64_t i = gw; i < n; i += n_warps) {
-        const uint64_t s = g.list ? g.list[i] : g.s_begin + i;
-        quant_general(g, scratch[warp], s, i, lane);
+        const uint64_t entry = i / split;
+        const uint64_t s = g.list ? g.list[entry] : g.s_begin + entry;
+        quant_general(g, scratch[warp], s, entry, uint32_t(i - entry * split), lane);
     }
 }
 

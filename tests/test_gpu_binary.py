@@ -229,3 +229,27 @@ def test_invalid_row_index_is_reported(gpu_ctx, oracle):
     spo, peo, er = H.csr_from_lists([[[0], [7]]])
     with pytest.raises(stoat_b200.StoatGpuError):
         gpu_ctx.binary_batch(stoat_b200.SnarlPaths(spo, peo, er))
+
+
+def test_reused_context_big_snarl_after_biallelic_batch(oracle):
+    """Regression: the path-program buffer is reused between batches; a snarl that takes the LDG path must not leave the
+    previous batch's shape class / first-path index where the TMA kernel reads them (it used to write two stale counts)."""
+    import stoat_b200
+    from stoat_b200 import SnarlPaths
+
+    rng = np.random.default_rng(77)
+    S, n_samples = 6000, 40
+    H2 = 2 * n_samples
+    dense = rng.random((4 * S + 8, H2)) < 0.7
+    is_case = (rng.random(n_samples) < 0.5).astype(np.uint8)
+    bial = [[[4 * s, 4 * s + 1], [4 * s + 2, 4 * s + 3]] for s in range(S)]
+    big_last = bial[:-1] + [[[4 * S - 4 + k for k in range(8)]]]  # one path, 8 distinct rows: over the 6-row stage limit
+    bits = oracle.pack_matrix(dense)
+    with stoat_b200.Context(0) as ctx:
+        ctx.set_matrix(bits, dense.shape[0], H2)
+        ctx.set_binary_phenotype(is_case)
+        for snarls in (bial, big_last, bial, big_last):
+            spo, peo, er = H.csr_from_lists(snarls)
+            got = ctx.binary_batch(SnarlPaths(spo, peo, er), min_ind=0, min_hap=0, maf=0.0)
+            ref = oracle.binary_batch(bits, H2, is_case, oracle.Paths(spo, peo, er), min_ind=0, min_hap=0, maf=0.0)
+            H.assert_binary_equal(got, ref)
