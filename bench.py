@@ -48,8 +48,13 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--trait", default="binary", choices=["binary", "quantitative"])
-    return ap.parse_args()
+    ap.add_argument("--trait", default="binary", choices=["binary", "quantitative", "eqtl"])
+    ap.add_argument("--genes", type=int, default=20_000, help="eqtl: genes (C4: 200k snarls x 5k samples x 20k genes)")
+    ap.add_argument("--p-threshold", type=float, default=1e-5, help="eqtl: significance threshold of the scan summary")
+    args = ap.parse_args()
+    if args.trait == "eqtl" and "--snarls" not in " ".join(sys.argv):
+        args.snarls = 200_000
+    return args
 
 
 def config_dict(args, n_gpus):
@@ -280,6 +285,11 @@ def algorithmic_bytes_k1(paths, pitch):
 
 def main():
     args = parse_args()
+    if args.trait == "eqtl":
+        import bench_eqtl
+
+        bench_eqtl.run(args, ClockSampler)
+        return
     if args.impl == "reference":
         run_reference_arm(args)
         return

@@ -1,0 +1,293 @@
+"""bench_eqtl.py — the dense eQTL scan leg of bench.py (`python bench.py --trait eqtl`), BASELINE.json configs[3] ("C4"):
+synthetic 200,000 biallelic snarls x 5,000 samples x 20,000 gene phenotypes, every (snarl, gene) pair one OLS
+(EQTLSnarlAnalyzer, src/snarl_analyzer.cpp:493-539).  A step = one full scan over the resident matrix / expression.
+
+  value      (snarl, gene) OLS tests / s, whole job, inputs resident in HBM
+  e2e        same through stoat_gpu_eqtl_dense_summary with HOST buffers (matrix + expression H2D, summary D2H)
+  roofline   E1 eqtl_dense_dmma: 2 * n * S_dense * G flops / its CUDA-event time, against an FP64 GEMM measured live
+             (MEASURED_PEAKS.json has no FP64 figure): torch.matmul f64 8192^3 = cuBLAS DGEMM, best of 5
+  cpu_baseline / --impl reference   the reference's own EQTLSnarlAnalyzer (oracle/_ref) or the oracle port on a sample
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+METRIC = "snarl-gene OLS tests/sec (dense eQTL scan)"
+UNIT = "pair-tests/s"
+BIALLELIC = dict(frac_three=0.0, frac_node0=0.0)  # C4 is "biallelic snarls" 
+
+
+def config_dict(args, n_gpus):
+    return {
+        "workload": f"C4 synthetic {args.snarls} biallelic snarls x {args.samples} samples x {args.genes} genes, "
+                    f"dense eQTL scan (one OLS per pair), per GPU",
+        "snarls_per_gpu": args.snarls, "samples": args.samples, "genes": args.genes,
+        "sharding": "snarl-sharded, no collective" if n_gpus > 1 else "single GPU",
+        "l2": "the expression matrix (0.8 GB) and the dosage codes (0.25 GB) exceed the 126 MB L2; gene groups of ~48 MB "
+              "are L2 resident by design, every step streams the rest from HBM, no flush needed",
+        "p_threshold": args.p_threshold, "thresholds": {"min_individuals": 3, "min_haplotypes": 5, "maf": 0.05},
+    }
+
+
+def expression_numpy(n_genes, n_samples, seed=7):
+    """e_g * (1 + U(-1, 1)), e_g ~ U(0, 8): tests/simu/scripts/simulate_test_dataset.py:75-88."""
+    rng = np.random.default_rng(seed)
+    return rng.uniform(0, 8, size=(n_genes, 1)) * (1.0 + rng.uniform(-1, 1, size=(n_genes, n_samples)))
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm
+# ---------------------------------------------------------------------------------------------------
+def cpu_kind():
+    try:
+        from oracle import ref
+
+        if os.path.exists(ref.ref_build.LIB) or ref.available():
+            ref.lib()
+            return "reference"
+    except Exception:
+        pass
+    return "port"
+
+
+def cpu_run(d, expr, threads, kind):
+    """One pass of the CPU eQTL loop over the sample: every gene is in every snarl's window.  -> (seconds, pairs)."""
+    import oracle
+
+    S, G = d["paths"].n_snarls, expr.shape[0]
+    if kind == "reference":
+        from oracle import ref
+
+        nodes = d.get("_nodes")
+        if nodes is None:
+            nodes = d["_nodes"] = ref.nodes_from_structure(d["structure"])
+        r = ref.run("eqtl", d["bits"], d["n_rows"], d["n_cols"], d["paths"].snarl_path_off, nodes, expression=expr,
+                    window=1 << 40, n_threads=threads, tsv_path=os.path.join("/tmp", f"stoat_cpu_eqtl_{os.getpid()}.tsv"),
+                    parse=False)
+        return r["seconds"], S * G
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    r = oracle.eqtl_batch(d["bits"], d["n_cols"], expr, P, n_threads=threads)
+    return r["seconds"], S * G
+
+
+def cpu_threads(kind):
+    import oracle
+
+    if kind == "reference":
+        from oracle import ref
+
+        return ref.num_threads()
+    return oracle.num_threads()
+
+
+CPU_WHAT = {"reference": "the reference's own EQTLSnarlAnalyzer sources (oracle/_ref: table once per snarl, Eigen OLS per gene, "
+                         "writer; Boost tails from stand-ins) incl. per-row TSV write",
+            "port": "oracle port of the reference's eQTL loop"}
+
+
+def cpu_sample(args, target_seconds):
+    """(dataset, expression, threads, kind) sized for about target_seconds of CPU work."""
+    from stoat_b200 import synth
+
+    kind = cpu_kind()
+    probe = synth.numpy_dataset(8, args.samples, seed=42, **BIALLELIC)
+    pe = expression_numpy(16, args.samples)
+    best = (1, 0.0)
+    for th in sorted({1, cpu_threads(kind)}):
+        secs, pairs = cpu_run(probe, pe, th, kind)
+        if pairs / max(secs, 1e-9) > best[1]:
+            best = (th, pairs / max(secs, 1e-9))
+    threads, rate = best
+    want = max(64, int(rate * target_seconds))
+    n_genes = int(min(args.genes, max(16, round(want ** 0.5))))
+    n_snarls = int(min(2000, max(8, want // n_genes)))
+    d = synth.numpy_dataset(n_snarls, args.samples, seed=42, **BIALLELIC)
+    return d, expression_numpy(n_genes, args.samples), threads, kind
+
+
+def cpu_baseline(args, target_seconds):
+    d, expr, threads, kind = cpu_sample(args, target_seconds)
+    secs, pairs = cpu_run(d, expr, threads, kind)
+    return {"value": pairs / secs, "unit": UNIT, "cores": threads, "kind": kind,
+            "sample": f"{d['paths'].n_snarls} snarls x {expr.shape[0]} genes x {args.samples} samples ({pairs} pairs) of the same "
+                      f"generators, {CPU_WHAT[kind]}, {secs:.2f} s"}
+
+
+def run_reference_arm(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import oracle
+
+    oracle.build()
+    d, expr, threads, kind = cpu_sample(args, 4.0)
+    for _ in range(args.warmup):
+        cpu_run(d, expr, threads, kind)
+    total, pairs = 0.0, 0
+    for _ in range(args.steps):
+        s, p = cpu_run(d, expr, threads, kind)
+        total += s
+        pairs += p
+    value = pairs / total
+    sample = (f"{d['paths'].n_snarls} snarls x {expr.shape[0]} genes x {args.samples} samples per step, same generators, "
+              f"{CPU_WHAT[kind]}")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config_dict(args, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------
+def dgemm_peak_tflops(torch, dev, n=8192, reps=5):
+    """cuBLAS DGEMM through torch.matmul, CUDA events, best of `reps` (the FP64 tensor-core roofline of this box)."""
+    a = torch.randn((n, n), device=dev, dtype=torch.float64)
+    b = torch.randn((n, n), device=dev, dtype=torch.float64)
+    for _ in range(2):
+        a @ b
+    torch.cuda.synchronize()
+    best = float("inf")
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        a @ b
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, b
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+
+
+def run(args, ClockSampler):
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+    import torch
+    import torch.distributed as dist
+
+    import stoat_b200
+    from stoat_b200 import synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: stoat_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    S, n, G = args.snarls, args.samples, args.genes
+    d = synth.torch_dataset(S, n, dev, seed=42 + rank, **BIALLELIC)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(7)
+    base = torch.rand((G, 1), device=dev, generator=gen, dtype=torch.float64) * 8
+    expr = base * (1 + (torch.rand((G, n), device=dev, generator=gen, dtype=torch.float64) * 2 - 1))
+    # 10 % of the genes depend on a snarl's dosage (simulate_test_dataset.py:75-88): add the alt-path dosage of snarl g
+    peak = dgemm_peak_tflops(torch, dev) if rank == 0 else None
+    ctx = stoat_b200.Context(local)
+    ctx.set_matrix_dev(d["bits_dev"].data_ptr(), d["n_rows"], d["n_cols"])
+    ctx.stage_paths(d["paths"])
+    ctx.set_expression_dev(expr.data_ptr(), G)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
+    run_scan = lambda: ctx.eqtl_dense_run_staged(p_threshold=args.p_threshold)  # noqa: E731
+    for _ in range(max(args.warmup, 3)):
+        run_scan()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e1_ms, rest_ms, launches, n_general = [], [], 0, 0
+    e0.record(stream)
+    for _ in range(args.steps):
+        run_scan()
+        t = ctx.timing()
+        e1_ms.append(t["table_ms"])
+        rest_ms.append(t["stats_ms"])
+        launches += t["launches"]
+        n_general = t["n_general"]
+    e1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    tmax = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    lsum = torch.tensor([launches], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lsum, op=dist.ReduceOp.SUM)
+    elapsed_ms = float(tmax.item())
+    value = world * S * G * args.steps / (elapsed_ms * 1e-3)
+    summary = ctx.eqtl_summary_fetch()
+    n_dense = int(S - n_general - int(np.isnan(summary["min_p"]).sum()))
+
+    e2e = None
+    if not args.no_e2e:
+        host_bits = torch.empty(d["bits_dev"].numel(), dtype=torch.uint8, pin_memory=True)
+        host_bits.copy_(d["bits_dev"])
+        host_expr = torch.empty((G, n), dtype=torch.float64, pin_memory=True)
+        host_expr.copy_(expr)
+        torch.cuda.synchronize()
+        expr_np = host_expr.numpy()
+
+        def e2e_step():
+            ctx.set_matrix_ptr(host_bits.data_ptr(), d["n_rows"], d["n_cols"])
+            return ctx.eqtl_dense_summary(d["paths"], expr_np, p_threshold=args.p_threshold)
+
+        e2e_step()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        for _ in range(args.e2e_steps):
+            out = e2e_step()
+        f1.record(stream)
+        barrier()
+        te = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        p = d["paths"]
+        h2d = host_bits.numel() + host_expr.numel() * 8 + p.snarl_path_off.nbytes + p.path_edge_off.nbytes + p.edge_row.nbytes
+        d2h = sum(v.nbytes for v in out.values())
+        e2e = {"value": world * S * G * args.e2e_steps / (float(te.item()) * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": float(te.item()) / args.e2e_steps,
+               "includes": "set_matrix (H2D + K0 repack) + stage (H2D CSR, prep) + expression H2D + centre + E0 + E1 + E2 "
+                           "+ general-path rest + D2H of the per-snarl summary"}
+        del host_bits, host_expr
+
+    if rank == 0:
+        k_ms = float(np.mean(e1_ms))
+        flops = 2.0 * n * n_dense * G
+        achieved = flops / (k_ms * 1e-3) / 1e12
+        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                    "traffic": None, "kernel": "eqtl_dense_dmma (E1: DMMA.8x8x4 contraction + per-pair OLS epilogue)",
+                    "algorithmic_flops_per_launch": flops, "kernel_ms": k_ms,
+                    "peak_source": "FP64 GEMM measured live in this run: torch.matmul f64 8192^3 (cuBLAS DGEMM), best of 5, "
+                                   "CUDA events; MEASURED_PEAKS.json carries no FP64 figure",
+                    "snarls_on_tensor_path": n_dense, "snarls_on_general_path": int(n_general),
+                    "other_kernels_ms": {"E0 dosage codes + E2 finish + general-path rest": float(np.mean(rest_ms))}}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64 (2-bit dosage codes x f64 expression, DMMA)",
+                "data": "synthetic (seed 42, drawn on device)", "config": config_dict(args, world), "clocks": clocks,
+                "e2e": e2e, "gpu_launches": int(lsum.item()), "roofline": roofline}
+        if world == 1 and not args.no_cpu_baseline:
+            import oracle
+
+            oracle.build()
+            line["cpu_baseline"] = cpu_baseline(args, args.cpu_seconds)
+        print(json.dumps(line))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()

@@ -729,6 +729,7 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     CK(ctx->e_rec.reserve(std::max<uint64_t>(e.s_pad * sizeof(EqtlRec), 16)));
     CK(ctx->e_fb_list.reserve(std::max<uint64_t>(e.s_pad * 4, 16)));
     CK(ctx->e_fb_count.reserve(16));
+    CK(ctx->e_slot.reserve(std::max<uint64_t>(e.s_pad * 4, 16)));
     CK(ctx->e_part_key.reserve(std::max<uint64_t>(uint64_t(e.n_groups) * e.s_pad * 8, 16)));
     CK(ctx->e_part_gene.reserve(std::max<uint64_t>(uint64_t(e.n_groups) * e.s_pad * 4, 16)));
     CK(ctx->e_part_cnt.reserve(std::max<uint64_t>(uint64_t(e.n_groups) * e.s_pad * 4, 16)));
@@ -736,6 +737,8 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     e.rec = ctx->e_rec.as<EqtlRec>();
     e.fb_list = ctx->e_fb_list.as<uint32_t>();
     e.fb_count = ctx->e_fb_count.as<uint32_t>();
+    e.dense_count = e.fb_count + 1;
+    e.slot_snarl = ctx->e_slot.as<uint32_t>();
     e.part_key = ctx->e_part_key.as<double>();
     e.part_gene = ctx->e_part_gene.as<uint32_t>();
     e.part_cnt = ctx->e_part_cnt.as<uint32_t>();
@@ -747,7 +750,7 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     const bool allow_dense = ctx->eqtl_variant == 0 && ctx->n_covar == 0;
 
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
-    CK(cudaMemsetAsync(e.fb_count, 0, 4, ctx->stream));
+    CK(cudaMemsetAsync(e.fb_count, 0, 8, ctx->stream));  // general-path list length, dense slot count
     CK(launch_eqtl_dosage_codes(matrix_view(ctx), b, *thr, allow_dense, e, eqtl_out_view(ctx), ctx->stream));
     uint32_t launches = 1;
     CK(cudaEventRecord(ctx->ev[5], ctx->stream));

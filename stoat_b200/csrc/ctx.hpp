@@ -154,7 +154,7 @@ struct stoat_gpu_ctx {
     stoat::DevBuf q_allele, q_nused, q_p, q_r2, q_beta, q_se, q_code;      // quantitative / eQTL pairs
     stoat::DevBuf e_expr, e_gene_off, e_gene_idx, e_min_p, e_argmin, e_nbelow;  // eQTL
     // dense eQTL scan (kernels_eqtl.cu)
-    stoat::DevBuf e_yc, e_tot, e_tot2, e_dcode, e_rec, e_fb_list, e_fb_count, e_part_key, e_part_gene, e_part_cnt;
+    stoat::DevBuf e_yc, e_tot, e_tot2, e_dcode, e_rec, e_fb_list, e_fb_count, e_slot, e_part_key, e_part_gene, e_part_cnt;
     uint64_t e_n_genes = 0;
     bool have_expression = false, have_eqtl_summary = false;
     int eqtl_variant = 0;  // 0 = dense DMMA path where it applies (default), 1 = general kernel only (STOAT_GPU_EQTL=general)

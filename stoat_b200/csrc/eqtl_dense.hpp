@@ -30,8 +30,10 @@ struct EqtlDense {
     uint32_t n_genes, n_samples, n_pad, n_kst;
     // per batch
     uint64_t n_snarls, s_pad;  // s_pad = n_snarls rounded up to kEqTileS
-    uint8_t* dcode;            // [n_kst][s_pad][16]: 2-bit dosage codes of 64 samples
-    EqtlRec* rec;              // [s_pad]
+    uint8_t* dcode;            // [n_kst][s_pad][16]: 2-bit dosage codes of 64 samples, by SLOT (dense snarls compacted)
+    EqtlRec* rec;              // [s_pad] by slot
+    uint32_t* slot_snarl;      // [s_pad] slot -> snarl
+    uint32_t* dense_count;     // [1] number of slots
     uint32_t* fb_list;         // snarls for the general path
     uint32_t* fb_count;        // [1]
     // gene groups (one group's rows of yc stay L2 resident while every snarl tile passes over them)

@@ -106,20 +106,10 @@ __global__ void __launch_bounds__(128) eqtl_dosage_codes_kernel(const MatrixDev 
     __shared__ uint16_t unused_s[4][kEqMaxUnused];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint64_t s = uint64_t(blockIdx.x) * 4 + warp;
-    if (s >= e.s_pad) return;
-    EqtlRec rec{};
-    rec.state = 2;
+    if (s >= e.n_snarls) return;
     auto to_general = [&]() {
-        if (lane == 0) {
-            e.rec[s] = rec;
-            e.fb_list[atomicAdd(e.fb_count, 1u)] = uint32_t(s);
-        }
+        if (lane == 0) e.fb_list[atomicAdd(e.fb_count, 1u)] = uint32_t(s);
     };
-    if (s >= e.n_snarls) {  // tile padding: never reported
-        rec.state = 0;
-        if (lane == 0) e.rec[s] = rec;
-        return;
-    }
     const uint64_t p0 = b.snarl_path_off[s], p1 = b.snarl_path_off[s + 1];
     if (!allow_dense || p1 - p0 != 2 || e.n_samples > 65535u) return to_general();
     const uint32_t chunks = uint32_t(m.pitch / 16), n_hap = uint32_t(m.n_cols);
@@ -132,7 +122,6 @@ __global__ void __launch_bounds__(128) eqtl_dosage_codes_kernel(const MatrixDev 
             al0 += popc4(a);
             al1 += popc4(bb);
             const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {bb.x, bb.y, bb.z, bb.w};
-            uint32_t cw[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const LeanMasks mk = lean_masks(av[k], bv[k]);
@@ -140,11 +129,9 @@ __global__ void __launch_bounds__(128) eqtl_dosage_codes_kernel(const MatrixDev 
                 n_full0 += __popc(mk.full0);
                 n_half += __popc(mk.half);
                 nd |= mk.third | mk.tthird;
-                cw[k] = (mk.full0 << 1) | mk.half;  // sample i of the word at bits 2i..2i+1: 0 -> 0, 1 -> 1/2, 2 -> 1
                 un_mask[k] = ~mk.used & 0x55555555u & valid_word(4 * c + k, n_hap);
                 my_un += __popc(un_mask[k]);
             }
-            *reinterpret_cast<uint4*>(e.dcode + (uint64_t(c) * e.s_pad + s) * 16) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
         }
         // samples on no path: keep the first kEqMaxUnused (in sample order)
         uint32_t incl = my_un;
@@ -189,12 +176,16 @@ __global__ void __launch_bounds__(128) eqtl_dosage_codes_kernel(const MatrixDev 
         out.filtered[s] = filtered ? 1 : 0;
         out.n_used[s] = n_used;
     }
-    if (filtered) {
-        rec.state = 0;
-        if (lane == 0) e.rec[s] = rec;
+    if (filtered) {  // reported here: the scan never sees this snarl
+        if (lane == 0) {
+            e.min_p[s] = __longlong_as_double(0x7ff8000000000000LL);
+            e.argmin[s] = 0;
+            e.n_below[s] = 0;
+        }
         return;
     }
     if (n_un > uint32_t(kEqMaxUnused)) return to_general();
+    uint32_t slot = 0xFFFFFFFFu;
     if (lane == 0) {
         SmallMat<4> X, inv;
         for (int i = 0; i < 16; ++i) X.a[i] = 0.0;
@@ -203,9 +194,11 @@ __global__ void __launch_bounds__(128) eqtl_dosage_codes_kernel(const MatrixDev 
         X(0, 1) = X(1, 0) = colsum0;
         X(1, 1) = sdd;
         if (xtx_inverse<4>(X, 2, inv)) {  // rank deficient: the pseudo-inverse is not shift invariant -> raw y, general path
-            e.rec[s] = rec;
             e.fb_list[atomicAdd(e.fb_count, 1u)] = uint32_t(s);
         } else {
+            // dense snarls are compacted: the contraction runs over slots, not over filtered / general-path snarls
+            slot = atomicAdd(e.dense_count, 1u);
+            EqtlRec rec{};
             rec.inv00 = inv(0, 0);
             rec.inv01 = inv(0, 1);
             rec.inv11 = inv(1, 1);
@@ -215,15 +208,30 @@ __global__ void __launch_bounds__(128) eqtl_dosage_codes_kernel(const MatrixDev 
             rec.n_unused = uint8_t(n_un);
             for (uint32_t k = 0; k < n_un; ++k) rec.unused[k] = unused_s[warp][k];
             rec.state = 1;
-            e.rec[s] = rec;
+            e.rec[slot] = rec;
+            e.slot_snarl[slot] = uint32_t(s);
         }
+    }
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+    if (slot == 0xFFFFFFFFu) return;
+    // second pass over the (cache-hot) rows: the 2-bit codes, written at the snarl's slot
+    for (uint32_t c = lane; c < chunks; c += 32) {
+        const uint4 a = eq_path_chunk(m, b, p0, c), bb = eq_path_chunk(m, b, p0 + 1, c);
+        const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {bb.x, bb.y, bb.z, bb.w};
+        uint32_t cw[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const LeanMasks mk = lean_masks(av[k], bv[k]);
+            cw[k] = (mk.full0 << 1) | mk.half;  // sample i of the word at bits 2i..2i+1: 0 -> 0, 1 -> 1/2, 2 -> 1
+        }
+        *reinterpret_cast<uint4*>(e.dcode + (uint64_t(c) * e.s_pad + slot) * 16) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
     }
 }
 
 cudaError_t launch_eqtl_dosage_codes(const MatrixDev& m, const BatchDev& b, const stoat_gpu_thresholds& thr, bool allow_dense,
                                      const EqtlDense& e, QuantOut out, cudaStream_t st) {
-    if (e.s_pad == 0) return cudaSuccess;
-    eqtl_dosage_codes_kernel<<<unsigned((e.s_pad + 3) / 4), 128, 0, st>>>(m, b, thr, allow_dense, e, out);
+    if (e.n_snarls == 0) return cudaSuccess;
+    eqtl_dosage_codes_kernel<<<unsigned((e.n_snarls + 3) / 4), 128, 0, st>>>(m, b, thr, allow_dense, e, out);
     return cudaGetLastError();
 }
 
@@ -238,14 +246,27 @@ constexpr int kEqStageBytes = kEqStageB + kEqStageA;  // 38,912
 constexpr int kEqConsumerWarps = 8;                   // 4 (snarls) x 2 (genes), warp tile 32 x 32
 constexpr int kEqThreads = (kEqConsumerWarps + 1) * 32;
 
+// what the epilogue needs of EqtlDense, kept in shared memory so that the per-pair function takes one pointer
+struct EqConst {
+    const double* yc;
+    const double* tot;
+    const double* tot2;
+    const uint8_t* dcode;
+    uint64_t s_pad;
+    uint32_t n_pad, n_samples;
+    double p_threshold, z_threshold;
+};
+
 struct EqSmem {
     uint64_t full[kEqStages], empty[kEqStages];
+    EqConst k;
     EqtlRec rec[kEqTileS];
     double best_key[2][kEqTileS];
     uint32_t best_gene[2][kEqTileS];
     uint32_t cnt[2][kEqTileS];
 };
-size_t eqtl_dense_smem_bytes() { return sizeof(EqSmem) + 128 + size_t(kEqStages) * kEqStageBytes; }
+constexpr size_t kEqStageOff = (sizeof(EqSmem) + 127) / 128 * 128;
+size_t eqtl_dense_smem_bytes() { return kEqStageOff + size_t(kEqStages) * kEqStageBytes; }
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -276,12 +297,43 @@ __device__ __noinline__ double eq_rss_explicit(const double* y, const uint8_t* d
     return rss;
 }
 
+// One (snarl, gene) regression from its moments: the tail of linear_regression (stats_test.cpp:455-489) for X = [1, d].
+// Returns (|t| + 1), negated when the pair's p-value is below the threshold; an invalid t (p = 1, :480-482) ranks as t = 0.
+__device__ __noinline__ double eq_pair_stat(const EqConst* k, const EqtlRec* rp, uint64_t s, uint32_t g, double sdy) {
+    const EqtlRec& r = *rp;
+    const double n_used = double(r.n_used);
+    int df_res = int(r.n_used) - 2 + 1;  // stats_test.cpp:467 (sic)
+    if (df_res < 1) df_res = 1;
+    const double* yrow = k->yc + uint64_t(g) * k->n_pad;
+    double sy = k->tot[g], syy = k->tot2[g];
+    for (uint32_t u = 0; u < r.n_unused; ++u) {  // samples on no path are not rows of the table
+        const double y = yrow[r.unused[u]];
+        sy -= y;
+        syy = fma(-y, y, syy);
+    }
+    const double b0 = r.inv00 * sy + r.inv01 * sdy, b1 = r.inv01 * sy + r.inv11 * sdy;
+    const double bxy = b0 * sy + b1 * sdy;
+    const double bxxb = b0 * (n_used * b0 + r.sd * b1) + b1 * (r.sd * b0 + r.sdd * b1);
+    double rss = syy - 2.0 * bxy + bxxb;
+    const double tss = syy - sy * sy / n_used;
+    if (!(rss > 1e-6 * tss)) rss = eq_rss_explicit(yrow, k->dcode + s * 16, k->s_pad, k->n_samples, rp, b0, b1);
+    const double se = sqrt(r.inv11 * (rss / double(df_res)));
+    const double t = b1 / se;
+    const bool fin = !(isnan(t) || isinf(t));
+    const double key = fin ? fabs(t) : 0.0;
+    const bool below = fin ? (key > k->z_threshold && 2.0 * student_t_upper_tail(double(df_res), key) < k->p_threshold)
+                           : (1.0 < k->p_threshold);
+    return below ? -(key + 1.0) : key + 1.0;
+}
+
 __global__ void __launch_bounds__(kEqThreads, 1) eqtl_dense_dmma_kernel(const EqtlDense e) {
-    extern __shared__ __align__(16) uint8_t eq_smem_raw[];
+    extern __shared__ __align__(128) uint8_t eq_smem_raw[];
     EqSmem& sm = *reinterpret_cast<EqSmem*>(eq_smem_raw);
-    uint8_t* stages = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(eq_smem_raw) + sizeof(EqSmem) + 127) & ~uintptr_t(127));
+    uint8_t* stages = eq_smem_raw + kEqStageOff;  // plain offset from the shared array: the compiler emits LDS, not generic LD
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint64_t s0 = uint64_t(blockIdx.x) * kEqTileS;
+    const uint64_t s0 = uint64_t(blockIdx.x) * kEqTileS;  // first SLOT of this tile (dense snarls, compacted by E0)
+    const uint32_t n_dense = *e.dense_count;
+    if (s0 >= n_dense) return;
     const uint32_t grp = blockIdx.y;
     const uint32_t g_begin = grp * e.genes_per_group;
     const uint32_t g_end = min(e.n_genes, g_begin + e.genes_per_group);
@@ -294,9 +346,12 @@ __global__ void __launch_bounds__(kEqThreads, 1) eqtl_dense_dmma_kernel(const Eq
             mbar_init(&sm.empty[i], kEqConsumerWarps);
         }
         mbar_fence_init();
+        sm.k = EqConst{e.yc, e.tot, e.tot2, e.dcode, e.s_pad, e.n_pad, e.n_samples, e.p_threshold, e.z_threshold};
     }
-    for (uint32_t i = tid; i < kEqTileS * (sizeof(EqtlRec) / 16); i += kEqThreads)
-        reinterpret_cast<uint4*>(sm.rec)[i] = reinterpret_cast<const uint4*>(e.rec + s0)[i];
+    for (uint32_t i = tid; i < kEqTileS * (sizeof(EqtlRec) / 16); i += kEqThreads) {
+        const bool live = s0 + i / (sizeof(EqtlRec) / 16) < n_dense;  // slots past the end: state 0, never reported
+        reinterpret_cast<uint4*>(sm.rec)[i] = live ? reinterpret_cast<const uint4*>(e.rec + s0)[i] : make_uint4(0, 0, 0, 0);
+    }
     for (uint32_t i = tid; i < 2 * kEqTileS; i += kEqThreads) {
         (&sm.best_key[0][0])[i] = -1.0;
         (&sm.best_gene[0][0])[i] = 0xFFFFFFFFu;
@@ -372,45 +427,26 @@ __global__ void __launch_bounds__(kEqThreads, 1) eqtl_dense_dmma_kernel(const Eq
         }
         // ---------------- epilogue of this gene tile: acc[mt][nt][c] = sum d * yc of (snarl, gene)
         const uint32_t g_tile = g_begin + gt * kEqTileG + wn * 32;
-#pragma unroll 1
+#pragma unroll
         for (int mt = 0; mt < 4; ++mt) {
             const uint32_t sl = wm * 32 + mt * 8 + gid;
-            const EqtlRec& r = sm.rec[sl];
+            const EqtlRec* r = &sm.rec[sl];
             double bk = -1.0;
             uint32_t bg = 0xFFFFFFFFu, cnt = 0;
-            if (r.state == 1) {
-                const double n_used = double(r.n_used);
-                int df_res = int(r.n_used) - 2 + 1;  // stats_test.cpp:467 (sic)
-                if (df_res < 1) df_res = 1;
+            if (r->state == 1) {
 #pragma unroll
                 for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
                     for (int c = 0; c < 2; ++c) {
                         const uint32_t g = g_tile + nt * 8 + 2 * tig + c;
-                        if (g >= g_end) continue;
-                        double sy = e.tot[g], syy = e.tot2[g];
-                        for (uint32_t k = 0; k < r.n_unused; ++k) {
-                            const double y = e.yc[uint64_t(g) * e.n_pad + r.unused[k]];
-                            sy -= y;
-                            syy = fma(-y, y, syy);
-                        }
-                        const double sdy = acc[mt][nt][c];
-                        const double b0 = r.inv00 * sy + r.inv01 * sdy, b1 = r.inv01 * sy + r.inv11 * sdy;
-                        const double bxy = b0 * sy + b1 * sdy;
-                        const double bxxb = b0 * (n_used * b0 + r.sd * b1) + b1 * (r.sd * b0 + r.sdd * b1);
-                        double rss = syy - 2.0 * bxy + bxxb;
-                        const double tss = syy - sy * sy / n_used;
-                        if (!(rss > 1e-6 * tss)) rss = eq_rss_explicit(e.yc + uint64_t(g) * e.n_pad, e.dcode + (s0 + sl) * 16, e.s_pad, e.n_samples, &r, b0, b1);
-                        const double se = sqrt(r.inv11 * (rss / double(df_res)));
-                        const double t = b1 / se;
-                        const bool fin = !(isnan(t) || isinf(t));
-                        const double key = fin ? fabs(t) : 0.0;  // invalid t: p = 1 (stats_test.cpp:480-482) = p at t = 0
-                        if (fin ? (key > e.z_threshold && 2.0 * student_t_upper_tail(double(df_res), key) < e.p_threshold)
-                                : (1.0 < e.p_threshold))
-                            ++cnt;
-                        if (key > bk || (key == bk && g < bg)) {
-                            bk = key;
-                            bg = g;
+                        if (g < g_end) {
+                            const double key = eq_pair_stat(&sm.k, r, s0 + sl, g, acc[mt][nt][c]);  // < 0: also below threshold
+                            const double ak = fabs(key) - 1.0;
+                            cnt += key < 0.0 ? 1u : 0u;
+                            if (ak > bk || (ak == bk && g < bg)) {
+                                bk = ak;
+                                bg = g;
+                            }
                         }
                     }
             }
@@ -425,7 +461,7 @@ __global__ void __launch_bounds__(kEqThreads, 1) eqtl_dense_dmma_kernel(const Eq
                     bg = og;
                 }
             }
-            if (tig == 0 && r.state == 1) {  // this warp alone owns [wn][its 32 snarls]
+            if (tig == 0 && r->state == 1) {  // this warp alone owns [wn][its 32 snarls]
                 sm.cnt[wn][sl] += cnt;
                 const double cur = sm.best_key[wn][sl];
                 if (bk > cur || (bk == cur && bg < sm.best_gene[wn][sl])) {
@@ -465,21 +501,15 @@ cudaError_t launch_eqtl_dense(const EqtlDense& e, int /*num_sms*/, cudaStream_t 
 // E2: merge the gene groups, p of the best gene
 // =================================================================================================
 __global__ void __launch_bounds__(128) eqtl_dense_finish_kernel(const EqtlDense e) {
-    const uint64_t s = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (s >= e.n_snarls) return;
-    const EqtlRec r = e.rec[s];
-    if (r.state == 2) return;  // the general path reports this snarl
+    const uint64_t slot = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (slot >= *e.dense_count) return;
+    const EqtlRec r = e.rec[slot];
+    const uint32_t s = e.slot_snarl[slot];
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
-    if (r.state == 0) {
-        e.min_p[s] = nan;
-        e.argmin[s] = 0;
-        e.n_below[s] = 0;
-        return;
-    }
     double bk = -1.0;
     uint32_t bg = 0xFFFFFFFFu, cnt = 0;
     for (uint32_t grp = 0; grp < e.n_groups; ++grp) {
-        const uint64_t o = uint64_t(grp) * e.s_pad + s;
+        const uint64_t o = uint64_t(grp) * e.s_pad + slot;
         const double k = e.part_key[o];
         const uint32_t g = e.part_gene[o];
         cnt += e.part_cnt[o];
