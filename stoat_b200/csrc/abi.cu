@@ -48,7 +48,7 @@ MatrixDev matrix_view(const stoat_gpu_ctx* ctx) {
 }
 
 struct QuantState {
-    DevBuf yc, ys, mom;
+    DevBuf yc, ys, mom, part_i, part_d, slow;
     double sy_all = 0.0, syy_all = 0.0;
 };
 
@@ -129,6 +129,9 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     x->q.yc.release();
     x->q.ys.release();
     x->q.mom.release();
+    x->q.part_i.release();
+    x->q.part_d.release();
+    x->q.slow.release();
     for (auto& ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -461,6 +464,10 @@ static int quant_reserve(stoat_gpu_ctx* ctx) {
     CK(ctx->q_se.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
     CK(ctx->q_code.reserve(std::max<uint64_t>(b.n_snarls, 16)));
     CK(x->q.mom.reserve(std::max<size_t>(quant_moments_bytes(b.n_snarls), 16)));
+    const uint64_t slices = std::max<uint32_t>(quant_reg_slices(ctx->pitch), 1);
+    CK(x->q.part_i.reserve(std::max<uint64_t>(slices * 7 * b.n_snarls * 4, 16)));
+    CK(x->q.part_d.reserve(std::max<uint64_t>(slices * 3 * b.n_snarls * 8, 16)));
+    CK(x->q.slow.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
     return STOAT_GPU_OK;
 }
 
@@ -494,7 +501,8 @@ int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresh
     CK(launch_quantitative_impl(matrix_view(ctx), ctx->y.as<double>(), x->q.ys.as<double>(), x->q.sy_all,
                                 x->q.syy_all, ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar),
                                 ctx->batch, x->max_stage_rows, *thr, out,
-                                reinterpret_cast<QuantMoments*>(x->q.mom.p), ctx->num_sms, ctx->k1_variant,
+                                reinterpret_cast<QuantMoments*>(x->q.mom.p), x->q.part_i.as<uint32_t>(),
+                                x->q.part_d.as<double>(), x->q.slow.as<uint32_t>(), ctx->num_sms, ctx->k1_variant,
                                 ctx->stream, &ctx->timing.launches));
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
     CK(cudaMemcpyAsync(x->readback, ctx->d_counters.p, 4, cudaMemcpyDeviceToHost, ctx->stream));

@@ -101,8 +101,10 @@ struct QuantOut {
 cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, const double* ys_perm,
                                      double sy_all, double syy_all, const double* covar, uint32_t n_covar,
                                      const BatchDev& b, uint32_t max_stage_rows, const stoat_gpu_thresholds& thr,
-                                     QuantOut out, QuantMoments* mom, int num_sms, int variant, cudaStream_t st,
+                                     QuantOut out, QuantMoments* mom, uint32_t* part_i, double* part_d,
+                                     uint32_t* slow_list, int num_sms, int variant, cudaStream_t st,
                                      uint32_t* launches);
+uint32_t quant_reg_slices(uint64_t pitch);  // slices of the haplotype range K3R uses (0: K3R switched off)
 cudaError_t launch_centre_permute(const double* y, uint32_t n, double mean, uint32_t n_words, double* yc, double* ys,
                                   cudaStream_t st);
 size_t quant_moments_bytes(uint64_t n_snarls);

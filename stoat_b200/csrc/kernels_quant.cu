@@ -59,6 +59,8 @@ struct K3Params {
     QuantMoments* mom;
     uint32_t* g_list;
     uint32_t* g_count;
+    const uint32_t* list;        // K3 over a list of snarls (those K3R left over); nullptr: all snarls
+    const uint32_t* list_count;  // device-side length of `list`
 };
 
 
@@ -358,6 +360,7 @@ __device__ bool quant_fast(const K3Params& p, const uint8_t* blob, const uint8_t
 }
 
 #include "quant_lean.cuh"
+#include "quant_reg.cuh"
 
 // =================================================================================================
 // K3 kernel: per-warp TMA pipelines (same structure as K1), fast path per snarl
@@ -366,6 +369,8 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t n_warps = blockDim.x >> 5;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint64_t n_items = p.list ? uint64_t(__ldg(p.list_count)) : p.n_snarls;
+    if (uint64_t(blockIdx.x) * n_warps >= n_items) return;  // CTA-uniform: a short list leaves most of the grid idle
     const uint32_t stage_bytes = kBlobBytesQ + p.stage_rows * p.pitch;
     const uint32_t n_words = p.pitch / 4;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
@@ -381,6 +386,7 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
     for (uint32_t i = threadIdx.x; i < 16u * n_words; i += blockDim.x) ys_s[i] = __ldg(p.ys + i);
     __syncthreads();
 
+    auto snarl_at = [&](uint64_t k) -> uint64_t { return p.list ? uint64_t(__ldg(p.list + k)) : k; };
     const uint64_t gw = uint64_t(blockIdx.x) * n_warps + warp;
     const uint64_t stride = uint64_t(gridDim.x) * n_warps;
     uint64_t* my_full = full + warp * p.n_stages;
@@ -389,18 +395,19 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
 
     // prologue: fill the pipeline (lane-distributed issue, consecutive rows merged: stage_pipeline.cuh)
     {
-        uint64_t s = gw;
-        for (uint32_t st = 0; st < p.n_stages && s < p.n_snarls; ++st, s += stride)
-            issue_stage(load_rec_word(p.rec, s, lane), lane, my_stages + size_t(st) * stage_bytes, &my_full[st], p.rows,
-                        p.blob, p.pitch, policy);
+        uint64_t k = gw;
+        for (uint32_t st = 0; st < p.n_stages && k < n_items; ++st, k += stride)
+            issue_stage(load_rec_word(p.rec, snarl_at(k), lane), lane, my_stages + size_t(st) * stage_bytes, &my_full[st],
+                        p.rows, p.blob, p.pitch, policy);
     }
 
     uint32_t it = 0;
-    for (uint64_t s = gw; s < p.n_snarls; s += stride, ++it) {
+    for (uint64_t k = gw; k < n_items; k += stride, ++it) {
+        const uint64_t s = snarl_at(k);
         const uint32_t stage = it % p.n_stages;
         const uint32_t parity = (it / p.n_stages) & 1u;
-        const uint64_t s_next = s + uint64_t(p.n_stages) * stride;
-        uint32_t next_word = (s_next < p.n_snarls) ? load_rec_word(p.rec, s_next, lane) : 0u;
+        const uint64_t k_next = k + uint64_t(p.n_stages) * stride;
+        uint32_t next_word = (k_next < n_items) ? load_rec_word(p.rec, snarl_at(k_next), lane) : 0u;
         mbar_wait(&my_full[stage], parity);
         const uint8_t* blob = my_stages + size_t(stage) * stage_bytes;
         const uint8_t* rows_s = blob + kBlobBytesQ;
@@ -424,7 +431,7 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
         }
         __syncwarp();
         asm volatile("" : "+r"(next_word));
-        if (s_next < p.n_snarls)  // WAR on a read-only stage: no proxy fence (see issue_stage)
+        if (k_next < n_items)  // WAR on a read-only stage: no proxy fence (see issue_stage)
             issue_stage(next_word, lane, my_stages + size_t(stage) * stage_bytes, &my_full[stage], p.rows, p.blob,
                         p.pitch, policy);
     }
@@ -433,12 +440,43 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
 // =================================================================================================
 // K4: solve
 // =================================================================================================
+// state 1: moments written by K3 (warp-per-snarl kernel); state 2: two-path snarl whose class counts and sums K3R left
+// in `part` (n_slices slices, added here) — filters and moments are then built in registers (lean_finish).
 __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __restrict__ mom, uint64_t n_snarls,
-                                                        QuantOut out, uint32_t* g_list, uint32_t* g_count) {
+                                                        const K3Params kp, const LeanPartials part, uint32_t n_slices,
+                                                        const uint64_t* __restrict__ snarl_path_off, QuantOut out,
+                                                        uint32_t* g_list, uint32_t* g_count) {
     const uint64_t s = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (s >= n_snarls) return;
-    const QuantMoments m = mom[s];
-    if (m.state != 1) return;
+    const uint8_t state = mom[s].state;
+    if (state != 1 && state != 2) return;
+    QuantMoments m;
+    if (state == 2) {
+        LeanSums t{};
+        for (uint32_t sl = 0; sl < n_slices; ++sl) {
+            const uint32_t* pi = part.i + size_t(sl) * 7 * part.stride + s;
+            const double* pd = part.d + size_t(sl) * 3 * part.stride + s;
+            t.al0 += pi[0];
+            t.al1 += pi[part.stride];
+            t.n_used += pi[2 * part.stride];
+            t.n_full0 += pi[3 * part.stride];
+            t.n_half += pi[4 * part.stride];
+            t.n_third += pi[5 * part.stride];
+            t.n_tthird += pi[6 * part.stride];
+            t.xty1 += pd[0];
+            t.su_un += pd[part.stride];
+            t.suu_un += pd[2 * part.stride];
+        }
+        const int r = lean_finish(kp, s, uint32_t(snarl_path_off[s]), t, m);
+        if (r == 0) return;
+        if (r == 2) {
+            const uint32_t slot = atomicAdd(g_count, 1u);
+            g_list[slot] = uint32_t(s);
+            return;
+        }
+    } else {
+        m = mom[s];
+    }
     const int p = m.p;
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
     if (p < 2) {  // no regression column left: the reference indexes past the end (stats_test.cpp:487-489)
@@ -523,11 +561,68 @@ static bool choose_k3_config(uint32_t pitch, uint32_t stage_rows, K3Config& cfg)
     return true;
 }
 
-// scratch owned by the caller: mom [n_snarls], ys permuted, sums
+// ---- K3R launch plan ---------------------------------------------------------------------------------
+struct K3RPlan {
+    int wpt = 0;  // 0: K3R does not apply
+    uint32_t threads = 0, n_slices = 0, slice_words = 0, n_ring = 0, smem_bytes = 0, ctas_per_sm = 0;
+};
+using K3RKernel = void (*)(const K3RParams);
+static K3RKernel k3r_kernel(int wpt) {
+    return wpt == 1 ? dosage_moments_reg_kernel<1> : wpt == 2 ? dosage_moments_reg_kernel<2> : dosage_moments_reg_kernel<4>;
+}
+static int env_int(const char* name, int dflt) {
+    const char* e = std::getenv(name);
+    return e ? std::atoi(e) : dflt;
+}
+static void k3r_shape(uint32_t pitch, K3RPlan& pl) {
+    const uint32_t n_words = pitch / 4;
+    int wpt = env_int("STOAT_GPU_K3R_WPT", 2);
+    if (wpt != 1 && wpt != 2 && wpt != 4) wpt = 2;
+    const uint32_t per_cta = uint32_t(kRegMaxWarps) * 32u * uint32_t(wpt);
+    pl.wpt = wpt;
+    pl.n_slices = (n_words + per_cta - 1) / per_cta;
+    pl.slice_words = (((n_words + pl.n_slices - 1) / pl.n_slices) + 3u) & ~3u;
+    pl.threads = (((pl.slice_words + wpt - 1) / wpt) + 31u) & ~31u;
+}
+uint32_t quant_reg_slices(uint64_t pitch) {
+    if (env_int("STOAT_GPU_K3R", 1) == 0 || pitch == 0) return 0;
+    K3RPlan pl;
+    k3r_shape(uint32_t(pitch), pl);
+    return pl.n_slices;
+}
+static bool k3r_plan(uint32_t pitch, uint32_t stage_rows, K3RPlan& pl) {
+    if (env_int("STOAT_GPU_K3R", 1) == 0) return false;
+    if (stage_rows == 0) stage_rows = 1;
+    k3r_shape(pitch, pl);
+    const uint32_t stage_bytes = kStageBlobBytes + stage_rows * pl.slice_words * 4;
+    K3RKernel fn = k3r_kernel(pl.wpt);
+    const uint32_t budget = 224 * 1024;
+    if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(budget)) != cudaSuccess) return false;
+    int occ = 0;  // CTAs per SM that registers / threads allow with the smallest ring
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, int(pl.threads), 128 + 2 * stage_bytes) != cudaSuccess ||
+        occ < 1)
+        return false;
+    const int want = env_int("STOAT_GPU_K3R_CTAS", 0);
+    if (want >= 1 && want < occ) occ = want;
+    const uint32_t per_cta = (budget - 1024) / uint32_t(occ) - 1024;  // 1 KB per CTA is reserved by the driver
+    uint32_t ring = (per_cta - 128) / stage_bytes;
+    const int ring_env = env_int("STOAT_GPU_K3R_RING", 0);
+    const uint32_t ring_max = ring_env >= 2 ? uint32_t(ring_env) : 8u;
+    if (ring > ring_max) ring = ring_max;
+    if (ring < 2) return false;
+    pl.n_ring = ring;
+    pl.smem_bytes = ((ring * 8 + 127) & ~127u) + ring * stage_bytes;
+    pl.ctas_per_sm = uint32_t(occ);
+    return true;
+}
+
+// scratch owned by the caller: mom [n_snarls], ys permuted, sums; K3R: part_i [slices][7][S], part_d [slices][3][S],
+// slow_list [S]; counters[3] = length of the slow list
 cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, const double* ys_perm,
                                      double sy_all, double syy_all, const double* covar, uint32_t n_covar,
                                      const BatchDev& b, uint32_t max_stage_rows, const stoat_gpu_thresholds& thr,
-                                     QuantOut out, QuantMoments* mom, int num_sms, int variant, cudaStream_t st,
+                                     QuantOut out, QuantMoments* mom, uint32_t* part_i, double* part_d,
+                                     uint32_t* slow_list, int num_sms, int variant, cudaStream_t st,
                                      uint32_t* launches) {
     if (b.n_snarls == 0) return cudaSuccess;
     const uint32_t pitch = uint32_t(m.pitch);
@@ -569,12 +664,39 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         e = cudaFuncSetAttribute(dosage_moments_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  int(cfg.smem_bytes));
         if (e != cudaSuccess) return e;
-        const uint64_t want = (b.n_snarls + cfg.n_warps - 1) / cfg.n_warps;
-        const unsigned grid = unsigned(want < uint64_t(num_sms) ? want : uint64_t(num_sms));
-        dosage_moments_tma_kernel<<<grid, cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
-        ols_solve_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(mom, b.n_snarls, out, b.big_list,
-                                                                            b.counters);
+        K3RPlan pl;
+        LeanPartials part{part_i, part_d, b.n_snarls};
+        uint32_t n_slices = 0;
+        if (part_i && part_d && slow_list && k3r_plan(pitch, cfg.stage_rows, pl)) {
+            // K3R over every snarl (two-path snarls -> partial sums), then K3 over what it left on the slow list
+            K3RParams q{};
+            q.k = p;
+            q.slice_words = pl.n_slices == 1 ? pitch / 4 : pl.slice_words;
+            q.n_ring = pl.n_ring;
+            q.slow_list = slow_list;
+            q.slow_count = b.counters + 3;
+            q.part = part;
+            q.partial_only = 1;
+            n_slices = pl.n_slices;
+            if ((e = cudaMemsetAsync(b.counters + 3, 0, 4, st)) != cudaSuccess) return e;
+            uint64_t ctas = uint64_t(num_sms) * pl.ctas_per_sm / pl.n_slices;
+            if (ctas < 1) ctas = 1;
+            if (ctas > b.n_snarls) ctas = b.n_snarls;
+            k3r_kernel(pl.wpt)<<<dim3(unsigned(ctas), pl.n_slices), pl.threads, pl.smem_bytes, st>>>(q);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            p.list = slow_list;
+            p.list_count = b.counters + 3;
+            dosage_moments_tma_kernel<<<unsigned(num_sms), cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            if (launches) *launches += 1;
+        } else {
+            const uint64_t want = (b.n_snarls + cfg.n_warps - 1) / cfg.n_warps;
+            const unsigned grid = unsigned(want < uint64_t(num_sms) ? want : uint64_t(num_sms));
+            dosage_moments_tma_kernel<<<grid, cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        }
+        ols_solve_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(mom, b.n_snarls, p, part, n_slices,
+                                                                            b.snarl_path_off, out, b.big_list, b.counters);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         g.list = b.big_list;
         g.n_list_dev = b.counters;

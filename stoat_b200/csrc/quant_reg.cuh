@@ -1,0 +1,376 @@
+// quant_reg.cuh — K3R, the register-resident form of K3 for two-path snarls (included by kernels_quant.cu,
+// namespace stoat).
+//
+// K3 (quant_lean.cuh) gives a snarl to a warp, so a lane meets different samples in every iteration and has to fetch
+// their phenotype values from shared memory: one LDS.64 + bit tests + selects per sample and class, ~20 instructions per
+// sample, which made the quantitative step issue bound at 0.14 of the HBM roofline.  K3R turns the mapping round: a CTA
+// takes ONE snarl at a time and thread t always owns the same WPT 32-haplotype words (16 * WPT samples), so the centred
+// phenotype of those samples is loaded ONCE into registers and stays there for the whole kernel.  Per sample and class
+// the inner loop is then a predicate-writing LOP3 and a predicated DADD — 4 issue slots per sample, at the rate of the
+// FP64 pipe (2 DADDs per sample).
+//
+//   * rows are staged exactly as in K1 / K3 (cp.async.bulk into a ring of shared-memory stages, one mbarrier per stage,
+//     issued lane-distributed by warp 0), but the ring belongs to the CTA; a stage is refilled after the CTA-wide
+//     barrier that also publishes the per-warp partial sums;
+//   * per snarl every warp reduces its class counts (packed REDUX) and three FP64 sums (shuffles), a rotating warp adds
+//     the warps' partials and either finishes the snarl (filters of snarl_analyzer.cpp:542-579, moments for K4) or, when
+//     the haplotype range is split over gridDim.y slices / over GPUs (sample sharding), stores the slice's partial sums
+//     for K3F (lean_finish_kernel), which runs after the slices are added up;
+//   * any other shape (1, 3, 4 paths, > 4 checked edges) goes to the slow list and is done by K3's warp-per-snarl kernel.
+#pragma once
+
+struct LeanSums {
+    uint32_t al0, al1, n_used, n_full0, n_half, n_third, n_tthird;
+    double xty1, su_un, suu_un;  // sum d0 * y over the used samples; sum y, sum y^2 over the UNUSED samples
+};
+
+// SoA partial sums of a slice (and the buffer a sample-sharded run all-reduces): ints [7][S], doubles [3][S]
+struct LeanPartials {
+    uint32_t* i;
+    double* d;
+    uint64_t stride;  // S
+};
+
+struct K3RParams {
+    K3Params k;
+    uint32_t slice_words;  // words of a row one CTA (slice) covers; == n_words when gridDim.y == 1
+    uint32_t n_ring;       // stages in the CTA's ring
+    uint32_t* slow_list;
+    uint32_t* slow_count;
+    LeanPartials part;     // used when partial_only
+    uint32_t partial_only;
+};
+
+// Filters + moments of a two-path snarl from its class counts and sums (what quant_lean2 does after its passes).
+// One thread.  Returns 0: filtered (outputs written), 1: moments ready in `mom`, 2: the snarl must be replayed by the
+// general path (non-dyadic borderline filters).
+__device__ int lean_finish(const K3Params& p, uint64_t s, uint32_t p0, const LeanSums& t, QuantMoments& mom) {
+    p.out.allele_paths[p0] = t.al0;  // quantitative_table.cpp:54-55
+    p.out.allele_paths[p0 + 1] = t.al1;
+    const bool nondyadic = (t.n_third | t.n_tthird) != 0u;
+    const uint32_t n_used = t.n_used;
+    const uint32_t n_full1 = n_used - t.n_full0 - t.n_half - t.n_third - t.n_tthird;
+    const double third = 1.0 / 3.0, tthird = 2.0 / 3.0;
+    const double colsum0 =
+        double(t.n_full0) + 0.5 * double(t.n_half) + third * double(t.n_third) + tthird * double(t.n_tthird);
+    const double colsum1 = double(n_full1) + 0.5 * double(t.n_half) + tthird * double(t.n_third) + third * double(t.n_tthird);
+    bool filtered = (n_used == 0) || (t.al0 == 0) || (t.al1 == 0) || (uint64_t(n_used) < p.thr.min_individuals);
+    if (!filtered) {
+        const double total = double(n_used);  // every used row sums to 1
+        if (nondyadic && uint64_t(n_used) == p.thr.min_haplotypes) return 2;  // borderline: exact replay
+        if (total < double(p.thr.min_haplotypes)) filtered = true;
+        const double f0 = __ddiv_rn(colsum0, total), f1 = __ddiv_rn(colsum1, total);
+        const double maf0 = fmin(f0, __dsub_rn(1.0, f0)), maf1 = fmin(f1, __dsub_rn(1.0, f1));
+        if (nondyadic && (fabs(maf0 - p.thr.maf_threshold) <= 1e-9 || fabs(maf1 - p.thr.maf_threshold) <= 1e-9))
+            return 2;
+        if (!(maf0 > p.thr.maf_threshold && maf1 > p.thr.maf_threshold)) filtered = true;
+    }
+    p.out.filtered[s] = filtered ? 1 : 0;
+    p.out.n_used[s] = n_used;
+    if (filtered) return 0;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) mom.xtx[i] = 0.0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) mom.xty[i] = 0.0;
+    mom.n_used = n_used;
+    mom.p = 2;
+    mom.state = 1;
+    mom.pad = 0;
+    const double su = p.sy_all - t.su_un, suu = p.syy_all - t.suu_un;
+    mom.xtx[0] = double(n_used);
+    mom.xtx[1] = colsum0;
+    mom.xtx[2] =
+        double(t.n_full0) + 0.25 * double(t.n_half) + (1.0 / 9.0) * double(t.n_third) + (4.0 / 9.0) * double(t.n_tthird);
+    mom.xty[0] = su;
+    mom.xty[1] = t.xty1;
+    mom.sy = su;
+    mom.syy = suu;
+    return 1;
+}
+
+// Stage refill for a slice of the haplotype range: like issue_stage (stage_pipeline.cuh), but every row contributes only
+// the bytes [slice_off, slice_off + slice_bytes) and lands in a slot of slot_bytes.  Whole rows (slice_bytes == pitch):
+// runs of consecutive matrix rows still go out as one bulk copy.
+__device__ __forceinline__ void issue_stage_slice(uint32_t rec_word, uint32_t lane, uint8_t* dst, uint64_t* bar,
+                                                  const uint8_t* rows, const uint8_t* blob, uint32_t pitch,
+                                                  uint32_t slice_off, uint32_t slice_bytes, uint32_t slot_bytes,
+                                                  uint64_t policy) {
+    const uint32_t packed = __shfl_sync(0xffffffffu, rec_word, 7);
+    const uint32_t n_rows = packed & 0xFFu, blob_bytes = ((packed >> 8) & 0xFFu) * 16u;
+    if (lane == 7) mbar_arrive_expect_tx(bar, blob_bytes + n_rows * slice_bytes);
+    __syncwarp();
+    const bool whole = slice_bytes == pitch && slot_bytes == pitch;
+    const uint32_t prev = __shfl_up_sync(0xffffffffu, rec_word, 1);
+    const bool head = lane < n_rows && (!whole || lane == 0 || rec_word != prev + 1u);
+    const uint32_t heads = __ballot_sync(0xffffffffu, head) | (1u << n_rows);
+    if (head) {
+        const uint32_t run = whole ? uint32_t(__ffs(int(heads >> (lane + 1)))) : 1u;
+        tma_bulk_g2s_hint(dst + kStageBlobBytes + lane * slot_bytes, rows + size_t(rec_word) * pitch + slice_off,
+                          run * slice_bytes, bar, policy);
+    } else if (lane == 6) {
+        tma_bulk_g2s(dst, blob + size_t(rec_word) * 16, blob_bytes, bar);
+    }
+}
+
+template <int WPT>
+struct WordVec;
+template <>
+struct WordVec<1> {
+    uint32_t v[1];
+    __device__ __forceinline__ void load(const uint8_t* p) { v[0] = *reinterpret_cast<const uint32_t*>(p); }
+};
+template <>
+struct WordVec<2> {
+    uint32_t v[2];
+    __device__ __forceinline__ void load(const uint8_t* p) {
+        const uint2 t = *reinterpret_cast<const uint2*>(p);
+        v[0] = t.x; v[1] = t.y;
+    }
+};
+template <>
+struct WordVec<4> {
+    uint32_t v[4];
+    __device__ __forceinline__ void load(const uint8_t* p) {
+        const uint4 t = *reinterpret_cast<const uint4*>(p);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    }
+};
+
+// Weight 1 + d/2 of sample I (d = its path-0 dosage in {0, 1/2, 1}) as a double: the 2-bit field (2 d) of `fld` at bits
+// 2I, 2I + 1 moved to mantissa bits 18, 19 of 1.0 — the values 1.0, 1.25, 1.5 are LINEAR in the field, so the weight
+// costs one LOP3 and one IMAD (field * 2^k + 0x3FF00000; fld_hi = fld >> 14 keeps k positive for the upper samples), and
+// sum d*y = 2 (sum (1 + d/2) y - sum y) needs ONE DFMA per sample (nvcc turns a conditional add into two FSELs + DADD
+// per class instead).
+template <int I>
+__device__ __forceinline__ double dosage_weight(uint32_t fld, uint32_t fld_hi) {
+    uint32_t hi;
+    if (I < 10)
+        hi = (fld & (3u << (2 * I))) * (1u << (18 - 2 * I)) + 0x3FF00000u;
+    else
+        hi = (fld_hi & (3u << (2 * I - 14))) * (1u << (32 - 2 * I)) + 0x3FF00000u;
+    return __hiloint2double(int(hi), 0);
+}
+template <int I>
+__device__ __forceinline__ bool bit_of_sample(uint32_t m) {
+    return (m & (1u << (2 * I))) != 0u;
+}
+
+constexpr int kRegMaxWarps = 8;  // warps of a K3R CTA (256 threads)
+
+// One path's presence words for this thread (codes as in quant_lean.cuh; branches are CTA-uniform).
+template <int WPT>
+__device__ __forceinline__ void reg_path_words(const uint8_t* rows_s, const uint8_t* locals, uint32_t code,
+                                               uint32_t slot_bytes, uint32_t byte_off, uint32_t first_word,
+                                               uint32_t n_hap, uint32_t (&out)[WPT]) {
+    if (code == 0xFFu) {
+#pragma unroll
+        for (int k = 0; k < WPT; ++k) out[k] = 0u;
+        return;
+    }
+    if (code == 0u) {
+#pragma unroll
+        for (int k = 0; k < WPT; ++k) out[k] = valid_word(first_word + k, n_hap);
+        return;
+    }
+    WordVec<WPT> a;
+    a.load(rows_s + uint32_t(locals[0]) * slot_bytes + byte_off);
+#pragma unroll
+    for (int k = 0; k < WPT; ++k) out[k] = a.v[k];
+#pragma unroll
+    for (uint32_t r = 1; r < 4; ++r)
+        if (r < code) {  // code <= 4 on this path
+            a.load(rows_s + uint32_t(locals[r]) * slot_bytes + byte_off);
+#pragma unroll
+            for (int k = 0; k < WPT; ++k) out[k] &= a.v[k];
+        }
+}
+
+// =================================================================================================
+// K3R kernel.  grid = (CTAs per slice, slices); CTA b of a slice takes snarls b, b + gridDim.x, ...
+// dynamic shared memory: [n_ring mbarriers | pad to 128][n_ring stages of (64 B program + stage_rows slots)]
+// =================================================================================================
+template <int WPT>
+__global__ void __launch_bounds__(kRegMaxWarps * 32) dosage_moments_reg_kernel(const K3RParams q) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ uint32_t red_i[2][4][kRegMaxWarps];
+    __shared__ double red_d[2][3][kRegMaxWarps];
+    const K3Params& p = q.k;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, n_warps = blockDim.x >> 5;
+    const uint32_t n_words = p.pitch / 4;
+    const uint32_t slice = blockIdx.y, slice_first = slice * q.slice_words;
+    const uint32_t slice_len = min(q.slice_words, n_words - slice_first);  // words of this slice (multiple of 4)
+    const uint32_t slot_bytes = q.slice_words * 4, slice_bytes = slice_len * 4;
+    const uint32_t stage_bytes = kStageBlobBytes + p.stage_rows * slot_bytes;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+    uint8_t* stages = smem + ((q.n_ring * 8 + 127) & ~127u);
+
+    if (tid == 0) {
+        for (uint32_t i = 0; i < q.n_ring; ++i) mbar_init(&full[i], 1);
+        mbar_fence_init();
+    }
+    // this thread's samples: words [first_word, first_word + WPT) of the row, 16 samples each
+    const uint32_t local_word = tid * WPT, first_word = slice_first + local_word;
+    const bool active = local_word < slice_len;
+    const uint32_t byte_off = local_word * 4;
+    double y[16 * WPT];
+#pragma unroll
+    for (int k = 0; k < WPT; ++k)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) y[k * 16 + i] = active ? __ldg(p.ys + size_t(i) * n_words + first_word + k) : 0.0;
+    double y_total = 0.0;  // in the order the accumulators see the samples
+    {
+        double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
+#pragma unroll
+        for (int k = 0; k < WPT; ++k)
+#pragma unroll
+            for (int i = 0; i < 16; i += 4) {
+                t0 += y[k * 16 + i];
+                t1 += y[k * 16 + i + 1];
+                t2 += y[k * 16 + i + 2];
+                t3 += y[k * 16 + i + 3];
+            }
+        y_total = (t0 + t1) + (t2 + t3);
+    }
+    uint32_t valid[WPT];
+#pragma unroll
+    for (int k = 0; k < WPT; ++k) valid[k] = active ? (valid_word(first_word + k, p.n_hap) & 0x55555555u) : 0u;
+    __syncthreads();
+
+    const uint64_t stride = gridDim.x;
+    const uint64_t policy = make_evict_first_policy();
+    if (warp == 0) {
+        uint64_t s = blockIdx.x;
+        for (uint32_t st = 0; st < q.n_ring && s < p.n_snarls; ++st, s += stride)
+            issue_stage_slice(load_rec_word(p.rec, s, lane), lane, stages + size_t(st) * stage_bytes, &full[st], p.rows,
+                              p.blob, p.pitch, slice_first * 4, slice_bytes, slot_bytes, policy);
+    }
+
+    uint32_t stage = 0, parity = 0, buf = 0, fin_warp = n_warps > 1 ? 1u : 0u;  // (no divisions in the loop)
+    for (uint64_t s = blockIdx.x; s < p.n_snarls; s += stride) {
+        const uint64_t s_next = s + uint64_t(q.n_ring) * stride;
+        uint32_t next_word = 0;
+        if (warp == 0 && s_next < p.n_snarls) next_word = load_rec_word(p.rec, s_next, lane);
+        mbar_wait(&full[stage], parity);
+        const uint8_t* blob = stages + size_t(stage) * stage_bytes;
+        const uint8_t* rows_s = blob + kStageBlobBytes;
+        const uint32_t np = blob[0];
+        const uint32_t code0 = blob[kBlobHeaderQ], code1 = blob[kBlobHeaderQ + 1];
+        const bool lean = np == 2 && (code0 == 0xFFu || code0 <= 4u) && (code1 == 0xFFu || code1 <= 4u);
+        if (lean) {
+            const uint8_t* loc0 = blob + kBlobHeaderQ + 2;
+            const uint8_t* loc1 = loc0 + ((code0 == 0xFFu) ? 0u : code0);
+            uint32_t a[WPT], b[WPT];
+            if (active) {
+                reg_path_words<WPT>(rows_s, loc0, code0, slot_bytes, byte_off, first_word, p.n_hap, a);
+                reg_path_words<WPT>(rows_s, loc1, code1, slot_bytes, byte_off, first_word, p.n_hap, b);
+            } else {
+#pragma unroll
+                for (int k = 0; k < WPT; ++k) a[k] = b[k] = 0u;
+            }
+            uint32_t cA = 0, cB = 0, cC = 0, cD = 0;  // al0 | al1 << 16, n_used | n_full0 << 16, n_half, n_third | n_tthird << 16
+            double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0, su_un = 0.0, suu_un = 0.0, s_nd = 0.0;
+#pragma unroll
+            for (int k = 0; k < WPT; ++k) {
+                const LeanMasks m = lean_masks(a[k], b[k]);
+                cA += __popc(a[k]) | (__popc(b[k]) << 16);
+                cB += __popc(m.used) | (__popc(m.full0) << 16);
+                cC += __popc(m.half);
+                const uint32_t fld = m.half | (m.full0 << 1), fld_hi = fld >> 14;  // 2-bit field per sample: 2 * dosage
+                acc0 = fma(dosage_weight<0>(fld, fld_hi), y[k * 16 + 0], acc0);
+                acc1 = fma(dosage_weight<1>(fld, fld_hi), y[k * 16 + 1], acc1);
+                acc2 = fma(dosage_weight<2>(fld, fld_hi), y[k * 16 + 2], acc2);
+                acc3 = fma(dosage_weight<3>(fld, fld_hi), y[k * 16 + 3], acc3);
+                acc0 = fma(dosage_weight<4>(fld, fld_hi), y[k * 16 + 4], acc0);
+                acc1 = fma(dosage_weight<5>(fld, fld_hi), y[k * 16 + 5], acc1);
+                acc2 = fma(dosage_weight<6>(fld, fld_hi), y[k * 16 + 6], acc2);
+                acc3 = fma(dosage_weight<7>(fld, fld_hi), y[k * 16 + 7], acc3);
+                acc0 = fma(dosage_weight<8>(fld, fld_hi), y[k * 16 + 8], acc0);
+                acc1 = fma(dosage_weight<9>(fld, fld_hi), y[k * 16 + 9], acc1);
+                acc2 = fma(dosage_weight<10>(fld, fld_hi), y[k * 16 + 10], acc2);
+                acc3 = fma(dosage_weight<11>(fld, fld_hi), y[k * 16 + 11], acc3);
+                acc0 = fma(dosage_weight<12>(fld, fld_hi), y[k * 16 + 12], acc0);
+                acc1 = fma(dosage_weight<13>(fld, fld_hi), y[k * 16 + 13], acc1);
+                acc2 = fma(dosage_weight<14>(fld, fld_hi), y[k * 16 + 14], acc2);
+                acc3 = fma(dosage_weight<15>(fld, fld_hi), y[k * 16 + 15], acc3);
+                const uint32_t un = ~m.used & valid[k];
+                if (un) {  // rare: samples on neither path
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (un & (1u << (2 * i))) {
+                            su_un += y[k * 16 + i];
+                            suu_un = fma(y[k * 16 + i], y[k * 16 + i], suu_un);
+                        }
+                }
+                if (m.third | m.tthird) {  // rare: a sample on three path-haplotypes (dosages 1/3, 2/3)
+                    cD += __popc(m.third) | (__popc(m.tthird) << 16);
+                    double s3 = 0.0, s23 = 0.0;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        if (m.third & (1u << (2 * i))) s3 += y[k * 16 + i];
+                        if (m.tthird & (1u << (2 * i))) s23 += y[k * 16 + i];
+                    }
+                    s_nd += (1.0 / 3.0) * s3 + (2.0 / 3.0) * s23;
+                }
+            }
+            double xty = 2.0 * (((acc0 + acc1) + (acc2 + acc3)) - y_total) + s_nd;  // 2 (sum (1 + d/2) y - sum y)
+            // ---- warp level: packed integer reductions, FP64 by shuffles (the rare ones only when somebody has any)
+            cA = __reduce_add_sync(0xffffffffu, cA);
+            cB = __reduce_add_sync(0xffffffffu, cB);
+            cC = __reduce_add_sync(0xffffffffu, cC);
+            xty = warp_sum(xty);
+            const bool any_un = __any_sync(0xffffffffu, su_un != 0.0 || suu_un != 0.0);
+            const bool any_nd = __any_sync(0xffffffffu, cD != 0u);
+            if (any_un) {
+                su_un = warp_sum(su_un);
+                suu_un = warp_sum(suu_un);
+            }
+            if (any_nd) cD = __reduce_add_sync(0xffffffffu, cD);
+            if (lane == 0) {
+                red_i[buf][0][warp] = cA;
+                red_i[buf][1][warp] = cB;
+                red_i[buf][2][warp] = cC;
+                red_i[buf][3][warp] = cD;
+                red_d[buf][0][warp] = xty;
+                red_d[buf][1][warp] = su_un;
+                red_d[buf][2][warp] = suu_un;
+            }
+        }
+        __syncthreads();  // partials published; every thread is done with the stage
+        if (warp == 0) {
+            if (s_next < p.n_snarls)  // WAR on a read-only stage: no proxy fence (see stage_pipeline.cuh)
+                issue_stage_slice(next_word, lane, stages + size_t(stage) * stage_bytes, &full[stage], p.rows, p.blob,
+                                  p.pitch, slice_first * 4, slice_bytes, slot_bytes, policy);
+        }
+        if (warp == fin_warp) {  // rotates over warps 1 .. n_warps - 1 (warp 0 has the refill to do)
+            if (lean) {
+                // lanes 0..6: one class count each; lanes 8..10: one FP64 sum each; added over the warps in warp order
+                if (lane < 7) {
+                    const uint32_t src = (lane < 2) ? 0u : (lane < 4) ? 1u : (lane == 4) ? 2u : 3u;
+                    const uint32_t sh = (lane == 1 || lane == 3 || lane == 6) ? 16u : 0u;
+                    const uint32_t mask = (lane == 4) ? 0xFFFFFFFFu : 0xFFFFu;
+                    uint32_t v = 0;
+                    for (uint32_t w = 0; w < n_warps; ++w) v += (red_i[buf][src][w] >> sh) & mask;
+                    q.part.i[(size_t(slice) * 7 + lane) * q.part.stride + s] = v;
+                } else if (lane >= 8 && lane < 11) {
+                    double v = 0.0;
+                    for (uint32_t w = 0; w < n_warps; ++w) v += red_d[buf][lane - 8][w];
+                    q.part.d[(size_t(slice) * 3 + (lane - 8)) * q.part.stride + s] = v;
+                } else if (lane == 11 && slice == 0) {
+                    p.mom[s].state = 2;  // K4 builds the moments from the partial sums
+                }
+            } else if (lane == 0 && slice == 0) {
+                p.mom[s].state = 0;
+                if (np) {  // np == 0: prep already put the snarl on the general list
+                    const uint32_t slot = atomicAdd(q.slow_count, 1u);
+                    q.slow_list[slot] = uint32_t(s);
+                }
+            }
+        }
+        if (++stage == q.n_ring) {
+            stage = 0;
+            parity ^= 1u;
+        }
+        buf ^= 1u;
+        if (n_warps > 1 && ++fin_warp == n_warps) fin_warp = 1u;
+    }
+}
