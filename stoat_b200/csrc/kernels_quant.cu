@@ -599,19 +599,19 @@ static bool k3r_plan(uint32_t pitch, uint32_t stage_rows, K3RPlan& pl) {
     const uint32_t budget = 224 * 1024;
     if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(budget)) != cudaSuccess) return false;
     int occ = 0;  // CTAs per SM that registers / threads allow with the smallest ring
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, int(pl.threads), 128 + 2 * stage_bytes) != cudaSuccess ||
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, int(pl.threads), 384 + 2 * stage_bytes) != cudaSuccess ||
         occ < 1)
         return false;
     const int want = env_int("STOAT_GPU_K3R_CTAS", 0);
     if (want >= 1 && want < occ) occ = want;
     const uint32_t per_cta = (budget - 1024) / uint32_t(occ) - 1024;  // 1 KB per CTA is reserved by the driver
-    uint32_t ring = (per_cta - 128) / stage_bytes;
+    uint32_t ring = (per_cta - 384) / stage_bytes;
     const int ring_env = env_int("STOAT_GPU_K3R_RING", 0);
     const uint32_t ring_max = ring_env >= 2 ? uint32_t(ring_env) : 8u;
     if (ring > ring_max) ring = ring_max;
-    if (ring < 2) return false;
+    if (ring < uint32_t(kRegLag) + 1) return false;
     pl.n_ring = ring;
-    pl.smem_bytes = ((ring * 8 + 127) & ~127u) + ring * stage_bytes;
+    pl.smem_bytes = (((2 * ring + 2 * kRegBufs) * 8 + 127) & ~127u) + ring * stage_bytes;
     pl.ctas_per_sm = uint32_t(occ);
     return true;
 }
@@ -677,6 +677,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             q.slow_count = b.counters + 3;
             q.part = part;
             q.partial_only = 1;
+            q.zero4[0] = q.zero4[1] = q.zero4[2] = q.zero4[3] = 0u;
             n_slices = pl.n_slices;
             if ((e = cudaMemsetAsync(b.counters + 3, 0, 4, st)) != cudaSuccess) return e;
             uint64_t ctas = uint64_t(num_sms) * pl.ctas_per_sm / pl.n_slices;

@@ -39,6 +39,7 @@ struct K3RParams {
     uint32_t* slow_count;
     LeanPartials part;     // used when partial_only
     uint32_t partial_only;
+    uint32_t zero4[4];  // zeros (see dosage_weight_at)
 };
 
 // Filters + moments of a two-path snarl from its class counts and sums (what quant_lean2 does after its passes).
@@ -136,24 +137,26 @@ struct WordVec<4> {
     }
 };
 
-// Weight 1 + d/2 of sample I (d = its path-0 dosage in {0, 1/2, 1}) as a double: the 2-bit field (2 d) of `fld` at bits
-// 2I, 2I + 1 moved to mantissa bits 18, 19 of 1.0 — the values 1.0, 1.25, 1.5 are LINEAR in the field, so the weight
-// costs one LOP3 and one IMAD (field * 2^k + 0x3FF00000; fld_hi = fld >> 14 keeps k positive for the upper samples), and
-// sum d*y = 2 (sum (1 + d/2) y - sum y) needs ONE DFMA per sample (nvcc turns a conditional add into two FSELs + DADD
-// per class instead).
-template <int I>
-__device__ __forceinline__ double dosage_weight(uint32_t fld, uint32_t fld_hi) {
-    uint32_t hi;
-    if (I < 10)
-        hi = (fld & (3u << (2 * I))) * (1u << (18 - 2 * I)) + 0x3FF00000u;
-    else
-        hi = (fld_hi & (3u << (2 * I - 14))) * (1u << (32 - 2 * I)) + 0x3FF00000u;
-    return __hiloint2double(int(hi), 0);
+// Weight 1 + d/2 of a sample (d = its path-0 dosage in {0, 1/2, 1}) as a double: 1.0, 1.25, 1.5 are LINEAR in the 2-bit
+// field 2d placed at mantissa bits 50, 51, so with the field (masked, at bit B >= 19 of a 32-bit word) the whole 64-bit
+// pattern is ONE wide multiply-add, field * 2^(50 - B) + bits(1.0) (SASS IMAD.WIDE.U32 writes the register pair; no
+// separate zeroing of the low word).  sum d*y = 2 (sum (1 + d/2) y - sum y) then needs one LOP3, one IMAD.WIDE and one
+// DFMA per sample (nvcc turns a conditional add into two FSELs + DADD per class instead).
+template <int B>
+__device__ __forceinline__ double dosage_weight_at(uint32_t word, uint32_t lo_zero) {
+    static_assert(B >= 18 && B <= 30, "field must sit at bits 18..30");
+    // hi word = (field >> (B - 18)) + hi(1.0); the low word is a zero the compiler cannot see through (a kernel
+    // parameter), one per accumulator: with a shared literal 0 ptxas funnels every weight through ONE register pair and
+    // the 16 DFMAs of a word become a single dependent chain.
+    const uint32_t hi = ((word & (3u << B)) >> (B - 18)) + 0x3FF00000u;
+    return __hiloint2double(int(hi), int(lo_zero));
 }
-template <int I>
-__device__ __forceinline__ bool bit_of_sample(uint32_t m) {
-    return (m & (1u << (2 * I))) != 0u;
-}
+// 16 samples of one word: fields at bits 20..30 of w2 = fld (samples 10..15), of w1 = fld << 12 (samples 4..9) and at
+// bits 24..30 of w0 = fld << 24 (samples 0..3)
+#define STOAT_W(I, fld, w1, w0, z)                                                                            \
+    ((I) >= 10 ? dosage_weight_at<((I) >= 10 ? 2 * (I) : 20)>(fld, z)                                         \
+               : (I) >= 4 ? dosage_weight_at<((I) >= 4 && (I) < 10 ? 2 * (I) + 12 : 20)>(w1, z)               \
+                          : dosage_weight_at<((I) < 4 ? 2 * (I) + 24 : 20)>(w0, z))
 
 constexpr int kRegMaxWarps = 8;  // warps of a K3R CTA (256 threads)
 
@@ -185,15 +188,23 @@ __device__ __forceinline__ void reg_path_words(const uint8_t* rows_s, const uint
         }
 }
 
+
+constexpr int kRegBufs = 4;  // partial-sum buffers: warps may run up to 4 snarls ahead of the slowest finisher
+constexpr int kRegLag = 2;   // a stage is refilled two iterations after its snarl (nobody waits for the slowest reader)
+
 // =================================================================================================
 // K3R kernel.  grid = (CTAs per slice, slices); CTA b of a slice takes snarls b, b + gridDim.x, ...
-// dynamic shared memory: [n_ring mbarriers | pad to 128][n_ring stages of (64 B program + stage_rows slots)]
+// dynamic shared memory: [mbarriers: full[ring] empty[ring] ready[4] free[4] | pad to 128][ring stages of
+// (64 B program + stage_rows slots)].  No CTA-wide barrier in the loop: warps run freely, coupled only through
+//   full[st]   TMA landed (tx count)                      empty[st]  every warp has read its words of the stage
+//   free[b]    the last warp to publish its partial sums in buffer b has added them up (smem counter arrived[b])
 // =================================================================================================
 template <int WPT>
 __global__ void __launch_bounds__(kRegMaxWarps * 32) dosage_moments_reg_kernel(const K3RParams q) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ uint32_t red_i[2][4][kRegMaxWarps];
-    __shared__ double red_d[2][3][kRegMaxWarps];
+    __shared__ uint32_t red_i[kRegBufs][4][kRegMaxWarps];
+    __shared__ double red_d[kRegBufs][3][kRegMaxWarps];
+    __shared__ uint32_t arrived[kRegBufs];
     const K3Params& p = q.k;
     const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, n_warps = blockDim.x >> 5;
     const uint32_t n_words = p.pitch / 4;
@@ -201,23 +212,37 @@ __global__ void __launch_bounds__(kRegMaxWarps * 32) dosage_moments_reg_kernel(c
     const uint32_t slice_len = min(q.slice_words, n_words - slice_first);  // words of this slice (multiple of 4)
     const uint32_t slot_bytes = q.slice_words * 4, slice_bytes = slice_len * 4;
     const uint32_t stage_bytes = kStageBlobBytes + p.stage_rows * slot_bytes;
+    const uint32_t ring = q.n_ring;
+    if (tid < kRegBufs) arrived[tid] = 0u;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-    uint8_t* stages = smem + ((q.n_ring * 8 + 127) & ~127u);
+    uint64_t* empty = full + ring;
+    uint64_t* ready = empty + ring;
+    uint64_t* bfree = ready + kRegBufs;
+    uint8_t* stages = smem + (((2 * ring + 2 * kRegBufs) * 8 + 127) & ~127u);
 
     if (tid == 0) {
-        for (uint32_t i = 0; i < q.n_ring; ++i) mbar_init(&full[i], 1);
+        for (uint32_t i = 0; i < ring; ++i) {
+            mbar_init(&full[i], 1);
+            mbar_init(&empty[i], n_warps);
+        }
+        for (uint32_t i = 0; i < kRegBufs; ++i) {
+            mbar_init(&ready[i], n_warps);
+            mbar_init(&bfree[i], 1);
+        }
         mbar_fence_init();
     }
+    for (uint32_t i = tid; i < kRegBufs * 4 * kRegMaxWarps; i += blockDim.x) (&red_i[0][0][0])[i] = 0u;
+    for (uint32_t i = tid; i < kRegBufs * 3 * kRegMaxWarps; i += blockDim.x) (&red_d[0][0][0])[i] = 0.0;
     // this thread's samples: words [first_word, first_word + WPT) of the row, 16 samples each
     const uint32_t local_word = tid * WPT, first_word = slice_first + local_word;
     const bool active = local_word < slice_len;
-    const uint32_t byte_off = local_word * 4;
+    const uint32_t byte_off = active ? local_word * 4 : 0u;  // idle threads read word 0 of the slot and discard it
     double y[16 * WPT];
 #pragma unroll
     for (int k = 0; k < WPT; ++k)
 #pragma unroll
         for (int i = 0; i < 16; ++i) y[k * 16 + i] = active ? __ldg(p.ys + size_t(i) * n_words + first_word + k) : 0.0;
-    double y_total = 0.0;  // in the order the accumulators see the samples
+    double y_total;  // in the order the accumulators see the samples
     {
         double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
 #pragma unroll
@@ -234,126 +259,176 @@ __global__ void __launch_bounds__(kRegMaxWarps * 32) dosage_moments_reg_kernel(c
     uint32_t valid[WPT];
 #pragma unroll
     for (int k = 0; k < WPT; ++k) valid[k] = active ? (valid_word(first_word + k, p.n_hap) & 0x55555555u) : 0u;
+    const uint32_t live = active ? 0xFFFFFFFFu : 0u;
     __syncthreads();
 
     const uint64_t stride = gridDim.x;
     const uint64_t policy = make_evict_first_policy();
     if (warp == 0) {
         uint64_t s = blockIdx.x;
-        for (uint32_t st = 0; st < q.n_ring && s < p.n_snarls; ++st, s += stride)
+        for (uint32_t st = 0; st < ring && s < p.n_snarls; ++st, s += stride)
             issue_stage_slice(load_rec_word(p.rec, s, lane), lane, stages + size_t(st) * stage_bytes, &full[st], p.rows,
                               p.blob, p.pitch, slice_first * 4, slice_bytes, slot_bytes, policy);
     }
 
-    uint32_t stage = 0, parity = 0, buf = 0, fin_warp = n_warps > 1 ? 1u : 0u;  // (no divisions in the loop)
-    for (uint64_t s = blockIdx.x; s < p.n_snarls; s += stride) {
-        const uint64_t s_next = s + uint64_t(q.n_ring) * stride;
-        uint32_t next_word = 0;
-        if (warp == 0 && s_next < p.n_snarls) next_word = load_rec_word(p.rec, s_next, lane);
+    uint32_t stage = 0, parity = 0;      // stage / phase of the current snarl
+    uint32_t rstage = 0, rparity = 0;    // stage / phase of the snarl kRegLag iterations back (warp 0 refills it)
+    uint32_t buf = 0, bphase = 0, it = 0;
+    uint32_t rec_ahead = 0;  // warp 0: record words of the snarl the NEXT iteration stages
+    if (warp == 0) {
+        const uint64_t s0 = uint64_t(blockIdx.x) + uint64_t(ring - kRegLag) * stride;
+        if (s0 < p.n_snarls) rec_ahead = load_rec_word(p.rec, s0, lane);
+    }
+    for (uint64_t s = blockIdx.x; s < p.n_snarls; s += stride, ++it) {
+        // ---- warp 0: refill the stage every warp left kRegLag iterations ago ------------------------------
+        if (warp == 0) {
+            // (the record of the snarl to stage was fetched one iteration earlier: its latency is off this warp's path)
+            const uint64_t s_new = s + uint64_t(ring - kRegLag) * stride;
+            const uint32_t w = rec_ahead;
+            rec_ahead = (s_new + stride < p.n_snarls) ? load_rec_word(p.rec, s_new + stride, lane) : 0u;
+            if (it >= uint32_t(kRegLag)) {
+                if (s_new < p.n_snarls) {
+                    mbar_wait(&empty[rstage], rparity);
+                    issue_stage_slice(w, lane, stages + size_t(rstage) * stage_bytes, &full[rstage], p.rows, p.blob,
+                                      p.pitch, slice_first * 4, slice_bytes, slot_bytes, policy);
+                }
+                if (++rstage == ring) {
+                    rstage = 0;
+                    rparity ^= 1u;
+                }
+            }
+        }
         mbar_wait(&full[stage], parity);
         const uint8_t* blob = stages + size_t(stage) * stage_bytes;
         const uint8_t* rows_s = blob + kStageBlobBytes;
-        const uint32_t np = blob[0];
-        const uint32_t code0 = blob[kBlobHeaderQ], code1 = blob[kBlobHeaderQ + 1];
+        const uint4 hdr = *reinterpret_cast<const uint4*>(blob);  // np, shape class | p0 | codes, locals ...
+        const uint32_t np = hdr.x & 0xFFu, shape = (hdr.x >> 8) & 0xFFu;
+        const uint32_t code0 = hdr.z & 0xFFu, code1 = (hdr.z >> 8) & 0xFFu;
         const bool lean = np == 2 && (code0 == 0xFFu || code0 <= 4u) && (code1 == 0xFFu || code1 <= 4u);
-        if (lean) {
+        uint32_t a[WPT], b[WPT];
+        if (shape == 1u) {  // two paths, two checked edges each: locals in bytes 10..13
+            WordVec<WPT> r0, r1, r2, r3;
+            r0.load(rows_s + ((hdr.z >> 16) & 0xFFu) * slot_bytes + byte_off);
+            r1.load(rows_s + (hdr.z >> 24) * slot_bytes + byte_off);
+            r2.load(rows_s + (hdr.w & 0xFFu) * slot_bytes + byte_off);
+            r3.load(rows_s + ((hdr.w >> 8) & 0xFFu) * slot_bytes + byte_off);
+#pragma unroll
+            for (int k = 0; k < WPT; ++k) {
+                a[k] = r0.v[k] & r1.v[k] & live;
+                b[k] = r2.v[k] & r3.v[k] & live;
+            }
+        } else if (lean) {
             const uint8_t* loc0 = blob + kBlobHeaderQ + 2;
             const uint8_t* loc1 = loc0 + ((code0 == 0xFFu) ? 0u : code0);
-            uint32_t a[WPT], b[WPT];
-            if (active) {
-                reg_path_words<WPT>(rows_s, loc0, code0, slot_bytes, byte_off, first_word, p.n_hap, a);
-                reg_path_words<WPT>(rows_s, loc1, code1, slot_bytes, byte_off, first_word, p.n_hap, b);
-            } else {
+            reg_path_words<WPT>(rows_s, loc0, code0, slot_bytes, byte_off, first_word, p.n_hap, a);
+            reg_path_words<WPT>(rows_s, loc1, code1, slot_bytes, byte_off, first_word, p.n_hap, b);
 #pragma unroll
-                for (int k = 0; k < WPT; ++k) a[k] = b[k] = 0u;
+            for (int k = 0; k < WPT; ++k) {
+                a[k] &= live;
+                b[k] &= live;
             }
-            uint32_t cA = 0, cB = 0, cC = 0, cD = 0;  // al0 | al1 << 16, n_used | n_full0 << 16, n_half, n_third | n_tthird << 16
-            double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0, su_un = 0.0, suu_un = 0.0, s_nd = 0.0;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[stage]);  // this warp is done with the stage
+
+        uint32_t cA = 0, cB = 0, cC = 0, cD = 0;  // al0 | al1 << 16, n_used | n_full0 << 16, n_half, n_third | n_tthird << 16
+        double xty = 0.0, su_un = 0.0, suu_un = 0.0;
+        if (lean) {
+            double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+            const uint32_t z0 = q.zero4[0], z1 = q.zero4[1], z2 = q.zero4[2], z3 = q.zero4[3];
+            uint32_t rare = 0;
 #pragma unroll
             for (int k = 0; k < WPT; ++k) {
                 const LeanMasks m = lean_masks(a[k], b[k]);
                 cA += __popc(a[k]) | (__popc(b[k]) << 16);
                 cB += __popc(m.used) | (__popc(m.full0) << 16);
                 cC += __popc(m.half);
-                const uint32_t fld = m.half | (m.full0 << 1), fld_hi = fld >> 14;  // 2-bit field per sample: 2 * dosage
-                acc0 = fma(dosage_weight<0>(fld, fld_hi), y[k * 16 + 0], acc0);
-                acc1 = fma(dosage_weight<1>(fld, fld_hi), y[k * 16 + 1], acc1);
-                acc2 = fma(dosage_weight<2>(fld, fld_hi), y[k * 16 + 2], acc2);
-                acc3 = fma(dosage_weight<3>(fld, fld_hi), y[k * 16 + 3], acc3);
-                acc0 = fma(dosage_weight<4>(fld, fld_hi), y[k * 16 + 4], acc0);
-                acc1 = fma(dosage_weight<5>(fld, fld_hi), y[k * 16 + 5], acc1);
-                acc2 = fma(dosage_weight<6>(fld, fld_hi), y[k * 16 + 6], acc2);
-                acc3 = fma(dosage_weight<7>(fld, fld_hi), y[k * 16 + 7], acc3);
-                acc0 = fma(dosage_weight<8>(fld, fld_hi), y[k * 16 + 8], acc0);
-                acc1 = fma(dosage_weight<9>(fld, fld_hi), y[k * 16 + 9], acc1);
-                acc2 = fma(dosage_weight<10>(fld, fld_hi), y[k * 16 + 10], acc2);
-                acc3 = fma(dosage_weight<11>(fld, fld_hi), y[k * 16 + 11], acc3);
-                acc0 = fma(dosage_weight<12>(fld, fld_hi), y[k * 16 + 12], acc0);
-                acc1 = fma(dosage_weight<13>(fld, fld_hi), y[k * 16 + 13], acc1);
-                acc2 = fma(dosage_weight<14>(fld, fld_hi), y[k * 16 + 14], acc2);
-                acc3 = fma(dosage_weight<15>(fld, fld_hi), y[k * 16 + 15], acc3);
-                const uint32_t un = ~m.used & valid[k];
-                if (un) {  // rare: samples on neither path
+                rare |= (~m.used & valid[k]) | m.third | m.tthird;
+                const uint32_t fld = m.half | (m.full0 << 1);  // 2-bit field per sample: 2 * dosage
+                const uint32_t w1 = fld << 12, w0 = fld << 24;
+                const double* yk = y + k * 16;
+                acc0 = fma(STOAT_W(0, fld, w1, w0, z0), yk[0], acc0);
+                acc1 = fma(STOAT_W(1, fld, w1, w0, z1), yk[1], acc1);
+                acc2 = fma(STOAT_W(2, fld, w1, w0, z2), yk[2], acc2);
+                acc3 = fma(STOAT_W(3, fld, w1, w0, z3), yk[3], acc3);
+                acc0 = fma(STOAT_W(4, fld, w1, w0, z0), yk[4], acc0);
+                acc1 = fma(STOAT_W(5, fld, w1, w0, z1), yk[5], acc1);
+                acc2 = fma(STOAT_W(6, fld, w1, w0, z2), yk[6], acc2);
+                acc3 = fma(STOAT_W(7, fld, w1, w0, z3), yk[7], acc3);
+                acc0 = fma(STOAT_W(8, fld, w1, w0, z0), yk[8], acc0);
+                acc1 = fma(STOAT_W(9, fld, w1, w0, z1), yk[9], acc1);
+                acc2 = fma(STOAT_W(10, fld, w1, w0, z2), yk[10], acc2);
+                acc3 = fma(STOAT_W(11, fld, w1, w0, z3), yk[11], acc3);
+                acc0 = fma(STOAT_W(12, fld, w1, w0, z0), yk[12], acc0);
+                acc1 = fma(STOAT_W(13, fld, w1, w0, z1), yk[13], acc1);
+                acc2 = fma(STOAT_W(14, fld, w1, w0, z2), yk[14], acc2);
+                acc3 = fma(STOAT_W(15, fld, w1, w0, z3), yk[15], acc3);
+            }
+            xty = 2.0 * (((acc0 + acc1) + (acc2 + acc3)) - y_total);  // 2 (sum (1 + d/2) y - sum y)
+            if (rare) {  // samples on neither path / on three path-haplotypes (dosages 1/3, 2/3): a few lanes, rarely
 #pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (un & (1u << (2 * i))) {
-                            su_un += y[k * 16 + i];
-                            suu_un = fma(y[k * 16 + i], y[k * 16 + i], suu_un);
-                        }
-                }
-                if (m.third | m.tthird) {  // rare: a sample on three path-haplotypes (dosages 1/3, 2/3)
+                for (int k = 0; k < WPT; ++k) {
+                    const LeanMasks m = lean_masks(a[k], b[k]);
+                    const uint32_t un = ~m.used & valid[k];
                     cD += __popc(m.third) | (__popc(m.tthird) << 16);
                     double s3 = 0.0, s23 = 0.0;
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        if (m.third & (1u << (2 * i))) s3 += y[k * 16 + i];
-                        if (m.tthird & (1u << (2 * i))) s23 += y[k * 16 + i];
+                        const double yy = y[k * 16 + i];
+                        if (un & (1u << (2 * i))) {
+                            su_un += yy;
+                            suu_un = fma(yy, yy, suu_un);
+                        }
+                        if (m.third & (1u << (2 * i))) s3 += yy;
+                        if (m.tthird & (1u << (2 * i))) s23 += yy;
                     }
-                    s_nd += (1.0 / 3.0) * s3 + (2.0 / 3.0) * s23;
+                    xty += (1.0 / 3.0) * s3 + (2.0 / 3.0) * s23;
                 }
             }
-            double xty = 2.0 * (((acc0 + acc1) + (acc2 + acc3)) - y_total) + s_nd;  // 2 (sum (1 + d/2) y - sum y)
-            // ---- warp level: packed integer reductions, FP64 by shuffles (the rare ones only when somebody has any)
+            // ---- warp level: packed integer reductions, FP64 by shuffles (the rare sums only when some lane has any)
             cA = __reduce_add_sync(0xffffffffu, cA);
             cB = __reduce_add_sync(0xffffffffu, cB);
             cC = __reduce_add_sync(0xffffffffu, cC);
             xty = warp_sum(xty);
-            const bool any_un = __any_sync(0xffffffffu, su_un != 0.0 || suu_un != 0.0);
-            const bool any_nd = __any_sync(0xffffffffu, cD != 0u);
-            if (any_un) {
+            if (__any_sync(0xffffffffu, rare != 0u)) {
                 su_un = warp_sum(su_un);
                 suu_un = warp_sum(suu_un);
-            }
-            if (any_nd) cD = __reduce_add_sync(0xffffffffu, cD);
-            if (lane == 0) {
-                red_i[buf][0][warp] = cA;
-                red_i[buf][1][warp] = cB;
-                red_i[buf][2][warp] = cC;
-                red_i[buf][3][warp] = cD;
-                red_d[buf][0][warp] = xty;
-                red_d[buf][1][warp] = su_un;
-                red_d[buf][2][warp] = suu_un;
+                cD = __reduce_add_sync(0xffffffffu, cD);
             }
         }
-        __syncthreads();  // partials published; every thread is done with the stage
-        if (warp == 0) {
-            if (s_next < p.n_snarls)  // WAR on a read-only stage: no proxy fence (see stage_pipeline.cuh)
-                issue_stage_slice(next_word, lane, stages + size_t(stage) * stage_bytes, &full[stage], p.rows, p.blob,
-                                  p.pitch, slice_first * 4, slice_bytes, slot_bytes, policy);
+        // ---- publish this warp's partial sums; the LAST warp to arrive adds them up ---------------------------
+        // (a designated finishing warp would have to wait for the slowest warp and then delays its own next snarl: with a
+        //  rotating finisher that wait becomes a serial chain through the whole CTA)
+        if (it >= uint32_t(kRegBufs)) mbar_wait(&bfree[buf], bphase ^ 1u);  // the buffer's previous snarl is finished
+        uint32_t last = 0;
+        if (lane == 0) {
+            red_i[buf][0][warp] = cA;
+            red_i[buf][1][warp] = cB;
+            red_i[buf][2][warp] = cC;
+            red_i[buf][3][warp] = cD;
+            red_d[buf][0][warp] = xty;
+            red_d[buf][1][warp] = su_un;
+            red_d[buf][2][warp] = suu_un;
+            __threadfence_block();
+            last = (atomicAdd(&arrived[buf], 1u) == n_warps - 1u) ? 1u : 0u;
         }
-        if (warp == fin_warp) {  // rotates over warps 1 .. n_warps - 1 (warp 0 has the refill to do)
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (last) {
+            __threadfence_block();
             if (lean) {
-                // lanes 0..6: one class count each; lanes 8..10: one FP64 sum each; added over the warps in warp order
+                // lanes 0..6: one class count each; lanes 8..10: one FP64 sum each; added in warp order
                 if (lane < 7) {
                     const uint32_t src = (lane < 2) ? 0u : (lane < 4) ? 1u : (lane == 4) ? 2u : 3u;
                     const uint32_t sh = (lane == 1 || lane == 3 || lane == 6) ? 16u : 0u;
                     const uint32_t mask = (lane == 4) ? 0xFFFFFFFFu : 0xFFFFu;
                     uint32_t v = 0;
-                    for (uint32_t w = 0; w < n_warps; ++w) v += (red_i[buf][src][w] >> sh) & mask;
+#pragma unroll
+                    for (int w = 0; w < kRegMaxWarps; ++w) v += (red_i[buf][src][w] >> sh) & mask;
                     q.part.i[(size_t(slice) * 7 + lane) * q.part.stride + s] = v;
                 } else if (lane >= 8 && lane < 11) {
                     double v = 0.0;
-                    for (uint32_t w = 0; w < n_warps; ++w) v += red_d[buf][lane - 8][w];
+#pragma unroll
+                    for (int w = 0; w < kRegMaxWarps; ++w) v += red_d[buf][lane - 8][w];
                     q.part.d[(size_t(slice) * 3 + (lane - 8)) * q.part.stride + s] = v;
                 } else if (lane == 11 && slice == 0) {
                     p.mom[s].state = 2;  // K4 builds the moments from the partial sums
@@ -365,12 +440,19 @@ __global__ void __launch_bounds__(kRegMaxWarps * 32) dosage_moments_reg_kernel(c
                     q.slow_list[slot] = uint32_t(s);
                 }
             }
+            __syncwarp();
+            if (lane == 0) {
+                arrived[buf] = 0u;
+                mbar_arrive(&bfree[buf]);  // (release: the reset is visible before anybody passes the wait above)
+            }
         }
-        if (++stage == q.n_ring) {
+        if (++stage == ring) {
             stage = 0;
             parity ^= 1u;
         }
-        buf ^= 1u;
-        if (n_warps > 1 && ++fin_warp == n_warps) fin_warp = 1u;
+        if (++buf == uint32_t(kRegBufs)) {
+            buf = 0;
+            bphase ^= 1u;
+        }
     }
 }
