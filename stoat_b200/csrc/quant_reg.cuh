@@ -31,6 +31,9 @@ struct LeanPartials {
     uint64_t stride;  // S
 };
 
+// n_tthird partial >= this: some slice met a sample on three path-haplotypes and did not sum it (K3M) -> general path
+constexpr uint32_t kLeanReplayMark = 0x01000000u;
+
 struct K3RParams {
     K3Params k;
     uint32_t slice_words;  // words of a row one CTA (slice) covers; == n_words when gridDim.y == 1
@@ -48,6 +51,7 @@ struct K3RParams {
 __device__ int lean_finish(const K3Params& p, uint64_t s, uint32_t p0, const LeanSums& t, QuantMoments& mom) {
     p.out.allele_paths[p0] = t.al0;  // quantitative_table.cpp:54-55
     p.out.allele_paths[p0 + 1] = t.al1;
+    if (t.n_tthird >= kLeanReplayMark) return 2;
     const bool nondyadic = (t.n_third | t.n_tthird) != 0u;
     const uint32_t n_used = t.n_used;
     const uint32_t n_full1 = n_used - t.n_full0 - t.n_half - t.n_third - t.n_tthird;
