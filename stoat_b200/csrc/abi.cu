@@ -48,7 +48,7 @@ MatrixDev matrix_view(const stoat_gpu_ctx* ctx) {
 }
 
 struct QuantState {
-    DevBuf yc, ys, mom, part_i, part_d, slow, yslices;
+    DevBuf yc, ys, mom, part_i, part_d, slow, yslices, lean_rec;
     double sy_all = 0.0, syy_all = 0.0, y_scale = 1.0;
 };
 
@@ -133,6 +133,7 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     x->q.part_d.release();
     x->q.slow.release();
     x->q.yslices.release();
+    x->q.lean_rec.release();
     for (auto& ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -249,16 +250,16 @@ int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, ui
                              x->q.ys.as<double>(), ctx->stream));
     // K3M's operand: the centred phenotype as 8 signed 7-bit slices of one fixed-point scale,
     //     y - mean = scale * sum_t q_t * 128^-(t+1)   (every step below is exact in FP64; residual <= 2^-57 scale),
-    // laid out as the B fragments of its integer MMAs (csrc/quant_mma.cuh): [16-byte chunk j][mma m][lane (g, t)][8 B],
-    // register b, byte bb <-> slice g of sample (4 j + t) * 16 + 4 bb + 2 m + b.
+    // laid out as the B fragments of its integer MMAs (csrc/quant_mma.cuh): [round c][word j][mma m][lane (g, t)][8 B];
+    // lane (g, t) works on the 16-byte chunk 4 c + t of a row, i.e. on word (4 c + t) * 4 + j, and register b, byte bb
+    // of its fragment is slice g of that word's sample 4 bb + 2 m + b.
     {
         double vmax = 0.0;
         for (uint64_t i = 0; i < n_samples; ++i) vmax = std::max(vmax, std::fabs(y[i] - mean));
         int ex = 0;
         if (vmax > 0.0 && std::isfinite(vmax)) std::frexp(vmax, &ex);  // vmax = f * 2^ex, f in [0.5, 1)
         x->q.y_scale = std::ldexp(1.0, ex + 1);                        // |y - mean| / scale < 0.5
-        const uint64_t n_chunks = ctx->pitch / 16;
-        std::vector<int8_t> tab(size_t(n_chunks) * 512, 0);
+        std::vector<int8_t> tab(quant_yslices_bytes(ctx->pitch), 0);
         for (uint64_t i = 0; i < n_samples; ++i) {
             double r = std::ldexp(y[i] - mean, -(ex + 1));
             int8_t qs[8];
@@ -269,8 +270,10 @@ int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, ui
                 r -= qv;
             }
             const uint64_t word = i / 16, k = i % 16;  // k = 4 bb + 2 m + b
-            const uint64_t j = word / 4, t = word % 4, bb = k / 4, m = (k % 4) / 2, b = k % 2;
-            for (uint64_t g = 0; g < 8; ++g) tab[(((j * 2 + m) * 32 + (g * 4 + t)) * 8) + b * 4 + bb] = qs[g];
+            const uint64_t chunk = word / 4, j = word % 4, c = chunk / 4, t = chunk % 4;
+            const uint64_t bb = k / 4, m = (k % 4) / 2, b = k % 2;
+            for (uint64_t g = 0; g < 8; ++g)
+                tab[((((c * 4 + j) * 2 + m) * 32 + (g * 4 + t)) * 8) + b * 4 + bb] = qs[g];
         }
         CK(x->q.yslices.reserve(std::max<size_t>(tab.size(), 16)));
         CK(cudaMemcpyAsync(x->q.yslices.p, tab.data(), tab.size(), cudaMemcpyHostToDevice, ctx->stream));
@@ -498,6 +501,7 @@ static int quant_reserve(stoat_gpu_ctx* ctx) {
     CK(x->q.part_i.reserve(std::max<uint64_t>(slices * 7 * b.n_snarls * 4, 16)));
     CK(x->q.part_d.reserve(std::max<uint64_t>(slices * 3 * b.n_snarls * 8, 16)));
     CK(x->q.slow.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
+    CK(x->q.lean_rec.reserve(std::max<uint64_t>(b.n_snarls * 16, 16)));
     return STOAT_GPU_OK;
 }
 
@@ -532,7 +536,8 @@ int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresh
                                 x->q.syy_all, ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar),
                                 ctx->batch, x->max_stage_rows, *thr, out,
                                 reinterpret_cast<QuantMoments*>(x->q.mom.p), x->q.part_i.as<uint32_t>(),
-                                x->q.part_d.as<double>(), x->q.slow.as<uint32_t>(), x->q.yslices.as<uint8_t>(),
+                                x->q.part_d.as<double>(), x->q.slow.as<uint32_t>(), x->q.lean_rec.as<uint4>(),
+                                x->q.yslices.as<uint8_t>(),
                                 x->q.yc.as<double>(), x->q.y_scale, ctx->num_sms, ctx->k1_variant, ctx->stream,
                                 &ctx->timing.launches));
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));

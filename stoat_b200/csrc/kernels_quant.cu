@@ -619,36 +619,23 @@ static bool k3r_plan(uint32_t pitch, uint32_t stage_rows, K3RPlan& pl) {
 
 // ---- K3M launch plan ---------------------------------------------------------------------------------
 struct K3MPlan {
-    uint32_t n_slices = 0, chunk_count = 0, row_stride = 0, slot_bytes = 0, smem_bytes = 0;
+    uint32_t n_slices = 0, rounds_per_slice = 0, n_rounds = 0, smem_bytes = 0;
 };
-static bool k3m_plan(uint32_t pitch, uint64_t n_hap, uint32_t stage_rows, K3MPlan& pl) {
+static bool k3m_plan(uint32_t pitch, uint64_t n_hap, K3MPlan& pl) {
     if (env_int("STOAT_GPU_K3M", 1) == 0 || pitch == 0 || n_hap >= 65536) return false;
-    if (stage_rows == 0) stage_rows = 1;
-    if (stage_rows > 4) stage_rows = 4;  // snarls with more distinct rows are not staged (quant_mma.cuh: mma_issue_tile)
-    const uint32_t n_chunks = pitch / 16;
-    const uint32_t budget = 227 * 1024;
-    const uint32_t sums_bytes = (2u * uint32_t(sizeof(MmaTileSums)) + 127u) & ~127u;
-    for (uint32_t slices = 1; slices <= 64; ++slices) {
-        const uint32_t cc = (n_chunks + slices - 1) / slices;
-        const uint32_t row_stride = cc * 16;
-        uint32_t slot = kStageBlobBytes + stage_rows * row_stride;
-        slot += (16u + 128u - (slot & 127u)) & 127u;  // == 16 mod 128: the 8 lane groups of a warp hit distinct banks
-        const uint32_t total = 128 + sums_bytes + ((cc * 512u + 127u) & ~127u) + 2u * kMmaTile * slot;
-        if (total <= budget) {
-            pl.n_slices = slices;
-            pl.chunk_count = cc;
-            pl.row_stride = row_stride;
-            pl.slot_bytes = slot;
-            pl.smem_bytes = total;
-            return true;
-        }
-    }
-    return false;
+    const uint32_t n_rounds = (pitch / 16 + 3) / 4;
+    pl.n_rounds = n_rounds;
+    pl.n_slices = (n_rounds + kMmaMaxRounds - 1) / kMmaMaxRounds;
+    pl.rounds_per_slice = (n_rounds + pl.n_slices - 1) / pl.n_slices;
+    pl.smem_bytes = pl.rounds_per_slice * 2048;
+    return true;
 }
+size_t quant_yslices_bytes(uint64_t pitch) { return size_t((pitch / 16 + 3) / 4) * 2048; }
 // slices of the haplotype range the two-path kernel uses (sizes the partial-sum buffers); 0: neither K3M nor K3R
 uint32_t quant_lean_slices(uint64_t pitch, uint64_t n_hap, uint32_t stage_rows) {
     K3MPlan pm;
-    if (k3m_plan(uint32_t(pitch), n_hap, stage_rows, pm)) return pm.n_slices;
+    (void)stage_rows;
+    if (k3m_plan(uint32_t(pitch), n_hap, pm)) return pm.n_slices;
     return quant_reg_slices(pitch);
 }
 
@@ -658,8 +645,8 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                                      double sy_all, double syy_all, const double* covar, uint32_t n_covar,
                                      const BatchDev& b, uint32_t max_stage_rows, const stoat_gpu_thresholds& thr,
                                      QuantOut out, QuantMoments* mom, uint32_t* part_i, double* part_d,
-                                     uint32_t* slow_list, const uint8_t* yslices, const double* yc, double y_scale,
-                                     int num_sms, int variant, cudaStream_t st, uint32_t* launches) {
+                                     uint32_t* slow_list, uint4* lean_rec, const uint8_t* yslices, const double* yc,
+                                     double y_scale, int num_sms, int variant, cudaStream_t st, uint32_t* launches) {
     if (b.n_snarls == 0) return cudaSuccess;
     const uint32_t pitch = uint32_t(m.pitch);
     const uint32_t n_samples = uint32_t(m.n_cols / 2);
@@ -704,36 +691,43 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         LeanPartials part{part_i, part_d, b.n_snarls};
         uint32_t n_slices = 0;
         K3MPlan pm;
-        if (part_i && part_d && slow_list && yslices && yc && k3m_plan(pitch, m.n_cols, cfg.stage_rows, pm)) {
+        if (part_i && part_d && slow_list && lean_rec && yslices && yc && k3m_plan(pitch, m.n_cols, pm)) {
             // K3M over every snarl (two-path snarls -> exact integer partial sums), then K3 over the slow list
             K3MParams q{};
             q.k = p;
+            q.lean_rec = lean_rec;
             q.yslices = yslices;
             q.yc = yc;
             q.y_scale = y_scale;
-            q.chunk_first = 0;
-            q.chunk_count = pm.chunk_count;
-            q.row_stride = pm.row_stride;
-            q.slot_bytes = pm.slot_bytes;
+            q.rounds_per_slice = pm.rounds_per_slice;
+            q.n_rounds = pm.n_rounds;
             q.slow_list = slow_list;
             q.slow_count = b.counters + 3;
             q.part = part;
             n_slices = pm.n_slices;
             if ((e = cudaMemsetAsync(b.counters + 3, 0, 4, st)) != cudaSuccess) return e;
+            lean_rec_kernel<<<unsigned((b.n_snarls + 255) / 256), 256, 0, st>>>(b.rec, b.blob, b.n_snarls, lean_rec);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
             e = cudaFuncSetAttribute(dosage_moments_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      int(pm.smem_bytes));
             if (e != cudaSuccess) return e;
+            int occ = 1;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dosage_moments_mma_kernel, kMmaWarps * 32,
+                                                              pm.smem_bytes) != cudaSuccess || occ < 1)
+                occ = 1;
+            const int occ_env = env_int("STOAT_GPU_K3M_CTAS", 0);
+            if (occ_env >= 1 && occ_env < occ) occ = occ_env;
             const uint64_t n_tiles = (b.n_snarls + kMmaTile - 1) / kMmaTile;
-            uint64_t ctas = uint64_t(num_sms) / pm.n_slices;
+            uint64_t ctas = uint64_t(num_sms) * uint64_t(occ) / pm.n_slices;
             if (ctas < 1) ctas = 1;
-            if (ctas > n_tiles) ctas = n_tiles;
+            if (ctas > (n_tiles + kMmaWarps - 1) / kMmaWarps) ctas = (n_tiles + kMmaWarps - 1) / kMmaWarps;
             dosage_moments_mma_kernel<<<dim3(unsigned(ctas), pm.n_slices), kMmaWarps * 32, pm.smem_bytes, st>>>(q);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             p.list = slow_list;
             p.list_count = b.counters + 3;
             dosage_moments_tma_kernel<<<unsigned(num_sms), cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
-            if (launches) *launches += 1;
+            if (launches) *launches += 2;
         } else if (part_i && part_d && slow_list && k3r_plan(pitch, cfg.stage_rows, pl)) {
             // K3R over every snarl (two-path snarls -> partial sums), then K3 over what it left on the slow list
             K3RParams q{};
