@@ -283,6 +283,31 @@ def algorithmic_bytes_k1(paths, pitch):
     return distinct * pitch + pitch + 4 * er.size + 8 * (S + P) + 8 * P
 
 
+def algorithmic_bytes_k3m(paths, pitch):
+    """K3M touches the rows of the two-path snarls only (the others go to the left-over list): sum over those snarls of
+    U_s * W, + 16 B lean record in, + 52 B partial sums and 1 B state out per snarl."""
+    spo = np.asarray(paths.snarl_path_off, dtype=np.int64)
+    peo = np.asarray(paths.path_edge_off, dtype=np.int64)
+    er = np.asarray(paths.edge_row)
+    two = np.nonzero(np.diff(spo) == 2)[0]
+    e0, e1 = peo[spo[two]], peo[spo[two + 1]]
+    take = np.zeros(er.size + 1, np.int64)
+    np.add.at(take, e0, 1)
+    np.add.at(take, e1, -1)
+    sel = er[np.cumsum(take[:-1]) > 0]
+    distinct = np.unique(sel[sel != 0xFFFFFFFF]).size
+    return distinct * pitch + (16 + 53) * paths.n_snarls
+
+
+def quant_traffic():
+    """dram bytes per launch of K3M from the committed ncu capture (profiles/k3m_traffic.json), or None"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "k3m_traffic.json")) as f:
+            return json.load(f).get("dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
 def main():
     args = parse_args()
     if args.trait == "eqtl":
@@ -323,7 +348,7 @@ def main():
     ctx = stoat_b200.Context(local)
     ctx.set_matrix_dev(d["bits_dev"].data_ptr(), d["n_rows"], d["n_cols"])
     t_repack = ctx.timing()["repack_ms"]
-    pitch = ctx.row_pitch
+    pitch = ((int(d["n_cols"]) + 127) // 128) * 16  # SURVEY §8d W (the device pitch is rounded up to whole 32 B sectors)
     if args.trait == "binary":
         ctx.set_binary_phenotype(d["is_case"])
         run = ctx.binary_run_staged
@@ -411,7 +436,7 @@ def main():
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s (B200_PROFILING.md)"
         k1 = float(np.mean(k1_ms))
-        alg = algorithmic_bytes_k1(paths, pitch)
+        alg = algorithmic_bytes_k1(paths, pitch) if args.trait == "binary" else algorithmic_bytes_k3m(paths, pitch)
         achieved = alg / (k1 * 1e-3) / 1e9
         traffic = None
         try:
@@ -420,10 +445,12 @@ def main():
         except Exception:
             pass
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": traffic, "kernel": "path_and_popc (K1)", "algorithmic_bytes_per_launch": int(alg),
+                    "traffic": traffic if args.trait == "binary" else quant_traffic(),
+                    "kernel": "path_and_popc (K1)" if args.trait == "binary" else "dosage_moments_mma (K3M)", "algorithmic_bytes_per_launch": int(alg),
                     "kernel_ms": k1, "peak_source": peak_src,
                     "snarls_off_fast_path": int(n_general), "fisher_tables": int(n_fisher),
-                    "other_kernels_ms": {"binary_stats (K2)" if args.trait == "binary" else "solve": float(np.mean(k2_ms)),
+                    "other_kernels_ms": {"binary_stats (K2a) + fisher_exact (K2b)" if args.trait == "binary"
+                                         else "left-over list (K3) + ols_solve (K4) + general path (K3G)": float(np.mean(k2_ms)),
                                          "repack_rows (K0, once per matrix, not in the step)": t_repack}}
         line = {
             "metric": METRIC if args.trait == "binary" else "snarl-path tests/sec (quantitative OLS)",

@@ -71,8 +71,11 @@ enum {
     STOAT_P_DBLMAX = 4,  /* set_precision(DBL_MAX) (an expected count is zero, :196-197)    */
     STOAT_P_UNDEF = 5,   /* the reference reads out of bounds here (zero dosage columns
                             reach linear_regression, stats_test.cpp:487-489): value is NaN  */
-    STOAT_P_OVERLIMIT = 6 /* snarl exceeds STOAT_GPU_MAX_*: not computed (value NaN); the host
+    STOAT_P_OVERLIMIT = 6, /* snarl exceeds STOAT_GPU_MAX_*: not computed (value NaN); the host
                             must run its own per-snarl analyzer for it                      */
+    STOAT_P_DEFERRED = 7  /* sample-sharded quantitative run only: the snarl needs every column
+                            (not a two-path table, rank deficient, near-perfect fit): replay it
+                            with the whole rows (stoat_b200/shard.py does)                   */
 };
 
 /* filtering thresholds, defaults of `stoat vcf` (src/subcommand/vcf.cpp:61-73)             */
@@ -227,11 +230,31 @@ STOAT_GPU_API int stoat_gpu_binary_stats_staged(stoat_gpu_ctx* ctx, const stoat_
 STOAT_GPU_API int stoat_gpu_binary_fetch(stoat_gpu_ctx* ctx, stoat_gpu_binary_out* out);
 STOAT_GPU_API int stoat_gpu_quantitative_fetch(stoat_gpu_ctx* ctx, stoat_gpu_quant_out* out);
 
+/* ---- sample-sharded quantitative run (the reference has no counterpart: its unit of
+ *      parallelism is the snarl, src/snarl_analyzer.cpp:165-172) ---------------------------------
+ * Every GPU holds a column range (whole samples) of the matrix and the matching slice of the
+ * phenotype.  The two-path tables of quantitative_table.cpp:22-104 and the X^T X / X^T y build of
+ * stats_test.cpp:444-458 are sums over samples, so the step splits around ONE all-reduce:
+ *   set_quantitative_phenotype_shard   local slice + the WHOLE phenotype's mean, sum (y - mean),
+ *                                      sum (y - mean)^2 and max |y - mean| (host, O(n))
+ *   quantitative_moments_staged        per snarl 7 class counts (u32) + 3 sums (f64) of the local columns
+ *   quantitative_partials_dev          the two device buffers to all-reduce(sum) in place (NCCL)
+ *   quantitative_solve_staged          filters + OLS on the summed partials; snarls that need more
+ *                                      than that come back with code STOAT_P_DEFERRED
+ *   quantitative_fetch                 as usual                                                  */
+STOAT_GPU_API int stoat_gpu_set_quantitative_phenotype_shard(stoat_gpu_ctx* ctx, const double* y_local, uint64_t n_local,
+                                                             double mean, double sum_centred, double sum_centred_sq,
+                                                             double max_abs_centred);
+STOAT_GPU_API int stoat_gpu_quantitative_moments_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
+STOAT_GPU_API int stoat_gpu_quantitative_partials_dev(stoat_gpu_ctx* ctx, uint32_t** ints_dev, uint64_t* n_ints,
+                                                      double** doubles_dev, uint64_t* n_doubles);
+STOAT_GPU_API int stoat_gpu_quantitative_solve_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
+
 /* ---- introspection --------------------------------------------------------------------- */
 STOAT_GPU_API int stoat_gpu_last_timing(const stoat_gpu_ctx* ctx, stoat_gpu_timing* out);
 /* cudaStream_t of the context as an integer (so the caller can record its own events)       */
 STOAT_GPU_API uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx);
-/* bytes per repacked row on the device: ceil(n_cols / 128) * 16                             */
+/* bytes per repacked row on the device: ceil(n_cols / 256) * 32 (whole 32-byte sectors)         */
 STOAT_GPU_API uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx);
 /* read back one repacked row (tests of K0)                                                  */
 STOAT_GPU_API int stoat_gpu_read_row(stoat_gpu_ctx* ctx, uint64_t row, uint8_t* out, uint64_t out_bytes);

@@ -3,6 +3,7 @@
 
 Both shardings of SURVEY §8e on a seeded problem; rank 0 compares with the oracle's single-process result:
   * snarl-sharded binary and quantitative (no data-path collective, host gather of the result arrays)
+  * sample-sharded quantitative: K3M moments of the local columns, ONE all-reduce of the partial sums, K4 on the sums
   * sample-sharded binary: count pass on the local columns, ONE ncclAllReduce(sum) applied in place to the context's
     device count buffer, statistics on the summed counts — every rank must hold the full, bit-exact result.
 Exit code 0 = parity.
@@ -52,6 +53,21 @@ def main():
             print(f"sample-sharded binary x{world} (NCCL all-reduce of the count buffer): "
                   f"{'parity ok on every rank' if flag.item() else 'MISMATCH'}", flush=True)
         ok = bool(flag.item())
+        # sample-sharded quantitative: local moments (K3M) -> NCCL all-reduce of the partial sums -> solve (K4); deferred
+        # snarls replayed from the re-assembled rows
+        got = shard.run_quantitative_sample_sharded(ctx, bits, n_rows, n_cols, paths, d["y"], rank, world)
+        okq = True
+        try:
+            H.assert_quant_equal(got, oracle.quantitative_batch(bits, n_cols, d["y"], P))  # on EVERY rank
+        except AssertionError as e:
+            print(f"rank {rank}: sample-sharded quantitative mismatch: {e}", flush=True)
+            okq = False
+        flag = torch.tensor([1 if okq else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            print(f"sample-sharded quantitative x{world} (NCCL all-reduce of the class counts + phenotype sums): "
+                  f"{'parity ok on every rank' if flag.item() else 'MISMATCH'}", flush=True)
+        ok = ok and bool(flag.item())
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 

@@ -83,6 +83,11 @@ SIGNATURES = {
     "stoat_gpu_binary_stats_staged": (C.c_int, [CTX, C.POINTER(Thresholds)]),
     "stoat_gpu_binary_fetch": (C.c_int, [CTX, C.POINTER(BinaryOut)]),
     "stoat_gpu_quantitative_fetch": (C.c_int, [CTX, C.POINTER(QuantOut)]),
+    "stoat_gpu_set_quantitative_phenotype_shard": (C.c_int, [CTX, C.c_void_p, C.c_uint64, C.c_double, C.c_double,
+                                                             C.c_double, C.c_double]),
+    "stoat_gpu_quantitative_moments_staged": (C.c_int, [CTX, C.POINTER(Thresholds)]),
+    "stoat_gpu_quantitative_partials_dev": (C.c_int, [CTX, C.POINTER(C.c_void_p), u64p, C.POINTER(C.c_void_p), u64p]),
+    "stoat_gpu_quantitative_solve_staged": (C.c_int, [CTX, C.POINTER(Thresholds)]),
     "stoat_gpu_last_timing": (C.c_int, [CTX, C.POINTER(Timing)]),
     "stoat_gpu_stream": (C.c_uint64, [CTX]),
     "stoat_gpu_row_pitch": (C.c_uint64, [CTX]),

@@ -281,6 +281,29 @@ class Context:
         thr = self._thr(min_ind, min_hap, maf)
         self._check(self._lib.stoat_gpu_quantitative_run_staged(self._ctx, C.byref(thr)))
 
+    # ---- sample-sharded quantitative run (include/stoat_gpu.h): moments | all-reduce | solve ----------
+    def set_quantitative_phenotype_shard(self, y_local, mean: float, sum_centred: float, sum_centred_sq: float,
+                                         max_abs_centred: float):
+        a = np.ascontiguousarray(y_local, dtype=np.float64)
+        self._keep_y = a
+        self._check(self._lib.stoat_gpu_set_quantitative_phenotype_shard(
+            self._ctx, _ptr(a), a.size, float(mean), float(sum_centred), float(sum_centred_sq), float(max_abs_centred)))
+
+    def quantitative_moments_staged(self, min_ind=3, min_hap=5, maf=0.05):
+        thr = self._thr(min_ind, min_hap, maf)
+        self._check(self._lib.stoat_gpu_quantitative_moments_staged(self._ctx, C.byref(thr)))
+
+    def quantitative_partials_dev(self) -> tuple[int, int, int, int]:
+        """(device pointer, length) of the uint32 class counts and of the float64 sums to all-reduce in place"""
+        pi, ni, pd, nd = C.c_void_p(), C.c_uint64(), C.c_void_p(), C.c_uint64()
+        self._check(self._lib.stoat_gpu_quantitative_partials_dev(self._ctx, C.byref(pi), C.byref(ni), C.byref(pd),
+                                                                 C.byref(nd)))
+        return int(pi.value), int(ni.value), int(pd.value), int(nd.value)
+
+    def quantitative_solve_staged(self, min_ind=3, min_hap=5, maf=0.05):
+        thr = self._thr(min_ind, min_hap, maf)
+        self._check(self._lib.stoat_gpu_quantitative_solve_staged(self._ctx, C.byref(thr)))
+
     def quantitative_fetch(self, out: dict | None = None) -> dict:
         S, P = self._staged
         o = out if out is not None else self._quant_arrays(S, P)

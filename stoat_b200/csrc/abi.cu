@@ -36,7 +36,9 @@ int fail_cuda(stoat_gpu_ctx* ctx, cudaError_t e, const char* where) {
         if (e__ != cudaSuccess) return fail_cuda(ctx, e__, #expr); \
     } while (0)
 
-uint64_t pitch_for(uint64_t n_cols) { return ((n_cols + 127) / 128) * 16; }
+// Row pitch: whole 32-byte sectors.  K3M's lane groups read 64 bytes of a row at a time; with 16-byte aligned rows every
+// second row made those reads straddle three sectors (ncu: 26 % more DRAM traffic than the algorithmic bytes).
+uint64_t pitch_for(uint64_t n_cols) { return ((n_cols + 255) / 256) * 32; }
 
 MatrixDev matrix_view(const stoat_gpu_ctx* ctx) {
     MatrixDev m;
@@ -50,6 +52,7 @@ MatrixDev matrix_view(const stoat_gpu_ctx* ctx) {
 struct QuantState {
     DevBuf yc, ys, mom, part_i, part_d, slow, yslices, lean_rec;
     double sy_all = 0.0, syy_all = 0.0, y_scale = 1.0;
+    bool have_partials = false;
 };
 
 }  // namespace
@@ -222,25 +225,14 @@ int stoat_gpu_set_binary_phenotype(stoat_gpu_ctx* ctx, const uint8_t* is_case, u
     return STOAT_GPU_OK;
 }
 
-int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, uint64_t n_samples) {
-    if (!ctx || !y) return fail(ctx, STOAT_GPU_ERR_ARG, "set_quantitative_phenotype: NULL argument");
-    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, "set_quantitative_phenotype: set the matrix first");
-    if (n_samples * 2 != ctx->n_cols)
-        return fail(ctx, STOAT_GPU_ERR_ARG, "set_quantitative_phenotype: n_samples must be n_cols / 2");
+// shared by the whole-phenotype and the sample-shard entry points: `mean`, `s1`, `s2` (sums of y - mean and its square)
+// and `vmax` (max |y - mean|) describe the WHOLE phenotype, y[0 .. n_samples) is what this GPU holds
+static int set_quant_common(stoat_gpu_ctx* ctx, const double* y, uint64_t n_samples, double mean, double s1, double s2,
+                            double vmax) {
     CK(cudaSetDevice(ctx->device));
     CtxExtra* x = extra_of(ctx);
-    // centring constant and the all-sample sums of the centred values (O(n), once per phenotype)
-    long double acc = 0.0L;
-    for (uint64_t i = 0; i < n_samples; ++i) acc += y[i];
-    const double mean = double(acc / (long double)n_samples);
-    long double s1 = 0.0L, s2 = 0.0L;
-    for (uint64_t i = 0; i < n_samples; ++i) {
-        const double v = y[i] - mean;
-        s1 += v;
-        s2 += (long double)v * v;
-    }
-    x->q.sy_all = double(s1);
-    x->q.syy_all = double(s2);
+    x->q.sy_all = s1;
+    x->q.syy_all = s2;
     const uint32_t n_words = uint32_t(ctx->pitch / 4);
     CK(ctx->y.reserve(n_samples * 8));
     CK(x->q.yc.reserve(n_samples * 8));
@@ -254,8 +246,6 @@ int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, ui
     // lane (g, t) works on the 16-byte chunk 4 c + t of a row, i.e. on word (4 c + t) * 4 + j, and register b, byte bb
     // of its fragment is slice g of that word's sample 4 bb + 2 m + b.
     {
-        double vmax = 0.0;
-        for (uint64_t i = 0; i < n_samples; ++i) vmax = std::max(vmax, std::fabs(y[i] - mean));
         int ex = 0;
         if (vmax > 0.0 && std::isfinite(vmax)) std::frexp(vmax, &ex);  // vmax = f * 2^ex, f in [0.5, 1)
         x->q.y_scale = std::ldexp(1.0, ex + 1);                        // |y - mean| / scale < 0.5
@@ -266,7 +256,7 @@ int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, ui
             for (int t = 0; t < 8; ++t) {
                 r *= 128.0;
                 const double qv = std::nearbyint(r);
-                qs[t] = std::isfinite(qv) ? int8_t(qv) : int8_t(0);
+                qs[t] = (std::isfinite(qv) && std::fabs(qv) <= 127.0) ? int8_t(qv) : int8_t(0);
                 r -= qv;
             }
             const uint64_t word = i / 16, k = i % 16;  // k = 4 bb + 2 m + b
@@ -282,7 +272,38 @@ int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, ui
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->n_samples_quant = n_samples;
     ctx->have_quant = true;
+    ctx->have_quant_result = false;
     return STOAT_GPU_OK;
+}
+
+int stoat_gpu_set_quantitative_phenotype(stoat_gpu_ctx* ctx, const double* y, uint64_t n_samples) {
+    if (!ctx || !y) return fail(ctx, STOAT_GPU_ERR_ARG, "set_quantitative_phenotype: NULL argument");
+    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, "set_quantitative_phenotype: set the matrix first");
+    if (n_samples * 2 != ctx->n_cols)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "set_quantitative_phenotype: n_samples must be n_cols / 2");
+    // centring constant and the all-sample sums of the centred values (O(n), once per phenotype)
+    long double acc = 0.0L;
+    for (uint64_t i = 0; i < n_samples; ++i) acc += y[i];
+    const double mean = double(acc / (long double)n_samples);
+    long double s1 = 0.0L, s2 = 0.0L;
+    double vmax = 0.0;
+    for (uint64_t i = 0; i < n_samples; ++i) {
+        const double v = y[i] - mean;
+        s1 += v;
+        s2 += (long double)v * v;
+        vmax = std::max(vmax, std::fabs(v));
+    }
+    return set_quant_common(ctx, y, n_samples, mean, double(s1), double(s2), vmax);
+}
+
+int stoat_gpu_set_quantitative_phenotype_shard(stoat_gpu_ctx* ctx, const double* y_local, uint64_t n_local, double mean,
+                                               double sum_centred, double sum_centred_sq, double max_abs_centred) {
+    if (!ctx) return STOAT_GPU_ERR_ARG;
+    if (!y_local) return fail(ctx, STOAT_GPU_ERR_ARG, "set_quantitative_phenotype_shard: y is NULL");
+    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, "set_quantitative_phenotype_shard: set the matrix first");
+    if (n_local * 2 != ctx->n_cols)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "set_quantitative_phenotype_shard: n_local must be n_cols / 2");
+    return set_quant_common(ctx, y_local, n_local, mean, sum_centred, sum_centred_sq, max_abs_centred);
 }
 
 int stoat_gpu_set_covariates(stoat_gpu_ctx* ctx, const double* covar, uint64_t n_samples, uint64_t n_covar) {
@@ -329,6 +350,7 @@ int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths) {
     CtxExtra* x = extra_of(ctx);
     ctx->have_batch = false;
     ctx->have_binary_counts = ctx->have_binary_result = ctx->have_quant_result = false;
+    extra_of(ctx)->q.have_partials = false;
     CK(ctx->d_snarl_path_off.reserve((S + 1) * 8));
     CK(ctx->d_path_edge_off.reserve((P + 1) * 8));
     CK(ctx->d_edge_row.reserve(std::max<uint64_t>(E * 4, 16)));
@@ -505,22 +527,25 @@ static int quant_reserve(stoat_gpu_ctx* ctx) {
     return STOAT_GPU_OK;
 }
 
-int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr) {
+// phase 0: the whole step; 1: moments only (K3M partial sums stay on the device); 2: solve on the (all-reduced) partials
+static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int phase) {
     if (!ctx || !thr) return fail(ctx, STOAT_GPU_ERR_ARG, "quantitative: NULL argument");
     if (!ctx->have_batch) return fail(ctx, STOAT_GPU_ERR_STATE, "quantitative: no staged batch");
     if (!ctx->have_quant) return fail(ctx, STOAT_GPU_ERR_STATE, "quantitative: no quantitative phenotype");
     if (ctx->n_covar && ctx->n_samples_covar * 2 < ctx->n_cols)
         return fail(ctx, STOAT_GPU_ERR_ARG, "quantitative: fewer covariate rows than samples");
     CK(cudaSetDevice(ctx->device));
+    if (phase != 0 && ctx->n_covar) return fail(ctx, STOAT_GPU_ERR_STATE, "quantitative: the sample-sharded phases do not take covariates");
     int rc = quant_reserve(ctx);
     if (rc) return rc;
     CtxExtra* x = extra_of(ctx);
     const uint64_t S = ctx->batch.n_snarls;
+    if (phase == 2 && !x->q.have_partials) return fail(ctx, STOAT_GPU_ERR_STATE, "quantitative_solve_staged: run quantitative_moments_staged first");
     // the general-path list grows during the run: reset its length to what prep put there
     x->counters_host[0] = ctx->n_big;
     CK(cudaMemcpyAsync(ctx->d_counters.p, x->counters_host, 4, cudaMemcpyHostToDevice, ctx->stream));
     // filtered snarls keep NaN / NA outputs
-    if (S) {
+    if (S && phase != 1) {
         CK(cudaMemsetAsync(ctx->q_p.p, 0xFF, S * 8, ctx->stream));
         CK(cudaMemsetAsync(ctx->q_r2.p, 0xFF, S * 8, ctx->stream));
         CK(cudaMemsetAsync(ctx->q_beta.p, 0xFF, S * 8, ctx->stream));
@@ -539,17 +564,51 @@ int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresh
                                 x->q.part_d.as<double>(), x->q.slow.as<uint32_t>(), x->q.lean_rec.as<uint4>(),
                                 x->q.yslices.as<uint8_t>(),
                                 x->q.yc.as<double>(), x->q.y_scale, ctx->num_sms, ctx->k1_variant, ctx->stream,
-                                &ctx->timing.launches));
+                                &ctx->timing.launches, ctx->ev[4], phase));
+    if (phase == 2) CK(cudaEventRecord(ctx->ev[4], ctx->stream));
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
     CK(cudaMemcpyAsync(x->readback, ctx->d_counters.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->timing.n_general = S ? x->readback[0] : 0;
     ctx->timing.n_fisher = 0;
-    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));
-    ctx->timing.stats_ms = 0.f;
-    ctx->have_quant_result = true;
+    if (S) {
+        CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[4]));  // the moments pass (K3M / K3R / K3)
+        CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ctx->ev[4], ctx->ev[3]));  // left-over list, K4, general path
+    } else {
+        ctx->timing.table_ms = ctx->timing.stats_ms = 0.f;
+    }
+    x->q.have_partials = phase == 1;
+    ctx->have_quant_result = phase != 1;
     return STOAT_GPU_OK;
 }
+
+int stoat_gpu_quantitative_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr) { return quant_run(ctx, thr, 0); }
+
+int stoat_gpu_quantitative_moments_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr) {
+    const int rc = quant_run(ctx, thr, 1);
+    if (rc == STOAT_GPU_ERR_CUDA && ctx && ctx->err.find("not supported") != std::string::npos)
+        return fail(ctx, STOAT_GPU_ERR_STATE,
+                    "quantitative_moments_staged: the two-path moments kernel does not apply (needs < 65536 local "
+                    "haplotypes, no covariates)");
+    return rc;
+}
+
+int stoat_gpu_quantitative_solve_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr) { return quant_run(ctx, thr, 2); }
+
+int stoat_gpu_quantitative_partials_dev(stoat_gpu_ctx* ctx, uint32_t** ints_dev, uint64_t* n_ints, double** doubles_dev,
+                                        uint64_t* n_doubles) {
+    if (!ctx || !ints_dev || !n_ints || !doubles_dev || !n_doubles)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "quantitative_partials_dev: NULL argument");
+    CtxExtra* x = extra_of(ctx);
+    if (!x->q.have_partials) return fail(ctx, STOAT_GPU_ERR_STATE, "quantitative_partials_dev: no partial sums (run quantitative_moments_staged)");
+    const uint64_t slices = std::max<uint32_t>(quant_lean_slices(ctx->pitch, ctx->n_cols, x->max_stage_rows), 1);
+    *ints_dev = x->q.part_i.as<uint32_t>();
+    *n_ints = slices * 7 * ctx->batch.n_snarls;
+    *doubles_dev = x->q.part_d.as<double>();
+    *n_doubles = slices * 3 * ctx->batch.n_snarls;
+    return STOAT_GPU_OK;
+}
+
 
 int stoat_gpu_quantitative_fetch(stoat_gpu_ctx* ctx, stoat_gpu_quant_out* out) {
     if (!ctx || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "quantitative_fetch: NULL argument");

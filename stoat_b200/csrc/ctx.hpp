@@ -103,7 +103,9 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                                      const BatchDev& b, uint32_t max_stage_rows, const stoat_gpu_thresholds& thr,
                                      QuantOut out, QuantMoments* mom, uint32_t* part_i, double* part_d,
                                      uint32_t* slow_list, uint4* lean_rec, const uint8_t* yslices, const double* yc,
-                                     double y_scale, int num_sms, int variant, cudaStream_t st, uint32_t* launches);
+                                     double y_scale, int num_sms, int variant, cudaStream_t st, uint32_t* launches,
+                                     cudaEvent_t ev_table_done,  // recorded after the moments pass (K3M / K3R / K3)
+                                     int phase);  // 0: whole step; 1: moments only; 2: solve only (sample-sharded)
 size_t quant_yslices_bytes(uint64_t pitch);  // K3M's phenotype slice table
 // slices of the haplotype range the two-path kernels (K3M / K3R) use: sizes the partial-sum buffers (0: neither runs)
 uint32_t quant_lean_slices(uint64_t pitch, uint64_t n_hap, uint32_t stage_rows);

@@ -16,7 +16,7 @@
 namespace stoat {
 
 // codes of include/stoat_gpu.h
-enum : uint8_t { kPValue = 0, kPNa = 1, kPZero = 2, kPOne = 3, kPDblMax = 4, kPUndef = 5, kPOverLimit = 6 };
+enum : uint8_t { kPValue = 0, kPNa = 1, kPZero = 2, kPOne = 3, kPDblMax = 4, kPUndef = 5, kPOverLimit = 6, kPDeferred = 7 };
 
 struct PVal {
     double v;

@@ -446,11 +446,26 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
 __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __restrict__ mom, uint64_t n_snarls,
                                                         const K3Params kp, const LeanPartials part, uint32_t n_slices,
                                                         const uint64_t* __restrict__ snarl_path_off, QuantOut out,
-                                                        uint32_t* g_list, uint32_t* g_count) {
+                                                        uint32_t* g_list, uint32_t* g_count, uint32_t defer) {
+    // defer (sample-sharded runs): a snarl that needs more than the summed two-path partials — any other shape, a
+    // rank-deficient or near-perfect fit — is not sent to the general path (this GPU holds only some of the columns)
+    // but marked STOAT_P_DEFERRED; the host replays those snarls with all columns (stoat_b200/shard.py).
     const uint64_t s = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (s >= n_snarls) return;
     const uint8_t state = mom[s].state;
-    if (state != 1 && state != 2) return;
+    auto hand_on = [&]() {
+        if (defer) {
+            out.code[s] = kPDeferred;
+            out.filtered[s] = 0;
+        } else {
+            const uint32_t slot = atomicAdd(g_count, 1u);
+            g_list[slot] = uint32_t(s);
+        }
+    };
+    if (state != 1 && state != 2) {
+        if (defer) hand_on();
+        return;
+    }
     QuantMoments m;
     if (state == 2) {
         LeanSums t{};
@@ -471,8 +486,7 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
         const int r = lean_finish(kp, s, uint32_t(snarl_path_off[s]), t, m);
         if (r == 0) return;
         if (r == 2) {
-            const uint32_t slot = atomicAdd(g_count, 1u);
-            g_list[slot] = uint32_t(s);
+            hand_on();
             return;
         }
     } else {
@@ -495,8 +509,7 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
     if (xtx_inverse<4>(X, p, inv)) {
         // rank deficient: the pseudo-inverse picks the minimum-norm solution, which is NOT invariant under the
         // centring of y used by the moment path -> redo on the general path with the raw phenotype
-        const uint32_t slot = atomicAdd(g_count, 1u);
-        g_list[slot] = uint32_t(s);
+        hand_on();
         return;
     }
     double beta[4];
@@ -517,8 +530,7 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
     const double tss = m.syy - m.sy * m.sy / double(m.n_used);
     if (!(rss > 1e-6 * tss)) {
         // expansion not trustworthy (near-perfect fit): redo with explicit residuals on the general path
-        const uint32_t slot = atomicAdd(g_count, 1u);
-        g_list[slot] = uint32_t(s);
+        hand_on();
         return;
     }
     const OlsOut o = ols_statistics(beta[1], inv(1, 1), rss, tss, m.n_used, p);
@@ -646,7 +658,10 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                                      const BatchDev& b, uint32_t max_stage_rows, const stoat_gpu_thresholds& thr,
                                      QuantOut out, QuantMoments* mom, uint32_t* part_i, double* part_d,
                                      uint32_t* slow_list, uint4* lean_rec, const uint8_t* yslices, const double* yc,
-                                     double y_scale, int num_sms, int variant, cudaStream_t st, uint32_t* launches) {
+                                     double y_scale, int num_sms, int variant, cudaStream_t st, uint32_t* launches,
+                                     cudaEvent_t ev_table_done, int phase) {
+    // phase 0: the whole step.  Sample-sharded runs split it around the all-reduce of the partial sums:
+    // phase 1 = lean records + K3M only, phase 2 = K4 on the summed partials with everything else deferred to the host.
     if (b.n_snarls == 0) return cudaSuccess;
     const uint32_t pitch = uint32_t(m.pitch);
     const uint32_t n_samples = uint32_t(m.n_cols / 2);
@@ -691,6 +706,16 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         LeanPartials part{part_i, part_d, b.n_snarls};
         uint32_t n_slices = 0;
         K3MPlan pm;
+        if (phase == 2) {
+            if (!k3m_plan(pitch, m.n_cols, pm)) return cudaErrorNotSupported;
+            ols_solve_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(
+                mom, b.n_snarls, p, part, pm.n_slices, b.snarl_path_off, out, b.big_list, b.counters, 1u);
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            if (launches) *launches += 1;
+            return cudaSuccess;
+        }
+        if (phase == 1 && !(part_i && part_d && slow_list && lean_rec && yslices && yc && k3m_plan(pitch, m.n_cols, pm)))
+            return cudaErrorNotSupported;
         if (part_i && part_d && slow_list && lean_rec && yslices && yc && k3m_plan(pitch, m.n_cols, pm)) {
             // K3M over every snarl (two-path snarls -> exact integer partial sums), then K3 over the slow list
             K3MParams q{};
@@ -723,11 +748,14 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             if (ctas > (n_tiles + kMmaWarps - 1) / kMmaWarps) ctas = (n_tiles + kMmaWarps - 1) / kMmaWarps;
             dosage_moments_mma_kernel<<<dim3(unsigned(ctas), pm.n_slices), kMmaWarps * 32, pm.smem_bytes, st>>>(q);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            if (ev_table_done && (e = cudaEventRecord(ev_table_done, st)) != cudaSuccess) return e;
+            if (launches) *launches += 2;
+            if (phase == 1) return cudaSuccess;
             p.list = slow_list;
             p.list_count = b.counters + 3;
             dosage_moments_tma_kernel<<<unsigned(num_sms), cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
-            if (launches) *launches += 2;
+            if (launches) *launches += 1;
         } else if (part_i && part_d && slow_list && k3r_plan(pitch, cfg.stage_rows, pl)) {
             // K3R over every snarl (two-path snarls -> partial sums), then K3 over what it left on the slow list
             K3RParams q{};
@@ -746,6 +774,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             if (ctas > b.n_snarls) ctas = b.n_snarls;
             k3r_kernel(pl.wpt)<<<dim3(unsigned(ctas), pl.n_slices), pl.threads, pl.smem_bytes, st>>>(q);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            if (ev_table_done && (e = cudaEventRecord(ev_table_done, st)) != cudaSuccess) return e;
             p.list = slow_list;
             p.list_count = b.counters + 3;
             dosage_moments_tma_kernel<<<unsigned(num_sms), cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
@@ -756,9 +785,10 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             const unsigned grid = unsigned(want < uint64_t(num_sms) ? want : uint64_t(num_sms));
             dosage_moments_tma_kernel<<<grid, cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            if (ev_table_done && (e = cudaEventRecord(ev_table_done, st)) != cudaSuccess) return e;
         }
         ols_solve_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(mom, b.n_snarls, p, part, n_slices,
-                                                                            b.snarl_path_off, out, b.big_list, b.counters);
+                                                                            b.snarl_path_off, out, b.big_list, b.counters, 0u);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         g.list = b.big_list;
         g.n_list_dev = b.counters;
@@ -766,11 +796,14 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         if (launches) *launches += 3;
         return cudaSuccess;
     }
+    if (phase != 0) return cudaErrorNotSupported;  // covariates / K3M unavailable: no sample-sharded moments path
     g.list = nullptr;
     g.n_list_dev = nullptr;
     g.n_list_host = b.n_snarls;
     if (launches) *launches += 1;
-    return launch_quant_general(g, b.n_snarls, num_sms, st);
+    e = launch_quant_general(g, b.n_snarls, num_sms, st);
+    if (e == cudaSuccess && ev_table_done) e = cudaEventRecord(ev_table_done, st);
+    return e;
 }
 
 // centre + permute the phenotype:  yc[i] = y[i] - mean;  ys[(i % 16) * n_words + i / 16] = yc[i] (0 beyond n)

@@ -208,3 +208,149 @@ def run_binary_sample_sharded(ctx, bits, n_rows: int, n_cols: int, paths: SnarlP
         allreduce_counts_inplace(ctx, group)
     ctx.binary_stats_staged(mi, mh, maf)
     return ctx.binary_fetch()
+
+
+# ---------------------------------------------------------------------------------------------------
+# sample-sharded, quantitative
+# ---------------------------------------------------------------------------------------------------
+P_DEFERRED = 7  # STOAT_P_DEFERRED (include/stoat_gpu.h)
+
+
+def phenotype_summary(y) -> tuple[float, float, float, float]:
+    """mean, sum (y - mean), sum (y - mean)^2, max |y - mean| of the WHOLE phenotype: what every rank of a
+    sample-sharded run passes to set_quantitative_phenotype_shard (same numbers on every rank: computed here in
+    extended precision exactly as the library does for an unsharded phenotype)."""
+    a = np.asarray(y, dtype=np.float64)
+    if a.size == 0:
+        return 0.0, 0.0, 0.0, 0.0
+    mean = float(np.sum(a.astype(np.longdouble)) / np.longdouble(a.size))
+    v = a - mean
+    vl = v.astype(np.longdouble)
+    return mean, float(np.sum(vl)), float(np.sum(vl * vl)), float(np.max(np.abs(v)))
+
+
+class _DevF64:
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 3}
+
+
+def allreduce_partials_inplace(ctx, group=None):
+    """The ONE exchange of a sample-sharded quantitative run: NCCL all-reduce(sum) of the per-snarl class counts
+    (uint32 [7 S] per haplotype slice) and sums (float64 [3 S]) in place on the context's device buffers."""
+    import torch
+    import torch.distributed as dist
+
+    pi, ni, pd, nd = ctx.quantitative_partials_dev()
+    dev = torch.device("cuda", ctx.device)
+    if ni:
+        dist.all_reduce(torch.as_tensor(_DevU32(pi, ni), device=dev), op=dist.ReduceOp.SUM, group=group)
+    if nd:
+        dist.all_reduce(torch.as_tensor(_DevF64(pd, nd), device=dev), op=dist.ReduceOp.SUM, group=group)
+    torch.cuda.synchronize(ctx.device)
+
+
+def deferred_snarls(result: dict) -> np.ndarray:
+    """snarls a sample-sharded solve could not finish from the summed two-path partials"""
+    return np.flatnonzero(np.asarray(result["code"]) == P_DEFERRED)
+
+
+def gather_deferred_rows(local_bits: np.ndarray, n_rows: int, local_cols: int, paths: SnarlPaths, todo: np.ndarray,
+                         col_ranges: list[tuple[int, int]], allgather) -> tuple[np.ndarray, int, SnarlPaths]:
+    """Whole rows of the snarls in `todo`, rebuilt from every rank's column slice.
+
+    `allgather(obj) -> list` is the collective (dist.all_gather_object in a real run).  Returns a compact
+    reference-layout matrix (rows x all columns), its row count and the sub-batch whose edge_row indices point into it."""
+    sub = select_snarls(paths, todo)
+    er = sub.edge_row
+    rows = np.unique(er[er != MISSING_EDGE])
+    mine = gather_rows(local_bits, local_cols, rows) if local_cols else np.zeros(0, np.uint8)
+    parts = allgather((mine, local_cols))
+    n_cols = sum(c1 - c0 for c0, c1 in col_ranges)
+    dense = np.zeros((rows.size, n_cols), dtype=bool)
+    for (c0, c1), (chunk, w) in zip(col_ranges, parts):
+        if c1 <= c0:
+            continue
+        assert w == c1 - c0
+        d = np.unpackbits(np.asarray(chunk, np.uint8), bitorder="little")[: rows.size * w].reshape(rows.size, w)
+        dense[:, c0:c1] = d.astype(bool)
+    remap = np.full(int(rows.max()) + 1 if rows.size else 1, MISSING_EDGE, dtype=np.uint32)
+    remap[rows] = np.arange(rows.size, dtype=np.uint32)
+    er2 = er.copy()
+    ok = er != MISSING_EDGE
+    er2[ok] = remap[er[ok]]
+    bits = np.packbits(dense.reshape(-1), bitorder="little")
+    return bits, int(rows.size), SnarlPaths(sub.snarl_path_off, sub.path_edge_off, er2)
+
+
+def select_snarls(paths: SnarlPaths, idx: np.ndarray) -> SnarlPaths:
+    """The CSR of the snarls `idx` (in that order)."""
+    spo = np.asarray(paths.snarl_path_off, dtype=np.int64)
+    peo = np.asarray(paths.path_edge_off, dtype=np.int64)
+    er = np.asarray(paths.edge_row, dtype=np.uint32)
+    n_paths = spo[idx + 1] - spo[idx]
+    new_spo = np.concatenate([[0], np.cumsum(n_paths)]).astype(np.uint64)
+    path_ids = np.concatenate([np.arange(spo[s], spo[s + 1]) for s in idx]) if len(idx) else np.zeros(0, np.int64)
+    n_edges = peo[path_ids + 1] - peo[path_ids]
+    new_peo = np.concatenate([[0], np.cumsum(n_edges)]).astype(np.uint64)
+    edges = np.concatenate([er[peo[p]:peo[p + 1]] for p in path_ids]) if len(path_ids) else np.zeros(0, np.uint32)
+    return SnarlPaths(new_spo, new_peo, edges.astype(np.uint32))
+
+
+def merge_deferred(result: dict, todo: np.ndarray, replay: dict, paths: SnarlPaths) -> dict:
+    """Write the replayed snarls' rows over the deferred ones (per-snarl arrays by snarl, allele_paths by path)."""
+    spo = np.asarray(paths.snarl_path_off, dtype=np.int64)
+    out = {k: np.array(v, copy=True) for k, v in result.items()}
+    for k, v in replay.items():
+        if k == "allele_paths":
+            pos = 0
+            for s in todo:
+                n = int(spo[s + 1] - spo[s])
+                out[k][spo[s]:spo[s] + n] = v[pos:pos + n]
+                pos += n
+        else:
+            out[k][todo] = v
+    return out
+
+
+def run_quantitative_sample_sharded(ctx, bits, n_rows: int, n_cols: int, paths: SnarlPaths, y, rank: int, world: int,
+                                    group=None, thresholds=(3, 5, 0.05)) -> dict:
+    """One rank's part of a sample-sharded quantitative run (every rank returns the full result).
+
+    moments of the local columns (K3M: per snarl 7 class counts + 3 phenotype sums) -> ONE all-reduce -> filters and OLS
+    on the sums (K4).  Snarls that need more than the two-path sums (other shapes, rank-deficient or near-perfect
+    fits: a few per cent) come back deferred; their rows are re-assembled from all ranks' column slices and replayed
+    through the ordinary batch call, replicated."""
+    import torch.distributed as dist
+
+    ranges = plan_column_shards(n_cols, world)
+    c0, c1 = ranges[rank]
+    if c1 <= c0:
+        raise ValueError("sample-sharded run needs at least 128 columns per rank")
+    mi, mh, maf = thresholds
+    yy = np.asarray(y, dtype=np.float64)
+    mean, s1, s2, vmax = phenotype_summary(yy)
+    local = split_columns(bits, n_rows, n_cols, c0, c1)
+    ctx.set_matrix(local, n_rows, c1 - c0)
+    ctx.set_quantitative_phenotype_shard(yy[c0 // 2:c1 // 2], mean, s1, s2, vmax)
+    ctx.stage_paths(paths)
+    ctx.quantitative_moments_staged(mi, mh, maf)
+    if world > 1:
+        allreduce_partials_inplace(ctx, group)
+    ctx.quantitative_solve_staged(mi, mh, maf)
+    res = ctx.quantitative_fetch()
+    todo = deferred_snarls(res)
+    if todo.size == 0:
+        return res
+
+    def allgather(obj):
+        if world == 1:
+            return [obj]
+        out = [None] * world
+        dist.all_gather_object(out, obj, group=group)
+        return out
+
+    full_bits, full_rows, sub = gather_deferred_rows(local, n_rows, c1 - c0, paths, todo, ranges, allgather)
+    ctx.set_matrix(full_bits, full_rows, n_cols)
+    ctx.set_quantitative_phenotype(yy)
+    replay = ctx.quantitative_batch(sub, mi, mh, maf)
+    return merge_deferred(res, todo, replay, paths)

@@ -35,7 +35,7 @@ def test_repack_rows(gpu_ctx, oracle, n_cols):
     bits = oracle.pack_matrix(dense)
     gpu_ctx.set_matrix(bits, n_rows, n_cols)
     pitch = gpu_ctx.row_pitch
-    assert pitch == ((n_cols + 127) // 128) * 16
+    assert pitch == ((n_cols + 255) // 256) * 32
     for r in (0, 1, 17, n_rows - 1):
         row = gpu_ctx.read_row(r)
         got = np.unpackbits(row, bitorder="little")

@@ -125,3 +125,82 @@ def test_synthetic_generator_and_staged_mode(gpu_ctx, oracle):
         np.testing.assert_array_equal(got[k], again[k], err_msg=k)
     for k in ("p_value", "beta", "se", "r2"):
         np.testing.assert_array_equal(np.nan_to_num(got[k], nan=-7.0), np.nan_to_num(again[k], nan=-7.0), err_msg=k)
+
+
+def _two_path_problem(rng, n_snarls, n_samples, frac_missing, overlap_every=0):
+    """Two-path snarls with 1 or 2 checked edges per path; some haplotypes on neither path; every `overlap_every`-th
+    snarl has haplotypes on BOTH paths (row sums of 3: dosages 1/3, 2/3, which the integer kernel hands on)."""
+    Hn = 2 * n_samples
+    dense = np.zeros((4 * n_snarls, Hn), dtype=bool)
+    snarls = []
+    for s in range(n_snarls):
+        f = rng.uniform(0.05, 0.95)
+        alt = rng.random(Hn) < f
+        present = rng.random(Hn) >= frac_missing
+        r = 4 * s
+        dense[r] = dense[r + 1] = present & ~alt
+        dense[r + 2] = dense[r + 3] = present & alt
+        if overlap_every and s % overlap_every == 0:
+            both = rng.random(Hn) < 0.02
+            dense[r] |= both
+            dense[r + 1] |= both
+            dense[r + 2] |= both
+            dense[r + 3] |= both
+        e0 = [r, r + 1] if s % 3 else [r]
+        e1 = [r + 2, r + 3] if s % 5 else [r + 3]
+        snarls.append([e0, e1])
+    return dense, snarls
+
+
+@pytest.mark.parametrize("seed,n_samples,frac_missing,overlap", [(21, 700, 0.01, 0), (22, 1300, 0.45, 0),
+                                                                (23, 500, 0.02, 7), (24, 7000, 0.01, 0)])
+def test_two_path_integer_contraction(gpu_ctx, oracle, seed, n_samples, frac_missing, overlap):
+    """K3M (csrc/quant_mma.cuh): X^T y as an exact int8 MMA over 8 phenotype slices.  Cases: plain; nearly half of the
+    haplotypes on neither path (the FP64 side sums over unused samples); overlapping paths (replay on the general
+    path); 14,000 haplotypes = 28 rounds > 24, i.e. two haplotype slices whose partial sums K4 adds."""
+    rng = np.random.default_rng(seed)
+    dense, snarls = _two_path_problem(rng, 96 if n_samples >= 7000 else 330, n_samples, frac_missing, overlap)
+    y = rng.normal(size=n_samples) * 2.5 - 40.0
+    y = y + 0.8 * dense[snarls[1][0][0]].reshape(n_samples, 2).sum(1)
+    got, ref = run_both(gpu_ctx, oracle, dense, snarls, y, min_ind=2, min_hap=2, maf=0.01)
+    H.assert_quant_equal(got, ref)
+    assert (ref["filtered"] == 0).sum() > 20
+
+
+def test_two_path_integer_contraction_phenotype_range(gpu_ctx, oracle):
+    """The slice split uses ONE fixed-point scale for the whole phenotype: a heavy-tailed phenotype (values from 1e-7 to
+    1e5) must still give 1e-9 parity, and a constant phenotype (all slices zero) the reference's degenerate rows."""
+    rng = np.random.default_rng(31)
+    n = 900
+    dense, snarls = _two_path_problem(rng, 200, n, 0.01)
+    y = np.exp(rng.normal(size=n) * 4.0) * np.sign(rng.normal(size=n))
+    got, ref = run_both(gpu_ctx, oracle, dense, snarls, y, min_ind=2, min_hap=2, maf=0.01)
+    H.assert_quant_equal(got, ref)
+    y0 = np.full(n, 3.25)
+    got, ref = run_both(gpu_ctx, oracle, dense, snarls[:40], y0, min_ind=2, min_hap=2, maf=0.01)
+    np.testing.assert_array_equal(got["filtered"], ref["filtered"])
+    np.testing.assert_array_equal(got["allele_paths"], ref["allele_paths"])
+
+
+def test_sample_sharded_phases_single_gpu(gpu_ctx, oracle):
+    """moments | (all-reduce) | solve on ONE GPU (world 1): the phase split, the deferred marking of snarls that need more
+    than the two-path sums and their replay (stoat_b200/shard.py) must reproduce the ordinary batch call."""
+    from stoat_b200 import shard, synth
+
+    d = synth.numpy_dataset(1500, 448, seed=12, frac_missing_edge=0.02)
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    ref = oracle.quantitative_batch(d["bits"], d["n_cols"], d["y"], P)
+    got = shard.run_quantitative_sample_sharded(gpu_ctx, d["bits"], d["n_rows"], d["n_cols"], d["paths"], d["y"], 0, 1)
+    H.assert_quant_equal(got, ref)
+    # the deferred set is what the two-path kernel does not take: here the three-path snarls at least
+    gpu_ctx.set_matrix(d["bits"], d["n_rows"], d["n_cols"])
+    gpu_ctx.set_quantitative_phenotype_shard(d["y"], *shard.phenotype_summary(d["y"]))
+    gpu_ctx.stage_paths(d["paths"])
+    gpu_ctx.quantitative_moments_staged()
+    pi, ni, pd, nd = gpu_ctx.quantitative_partials_dev()
+    assert ni == 7 * d["paths"].n_snarls and nd == 3 * d["paths"].n_snarls and pi and pd
+    gpu_ctx.quantitative_solve_staged()
+    res = gpu_ctx.quantitative_fetch()
+    todo = shard.deferred_snarls(res)
+    n_paths = np.diff(d["paths"].snarl_path_off.astype(np.int64))
+    assert set(np.flatnonzero(n_paths != 2)) <= set(todo) and todo.size < d["paths"].n_snarls // 4

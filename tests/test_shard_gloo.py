@@ -91,6 +91,22 @@ def _worker(rank, world, port, mode, out_path):
             dist.gather_object(part, gathered, dst=0)  # host merge only: no data-path collective
             if rank == 0:
                 np.savez(out_path, **shard.merge_snarl_results(gathered))
+        elif mode == "deferred":
+            # the replay step of the sample-sharded quantitative run: whole rows of a few snarls rebuilt from every
+            # rank's column slice (all_gather_object), edge_row remapped to the compact matrix
+            ranges = shard.plan_column_shards(n_cols, world)
+            c0, c1 = ranges[rank]
+            local = shard.split_columns(bits, n_rows, n_cols, c0, c1)
+            todo = np.array([2, 3, 7, 9, 31, 58])
+
+            def allgather(obj):
+                out = [None] * world
+                dist.all_gather_object(out, obj)
+                return out
+
+            fb, fr, sub = shard.gather_deferred_rows(local, n_rows, c1 - c0, paths, todo, ranges, allgather)
+            if rank == 1:
+                np.savez(out_path, bits=fb, n_rows=fr, spo=sub.snarl_path_off, peo=sub.path_edge_off, er=sub.edge_row)
         else:
             c0, c1 = shard.plan_column_shards(n_cols, world)[rank]
             local = shard.split_columns(bits, n_rows, n_cols, c0, c1)
@@ -133,3 +149,40 @@ def test_sample_sharded_world2_counts_allreduce(oracle, tmp_path):
         g0 = got["g0"][spo[s]:spo[s + 1]].astype(np.uint64)
         g1 = got["g1"][spo[s]:spo[s + 1]].astype(np.uint64)
         assert int((g0 + g1).sum()) == int(full["total_sum"][s])
+
+
+def test_deferred_rows_reassembled_world2(oracle, tmp_path):
+    """Sample-sharded quantitative run, replay step: the compact full-width matrix + sub-batch built from two ranks'
+    column slices gives, snarl by snarl, what the whole matrix gives (oracle as the compute)."""
+    got = _spawn("deferred", tmp_path)
+    bits, n_rows, n_cols, paths, _ = _problem()
+    todo = np.array([2, 3, 7, 9, 31, 58])
+    rng = np.random.default_rng(3)
+    y = rng.normal(size=n_cols // 2)
+    full = oracle.quantitative_batch(bits, n_cols, y, oracle.Paths(paths.snarl_path_off, paths.path_edge_off, paths.edge_row),
+                                     min_ind=2, min_hap=2, maf=0.01)
+    part = oracle.quantitative_batch(got["bits"], n_cols, y, oracle.Paths(got["spo"], got["peo"], got["er"]),
+                                     min_ind=2, min_hap=2, maf=0.01)
+    for k in ("filtered", "n_used", "code"):
+        np.testing.assert_array_equal(part[k], full[k][todo], err_msg=k)
+    for k in ("p_value", "beta", "se", "r2"):
+        np.testing.assert_array_equal(np.nan_to_num(part[k], nan=-7.0), np.nan_to_num(full[k][todo], nan=-7.0), err_msg=k)
+    merged = shard.merge_deferred({k: np.zeros_like(v) for k, v in full.items() if k != "seconds"}, todo,
+                                  {k: v for k, v in part.items() if k != "seconds"}, paths)
+    spo = paths.snarl_path_off.astype(np.int64)
+    for s in todo:
+        np.testing.assert_array_equal(merged["allele_paths"][spo[s]:spo[s + 1]], full["allele_paths"][spo[s]:spo[s + 1]])
+        assert merged["n_used"][s] == full["n_used"][s]
+
+
+def test_phenotype_summary_matches_library_definition():
+    rng = np.random.default_rng(8)
+    y = rng.normal(size=777) * 5 + 100
+    mean, s1, s2, vmax = shard.phenotype_summary(y)
+    assert abs(mean - y.mean()) < 1e-12 and abs(s1) < 1e-9
+    assert abs(s2 - ((y - mean) ** 2).sum()) < 1e-9 * s2 and vmax == np.abs(y - mean).max()
+    sel = shard.select_snarls(_problem()[3], np.array([5, 1]))
+    full = _problem()[3]
+    spo, peo = full.snarl_path_off.astype(np.int64), full.path_edge_off.astype(np.int64)
+    assert sel.n_snarls == 2 and sel.n_paths == (spo[6] - spo[5]) + (spo[2] - spo[1])
+    np.testing.assert_array_equal(sel.edge_row[: peo[spo[6]] - peo[spo[5]]], full.edge_row[peo[spo[5]]:peo[spo[6]]])
