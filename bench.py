@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--snarls", type=int, default=1_000_000, help="snarls per GPU")
     ap.add_argument("--samples", type=int, default=5_000, help="samples (haplotypes = 2x)")
+    ap.add_argument("--seed", type=int, default=42, help="generator seed of rank 0 (rank r draws seed + r)")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -342,7 +343,7 @@ def main():
         torch.cuda.synchronize()
 
     # ---- data: drawn on the device, one independent shard per rank (weak scaling) ------------------
-    d = synth.torch_dataset(args.snarls, args.samples, dev, seed=42 + rank)
+    d = synth.torch_dataset(args.snarls, args.samples, dev, seed=args.seed + rank)
     paths = d["paths"]
     S, P = paths.n_snarls, paths.n_paths
     ctx = stoat_b200.Context(local)
@@ -378,6 +379,9 @@ def main():
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     elapsed_ms = e0.elapsed_time(e1)
+    if os.environ.get("STOAT_BENCH_DEBUG"):
+        print(f"[rank {rank}] elapsed {elapsed_ms:.3f} ms over {args.steps} steps; kernels {np.sum(k1_ms) + np.sum(k2_ms):.3f} ms; "
+              f"per step table {np.round(k1_ms, 3).tolist()} stats {np.round(k2_ms, 3).tolist()}", file=sys.stderr, flush=True)
     t_max = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
     launches_t = torch.tensor([launches], dtype=torch.float64, device=dev)
     if world > 1:

@@ -454,7 +454,7 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
     if (s >= n_snarls) return;
     const uint8_t state = mom[s].state;
     auto hand_on = [&]() {
-        if (defer) {
+        if (defer & 1u) {
             out.code[s] = kPDeferred;
             out.filtered[s] = 0;
         } else {
@@ -463,7 +463,7 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
         }
     };
     if (state != 1 && state != 2) {
-        if (defer) hand_on();
+        if (defer & 1u) hand_on();
         return;
     }
     QuantMoments m;
@@ -699,9 +699,19 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         p.mom = mom;
         p.g_list = b.big_list;
         p.g_count = b.counters;
-        e = cudaFuncSetAttribute(dosage_moments_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 int(cfg.smem_bytes));
-        if (e != cudaSuccess) return e;
+        {
+            static thread_local int k3_dev = -1;
+            static thread_local uint32_t k3_smem = 0;
+            int dev_now = 0;
+            cudaGetDevice(&dev_now);
+            if (dev_now != k3_dev || cfg.smem_bytes != k3_smem) {
+                e = cudaFuncSetAttribute(dosage_moments_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         int(cfg.smem_bytes));
+                if (e != cudaSuccess) return e;
+                k3_dev = dev_now;
+                k3_smem = cfg.smem_bytes;
+            }
+        }
         K3RPlan pl;
         LeanPartials part{part_i, part_d, b.n_snarls};
         uint32_t n_slices = 0;
@@ -733,13 +743,24 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             if ((e = cudaMemsetAsync(b.counters + 3, 0, 4, st)) != cudaSuccess) return e;
             lean_rec_kernel<<<unsigned((b.n_snarls + 255) / 256), 256, 0, st>>>(b.rec, b.blob, b.n_snarls, lean_rec);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
-            e = cudaFuncSetAttribute(dosage_moments_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     int(pm.smem_bytes));
-            if (e != cudaSuccess) return e;
-            int occ = 1;
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, dosage_moments_mma_kernel, kMmaWarps * 32,
-                                                              pm.smem_bytes) != cudaSuccess || occ < 1)
-                occ = 1;
+            // attribute + occupancy query once per (device, shared-memory size): they are driver calls, not free per step
+            static thread_local int cached_dev = -1, cached_occ = 1;
+            static thread_local uint32_t cached_smem = 0;
+            int dev_now = 0;
+            cudaGetDevice(&dev_now);
+            if (dev_now != cached_dev || pm.smem_bytes != cached_smem) {
+                e = cudaFuncSetAttribute(dosage_moments_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         int(pm.smem_bytes));
+                if (e != cudaSuccess) return e;
+                int o = 1;
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, dosage_moments_mma_kernel, kMmaWarps * 32,
+                                                                  pm.smem_bytes) != cudaSuccess || o < 1)
+                    o = 1;
+                cached_dev = dev_now;
+                cached_smem = pm.smem_bytes;
+                cached_occ = o;
+            }
+            int occ = cached_occ;
             const int occ_env = env_int("STOAT_GPU_K3M_CTAS", 0);
             if (occ_env >= 1 && occ_env < occ) occ = occ_env;
             const uint64_t n_tiles = (b.n_snarls + kMmaTile - 1) / kMmaTile;
