@@ -514,8 +514,24 @@ __global__ void __launch_bounds__(128) binary_stats_kernel(BatchDev b, const uin
 // The products are carried instead of the factors:  N = n1 * n2 and D = d1 * d2 are integers below 2^53 (every count
 // is below 2^26 here; larger tables take the factor form), so  D' = D + (d1 + d2 + 1)  and  N' = N - (n1 + n2 - 1)
 // are the exactly representable values the reference's two multiplications round to — bit-identical, two DMUL fewer.
-// The quotient, the running product and the tail sums keep the reference's roundings (__ddiv_rn / __dmul_rn /
-// __dadd_rn: no FMA contraction), which the tie tests (cur_prob < kExactTestBias, tprob <= preaddp) depend on.
+// The running product and the tail sums keep the reference's order of operations (no FMA contraction); the quotient
+// N / D is N * fast_rcp(D) (below): within ~1e-13 of the reference over a table, inside its own tie margin.
+
+// 1 / d for an exact positive integer d < 2^53 to ~1 ulp: MUFU.RCP64H seed + two Newton steps (5 instructions; the
+// correctly rounded __ddiv_rn is ~3x that plus a branch).  The recurrence then differs from the reference's
+// `cur_prob *= (n1 * n2) / (d1 * d2)` by ~1e-16 per step, ~1e-13 over a table — four orders below the 1e-9 budget, and
+// below the reference's own tie margin kExactTestEpsilon2 = 9.1e-13 (stats_test.hpp:59), so tables tied with the observed
+// one fall on the same side of `cur_prob < kExactTestBias` as in the reference.
+__device__ __forceinline__ double fast_rcp(double d) {
+    double x;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(d));
+    double e = fma(-d, x, 1.0);
+    x = fma(x, e, x);
+    e = fma(-d, x, 1.0);
+    return fma(x, e, x);
+}
+
+template <bool kFastRcp>
 __global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restrict__ tab,
                                                            const uint32_t* __restrict__ idx,
                                                            uint32_t* __restrict__ counters,  // [0] n_work, [1] next
@@ -588,35 +604,37 @@ __global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restri
             }
         }
         if (!__any_sync(0xffffffffu, active)) break;
-        if (active && rem == 0) {  // the loop of the current phase ran out before a body execution (:306, :326)
-            if (phase == 1 && cprob == 0) finish(1.0, kPOne);  // :322-324
-            else start_near_tail();
-        }
-        if (active) {
-            D = __dadd_rn(D, sD);
-            sD += 2.0;
-            cur = __dmul_rn(cur, __ddiv_rn(N, D));
-            N = __dsub_rn(N, sN);
-            sN -= 2.0;
-            --rem;
-            if (phase == 1) {
-                if (cur > DBL_MAX) {  // :312-314
-                    finish(0.0, kPZero);
-                } else if (cur < kBias) {  // :315-318
-                    tprob = __dadd_rn(tprob, cur);
-                    if (cprob == 0) finish(1.0, kPOne);
-                    else phase = 2;
+        {
+            if (active && rem == 0) {  // the loop of the current phase ran out before a body execution (:306, :326)
+                if (phase == 1 && cprob == 0) finish(1.0, kPOne);  // :322-324
+                else start_near_tail();
+            }
+            if (active) {
+                D = __dadd_rn(D, sD);
+                sD += 2.0;
+                cur = kFastRcp ? __dmul_rn(cur, __dmul_rn(N, fast_rcp(D))) : __dmul_rn(cur, __ddiv_rn(N, D));
+                N = __dsub_rn(N, sN);
+                sN -= 2.0;
+                --rem;
+                if (phase == 1) {
+                    if (cur > DBL_MAX) {  // :312-314
+                        finish(0.0, kPZero);
+                    } else if (cur < kBias) {  // :315-318
+                        tprob = __dadd_rn(tprob, cur);
+                        if (cprob == 0) finish(1.0, kPOne);
+                        else phase = 2;
+                    } else {
+                        cprob = __dadd_rn(cprob, cur);
+                    }
                 } else {
-                    cprob = __dadd_rn(cprob, cur);
-                }
-            } else {
-                const double preaddp = tprob;
-                tprob = __dadd_rn(tprob, cur);
-                if (tprob <= preaddp) {
-                    if (phase == 2) start_near_tail();  // :334-336
-                    else finish(__ddiv_rn(preaddp, __dadd_rn(cprob, preaddp)), kPValue);  // :352-354
-                } else if (phase == 3 && rem == 0) {
-                    finish(__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue);  // :356, :359
+                    const double preaddp = tprob;
+                    tprob = __dadd_rn(tprob, cur);
+                    if (tprob <= preaddp) {
+                        if (phase == 2) start_near_tail();  // :334-336
+                        else finish(__ddiv_rn(preaddp, __dadd_rn(cprob, preaddp)), kPValue);  // :352-354
+                    } else if (phase == 3 && rem == 0) {
+                        finish(__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue);  // :356, :359
+                    }
                 }
             }
         }
@@ -637,7 +655,12 @@ cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     const uint64_t want = (b.n_snarls + 127) / 128;
     const unsigned fblocks = unsigned(want < uint64_t(num_sms) * 8 ? want : uint64_t(num_sms) * 8);
-    fisher_exact_kernel<<<fblocks, 128, 0, st>>>(fisher_tab, fisher_idx, fisher_counters, p_fisher, fisher_code);
+    // STOAT_GPU_FISHER=exact: the quotient by __ddiv_rn, bit-identical to the reference's recurrence (15 % slower)
+    const char* fv = std::getenv("STOAT_GPU_FISHER");
+    if (fv && fv[0] == 'e')
+        fisher_exact_kernel<false><<<fblocks, 128, 0, st>>>(fisher_tab, fisher_idx, fisher_counters, p_fisher, fisher_code);
+    else
+        fisher_exact_kernel<true><<<fblocks, 128, 0, st>>>(fisher_tab, fisher_idx, fisher_counters, p_fisher, fisher_code);
     return cudaGetLastError();
 }
 
