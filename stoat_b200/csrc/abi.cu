@@ -57,12 +57,16 @@ struct QuantState {
 
 }  // namespace
 
+constexpr int kMaxRunChunks = 8;  // chunks of an overlapped binary run (stoat_gpu_binary_run_staged)
+
 // extra per-context state that does not need to be visible to the kernel translation units
 struct CtxExtra {
     QuantState q;
     uint32_t max_stage_rows = 0;
     uint32_t counters_host[4] = {0, 0, 0, 0};
     uint32_t readback[2] = {0, 0};
+    uint32_t fisher_readback[2 * kMaxRunChunks] = {};
+    cudaEvent_t chunk_done[kMaxRunChunks] = {};
 };
 static CtxExtra* extra_of(stoat_gpu_ctx* ctx);
 
@@ -109,6 +113,16 @@ int stoat_gpu_create(stoat_gpu_ctx** out, int device) {
             delete full;
             return fail_cuda(nullptr, e, "cudaEventCreate");
         }
+    // second stream + hand-over events of the overlapped binary run (stoat_gpu_binary_run_staged)
+    if ((e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        delete full;
+        return fail_cuda(nullptr, e, "cudaStreamCreate");
+    }
+    for (auto& ev : full->extra.chunk_done)
+        if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) {
+            delete full;
+            return fail_cuda(nullptr, e, "cudaEventCreate");
+        }
     const char* k1 = std::getenv("STOAT_GPU_K1");
     ctx->k1_variant = (k1 && std::strcmp(k1, "ldg") == 0) ? 1 : 0;
     const char* eq = std::getenv("STOAT_GPU_EQTL");
@@ -121,6 +135,7 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
     DevBuf* bufs[] = {&ctx->rows, &ctx->raw_stage[0], &ctx->raw_stage[1], &ctx->case_mask, &ctx->is_case_dev, &ctx->y,
                       &ctx->covar, &ctx->d_snarl_path_off, &ctx->d_path_edge_off, &ctx->d_edge_row, &ctx->d_rec,
                       &ctx->d_blob, &ctx->d_big, &ctx->d_counters, &ctx->counts, &ctx->total_sum, &ctx->filtered,
@@ -139,6 +154,9 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     x->q.lean_rec.release();
     for (auto& ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);
+    for (auto& ev : x->chunk_done)
+        if (ev) cudaEventDestroy(ev);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete static_cast<stoat_gpu_ctx_full*>(ctx);
 }
@@ -408,7 +426,7 @@ static int binary_reserve(stoat_gpu_ctx* ctx) {
     CK(ctx->code_b.reserve(std::max<uint64_t>(b.n_snarls, 16)));
     CK(ctx->fisher_tab.reserve(std::max<uint64_t>(b.n_snarls * 16, 16)));
     CK(ctx->fisher_idx.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
-    CK(ctx->fisher_cnt.reserve(16));
+    CK(ctx->fisher_cnt.reserve(8 * kMaxRunChunks));  // a pair of work-list counters per chunk of an overlapped run
     return STOAT_GPU_OK;
 }
 
@@ -457,13 +475,61 @@ int stoat_gpu_binary_stats_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds
 }
 
 int stoat_gpu_binary_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr) {
-    int rc = stoat_gpu_binary_counts_staged(ctx);
-    if (rc) return rc;
-    rc = stoat_gpu_binary_stats_staged(ctx, thr);
+    if (!ctx || !thr) return fail(ctx, STOAT_GPU_ERR_ARG, "binary: NULL argument");
+    if (!ctx->have_batch) return fail(ctx, STOAT_GPU_ERR_STATE, "binary: no staged batch");
+    if (!ctx->have_binary) return fail(ctx, STOAT_GPU_ERR_STATE, "binary: no binary phenotype");
+    CK(cudaSetDevice(ctx->device));
+    int rc = binary_reserve(ctx);
     if (rc) return rc;
     CtxExtra* x = extra_of(ctx);
-    CK(cudaMemcpyAsync(x->readback, ctx->fisher_cnt.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
+    const uint64_t S = ctx->batch.n_snarls;
+    // The count pass (K1) is HBM bound and leaves the FP64 pipe idle, the Fisher work list (K2b) is the opposite, so the run
+    // CAN be cut into chunks of snarls with K1 of chunk c + 1 (main stream) overlapping K2a / K2b of chunk c (second
+    // stream): STOAT_GPU_OVERLAP=<chunks>.  Measured on B200 at C3 it does not pay — 1.94 ms back to back, 2.09 / 2.35 /
+    // 2.75 ms with 2 / 4 / 8 chunks: K1 is a persistent kernel that takes all of an SM's shared memory, the Fisher blocks
+    // hold the registers its next launch needs, and every chunk adds two kernel tails — so the default is one chunk.
+    int n_chunks = 1;
+    if (S >= 65536) {
+        if (const char* e = std::getenv("STOAT_GPU_OVERLAP")) {
+            const int v = std::atoi(e);
+            n_chunks = v <= 1 ? 1 : (v > kMaxRunChunks ? kMaxRunChunks : v);
+        }
+    }
+    ctx->timing.launches = 0;
+    const uint64_t per = (S + uint64_t(n_chunks) - 1) / uint64_t(n_chunks);
+    cudaStream_t main_st = ctx->stream, side_st = n_chunks > 1 ? ctx->copy_stream : ctx->stream;
+    CK(cudaEventRecord(ctx->ev[2], main_st));
+    for (int c = 0; c < n_chunks && S; ++c) {
+        const uint64_t s0 = per * uint64_t(c);
+        if (s0 >= S) break;
+        const uint64_t cnt = std::min<uint64_t>(per, S - s0);
+        CK(launch_path_and_popc(matrix_view(ctx), ctx->case_mask.as<uint8_t>(), ctx->n_case_hap, ctx->batch, ctx->n_big,
+                                x->max_stage_rows, ctx->counts.as<uint32_t>(), ctx->num_sms, ctx->k1_variant, main_st,
+                                &ctx->timing.launches, s0, cnt));
+        if (n_chunks > 1) {
+            CK(cudaEventRecord(x->chunk_done[c], main_st));
+            CK(cudaStreamWaitEvent(side_st, x->chunk_done[c], 0));
+        } else {
+            CK(cudaEventRecord(ctx->ev[3], main_st));
+        }
+        if (c == 0) CK(cudaEventRecord(ctx->ev[4], side_st));
+        CK(launch_binary_stats(ctx->batch, ctx->counts.as<uint32_t>(), *thr, ctx->total_sum.as<uint64_t>(),
+                               ctx->filtered.as<uint8_t>(), ctx->p_a.as<double>(), ctx->p_b.as<double>(),
+                               ctx->code_a.as<uint8_t>(), ctx->code_b.as<uint8_t>(), ctx->fisher_tab.as<uint4>(),
+                               ctx->fisher_idx.as<uint32_t>(), ctx->fisher_cnt.as<uint32_t>() + 2 * c, ctx->num_sms,
+                               side_st, s0, cnt));
+        ctx->timing.launches += 2;
+    }
+    if (n_chunks > 1) CK(cudaEventRecord(ctx->ev[3], main_st));  // end of the last count pass
+    CK(cudaEventRecord(ctx->ev[5], side_st));
+    if (n_chunks > 1) CK(cudaStreamWaitEvent(main_st, ctx->ev[5], 0));
+    ctx->have_binary_counts = true;
+    ctx->have_binary_result = true;
+    CK(cudaMemcpyAsync(x->fisher_readback, ctx->fisher_cnt.p, 8 * kMaxRunChunks, cudaMemcpyDeviceToHost, main_st));
+    CK(cudaStreamSynchronize(main_st));
+    uint32_t n_fisher = 0;
+    for (int c = 0; c < n_chunks; ++c) n_fisher += x->fisher_readback[2 * c];
+    x->readback[0] = n_fisher;
     ctx->timing.n_general = ctx->n_big;
     ctx->timing.n_fisher = ctx->batch.n_snarls ? x->readback[0] : 0;
     CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));

@@ -81,11 +81,13 @@ cudaError_t launch_build_case_mask(const uint8_t* is_case, uint64_t n_samples, u
 cudaError_t launch_binary_prep(const BatchDev& b, uint64_t n_matrix_rows, cudaStream_t st);
 cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, uint32_t n_case_hap, const BatchDev& b,
                                  uint32_t n_big, uint32_t max_stage_rows, uint32_t* counts, int num_sms, int variant,
-                                 cudaStream_t st, uint32_t* launches);
+                                 cudaStream_t st, uint32_t* launches, uint64_t s_begin = 0,
+                                 uint64_t s_count = ~uint64_t(0));
 cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const stoat_gpu_thresholds& thr,
                                 uint64_t* total_sum, uint8_t* filtered, double* p_chi2, double* p_fisher,
                                 uint8_t* chi2_code, uint8_t* fisher_code, uint4* fisher_tab, uint32_t* fisher_idx,
-                                uint32_t* fisher_counters, int num_sms, cudaStream_t st);
+                                uint32_t* fisher_counters, int num_sms, cudaStream_t st, uint64_t s_begin = 0,
+                                uint64_t s_count = ~uint64_t(0));
 // quantitative
 struct QuantMoments;  // kernels_quant.cu
 struct QuantOut {

@@ -371,8 +371,13 @@ static bool choose_k1_config(uint32_t pitch, uint32_t stage_rows, K1Config& cfg)
 
 cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, uint32_t n_case_hap,
                                      const BatchDev& b, uint32_t n_big, uint32_t max_stage_rows, uint32_t* counts,
-                                     int num_sms, int variant, cudaStream_t st, uint32_t* launches) {
-    if (b.n_snarls == 0) return cudaSuccess;
+                                     int num_sms, int variant, cudaStream_t st, uint32_t* launches, uint64_t s_begin,
+                                     uint64_t s_count) {
+    // [s_begin, s_begin + s_count): the snarls of this launch (the run is cut into chunks so that the statistics of a chunk
+    // overlap the count pass of the next one, abi.cu); snarls on the LDG list are done with the first chunk
+    if (b.n_snarls == 0 || s_count == 0) return cudaSuccess;
+    if (s_begin >= b.n_snarls) return cudaSuccess;
+    if (s_count > b.n_snarls - s_begin) s_count = b.n_snarls - s_begin;
     uint32_t* g0 = counts;
     uint32_t* g1 = counts + b.n_paths;
     const uint32_t pitch = uint32_t(m.pitch);
@@ -382,11 +387,11 @@ cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, u
         K1Params p{};
         p.rows = m.rows;
         p.case_mask = case_mask;
-        p.rec = b.rec;
+        p.rec = b.rec + s_begin;
         p.blob = b.blob;
         p.g0 = g0;
         p.g1 = g1;
-        p.n_snarls = b.n_snarls;
+        p.n_snarls = s_count;
         p.pitch = pitch;
         p.n_hap = uint32_t(m.n_cols);
         p.n_case_hap = n_case_hap;
@@ -395,13 +400,13 @@ cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, u
         cudaError_t e = cudaFuncSetAttribute(path_and_popc_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              int(cfg.smem_bytes));
         if (e != cudaSuccess) return e;
-        uint64_t want = (b.n_snarls + cfg.n_warps - 1) / cfg.n_warps;
+        uint64_t want = (s_count + cfg.n_warps - 1) / cfg.n_warps;
         const unsigned grid = unsigned(want < uint64_t(num_sms) ? want : uint64_t(num_sms));
         path_and_popc_tma_kernel<<<grid, cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;
-        if (n_big) {
+        if (n_big && s_begin == 0) {
             const unsigned blocks = unsigned(n_big < 148u * 8 ? (n_big + 7) / 8 : 148u * 8);
             path_and_popc_ldg_kernel<<<blocks, 256, 0, st>>>(m.rows, case_mask, pitch, uint32_t(m.n_cols), n_case_hap,
                                                              b, b.big_list, n_big, g0, g1);
@@ -411,6 +416,7 @@ cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, u
         }
         return cudaSuccess;
     }
+    if (s_begin != 0) return cudaSuccess;  // LDG-only variant: everything went with the first chunk
     const uint64_t want = (b.n_snarls + 7) / 8;
     const unsigned blocks = unsigned(want < 148ull * 16 ? want : 148ull * 16);
     path_and_popc_ldg_kernel<<<blocks, 256, 0, st>>>(m.rows, case_mask, pitch, uint32_t(m.n_cols), n_case_hap, b,
@@ -436,12 +442,13 @@ __global__ void __launch_bounds__(128) binary_stats_kernel(BatchDev b, const uin
                                                            uint8_t* __restrict__ fisher_code,
                                                            uint4* __restrict__ fisher_tab,
                                                            uint32_t* __restrict__ fisher_idx,
-                                                           uint32_t* __restrict__ fisher_cnt) {
-    const uint64_t s = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+                                                           uint32_t* __restrict__ fisher_cnt, uint64_t s_begin,
+                                                           uint64_t s_end) {
+    const uint64_t s = s_begin + uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31;
     bool want_fisher = false;
     uint64_t c0[2] = {0, 0}, c1[2] = {0, 0};  // first two non-empty columns (the 2x2 case)
-    if (s < b.n_snarls) {
+    if (s < s_end) {
         const uint64_t p0 = b.snarl_path_off[s], p1 = b.snarl_path_off[s + 1];
         // pass 1 over the columns: totals, compaction count, MAF count (snarl_analyzer.cpp:686-732)
         uint64_t tot = 0, row0 = 0, row1 = 0;
@@ -641,26 +648,33 @@ __global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restri
     }
 }
 
+// statistics of the snarls [s_begin, s_begin + s_count); the Fisher work list of the range lives at fisher_tab / fisher_idx
+// + s_begin (at most one table per snarl) with its own pair of counters
 cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const stoat_gpu_thresholds& thr,
                                 uint64_t* total_sum, uint8_t* filtered, double* p_chi2, double* p_fisher,
                                 uint8_t* chi2_code, uint8_t* fisher_code, uint4* fisher_tab, uint32_t* fisher_idx,
-                                uint32_t* fisher_counters, int num_sms, cudaStream_t st) {
-    if (b.n_snarls == 0) return cudaSuccess;
+                                uint32_t* fisher_counters, int num_sms, cudaStream_t st, uint64_t s_begin,
+                                uint64_t s_count) {
+    if (b.n_snarls == 0 || s_count == 0) return cudaSuccess;
+    if (s_begin >= b.n_snarls) return cudaSuccess;
+    if (s_count > b.n_snarls - s_begin) s_count = b.n_snarls - s_begin;
     cudaError_t e = cudaMemsetAsync(fisher_counters, 0, 8, st);
     if (e != cudaSuccess) return e;
-    const unsigned blocks = unsigned((b.n_snarls + 127) / 128);
+    const unsigned blocks = unsigned((s_count + 127) / 128);
     binary_stats_kernel<<<blocks, 128, 0, st>>>(b, counts, counts + b.n_paths, thr, total_sum, filtered, p_chi2,
-                                                p_fisher, chi2_code, fisher_code, fisher_tab, fisher_idx,
-                                                fisher_counters);
+                                                p_fisher, chi2_code, fisher_code, fisher_tab + s_begin,
+                                                fisher_idx + s_begin, fisher_counters, s_begin, s_begin + s_count);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    const uint64_t want = (b.n_snarls + 127) / 128;
+    const uint64_t want = (s_count + 127) / 128;
     const unsigned fblocks = unsigned(want < uint64_t(num_sms) * 8 ? want : uint64_t(num_sms) * 8);
     // STOAT_GPU_FISHER=exact: the quotient by __ddiv_rn, bit-identical to the reference's recurrence (15 % slower)
     const char* fv = std::getenv("STOAT_GPU_FISHER");
     if (fv && fv[0] == 'e')
-        fisher_exact_kernel<false><<<fblocks, 128, 0, st>>>(fisher_tab, fisher_idx, fisher_counters, p_fisher, fisher_code);
+        fisher_exact_kernel<false><<<fblocks, 128, 0, st>>>(fisher_tab + s_begin, fisher_idx + s_begin, fisher_counters,
+                                                            p_fisher, fisher_code);
     else
-        fisher_exact_kernel<true><<<fblocks, 128, 0, st>>>(fisher_tab, fisher_idx, fisher_counters, p_fisher, fisher_code);
+        fisher_exact_kernel<true><<<fblocks, 128, 0, st>>>(fisher_tab + s_begin, fisher_idx + s_begin, fisher_counters,
+                                                           p_fisher, fisher_code);
     return cudaGetLastError();
 }
 
