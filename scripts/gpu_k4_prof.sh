@@ -1,0 +1,7 @@
+#!/bin/bash
+mkdir -p gpurun_out
+BQ1="python bench.py --trait quantitative --steps 1 --warmup 3 --no-cpu-baseline --no-e2e"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:ols_solve -s 3 -c 1 -f -o gpurun_out/prof_k4 $BQ1 > gpurun_out/ncu_k4.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:dosage_moments_tma -s 3 -c 1 -f -o gpurun_out/prof_k3slow $BQ1 > gpurun_out/ncu_k3slow.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:dosage_moments_mma -s 3 -c 1 -f -o gpurun_out/prof_k3m $BQ1 > gpurun_out/ncu_k3m.log 2>&1
+ls -la gpurun_out/*.ncu-rep

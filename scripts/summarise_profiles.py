@@ -110,8 +110,19 @@ def main():
     os.makedirs(PROF, exist_ok=True)
     for t in ("binary", "quant", "eqtl"):
         launches(tag, t)
-    for name in ("k1", "fisher", "stats", "k3", "general", "eqtl"):
+    for name in ("k1", "fisher", "stats", "k3", "k3m", "k4", "general", "eqtl"):
         vals = full(tag, name)
+        if name == "k3m" and vals:
+            raw = ncu_csv(os.path.join(OUT, "prof_k3m.ncu-rep"), "raw")
+            h, u, v = raw[0], raw[1], raw[2]
+
+            def nbytes3(key):
+                i = h.index(key)
+                scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u[i]]
+                return num(v[i]) * scale
+            tr = nbytes3("dram__bytes_read.sum") + nbytes3("dram__bytes_write.sum")
+            json.dump({"dram_bytes_per_launch": tr, "source": f"profiles/{tag}_k3m.txt (ncu --set full, one launch, "
+                       "bench.py --trait quantitative, C3 workload)"}, open(os.path.join(PROF, "k3m_traffic.json"), "w"))
         if name == "k1" and vals:
             raw = ncu_csv(os.path.join(OUT, "prof_k1.ncu-rep"), "raw")
             h, u, v = raw[0], raw[1], raw[2]

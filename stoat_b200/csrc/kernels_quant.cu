@@ -736,6 +736,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             q.y_scale = y_scale;
             q.rounds_per_slice = pm.rounds_per_slice;
             q.n_rounds = pm.n_rounds;
+            q.prefetch = env_int("STOAT_GPU_K3M_PREFETCH", 0) ? 1u : 0u;  // measured slower on B200 (1.54 vs 1.24 ms): off
             q.slow_list = slow_list;
             q.slow_count = b.counters + 3;
             q.part = part;

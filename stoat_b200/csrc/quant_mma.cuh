@@ -44,6 +44,7 @@ struct K3MParams {
     double y_scale;           // y = y_scale * sum_t q_t 128^-(t+1)
     uint32_t rounds_per_slice;  // blockIdx.y covers rounds [y * rounds_per_slice, ...)
     uint32_t n_rounds;          // ceil(chunks / 4)
+    uint32_t prefetch;          // 1: L2 prefetch of the rows four to eight rounds ahead
     uint32_t* slow_list;
     uint32_t* slow_count;
     LeanPartials part;
@@ -148,6 +149,23 @@ __device__ __forceinline__ void mma_load_round(const K3MParams& q, const uint4 (
         }
     }
 }
+// L2 prefetch of 256 bytes (4 rounds) of the rows of this lane group's two snarls: lane t takes row t of each.  The
+// kernel's own loads are 64-byte pieces of 64 different rows per warp instruction — poor DRAM page locality when they
+// miss; the prefetch turns the DRAM side into 256-byte bursts and the LDGs into L2 hits.
+__device__ __forceinline__ void mma_prefetch_rounds(const K3MParams& q, const uint4 (&lr)[2], uint32_t t, uint32_t round) {
+    const K3Params& p = q.k;
+    const uint32_t off = round * 64;
+    if (off >= p.pitch) return;
+    const uint32_t bytes = min(256u, p.pitch - off);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        if (lr[h].x == kLeanNo) continue;
+        const uint32_t row = t == 0 ? lr[h].x : t == 1 ? lr[h].y : t == 2 ? lr[h].z : lr[h].w;
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.rows + size_t(row) * p.pitch + off), "r"(bytes)
+                     : "memory");
+    }
+}
+
 __device__ __forceinline__ uint32_t u4_word(const uint4& v, int j) { return j == 0 ? v.x : j == 1 ? v.y : j == 2 ? v.z : v.w; }
 
 __device__ __forceinline__ void mma_compute_round(const K3MParams& q, MmaLaneSums& z, const MmaRound& d, uint32_t chunk,
@@ -213,7 +231,12 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma_kernel(c
         // ---- rounds: software pipelined two deep (A / B register sets) ------------------------------------------
         MmaRound ra, rb;
         mma_load_round(q, lr, z.live, (r_first + 0) * 4 + t, ra);
+        if (q.prefetch) {
+            mma_prefetch_rounds(q, lr, t, r_first + 4);       // rounds 4..7 of this tile
+            mma_prefetch_rounds(q, lr_next, t, r_first + 0);  // rounds 0..3 of the warp's next tile
+        }
         for (uint32_t c = 0; c < r_len; c += 2) {
+            if (q.prefetch && (c & 3u) == 0u && c + 8 < r_len + 4) mma_prefetch_rounds(q, lr, t, r_first + c + 8);
             mma_load_round(q, lr, z.live, (c + 1 < r_len) ? (r_first + c + 1) * 4 + t : 0xFFFFFFF0u, rb);
             mma_compute_round(q, z, ra, (r_first + c) * 4 + t, bfrag_lane + size_t(c) * 2048);
             mma_load_round(q, lr, z.live, (c + 2 < r_len) ? (r_first + c + 2) * 4 + t : 0xFFFFFFF0u, ra);
