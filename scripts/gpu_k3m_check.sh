@@ -5,7 +5,7 @@ BQ="python bench.py --trait quantitative --steps 5 --warmup 3 --no-cpu-baseline 
 show() { python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); r=d['roofline']; print('$1 quant step %.3f ms  off-fast %s frac %.3f' % (d['ms_per_step'], r.get('snarls_off_fast_path'), r['frac']))"; }
 STOAT_GPU_K3M=0 timeout 300 $BQ 2>&1 | show "K3M=off"
 timeout 300 $BQ 2>&1 | tail -3 | show "K3M"
-K='regex:dosage_moments|ols_solve|quant_general'
+K='regex:dosage_moments|ols_solve|quant_general|student_tail'
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k "$K" -c 8 --csv --log-file gpurun_out/launches_quant.csv $BQ > gpurun_out/ncu_q.log 2>&1
 grep -v "^==" gpurun_out/launches_quant.csv | python -c "
 import csv,sys

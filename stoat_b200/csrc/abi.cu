@@ -50,7 +50,7 @@ MatrixDev matrix_view(const stoat_gpu_ctx* ctx) {
 }
 
 struct QuantState {
-    DevBuf yc, ys, mom, part_i, part_d, slow, yslices, lean_rec;
+    DevBuf yc, ys, mom, part_i, part_d, slow, yslices, lean_rec, tail_t, tail_x, tail_df;
     double sy_all = 0.0, syy_all = 0.0, y_scale = 1.0;
     bool have_partials = false;
 };
@@ -152,6 +152,9 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     x->q.slow.release();
     x->q.yslices.release();
     x->q.lean_rec.release();
+    x->q.tail_t.release();
+    x->q.tail_df.release();
+    x->q.tail_x.release();
     for (auto& ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : x->chunk_done)
@@ -376,7 +379,7 @@ int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths) {
     const uint64_t blob_bytes = 16 * (2 * S + ((P + E) >> 4) + 2 + kMaxBlob16);
     CK(ctx->d_blob.reserve(blob_bytes));
     CK(ctx->d_big.reserve(std::max<uint64_t>(S * 4, 16)));
-    CK(ctx->d_counters.reserve(16));
+    CK(ctx->d_counters.reserve(32));  // [0..3] see BatchDev, [4] K4b's work counter
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     const uint64_t zero = 0;
     if (S) {
@@ -385,7 +388,7 @@ int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths) {
                            ctx->stream));
         if (E) CK(cudaMemcpyAsync(ctx->d_edge_row.p, paths->edge_row, E * 4, cudaMemcpyHostToDevice, ctx->stream));
     }
-    CK(cudaMemsetAsync(ctx->d_counters.p, 0, 16, ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_counters.p, 0, 32, ctx->stream));
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
     BatchDev& b = ctx->batch;
     b.n_snarls = S;
@@ -590,6 +593,9 @@ static int quant_reserve(stoat_gpu_ctx* ctx) {
     CK(x->q.part_d.reserve(std::max<uint64_t>(slices * 3 * b.n_snarls * 8, 16)));
     CK(x->q.slow.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
     CK(x->q.lean_rec.reserve(std::max<uint64_t>(b.n_snarls * 16, 16)));
+    CK(x->q.tail_t.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
+    CK(x->q.tail_df.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
+    CK(x->q.tail_x.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
     return STOAT_GPU_OK;
 }
 
@@ -617,6 +623,7 @@ static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int ph
         CK(cudaMemsetAsync(ctx->q_beta.p, 0xFF, S * 8, ctx->stream));
         CK(cudaMemsetAsync(ctx->q_se.p, 0xFF, S * 8, ctx->stream));
         CK(cudaMemsetAsync(ctx->q_code.p, STOAT_P_NA, S, ctx->stream));
+        CK(cudaMemsetAsync(x->q.tail_t.p, 0xFF, S * 8, ctx->stream));  // NaN: no Student-t tail to evaluate
     }
     QuantOut out{ctx->q_allele.as<uint32_t>(), ctx->filtered.as<uint8_t>(), ctx->q_nused.as<uint32_t>(),
                  ctx->q_p.as<double>(),        ctx->q_r2.as<double>(),      ctx->q_beta.as<double>(),
@@ -630,7 +637,8 @@ static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int ph
                                 x->q.part_d.as<double>(), x->q.slow.as<uint32_t>(), x->q.lean_rec.as<uint4>(),
                                 x->q.yslices.as<uint8_t>(),
                                 x->q.yc.as<double>(), x->q.y_scale, ctx->num_sms, ctx->k1_variant, ctx->stream,
-                                &ctx->timing.launches, ctx->ev[4], phase));
+                                &ctx->timing.launches, ctx->ev[4], phase, x->q.tail_t.as<double>(),
+                                x->q.tail_x.as<double>(), x->q.tail_df.as<uint32_t>()));
     if (phase == 2) CK(cudaEventRecord(ctx->ev[4], ctx->stream));
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
     CK(cudaMemcpyAsync(x->readback, ctx->d_counters.p, 4, cudaMemcpyDeviceToHost, ctx->stream));

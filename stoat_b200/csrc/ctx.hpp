@@ -107,7 +107,8 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                                      uint32_t* slow_list, uint4* lean_rec, const uint8_t* yslices, const double* yc,
                                      double y_scale, int num_sms, int variant, cudaStream_t st, uint32_t* launches,
                                      cudaEvent_t ev_table_done,  // recorded after the moments pass (K3M / K3R / K3)
-                                     int phase);  // 0: whole step; 1: moments only; 2: solve only (sample-sharded)
+                                     int phase,  // 0: whole step; 1: moments only; 2: solve only (sample-sharded)
+                                     double* tail_t, double* tail_x, uint32_t* tail_df);  // [n_snarls] K4 -> K4b hand-over
 size_t quant_yslices_bytes(uint64_t pitch);  // K3M's phenotype slice table
 // slices of the haplotype range the two-path kernels (K3M / K3R) use: sizes the partial-sum buffers (0: neither runs)
 uint32_t quant_lean_slices(uint64_t pitch, uint64_t n_hap, uint32_t stage_rows);

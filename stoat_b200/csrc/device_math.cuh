@@ -108,6 +108,46 @@ __device__ inline double ibeta_cf(double a, double b, double x) {
     return h;
 }
 
+// The same continued fraction one iteration at a time (K4b runs it on persistent lanes that pick up the next snarl as
+// soon as theirs has converged: the iteration count varies from ~5 to hundreds with x).  init + step() until it returns
+// true reproduce ibeta_cf() operation for operation.
+struct IbetaCf {
+    double a, b, x, qab, qap, qam, c, d, h;
+    int m;
+    __device__ void init(double a_, double b_, double x_) {
+        const double tiny = 1e-300;
+        a = a_; b = b_; x = x_;
+        qab = a + b; qap = a + 1.0; qam = a - 1.0;
+        c = 1.0;
+        d = 1.0 - qab * x / qap;
+        if (fabs(d) < tiny) d = tiny;
+        d = 1.0 / d;
+        h = d;
+        m = 1;
+    }
+    __device__ bool step() {  // true: converged (or out of iterations), h is the value
+        const double tiny = 1e-300;
+        const double m2 = 2.0 * m;
+        double aa = m * (b - m) * x / ((qam + m2) * (a + m2));
+        d = 1.0 + aa * d;
+        if (fabs(d) < tiny) d = tiny;
+        c = 1.0 + aa / c;
+        if (fabs(c) < tiny) c = tiny;
+        d = 1.0 / d;
+        h *= d * c;
+        aa = -(a + m) * (qab + m) * x / ((a + m2) * (qap + m2));
+        d = 1.0 + aa * d;
+        if (fabs(d) < tiny) d = tiny;
+        c = 1.0 + aa / c;
+        if (fabs(c) < tiny) c = tiny;
+        d = 1.0 / d;
+        const double delta = d * c;
+        h *= delta;
+        ++m;
+        return fabs(delta - 1.0) < 2e-16 || m > 2000;
+    }
+};
+
 // ln B(a, 1/2) = lgamma(a) + lgamma(1/2) - lgamma(a + 1/2); asymptotic difference for large a so
 // that two ~1e5-sized lgamma values are never subtracted.
 __device__ inline double log_beta_half(double a) {

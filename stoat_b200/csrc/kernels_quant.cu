@@ -446,7 +446,9 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
 __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __restrict__ mom, uint64_t n_snarls,
                                                         const K3Params kp, const LeanPartials part, uint32_t n_slices,
                                                         const uint64_t* __restrict__ snarl_path_off, QuantOut out,
-                                                        uint32_t* g_list, uint32_t* g_count, uint32_t defer) {
+                                                        uint32_t* g_list, uint32_t* g_count, uint32_t defer,
+                                                        double* __restrict__ tail_t, double* __restrict__ tail_x,
+                                                        uint32_t* __restrict__ tail_df) {
     // defer (sample-sharded runs): a snarl that needs more than the summed two-path partials — any other shape, a
     // rank-deficient or near-perfect fit — is not sent to the general path (this GPU holds only some of the columns)
     // but marked STOAT_P_DEFERRED; the host replays those snarls with all columns (stoat_b200/shard.py).
@@ -533,12 +535,87 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
         hand_on();
         return;
     }
-    const OlsOut o = ols_statistics(beta[1], inv(1, 1), rss, tss, m.n_used, p);
-    out.p[s] = o.p;
-    out.r2[s] = o.r2;
-    out.beta[s] = o.beta;
-    out.se[s] = o.se;
+    // the tail of linear_regression (src/stats_test.cpp:460-489) as in ols_statistics (ols.cuh), except that the
+    // Student-t tail — a continued fraction of 5 .. hundreds of iterations — is left to K4b (student_tail_kernel)
+    int df_res = int(m.n_used) - p + 1;  // :467 (sic)
+    if (df_res < 1) df_res = 1;          // :468
+    const double mse = rss / double(df_res);
+    const double se = sqrt(inv(1, 1) * mse);
+    const double t = beta[1] / se;
+    out.r2[s] = 1.0 - (rss / tss);
+    out.beta[s] = beta[1];
+    out.se[s] = se;
     out.code[s] = kPValue;
+    if (isnan(t) || isinf(t)) {
+        out.p[s] = 1.0;  // :480-482
+    } else {
+        // set-up of student_t_upper_tail (device_math.cuh) here, where every lane has one: the prefactor
+        // x^a (1-x)^b / B(a, b) and the argument / side of the continued fraction, which K4b then only iterates
+        const double df = double(df_res), t2 = t * t;
+        if (t2 == 0.0) {
+            out.p[s] = 1.0;  // 2 * 0.5
+        } else {
+            const double a = 0.5 * df, bb = 0.5;
+            const double z = t2 / (df + t2);  // 1 - x
+            const double log_front = -a * log1p(t2 / df) + bb * log(z) - log_beta_half(a);
+            const bool upper_side = z > 1.5 / (a + 2.5);
+            tail_t[s] = exp(log_front);
+            tail_x[s] = upper_side ? df / (df + t2) : z;
+            tail_df[s] = uint32_t(df_res) | (upper_side ? 0x80000000u : 0u);
+        }
+    }
+}
+
+// K4b: p = 2 * P(T_df > |t|) (stats_test.cpp:484) for every snarl K4 left a prefactor for (tail_t[s] is NaN otherwise).
+// One lane = one running continued fraction (student_t_upper_tail of device_math.cuh, operation for operation); a lane
+// whose fraction has converged takes the next snarl from the shared counter, so the lanes of a warp stay in the common
+// loop body (thread-per-snarl: 6.5 of 32 lanes active, ncu r1e_k4.txt).  The refill is a few loads and one division:
+// the expensive set-up (log1p, log, exp, ln B) was done by K4 with all lanes busy.
+__global__ void __launch_bounds__(128) student_tail_kernel(const double* __restrict__ tail_t,
+                                                           const double* __restrict__ tail_x,
+                                                           const uint32_t* __restrict__ tail_df, uint32_t n_snarls,
+                                                           uint32_t* __restrict__ next, double* __restrict__ p_out) {
+    const uint32_t lane = threadIdx.x & 31;
+    bool active = false, drained = false;
+    uint32_t snarl = 0;
+    IbetaCf cf;
+    double front = 0.0;
+    bool upper_side = false;
+    for (;;) {
+        const uint32_t need = __ballot_sync(0xffffffffu, !active && !drained);
+        if (need) {
+            const int leader = __ffs(need) - 1;
+            uint32_t base = 0;
+            if (int(lane) == leader) base = atomicAdd(next, uint32_t(__popc(need)));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!active && !drained) {
+                const uint32_t w = base + __popc(need & ((1u << lane) - 1u));
+                if (w < n_snarls) {
+                    front = tail_t[w];
+                    if (!isnan(front)) {
+                        const uint32_t d = tail_df[w];
+                        const double a = 0.5 * double(d & 0x7FFFFFFFu);
+                        upper_side = (d >> 31) != 0u;
+                        if (upper_side) cf.init(a, 0.5, tail_x[w]);
+                        else cf.init(0.5, a, tail_x[w]);
+                        snarl = w;
+                        active = true;
+                    }
+                } else {
+                    drained = true;
+                }
+            }
+        }
+        if (!__any_sync(0xffffffffu, active)) {
+            if (__all_sync(0xffffffffu, drained)) break;
+            continue;
+        }
+        if (active && cf.step()) {
+            const double tail = upper_side ? 0.5 * front * cf.h / cf.a : 0.5 * (1.0 - front * cf.h / cf.a);
+            p_out[snarl] = 2.0 * tail;
+            active = false;
+        }
+    }
 }
 
 #include "quant_general.cuh"
@@ -651,6 +728,17 @@ uint32_t quant_lean_slices(uint64_t pitch, uint64_t n_hap, uint32_t stage_rows) 
     return quant_reg_slices(pitch);
 }
 
+// K4b over every snarl of the batch (tail_t[s] NaN: nothing to do); counters[4] is the shared work counter
+static cudaError_t launch_student_tail(const double* tail_t, const double* tail_x, const uint32_t* tail_df,
+                                       const BatchDev& b, double* p_out, int num_sms, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(b.counters + 4, 0, 4, st);
+    if (e != cudaSuccess) return e;
+    const uint64_t want = (b.n_snarls + 127) / 128;
+    const unsigned blocks = unsigned(want < uint64_t(num_sms) * 8 ? want : uint64_t(num_sms) * 8);
+    student_tail_kernel<<<blocks, 128, 0, st>>>(tail_t, tail_x, tail_df, uint32_t(b.n_snarls), b.counters + 4, p_out);
+    return cudaGetLastError();
+}
+
 // scratch owned by the caller: mom [n_snarls], ys permuted, sums; K3R: part_i [slices][7][S], part_d [slices][3][S],
 // slow_list [S]; counters[3] = length of the slow list
 cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, const double* ys_perm,
@@ -659,7 +747,8 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                                      QuantOut out, QuantMoments* mom, uint32_t* part_i, double* part_d,
                                      uint32_t* slow_list, uint4* lean_rec, const uint8_t* yslices, const double* yc,
                                      double y_scale, int num_sms, int variant, cudaStream_t st, uint32_t* launches,
-                                     cudaEvent_t ev_table_done, int phase) {
+                                     cudaEvent_t ev_table_done, int phase, double* tail_t, double* tail_x,
+                                     uint32_t* tail_df) {
     // phase 0: the whole step.  Sample-sharded runs split it around the all-reduce of the partial sums:
     // phase 1 = lean records + K3M only, phase 2 = K4 on the summed partials with everything else deferred to the host.
     if (b.n_snarls == 0) return cudaSuccess;
@@ -719,9 +808,10 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         if (phase == 2) {
             if (!k3m_plan(pitch, m.n_cols, pm)) return cudaErrorNotSupported;
             ols_solve_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(
-                mom, b.n_snarls, p, part, pm.n_slices, b.snarl_path_off, out, b.big_list, b.counters, 1u);
+                mom, b.n_snarls, p, part, pm.n_slices, b.snarl_path_off, out, b.big_list, b.counters, 1u, tail_t, tail_x, tail_df);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
-            if (launches) *launches += 1;
+            if ((e = launch_student_tail(tail_t, tail_x, tail_df, b, out.p, num_sms, st)) != cudaSuccess) return e;
+            if (launches) *launches += 2;
             return cudaSuccess;
         }
         if (phase == 1 && !(part_i && part_d && slow_list && lean_rec && yslices && yc && k3m_plan(pitch, m.n_cols, pm)))
@@ -809,9 +899,11 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             if (ev_table_done && (e = cudaEventRecord(ev_table_done, st)) != cudaSuccess) return e;
         }
-        ols_solve_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(mom, b.n_snarls, p, part, n_slices,
-                                                                            b.snarl_path_off, out, b.big_list, b.counters, 0u);
+        ols_solve_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(
+            mom, b.n_snarls, p, part, n_slices, b.snarl_path_off, out, b.big_list, b.counters, 0u, tail_t, tail_x, tail_df);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if ((e = launch_student_tail(tail_t, tail_x, tail_df, b, out.p, num_sms, st)) != cudaSuccess) return e;
+        if (launches) *launches += 1;
         g.list = b.big_list;
         g.n_list_dev = b.counters;
         if ((e = launch_quant_general(g, b.n_snarls, num_sms, st)) != cudaSuccess) return e;
