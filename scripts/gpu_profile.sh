@@ -4,7 +4,7 @@
 set -u
 OUT=gpurun_out
 mkdir -p $OUT
-K='regex:path_and_popc|binary_prep|binary_stats|fisher_exact|repack_rows|build_case_mask|dosage_moments|lean_rec|ols_solve|quant_general|centre_permute|eqtl'
+K='regex:path_and_popc|binary_prep|binary_stats|fisher_exact|repack_rows|build_case_mask|dosage_moments|lean_rec|ols_solve|student_tail|quant_general|centre_permute|eqtl'
 BENCH="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
 python -m pytest tests -m gpu -x -q 2>&1 | tail -5 > $OUT/pytest_gpu.log; cat $OUT/pytest_gpu.log
 python bench.py --steps 10 --warmup 3 > $OUT/bench_binary.json 2> $OUT/bench_binary.err; cat $OUT/bench_binary.json; tail -3 $OUT/bench_binary.err
@@ -22,3 +22,6 @@ ncu --set full --clock-control none --import-source on -k regex:dosage_moments_m
 ncu --set full --clock-control none --import-source on -k regex:ols_solve -s 3 -c 1 -f -o $OUT/prof_k4 $BQ > $OUT/ncu_k4.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:dosage_moments_tma -s 3 -c 1 -f -o $OUT/prof_k3 $BQ > $OUT/ncu_k3.log 2>&1
 ls -la $OUT
+timeout 900 python bench.py --trait eqtl --steps 3 --warmup 3 --no-cpu-baseline > $OUT/bench_eqtl.json 2> $OUT/bench_eqtl.err; cut -c1-300 $OUT/bench_eqtl.json
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_binary_ref.json 2> $OUT/bench_binary_ref.err; cut -c1-300 $OUT/bench_binary_ref.json
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
