@@ -300,6 +300,21 @@ def algorithmic_bytes_k3m(paths, pitch):
     return distinct * pitch + (16 + 53) * paths.n_snarls
 
 
+def bind_to_gpu_numa(local: int) -> None:
+    """One process per GPU: run on the CPUs next to that GPU (NVML's ideal affinity) so that the pinned host buffers of the
+    end-to-end leg are first-touched on its NUMA node — with 4 or 8 ranks on the default affinity the host-to-device copies
+    of all ranks cross the socket interconnect and e2e stops scaling (measured: 111 GB/s aggregate at N = 4)."""
+    if os.environ.get("STOAT_BENCH_NO_BIND"):
+        return
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local))
+    except Exception as e:  # no NVML / not permitted: keep the inherited affinity
+        print(f"[bench] cpu affinity not set for GPU {local}: {e}", file=sys.stderr)
+
+
 def quant_traffic():
     """dram bytes per launch of K3M from the committed ncu capture (profiles/k3m_traffic.json), or None"""
     try:
@@ -330,6 +345,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
+        bind_to_gpu_numa(local)
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if not torch.cuda.is_available():

@@ -111,6 +111,24 @@ __device__ void g_exact_sums(const GParams& g, GScratch& sc, const GSnarl& sn, u
         const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
         const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
         __syncwarp();
+        if (sn.nk <= uint32_t(kMaxFeat + 1)) {
+            // the quotients of the block's 32 samples in parallel (lane = sample, sc.tile is free at this point), then only
+            // the ADDITIONS in the reference's order: with the divisions inside the serial loop one such snarl cost ~1 ms
+            for (uint32_t c = 0; c < sn.nk; ++c) {
+                const uint32_t k = sc.cnt[lane][c];
+                sc.tile[lane][c] = (k > 0) ? __ddiv_rn(double(k), double(rs > 255 ? 255 : rs)) : 0.0;
+            }
+            __syncwarp();
+            if (lane < sn.nk)
+                for (uint32_t i = 0; i < 32; ++i)
+                    if ((used_ballot >> i) & 1u) colsum0 = __dadd_rn(colsum0, sc.tile[i][lane]);
+            if (lane == 0)
+                for (uint32_t i = 0; i < 32; ++i)
+                    if ((used_ballot >> i) & 1u)
+                        for (uint32_t c = 0; c < sn.nk; ++c) t = __dadd_rn(t, sc.tile[i][c]);
+            __syncwarp();
+            continue;
+        }
         for (uint32_t i = 0; i < 32; ++i) {
             if (!((used_ballot >> i) & 1u)) continue;
             const double rsum = double(sc.rs[i]);
