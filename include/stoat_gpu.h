@@ -254,6 +254,13 @@ STOAT_GPU_API int stoat_gpu_quantitative_solve_staged(stoat_gpu_ctx* ctx, const 
 STOAT_GPU_API int stoat_gpu_last_timing(const stoat_gpu_ctx* ctx, stoat_gpu_timing* out);
 /* cudaStream_t of the context as an integer (so the caller can record its own events)       */
 STOAT_GPU_API uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx);
+/* The matrix from its set bits: the device half of make_edge_matrix (src/snarl_analyzer.cpp:190-260).
+ * While it parses a VCF record the reference sets bit (row of the allele edge, 2 * sample + haplotype) one by one
+ * (EdgeBySampleMatrix::set, src/matrix.cpp:76-84); a host that keeps those (row, column) pairs instead of the dense
+ * byte matrix passes them here and the bits are set straight into the device layout (no repack pass; 8 bytes per set
+ * bit go over PCIe instead of n_rows * n_cols / 8).  Pairs may repeat and come in any order.                       */
+STOAT_GPU_API int stoat_gpu_set_matrix_pairs(stoat_gpu_ctx* ctx, const uint32_t* rows, const uint32_t* cols,
+                                             uint64_t n_pairs, uint64_t n_rows, uint64_t n_cols);
 /* bytes per repacked row on the device: ceil(n_cols / 256) * 32 (whole 32-byte sectors)         */
 STOAT_GPU_API uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx);
 /* read back one repacked row (tests of K0)                                                  */

@@ -95,6 +95,15 @@ class Context:
         self._check(self._lib.stoat_gpu_set_matrix(self._ctx, _ptr(bits), n_rows, n_cols))
         self.n_rows, self.n_cols = n_rows, n_cols
 
+    def set_matrix_pairs(self, rows, cols, n_rows: int, n_cols: int):
+        """The matrix from its set bits (row, column) — what make_edge_matrix emits per allele edge and carrier."""
+        r = np.ascontiguousarray(rows, dtype=np.uint32)
+        c = np.ascontiguousarray(cols, dtype=np.uint32)
+        if r.size != c.size:
+            raise ValueError("rows and cols differ in length")
+        self._check(self._lib.stoat_gpu_set_matrix_pairs(self._ctx, _ptr(r), _ptr(c), r.size, n_rows, n_cols))
+        self.n_rows, self.n_cols = n_rows, n_cols
+
     def set_matrix_ptr(self, host_ptr: int, n_rows: int, n_cols: int):
         """Same, from a raw host pointer (e.g. a pinned torch tensor's data_ptr())."""
         self._check(self._lib.stoat_gpu_set_matrix(self._ctx, C.c_void_p(host_ptr), n_rows, n_cols))

@@ -211,6 +211,60 @@ int stoat_gpu_set_matrix_dev(stoat_gpu_ctx* ctx, const uint8_t* bits_dev, uint64
     return set_matrix_common(ctx, bits_dev, true, n_rows, n_cols);
 }
 
+int stoat_gpu_set_matrix_pairs(stoat_gpu_ctx* ctx, const uint32_t* rows, const uint32_t* cols, uint64_t n_pairs,
+                               uint64_t n_rows, uint64_t n_cols) {
+    if (!ctx) return STOAT_GPU_ERR_ARG;
+    if (n_cols == 0 || (n_cols & 1)) return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_pairs: n_cols must be even and > 0");
+    if (n_cols >= (1ull << 32) || n_rows >= 0xFFFFFFFFull)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_pairs: dimensions exceed 32-bit row / column indices");
+    if (n_pairs && (!rows || !cols)) return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_pairs: rows / cols is NULL");
+    CK(cudaSetDevice(ctx->device));
+    const uint64_t pitch = pitch_for(n_cols);
+    CK(ctx->rows.reserve(std::max<uint64_t>(n_rows * pitch, 16)));
+    CK(ctx->d_counters.reserve(32));
+    ctx->timing = stoat_gpu_timing{};
+    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    CK(cudaMemsetAsync(ctx->rows.p, 0, std::max<uint64_t>(n_rows * pitch, 16), ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_counters.p, 0, 32, ctx->stream));
+    // pairs go up in chunks through the two staging buffers: the copy of chunk k + 1 overlaps the scatter of chunk k
+    const uint64_t chunk = 1ull << 25;  // 32M pairs = 256 MB
+    CtxExtra* x = extra_of(ctx);
+    float scatter_ms = 0.f;
+    for (uint64_t p0 = 0, k = 0; p0 < n_pairs; p0 += chunk, ++k) {
+        const uint64_t n = std::min(chunk, n_pairs - p0);
+        DevBuf& st = ctx->raw_stage[k & 1];
+        CK(st.reserve(std::min(chunk, n_pairs) * 8));
+        uint32_t* d_rows = st.as<uint32_t>();
+        uint32_t* d_cols = d_rows + n;
+        if (k >= 2) CK(cudaStreamWaitEvent(ctx->copy_stream, x->chunk_done[k & 1], 0));  // the buffer's previous scatter
+        CK(cudaMemcpyAsync(d_rows, rows + p0, n * 4, cudaMemcpyHostToDevice, ctx->copy_stream));
+        CK(cudaMemcpyAsync(d_cols, cols + p0, n * 4, cudaMemcpyHostToDevice, ctx->copy_stream));
+        CK(cudaEventRecord(x->chunk_done[2 + (k & 1)], ctx->copy_stream));
+        CK(cudaStreamWaitEvent(ctx->stream, x->chunk_done[2 + (k & 1)], 0));
+        CK(launch_scatter_bits(d_rows, d_cols, n, n_rows, n_cols, pitch, ctx->rows.as<uint8_t>(),
+                               ctx->d_counters.as<uint32_t>() + 1, ctx->num_sms, ctx->stream));
+        CK(cudaEventRecord(x->chunk_done[k & 1], ctx->stream));
+    }
+    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    CK(cudaMemcpyAsync(x->counters_host, ctx->d_counters.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&scatter_ms, ctx->ev[0], ctx->ev[1]));
+    ctx->timing.h2d_ms = scatter_ms;  // upload and scatter overlap: one figure
+    ctx->timing.repack_ms = 0.f;
+    ctx->timing.launches = uint32_t((n_pairs + chunk - 1) / chunk);
+    ctx->have_matrix = false;
+    if (x->counters_host[1])
+        return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_pairs: a (row, column) pair lies outside the matrix");
+    ctx->n_rows = n_rows;
+    ctx->n_cols = n_cols;
+    ctx->pitch = pitch;
+    ctx->have_matrix = true;
+    if (ctx->have_binary && ctx->n_samples_binary * 2 != n_cols) ctx->have_binary = false;
+    if (ctx->have_quant && ctx->n_samples_quant * 2 != n_cols) ctx->have_quant = false;
+    ctx->have_batch = false;
+    return STOAT_GPU_OK;
+}
+
 uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx) { return ctx ? ctx->pitch : 0; }
 uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx) { return ctx ? reinterpret_cast<uint64_t>(ctx->stream) : 0; }
 

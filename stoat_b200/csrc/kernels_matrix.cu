@@ -88,4 +88,34 @@ cudaError_t launch_build_case_mask(const uint8_t* is_case, uint64_t n_samples, u
     return cudaGetLastError();
 }
 
+// =================================================================================================
+// Matrix from its set bits — the device half of make_edge_matrix (src/snarl_analyzer.cpp:190-260): while it parses a VCF
+// record the reference sets bit (row of the allele edge, 2 * sample + haplotype) one at a time (matrix.cpp:76-84); here
+// the host hands over those (row, column) pairs and the bits are set straight into the pitched layout (no K0, and the
+// upload is 8 bytes per set bit instead of the dense matrix: smaller below 1.5 % density).  `out` is zeroed by the caller.
+// =================================================================================================
+__global__ void __launch_bounds__(256) scatter_bits_kernel(const uint32_t* __restrict__ row, const uint32_t* __restrict__ col,
+                                                           uint64_t n_pairs, uint64_t n_rows, uint64_t n_cols, uint64_t pitch,
+                                                           uint32_t* __restrict__ out, uint32_t* __restrict__ bad) {
+    const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_pairs; i += stride) {
+        const uint32_t r = row[i], c = col[i];
+        if (uint64_t(r) >= n_rows || uint64_t(c) >= n_cols) {
+            atomicExch(bad, 1u);
+            continue;
+        }
+        atomicOr(out + uint64_t(r) * (pitch / 4) + (c >> 5), 1u << (c & 31u));
+    }
+}
+
+cudaError_t launch_scatter_bits(const uint32_t* row, const uint32_t* col, uint64_t n_pairs, uint64_t n_rows, uint64_t n_cols,
+                                uint64_t pitch, uint8_t* out, uint32_t* bad, int num_sms, cudaStream_t st) {
+    if (n_pairs == 0) return cudaSuccess;
+    const uint64_t want = (n_pairs + 255) / 256;
+    const unsigned blocks = unsigned(want < uint64_t(num_sms) * 16 ? want : uint64_t(num_sms) * 16);
+    scatter_bits_kernel<<<blocks, 256, 0, st>>>(row, col, n_pairs, n_rows, n_cols, pitch, reinterpret_cast<uint32_t*>(out),
+                                                bad);
+    return cudaGetLastError();
+}
+
 }  // namespace stoat

@@ -260,3 +260,36 @@ def test_reused_context_big_snarl_after_biallelic_batch(oracle):
             got = ctx.binary_batch(SnarlPaths(spo, peo, er), min_ind=0, min_hap=0, maf=0.0)
             ref = oracle.binary_batch(bits, H2, is_case, oracle.Paths(spo, peo, er), min_ind=0, min_hap=0, maf=0.0)
             H.assert_binary_equal(got, ref)
+
+
+def test_matrix_from_set_bits(gpu_ctx, oracle):
+    """stoat_gpu_set_matrix_pairs (the device half of make_edge_matrix): the (row, column) pairs of the set
+    bits, in any order and with repeats, give the same device matrix and the same results as the dense upload."""
+    import stoat_b200
+    from stoat_b200 import SnarlPaths
+
+    rng = np.random.default_rng(77)
+    dense, snarls = H.partition_problem(rng, 120, 333)  # 666 columns: rows are not byte aligned in the reference layout
+    n_rows, n_cols = dense.shape
+    is_case = (rng.random(333) < 0.5).astype(np.uint8)
+    bits = oracle.pack_matrix(dense)
+    spo, peo, er = H.csr_from_lists(snarls)
+    gpu_ctx.set_matrix(bits, n_rows, n_cols)
+    want_rows = [gpu_ctx.read_row(r).copy() for r in range(n_rows)]
+    gpu_ctx.set_binary_phenotype(is_case)
+    want = gpu_ctx.binary_batch(SnarlPaths(spo, peo, er))
+    r, c = np.nonzero(dense)
+    order = rng.permutation(r.size)
+    r = np.concatenate([r[order], r[:50]]).astype(np.uint32)  # shuffled, with repeats
+    c = np.concatenate([c[order], c[:50]]).astype(np.uint32)
+    gpu_ctx.set_matrix_pairs(r, c, n_rows, n_cols)
+    for k in range(n_rows):
+        np.testing.assert_array_equal(gpu_ctx.read_row(k), want_rows[k], err_msg=f"row {k}")
+    gpu_ctx.set_binary_phenotype(is_case)
+    got = gpu_ctx.binary_batch(SnarlPaths(spo, peo, er))
+    for k in want:
+        np.testing.assert_array_equal(got[k], want[k], err_msg=k)
+    with pytest.raises(stoat_b200.StoatGpuError):
+        gpu_ctx.set_matrix_pairs(np.array([n_rows], np.uint32), np.array([0], np.uint32), n_rows, n_cols)
+    gpu_ctx.set_matrix_pairs(np.zeros(0, np.uint32), np.zeros(0, np.uint32), n_rows, n_cols)  # empty: all-zero matrix
+    assert not gpu_ctx.read_row(0).any()
