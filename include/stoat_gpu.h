@@ -261,6 +261,11 @@ STOAT_GPU_API uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx);
  * bit go over PCIe instead of n_rows * n_cols / 8).  Pairs may repeat and come in any order.                       */
 STOAT_GPU_API int stoat_gpu_set_matrix_pairs(stoat_gpu_ctx* ctx, const uint32_t* rows, const uint32_t* cols,
                                              uint64_t n_pairs, uint64_t n_rows, uint64_t n_cols);
+/* Benjamini-Hochberg adjustment of a p-value column — adjust_pvalues_with_BH (src/post_processing.cpp:7-38, SURVEY.md
+ * §8f-3): p_adjusted[i] in the order of p[i]; bit-identical to the reference (same two roundings per value, ties get equal
+ * values).  p must be finite and >= 0: the caller drops the rows the reference's string_to_pvalue would not parse.  Host
+ * buffers; n < 2^31.                                                                                                  */
+STOAT_GPU_API int stoat_gpu_bh_adjust(stoat_gpu_ctx* ctx, const double* p, uint64_t n, double* p_adjusted);
 /* bytes per repacked row on the device: ceil(n_cols / 256) * 32 (whole 32-byte sectors)         */
 STOAT_GPU_API uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx);
 /* read back one repacked row (tests of K0)                                                  */

@@ -376,3 +376,19 @@ def quantitative_table(bits, n_cols, paths: Paths, snarl: int, min_ind=3, min_ha
 
 def num_threads() -> int:
     return lib().orc_num_threads()
+
+
+def bh_adjust(p) -> np.ndarray:
+    """adjust_pvalues_with_BH (src/post_processing.cpp:7-38), restated in numpy: sort by raw p (:12-14), adjusted[i] =
+    p * n / (i + 1) in that order of operations (:19-22), running minimum from the largest p down (:26-28), clamp to 1
+    (:31-33), back to the original order (:36-38).  Ties get equal values whatever order the sort leaves them in."""
+    a = np.asarray(p, dtype=np.float64)
+    n = a.size
+    if n == 0:
+        return a.copy()
+    order = np.argsort(a, kind="stable")
+    adj = (a[order] * np.float64(n)) / np.arange(1, n + 1, dtype=np.float64)
+    adj = np.minimum.accumulate(adj[::-1])[::-1]
+    out = np.empty(n, dtype=np.float64)
+    out[order] = np.minimum(1.0, adj)
+    return out

@@ -128,6 +128,13 @@ class Context:
         a = np.ascontiguousarray(covar, dtype=np.float64)
         self._check(self._lib.stoat_gpu_set_covariates(self._ctx, _ptr(a), a.shape[0], a.shape[1]))
 
+    def bh_adjust(self, p) -> np.ndarray:
+        """Benjamini-Hochberg adjusted p-values, adjust_pvalues_with_BH (src/post_processing.cpp:7-38)."""
+        a = np.ascontiguousarray(p, dtype=np.float64)
+        out = np.empty_like(a)
+        self._check(self._lib.stoat_gpu_bh_adjust(self._ctx, _ptr(a), a.size, _ptr(out)))
+        return out
+
     @property
     def row_pitch(self) -> int:
         return int(self._lib.stoat_gpu_row_pitch(self._ctx))

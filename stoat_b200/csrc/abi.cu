@@ -66,6 +66,7 @@ struct CtxExtra {
     uint32_t counters_host[4] = {0, 0, 0, 0};
     uint32_t readback[2] = {0, 0};
     uint32_t fisher_readback[2 * kMaxRunChunks] = {};
+    DevBuf bh;  // scratch of stoat_gpu_bh_adjust
     cudaEvent_t chunk_done[kMaxRunChunks] = {};
 };
 static CtxExtra* extra_of(stoat_gpu_ctx* ctx);
@@ -155,6 +156,7 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     x->q.tail_t.release();
     x->q.tail_df.release();
     x->q.tail_x.release();
+    x->bh.release();
     for (auto& ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : x->chunk_done)
@@ -262,6 +264,37 @@ int stoat_gpu_set_matrix_pairs(stoat_gpu_ctx* ctx, const uint32_t* rows, const u
     if (ctx->have_binary && ctx->n_samples_binary * 2 != n_cols) ctx->have_binary = false;
     if (ctx->have_quant && ctx->n_samples_quant * 2 != n_cols) ctx->have_quant = false;
     ctx->have_batch = false;
+    return STOAT_GPU_OK;
+}
+
+// ---- post-processing ----------------------------------------------------------------------------------
+int stoat_gpu_bh_adjust(stoat_gpu_ctx* ctx, const double* p, uint64_t n, double* p_adjusted) {
+    if (!ctx) return STOAT_GPU_ERR_ARG;
+    if (n == 0) return STOAT_GPU_OK;  // src/post_processing.cpp:9
+    if (!p || !p_adjusted) return fail(ctx, STOAT_GPU_ERR_ARG, "bh_adjust: NULL argument");
+    if (n >= (1ull << 31)) return fail(ctx, STOAT_GPU_ERR_ARG, "bh_adjust: more than 2^31 - 1 p-values");
+    for (uint64_t i = 0; i < n; ++i)
+        if (!(p[i] >= 0.0) || !std::isfinite(p[i]))
+            return fail(ctx, STOAT_GPU_ERR_ARG, "bh_adjust: p-values must be finite and >= 0 (drop the NA rows first)");
+    CK(cudaSetDevice(ctx->device));
+    CtxExtra* x = extra_of(ctx);
+    const size_t temp = bh_temp_bytes(n);
+    // one scratch block: p | out | keys | a | b (8 n each) | idx_in | idx_sorted (4 n each) | temp
+    const size_t need = size_t(n) * (5 * 8 + 2 * 4) + 256 + temp;
+    CK(x->bh.reserve(need));
+    uint8_t* base = x->bh.as<uint8_t>();
+    double* d_p = reinterpret_cast<double*>(base);
+    double* d_out = d_p + n;
+    uint64_t* d_keys = reinterpret_cast<uint64_t*>(d_out + n);
+    double* d_a = reinterpret_cast<double*>(d_keys + n);
+    double* d_b = d_a + n;
+    uint32_t* d_i0 = reinterpret_cast<uint32_t*>(d_b + n);
+    uint32_t* d_i1 = d_i0 + n;
+    void* d_temp = base + ((size_t(n) * 48 + 255) & ~size_t(255));
+    CK(cudaMemcpyAsync(d_p, p, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CK(launch_bh_adjust(d_p, n, d_out, d_keys, d_i0, d_i1, d_a, d_b, d_temp, temp, ctx->stream));
+    CK(cudaMemcpyAsync(p_adjusted, d_out, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
     return STOAT_GPU_OK;
 }
 

@@ -90,6 +90,10 @@ cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const
                                 uint8_t* chi2_code, uint8_t* fisher_code, uint4* fisher_tab, uint32_t* fisher_idx,
                                 uint32_t* fisher_counters, int num_sms, cudaStream_t st, uint64_t s_begin = 0,
                                 uint64_t s_count = ~uint64_t(0));
+// post-processing (kernels_post.cu): Benjamini-Hochberg adjustment
+size_t bh_temp_bytes(uint64_t n);
+cudaError_t launch_bh_adjust(const double* p, uint64_t n, double* out, uint64_t* keys_sorted, uint32_t* idx_in,
+                             uint32_t* idx_sorted, double* a, double* b, void* temp, size_t temp_bytes, cudaStream_t st);
 // quantitative
 struct QuantMoments;  // kernels_quant.cu
 struct QuantOut {

@@ -122,3 +122,19 @@ def test_ols_golden_row_identities(oracle):
         assert abs(q / t2 - 1) < 2e-3
         assert abs(2 * oracle.student_t_sf(n - 1, abs(b / se)) - p) <= 2e-2 * p
     assert checked > 300 and quirk_closer > 0.95 * checked
+
+
+def test_bh_adjust_reference_unit_vectors(oracle):
+    """tests/unittest/post_processing_unit.cpp:12-46 (known answers), :54-66 (clamp), :48-52 (empty)."""
+    import numpy as np
+
+    got = oracle.bh_adjust([0.01, 0.04, 0.03, 0.002, 0.05])
+    np.testing.assert_allclose(got, [0.025, 0.05, 0.05, 0.01, 0.05], rtol=1e-12)
+    assert (oracle.bh_adjust([0.9, 0.95, 0.99]) <= 1.0).all()
+    assert oracle.bh_adjust([]).size == 0
+    # monotone in p and never below p
+    rng = np.random.default_rng(1)
+    p = rng.random(1000) ** 3
+    adj = oracle.bh_adjust(p)
+    o = np.argsort(p)
+    assert (np.diff(adj[o]) >= 0).all() and (adj >= p).all()
