@@ -832,7 +832,13 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             q.part = part;
             n_slices = pm.n_slices;
             if ((e = cudaMemsetAsync(b.counters + 3, 0, 4, st)) != cudaSuccess) return e;
-            lean_rec_kernel<<<unsigned((b.n_snarls + 255) / 256), 256, 0, st>>>(b.rec, b.blob, b.n_snarls, lean_rec);
+            // three-path snarls: K3M3 when one CTA row covers the haplotype range and the step is not sample-sharded
+            // (K3M3 writes moments, not partial sums); their records live behind the two-path records
+            const bool three = phase == 0 && pm.n_slices == 1 && env_int("STOAT_GPU_K3M3", 1) != 0;
+            uint4* rec3 = three ? lean_rec + b.n_snarls : nullptr;
+            if (three && (e = cudaMemsetAsync(b.counters + 5, 0, 4, st)) != cudaSuccess) return e;
+            lean_rec_kernel<<<unsigned((b.n_snarls + 255) / 256), 256, 0, st>>>(b.rec, b.blob, b.n_snarls, lean_rec, rec3,
+                                                                                b.counters + 5);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             // attribute + occupancy query once per (device, shared-memory size): they are driver calls, not free per step
             static thread_local int cached_dev = -1, cached_occ = 1;
@@ -863,6 +869,28 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             if (ev_table_done && (e = cudaEventRecord(ev_table_done, st)) != cudaSuccess) return e;
             if (launches) *launches += 2;
             if (phase == 1) return cudaSuccess;
+            if (three) {
+                static thread_local int dev3 = -1, occ3 = 1;
+                static thread_local uint32_t smem3 = 0;
+                if (dev_now != dev3 || pm.smem_bytes != smem3) {
+                    e = cudaFuncSetAttribute(dosage_moments_mma3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             int(pm.smem_bytes));
+                    if (e != cudaSuccess) return e;
+                    int o = 1;
+                    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, dosage_moments_mma3_kernel, kMmaWarps * 32,
+                                                                      pm.smem_bytes) != cudaSuccess || o < 1)
+                        o = 1;
+                    dev3 = dev_now;
+                    smem3 = pm.smem_bytes;
+                    occ3 = o;
+                }
+                const uint64_t tiles3 = (b.n_snarls + kMma3Tile - 1) / kMma3Tile;
+                uint64_t ctas3 = uint64_t(num_sms) * uint64_t(occ3);
+                if (ctas3 > (tiles3 + kMmaWarps - 1) / kMmaWarps) ctas3 = (tiles3 + kMmaWarps - 1) / kMmaWarps;
+                dosage_moments_mma3_kernel<<<unsigned(ctas3), kMmaWarps * 32, pm.smem_bytes, st>>>(q, rec3, b.counters + 5);
+                if ((e = cudaGetLastError()) != cudaSuccess) return e;
+                if (launches) *launches += 1;
+            }
             p.list = slow_list;
             p.list_count = b.counters + 3;
             dosage_moments_tma_kernel<<<unsigned(num_sms), cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);

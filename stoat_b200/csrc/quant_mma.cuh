@@ -51,15 +51,52 @@ struct K3MParams {
 };
 
 // rec / path program -> lean record (one thread per snarl; 48 B in, 16 B out)
+// Three-path snarls (rec3 != nullptr): every path with 1 or 2 checked edges -> a record of six rows in rec3 (compacted,
+// order free: the results are stored by snarl) for dosage_moments_mma3_kernel, and nothing for the slow list.
 __global__ void __launch_bounds__(256) lean_rec_kernel(const SnarlRec* __restrict__ rec, const uint8_t* __restrict__ blob,
-                                                       uint64_t n_snarls, uint4* __restrict__ out) {
+                                                       uint64_t n_snarls, uint4* __restrict__ out, uint4* __restrict__ rec3,
+                                                       uint32_t* __restrict__ count3) {
     const uint64_t s = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (s >= n_snarls) return;
-    const SnarlRec r = rec[s];
-    const uint4 hdr = *reinterpret_cast<const uint4*>(blob + size_t(r.blob16) * 16);  // np, class | p0 | codes, locals ...
+    const bool in = s < n_snarls;
+    SnarlRec r{};
+    uint4 hdr = make_uint4(0u, 0u, 0u, 0u);
+    if (in) {
+        r = rec[s];
+        hdr = *reinterpret_cast<const uint4*>(blob + size_t(r.blob16) * 16);  // np, class | p0 | codes, locals ...
+    }
     const uint32_t np = hdr.x & 0xFFu, code0 = hdr.z & 0xFFu, code1 = (hdr.z >> 8) & 0xFFu;
+    const uint32_t code2 = (hdr.z >> 16) & 0xFFu;
+    const bool ok3 = in && rec3 != nullptr && r.n_rows != 0 && np == 3u && (code0 == 1u || code0 == 2u) &&
+                     (code1 == 1u || code1 == 2u) && (code2 == 1u || code2 == 2u);
+    {
+        const uint32_t votes = __ballot_sync(0xffffffffu, ok3);
+        uint32_t base = 0;
+        const uint32_t lane = threadIdx.x & 31u;
+        if (votes != 0u) {
+            if (lane == 0) base = atomicAdd(count3, uint32_t(__popc(votes)));
+            base = __shfl_sync(0xffffffffu, base, 0);
+        }
+        if (ok3) {
+            // program bytes: 8.. codes (3), 11.. locals of path 0, 1, 2
+            const uint8_t* loc = blob + size_t(r.blob16) * 16 + kBlobHeaderQ + 3;
+            uint32_t rows6[6];
+            uint32_t off = 0;
+            const uint32_t codes[3] = {code0, code1, code2};
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const uint32_t la = loc[off], lb = (codes[j] == 2u) ? loc[off + 1] : la;
+                rows6[2 * j] = r.rows[la];
+                rows6[2 * j + 1] = r.rows[lb];
+                off += codes[j];
+            }
+            const uint32_t slot = base + uint32_t(__popc(votes & ((1u << lane) - 1u)));
+            rec3[2 * size_t(slot)] = make_uint4(rows6[0], rows6[1], rows6[2], rows6[3]);
+            rec3[2 * size_t(slot) + 1] = make_uint4(rows6[4], rows6[5], hdr.y, uint32_t(s));
+        }
+    }
+    if (!in) return;
     const bool ok = r.n_rows != 0 && np == 2u && (code0 == 1u || code0 == 2u) && (code1 == 1u || code1 == 2u);
-    uint4 o = make_uint4(kLeanNo, np != 0u ? 1u : 0u, 0u, 0u);
+    uint4 o = make_uint4(kLeanNo, (np != 0u && !ok3) ? 1u : 0u, 0u, 0u);
     if (ok) {
         const uint64_t loc = (uint64_t(hdr.w) << 16) | (hdr.z >> 16);  // bytes 10.. of the program: locals
         const uint32_t l0 = uint32_t(loc) & 0xFFu;
@@ -295,5 +332,229 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma_kernel(c
         }
         lr[0] = lr_next[0];
         lr[1] = lr_next[1];
+    }
+}
+
+// =================================================================================================
+// K3M3: the same contraction for THREE-path snarls.  The regression keeps the columns of path 0 and path 1 (path 2 is
+// the baseline the reference drops, snarl_analyzer.cpp:676-684), so the two M rows of a lane group (g, g + 8) are the
+// two dosage columns of ONE snarl and a warp's tile is 8 snarls of the compacted three-path list (lean_rec_kernel).
+// X^T X comes from popcounts of the class masks quant_fast<3> uses (kernels_quant.cu), X^T y from the integer MMA, and
+// the lane that ends up with a snarl's sums applies the filters (snarl_analyzer.cpp:542-579) and writes its moments —
+// no partial sums, so this kernel only runs when one CTA row covers the whole haplotype range (gridDim.y == 1).
+// Data-dependent shapes the fast formulas do not cover (a sample on 3+ path-haplotypes, an empty path, two identical
+// columns that the reference merges, :620-660) are pushed to the slow list: K3's warp-per-snarl kernel runs after this.
+// =================================================================================================
+constexpr int kMma3Tile = 8;
+
+struct Mma3Sums {
+    int c[4];
+    uint32_t cAl01, cAl2U, cN1, cNh, cN2, cHh;  // packed pairs: allele 0 | 1, allele 2 | n_used, n1, nh, n2 of col 0 | 1
+    uint32_t d01, d02, d12, bad;               // OR of the differences between columns; samples with row sum >= 3
+    double su, suu;                            // sum y, sum y^2 over the samples on no path
+    uint32_t live;
+    bool saw_unused;
+};
+
+__device__ __forceinline__ void bitslice_add(uint32_t& s0, uint32_t& s1, uint32_t& ovf, uint32_t x) {
+    const uint32_t c = s0 & x;
+    s0 ^= x;
+    ovf |= s1 & c;
+    s1 ^= c;
+}
+
+__device__ __forceinline__ void mma3_word_step(const K3MParams& q, Mma3Sums& z, uint32_t a, uint32_t b, uint32_t c,
+                                               uint32_t word, const uint8_t* bfrag) {
+    const uint32_t M = 0x55555555u;
+    const uint2 bm0 = *reinterpret_cast<const uint2*>(bfrag);
+    const uint2 bm1 = *reinterpret_cast<const uint2*>(bfrag + 256);
+    const uint32_t lo0 = a & M, hi0 = (a >> 1) & M, lo1 = b & M, hi1 = (b >> 1) & M, lo2 = c & M, hi2 = (c >> 1) & M;
+    const uint32_t c1_0 = lo0 ^ hi0, c2_0 = lo0 & hi0, c1_1 = lo1 ^ hi1, c2_1 = lo1 & hi1, c1_2 = lo2 ^ hi2, c2_2 = lo2 & hi2;
+    uint32_t s0 = lo0, s1 = 0u, ovf = 0u;  // bit-sliced row sum of the six presence bits
+    bitslice_add(s0, s1, ovf, hi0);
+    bitslice_add(s0, s1, ovf, lo1);
+    bitslice_add(s0, s1, ovf, hi1);
+    bitslice_add(s0, s1, ovf, lo2);
+    bitslice_add(s0, s1, ovf, hi2);
+    const uint32_t a1 = s0 & ~s1, a2 = s1 & ~s0, used = s0 | s1 | ovf;
+    z.bad |= ovf | (s0 & s1);
+    z.cAl01 += __popc(a) | (__popc(b) << 16);
+    z.cAl2U += __popc(c) | (__popc(used) << 16);
+    z.cN1 += __popc(c1_0 & a1) | (__popc(c1_1 & a1) << 16);
+    z.cNh += __popc(c1_0 & a2) | (__popc(c1_1 & a2) << 16);
+    z.cN2 += __popc(c2_0) | (__popc(c2_1) << 16);
+    z.cHh += __popc(c1_0 & c1_1 & a2);
+    z.d01 |= (c1_0 ^ c1_1) | (c2_0 ^ c2_1);
+    z.d02 |= (c1_0 ^ c1_2) | (c2_0 ^ c2_2);
+    z.d12 |= (c1_1 ^ c1_2) | (c2_1 ^ c2_2);
+    // 2-bit fields 2 * dosage of the two regression columns: 1 = half (one of two), 2 = the only / both haplotypes
+    const uint32_t f0 = (c1_0 & a2) | (((c1_0 & a1) | c2_0) << 1);
+    const uint32_t f1 = (c1_1 & a2) | (((c1_1 & a1) | c2_1) << 1);
+    mma_s8_16832(z.c, f0 & 0x03030303u, f1 & 0x03030303u, (f0 >> 2) & 0x03030303u, (f1 >> 2) & 0x03030303u, bm0.x, bm0.y);
+    mma_s8_16832(z.c, (f0 >> 4) & 0x03030303u, (f1 >> 4) & 0x03030303u, (f0 >> 6) & 0x03030303u, (f1 >> 6) & 0x03030303u,
+                 bm1.x, bm1.y);
+    uint32_t un = ~used & M & valid_word(word, q.k.n_hap) & z.live;
+    if (un != 0u) {
+        z.saw_unused = true;
+        while (un) {
+            const int bit = __ffs(un) - 1;
+            un &= un - 1;
+            const double yv = __ldg(q.yc + size_t(word) * 16 + (bit >> 1));
+            z.su += yv;
+            z.suu = fma(yv, yv, z.suu);
+        }
+    }
+}
+
+struct Mma3Round {
+    uint4 v[6];
+};
+__device__ __forceinline__ void mma3_load_round(const K3MParams& q, const uint4& ra, const uint4& rb, uint32_t live,
+                                                uint32_t chunk, Mma3Round& d) {
+    const K3Params& p = q.k;
+    const bool in = chunk < p.pitch / 16 && live != 0u;
+    const uint32_t rr[6] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y};
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        d.v[k] = make_uint4(0u, 0u, 0u, 0u);
+        if (in) d.v[k] = ldg_stream(reinterpret_cast<const uint4*>(p.rows + size_t(rr[k]) * p.pitch + size_t(chunk) * 16));
+    }
+}
+__device__ __forceinline__ void mma3_compute_round(const K3MParams& q, Mma3Sums& z, const Mma3Round& d, uint32_t chunk,
+                                                   const uint8_t* bfrag_round) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        mma3_word_step(q, z, u4_word(d.v[0], j) & u4_word(d.v[1], j), u4_word(d.v[2], j) & u4_word(d.v[3], j),
+                       u4_word(d.v[4], j) & u4_word(d.v[5], j), chunk * 4 + j, bfrag_round + j * 512);
+}
+
+__global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma3_kernel(const K3MParams q,
+                                                                                const uint4* __restrict__ rec3,
+                                                                                const uint32_t* __restrict__ count3) {
+    extern __shared__ __align__(128) uint8_t ysl[];
+    const K3Params& p = q.k;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const uint32_t n3 = *count3;
+    if (n3 == 0u) return;
+    const uint32_t r_len = q.n_rounds;
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(q.yslices);
+        uint4* dst = reinterpret_cast<uint4*>(ysl);
+        for (uint32_t i = tid; i < r_len * 128u; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    const uint8_t* bfrag_lane = ysl + lane * 8;
+    const uint32_t n_tiles = (n3 + kMma3Tile - 1) / kMma3Tile;
+    const uint32_t stride = gridDim.x * kMmaWarps;
+    const double sc0 = __hiloint2double(int((1023u - 7u * (2u * t + 1u)) << 20), 0);
+    const double sc1 = __hiloint2double(int((1023u - 7u * (2u * t + 2u)) << 20), 0);
+
+    for (uint32_t tile = blockIdx.x * kMmaWarps + warp; tile < n_tiles; tile += stride) {
+        const uint32_t idx = tile * kMma3Tile + g;
+        uint4 ra = make_uint4(0u, 0u, 0u, 0u), rb = ra;
+        Mma3Sums z;
+        z.live = 0u;
+        if (idx < n3) {
+            ra = __ldg(rec3 + 2 * size_t(idx));
+            rb = __ldg(rec3 + 2 * size_t(idx) + 1);
+            z.live = 0xFFFFFFFFu;
+        }
+        z.c[0] = z.c[1] = z.c[2] = z.c[3] = 0;
+        z.cAl01 = z.cAl2U = z.cN1 = z.cNh = z.cN2 = z.cHh = 0u;
+        z.d01 = z.d02 = z.d12 = z.bad = 0u;
+        z.su = z.suu = 0.0;
+        z.saw_unused = false;
+        Mma3Round da, db;
+        mma3_load_round(q, ra, rb, z.live, t, da);
+        for (uint32_t c = 0; c < r_len; c += 2) {
+            mma3_load_round(q, ra, rb, z.live, (c + 1 < r_len) ? (c + 1) * 4 + t : 0xFFFFFFF0u, db);
+            mma3_compute_round(q, z, da, c * 4 + t, bfrag_lane + size_t(c) * 2048);
+            mma3_load_round(q, ra, rb, z.live, (c + 2 < r_len) ? (c + 2) * 4 + t : 0xFFFFFFF0u, da);
+            if (c + 1 < r_len) mma3_compute_round(q, z, db, (c + 1) * 4 + t, bfrag_lane + size_t(c + 1) * 2048);
+        }
+        // ---- the 4 lanes of a group hold the pieces of one snarl ---------------------------------------------------
+        double xs[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) xs[h] = double(z.c[2 * h]) * sc0 + double(z.c[2 * h + 1]) * sc1;
+#pragma unroll
+        for (int o = 1; o <= 2; o <<= 1) {
+            z.cAl01 += __shfl_xor_sync(0xffffffffu, z.cAl01, o);
+            z.cAl2U += __shfl_xor_sync(0xffffffffu, z.cAl2U, o);
+            z.cN1 += __shfl_xor_sync(0xffffffffu, z.cN1, o);
+            z.cNh += __shfl_xor_sync(0xffffffffu, z.cNh, o);
+            z.cN2 += __shfl_xor_sync(0xffffffffu, z.cN2, o);
+            z.cHh += __shfl_xor_sync(0xffffffffu, z.cHh, o);
+            z.d01 |= __shfl_xor_sync(0xffffffffu, z.d01, o);
+            z.d02 |= __shfl_xor_sync(0xffffffffu, z.d02, o);
+            z.d12 |= __shfl_xor_sync(0xffffffffu, z.d12, o);
+            z.bad |= __shfl_xor_sync(0xffffffffu, z.bad, o);
+            xs[0] += __shfl_xor_sync(0xffffffffu, xs[0], o);
+            xs[1] += __shfl_xor_sync(0xffffffffu, xs[1], o);
+        }
+        if (__any_sync(0xffffffffu, z.saw_unused)) {
+#pragma unroll
+            for (int o = 1; o <= 2; o <<= 1) {
+                z.su += __shfl_xor_sync(0xffffffffu, z.su, o);
+                z.suu += __shfl_xor_sync(0xffffffffu, z.suu, o);
+            }
+        }
+        if (t != 0 || !z.live) continue;
+        const uint64_t s = rb.w;
+        const uint32_t p0 = rb.z;
+        const uint32_t al0 = z.cAl01 & 0xFFFFu, al1 = z.cAl01 >> 16, al2 = z.cAl2U & 0xFFFFu, n_used = z.cAl2U >> 16;
+        p.out.allele_paths[p0] = al0;  // quantitative_table.cpp:54-55
+        p.out.allele_paths[p0 + 1] = al1;
+        p.out.allele_paths[p0 + 2] = al2;
+        if (z.bad != 0u || al0 == 0u || al1 == 0u || al2 == 0u || z.d01 == 0u || z.d02 == 0u || z.d12 == 0u) {
+            p.mom[s].state = 0;
+            const uint32_t slot = atomicAdd(q.slow_count, 1u);
+            q.slow_list[slot] = uint32_t(s);
+            continue;
+        }
+        const double n1_0 = double(z.cN1 & 0xFFFFu), n1_1 = double(z.cN1 >> 16);
+        const double nh_0 = double(z.cNh & 0xFFFFu), nh_1 = double(z.cNh >> 16);
+        const double n2_0 = double(z.cN2 & 0xFFFFu), n2_1 = double(z.cN2 >> 16);
+        const double total = double(n_used);  // every used row sums to 1 (no sample with row sum >= 3)
+        const double col0 = n1_0 + 0.5 * nh_0 + n2_0, col1 = n1_1 + 0.5 * nh_1 + n2_1, col2 = total - col0 - col1;
+        bool filtered = uint64_t(n_used) < p.thr.min_individuals;
+        if (!filtered) {
+            if (total < double(p.thr.min_haplotypes)) filtered = true;
+            const double cols[3] = {col0, col1, col2};
+            int above = 0;
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const double freq = __ddiv_rn(cols[j], total);
+                const double maf = fmin(freq, __dsub_rn(1.0, freq));
+                if (maf > p.thr.maf_threshold) ++above;
+            }
+            if (above < 2) filtered = true;
+        }
+        p.out.filtered[s] = filtered ? 1 : 0;
+        p.out.n_used[s] = n_used;
+        if (filtered) {
+            p.mom[s].state = 0;
+            continue;
+        }
+        QuantMoments mom;
+#pragma unroll
+        for (int i = 0; i < 10; ++i) mom.xtx[i] = 0.0;
+        mom.xty[3] = 0.0;
+        const double su = p.sy_all - z.su, suu = p.syy_all - z.suu;
+        mom.n_used = n_used;
+        mom.p = 3;
+        mom.state = 1;
+        mom.pad = 0;
+        mom.xtx[0] = total;
+        mom.xtx[1] = col0;
+        mom.xtx[2] = n1_0 + 0.25 * nh_0 + n2_0;
+        mom.xtx[3] = col1;
+        mom.xtx[4] = 0.25 * double(z.cHh);
+        mom.xtx[5] = n1_1 + 0.25 * nh_1 + n2_1;
+        mom.xty[0] = su;
+        mom.xty[1] = 0.5 * q.y_scale * xs[0];
+        mom.xty[2] = 0.5 * q.y_scale * xs[1];
+        mom.sy = su;
+        mom.syy = suu;
+        p.mom[s] = mom;
     }
 }

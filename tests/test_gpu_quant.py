@@ -204,3 +204,50 @@ def test_sample_sharded_phases_single_gpu(gpu_ctx, oracle):
     todo = shard.deferred_snarls(res)
     n_paths = np.diff(d["paths"].snarl_path_off.astype(np.int64))
     assert set(np.flatnonzero(n_paths != 2)) <= set(todo) and todo.size < d["paths"].n_snarls // 4
+
+
+def _three_path_problem(rng, n_snarls, n_samples, frac_missing):
+    """Three-path snarls, 1 or 2 checked edges per path.  Every 11th snarl has a path nobody takes (the reference makes
+    no column for it), every 13th two paths over the SAME rows (identical columns, which the reference merges), every
+    17th a few haplotypes on two paths at once (row sums of 3)."""
+    Hn = 2 * n_samples
+    dense = np.zeros((6 * n_snarls, Hn), dtype=bool)
+    snarls = []
+    for s in range(n_snarls):
+        f = rng.dirichlet([2.0, 1.5, 1.0])
+        which = rng.choice(3, size=Hn, p=f)
+        present = rng.random(Hn) >= frac_missing
+        r = 6 * s
+        for j in range(3):
+            dense[r + 2 * j] = dense[r + 2 * j + 1] = present & (which == j)
+        if s % 11 == 5:
+            dense[r + 2] = dense[r + 3] = False
+        if s % 17 == 3:
+            both = rng.random(Hn) < 0.01
+            dense[r] |= both
+            dense[r + 1] |= both
+            dense[r + 4] |= both
+            dense[r + 5] |= both
+        paths = [[r, r + 1] if s % 3 else [r + 1], [r + 2, r + 3] if s % 5 else [r + 2], [r + 4, r + 5] if s % 2 else [r + 4]]
+        if s % 13 == 7:
+            paths[1] = list(paths[0])
+        snarls.append(paths)
+    return dense, snarls
+
+
+@pytest.mark.parametrize("seed,n_samples,frac_missing", [(41, 650, 0.01), (42, 1500, 0.3), (43, 5000, 0.005),
+                                                         (44, 7000, 0.01)])
+def test_three_path_integer_contraction(gpu_ctx, oracle, seed, n_samples, frac_missing):
+    """K3M3 (csrc/quant_mma.cuh): both regression columns of a three-path snarl from one int8 MMA, X^T X from class
+    popcounts.  Empty paths, merged columns and row sums of 3 are handed to the warp-per-snarl kernel; 14,000 haplotypes
+    need two haplotype slices, where every three-path snarl takes that kernel."""
+    rng = np.random.default_rng(seed)
+    dense, snarls = _three_path_problem(rng, 60 if n_samples >= 5000 else 240, n_samples, frac_missing)
+    y = rng.normal(size=n_samples) * 1.7 + 12.0
+    y = y + 0.6 * dense[snarls[2][0][0]].reshape(n_samples, 2).sum(1) - 0.4 * dense[snarls[2][1][0]].reshape(n_samples, 2).sum(1)
+    got, ref = run_both(gpu_ctx, oracle, dense, snarls, y, min_ind=2, min_hap=2, maf=0.01)
+    H.assert_quant_equal(got, ref)
+    assert (ref["filtered"] == 0).sum() > 20
+    # default thresholds filter some of them: the filter decisions must agree too
+    got, ref = run_both(gpu_ctx, oracle, dense, snarls, y, maf=0.2)
+    H.assert_quant_equal(got, ref)
