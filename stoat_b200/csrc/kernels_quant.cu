@@ -441,64 +441,77 @@ __global__ void __launch_bounds__(384, 1) dosage_moments_tma_kernel(const K3Para
 // =================================================================================================
 // K4: solve
 // =================================================================================================
-// state 1: moments written by K3 (warp-per-snarl kernel); state 2: two-path snarl whose class counts and sums K3R left
-// in `part` (n_slices slices, added here) — filters and moments are then built in registers (lean_finish).
-__global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __restrict__ mom, uint64_t n_snarls,
-                                                        const K3Params kp, const LeanPartials part, uint32_t n_slices,
-                                                        const uint64_t* __restrict__ snarl_path_off, QuantOut out,
-                                                        uint32_t* g_list, uint32_t* g_count, uint32_t defer,
-                                                        double* __restrict__ tail_t, double* __restrict__ tail_x,
-                                                        uint32_t* __restrict__ tail_df) {
-    // defer (sample-sharded runs): a snarl that needs more than the summed two-path partials — any other shape, a
-    // rank-deficient or near-perfect fit — is not sent to the general path (this GPU holds only some of the columns)
-    // but marked STOAT_P_DEFERRED; the host replays those snarls with all columns (stoat_b200/shard.py).
-    const uint64_t s = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (s >= n_snarls) return;
-    const uint8_t state = mom[s].state;
-    auto hand_on = [&]() {
-        if (defer & 1u) {
-            out.code[s] = kPDeferred;
-            out.filtered[s] = 0;
-        } else {
-            const uint32_t slot = atomicAdd(g_count, 1u);
-            g_list[slot] = uint32_t(s);
-        }
-    };
-    if (state != 1 && state != 2) {
-        if (defer & 1u) hand_on();
+// state 1: moments written by K3 / K3M3; state 2: two-path snarl whose class counts and sums K3M left in `part`
+// (n_slices slices, added here) — filters and moments are then built in registers (lean_finish).
+//
+// A block takes kSolveChunk consecutive snarls.  State-2 snarls (the bulk) are solved thread-per-snarl by solve_two, the
+// 2 x 2 case of xtx_inverse written out on scalars (no local-memory matrices, no loops).  State-1 snarls are only
+// collected into a shared-memory list and solved afterwards, densely packed, by the general small-matrix code: mixed
+// in the same warps they made ~80 % of the warps run both code paths (ncu r1f_k4.txt: 20 of 32 lanes active, 33 % of
+// the stalls waiting for instructions).
+constexpr int kSolveThreads = 256;
+constexpr int kSolveChunk = 1024;
+
+struct SolveArgs {
+    QuantOut out;
+    uint32_t* g_list;
+    uint32_t* g_count;
+    uint32_t defer;
+    double* tail_t;
+    double* tail_x;
+    uint32_t* tail_df;
+};
+
+__device__ __forceinline__ void solve_hand_on(const SolveArgs& a, uint64_t s) {
+    if (a.defer & 1u) {
+        a.out.code[s] = kPDeferred;
+        a.out.filtered[s] = 0;
+    } else {
+        const uint32_t slot = atomicAdd(a.g_count, 1u);
+        a.g_list[slot] = uint32_t(s);
+    }
+}
+
+// the tail of linear_regression (src/stats_test.cpp:460-489) as in ols_statistics (ols.cuh), except that the
+// Student-t tail — a continued fraction of 5 .. hundreds of iterations — is left to K4b (student_tail_kernel)
+__device__ __forceinline__ void solve_store(const SolveArgs& a, uint64_t s, int p, uint32_t n_used, double beta1,
+                                            double inv11, double rss, double tss) {
+    int df_res = int(n_used) - p + 1;  // :467 (sic)
+    if (df_res < 1) df_res = 1;        // :468
+    const double mse = rss / double(df_res);
+    const double se = sqrt(inv11 * mse);
+    const double t = beta1 / se;
+    a.out.r2[s] = 1.0 - (rss / tss);
+    a.out.beta[s] = beta1;
+    a.out.se[s] = se;
+    a.out.code[s] = kPValue;
+    if (isnan(t) || isinf(t)) {
+        a.out.p[s] = 1.0;  // :480-482
         return;
     }
-    QuantMoments m;
-    if (state == 2) {
-        LeanSums t{};
-        for (uint32_t sl = 0; sl < n_slices; ++sl) {
-            const uint32_t* pi = part.i + size_t(sl) * 7 * part.stride + s;
-            const double* pd = part.d + size_t(sl) * 3 * part.stride + s;
-            t.al0 += pi[0];
-            t.al1 += pi[part.stride];
-            t.n_used += pi[2 * part.stride];
-            t.n_full0 += pi[3 * part.stride];
-            t.n_half += pi[4 * part.stride];
-            t.n_third += pi[5 * part.stride];
-            t.n_tthird += pi[6 * part.stride];
-            t.xty1 += pd[0];
-            t.su_un += pd[part.stride];
-            t.suu_un += pd[2 * part.stride];
-        }
-        const int r = lean_finish(kp, s, uint32_t(snarl_path_off[s]), t, m);
-        if (r == 0) return;
-        if (r == 2) {
-            hand_on();
-            return;
-        }
-    } else {
-        m = mom[s];
+    // set-up of student_t_upper_tail (device_math.cuh) here, where every lane has one: the prefactor
+    // x^a (1-x)^b / B(a, b) and the argument / side of the continued fraction, which K4b then only iterates
+    const double df = double(df_res), t2 = t * t;
+    if (t2 == 0.0) {
+        a.out.p[s] = 1.0;  // 2 * 0.5
+        return;
     }
+    const double aa = 0.5 * df, bb = 0.5;
+    const double z = t2 / (df + t2);  // 1 - x
+    const double log_front = -aa * log1p(t2 / df) + bb * log(z) - log_beta_half(aa);
+    const bool upper_side = z > 1.5 / (aa + 2.5);
+    a.tail_t[s] = exp(log_front);
+    a.tail_x[s] = upper_side ? df / (df + t2) : z;
+    a.tail_df[s] = uint32_t(df_res) | (upper_side ? 0x80000000u : 0u);
+}
+
+// general case: X^T X up to 4 x 4 (ols.cuh)
+__device__ __noinline__ void solve_general(const SolveArgs& a, uint64_t s, const QuantMoments& m) {
     const int p = m.p;
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
     if (p < 2) {  // no regression column left: the reference indexes past the end (stats_test.cpp:487-489)
-        out.p[s] = out.r2[s] = out.beta[s] = out.se[s] = nan;
-        out.code[s] = kPUndef;
+        a.out.p[s] = a.out.r2[s] = a.out.beta[s] = a.out.se[s] = nan;
+        a.out.code[s] = kPUndef;
         return;
     }
     SmallMat<4> X, inv;
@@ -511,7 +524,7 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
     if (xtx_inverse<4>(X, p, inv)) {
         // rank deficient: the pseudo-inverse picks the minimum-norm solution, which is NOT invariant under the
         // centring of y used by the moment path -> redo on the general path with the raw phenotype
-        hand_on();
+        solve_hand_on(a, s);
         return;
     }
     double beta[4];
@@ -532,37 +545,105 @@ __global__ void __launch_bounds__(128) ols_solve_kernel(const QuantMoments* __re
     const double tss = m.syy - m.sy * m.sy / double(m.n_used);
     if (!(rss > 1e-6 * tss)) {
         // expansion not trustworthy (near-perfect fit): redo with explicit residuals on the general path
-        hand_on();
+        solve_hand_on(a, s);
         return;
     }
-    // the tail of linear_regression (src/stats_test.cpp:460-489) as in ols_statistics (ols.cuh), except that the
-    // Student-t tail — a continued fraction of 5 .. hundreds of iterations — is left to K4b (student_tail_kernel)
-    int df_res = int(m.n_used) - p + 1;  // :467 (sic)
-    if (df_res < 1) df_res = 1;          // :468
-    const double mse = rss / double(df_res);
-    const double se = sqrt(inv(1, 1) * mse);
-    const double t = beta[1] / se;
-    out.r2[s] = 1.0 - (rss / tss);
-    out.beta[s] = beta[1];
-    out.se[s] = se;
-    out.code[s] = kPValue;
-    if (isnan(t) || isinf(t)) {
-        out.p[s] = 1.0;  // :480-482
-    } else {
-        // set-up of student_t_upper_tail (device_math.cuh) here, where every lane has one: the prefactor
-        // x^a (1-x)^b / B(a, b) and the argument / side of the continued fraction, which K4b then only iterates
-        const double df = double(df_res), t2 = t * t;
-        if (t2 == 0.0) {
-            out.p[s] = 1.0;  // 2 * 0.5
-        } else {
-            const double a = 0.5 * df, bb = 0.5;
-            const double z = t2 / (df + t2);  // 1 - x
-            const double log_front = -a * log1p(t2 / df) + bb * log(z) - log_beta_half(a);
-            const bool upper_side = z > 1.5 / (a + 2.5);
-            tail_t[s] = exp(log_front);
-            tail_x[s] = upper_side ? df / (df + t2) : z;
-            tail_df[s] = uint32_t(df_res) | (upper_side ? 0x80000000u : 0u);
+    solve_store(a, s, p, m.n_used, beta[1], inv(1, 1), rss, tss);
+}
+
+// X^T X = [[n, c], [c, q]]: xtx_inverse<N>(.., 2, ..) of ols.cuh step by step on scalars — LDL^T with the pivot on the
+// larger diagonal entry (n >= q for dosages in [0, 1]; otherwise the general code), the two unit-vector solves, beta,
+// rss by the same expansion.  Returns false when the general code must take the snarl.
+__device__ __forceinline__ bool solve_two(const SolveArgs& a, uint64_t s, double n, double c, double q, double xty0,
+                                          double xty1, double syy, double sy, uint32_t n_used) {
+    if (fabs(q) > fabs(n)) return false;
+    const double d0 = n;
+    if (!(fabs(d0) >= 1e-10)) return false;
+    const double l = c / d0;
+    const double d1 = q - l * (d0 * l);
+    if (!(fabs(d1) >= 1e-10)) return false;  // rank deficient: decided by the general code
+    const double i11 = 1.0 / d1;
+    const double i10 = (0.0 - l) / d1;
+    const double i00 = 1.0 / d0 - l * i10;
+    const double i01 = 0.0 - l * i11;
+    const double beta0 = i00 * xty0 + i01 * xty1;
+    const double beta1 = i10 * xty0 + i11 * xty1;
+    const double bxy = beta0 * xty0 + beta1 * xty1;
+    const double r0 = n * beta0 + c * beta1, r1 = c * beta0 + q * beta1;
+    const double bxxb = beta0 * r0 + beta1 * r1;
+    const double rss = syy - 2.0 * bxy + bxxb;
+    const double tss = syy - sy * sy / double(n_used);
+    if (!(rss > 1e-6 * tss)) {
+        solve_hand_on(a, s);
+        return true;
+    }
+    solve_store(a, s, 2, n_used, beta1, i11, rss, tss);
+    return true;
+}
+
+__global__ void __launch_bounds__(kSolveThreads) ols_solve_kernel(const QuantMoments* __restrict__ mom, uint64_t n_snarls,
+                                                                  const K3Params kp, const LeanPartials part,
+                                                                  uint32_t n_slices,
+                                                                  const uint64_t* __restrict__ snarl_path_off,
+                                                                  QuantOut out, uint32_t* g_list, uint32_t* g_count,
+                                                                  uint32_t defer, double* __restrict__ tail_t,
+                                                                  double* __restrict__ tail_x,
+                                                                  uint32_t* __restrict__ tail_df) {
+    // defer (sample-sharded runs): a snarl that needs more than the summed two-path partials — any other shape, a
+    // rank-deficient or near-perfect fit — is not sent to the general path (this GPU holds only some of the columns)
+    // but marked STOAT_P_DEFERRED; the host replays those snarls with all columns (stoat_b200/shard.py).
+    __shared__ uint32_t later[kSolveChunk];
+    __shared__ uint32_t n_later;
+    const SolveArgs a{out, g_list, g_count, defer, tail_t, tail_x, tail_df};
+    if (threadIdx.x == 0) n_later = 0u;
+    __syncthreads();
+    const uint64_t base = uint64_t(blockIdx.x) * kSolveChunk;
+    for (uint32_t it = 0; it < uint32_t(kSolveChunk / kSolveThreads); ++it) {
+        const uint64_t s = base + uint64_t(it) * kSolveThreads + threadIdx.x;
+        const uint8_t state = s < n_snarls ? mom[s].state : uint8_t(0xFF);
+        bool general = state == 1;
+        if (state == 2) {
+            LeanSums t{};
+            for (uint32_t sl = 0; sl < n_slices; ++sl) {
+                const uint32_t* pi = part.i + size_t(sl) * 7 * part.stride + s;
+                const double* pd = part.d + size_t(sl) * 3 * part.stride + s;
+                t.al0 += pi[0];
+                t.al1 += pi[part.stride];
+                t.n_used += pi[2 * part.stride];
+                t.n_full0 += pi[3 * part.stride];
+                t.n_half += pi[4 * part.stride];
+                t.n_third += pi[5 * part.stride];
+                t.n_tthird += pi[6 * part.stride];
+                t.xty1 += pd[0];
+                t.su_un += pd[part.stride];
+                t.suu_un += pd[2 * part.stride];
+            }
+            QuantMoments m;
+            const int r = lean_finish(kp, s, uint32_t(snarl_path_off[s]), t, m);
+            if (r == 2) solve_hand_on(a, s);
+            // false: rank deficient (or q > n, impossible for dosage columns) — what xtx_inverse decides there
+            if (r == 1 && !solve_two(a, s, m.xtx[0], m.xtx[1], m.xtx[2], m.xty[0], m.xty[1], m.syy, m.sy, m.n_used)) {
+                const QuantMoments copy = m;  // only the copy's address escapes: m itself stays in registers
+                solve_general(a, s, copy);
+            }
+        } else if (state != 1 && state != 0xFF) {
+            if (defer & 1u) solve_hand_on(a, s);
         }
+        const uint32_t votes = __ballot_sync(0xffffffffu, general);
+        if (votes != 0u) {
+            const uint32_t lane = threadIdx.x & 31u;
+            uint32_t at = 0;
+            if (lane == 0) at = atomicAdd(&n_later, uint32_t(__popc(votes)));
+            at = __shfl_sync(0xffffffffu, at, 0);
+            if (general) later[at + __popc(votes & ((1u << lane) - 1u))] = uint32_t(s - base);
+        }
+    }
+    __syncthreads();
+    const uint32_t n_gen = n_later;
+    for (uint32_t i = threadIdx.x; i < n_gen; i += kSolveThreads) {
+        const uint64_t s = base + later[i];
+        const QuantMoments m = mom[s];
+        solve_general(a, s, m);
     }
 }
 
@@ -807,7 +888,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         K3MPlan pm;
         if (phase == 2) {
             if (!k3m_plan(pitch, m.n_cols, pm)) return cudaErrorNotSupported;
-            ols_solve_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(
+            ols_solve_kernel<<<unsigned((b.n_snarls + kSolveChunk - 1) / kSolveChunk), kSolveThreads, 0, st>>>(
                 mom, b.n_snarls, p, part, pm.n_slices, b.snarl_path_off, out, b.big_list, b.counters, 1u, tail_t, tail_x, tail_df);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             if ((e = launch_student_tail(tail_t, tail_x, tail_df, b, out.p, num_sms, st)) != cudaSuccess) return e;
@@ -927,7 +1008,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             if (ev_table_done && (e = cudaEventRecord(ev_table_done, st)) != cudaSuccess) return e;
         }
-        ols_solve_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(
+        ols_solve_kernel<<<unsigned((b.n_snarls + kSolveChunk - 1) / kSolveChunk), kSolveThreads, 0, st>>>(
             mom, b.n_snarls, p, part, n_slices, b.snarl_path_off, out, b.big_list, b.counters, 0u, tail_t, tail_x, tail_df);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         if ((e = launch_student_tail(tail_t, tail_x, tail_df, b, out.p, num_sms, st)) != cudaSuccess) return e;
