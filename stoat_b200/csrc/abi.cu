@@ -682,7 +682,7 @@ static int quant_reserve(stoat_gpu_ctx* ctx) {
     CK(x->q.lean_rec.reserve(std::max<uint64_t>(b.n_snarls * 48, 16)));  // [S] two-path records, then [S][2] three-path
     CK(x->q.tail_t.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
     CK(x->q.tail_df.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
-    CK(x->q.tail_x.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
+    CK(x->q.tail_x.reserve(std::max<uint64_t>(b.n_snarls * 16, 16)));  // [2][S]: argument, starting state
     return STOAT_GPU_OK;
 }
 

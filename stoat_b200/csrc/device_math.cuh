@@ -125,6 +125,15 @@ struct IbetaCf {
         h = d;
         m = 1;
     }
+    // resume after init(): d0 = the d (= h) init() computes (K4 does that division with all lanes busy)
+    __device__ void init_from(double a_, double b_, double x_, double d0) {
+        a = a_; b = b_; x = x_;
+        qab = a + b; qap = a + 1.0; qam = a - 1.0;
+        c = 1.0;
+        d = d0;
+        h = d0;
+        m = 1;
+    }
     __device__ bool step() {  // true: converged (or out of iterations), h is the value
         const double tiny = 1e-300;
         const double m2 = 2.0 * m;

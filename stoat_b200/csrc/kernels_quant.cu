@@ -457,9 +457,10 @@ struct SolveArgs {
     uint32_t* g_list;
     uint32_t* g_count;
     uint32_t defer;
-    double* tail_t;
-    double* tail_x;
+    double* tail_t;   // [S] prefactor / a of the fraction's side
+    double* tail_x;   // [2][S] argument x, then the state d = h the fraction starts from (IbetaCf::init)
     uint32_t* tail_df;
+    uint64_t n_snarls;
 };
 
 __device__ __forceinline__ void solve_hand_on(const SolveArgs& a, uint64_t s) {
@@ -500,8 +501,16 @@ __device__ __forceinline__ void solve_store(const SolveArgs& a, uint64_t s, int 
     const double z = t2 / (df + t2);  // 1 - x
     const double log_front = -aa * log1p(t2 / df) + bb * log(z) - log_beta_half(aa);
     const bool upper_side = z > 1.5 / (aa + 2.5);
-    a.tail_t[s] = exp(log_front);
-    a.tail_x[s] = upper_side ? df / (df + t2) : z;
+    // ... and the first step of ibeta_cf (IbetaCf::init) plus the division by a of the closing formula, so that a
+    // K4b refill and a K4b finish — executed with a handful of lanes active — contain no division at all
+    const double x = upper_side ? df / (df + t2) : z;
+    const double ca = upper_side ? aa : bb, cb = upper_side ? bb : aa;
+    double d0 = 1.0 - (ca + cb) * x / (ca + 1.0);
+    if (fabs(d0) < 1e-300) d0 = 1e-300;
+    d0 = 1.0 / d0;
+    a.tail_t[s] = exp(log_front) / ca;
+    a.tail_x[s] = x;
+    a.tail_x[a.n_snarls + s] = d0;
     a.tail_df[s] = uint32_t(df_res) | (upper_side ? 0x80000000u : 0u);
 }
 
@@ -594,7 +603,7 @@ __global__ void __launch_bounds__(kSolveThreads) ols_solve_kernel(const QuantMom
     // but marked STOAT_P_DEFERRED; the host replays those snarls with all columns (stoat_b200/shard.py).
     __shared__ uint32_t later[kSolveChunk];
     __shared__ uint32_t n_later;
-    const SolveArgs a{out, g_list, g_count, defer, tail_t, tail_x, tail_df};
+    const SolveArgs a{out, g_list, g_count, defer, tail_t, tail_x, tail_df, n_snarls};
     if (threadIdx.x == 0) n_later = 0u;
     __syncthreads();
     const uint64_t base = uint64_t(blockIdx.x) * kSolveChunk;
@@ -649,51 +658,84 @@ __global__ void __launch_bounds__(kSolveThreads) ols_solve_kernel(const QuantMom
 
 // K4b: p = 2 * P(T_df > |t|) (stats_test.cpp:484) for every snarl K4 left a prefactor for (tail_t[s] is NaN otherwise).
 // One lane = one running continued fraction (student_t_upper_tail of device_math.cuh, operation for operation); a lane
-// whose fraction has converged takes the next snarl from the shared counter, so the lanes of a warp stay in the common
-// loop body (thread-per-snarl: 6.5 of 32 lanes active, ncu r1e_k4.txt).  The refill is a few loads and one division:
-// the expensive set-up (log1p, log, exp, ln B) was done by K4 with all lanes busy.
-__global__ void __launch_bounds__(128) student_tail_kernel(const double* __restrict__ tail_t,
-                                                           const double* __restrict__ tail_x,
-                                                           const uint32_t* __restrict__ tail_df, uint32_t n_snarls,
-                                                           uint32_t* __restrict__ next, double* __restrict__ p_out) {
-    const uint32_t lane = threadIdx.x & 31;
-    bool active = false, drained = false;
+// whose fraction has converged takes the next snarl, so the lanes of a warp stay in the common loop body
+// (thread-per-snarl: 6.5 of 32 lanes active, ncu r1e_k4.txt).  The fractions are short (mean 7 iterations, median 5 on
+// the C3 data), so some lane refills in nearly every iteration: the refill must not touch global memory.  Each warp
+// therefore takes chunks of kTailChunk snarls from the shared counter, loads them coalesced, drops the snarls with
+// nothing to evaluate and keeps the rest as a queue in shared memory; a refill is a ballot, a rank and three LDS.
+// The expensive set-up (log1p, log, exp, ln B) was done by K4 with all lanes busy.
+constexpr int kTailChunk = 64;
+constexpr int kTailWarps = 4;
+__global__ void __launch_bounds__(kTailWarps * 32) student_tail_kernel(const double* __restrict__ tail_t,
+                                                                       const double* __restrict__ tail_x,
+                                                                       const uint32_t* __restrict__ tail_df,
+                                                                       uint32_t n_snarls, uint32_t* __restrict__ next,
+                                                                       double* __restrict__ p_out) {
+    __shared__ double q_front[kTailWarps][kTailChunk], q_x[kTailWarps][kTailChunk], q_d[kTailWarps][kTailChunk];
+    __shared__ uint32_t q_df[kTailWarps][kTailChunk], q_idx[kTailWarps][kTailChunk];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    bool active = false, drained = false;  // drained: warp-uniform
+    uint32_t avail = 0, taken = 0;         // the queue holds items [taken, avail) (warp-uniform)
     uint32_t snarl = 0;
     IbetaCf cf;
     double front = 0.0;
     bool upper_side = false;
     for (;;) {
-        const uint32_t need = __ballot_sync(0xffffffffu, !active && !drained);
+        const uint32_t need = __ballot_sync(0xffffffffu, !active);
         if (need) {
-            const int leader = __ffs(need) - 1;
-            uint32_t base = 0;
-            if (int(lane) == leader) base = atomicAdd(next, uint32_t(__popc(need)));
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (!active && !drained) {
-                const uint32_t w = base + __popc(need & ((1u << lane) - 1u));
-                if (w < n_snarls) {
-                    front = tail_t[w];
-                    if (!isnan(front)) {
-                        const uint32_t d = tail_df[w];
-                        const double a = 0.5 * double(d & 0x7FFFFFFFu);
-                        upper_side = (d >> 31) != 0u;
-                        if (upper_side) cf.init(a, 0.5, tail_x[w]);
-                        else cf.init(0.5, a, tail_x[w]);
-                        snarl = w;
-                        active = true;
-                    }
-                } else {
+            while (taken == avail && !drained) {  // queue empty: next chunk
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(next, uint32_t(kTailChunk));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                __syncwarp();
+                avail = taken = 0;
+                if (base >= n_snarls) {
                     drained = true;
+                    break;
+                }
+#pragma unroll
+                for (int k = 0; k < kTailChunk / 32; ++k) {
+                    const uint32_t w = base + 32u * k + lane;
+                    double f = __longlong_as_double(0x7ff8000000000000LL);
+                    if (w < n_snarls) f = tail_t[w];
+                    const bool has = !isnan(f);
+                    const uint32_t votes = __ballot_sync(0xffffffffu, has);
+                    if (has) {
+                        const uint32_t at = avail + __popc(votes & lt);
+                        q_front[warp][at] = f;
+                        q_x[warp][at] = tail_x[w];
+                        q_d[warp][at] = tail_x[size_t(n_snarls) + w];
+                        q_df[warp][at] = tail_df[w];
+                        q_idx[warp][at] = w;
+                    }
+                    avail += __popc(votes);
+                }
+                __syncwarp();
+            }
+            const uint32_t left = avail - taken;
+            if (!active) {
+                const uint32_t r = __popc(need & lt);
+                if (r < left) {
+                    const uint32_t at = taken + r;
+                    front = q_front[warp][at];
+                    const uint32_t d = q_df[warp][at];
+                    const double a = 0.5 * double(d & 0x7FFFFFFFu);
+                    upper_side = (d >> 31) != 0u;
+                    cf.init_from(upper_side ? a : 0.5, upper_side ? 0.5 : a, q_x[warp][at], q_d[warp][at]);
+                    snarl = q_idx[warp][at];
+                    active = true;
                 }
             }
+            taken += min(uint32_t(__popc(need)), left);
         }
         if (!__any_sync(0xffffffffu, active)) {
-            if (__all_sync(0xffffffffu, drained)) break;
+            if (drained && taken == avail) break;
             continue;
         }
         if (active && cf.step()) {
-            const double tail = upper_side ? 0.5 * front * cf.h / cf.a : 0.5 * (1.0 - front * cf.h / cf.a);
-            p_out[snarl] = 2.0 * tail;
+            // 2 * (0.5 * front * h / a) or 2 * 0.5 * (1 - front * h / a), front / a taken by K4
+            p_out[snarl] = upper_side ? front * cf.h : 1.0 - front * cf.h;
             active = false;
         }
     }
@@ -814,9 +856,13 @@ static cudaError_t launch_student_tail(const double* tail_t, const double* tail_
                                        const BatchDev& b, double* p_out, int num_sms, cudaStream_t st) {
     cudaError_t e = cudaMemsetAsync(b.counters + 4, 0, 4, st);
     if (e != cudaSuccess) return e;
-    const uint64_t want = (b.n_snarls + 127) / 128;
-    const unsigned blocks = unsigned(want < uint64_t(num_sms) * 8 ? want : uint64_t(num_sms) * 8);
-    student_tail_kernel<<<blocks, 128, 0, st>>>(tail_t, tail_x, tail_df, uint32_t(b.n_snarls), b.counters + 4, p_out);
+    // every warp ends with a drain of ~25 iterations in which its lanes run dry one by one, so the grid is as small as
+    // keeps the FP64 pipe busy, not as large as fits (measured, blocks per SM 1/2/3/4/6/8: 472/316/271/251/243/261 us)
+    static const int per_sm = env_int("STOAT_GPU_K4B_BLOCKS", 6);
+    const uint64_t want = (b.n_snarls + kTailWarps * kTailChunk - 1) / (kTailWarps * kTailChunk);
+    const uint64_t cap = uint64_t(num_sms) * uint64_t(per_sm < 1 ? 1 : per_sm);
+    const unsigned blocks = unsigned(want < cap ? want : cap);
+    student_tail_kernel<<<blocks, kTailWarps * 32, 0, st>>>(tail_t, tail_x, tail_df, uint32_t(b.n_snarls), b.counters + 4, p_out);
     return cudaGetLastError();
 }
 
