@@ -679,7 +679,7 @@ static int quant_reserve(stoat_gpu_ctx* ctx) {
     CK(x->q.part_i.reserve(std::max<uint64_t>(slices * 7 * b.n_snarls * 4, 16)));
     CK(x->q.part_d.reserve(std::max<uint64_t>(slices * 3 * b.n_snarls * 8, 16)));
     CK(x->q.slow.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
-    CK(x->q.lean_rec.reserve(std::max<uint64_t>(b.n_snarls * 48, 16)));  // [S] two-path records, then [S][2] three-path
+    CK(x->q.lean_rec.reserve(std::max<uint64_t>(b.n_snarls * 80, 16)));  // [S] two-path records, [S][2] three-path, [S][2] thirds
     CK(x->q.tail_t.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
     CK(x->q.tail_df.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
     CK(x->q.tail_x.reserve(std::max<uint64_t>(b.n_snarls * 16, 16)));  // [2][S]: argument, starting state

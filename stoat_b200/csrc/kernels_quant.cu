@@ -963,9 +963,13 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             // (K3M3 writes moments, not partial sums); their records live behind the two-path records
             const bool three = phase == 0 && pm.n_slices == 1 && env_int("STOAT_GPU_K3M3", 1) != 0;
             uint4* rec3 = three ? lean_rec + b.n_snarls : nullptr;
-            if (three && (e = cudaMemsetAsync(b.counters + 5, 0, 4, st)) != cudaSuccess) return e;
+            // ... and two-path snarls with dosages of 1/3, 2/3 (K3M2x), under the same conditions: [S][2] more records
+            const bool thirds = phase == 0 && pm.n_slices == 1 && env_int("STOAT_GPU_K3M2X", 1) != 0;
+            q.rec2x = thirds ? lean_rec + 3 * b.n_snarls : nullptr;
+            q.count2x = b.counters + 6;
+            if ((three || thirds) && (e = cudaMemsetAsync(b.counters + 5, 0, 8, st)) != cudaSuccess) return e;
             lean_rec_kernel<<<unsigned((b.n_snarls + 255) / 256), 256, 0, st>>>(b.rec, b.blob, b.n_snarls, lean_rec, rec3,
-                                                                                b.counters + 5);
+                                                                                b.counters + 5, q.rec2x, q.count2x);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             // attribute + occupancy query once per (device, shared-memory size): they are driver calls, not free per step
             static thread_local int cached_dev = -1, cached_occ = 1;
@@ -1015,6 +1019,28 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                 uint64_t ctas3 = uint64_t(num_sms) * uint64_t(occ3);
                 if (ctas3 > (tiles3 + kMmaWarps - 1) / kMmaWarps) ctas3 = (tiles3 + kMmaWarps - 1) / kMmaWarps;
                 dosage_moments_mma3_kernel<<<unsigned(ctas3), kMmaWarps * 32, pm.smem_bytes, st>>>(q, rec3, b.counters + 5);
+                if ((e = cudaGetLastError()) != cudaSuccess) return e;
+                if (launches) *launches += 1;
+            }
+            if (thirds) {
+                static thread_local int dev2 = -1, occ2 = 1;
+                static thread_local uint32_t smem2 = 0;
+                if (dev_now != dev2 || pm.smem_bytes != smem2) {
+                    e = cudaFuncSetAttribute(dosage_moments_mma2x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             int(pm.smem_bytes));
+                    if (e != cudaSuccess) return e;
+                    int o = 1;
+                    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, dosage_moments_mma2x_kernel, kMmaWarps * 32,
+                                                                      pm.smem_bytes) != cudaSuccess || o < 1)
+                        o = 1;
+                    dev2 = dev_now;
+                    smem2 = pm.smem_bytes;
+                    occ2 = o;
+                }
+                const uint64_t tiles2 = (b.n_snarls + kMma3Tile - 1) / kMma3Tile;
+                uint64_t ctas2 = uint64_t(num_sms) * uint64_t(occ2);
+                if (ctas2 > (tiles2 + kMmaWarps - 1) / kMmaWarps) ctas2 = (tiles2 + kMmaWarps - 1) / kMmaWarps;
+                dosage_moments_mma2x_kernel<<<unsigned(ctas2), kMmaWarps * 32, pm.smem_bytes, st>>>(q);
                 if ((e = cudaGetLastError()) != cudaSuccess) return e;
                 if (launches) *launches += 1;
             }

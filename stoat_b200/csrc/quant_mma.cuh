@@ -35,6 +35,7 @@ constexpr int kMmaMaxRounds = 24;  // rounds (4 chunks = 64 B of every row) per 
 // per snarl: the four matrix rows path 0 (r[0] & r[1]) and path 1 (r[2] & r[3]) AND; r[0] == kLeanNo: not done here
 // (r[1] != 0: the snarl has paths and goes to the slow list)
 constexpr uint32_t kLeanNo = 0xFFFFFFFFu;
+constexpr uint32_t kLeanAll = 0xFFFFFFFEu;  // rec2x: a row that every haplotype has (a path without a checked edge)
 
 struct K3MParams {
     K3Params k;
@@ -48,6 +49,8 @@ struct K3MParams {
     uint32_t* slow_list;
     uint32_t* slow_count;
     LeanPartials part;
+    uint4* rec2x;        // nullptr: snarls with non-dyadic dosages are marked for the general path instead
+    uint32_t* count2x;
 };
 
 // rec / path program -> lean record (one thread per snarl; 48 B in, 16 B out)
@@ -55,7 +58,8 @@ struct K3MParams {
 // order free: the results are stored by snarl) for dosage_moments_mma3_kernel, and nothing for the slow list.
 __global__ void __launch_bounds__(256) lean_rec_kernel(const SnarlRec* __restrict__ rec, const uint8_t* __restrict__ blob,
                                                        uint64_t n_snarls, uint4* __restrict__ out, uint4* __restrict__ rec3,
-                                                       uint32_t* __restrict__ count3) {
+                                                       uint32_t* __restrict__ count3, uint4* __restrict__ rec2x,
+                                                       uint32_t* __restrict__ count2x) {
     const uint64_t s = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     const bool in = s < n_snarls;
     SnarlRec r{};
@@ -94,9 +98,42 @@ __global__ void __launch_bounds__(256) lean_rec_kernel(const SnarlRec* __restric
             rec3[2 * size_t(slot) + 1] = make_uint4(rows6[4], rows6[5], hdr.y, uint32_t(s));
         }
     }
+    // Two paths of which one has no checked edge (it matches every haplotype, snarl_analyzer.cpp:343-354): every sample
+    // that takes the other path sits on three or four path-haplotypes -> dosages 1/3, 1/2: the 2x kernel (rec2x != nullptr)
+    const bool c0ok = code0 <= 2u, c1ok = code1 <= 2u;
+    const bool ok2x = in && rec2x != nullptr && r.n_rows != 0 && np == 2u && c0ok && c1ok && (code0 == 0u) != (code1 == 0u);
+    {
+        const uint32_t votes = __ballot_sync(0xffffffffu, ok2x);
+        uint32_t base = 0;
+        const uint32_t lane = threadIdx.x & 31u;
+        if (votes != 0u) {
+            if (lane == 0) base = atomicAdd(count2x, uint32_t(__popc(votes)));
+            base = __shfl_sync(0xffffffffu, base, 0);
+        }
+        if (ok2x) {
+            const uint8_t* loc = blob + size_t(r.blob16) * 16 + kBlobHeaderQ + 2;
+            uint32_t rows4[4];
+            uint32_t off = 0;
+            const uint32_t codes[2] = {code0, code1};
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                if (codes[j] == 0u) {
+                    rows4[2 * j] = rows4[2 * j + 1] = kLeanAll;
+                } else {
+                    const uint32_t la = loc[off], lb = (codes[j] == 2u) ? loc[off + 1] : la;
+                    rows4[2 * j] = r.rows[la];
+                    rows4[2 * j + 1] = r.rows[lb];
+                }
+                off += codes[j];
+            }
+            const uint32_t slot = base + uint32_t(__popc(votes & ((1u << lane) - 1u)));
+            rec2x[2 * size_t(slot)] = make_uint4(rows4[0], rows4[1], rows4[2], rows4[3]);
+            rec2x[2 * size_t(slot) + 1] = make_uint4(0u, 0u, hdr.y, uint32_t(s));
+        }
+    }
     if (!in) return;
     const bool ok = r.n_rows != 0 && np == 2u && (code0 == 1u || code0 == 2u) && (code1 == 1u || code1 == 2u);
-    uint4 o = make_uint4(kLeanNo, (np != 0u && !ok3) ? 1u : 0u, 0u, 0u);
+    uint4 o = make_uint4(kLeanNo, (np != 0u && !ok3 && !ok2x) ? 1u : 0u, hdr.y, 0u);
     if (ok) {
         const uint64_t loc = (uint64_t(hdr.w) << 16) | (hdr.z >> 16);  // bytes 10.. of the program: locals
         const uint32_t l0 = uint32_t(loc) & 0xFFu;
@@ -165,6 +202,14 @@ __device__ __forceinline__ void mma_word_step(const K3MParams& q, MmaLaneSums& z
             }
         }
     }
+}
+
+// rare, and kept out of line so that it does not take part in the register allocation of the K3M loop
+__device__ __noinline__ void mma_push_thirds(uint4* rec2x, uint32_t* count2x, QuantMoments* mom, uint32_t s, uint4 rows) {
+    mom[s].state = 0;
+    const uint32_t slot = atomicAdd(count2x, 1u);
+    rec2x[2 * size_t(slot)] = rows;
+    rec2x[2 * size_t(slot) + 1] = make_uint4(0u, 0u, 0u, s);
 }
 
 // the 64 bytes (4 words) of chunk 4 * round + t of the four rows of both snarls
@@ -307,7 +352,10 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma_kernel(c
             for (int h = 0; h < 2; ++h) {
                 const uint64_t s = tile * kMmaTile + g + 8u * h;
                 if (s >= p.n_snarls) continue;
-                if (z.live[h]) {
+                if (z.live[h] && z.nd[h] != 0u && q.rec2x != nullptr) {
+                    // a sample on three path-haplotypes (overlapping paths): dosages of 1/3, 2/3 -> the 2x kernel
+                    mma_push_thirds(q.rec2x, q.count2x, p.mom, uint32_t(s), lr[h]);
+                } else if (z.live[h]) {
                     uint32_t* pi = q.part.i + size_t(slice) * 7 * q.part.stride + s;
                     double* pd = q.part.d + size_t(slice) * 3 * q.part.stride + s;
                     pi[0] = z.cA[h] & 0xFFFFu;
@@ -556,5 +604,165 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma3_kernel(
         mom.sy = su;
         mom.syy = suu;
         p.mom[s] = mom;
+    }
+}
+
+// =================================================================================================
+// K3M2x: two-path snarls with NON-DYADIC dosages — a sample on three path-haplotypes has d0 = 1/3 or 2/3.  That is every
+// carrier of the other path when one path has no checked edge ('*', it matches everybody: known from the path program,
+// lean_rec_kernel lists those), and the occasional sample of a snarl with overlapping paths (K3M meets them and lists
+// the snarl).  The two M rows of a lane group are the two halves of ONE snarl's dosage column: 2d over the dyadic
+// classes (half, full) and 3d over the thirds (third, two thirds), so  sum d y = scale * (C_A / 2 + C_B / 3)  with both
+// contractions exact integers.  Class counts as in quant_lean2; filters and moments by lean_finish.  One haplotype slice
+// only (like K3M3).
+// =================================================================================================
+struct Mma2xSums {
+    int c[4];
+    uint32_t cAl, cUF, cHT, cTT;  // al0 | al1, n_used | n_full0, n_half | n_third, n_tthird
+    double su, suu;
+    uint32_t live;
+    bool saw_unused;
+};
+
+__device__ __forceinline__ void mma2x_word_step(const K3MParams& q, Mma2xSums& z, uint32_t a, uint32_t b, uint32_t word,
+                                                const uint8_t* bfrag) {
+    const uint2 bm0 = *reinterpret_cast<const uint2*>(bfrag);
+    const uint2 bm1 = *reinterpret_cast<const uint2*>(bfrag + 256);
+    const LeanMasks m = lean_masks(a, b);
+    z.cAl += __popc(a) | (__popc(b) << 16);
+    z.cUF += __popc(m.used) | (__popc(m.full0) << 16);
+    z.cHT += __popc(m.half) | (__popc(m.third) << 16);
+    z.cTT += __popc(m.tthird);
+    const uint32_t f0 = m.half | (m.full0 << 1);    // 2 * d0 where it is 1/2 or 1
+    const uint32_t f1 = m.third | (m.tthird << 1);  // 3 * d0 where it is 1/3 or 2/3
+    mma_s8_16832(z.c, f0 & 0x03030303u, f1 & 0x03030303u, (f0 >> 2) & 0x03030303u, (f1 >> 2) & 0x03030303u, bm0.x, bm0.y);
+    mma_s8_16832(z.c, (f0 >> 4) & 0x03030303u, (f1 >> 4) & 0x03030303u, (f0 >> 6) & 0x03030303u, (f1 >> 6) & 0x03030303u,
+                 bm1.x, bm1.y);
+    uint32_t un = ~m.used & 0x55555555u & valid_word(word, q.k.n_hap) & z.live;
+    if (un != 0u) {
+        z.saw_unused = true;
+        while (un) {
+            const int bit = __ffs(un) - 1;
+            un &= un - 1;
+            const double yv = __ldg(q.yc + size_t(word) * 16 + (bit >> 1));
+            z.su += yv;
+            z.suu = fma(yv, yv, z.suu);
+        }
+    }
+}
+
+struct Mma2xRound {
+    uint4 v[4];
+};
+__device__ __forceinline__ void mma2x_load_round(const K3MParams& q, const uint4& ra, uint32_t live, uint32_t chunk,
+                                                 Mma2xRound& d) {
+    const K3Params& p = q.k;
+    const bool in = chunk < p.pitch / 16 && live != 0u;
+    const uint32_t rr[4] = {ra.x, ra.y, ra.z, ra.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        d.v[k] = make_uint4(0u, 0u, 0u, 0u);
+        if (in) {
+            if (rr[k] == kLeanAll)
+                d.v[k] = make_uint4(valid_word(4 * chunk, p.n_hap), valid_word(4 * chunk + 1, p.n_hap),
+                                    valid_word(4 * chunk + 2, p.n_hap), valid_word(4 * chunk + 3, p.n_hap));
+            else
+                d.v[k] = ldg_stream(reinterpret_cast<const uint4*>(p.rows + size_t(rr[k]) * p.pitch + size_t(chunk) * 16));
+        }
+    }
+}
+__device__ __forceinline__ void mma2x_compute_round(const K3MParams& q, Mma2xSums& z, const Mma2xRound& d, uint32_t chunk,
+                                                    const uint8_t* bfrag_round) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        mma2x_word_step(q, z, u4_word(d.v[0], j) & u4_word(d.v[1], j), u4_word(d.v[2], j) & u4_word(d.v[3], j),
+                        chunk * 4 + j, bfrag_round + j * 512);
+}
+
+__global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma2x_kernel(const K3MParams q) {
+    extern __shared__ __align__(128) uint8_t ysl[];
+    const K3Params& p = q.k;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const uint32_t n2 = *q.count2x;
+    if (n2 == 0u) return;
+    const uint32_t r_len = q.n_rounds;
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(q.yslices);
+        uint4* dst = reinterpret_cast<uint4*>(ysl);
+        for (uint32_t i = tid; i < r_len * 128u; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    const uint8_t* bfrag_lane = ysl + lane * 8;
+    const uint32_t n_tiles = (n2 + kMma3Tile - 1) / kMma3Tile;
+    const uint32_t stride = gridDim.x * kMmaWarps;
+    const double sc0 = __hiloint2double(int((1023u - 7u * (2u * t + 1u)) << 20), 0);
+    const double sc1 = __hiloint2double(int((1023u - 7u * (2u * t + 2u)) << 20), 0);
+
+    for (uint32_t tile = blockIdx.x * kMmaWarps + warp; tile < n_tiles; tile += stride) {
+        const uint32_t idx = tile * kMma3Tile + g;
+        uint4 ra = make_uint4(0u, 0u, 0u, 0u), rb = ra;
+        Mma2xSums z;
+        z.live = 0u;
+        if (idx < n2) {
+            ra = __ldcg(q.rec2x + 2 * size_t(idx));  // written by the kernels before this one
+            rb = __ldcg(q.rec2x + 2 * size_t(idx) + 1);
+            z.live = 0xFFFFFFFFu;
+        }
+        z.c[0] = z.c[1] = z.c[2] = z.c[3] = 0;
+        z.cAl = z.cUF = z.cHT = z.cTT = 0u;
+        z.su = z.suu = 0.0;
+        z.saw_unused = false;
+        Mma2xRound da, db;
+        mma2x_load_round(q, ra, z.live, t, da);
+        for (uint32_t c = 0; c < r_len; c += 2) {
+            mma2x_load_round(q, ra, z.live, (c + 1 < r_len) ? (c + 1) * 4 + t : 0xFFFFFFF0u, db);
+            mma2x_compute_round(q, z, da, c * 4 + t, bfrag_lane + size_t(c) * 2048);
+            mma2x_load_round(q, ra, z.live, (c + 2 < r_len) ? (c + 2) * 4 + t : 0xFFFFFFF0u, da);
+            if (c + 1 < r_len) mma2x_compute_round(q, z, db, (c + 1) * 4 + t, bfrag_lane + size_t(c + 1) * 2048);
+        }
+        double xs[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) xs[h] = double(z.c[2 * h]) * sc0 + double(z.c[2 * h + 1]) * sc1;
+#pragma unroll
+        for (int o = 1; o <= 2; o <<= 1) {
+            z.cAl += __shfl_xor_sync(0xffffffffu, z.cAl, o);
+            z.cUF += __shfl_xor_sync(0xffffffffu, z.cUF, o);
+            z.cHT += __shfl_xor_sync(0xffffffffu, z.cHT, o);
+            z.cTT += __shfl_xor_sync(0xffffffffu, z.cTT, o);
+            xs[0] += __shfl_xor_sync(0xffffffffu, xs[0], o);
+            xs[1] += __shfl_xor_sync(0xffffffffu, xs[1], o);
+        }
+        if (__any_sync(0xffffffffu, z.saw_unused)) {
+#pragma unroll
+            for (int o = 1; o <= 2; o <<= 1) {
+                z.su += __shfl_xor_sync(0xffffffffu, z.su, o);
+                z.suu += __shfl_xor_sync(0xffffffffu, z.suu, o);
+            }
+        }
+        if (t != 0 || !z.live) continue;
+        const uint64_t s = rb.w;
+        const uint32_t p0 = *reinterpret_cast<const uint32_t*>(p.blob + size_t(p.rec[s].blob16) * 16 + 4);
+        LeanSums ls;
+        ls.al0 = z.cAl & 0xFFFFu;
+        ls.al1 = z.cAl >> 16;
+        ls.n_used = z.cUF & 0xFFFFu;
+        ls.n_full0 = z.cUF >> 16;
+        ls.n_half = z.cHT & 0xFFFFu;
+        ls.n_third = z.cHT >> 16;
+        ls.n_tthird = z.cTT;
+        ls.xty1 = q.y_scale * (0.5 * xs[0] + (1.0 / 3.0) * xs[1]);
+        ls.su_un = z.su;
+        ls.suu_un = z.suu;
+        QuantMoments mom;
+        const int r = lean_finish(p, s, p0, ls, mom);
+        if (r == 1) {
+            p.mom[s] = mom;
+        } else {
+            p.mom[s].state = 0;
+            if (r == 2) {  // a filter decision within rounding of its threshold: the general path replays the reference's sums
+                const uint32_t slot = atomicAdd(p.g_count, 1u);
+                p.g_list[slot] = uint32_t(s);
+            }
+        }
     }
 }
