@@ -18,7 +18,9 @@ ncu --set full --clock-control none --import-source on -k regex:binary_stats -s 
 BQ="python bench.py --trait quantitative --steps 1 --warmup 3 --no-cpu-baseline --no-e2e"
 $BQ > $OUT/plain_quant.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k "$K" -c 100 --csv --log-file $OUT/launches_quant.csv $BQ > $OUT/ncu_launches_quant.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:dosage_moments_mma -s 3 -c 1 -f -o $OUT/prof_k3m $BQ > $OUT/ncu_k3m.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:dosage_moments_mma_kernel -s 3 -c 1 -f -o $OUT/prof_k3m $BQ > $OUT/ncu_k3m.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:dosage_moments_mma3_kernel -s 3 -c 1 -f -o $OUT/prof_k3m3 $BQ > $OUT/ncu_k3m3.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:student_tail -s 3 -c 1 -f -o $OUT/prof_k4b $BQ > $OUT/ncu_k4b.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:ols_solve -s 3 -c 1 -f -o $OUT/prof_k4 $BQ > $OUT/ncu_k4.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:dosage_moments_tma -s 3 -c 1 -f -o $OUT/prof_k3 $BQ > $OUT/ncu_k3.log 2>&1
 ls -la $OUT

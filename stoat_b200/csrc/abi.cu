@@ -53,6 +53,7 @@ struct QuantState {
     DevBuf yc, ys, mom, part_i, part_d, slow, yslices, lean_rec, tail_t, tail_x, tail_df;
     double sy_all = 0.0, syy_all = 0.0, y_scale = 1.0;
     bool have_partials = false;
+    uint64_t lean_key = 0;  // what lean_rec holds: staging generation + participating kernels (launch_quantitative_impl)
 };
 
 }  // namespace
@@ -63,6 +64,7 @@ constexpr int kMaxRunChunks = 8;  // chunks of an overlapped binary run (stoat_g
 struct CtxExtra {
     QuantState q;
     uint32_t max_stage_rows = 0;
+    uint64_t stage_gen = 0;  // bumped by every stage_paths
     uint32_t counters_host[4] = {0, 0, 0, 0};
     uint32_t readback[2] = {0, 0};
     uint32_t fisher_readback[2 * kMaxRunChunks] = {};
@@ -227,7 +229,8 @@ int stoat_gpu_set_matrix_pairs(stoat_gpu_ctx* ctx, const uint32_t* rows, const u
     ctx->timing = stoat_gpu_timing{};
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     CK(cudaMemsetAsync(ctx->rows.p, 0, std::max<uint64_t>(n_rows * pitch, 16), ctx->stream));
-    CK(cudaMemsetAsync(ctx->d_counters.p, 0, 32, ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_counters.as<uint32_t>() + 1, 0, 4, ctx->stream));  // the scatter's error flag only
+    extra_of(ctx)->q.lean_key = 0;
     // pairs go up in chunks through the two staging buffers: the copy of chunk k + 1 overlaps the scatter of chunk k
     const uint64_t chunk = 1ull << 25;  // 32M pairs = 256 MB
     CtxExtra* x = extra_of(ctx);
@@ -459,6 +462,7 @@ int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths) {
     ctx->have_batch = false;
     ctx->have_binary_counts = ctx->have_binary_result = ctx->have_quant_result = false;
     extra_of(ctx)->q.have_partials = false;
+    ++x->stage_gen;  // lean records of the previous staging are stale
     CK(ctx->d_snarl_path_off.reserve((S + 1) * 8));
     CK(ctx->d_path_edge_off.reserve((P + 1) * 8));
     CK(ctx->d_edge_row.reserve(std::max<uint64_t>(E * 4, 16)));
@@ -466,7 +470,7 @@ int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths) {
     const uint64_t blob_bytes = 16 * (2 * S + ((P + E) >> 4) + 2 + kMaxBlob16);
     CK(ctx->d_blob.reserve(blob_bytes));
     CK(ctx->d_big.reserve(std::max<uint64_t>(S * 4, 16)));
-    CK(ctx->d_counters.reserve(32));  // [0..3] see BatchDev, [4] K4b's work counter
+    CK(ctx->d_counters.reserve(32));  // [0..3] see BatchDev, [4] thirds appended by K3M, [5] [6] three-path / thirds records, [7] K4b work counter
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     const uint64_t zero = 0;
     if (S) {
@@ -703,8 +707,8 @@ static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int ph
     // the general-path list grows during the run: reset its length to what prep put there
     x->counters_host[0] = ctx->n_big;
     CK(cudaMemcpyAsync(ctx->d_counters.p, x->counters_host, 4, cudaMemcpyHostToDevice, ctx->stream));
-    // filtered snarls keep NaN / NA outputs
-    if (S && phase != 1) {
+    // filtered snarls keep NaN / NA outputs (the moments path writes them in K4, which visits every snarl)
+    if (S && phase != 1 && !quant_fast_path(ctx->pitch, x->max_stage_rows, ctx->k1_variant, uint32_t(ctx->n_covar))) {
         CK(cudaMemsetAsync(ctx->q_p.p, 0xFF, S * 8, ctx->stream));
         CK(cudaMemsetAsync(ctx->q_r2.p, 0xFF, S * 8, ctx->stream));
         CK(cudaMemsetAsync(ctx->q_beta.p, 0xFF, S * 8, ctx->stream));
@@ -725,7 +729,7 @@ static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int ph
                                 x->q.yslices.as<uint8_t>(),
                                 x->q.yc.as<double>(), x->q.y_scale, ctx->num_sms, ctx->k1_variant, ctx->stream,
                                 &ctx->timing.launches, ctx->ev[4], phase, x->q.tail_t.as<double>(),
-                                x->q.tail_x.as<double>(), x->q.tail_df.as<uint32_t>()));
+                                x->q.tail_x.as<double>(), x->q.tail_df.as<uint32_t>(), x->stage_gen, &x->q.lean_key));
     if (phase == 2) CK(cudaEventRecord(ctx->ev[4], ctx->stream));
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
     CK(cudaMemcpyAsync(x->readback, ctx->d_counters.p, 4, cudaMemcpyDeviceToHost, ctx->stream));

@@ -611,6 +611,17 @@ __global__ void __launch_bounds__(kSolveThreads) ols_solve_kernel(const QuantMom
         const uint64_t s = base + uint64_t(it) * kSolveThreads + threadIdx.x;
         const uint8_t state = s < n_snarls ? mom[s].state : uint8_t(0xFF);
         bool general = state == 1;
+        if (s < n_snarls) {
+            // the outputs of a snarl nobody solves (filtered, or handed on) — this kernel visits every snarl, so it
+            // replaces six memsets per step; whoever solves the snarl (below, K4b, the general path) writes later
+            const double na = __longlong_as_double(-1LL);
+            out.p[s] = na;
+            out.r2[s] = na;
+            out.beta[s] = na;
+            out.se[s] = na;
+            out.code[s] = kPNa;
+            tail_t[s] = na;
+        }
         if (state == 2) {
             LeanSums t{};
             for (uint32_t sl = 0; sl < n_slices; ++sl) {
@@ -842,6 +853,11 @@ static bool k3m_plan(uint32_t pitch, uint64_t n_hap, K3MPlan& pl) {
     pl.smem_bytes = pl.rounds_per_slice * 2048;
     return true;
 }
+// true: launch_quantitative_impl takes the moments path, whose K4 initialises the outputs itself
+bool quant_fast_path(uint64_t pitch, uint32_t max_stage_rows, int variant, uint32_t n_covar) {
+    K3Config cfg{};
+    return variant == 0 && n_covar == 0 && choose_k3_config(uint32_t(pitch), max_stage_rows, cfg);
+}
 size_t quant_yslices_bytes(uint64_t pitch) { return size_t((pitch / 16 + 3) / 4) * 2048; }
 // slices of the haplotype range the two-path kernel uses (sizes the partial-sum buffers); 0: neither K3M nor K3R
 uint32_t quant_lean_slices(uint64_t pitch, uint64_t n_hap, uint32_t stage_rows) {
@@ -851,10 +867,10 @@ uint32_t quant_lean_slices(uint64_t pitch, uint64_t n_hap, uint32_t stage_rows) 
     return quant_reg_slices(pitch);
 }
 
-// K4b over every snarl of the batch (tail_t[s] NaN: nothing to do); counters[4] is the shared work counter
+// K4b over every snarl of the batch (tail_t[s] NaN: nothing to do); counters[7] is the shared work counter
 static cudaError_t launch_student_tail(const double* tail_t, const double* tail_x, const uint32_t* tail_df,
                                        const BatchDev& b, double* p_out, int num_sms, cudaStream_t st) {
-    cudaError_t e = cudaMemsetAsync(b.counters + 4, 0, 4, st);
+    cudaError_t e = cudaMemsetAsync(b.counters + 7, 0, 4, st);
     if (e != cudaSuccess) return e;
     // every warp ends with a drain of ~25 iterations in which its lanes run dry one by one, so the grid is as small as
     // keeps the FP64 pipe busy, not as large as fits (measured, blocks per SM 1/2/3/4/6/8: 472/316/271/251/243/261 us)
@@ -862,7 +878,7 @@ static cudaError_t launch_student_tail(const double* tail_t, const double* tail_
     const uint64_t want = (b.n_snarls + kTailWarps * kTailChunk - 1) / (kTailWarps * kTailChunk);
     const uint64_t cap = uint64_t(num_sms) * uint64_t(per_sm < 1 ? 1 : per_sm);
     const unsigned blocks = unsigned(want < cap ? want : cap);
-    student_tail_kernel<<<blocks, kTailWarps * 32, 0, st>>>(tail_t, tail_x, tail_df, uint32_t(b.n_snarls), b.counters + 4, p_out);
+    student_tail_kernel<<<blocks, kTailWarps * 32, 0, st>>>(tail_t, tail_x, tail_df, uint32_t(b.n_snarls), b.counters + 7, p_out);
     return cudaGetLastError();
 }
 
@@ -875,7 +891,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                                      uint32_t* slow_list, uint4* lean_rec, const uint8_t* yslices, const double* yc,
                                      double y_scale, int num_sms, int variant, cudaStream_t st, uint32_t* launches,
                                      cudaEvent_t ev_table_done, int phase, double* tail_t, double* tail_x,
-                                     uint32_t* tail_df) {
+                                     uint32_t* tail_df, uint64_t stage_gen, uint64_t* lean_key) {
     // phase 0: the whole step.  Sample-sharded runs split it around the all-reduce of the partial sums:
     // phase 1 = lean records + K3M only, phase 2 = K4 on the summed partials with everything else deferred to the host.
     if (b.n_snarls == 0) return cudaSuccess;
@@ -958,7 +974,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             q.slow_count = b.counters + 3;
             q.part = part;
             n_slices = pm.n_slices;
-            if ((e = cudaMemsetAsync(b.counters + 3, 0, 4, st)) != cudaSuccess) return e;
+            if ((e = cudaMemsetAsync(b.counters + 3, 0, 8, st)) != cudaSuccess) return e;
             // three-path snarls: K3M3 when one CTA row covers the haplotype range and the step is not sample-sharded
             // (K3M3 writes moments, not partial sums); their records live behind the two-path records
             const bool three = phase == 0 && pm.n_slices == 1 && env_int("STOAT_GPU_K3M3", 1) != 0;
@@ -967,10 +983,20 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             const bool thirds = phase == 0 && pm.n_slices == 1 && env_int("STOAT_GPU_K3M2X", 1) != 0;
             q.rec2x = thirds ? lean_rec + 3 * b.n_snarls : nullptr;
             q.count2x = b.counters + 6;
-            if ((three || thirds) && (e = cudaMemsetAsync(b.counters + 5, 0, 8, st)) != cudaSuccess) return e;
-            lean_rec_kernel<<<unsigned((b.n_snarls + 255) / 256), 256, 0, st>>>(b.rec, b.blob, b.n_snarls, lean_rec, rec3,
-                                                                                b.counters + 5, q.rec2x, q.count2x);
-            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            q.count2x_dyn = b.counters + 4;
+            // the records depend on the staged paths and on which kernels take part, not on the phenotype or the
+            // matrix: a caller that runs many steps on one staging (lean_key) builds them once.  What K3M appends to
+            // the thirds list during a step is counted apart (counters[4], zeroed with the slow list's length)
+            const uint64_t key = (stage_gen << 3) | 4u | (three ? 2u : 0u) | (thirds ? 1u : 0u);
+            const bool cached = lean_key != nullptr && *lean_key == key;
+            if (!cached) {
+                if ((three || thirds) && (e = cudaMemsetAsync(b.counters + 5, 0, 8, st)) != cudaSuccess) return e;
+                lean_rec_kernel<<<unsigned((b.n_snarls + 255) / 256), 256, 0, st>>>(b.rec, b.blob, b.n_snarls, lean_rec,
+                                                                                    rec3, b.counters + 5, q.rec2x, q.count2x);
+                if ((e = cudaGetLastError()) != cudaSuccess) return e;
+                if (lean_key) *lean_key = key;
+                if (launches) *launches += 1;
+            }
             // attribute + occupancy query once per (device, shared-memory size): they are driver calls, not free per step
             static thread_local int cached_dev = -1, cached_occ = 1;
             static thread_local uint32_t cached_smem = 0;
@@ -998,7 +1024,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             dosage_moments_mma_kernel<<<dim3(unsigned(ctas), pm.n_slices), kMmaWarps * 32, pm.smem_bytes, st>>>(q);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             if (ev_table_done && (e = cudaEventRecord(ev_table_done, st)) != cudaSuccess) return e;
-            if (launches) *launches += 2;
+            if (launches) *launches += 1;
             if (phase == 1) return cudaSuccess;
             if (three) {
                 static thread_local int dev3 = -1, occ3 = 1;

@@ -50,7 +50,8 @@ struct K3MParams {
     uint32_t* slow_count;
     LeanPartials part;
     uint4* rec2x;        // nullptr: snarls with non-dyadic dosages are marked for the general path instead
-    uint32_t* count2x;
+    uint32_t* count2x;      // records lean_rec_kernel listed (fixed for a staging)
+    uint32_t* count2x_dyn;  // records K3M appended behind them during this step
 };
 
 // rec / path program -> lean record (one thread per snarl; 48 B in, 16 B out)
@@ -205,9 +206,10 @@ __device__ __forceinline__ void mma_word_step(const K3MParams& q, MmaLaneSums& z
 }
 
 // rare, and kept out of line so that it does not take part in the register allocation of the K3M loop
-__device__ __noinline__ void mma_push_thirds(uint4* rec2x, uint32_t* count2x, QuantMoments* mom, uint32_t s, uint4 rows) {
+__device__ __noinline__ void mma_push_thirds(uint4* rec2x, const uint32_t* count2x, uint32_t* count2x_dyn, QuantMoments* mom,
+                                             uint32_t s, uint4 rows) {
     mom[s].state = 0;
-    const uint32_t slot = atomicAdd(count2x, 1u);
+    const uint32_t slot = *count2x + atomicAdd(count2x_dyn, 1u);
     rec2x[2 * size_t(slot)] = rows;
     rec2x[2 * size_t(slot) + 1] = make_uint4(0u, 0u, 0u, s);
 }
@@ -354,7 +356,7 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma_kernel(c
                 if (s >= p.n_snarls) continue;
                 if (z.live[h] && z.nd[h] != 0u && q.rec2x != nullptr) {
                     // a sample on three path-haplotypes (overlapping paths): dosages of 1/3, 2/3 -> the 2x kernel
-                    mma_push_thirds(q.rec2x, q.count2x, p.mom, uint32_t(s), lr[h]);
+                    mma_push_thirds(q.rec2x, q.count2x, q.count2x_dyn, p.mom, uint32_t(s), lr[h]);
                 } else if (z.live[h]) {
                     uint32_t* pi = q.part.i + size_t(slice) * 7 * q.part.stride + s;
                     double* pd = q.part.d + size_t(slice) * 3 * q.part.stride + s;
@@ -683,7 +685,7 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma2x_kernel
     extern __shared__ __align__(128) uint8_t ysl[];
     const K3Params& p = q.k;
     const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
-    const uint32_t n2 = *q.count2x;
+    const uint32_t n2 = *q.count2x + *q.count2x_dyn;
     if (n2 == 0u) return;
     const uint32_t r_len = q.n_rounds;
     {
