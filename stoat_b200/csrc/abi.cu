@@ -5,6 +5,7 @@
 // sm_100 GPU every entry point fails (there is no CPU fallback).
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -736,6 +737,13 @@ static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int ph
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->timing.n_general = S ? x->readback[0] : 0;
     ctx->timing.n_fisher = 0;
+    if (S && x->readback[0] && std::getenv("STOAT_GPU_DEBUG_GENERAL")) {  // which snarls took the general path
+        std::vector<uint32_t> ids(std::min<uint32_t>(x->readback[0], 64));
+        CK(cudaMemcpy(ids.data(), ctx->batch.big_list, ids.size() * 4, cudaMemcpyDeviceToHost));
+        std::fprintf(stderr, "[stoat_gpu] general path: %u snarls:", x->readback[0]);
+        for (uint32_t id : ids) std::fprintf(stderr, " %u", id);
+        std::fprintf(stderr, "\n");
+    }
     if (S) {
         CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[4]));  // the moments pass (K3M / K3R / K3)
         CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ctx->ev[4], ctx->ev[3]));  // left-over list, K4, general path

@@ -653,6 +653,53 @@ __device__ __forceinline__ void mma2x_word_step(const K3MParams& q, Mma2xSums& z
     }
 }
 
+// The filters of a two-path snarl whose decision lies within rounding of a threshold (lean_finish returned 2): exact
+// replay of filtration_quantitative_table's accumulation order (src/snarl_analyzer.cpp:558-576) — `total` is ONE running
+// sum over (sample, column), the column sums run down the samples — with the table entries count / row sum of
+// quantitative_table.cpp:93.  With thirds in the table the outcome of `maf > threshold` at an exact tie (250 carriers
+// x 1/3 against 0.05 x 5000 ...) depends on how those 5000 additions round.  One lane, serial by definition: three
+// independent chains of FP64 additions, ~0.1 ms — the general path took 1.4 ms for the same replay.
+struct ExactArgs {
+    const uint8_t* rows;
+    uint32_t pitch, n_hap;
+    double min_haplotypes, maf_threshold;
+};
+__device__ __noinline__ bool lean_exact_filtered(const ExactArgs p, uint4 rows) {
+    const uint32_t rr[4] = {rows.x, rows.y, rows.z, rows.w};
+    const uint32_t n_words = (p.n_hap + 31u) / 32u;
+    const double third = 1.0 / 3.0, two_thirds = 2.0 / 3.0;
+    double cs0 = 0.0, cs1 = 0.0, tot = 0.0;
+    for (uint32_t w = 0; w < n_words; ++w) {
+        uint32_t v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            v[k] = rr[k] == kLeanAll ? 0xFFFFFFFFu
+                                     : __ldg(reinterpret_cast<const uint32_t*>(p.rows + size_t(rr[k]) * p.pitch) + w);
+        const uint32_t valid = valid_word(w, p.n_hap);
+        uint32_t a = v[0] & v[1] & valid, b = v[2] & v[3] & valid;
+        for (uint32_t x = a | b; x != 0u; ) {  // samples of the word that sit on a path, in order
+            const uint32_t i = (uint32_t(__ffs(int(x))) - 1u) >> 1;
+            x &= ~(3u << (2 * i));
+            const uint32_t k0 = __popc((a >> (2 * i)) & 3u), k1 = __popc((b >> (2 * i)) & 3u), rs = k0 + k1;
+            const double d0 = k0 == 0u ? 0.0 : k0 == rs ? 1.0 : 2u * k0 == rs ? 0.5 : k0 == 1u ? third : two_thirds;
+            const double d1 = k1 == 0u ? 0.0 : k1 == rs ? 1.0 : 2u * k1 == rs ? 0.5 : k1 == 1u ? third : two_thirds;
+            cs0 = __dadd_rn(cs0, d0);
+            cs1 = __dadd_rn(cs1, d1);
+            tot = __dadd_rn(__dadd_rn(tot, d0), d1);
+        }
+    }
+    bool filt = tot < p.min_haplotypes;  // :565
+    int above = 0;
+    const double cs[2] = {cs0, cs1};
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {  // :570-576
+        const double freq = __ddiv_rn(cs[c], tot);
+        const double maf = fmin(freq, __dsub_rn(1.0, freq));
+        if (maf > p.maf_threshold) ++above;
+    }
+    return filt || above < 2;
+}
+
 struct Mma2xRound {
     uint4 v[4];
 };
@@ -756,15 +803,12 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma2x_kernel
         ls.su_un = z.su;
         ls.suu_un = z.suu;
         QuantMoments mom;
-        const int r = lean_finish(p, s, p0, ls, mom);
-        if (r == 1) {
-            p.mom[s] = mom;
-        } else {
-            p.mom[s].state = 0;
-            if (r == 2) {  // a filter decision within rounding of its threshold: the general path replays the reference's sums
-                const uint32_t slot = atomicAdd(p.g_count, 1u);
-                p.g_list[slot] = uint32_t(s);
-            }
-        }
+        int r = lean_finish(p, s, p0, ls, mom);
+        if (r == 2)  // a filter decision within rounding of its threshold: replay the reference's sums
+            r = lean_finish(p, s, p0, ls, mom,
+                            lean_exact_filtered(ExactArgs{p.rows, p.pitch, p.n_hap, double(p.thr.min_haplotypes),
+                                                          p.thr.maf_threshold}, ra) ? 1 : 0);
+        if (r == 1) p.mom[s] = mom;
+        else p.mom[s].state = 0;
     }
 }

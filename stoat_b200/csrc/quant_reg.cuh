@@ -48,7 +48,10 @@ struct K3RParams {
 // Filters + moments of a two-path snarl from its class counts and sums (what quant_lean2 does after its passes).
 // One thread.  Returns 0: filtered (outputs written), 1: moments ready in `mom`, 2: the snarl must be replayed by the
 // general path (non-dyadic borderline filters).
-__device__ int lean_finish(const K3Params& p, uint64_t s, uint32_t p0, const LeanSums& t, QuantMoments& mom) {
+// force: -1 decide here; 0 / 1: the decision of the total / allele-frequency filters was taken by an exact replay of the
+// reference's summation order (lean_exact_filtered, quant_mma.cuh): 1 = filtered
+__device__ int lean_finish(const K3Params& p, uint64_t s, uint32_t p0, const LeanSums& t, QuantMoments& mom,
+                           int force = -1) {
     p.out.allele_paths[p0] = t.al0;  // quantitative_table.cpp:54-55
     p.out.allele_paths[p0 + 1] = t.al1;
     if (t.n_tthird >= kLeanReplayMark) return 2;
@@ -60,7 +63,9 @@ __device__ int lean_finish(const K3Params& p, uint64_t s, uint32_t p0, const Lea
         double(t.n_full0) + 0.5 * double(t.n_half) + third * double(t.n_third) + tthird * double(t.n_tthird);
     const double colsum1 = double(n_full1) + 0.5 * double(t.n_half) + tthird * double(t.n_third) + third * double(t.n_tthird);
     bool filtered = (n_used == 0) || (t.al0 == 0) || (t.al1 == 0) || (uint64_t(n_used) < p.thr.min_individuals);
-    if (!filtered) {
+    if (!filtered && force >= 0) {
+        filtered = force != 0;
+    } else if (!filtered) {
         const double total = double(n_used);  // every used row sums to 1
         if (nondyadic && uint64_t(n_used) == p.thr.min_haplotypes) return 2;  // borderline: exact replay
         if (total < double(p.thr.min_haplotypes)) filtered = true;

@@ -251,3 +251,36 @@ def test_three_path_integer_contraction(gpu_ctx, oracle, seed, n_samples, frac_m
     # default thresholds filter some of them: the filter decisions must agree too
     got, ref = run_both(gpu_ctx, oracle, dense, snarls, y, maf=0.2)
     H.assert_quant_equal(got, ref)
+
+
+def test_thirds_exact_ties_at_the_maf_threshold(gpu_ctx, oracle):
+    """A path without checked edges matches everybody, so a carrier of the other path has dosage 1/3 (one haplotype) or
+    1/2 (both).  With n3 / 3 + n2 / 2 = 0.05 * n_samples the allele-frequency filter sits on an exact tie and its outcome
+    depends on how the reference's running sums round (src/snarl_analyzer.cpp:558-576): K3M2x replays them in order
+    (lean_exact_filtered) instead of sending the snarl to the general path.  The filter flags must be identical,
+    whichever way each tie falls (at 800 samples they fall both ways)."""
+    rng = np.random.default_rng(77)
+    n = 800
+    Hn = 2 * n
+    combos = [(120, 0), (114, 4), (108, 8), (90, 20), (60, 40), (30, 60), (6, 76), (0, 80)]
+    n_snarls = 48
+    dense = np.zeros((2 * n_snarls, Hn), dtype=bool)
+    snarls = []
+    for s in range(n_snarls):
+        n3, n2 = combos[s % len(combos)]
+        if s >= 32:  # off the tie by one carrier, either side
+            n3 = max(n3 + (1 if s % 2 else -1), 0)
+        who = rng.permutation(n)
+        one, both = who[:n3], who[n3:n3 + n2]
+        row = np.zeros(Hn, dtype=bool)
+        row[2 * one + rng.integers(0, 2, size=n3)] = True
+        row[2 * both] = True
+        row[2 * both + 1] = True
+        dense[2 * s] = dense[2 * s + 1] = row
+        snarls.append([[2 * s, 2 * s + 1] if s % 2 else [2 * s], []])
+    y = rng.normal(size=n)
+    got, ref = run_both(gpu_ctx, oracle, dense, snarls, y, min_ind=2, min_hap=2, maf=0.05)
+    np.testing.assert_array_equal(got["filtered"], ref["filtered"])
+    H.assert_quant_equal(got, ref)
+    assert 4 < int(ref["filtered"][:32].sum()) < 28  # the ties fall both ways
+    assert gpu_ctx.timing()["n_general"] == 0        # ... and none of them needed the general path
