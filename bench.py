@@ -470,7 +470,7 @@ def main():
                     "kernel_ms": k1, "peak_source": peak_src,
                     "snarls_off_fast_path": int(n_general), "fisher_tables": int(n_fisher),
                     "other_kernels_ms": {"binary_stats (K2a) + fisher_exact (K2b)" if args.trait == "binary"
-                                         else "left-over list (K3) + ols_solve (K4) + general path (K3G)": float(np.mean(k2_ms)),
+                                         else "three-path / thirds snarls (K3M3, K3M2x) + left-over list (K3) + ols_solve, student_tail (K4a, K4b) + general path (K3G)": float(np.mean(k2_ms)),
                                          "repack_rows (K0, once per matrix, not in the step)": t_repack}}
         line = {
             "metric": METRIC if args.trait == "binary" else "snarl-path tests/sec (quantitative OLS)",

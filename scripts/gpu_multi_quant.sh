@@ -6,7 +6,7 @@ for N in 1 2; do
   python -c "
 import json
 d=json.loads(open('gpurun_out/bq$N.json').read().strip().splitlines()[-1])
-print('quant n_gpus', d['n_gpus'], 'value %.4e' % d['value'], 'ms/step %.2f' % d['ms_per_step'], d['roofline']['kernel_ms'], d['roofline']['other_kernels_ms'])" || tail -5 gpurun_out/bq$N.err
+print('quant n_gpus', d['n_gpus'], 'value %.4e' % d['value'], 'ms/step %.2f' % d['ms_per_step'], d['roofline']['kernel_ms'], list(d['roofline']['other_kernels_ms'].values()))" || tail -5 gpurun_out/bq$N.err
 done
 CUDA_VISIBLE_DEVICES=1 timeout 300 python bench.py --trait quantitative --warmup 3 --steps 10 --no-e2e --no-cpu-baseline 2>/dev/null | tail -1 | python -c "
 import json,sys

@@ -663,30 +663,46 @@ struct ExactArgs {
     const uint8_t* rows;
     uint32_t pitch, n_hap;
     double min_haplotypes, maf_threshold;
+    const double2* tab;  // [16] (d0, d1) by the presence bits of a sample: path 0 bits | path 1 bits << 2
 };
+// table entry count / row sum of quantitative_table.cpp:93 for the sample with presence bits `idx`
+__device__ __forceinline__ double2 exact_tab_entry(uint32_t idx) {
+    const uint32_t k0 = __popc(idx & 3u), k1 = __popc(idx >> 2), rs = k0 + k1;
+    double2 d;
+    d.x = k0 ? __ddiv_rn(double(k0), double(rs)) : 0.0;
+    d.y = k1 ? __ddiv_rn(double(k1), double(rs)) : 0.0;
+    return d;
+}
 __device__ __noinline__ bool lean_exact_filtered(const ExactArgs p, uint4 rows) {
     const uint32_t rr[4] = {rows.x, rows.y, rows.z, rows.w};
-    const uint32_t n_words = (p.n_hap + 31u) / 32u;
-    const double third = 1.0 / 3.0, two_thirds = 2.0 / 3.0;
+    const uint32_t n_chunks = (p.n_hap + 127u) / 128u;  // <= pitch / 16
     double cs0 = 0.0, cs1 = 0.0, tot = 0.0;
-    for (uint32_t w = 0; w < n_words; ++w) {
-        uint32_t v[4];
+    auto load = [&](uint32_t c, uint4 (&v)[4]) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-            v[k] = rr[k] == kLeanAll ? 0xFFFFFFFFu
-                                     : __ldg(reinterpret_cast<const uint32_t*>(p.rows + size_t(rr[k]) * p.pitch) + w);
-        const uint32_t valid = valid_word(w, p.n_hap);
-        uint32_t a = v[0] & v[1] & valid, b = v[2] & v[3] & valid;
-        for (uint32_t x = a | b; x != 0u; ) {  // samples of the word that sit on a path, in order
-            const uint32_t i = (uint32_t(__ffs(int(x))) - 1u) >> 1;
-            x &= ~(3u << (2 * i));
-            const uint32_t k0 = __popc((a >> (2 * i)) & 3u), k1 = __popc((b >> (2 * i)) & 3u), rs = k0 + k1;
-            const double d0 = k0 == 0u ? 0.0 : k0 == rs ? 1.0 : 2u * k0 == rs ? 0.5 : k0 == 1u ? third : two_thirds;
-            const double d1 = k1 == 0u ? 0.0 : k1 == rs ? 1.0 : 2u * k1 == rs ? 0.5 : k1 == 1u ? third : two_thirds;
-            cs0 = __dadd_rn(cs0, d0);
-            cs1 = __dadd_rn(cs1, d1);
-            tot = __dadd_rn(__dadd_rn(tot, d0), d1);
+            v[k] = rr[k] == kLeanAll
+                       ? make_uint4(valid_word(4 * c, p.n_hap), valid_word(4 * c + 1, p.n_hap),
+                                    valid_word(4 * c + 2, p.n_hap), valid_word(4 * c + 3, p.n_hap))
+                       : __ldg(reinterpret_cast<const uint4*>(p.rows + size_t(rr[k]) * p.pitch) + c);
+    };
+    uint4 cur[4], nxt[4];
+    load(0, cur);
+    for (uint32_t c = 0; c < n_chunks; ++c) {
+        if (c + 1 < n_chunks) load(c + 1, nxt);  // in flight while this chunk's 64 samples are added
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t a = u4_word(cur[0], j) & u4_word(cur[1], j), b = u4_word(cur[2], j) & u4_word(cur[3], j);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                // a sample on no path has the entry (0, 0): adding +0.0 to a non-negative sum changes nothing
+                const double2 d = p.tab[((a >> (2 * i)) & 3u) | (((b >> (2 * i)) & 3u) << 2)];
+                cs0 = __dadd_rn(cs0, d.x);
+                cs1 = __dadd_rn(cs1, d.y);
+                tot = __dadd_rn(__dadd_rn(tot, d.x), d.y);
+            }
         }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) cur[k] = nxt[k];
     }
     bool filt = tot < p.min_haplotypes;  // :565
     int above = 0;
@@ -734,6 +750,8 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma2x_kernel
     const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const uint32_t n2 = *q.count2x + *q.count2x_dyn;
     if (n2 == 0u) return;
+    __shared__ double2 exact_tab[16];  // lean_exact_filtered
+    if (tid < 16) exact_tab[tid] = exact_tab_entry(tid);
     const uint32_t r_len = q.n_rounds;
     {
         const uint4* src = reinterpret_cast<const uint4*>(q.yslices);
@@ -807,7 +825,7 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma2x_kernel
         if (r == 2)  // a filter decision within rounding of its threshold: replay the reference's sums
             r = lean_finish(p, s, p0, ls, mom,
                             lean_exact_filtered(ExactArgs{p.rows, p.pitch, p.n_hap, double(p.thr.min_haplotypes),
-                                                          p.thr.maf_threshold}, ra) ? 1 : 0);
+                                                          p.thr.maf_threshold, exact_tab}, ra) ? 1 : 0);
         if (r == 1) p.mom[s] = mom;
         else p.mom[s].state = 0;
     }
