@@ -666,7 +666,12 @@ cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const
                                                 fisher_idx + s_begin, fisher_counters, s_begin, s_begin + s_count);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     const uint64_t want = (s_count + 127) / 128;
-    const unsigned fblocks = unsigned(want < uint64_t(num_sms) * 8 ? want : uint64_t(num_sms) * 8);
+    static const int per_sm = [] {
+        const char* v = std::getenv("STOAT_GPU_FISHER_BLOCKS");
+        const int n = v ? std::atoi(v) : 0;
+        return n >= 1 ? n : 8;
+    }();
+    const unsigned fblocks = unsigned(want < uint64_t(num_sms) * per_sm ? want : uint64_t(num_sms) * per_sm);
     // STOAT_GPU_FISHER=exact: the quotient by __ddiv_rn, bit-identical to the reference's recurrence (15 % slower)
     const char* fv = std::getenv("STOAT_GPU_FISHER");
     if (fv && fv[0] == 'e')
