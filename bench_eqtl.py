@@ -75,30 +75,21 @@ def cpu_run(d, expr, threads, kind):
     return r["seconds"], S * G
 
 
-def cpu_threads(kind):
-    import oracle
-
-    if kind == "reference":
-        from oracle import ref
-
-        return ref.num_threads()
-    return oracle.num_threads()
-
-
 CPU_WHAT = {"reference": "the reference's own EQTLSnarlAnalyzer sources (oracle/_ref: table once per snarl, Eigen OLS per gene, "
                          "writer; Boost tails from stand-ins) incl. per-row TSV write",
             "port": "oracle port of the reference's eQTL loop"}
 
 
-def cpu_sample(args, target_seconds):
-    """(dataset, expression, threads, kind) sized for about target_seconds of CPU work."""
+def cpu_sample(args, target_seconds, n_threads):
+    """(dataset, expression, threads, kind) sized for about target_seconds of CPU work; n_threads = the host threads this
+    process may use (bench.host_threads(): CPU affinity and cgroup quota, not OMP_NUM_THREADS)."""
     from stoat_b200 import synth
 
     kind = cpu_kind()
     probe = synth.numpy_dataset(8, args.samples, seed=42, **BIALLELIC)
     pe = expression_numpy(16, args.samples)
     best = (1, 0.0)
-    for th in sorted({1, cpu_threads(kind)}):
+    for th in sorted({1, n_threads}):
         secs, pairs = cpu_run(probe, pe, th, kind)
         if pairs / max(secs, 1e-9) > best[1]:
             best = (th, pairs / max(secs, 1e-9))
@@ -110,21 +101,19 @@ def cpu_sample(args, target_seconds):
     return d, expression_numpy(n_genes, args.samples), threads, kind
 
 
-def cpu_baseline(args, target_seconds):
-    d, expr, threads, kind = cpu_sample(args, target_seconds)
+def cpu_baseline(args, target_seconds, n_threads):
+    d, expr, threads, kind = cpu_sample(args, target_seconds, n_threads)
     secs, pairs = cpu_run(d, expr, threads, kind)
     return {"value": pairs / secs, "unit": UNIT, "cores": threads, "kind": kind,
             "sample": f"{d['paths'].n_snarls} snarls x {expr.shape[0]} genes x {args.samples} samples ({pairs} pairs) of the same "
                       f"generators, {CPU_WHAT[kind]}, {secs:.2f} s"}
 
 
-def run_reference_arm(args):
-    if int(os.environ.get("RANK", "0")) != 0:
-        return
+def reference_line(args, n_threads):
     import oracle
 
     oracle.build()
-    d, expr, threads, kind = cpu_sample(args, 4.0)
+    d, expr, threads, kind = cpu_sample(args, 4.0, n_threads)
     for _ in range(args.warmup):
         cpu_run(d, expr, threads, kind)
     total, pairs = 0.0, 0
@@ -135,12 +124,18 @@ def run_reference_arm(args):
     value = pairs / total
     sample = (f"{d['paths'].n_snarls} snarls x {expr.shape[0]} genes x {args.samples} samples per step, same generators, "
               f"{CPU_WHAT[kind]}")
-    print(json.dumps({
+    return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config_dict(args, args.gpus),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
-        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+
+
+def run_reference_arm(args, n_threads):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    print(json.dumps(reference_line(args, n_threads)))
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -165,30 +160,61 @@ def dgemm_peak_tflops(torch, dev, n=8192, reps=5):
     return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
-def run(args, ClockSampler):
-    if args.impl == "reference":
-        run_reference_arm(args)
-        return
-    import torch
-    import torch.distributed as dist
+def parity_spot_check(ctx_summary, d, expr_dev, args, n_check, n_threads):
+    """The first `n_check` snarls of the TIMED scan x every gene through the CPU oracle (one OLS per pair, as the
+    reference), against the device's per-snarl summary: min p (1e-9 relative), its gene, the count below the threshold."""
+    import time
 
+    import oracle
+
+    st = d["structure"]
+    n = min(n_check, d["paths"].n_snarls)
+    r1 = int(st.row0[n - 1] + st.n_rows_of[n - 1])
+    row_bytes = d["n_cols"] // 8
+    bits = d["bits_dev"][: r1 * row_bytes].cpu().numpy()
+    expr = expr_dev.cpu().numpy()
+    p = d["paths"]
+    P1, E1 = int(p.snarl_path_off[n]), int(p.path_edge_off[int(p.snarl_path_off[n])])
+    sub = oracle.Paths(p.snarl_path_off[: n + 1].copy(), p.path_edge_off[: P1 + 1].copy(), p.edge_row[:E1].copy())
+    t0 = time.time()
+    ref = oracle.eqtl_batch(bits, d["n_cols"], expr, sub, n_threads=n_threads)
+    G, thr, rtol = expr.shape[0], args.p_threshold, 1e-9
+    pv = ref["p_value"].reshape(n, G)
+    ok = ref["code"].reshape(n, G) == 0
+    bad = []
+    for s in range(n):
+        mp, ag, nb = ctx_summary["min_p"][s], int(ctx_summary["argmin_gene"][s]), int(ctx_summary["n_below"][s])
+        if ref["filtered"][s] or not ok[s].any():
+            if not (np.isnan(mp) and nb == 0):
+                bad.append((s, "filtered"))
+            continue
+        ps = np.where(ok[s], pv[s], np.inf)
+        g = int(np.argmin(ps))
+        near = np.abs(ps - thr) <= rtol * thr
+        lo, hi = int(((ps < thr) & ~near).sum()), int(((ps < thr) | near).sum())
+        if not (abs(mp - ps[g]) <= rtol * ps[g] + 1e-300):
+            bad.append((s, "min_p", float(mp), float(ps[g])))
+        elif ag != g and not abs(ps[ag] - ps[g]) <= rtol * ps[g]:
+            bad.append((s, "argmin", ag, g))
+        elif not lo <= nb <= hi:
+            bad.append((s, "n_below", nb, lo, hi))
+    out = {"checked_snarls": int(n), "checked_pair_tests": int(n * G), "mismatches": len(bad),
+           "against": "oracle port (oracle/stoat_oracle.cpp), one OLS per (snarl, gene) on the timed matrix's own rows and "
+                      "the timed expression matrix; min p 1e-9 relative, its gene, count below the threshold",
+           "seconds": round(time.time() - t0, 2)}
+    if bad:
+        out["first_mismatch"] = str(bad[0])
+    return out
+
+
+def measure(args, env, ClockSampler, n_threads, with_clocks=True):
+    """The C4 record on this rank's GPU; `env` = bench.Env (torch, process group).  -> the JSON line's dict on rank 0."""
     import stoat_b200
     from stoat_b200 import synth
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a B200: stoat_b200 has no CPU fallback (use --impl reference for the CPU arm)")
-    dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    torch, dist = env.torch, env.dist
+    world, rank, local, dev = env.world, env.rank, env.local, env.dev
+    barrier = env.barrier
 
     S, n, G = args.snarls, args.samples, args.genes
     d = synth.torch_dataset(S, n, dev, seed=42 + rank, **BIALLELIC)
@@ -208,7 +234,7 @@ def run(args, ClockSampler):
         run_scan()
     barrier()
     sampler = ClockSampler(local)
-    if rank == 0:
+    if rank == 0 and with_clocks:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e1_ms, rest_ms, launches, n_general = [], [], 0, 0
@@ -222,7 +248,7 @@ def run(args, ClockSampler):
         n_general = t["n_general"]
     e1.record(stream)
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop() if (rank == 0 and with_clocks) else None
     tmax = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     lsum = torch.tensor([launches], dtype=torch.float64, device=dev)
     if world > 1:
@@ -232,6 +258,9 @@ def run(args, ClockSampler):
     value = world * S * G * args.steps / (elapsed_ms * 1e-3)
     summary = ctx.eqtl_summary_fetch()
     n_dense = int(S - n_general - int(np.isnan(summary["min_p"]).sum()))
+    parity = None
+    if rank == 0 and not getattr(args, "no_parity", False):
+        parity = parity_spot_check(summary, d, expr, args, 8, n_threads)
 
     e2e = None
     if not args.no_e2e:
@@ -266,6 +295,7 @@ def run(args, ClockSampler):
                            "+ general-path rest + D2H of the per-snarl summary"}
         del host_bits, host_expr
 
+    line = None
     if rank == 0:
         k_ms = float(np.mean(e1_ms))
         flops = 2.0 * n * n_dense * G
@@ -281,13 +311,13 @@ def run(args, ClockSampler):
                 "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64 (2-bit dosage codes x f64 expression, DMMA)",
                 "data": "synthetic (seed 42, drawn on device)", "config": config_dict(args, world), "clocks": clocks,
-                "e2e": e2e, "gpu_launches": int(lsum.item()), "roofline": roofline}
+                "e2e": e2e, "gpu_launches": int(lsum.item()), "roofline": roofline, "parity": parity}
         if world == 1 and not args.no_cpu_baseline:
             import oracle
 
             oracle.build()
-            line["cpu_baseline"] = cpu_baseline(args, args.cpu_seconds)
-        print(json.dumps(line))
+            line["cpu_baseline"] = cpu_baseline(args, args.cpu_seconds, n_threads)
     ctx.close()
-    if world > 1:
-        dist.destroy_process_group()
+    del d, expr
+    torch.cuda.empty_cache()
+    return line if rank == 0 else None

@@ -251,7 +251,13 @@ STOAT_GPU_API int stoat_gpu_quantitative_partials_dev(stoat_gpu_ctx* ctx, uint32
 STOAT_GPU_API int stoat_gpu_quantitative_solve_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
 
 /* ---- introspection --------------------------------------------------------------------- */
+/* The staged run calls (stoat_gpu_*_run_staged) only ENQUEUE work on the context's stream; this call waits for the
+ * last one and reports its CUDA-event durations and counters.                                                   */
 STOAT_GPU_API int stoat_gpu_last_timing(const stoat_gpu_ctx* ctx, stoat_gpu_timing* out);
+/* table_ms / stats_ms averaged over the last n_runs staged runs of the same trait (at most 64 are kept); the other
+ * fields as stoat_gpu_last_timing.  Lets a caller time a kernel over a whole series of back-to-back runs without a
+ * host round trip between them.                                                                                 */
+STOAT_GPU_API int stoat_gpu_mean_timing(stoat_gpu_ctx* ctx, uint32_t n_runs, stoat_gpu_timing* out);
 /* cudaStream_t of the context as an integer (so the caller can record its own events)       */
 STOAT_GPU_API uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx);
 /* The matrix from its set bits: the device half of make_edge_matrix (src/snarl_analyzer.cpp:190-260).

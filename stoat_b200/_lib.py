@@ -89,6 +89,7 @@ SIGNATURES = {
     "stoat_gpu_quantitative_partials_dev": (C.c_int, [CTX, C.POINTER(C.c_void_p), u64p, C.POINTER(C.c_void_p), u64p]),
     "stoat_gpu_quantitative_solve_staged": (C.c_int, [CTX, C.POINTER(Thresholds)]),
     "stoat_gpu_last_timing": (C.c_int, [CTX, C.POINTER(Timing)]),
+    "stoat_gpu_mean_timing": (C.c_int, [CTX, C.c_uint32, C.POINTER(Timing)]),
     "stoat_gpu_stream": (C.c_uint64, [CTX]),
     "stoat_gpu_set_matrix_pairs": (C.c_int, [CTX, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64]),
     "stoat_gpu_bh_adjust": (C.c_int, [CTX, C.c_void_p, C.c_uint64, C.c_void_p]),

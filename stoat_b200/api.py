@@ -153,6 +153,12 @@ class Context:
         self._check(self._lib.stoat_gpu_last_timing(self._ctx, C.byref(t)))
         return {k: getattr(t, k) for k, _ in L.Timing._fields_}
 
+    def mean_timing(self, n_runs: int) -> dict:
+        """table_ms / stats_ms averaged over the last `n_runs` staged runs (the runs themselves are asynchronous)."""
+        t = L.Timing()
+        self._check(self._lib.stoat_gpu_mean_timing(self._ctx, int(n_runs), C.byref(t)))
+        return {k: getattr(t, k) for k, _ in L.Timing._fields_}
+
     # ---- output holders -----------------------------------------------------------------------------
     @staticmethod
     def _binary_arrays(S: int, P: int) -> dict:

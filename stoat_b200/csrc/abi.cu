@@ -60,6 +60,8 @@ struct QuantState {
 }  // namespace
 
 constexpr int kMaxRunChunks = 8;  // chunks of an overlapped binary run (stoat_gpu_binary_run_staged)
+constexpr int kDefaultRunChunks = 4;  // chunks of the overlapped binary run (measured: profiles/r2_*)
+constexpr int kRunRing = 64;      // staged runs whose events are kept for stoat_gpu_mean_timing
 
 // extra per-context state that does not need to be visible to the kernel translation units
 struct CtxExtra {
@@ -71,6 +73,15 @@ struct CtxExtra {
     uint32_t fisher_readback[2 * kMaxRunChunks] = {};
     DevBuf bh;  // scratch of stoat_gpu_bh_adjust
     cudaEvent_t chunk_done[kMaxRunChunks] = {};
+    // Events of the last kRunRing staged runs: [0] start, [1] end of the count / moments pass, [2] start and [3] end of the
+    // statistics.  A run only enqueues work; its timing (and the counters that come back with it) is read when somebody asks
+    // (finalize_timing), so that back-to-back runs keep the GPU busy without a host round trip in between.
+    cudaEvent_t ring[kRunRing][4] = {};
+    uint8_t ring_kind[kRunRing] = {};  // 1 binary, 2 quantitative
+    uint64_t run_seq = 0;
+    int pending = 0;         // kind of the run whose timing has not been read yet (0: none)
+    int pending_chunks = 1;  // chunks of that (binary) run
+    uint64_t expr_cols = 0;  // n_cols the expression matrix was centred and padded for
 };
 static CtxExtra* extra_of(stoat_gpu_ctx* ctx);
 
@@ -78,6 +89,54 @@ struct stoat_gpu_ctx_full : stoat_gpu_ctx {
     CtxExtra extra;
 };
 static CtxExtra* extra_of(stoat_gpu_ctx* ctx) { return &static_cast<stoat_gpu_ctx_full*>(ctx)->extra; }
+
+// Read the timing of the last staged run (and the counters that belong to it); the run itself only enqueued work.
+static int finalize_timing(stoat_gpu_ctx* ctx) {
+    CtxExtra* x = extra_of(ctx);
+    if (!x->pending) return STOAT_GPU_OK;
+    const int kind = x->pending;
+    x->pending = 0;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaEvent_t* ev = x->ring[(x->run_seq - 1) % kRunRing];
+    const uint64_t S = ctx->batch.n_snarls;
+    if (kind == 1) {
+        CK(cudaMemcpy(x->fisher_readback, ctx->fisher_cnt.p, 8 * kMaxRunChunks, cudaMemcpyDeviceToHost));
+        uint32_t n_fisher = 0;
+        for (int c = 0; c < x->pending_chunks; ++c) n_fisher += x->fisher_readback[2 * c];
+        ctx->timing.n_general = ctx->n_big;
+        ctx->timing.n_fisher = S ? n_fisher : 0;
+        CK(cudaEventElapsedTime(&ctx->timing.table_ms, ev[0], ev[1]));
+        CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ev[2], ev[3]));
+    } else {
+        CK(cudaMemcpy(x->readback, ctx->d_counters.p, 4, cudaMemcpyDeviceToHost));
+        ctx->timing.n_general = S ? x->readback[0] : 0;
+        ctx->timing.n_fisher = 0;
+        if (S && x->readback[0] && std::getenv("STOAT_GPU_DEBUG_GENERAL")) {  // which snarls took the general path
+            std::vector<uint32_t> ids(std::min<uint32_t>(x->readback[0], 64));
+            CK(cudaMemcpy(ids.data(), ctx->batch.big_list, ids.size() * 4, cudaMemcpyDeviceToHost));
+            std::fprintf(stderr, "[stoat_gpu] general path: %u snarls:", x->readback[0]);
+            for (uint32_t id : ids) std::fprintf(stderr, " %u", id);
+            std::fprintf(stderr, "\n");
+        }
+        if (S) {
+            CK(cudaEventElapsedTime(&ctx->timing.table_ms, ev[0], ev[1]));  // the moments pass (K3M / K3R / K3)
+            CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ev[1], ev[3]));  // left-over list, K4, general path
+        } else {
+            ctx->timing.table_ms = ctx->timing.stats_ms = 0.f;
+        }
+    }
+    return STOAT_GPU_OK;
+}
+
+// a new matrix invalidates everything that was derived from the old one
+static void invalidate_derived(stoat_gpu_ctx* ctx) {
+    ctx->have_batch = false;
+    ctx->have_expression = ctx->have_eqtl_summary = false;
+    ctx->have_binary_counts = ctx->have_binary_result = ctx->have_quant_result = false;
+    extra_of(ctx)->q.have_partials = false;
+    extra_of(ctx)->q.lean_key = 0;
+}
 
 extern "C" {
 
@@ -127,6 +186,12 @@ int stoat_gpu_create(stoat_gpu_ctx** out, int device) {
             delete full;
             return fail_cuda(nullptr, e, "cudaEventCreate");
         }
+    for (auto& slot : full->extra.ring)
+        for (auto& ev : slot)
+            if ((e = cudaEventCreate(&ev)) != cudaSuccess) {
+                delete full;
+                return fail_cuda(nullptr, e, "cudaEventCreate");
+            }
     const char* k1 = std::getenv("STOAT_GPU_K1");
     ctx->k1_variant = (k1 && std::strcmp(k1, "ldg") == 0) ? 1 : 0;
     const char* eq = std::getenv("STOAT_GPU_EQTL");
@@ -142,10 +207,12 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
     DevBuf* bufs[] = {&ctx->rows, &ctx->raw_stage[0], &ctx->raw_stage[1], &ctx->case_mask, &ctx->is_case_dev, &ctx->y,
                       &ctx->covar, &ctx->d_snarl_path_off, &ctx->d_path_edge_off, &ctx->d_edge_row, &ctx->d_rec,
-                      &ctx->d_blob, &ctx->d_big, &ctx->d_counters, &ctx->counts, &ctx->total_sum, &ctx->filtered,
+                      &ctx->d_blob, &ctx->d_big, &ctx->d_counters, &ctx->counts, &ctx->total_sum, &ctx->filtered, &ctx->filtered_bin,
                       &ctx->p_a, &ctx->p_b, &ctx->code_a, &ctx->code_b, &ctx->fisher_tab, &ctx->fisher_idx, &ctx->fisher_cnt, &ctx->q_allele, &ctx->q_nused, &ctx->q_p,
                       &ctx->q_r2, &ctx->q_beta, &ctx->q_se, &ctx->q_code, &ctx->e_expr, &ctx->e_gene_off, &ctx->e_gene_idx,
-                      &ctx->e_min_p, &ctx->e_argmin, &ctx->e_nbelow};
+                      &ctx->e_min_p, &ctx->e_argmin, &ctx->e_nbelow, &ctx->e_yc, &ctx->e_tot, &ctx->e_tot2, &ctx->e_dcode,
+                      &ctx->e_rec, &ctx->e_fb_list, &ctx->e_fb_count, &ctx->e_slot, &ctx->e_part_key, &ctx->e_part_gene,
+                      &ctx->e_part_cnt};
     for (DevBuf* b : bufs) b->release();
     CtxExtra* x = extra_of(ctx);
     x->q.yc.release();
@@ -164,6 +231,9 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : x->chunk_done)
         if (ev) cudaEventDestroy(ev);
+    for (auto& slot : x->ring)
+        for (auto& ev : slot)
+            if (ev) cudaEventDestroy(ev);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete static_cast<stoat_gpu_ctx_full*>(ctx);
@@ -180,24 +250,60 @@ static int set_matrix_common(stoat_gpu_ctx* ctx, const uint8_t* bits, bool on_de
     if (on_device && (reinterpret_cast<uintptr_t>(bits) & 3))
         return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_dev: device pointer must be 4-byte aligned");
     CK(cudaSetDevice(ctx->device));
+    if (int rc = finalize_timing(ctx)) return rc;
+    CtxExtra* x = extra_of(ctx);
     const uint64_t pitch = pitch_for(n_cols);
     const uint64_t raw_bytes = (n_rows * n_cols + 7) / 8;
+    ctx->have_matrix = false;
+    invalidate_derived(ctx);
     CK(ctx->rows.reserve(std::max<uint64_t>(n_rows * pitch, 16)));
     ctx->timing = stoat_gpu_timing{};
-    const uint8_t* raw_dev = bits;
+    uint32_t launches = 0;
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
-    if (!on_device) {
-        CK(ctx->raw_stage[0].reserve(raw_bytes + 16));
-        if (raw_bytes) CK(cudaMemcpyAsync(ctx->raw_stage[0].p, bits, raw_bytes, cudaMemcpyHostToDevice, ctx->stream));
-        raw_dev = ctx->raw_stage[0].as<uint8_t>();
+    if (on_device) {
+        CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+        CK(launch_repack_rows(bits, raw_bytes, 0, n_rows, n_cols, pitch, ctx->rows.as<uint8_t>(), ctx->stream));
+        launches = n_rows ? 1 : 0;
+    } else {
+        // The reference-layout bytes go up in chunks of whole rows through two staging buffers: the copy of chunk k + 1
+        // (copy stream) overlaps the repack of chunk k (main stream), and the staging never holds more than two chunks.
+        // A chunk starts at a multiple of 128 rows, so its first bit sits on a 16-byte boundary of the bit stream and the
+        // repack kernel can address the staging buffer as if it were the whole matrix (base pointer shifted back).
+        uint64_t chunk_bytes = 256ull << 20;
+        if (const char* e = std::getenv("STOAT_GPU_UPLOAD_CHUNK_MB")) chunk_bytes = std::max<uint64_t>(1, uint64_t(std::atoll(e))) << 20;
+        uint64_t rows_per = std::max<uint64_t>(128, (chunk_bytes * 8 / n_cols) / 128 * 128);
+        if (const char* e = std::getenv("STOAT_GPU_UPLOAD_CHUNK_ROWS"))  // tests: many chunks of a small matrix
+            rows_per = std::max<uint64_t>(128, (uint64_t(std::atoll(e)) + 127) / 128 * 128);
+        if (rows_per >= n_rows) rows_per = std::max<uint64_t>(n_rows, 1);
+        const uint64_t n_chunks = n_rows ? (n_rows + rows_per - 1) / rows_per : 0;
+        for (uint64_t k = 0; k < n_chunks; ++k) {
+            const uint64_t r0 = k * rows_per, r1 = std::min(n_rows, r0 + rows_per);
+            const uint64_t b0 = r0 * n_cols / 8;  // exact: r0 is a multiple of 128 (or 0)
+            const uint64_t b1 = std::min(raw_bytes, (r1 * n_cols + 7) / 8);
+            DevBuf& st = ctx->raw_stage[k & 1];
+            if (k < 2) CK(st.reserve(std::min(raw_bytes, (rows_per * n_cols + 7) / 8) + 64));
+            if (k >= 2) CK(cudaStreamWaitEvent(ctx->copy_stream, x->chunk_done[k & 1], 0));  // the buffer's previous repack
+            else CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev[0], 0));
+            CK(cudaMemcpyAsync(st.p, bits + b0, b1 - b0, cudaMemcpyHostToDevice, ctx->copy_stream));
+            CK(cudaEventRecord(x->chunk_done[2 + (k & 1)], ctx->copy_stream));
+            CK(cudaStreamWaitEvent(ctx->stream, x->chunk_done[2 + (k & 1)], 0));
+            CK(launch_repack_rows(st.as<uint8_t>() - b0, raw_bytes, r0, r1, n_cols, pitch, ctx->rows.as<uint8_t>(),
+                                  ctx->stream));
+            CK(cudaEventRecord(x->chunk_done[k & 1], ctx->stream));
+            ++launches;
+        }
+        CK(cudaEventRecord(ctx->ev[1], ctx->stream));
     }
-    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
-    CK(launch_repack_rows(raw_dev, raw_bytes, 0, n_rows, n_cols, pitch, ctx->rows.as<uint8_t>(), ctx->stream));
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    CK(cudaEventElapsedTime(&ctx->timing.h2d_ms, ctx->ev[0], ctx->ev[1]));
-    CK(cudaEventElapsedTime(&ctx->timing.repack_ms, ctx->ev[1], ctx->ev[2]));
-    ctx->timing.launches = n_rows ? 1 : 0;
+    if (on_device) {
+        CK(cudaEventElapsedTime(&ctx->timing.h2d_ms, ctx->ev[0], ctx->ev[1]));
+        CK(cudaEventElapsedTime(&ctx->timing.repack_ms, ctx->ev[1], ctx->ev[2]));
+    } else {
+        CK(cudaEventElapsedTime(&ctx->timing.h2d_ms, ctx->ev[0], ctx->ev[2]));  // upload and repack overlap: one figure
+        ctx->timing.repack_ms = 0.f;
+    }
+    ctx->timing.launches = launches;
     ctx->n_rows = n_rows;
     ctx->n_cols = n_cols;
     ctx->pitch = pitch;
@@ -205,7 +311,6 @@ static int set_matrix_common(stoat_gpu_ctx* ctx, const uint8_t* bits, bool on_de
     // phenotype masks depend on the pitch: they must be set again after a matrix of another width
     if (ctx->have_binary && ctx->n_samples_binary * 2 != n_cols) ctx->have_binary = false;
     if (ctx->have_quant && ctx->n_samples_quant * 2 != n_cols) ctx->have_quant = false;
-    ctx->have_batch = false;
     return STOAT_GPU_OK;
 }
 
@@ -224,7 +329,10 @@ int stoat_gpu_set_matrix_pairs(stoat_gpu_ctx* ctx, const uint32_t* rows, const u
         return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_pairs: dimensions exceed 32-bit row / column indices");
     if (n_pairs && (!rows || !cols)) return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_pairs: rows / cols is NULL");
     CK(cudaSetDevice(ctx->device));
+    if (int rc = finalize_timing(ctx)) return rc;
     const uint64_t pitch = pitch_for(n_cols);
+    ctx->have_matrix = false;
+    invalidate_derived(ctx);
     CK(ctx->rows.reserve(std::max<uint64_t>(n_rows * pitch, 16)));
     CK(ctx->d_counters.reserve(32));
     ctx->timing = stoat_gpu_timing{};
@@ -267,7 +375,6 @@ int stoat_gpu_set_matrix_pairs(stoat_gpu_ctx* ctx, const uint32_t* rows, const u
     ctx->have_matrix = true;
     if (ctx->have_binary && ctx->n_samples_binary * 2 != n_cols) ctx->have_binary = false;
     if (ctx->have_quant && ctx->n_samples_quant * 2 != n_cols) ctx->have_quant = false;
-    ctx->have_batch = false;
     return STOAT_GPU_OK;
 }
 
@@ -459,9 +566,10 @@ int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths) {
         if (paths->path_edge_off[p + 1] < paths->path_edge_off[p])
             return fail(ctx, STOAT_GPU_ERR_ARG, "stage_paths: path_edge_off is not monotone");
     CK(cudaSetDevice(ctx->device));
+    if (int rc = finalize_timing(ctx)) return rc;
     CtxExtra* x = extra_of(ctx);
     ctx->have_batch = false;
-    ctx->have_binary_counts = ctx->have_binary_result = ctx->have_quant_result = false;
+    ctx->have_binary_counts = ctx->have_binary_result = ctx->have_quant_result = ctx->have_eqtl_summary = false;
     extra_of(ctx)->q.have_partials = false;
     ++x->stage_gen;  // lean records of the previous staging are stale
     CK(ctx->d_snarl_path_off.reserve((S + 1) * 8));
@@ -514,7 +622,7 @@ static int binary_reserve(stoat_gpu_ctx* ctx) {
     const BatchDev& b = ctx->batch;
     CK(ctx->counts.reserve(std::max<uint64_t>(2 * b.n_paths * 4, 16)));
     CK(ctx->total_sum.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
-    CK(ctx->filtered.reserve(std::max<uint64_t>(b.n_snarls, 16)));
+    CK(ctx->filtered_bin.reserve(std::max<uint64_t>(b.n_snarls, 16)));
     CK(ctx->p_a.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
     CK(ctx->p_b.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
     CK(ctx->code_a.reserve(std::max<uint64_t>(b.n_snarls, 16)));
@@ -560,7 +668,7 @@ int stoat_gpu_binary_stats_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds
     CK(cudaSetDevice(ctx->device));
     CK(cudaEventRecord(ctx->ev[4], ctx->stream));
     CK(launch_binary_stats(ctx->batch, ctx->counts.as<uint32_t>(), *thr, ctx->total_sum.as<uint64_t>(),
-                           ctx->filtered.as<uint8_t>(), ctx->p_a.as<double>(), ctx->p_b.as<double>(),
+                           ctx->filtered_bin.as<uint8_t>(), ctx->p_a.as<double>(), ctx->p_b.as<double>(),
                            ctx->code_a.as<uint8_t>(), ctx->code_b.as<uint8_t>(), ctx->fisher_tab.as<uint4>(),
                            ctx->fisher_idx.as<uint32_t>(), ctx->fisher_cnt.as<uint32_t>(), ctx->num_sms, ctx->stream));
     CK(cudaEventRecord(ctx->ev[5], ctx->stream));
@@ -578,57 +686,62 @@ int stoat_gpu_binary_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* 
     if (rc) return rc;
     CtxExtra* x = extra_of(ctx);
     const uint64_t S = ctx->batch.n_snarls;
-    // The count pass (K1) is HBM bound and leaves the FP64 pipe idle, the Fisher work list (K2b) is the opposite, so the run
-    // CAN be cut into chunks of snarls with K1 of chunk c + 1 (main stream) overlapping K2a / K2b of chunk c (second
-    // stream): STOAT_GPU_OVERLAP=<chunks>.  Measured on B200 at C3 it does not pay — 1.94 ms back to back, 2.09 / 2.35 /
-    // 2.75 ms with 2 / 4 / 8 chunks: K1 is a persistent kernel that takes all of an SM's shared memory, the Fisher blocks
-    // hold the registers its next launch needs, and every chunk adds two kernel tails — so the default is one chunk.
+    // The count pass (K1) is HBM bound and leaves the FP64 pipe idle, the Fisher work list (K2b) is the opposite, so the
+    // run is cut into chunks of snarls with K1 of chunk c + 1 (main stream) overlapping K2a / K2b of chunk c (second
+    // stream).  For the two to share an SM the count pass runs in its 64-register build (416 threads x 64 registers +
+    // four 128-thread Fisher blocks fit the register file; the 105-register build and eight Fisher blocks did not, which
+    // is why this lost to the back-to-back order in round 1).  STOAT_GPU_OVERLAP=<chunks>, 1 = back to back.
     int n_chunks = 1;
     if (S >= 65536) {
+        n_chunks = kDefaultRunChunks;
         if (const char* e = std::getenv("STOAT_GPU_OVERLAP")) {
             const int v = std::atoi(e);
             n_chunks = v <= 1 ? 1 : (v > kMaxRunChunks ? kMaxRunChunks : v);
         }
     }
+    bool lean = n_chunks > 1;
+    if (const char* e = std::getenv("STOAT_GPU_K1_LEAN")) lean = std::atoi(e) != 0;
+    if (int frc = finalize_timing(ctx)) return frc;
     ctx->timing.launches = 0;
+    cudaEvent_t* ev = x->ring[x->run_seq % kRunRing];
+    x->ring_kind[x->run_seq % kRunRing] = 1;
     const uint64_t per = (S + uint64_t(n_chunks) - 1) / uint64_t(n_chunks);
     cudaStream_t main_st = ctx->stream, side_st = n_chunks > 1 ? ctx->copy_stream : ctx->stream;
-    CK(cudaEventRecord(ctx->ev[2], main_st));
+    CK(cudaEventRecord(ev[0], main_st));
+    if (!S) {
+        CK(cudaEventRecord(ev[1], main_st));
+        CK(cudaEventRecord(ev[2], main_st));
+    }
     for (int c = 0; c < n_chunks && S; ++c) {
         const uint64_t s0 = per * uint64_t(c);
         if (s0 >= S) break;
         const uint64_t cnt = std::min<uint64_t>(per, S - s0);
         CK(launch_path_and_popc(matrix_view(ctx), ctx->case_mask.as<uint8_t>(), ctx->n_case_hap, ctx->batch, ctx->n_big,
                                 x->max_stage_rows, ctx->counts.as<uint32_t>(), ctx->num_sms, ctx->k1_variant, main_st,
-                                &ctx->timing.launches, s0, cnt));
+                                &ctx->timing.launches, s0, cnt, lean));
         if (n_chunks > 1) {
             CK(cudaEventRecord(x->chunk_done[c], main_st));
             CK(cudaStreamWaitEvent(side_st, x->chunk_done[c], 0));
         } else {
-            CK(cudaEventRecord(ctx->ev[3], main_st));
+            CK(cudaEventRecord(ev[1], main_st));
         }
-        if (c == 0) CK(cudaEventRecord(ctx->ev[4], side_st));
+        if (c == 0) CK(cudaEventRecord(ev[2], side_st));
         CK(launch_binary_stats(ctx->batch, ctx->counts.as<uint32_t>(), *thr, ctx->total_sum.as<uint64_t>(),
-                               ctx->filtered.as<uint8_t>(), ctx->p_a.as<double>(), ctx->p_b.as<double>(),
+                               ctx->filtered_bin.as<uint8_t>(), ctx->p_a.as<double>(), ctx->p_b.as<double>(),
                                ctx->code_a.as<uint8_t>(), ctx->code_b.as<uint8_t>(), ctx->fisher_tab.as<uint4>(),
                                ctx->fisher_idx.as<uint32_t>(), ctx->fisher_cnt.as<uint32_t>() + 2 * c, ctx->num_sms,
-                               side_st, s0, cnt));
+                               side_st, s0, cnt, n_chunks > 1));
         ctx->timing.launches += 2;
     }
-    if (n_chunks > 1) CK(cudaEventRecord(ctx->ev[3], main_st));  // end of the last count pass
-    CK(cudaEventRecord(ctx->ev[5], side_st));
-    if (n_chunks > 1) CK(cudaStreamWaitEvent(main_st, ctx->ev[5], 0));
+    if (n_chunks > 1 && S) CK(cudaEventRecord(ev[1], main_st));  // end of the last count pass
+    CK(cudaEventRecord(ev[3], side_st));
+    if (n_chunks > 1) CK(cudaStreamWaitEvent(main_st, ev[3], 0));
     ctx->have_binary_counts = true;
     ctx->have_binary_result = true;
-    CK(cudaMemcpyAsync(x->fisher_readback, ctx->fisher_cnt.p, 8 * kMaxRunChunks, cudaMemcpyDeviceToHost, main_st));
-    CK(cudaStreamSynchronize(main_st));
-    uint32_t n_fisher = 0;
-    for (int c = 0; c < n_chunks; ++c) n_fisher += x->fisher_readback[2 * c];
-    x->readback[0] = n_fisher;
-    ctx->timing.n_general = ctx->n_big;
-    ctx->timing.n_fisher = ctx->batch.n_snarls ? x->readback[0] : 0;
-    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));
-    CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ctx->ev[4], ctx->ev[5]));
+    // nothing is read back here: the run is asynchronous, stoat_gpu_binary_fetch / stoat_gpu_last_timing wait for it
+    ++x->run_seq;
+    x->pending = 1;
+    x->pending_chunks = n_chunks;
     return STOAT_GPU_OK;
 }
 
@@ -642,13 +755,14 @@ int stoat_gpu_binary_fetch(stoat_gpu_ctx* ctx, stoat_gpu_binary_out* out) {
     if (P && out->g0) CK(cudaMemcpyAsync(out->g0, ctx->counts.as<uint32_t>(), P * 4, k, ctx->stream));
     if (P && out->g1) CK(cudaMemcpyAsync(out->g1, ctx->counts.as<uint32_t>() + P, P * 4, k, ctx->stream));
     if (S && out->total_sum) CK(cudaMemcpyAsync(out->total_sum, ctx->total_sum.p, S * 8, k, ctx->stream));
-    if (S && out->filtered) CK(cudaMemcpyAsync(out->filtered, ctx->filtered.p, S, k, ctx->stream));
+    if (S && out->filtered) CK(cudaMemcpyAsync(out->filtered, ctx->filtered_bin.p, S, k, ctx->stream));
     if (S && out->p_chi2) CK(cudaMemcpyAsync(out->p_chi2, ctx->p_a.p, S * 8, k, ctx->stream));
     if (S && out->p_fisher) CK(cudaMemcpyAsync(out->p_fisher, ctx->p_b.p, S * 8, k, ctx->stream));
     if (S && out->chi2_code) CK(cudaMemcpyAsync(out->chi2_code, ctx->code_a.p, S, k, ctx->stream));
     if (S && out->fisher_code) CK(cudaMemcpyAsync(out->fisher_code, ctx->code_b.p, S, k, ctx->stream));
     CK(cudaEventRecord(ctx->ev[7], ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    if (int rc = finalize_timing(ctx)) return rc;
     CK(cudaEventElapsedTime(&ctx->timing.d2h_ms, ctx->ev[6], ctx->ev[7]));
     return STOAT_GPU_OK;
 }
@@ -707,7 +821,10 @@ static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int ph
     if (phase == 2 && !x->q.have_partials) return fail(ctx, STOAT_GPU_ERR_STATE, "quantitative_solve_staged: run quantitative_moments_staged first");
     // the general-path list grows during the run: reset its length to what prep put there
     x->counters_host[0] = ctx->n_big;
-    CK(cudaMemcpyAsync(ctx->d_counters.p, x->counters_host, 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (ctx->n_big == 0)
+        CK(cudaMemsetAsync(ctx->d_counters.p, 0, 4, ctx->stream));
+    else
+        CK(cudaMemcpyAsync(ctx->d_counters.p, x->counters_host, 4, cudaMemcpyHostToDevice, ctx->stream));
     // filtered snarls keep NaN / NA outputs (the moments path writes them in K4, which visits every snarl)
     if (S && phase != 1 && !quant_fast_path(ctx->pitch, x->max_stage_rows, ctx->k1_variant, uint32_t(ctx->n_covar))) {
         CK(cudaMemsetAsync(ctx->q_p.p, 0xFF, S * 8, ctx->stream));
@@ -720,8 +837,12 @@ static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int ph
     QuantOut out{ctx->q_allele.as<uint32_t>(), ctx->filtered.as<uint8_t>(), ctx->q_nused.as<uint32_t>(),
                  ctx->q_p.as<double>(),        ctx->q_r2.as<double>(),      ctx->q_beta.as<double>(),
                  ctx->q_se.as<double>(),       ctx->q_code.as<uint8_t>()};
+    if (int frc = finalize_timing(ctx)) return frc;
     ctx->timing.launches = 0;
-    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    cudaEvent_t* ev = x->ring[x->run_seq % kRunRing];
+    x->ring_kind[x->run_seq % kRunRing] = 2;
+    CK(cudaEventRecord(ev[0], ctx->stream));
+    if (!S) CK(cudaEventRecord(ev[1], ctx->stream));
     CK(launch_quantitative_impl(matrix_view(ctx), ctx->y.as<double>(), x->q.ys.as<double>(), x->q.sy_all,
                                 x->q.syy_all, ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar),
                                 ctx->batch, x->max_stage_rows, *thr, out,
@@ -729,27 +850,12 @@ static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int ph
                                 x->q.part_d.as<double>(), x->q.slow.as<uint32_t>(), x->q.lean_rec.as<uint4>(),
                                 x->q.yslices.as<uint8_t>(),
                                 x->q.yc.as<double>(), x->q.y_scale, ctx->num_sms, ctx->k1_variant, ctx->stream,
-                                &ctx->timing.launches, ctx->ev[4], phase, x->q.tail_t.as<double>(),
+                                &ctx->timing.launches, ev[1], phase, x->q.tail_t.as<double>(),
                                 x->q.tail_x.as<double>(), x->q.tail_df.as<uint32_t>(), x->stage_gen, &x->q.lean_key));
-    if (phase == 2) CK(cudaEventRecord(ctx->ev[4], ctx->stream));
-    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
-    CK(cudaMemcpyAsync(x->readback, ctx->d_counters.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    ctx->timing.n_general = S ? x->readback[0] : 0;
-    ctx->timing.n_fisher = 0;
-    if (S && x->readback[0] && std::getenv("STOAT_GPU_DEBUG_GENERAL")) {  // which snarls took the general path
-        std::vector<uint32_t> ids(std::min<uint32_t>(x->readback[0], 64));
-        CK(cudaMemcpy(ids.data(), ctx->batch.big_list, ids.size() * 4, cudaMemcpyDeviceToHost));
-        std::fprintf(stderr, "[stoat_gpu] general path: %u snarls:", x->readback[0]);
-        for (uint32_t id : ids) std::fprintf(stderr, " %u", id);
-        std::fprintf(stderr, "\n");
-    }
-    if (S) {
-        CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[4]));  // the moments pass (K3M / K3R / K3)
-        CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ctx->ev[4], ctx->ev[3]));  // left-over list, K4, general path
-    } else {
-        ctx->timing.table_ms = ctx->timing.stats_ms = 0.f;
-    }
+    if (phase == 2) CK(cudaEventRecord(ev[1], ctx->stream));
+    CK(cudaEventRecord(ev[3], ctx->stream));
+    ++x->run_seq;
+    x->pending = 2;
     x->q.have_partials = phase == 1;
     ctx->have_quant_result = phase != 1;
     return STOAT_GPU_OK;
@@ -774,6 +880,8 @@ int stoat_gpu_quantitative_partials_dev(stoat_gpu_ctx* ctx, uint32_t** ints_dev,
         return fail(ctx, STOAT_GPU_ERR_ARG, "quantitative_partials_dev: NULL argument");
     CtxExtra* x = extra_of(ctx);
     if (!x->q.have_partials) return fail(ctx, STOAT_GPU_ERR_STATE, "quantitative_partials_dev: no partial sums (run quantitative_moments_staged)");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));  // the caller's collective runs on its own stream
     const uint64_t slices = std::max<uint32_t>(quant_lean_slices(ctx->pitch, ctx->n_cols, x->max_stage_rows), 1);
     *ints_dev = x->q.part_i.as<uint32_t>();
     *n_ints = slices * 7 * ctx->batch.n_snarls;
@@ -800,6 +908,7 @@ int stoat_gpu_quantitative_fetch(stoat_gpu_ctx* ctx, stoat_gpu_quant_out* out) {
     if (S && out->code) CK(cudaMemcpyAsync(out->code, ctx->q_code.p, S, k, ctx->stream));
     CK(cudaEventRecord(ctx->ev[7], ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    if (int rc = finalize_timing(ctx)) return rc;
     CK(cudaEventElapsedTime(&ctx->timing.d2h_ms, ctx->ev[6], ctx->ev[7]));
     return STOAT_GPU_OK;
 }
@@ -883,6 +992,7 @@ int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const
     int rc = eqtl_stage(ctx, paths, genes, &n_pairs);
     if (rc) return rc;
     const float h2d = ctx->timing.h2d_ms;
+    ctx->have_quant_result = false;  // the pair outputs live in the quantitative result buffers
     if ((rc = eqtl_reserve_pairs(ctx, n_pairs))) return rc;
     const uint64_t S = ctx->batch.n_snarls, P = ctx->batch.n_paths;
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
@@ -936,7 +1046,9 @@ static int eqtl_prepare_expression(stoat_gpu_ctx* ctx, uint64_t G) {
     CK(launch_eqtl_centre(ctx->e_expr.as<double>(), uint32_t(G), uint32_t(n), uint32_t(n_pad), ctx->e_yc.as<double>(),
                           ctx->e_tot.as<double>(), ctx->e_tot2.as<double>(), ctx->stream));
     ctx->e_n_genes = G;
+    extra_of(ctx)->expr_cols = ctx->n_cols;
     ctx->have_expression = true;
+    ctx->have_eqtl_summary = false;
     return STOAT_GPU_OK;
 }
 
@@ -977,6 +1089,11 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     if (ctx->n_covar && ctx->n_samples_covar * 2 < ctx->n_cols)
         return fail(ctx, STOAT_GPU_ERR_ARG, "eqtl: fewer covariate rows than samples");
     CK(cudaSetDevice(ctx->device));
+    if (extra_of(ctx)->expr_cols != ctx->n_cols)
+        return fail(ctx, STOAT_GPU_ERR_STATE, "eqtl_dense_run_staged: the expression matrix was prepared for another matrix width");
+    if (int frc = finalize_timing(ctx)) return frc;
+    ctx->have_quant_result = false;  // filtered / allele_paths / pair outputs are shared with the quantitative trait
+    ctx->have_eqtl_summary = false;
     const BatchDev& b = ctx->batch;
     const uint64_t S = b.n_snarls, G = ctx->e_n_genes, n = ctx->n_cols / 2;
     CK(ctx->q_allele.reserve(std::max<uint64_t>(b.n_paths * 4, 16)));
@@ -1116,7 +1233,36 @@ int stoat_gpu_format_value(double value, uint8_t code, char* buf, size_t buf_len
 
 int stoat_gpu_last_timing(const stoat_gpu_ctx* ctx, stoat_gpu_timing* out) {
     if (!ctx || !out) return STOAT_GPU_ERR_ARG;
+    if (int rc = finalize_timing(const_cast<stoat_gpu_ctx*>(ctx))) return rc;  // waits for a run that is still in flight
     *out = ctx->timing;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_mean_timing(stoat_gpu_ctx* ctx, uint32_t n_runs, stoat_gpu_timing* out) {
+    if (!ctx || !out) return STOAT_GPU_ERR_ARG;
+    if (int rc = finalize_timing(ctx)) return rc;
+    CtxExtra* x = extra_of(ctx);
+    *out = ctx->timing;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    uint64_t n = std::min<uint64_t>(std::min<uint64_t>(n_runs, x->run_seq), kRunRing);
+    if (n == 0) return STOAT_GPU_OK;
+    const uint8_t kind = x->ring_kind[(x->run_seq - 1) % kRunRing];
+    double table = 0.0, stats = 0.0;
+    uint64_t used = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+        const uint64_t slot = (x->run_seq - 1 - i) % kRunRing;
+        if (x->ring_kind[slot] != kind) break;  // an older run of the other trait
+        cudaEvent_t* ev = x->ring[slot];
+        float t = 0.f, u = 0.f;
+        CK(cudaEventElapsedTime(&t, ev[0], ev[1]));
+        CK(cudaEventElapsedTime(&u, kind == 1 ? ev[2] : ev[1], ev[3]));
+        table += t;
+        stats += u;
+        ++used;
+    }
+    out->table_ms = float(table / double(used));
+    out->stats_ms = float(stats / double(used));
     return STOAT_GPU_OK;
 }
 

@@ -16,6 +16,8 @@ struct DevBuf {
     size_t cap = 0;
     cudaError_t reserve(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
+        // The old contents are never needed after a growth, so the old block goes first (a C5-sized matrix and its
+        // replacement do not fit side by side); on failure the buffer is left empty, never dangling.
         if (p) cudaFree(p);
         p = nullptr;
         cap = 0;
@@ -23,10 +25,17 @@ struct DevBuf {
         size_t want = bytes + bytes / 8 + 256;
         cudaError_t e = cudaMalloc(&p, want);
         if (e != cudaSuccess) {
+            (void)cudaGetLastError();  // clear the failed attempt: it would surface at the next launch's error check
+            p = nullptr;
             e = cudaMalloc(&p, bytes);
             want = bytes;
         }
-        if (e == cudaSuccess) cap = want;
+        if (e == cudaSuccess)
+            cap = want;
+        else {
+            (void)cudaGetLastError();
+            p = nullptr;
+        }
         return e;
     }
     void release() {
@@ -84,12 +93,12 @@ cudaError_t launch_binary_prep(const BatchDev& b, uint64_t n_matrix_rows, cudaSt
 cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, uint32_t n_case_hap, const BatchDev& b,
                                  uint32_t n_big, uint32_t max_stage_rows, uint32_t* counts, int num_sms, int variant,
                                  cudaStream_t st, uint32_t* launches, uint64_t s_begin = 0,
-                                 uint64_t s_count = ~uint64_t(0));
+                                 uint64_t s_count = ~uint64_t(0), bool lean_registers = false);
 cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const stoat_gpu_thresholds& thr,
                                 uint64_t* total_sum, uint8_t* filtered, double* p_chi2, double* p_fisher,
                                 uint8_t* chi2_code, uint8_t* fisher_code, uint4* fisher_tab, uint32_t* fisher_idx,
                                 uint32_t* fisher_counters, int num_sms, cudaStream_t st, uint64_t s_begin = 0,
-                                uint64_t s_count = ~uint64_t(0));
+                                uint64_t s_count = ~uint64_t(0), bool beside_count_pass = false);
 // post-processing (kernels_post.cu): Benjamini-Hochberg adjustment
 size_t bh_temp_bytes(uint64_t n);
 cudaError_t launch_bh_adjust(const double* p, uint64_t n, double* out, uint64_t* keys_sorted, uint32_t* idx_in,
@@ -167,7 +176,8 @@ struct stoat_gpu_ctx {
     bool have_batch = false;
 
     // results (device)
-    stoat::DevBuf counts, total_sum, filtered, p_a, p_b, code_a, code_b;  // binary
+    stoat::DevBuf counts, total_sum, filtered_bin, p_a, p_b, code_a, code_b;  // binary (its own filter flags)
+    stoat::DevBuf filtered;                                                    // quantitative / eQTL filter flags
     stoat::DevBuf fisher_tab, fisher_idx, fisher_cnt;                      // Fisher work list
     stoat::DevBuf q_allele, q_nused, q_p, q_r2, q_beta, q_se, q_code;      // quantitative / eQTL pairs
     stoat::DevBuf e_expr, e_gene_off, e_gene_idx, e_min_p, e_argmin, e_nbelow;  // eQTL

@@ -134,28 +134,38 @@ struct K1Params {
     uint32_t n_case_hap;   // popcount of the case mask
     uint32_t stage_rows;   // row slots per stage
     uint32_t n_stages;     // pipeline depth per warp
+    uint32_t chunk_bytes;  // bytes of every row one stage holds (== pitch when a stage holds whole rows)
+    uint32_t n_chunks;     // column chunks per row: ceil(pitch / chunk_bytes)
 };
 
-// AND of R staged rows for one 16-byte chunk, then the two popcounts, packed as all | case << 16 (n_hap < 65536) or
-// kept apart.  R is a compile-time constant so the loads and ANDs are straight-line code.
+// AND of R staged rows for one 16-byte vector, then the two popcounts.  R is a compile-time constant so the loads and
+// ANDs are straight-line code.  `nvec` 16-byte vectors of this column chunk, `mask_c` the case mask at the chunk's offset.
 template <int R>
-__device__ __forceinline__ void path_counts(const uint8_t* rows_s, const uint8_t* mask_s, const uint32_t (&roff)[4],
-                                            uint32_t lane, uint32_t chunks, uint32_t& n_all, uint32_t& n_case) {
-    for (uint32_t c = lane; c < chunks; c += 32) {
+__device__ __forceinline__ void path_counts(const uint8_t* rows_s, const uint8_t* mask_c, const uint32_t (&roff)[4],
+                                            uint32_t lane, uint32_t nvec, uint32_t& n_all, uint32_t& n_case) {
+    for (uint32_t c = lane; c < nvec; c += 32) {
         uint4 v = *reinterpret_cast<const uint4*>(rows_s + roff[0] + c * 16);
 #pragma unroll
         for (int r = 1; r < R; ++r) v = and4(v, *reinterpret_cast<const uint4*>(rows_s + roff[r] + c * 16));
-        const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
+        const uint4 m = *reinterpret_cast<const uint4*>(mask_c + c * 16);
         n_all += popc4(v);
         n_case += popc4(and4(v, m));
     }
 }
 
-__global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Params p) {
+// One warp = one pipeline.  A work item is (snarl, column chunk): the stage receives the snarl's path program and the
+// bytes [chunk * chunk_bytes, +chunk_bytes) of each of its distinct rows, so the shared memory a stage needs — and with it
+// the number of warps and copies in flight per SM — does not depend on the haplotype count (C3: 1,280-byte rows, one
+// chunk; C5: 6,272-byte rows, four chunks of 1,568 bytes).  A warp walks the chunks of a snarl in order and carries the
+// per-lane popcounts across them; kMulti = false is the one-chunk case with the hand-over code compiled out.
+template <bool kMulti>
+__device__ __forceinline__ void path_and_popc_body(const K1Params& p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t n_warps = blockDim.x >> 5;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t stage_bytes = kBlobBytes + p.stage_rows * p.pitch;
+    const uint32_t slot = kMulti ? p.chunk_bytes : p.pitch;  // bytes of a row in a stage
+    const uint32_t n_chunks = kMulti ? p.n_chunks : 1u;
+    const uint32_t stage_bytes = kBlobBytes + p.stage_rows * slot;
     // layout: [full barriers: n_warps * n_stages * 8][pad to 128][case mask: pitch][pad to 128][stages]
     uint64_t* full = reinterpret_cast<uint64_t*>(smem);
     const uint32_t bar_bytes = (n_warps * p.n_stages * 8 + 127) & ~127u;
@@ -175,40 +185,59 @@ __global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Param
     const uint64_t stride = uint64_t(gridDim.x) * n_warps;
     uint64_t* my_full = full + warp * p.n_stages;
     uint8_t* my_stages = stages + size_t(warp) * p.n_stages * stage_bytes;
-    const uint32_t chunks = p.pitch / 16;
     const uint64_t policy = make_evict_first_policy();
     const bool packable = p.n_hap < 65536u;  // both counts of a path fit one 32-bit warp reduction
 
-    // prologue: fill the pipeline
-    {
-        uint64_t s = gw;
-        for (uint32_t st = 0; st < p.n_stages && s < p.n_snarls; ++st, s += stride)
-            issue_stage(load_rec_word(p.rec, s, lane), lane, my_stages + size_t(st) * stage_bytes, &my_full[st], p.rows,
-                        p.blob, p.pitch, policy);
-    }
+    // issue cursor: the (snarl, chunk) the next refill loads
+    uint64_t s_iss = gw;
+    uint32_t c_iss = 0;
+    auto issue = [&](uint32_t rec_word, uint32_t stage) {
+        if (kMulti) {
+            const uint32_t off = c_iss * slot;
+            const uint32_t bytes = (p.pitch - off < slot) ? p.pitch - off : slot;
+            issue_stage_slice(rec_word, lane, my_stages + size_t(stage) * stage_bytes, &my_full[stage], p.rows, p.blob,
+                              p.pitch, off, bytes, slot, policy);
+            if (++c_iss == n_chunks) {
+                c_iss = 0;
+                s_iss += stride;
+            }
+        } else {
+            issue_stage(rec_word, lane, my_stages + size_t(stage) * stage_bytes, &my_full[stage], p.rows, p.blob, p.pitch,
+                        policy);
+            s_iss += stride;
+        }
+    };
 
-    uint32_t it = 0;
-    for (uint64_t s = gw; s < p.n_snarls; s += stride, ++it) {
+    // prologue: fill the pipeline
+    for (uint32_t st = 0; st < p.n_stages && s_iss < p.n_snarls; ++st) issue(load_rec_word(p.rec, s_iss, lane), st);
+
+    uint32_t it = 0, chunk = 0;
+    uint32_t a0 = 0, c0 = 0, a1 = 0, c1 = 0;  // the biallelic shape's per-lane counts, carried over a snarl's chunks
+    for (uint64_t s = gw; s < p.n_snarls; ++it) {
         const uint32_t stage = it % p.n_stages;
         const uint32_t parity = (it / p.n_stages) & 1u;
         // record of the snarl that will refill this stage: requested now, consumed after the compute
-        const uint64_t s_next = s + uint64_t(p.n_stages) * stride;
-        uint32_t next_word = (s_next < p.n_snarls) ? load_rec_word(p.rec, s_next, lane) : 0u;
+        const bool more = s_iss < p.n_snarls;
+        uint32_t next_word = more ? load_rec_word(p.rec, s_iss, lane) : 0u;
         mbar_wait(&my_full[stage], parity);
         const uint8_t* blob = my_stages + size_t(stage) * stage_bytes;
         const uint8_t* rows_s = blob + kBlobBytes;
         const uint32_t hdr = *reinterpret_cast<const uint32_t*>(blob);
         const uint32_t np = hdr & 0xFFu;
         const uint32_t p0 = *reinterpret_cast<const uint32_t*>(blob + 4);
+        const uint32_t col0 = chunk * slot;  // byte offset of this chunk in a row / in the case mask
+        const uint32_t nvec = ((p.pitch - col0 < slot) ? p.pitch - col0 : slot) / 16;
+        const uint8_t* mask_c = mask_s + col0;
+        const bool first = !kMulti || chunk == 0, last = !kMulti || chunk + 1 == n_chunks;
         if ((hdr >> 8 & 0xFFu) == 1u) {
             // ---- the common shape: two paths with two checked edges each (a biallelic snarl) ----------
             const uint32_t loc = uint32_t(blob[10]) | uint32_t(blob[11]) << 8 | uint32_t(blob[12]) << 16 |
                                  uint32_t(blob[13]) << 24;
-            const uint32_t o00 = (loc & 0xFFu) * p.pitch, o01 = (loc >> 8 & 0xFFu) * p.pitch;
-            const uint32_t o10 = (loc >> 16 & 0xFFu) * p.pitch, o11 = (loc >> 24) * p.pitch;
-            uint32_t a0 = 0, c0 = 0, a1 = 0, c1 = 0;
-            for (uint32_t c = lane; c < chunks; c += 32) {
-                const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
+            const uint32_t o00 = (loc & 0xFFu) * slot, o01 = (loc >> 8 & 0xFFu) * slot;
+            const uint32_t o10 = (loc >> 16 & 0xFFu) * slot, o11 = (loc >> 24) * slot;
+            if (first) a0 = c0 = a1 = c1 = 0;
+            for (uint32_t c = lane; c < nvec; c += 32) {
+                const uint4 m = *reinterpret_cast<const uint4*>(mask_c + c * 16);
                 const uint4 v0 = and4(*reinterpret_cast<const uint4*>(rows_s + o00 + c * 16),
                                       *reinterpret_cast<const uint4*>(rows_s + o01 + c * 16));
                 const uint4 v1 = and4(*reinterpret_cast<const uint4*>(rows_s + o10 + c * 16),
@@ -218,46 +247,52 @@ __global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Param
                 a1 += popc4(v1);
                 c1 += popc4(and4(v1, m));
             }
-            if (packable) {
-                const uint32_t r0 = __reduce_add_sync(0xffffffffu, a0 | c0 << 16);
-                const uint32_t r1 = __reduce_add_sync(0xffffffffu, a1 | c1 << 16);
-                a0 = r0 & 0xFFFFu; c0 = r0 >> 16;
-                a1 = r1 & 0xFFFFu; c1 = r1 >> 16;
-            } else {
-                a0 = __reduce_add_sync(0xffffffffu, a0); c0 = __reduce_add_sync(0xffffffffu, c0);
-                a1 = __reduce_add_sync(0xffffffffu, a1); c1 = __reduce_add_sync(0xffffffffu, c1);
-            }
-            if (lane < 4) {  // lane = path + 2 * (cases ? 1 : 0)
-                const uint32_t a = (lane & 1u) ? a1 : a0, c = (lane & 1u) ? c1 : c0;
-                uint32_t* dst = (lane & 2u) ? p.g1 : p.g0;
-                dst[p0 + (lane & 1u)] = (lane & 2u) ? c : a - c;  // cases / controls (binary_table.cpp:35-39)
+            if (last) {
+                uint32_t ra0, rc0, ra1, rc1;
+                if (packable) {
+                    const uint32_t r0 = __reduce_add_sync(0xffffffffu, a0 | c0 << 16);
+                    const uint32_t r1 = __reduce_add_sync(0xffffffffu, a1 | c1 << 16);
+                    ra0 = r0 & 0xFFFFu; rc0 = r0 >> 16;
+                    ra1 = r1 & 0xFFFFu; rc1 = r1 >> 16;
+                } else {
+                    ra0 = __reduce_add_sync(0xffffffffu, a0); rc0 = __reduce_add_sync(0xffffffffu, c0);
+                    ra1 = __reduce_add_sync(0xffffffffu, a1); rc1 = __reduce_add_sync(0xffffffffu, c1);
+                }
+                if (lane < 4) {  // lane = path + 2 * (cases ? 1 : 0)
+                    const uint32_t a = (lane & 1u) ? ra1 : ra0, c = (lane & 1u) ? rc1 : rc0;
+                    uint32_t* dst = (lane & 2u) ? p.g1 : p.g0;
+                    dst[p0 + (lane & 1u)] = (lane & 2u) ? c : a - c;  // cases / controls (binary_table.cpp:35-39)
+                }
             }
         } else {
-            // ---- any other staged shape: one path at a time ----------------------------------------------
+            // ---- any other staged shape: one path at a time; with several chunks lane 0 adds each chunk's counts to
+            // what the earlier chunks of the snarl left in g0 / g1 (same thread, program order) ----------------------
             uint32_t off = kBlobHeader + np;
             for (uint32_t j = 0; j < np; ++j) {
                 const uint32_t code = blob[kBlobHeader + j];
                 uint32_t n_all = 0, n_case = 0;
                 if (code == 0u) {  // no checked edge: every haplotype (snarl_analyzer.cpp:343-354)
-                    n_all = p.n_hap;
-                    n_case = p.n_case_hap;
+                    if (first) {
+                        n_all = p.n_hap;
+                        n_case = p.n_case_hap;
+                    }
                 } else if (code != 0xFFu) {
                     if (code <= 4u) {
                         uint32_t roff[4];
 #pragma unroll
-                        for (int r = 0; r < 4; ++r) roff[r] = (uint32_t(r) < code) ? uint32_t(blob[off + r]) * p.pitch : 0u;
+                        for (int r = 0; r < 4; ++r) roff[r] = (uint32_t(r) < code) ? uint32_t(blob[off + r]) * slot : 0u;
                         switch (code) {
-                            case 1: path_counts<1>(rows_s, mask_s, roff, lane, chunks, n_all, n_case); break;
-                            case 2: path_counts<2>(rows_s, mask_s, roff, lane, chunks, n_all, n_case); break;
-                            case 3: path_counts<3>(rows_s, mask_s, roff, lane, chunks, n_all, n_case); break;
-                            default: path_counts<4>(rows_s, mask_s, roff, lane, chunks, n_all, n_case); break;
+                            case 1: path_counts<1>(rows_s, mask_c, roff, lane, nvec, n_all, n_case); break;
+                            case 2: path_counts<2>(rows_s, mask_c, roff, lane, nvec, n_all, n_case); break;
+                            case 3: path_counts<3>(rows_s, mask_c, roff, lane, nvec, n_all, n_case); break;
+                            default: path_counts<4>(rows_s, mask_c, roff, lane, nvec, n_all, n_case); break;
                         }
                     } else {
-                        for (uint32_t c = lane; c < chunks; c += 32) {
-                            uint4 v = *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[off]) * p.pitch + c * 16);
+                        for (uint32_t c = lane; c < nvec; c += 32) {
+                            uint4 v = *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[off]) * slot + c * 16);
                             for (uint32_t r = 1; r < code; ++r)
-                                v = and4(v, *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[off + r]) * p.pitch + c * 16));
-                            const uint4 m = *reinterpret_cast<const uint4*>(mask_s + c * 16);
+                                v = and4(v, *reinterpret_cast<const uint4*>(rows_s + uint32_t(blob[off + r]) * slot + c * 16));
+                            const uint4 m = *reinterpret_cast<const uint4*>(mask_c + c * 16);
                             n_all += popc4(v);
                             n_case += popc4(and4(v, m));
                         }
@@ -273,18 +308,40 @@ __global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Param
                     }
                 }
                 if (lane == 0) {
-                    p.g0[p0 + j] = n_all - n_case;  // controls  (binary_table.cpp:37-39)
-                    p.g1[p0 + j] = n_case;          // cases     (binary_table.cpp:35-36)
+                    uint32_t ctl = n_all - n_case, cas = n_case;  // controls / cases (binary_table.cpp:35-39)
+                    if (!first) {
+                        ctl += p.g0[p0 + j];
+                        cas += p.g1[p0 + j];
+                    }
+                    p.g0[p0 + j] = ctl;
+                    p.g1[p0 + j] = cas;
                 }
             }
         }
-        // all lanes are done reading this stage: refill it with the snarl n_stages ahead
+        // all lanes are done reading this stage: refill it with the item n_stages ahead
         __syncwarp();
         asm volatile("" : "+r"(next_word));  // keep the record's consumers below the compute
-        if (s_next < p.n_snarls)
-            issue_stage(next_word, lane, my_stages + size_t(stage) * stage_bytes, &my_full[stage], p.rows, p.blob,
-                        p.pitch, policy);
+        if (more) issue(next_word, stage);
+        if (kMulti) {
+            if (++chunk == n_chunks) {
+                chunk = 0;
+                s += stride;
+            }
+        } else {
+            s += stride;
+        }
     }
+}
+
+__global__ void __launch_bounds__(512, 1) path_and_popc_tma_kernel(const K1Params p) { path_and_popc_body<false>(p); }
+__global__ void __launch_bounds__(512, 1) path_and_popc_tma_chunked_kernel(const K1Params p) { path_and_popc_body<true>(p); }
+// The same two kernels held to 64 registers per thread: 416 threads x 64 leave room in an SM's register file for four
+// fisher_exact blocks next to the persistent count pass (the overlapped run of abi.cu: FP64 work under the HBM stream).
+__global__ void __maxnreg__(64) path_and_popc_tma_lean_kernel(const K1Params p) {
+    path_and_popc_body<false>(p);
+}
+__global__ void __maxnreg__(64) path_and_popc_tma_chunked_lean_kernel(const K1Params p) {
+    path_and_popc_body<true>(p);
 }
 
 // =================================================================================================
@@ -334,25 +391,41 @@ __global__ void __launch_bounds__(256) path_and_popc_ldg_kernel(const uint8_t* _
 // configuration of the TMA kernel for a given pitch / stage width; returns false if a single stage
 // does not fit shared memory (then everything takes the LDG path)
 struct K1Config {
-    uint32_t n_warps, n_stages, stage_rows, smem_bytes;
+    uint32_t n_warps, n_stages, stage_rows, smem_bytes, chunk_bytes, n_chunks;
 };
+static int k1_env(const char* name, int dflt) {
+    const char* e = std::getenv(name);
+    return e ? std::atoi(e) : dflt;
+}
 static bool choose_k1_config(uint32_t pitch, uint32_t stage_rows, K1Config& cfg) {
     const uint32_t budget = 200 * 1024;
     if (stage_rows == 0) stage_rows = 1;
-    const uint32_t stage_bytes = kBlobBytes + stage_rows * pitch;
+    // Rows wider than 2 KB are staged in column chunks of about 1.5 KB, so that the stage stays the size it has at C3
+    // (1,280-byte rows) and the SM keeps ~10-13 warps x 2 stages in flight whatever the haplotype count.  Whole-row stages
+    // at H = 50,000 (6,272-byte rows) would leave 2 warps per SM.
+    uint32_t target = uint32_t(k1_env("STOAT_GPU_K1_CHUNK", 1536));
+    if (target < 256) target = 256;
+    target = (target + 15u) & ~15u;
+    uint32_t n_chunks = 1, chunk_bytes = pitch;
+    if (pitch > 2048 || pitch > target + target / 3) {
+        n_chunks = (pitch + target - 1) / target;
+        chunk_bytes = (((pitch + n_chunks - 1) / n_chunks) + 15u) & ~15u;
+        n_chunks = (pitch + chunk_bytes - 1) / chunk_bytes;
+    }
+    const uint32_t stage_bytes = kBlobBytes + stage_rows * chunk_bytes;
     const uint32_t mask_bytes = (pitch + 127) & ~127u;
     if (mask_bytes + 2 * stage_bytes + 1024 > budget) return false;
     const uint32_t total_stages = (budget - mask_bytes - 1024) / stage_bytes;
     // measured on B200 (C3, profiles/): 13 warps x 2 stages 0.78 ms, 8 x 3 0.92 ms, 6 x 4 1.22 ms — a warp's compute
     // chain, not the copy depth, limits the rate, so shared memory goes to warps first
     uint32_t n_stages = 2;
-    if (const char* e = std::getenv("STOAT_GPU_K1_STAGES")) {
-        const int v = std::atoi(e);
+    {
+        const int v = k1_env("STOAT_GPU_K1_STAGES", 0);
         if (v >= 2 && v <= 8 && uint32_t(v) <= total_stages) n_stages = uint32_t(v);
     }
     uint32_t n_warps = total_stages / n_stages;
-    if (const char* e = std::getenv("STOAT_GPU_K1_WARPS")) {
-        const int v = std::atoi(e);
+    {
+        const int v = k1_env("STOAT_GPU_K1_WARPS", 0);
         if (v >= 1 && uint32_t(v) <= n_warps) n_warps = uint32_t(v);
     }
     if (n_warps > 16) {
@@ -364,6 +437,8 @@ static bool choose_k1_config(uint32_t pitch, uint32_t stage_rows, K1Config& cfg)
     cfg.n_warps = n_warps;
     cfg.n_stages = n_stages;
     cfg.stage_rows = stage_rows;
+    cfg.chunk_bytes = chunk_bytes;
+    cfg.n_chunks = n_chunks;
     const uint32_t bar_bytes = (n_warps * n_stages * 8 + 127) & ~127u;
     cfg.smem_bytes = bar_bytes + mask_bytes + n_warps * n_stages * stage_bytes;
     return true;
@@ -372,7 +447,7 @@ static bool choose_k1_config(uint32_t pitch, uint32_t stage_rows, K1Config& cfg)
 cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, uint32_t n_case_hap,
                                      const BatchDev& b, uint32_t n_big, uint32_t max_stage_rows, uint32_t* counts,
                                      int num_sms, int variant, cudaStream_t st, uint32_t* launches, uint64_t s_begin,
-                                     uint64_t s_count) {
+                                     uint64_t s_count, bool lean_registers) {
     // [s_begin, s_begin + s_count): the snarls of this launch (the run is cut into chunks so that the statistics of a chunk
     // overlap the count pass of the next one, abi.cu); snarls on the LDG list are done with the first chunk
     if (b.n_snarls == 0 || s_count == 0) return cudaSuccess;
@@ -397,12 +472,17 @@ cudaError_t launch_path_and_popc(const MatrixDev& m, const uint8_t* case_mask, u
         p.n_case_hap = n_case_hap;
         p.stage_rows = cfg.stage_rows;
         p.n_stages = cfg.n_stages;
-        cudaError_t e = cudaFuncSetAttribute(path_and_popc_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             int(cfg.smem_bytes));
+        p.chunk_bytes = cfg.chunk_bytes;
+        p.n_chunks = cfg.n_chunks;
+        using K1Kernel = void (*)(const K1Params);
+        const bool multi = cfg.n_chunks > 1;
+        K1Kernel fn = lean_registers ? (multi ? path_and_popc_tma_chunked_lean_kernel : path_and_popc_tma_lean_kernel)
+                                     : (multi ? path_and_popc_tma_chunked_kernel : path_and_popc_tma_kernel);
+        cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cfg.smem_bytes));
         if (e != cudaSuccess) return e;
         uint64_t want = (s_count + cfg.n_warps - 1) / cfg.n_warps;
         const unsigned grid = unsigned(want < uint64_t(num_sms) ? want : uint64_t(num_sms));
-        path_and_popc_tma_kernel<<<grid, cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
+        fn<<<grid, cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;
@@ -538,8 +618,24 @@ __device__ __forceinline__ double fast_rcp(double d) {
     return fma(x, e, x);
 }
 
+// Control flow.  A table passes through three loops (phase 1: towards the centre until the term drops below the bias,
+// 2: the rest of that tail, 3: the near tail from the observed table outwards), ~380 iterations in all at H = 10k, and
+// has exactly two or three "events": the hand-over 2 -> 3, the end, and the rare early exits.  The loop below keeps every
+// lane in ONE branch-free body — the phase only selects which running sum the term goes to, by predication — and leaves
+// it when some lane reports an event; events and refills from the work list are handled in the (divergent) code behind
+// it.  The first version ran each phase's bookkeeping as its own branch and polled the work list in every iteration:
+// 21 of 32 lanes active, more than half of the issued instructions control flow (profiles/r1g_fisher.txt).
+// Positive doubles order like their bit patterns, so the two comparisons of the body are integer compares and stay off
+// the FP64 pipe, which is what bounds this kernel.
+// tables with a count of 2^26 or more: the factor form of device_math.cuh, kept out of line (never taken below 6.7e7 haplotypes)
+__device__ __noinline__ void fisher_big_table(uint4 t, uint32_t snarl, double* p_fisher, uint8_t* fisher_code) {
+    const PVal r = fisher_2x2(t.x, t.y, t.z, t.w);
+    p_fisher[snarl] = r.v;
+    fisher_code[snarl] = r.code;
+}
+
 template <bool kFastRcp>
-__global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restrict__ tab,
+__global__ void __launch_bounds__(128, 8) fisher_exact_kernel(const uint4* __restrict__ tab,
                                                            const uint32_t* __restrict__ idx,
                                                            uint32_t* __restrict__ counters,  // [0] n_work, [1] next
                                                            double* __restrict__ p_fisher,
@@ -547,12 +643,14 @@ __global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restri
     constexpr double kEps2 = 9.094947017729282e-13;
     constexpr double kBias = 1.0339757656912846e-25;
     constexpr double kStart = (1 - kEps2) * kBias;
+    const long long kBiasBits = __double_as_longlong(kBias);
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t n_work = counters[0];
     bool active = false, drained = false;
-    uint32_t snarl = 0, a11 = 0, a12 = 0, a21 = 0, a22 = 0, rem = 0;
-    int phase = 0;
-    double N = 0, sN = 0, D = 0, sD = 0, cur = 0, tprob = 0, cprob = 0;
+    uint32_t snarl = 0, a11 = 0, a12 = 0, a21 = 0, a22 = 0, rem = 1;
+    int phase = 2;
+    // an idle lane runs the body on these values: finite, no event
+    double N = 0, sN = 0, D = 1, sD = 0, cur = 0, tprob = 1, cprob = 0;
     auto finish = [&](double v, uint8_t code) {
         p_fisher[snarl] = v;
         fisher_code[snarl] = code;
@@ -572,6 +670,7 @@ __global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restri
         phase = 3;
     };
     for (;;) {
+        // ---- refill the idle lanes from the work list ----------------------------------------------------------
         const uint32_t need = __ballot_sync(0xffffffffu, !active && !drained);
         if (need) {
             const int leader = __ffs(need) - 1;
@@ -584,9 +683,7 @@ __global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restri
                     const uint4 t = tab[w];
                     snarl = idx[w];
                     if ((t.x | t.y | t.z | t.w) >> 26) {  // products would leave the exact-integer range
-                        const PVal r = fisher_2x2(t.x, t.y, t.z, t.w);
-                        p_fisher[snarl] = r.v;
-                        fisher_code[snarl] = r.code;
+                        fisher_big_table(t, snarl, p_fisher, fisher_code);
                     } else {
                         a11 = t.x; a12 = t.y; a21 = t.z; a22 = t.w;
                         uint32_t u;
@@ -596,53 +693,65 @@ __global__ void __launch_bounds__(128) fisher_exact_kernel(const uint4* __restri
                             u = a11; a11 = a12; a12 = u;
                             u = a21; a21 = a22; a22 = u;
                         }
-                        N = __dmul_rn(double(a12), double(a21));
-                        sN = double(a12) + double(a21) - 1.0;
-                        D = __dmul_rn(double(a11), double(a22));
-                        sD = double(a11) + double(a22) + 1.0;
-                        tprob = kStart; cur = kStart; cprob = 0.0;
-                        rem = a12;
-                        phase = 1;
-                        active = true;
+                        if (a12 == 0) {  // the first loop does not run (:306), cprob == 0 (:322-324)
+                            p_fisher[snarl] = 1.0;
+                            fisher_code[snarl] = kPOne;
+                        } else {
+                            N = __dmul_rn(double(a12), double(a21));
+                            sN = double(a12) + double(a21) - 1.0;
+                            D = __dmul_rn(double(a11), double(a22));
+                            sD = double(a11) + double(a22) + 1.0;
+                            tprob = kStart; cur = kStart; cprob = 0.0;
+                            rem = a12;
+                            phase = 1;
+                            active = true;
+                        }
                     }
                 } else {
                     drained = true;
                 }
             }
+            if (__any_sync(0xffffffffu, !active && !drained)) continue;  // a lane drew a table that was done at once
         }
         if (!__any_sync(0xffffffffu, active)) break;
-        {
-            if (active && rem == 0) {  // the loop of the current phase ran out before a body execution (:306, :326)
-                if (phase == 1 && cprob == 0) finish(1.0, kPOne);  // :322-324
-                else start_near_tail();
-            }
-            if (active) {
-                D = __dadd_rn(D, sD);
-                sD += 2.0;
-                cur = kFastRcp ? __dmul_rn(cur, __dmul_rn(N, fast_rcp(D))) : __dmul_rn(cur, __ddiv_rn(N, D));
-                N = __dsub_rn(N, sN);
-                sN -= 2.0;
-                --rem;
-                if (phase == 1) {
-                    if (cur > DBL_MAX) {  // :312-314
-                        finish(0.0, kPZero);
-                    } else if (cur < kBias) {  // :315-318
-                        tprob = __dadd_rn(tprob, cur);
-                        if (cprob == 0) finish(1.0, kPOne);
-                        else phase = 2;
-                    } else {
-                        cprob = __dadd_rn(cprob, cur);
-                    }
-                } else {
-                    const double preaddp = tprob;
-                    tprob = __dadd_rn(tprob, cur);
-                    if (tprob <= preaddp) {
-                        if (phase == 2) start_near_tail();  // :334-336
-                        else finish(__ddiv_rn(preaddp, __dadd_rn(cprob, preaddp)), kPValue);  // :352-354
-                    } else if (phase == 3 && rem == 0) {
-                        finish(__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue);  // :356, :359
-                    }
-                }
+        if (!active) {  // parked: a lane whose list ran dry iterates on harmless values
+            N = 0; sN = 0; D = 1; sD = 0; cur = 0; tprob = 1; cprob = 0; rem = 0x7FFFFFFFu; phase = 2;
+        }
+        // ---- the recurrence: every lane in the same straight-line body until some lane has an event ---------------
+        bool ev, to_t;
+        double pre;
+        do {
+            D = __dadd_rn(D, sD);
+            sD += 2.0;
+            cur = kFastRcp ? __dmul_rn(cur, __dmul_rn(N, fast_rcp(D))) : __dmul_rn(cur, __ddiv_rn(N, D));
+            N = __dsub_rn(N, sN);
+            sN -= 2.0;
+            --rem;
+            const bool p1 = phase == 1;
+            // cur >= +0: `cur < kBias` (:315) on the bit patterns; +inf and NaN patterns are above kBias's
+            to_t = !p1 || __double_as_longlong(cur) < kBiasBits;
+            pre = tprob;
+            if (to_t) tprob = __dadd_rn(tprob, cur);   // :316 / :331-332 / :349-350
+            else cprob = __dadd_rn(cprob, cur);        // :320
+            // phase 1: overflow (:312), the term fell below the bias (:315), or the loop ran out;
+            // phases 2, 3: the sum stopped growing (:333 / :351: tprob <= preaddp, i.e. == for a term >= 0), or ran out
+            const bool stalled = __double_as_longlong(tprob) == __double_as_longlong(pre);
+            ev = (p1 ? to_t || __double2hiint(cur) >= 0x7FF00000 : stalled) || rem == 0;
+            ev = ev && active;
+        } while (!__any_sync(0xffffffffu, ev));
+        // ---- events --------------------------------------------------------------------------------------------------
+        if (ev) {
+            if (phase == 1) {
+                if (cur > DBL_MAX) finish(0.0, kPZero);            // :312-314
+                else if (cprob == 0) finish(1.0, kPOne);           // :322-324 (only after a break: cprob grows otherwise)
+                else if (to_t && rem != 0) phase = 2;              // :315-318, on to the second loop
+                else start_near_tail();                            // the first loop used up the column: the second is empty
+            } else if (phase == 2) {
+                start_near_tail();                                 // :334-336 or ran out
+            } else if (__double_as_longlong(tprob) == __double_as_longlong(pre)) {
+                finish(__ddiv_rn(pre, __dadd_rn(cprob, pre)), kPValue);    // :352-354
+            } else {
+                finish(__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue);  // :356, :359
             }
         }
     }
@@ -654,7 +763,7 @@ cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const
                                 uint64_t* total_sum, uint8_t* filtered, double* p_chi2, double* p_fisher,
                                 uint8_t* chi2_code, uint8_t* fisher_code, uint4* fisher_tab, uint32_t* fisher_idx,
                                 uint32_t* fisher_counters, int num_sms, cudaStream_t st, uint64_t s_begin,
-                                uint64_t s_count) {
+                                uint64_t s_count, bool beside_count_pass) {
     if (b.n_snarls == 0 || s_count == 0) return cudaSuccess;
     if (s_begin >= b.n_snarls) return cudaSuccess;
     if (s_count > b.n_snarls - s_begin) s_count = b.n_snarls - s_begin;
@@ -666,11 +775,10 @@ cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const
                                                 fisher_idx + s_begin, fisher_counters, s_begin, s_begin + s_count);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     const uint64_t want = (s_count + 127) / 128;
-    static const int per_sm = [] {
-        const char* v = std::getenv("STOAT_GPU_FISHER_BLOCKS");
-        const int n = v ? std::atoi(v) : 0;
-        return n >= 1 ? n : 8;
-    }();
+    // blocks per SM: 8 when the kernel has the SMs to itself; 4 next to the persistent count pass of the following chunk
+    // (416 threads x 64 registers + 4 x 128 x 64 fit one SM's register file; more would wait for the count pass to end)
+    int per_sm = beside_count_pass ? k1_env("STOAT_GPU_FISHER_BLOCKS_BESIDE", 4) : k1_env("STOAT_GPU_FISHER_BLOCKS", 8);
+    if (per_sm < 1) per_sm = beside_count_pass ? 4 : 8;
     const unsigned fblocks = unsigned(want < uint64_t(num_sms) * per_sm ? want : uint64_t(num_sms) * per_sm);
     // STOAT_GPU_FISHER=exact: the quotient by __ddiv_rn, bit-identical to the reference's recurrence (15 % slower)
     const char* fv = std::getenv("STOAT_GPU_FISHER");

@@ -98,30 +98,6 @@ __device__ int lean_finish(const K3Params& p, uint64_t s, uint32_t p0, const Lea
     return 1;
 }
 
-// Stage refill for a slice of the haplotype range: like issue_stage (stage_pipeline.cuh), but every row contributes only
-// the bytes [slice_off, slice_off + slice_bytes) and lands in a slot of slot_bytes.  Whole rows (slice_bytes == pitch):
-// runs of consecutive matrix rows still go out as one bulk copy.
-__device__ __forceinline__ void issue_stage_slice(uint32_t rec_word, uint32_t lane, uint8_t* dst, uint64_t* bar,
-                                                  const uint8_t* rows, const uint8_t* blob, uint32_t pitch,
-                                                  uint32_t slice_off, uint32_t slice_bytes, uint32_t slot_bytes,
-                                                  uint64_t policy) {
-    const uint32_t packed = __shfl_sync(0xffffffffu, rec_word, 7);
-    const uint32_t n_rows = packed & 0xFFu, blob_bytes = ((packed >> 8) & 0xFFu) * 16u;
-    if (lane == 7) mbar_arrive_expect_tx(bar, blob_bytes + n_rows * slice_bytes);
-    __syncwarp();
-    const bool whole = slice_bytes == pitch && slot_bytes == pitch;
-    const uint32_t prev = __shfl_up_sync(0xffffffffu, rec_word, 1);
-    const bool head = lane < n_rows && (!whole || lane == 0 || rec_word != prev + 1u);
-    const uint32_t heads = __ballot_sync(0xffffffffu, head) | (1u << n_rows);
-    if (head) {
-        const uint32_t run = whole ? uint32_t(__ffs(int(heads >> (lane + 1)))) : 1u;
-        tma_bulk_g2s_hint(dst + kStageBlobBytes + lane * slot_bytes, rows + size_t(rec_word) * pitch + slice_off,
-                          run * slice_bytes, bar, policy);
-    } else if (lane == 6) {
-        tma_bulk_g2s(dst, blob + size_t(rec_word) * 16, blob_bytes, bar);
-    }
-}
-
 template <int WPT>
 struct WordVec;
 template <>

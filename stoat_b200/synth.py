@@ -137,21 +137,35 @@ def numpy_dataset(n_snarls: int, n_samples: int, seed: int = 42, frac_missing_ha
 
 
 def torch_dataset(n_snarls: int, n_samples: int, device, seed: int = 42, frac_missing_hap=0.01,
-                  chunk_snarls: int = 16384, **kw):
+                  chunk_snarls: int = 0, cols: tuple | None = None, **kw):
     """Draw the matrix on the GPU (Philox, torch CUDA generator) straight into the reference's byte layout.
 
     -> dict(bits_dev (torch.uint8 [n_rows * n_cols / 8]), n_rows, n_cols, paths, is_case, y, structure)
     Requires n_cols % 8 == 0 (then rows are byte aligned in the reference layout).
+
+    `cols` = (c0, c1): only the haplotype columns [c0, c1) of the cohort — the slice one GPU of a sample-sharded run
+    holds (c0, c1 even).  The snarl structure and the phenotype split stay those of the whole cohort of
+    `n_samples`; the draws of a slice come from their own Philox stream (seed, c0), so the ranks' slices side by side are
+    one valid cohort.  n_cols / is_case / y of the result describe the slice.
     """
     import torch
 
     st = make_structure(n_snarls, seed, **kw)
-    H = 2 * n_samples
-    if H % 8:
-        raise ValueError("torch_dataset needs n_cols % 8 == 0")
     is_case, y = phenotypes(n_samples, seed)
     gen = torch.Generator(device=device)
     gen.manual_seed(seed)
+    if cols is not None:
+        c0, c1 = int(cols[0]), int(cols[1])
+        if c0 % 2 or c1 % 2 or not (0 <= c0 < c1 <= 2 * n_samples):
+            raise ValueError("cols must be an even, non-empty sub-range of the haplotype columns")
+        is_case, y = is_case[c0 // 2:c1 // 2], y[c0 // 2:c1 // 2]
+        n_samples = (c1 - c0) // 2
+        gen.manual_seed(seed * 1_000_003 + c0 + 1)
+    H = 2 * n_samples
+    if H % 8:
+        raise ValueError("torch_dataset needs n_cols % 8 == 0")
+    if chunk_snarls <= 0:  # ~0.16e9 cells per chunk: three float32 draws of that size stay below 2 GB
+        chunk_snarls = max(256, min(16384, (1 << 27) // max(H, 1) // 256 * 256))
     row_bytes = H // 8
     bits = torch.empty(st.n_rows * row_bytes, dtype=torch.uint8, device=device)
     out = bits.view(st.n_rows, row_bytes)

@@ -1,0 +1,172 @@
+"""Parity at the widths and batch sizes config C5 (10M snarls x 50,000 haplotypes) reaches and C3 does not:
+
+  * K1's column-chunked stages (rows wider than 2 KB; forced at small widths with STOAT_GPU_K1_CHUNK), including the
+    hand-over of per-path counts between the chunks of a non-biallelic snarl;
+  * 50,000 haplotypes: Fisher tables of ~850 recurrence steps, K3M's haplotype slices (gridDim.y > 1);
+  * >= 65,536 haplotypes: the reductions that no longer pack two counts into one 32-bit word;
+  * >= 65,536 snarls: the overlapped run (count pass of chunk c + 1 beside the Fisher list of chunk c).
+
+Same bars as everywhere: tables / flags bit-exact, p-values 1e-9 relative (Fisher additionally 1e-12)."""
+import numpy as np
+import pytest
+
+import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+
+def binary_both(ctx, oracle, dense, snarls, is_case, **thr):
+    from stoat_b200 import SnarlPaths
+
+    n_rows, n_cols = dense.shape
+    bits = oracle.pack_matrix(dense)
+    spo, peo, er = H.csr_from_lists(snarls)
+    ctx.set_matrix(bits, n_rows, n_cols)
+    ctx.set_binary_phenotype(is_case)
+    got = ctx.binary_batch(SnarlPaths(spo, peo, er), **thr)
+    ref = oracle.binary_batch(bits, n_cols, is_case, oracle.Paths(spo, peo, er), **thr)
+    return got, ref
+
+
+def quant_both(ctx, oracle, dense, snarls, y, **thr):
+    from stoat_b200 import SnarlPaths
+
+    n_rows, n_cols = dense.shape
+    bits = oracle.pack_matrix(dense)
+    spo, peo, er = H.csr_from_lists(snarls)
+    ctx.set_matrix(bits, n_rows, n_cols)
+    ctx.set_quantitative_phenotype(y)
+    ctx.set_covariates(None)
+    got = ctx.quantitative_batch(SnarlPaths(spo, peo, er), **thr)
+    ref = oracle.quantitative_batch(bits, n_cols, y, oracle.Paths(spo, peo, er), **thr)
+    return got, ref
+
+
+@pytest.mark.parametrize("chunk", [256, 272, 512])
+def test_column_chunks_forced_at_small_width(gpu_ctx, oracle, monkeypatch, chunk):
+    """Every snarl shape through the chunked K1 (2 - 5 chunks per row at these widths): adversarial lists (shared rows,
+    match-all and missing paths, > 4 checked edges) and partitions with up to 6 distinct rows."""
+    monkeypatch.setenv("STOAT_GPU_K1_CHUNK", str(chunk))
+    rng = np.random.default_rng(chunk)
+    for n_samples, n_rows in ((1300, 60), (2500, 90), (4100, 40)):
+        dense, snarls = H.random_snarl_problem(rng, 200, n_samples, n_rows)
+        is_case = (rng.random(n_samples) < 0.45).astype(np.uint8)
+        got, ref = binary_both(gpu_ctx, oracle, dense, snarls, is_case, min_ind=2, min_hap=3, maf=0.01)
+        H.assert_binary_equal(got, ref)
+    dense, snarls = H.partition_problem(rng, 150, 3000, max_paths=3)
+    is_case = (rng.random(3000) < 0.5).astype(np.uint8)
+    got, ref = binary_both(gpu_ctx, oracle, dense, snarls, is_case)
+    H.assert_binary_equal(got, ref)
+    assert (ref["filtered"] == 0).sum() > 10
+
+
+@pytest.mark.parametrize("n_samples", [25000, 33000])
+def test_generator_at_c5_width(gpu_ctx, oracle, n_samples):
+    """The bench generator at 50,000 haplotypes (C5; 6,272-byte rows, four column chunks, packed reductions) and at
+    66,000 (8,256-byte rows, unpacked reductions), binary and quantitative, against the oracle."""
+    from stoat_b200 import synth
+
+    d = synth.numpy_dataset(240, n_samples, seed=9, frac_missing_edge=0.03)
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    gpu_ctx.set_matrix(d["bits"], d["n_rows"], d["n_cols"])
+    gpu_ctx.set_binary_phenotype(d["is_case"])
+    got = gpu_ctx.binary_batch(d["paths"])
+    ref = oracle.binary_batch(d["bits"], d["n_cols"], d["is_case"], P)
+    H.assert_binary_equal(got, ref)
+    m = (ref["filtered"] == 0) & (ref["fisher_code"] == 0)
+    assert m.sum() > 100
+    np.testing.assert_allclose(got["p_fisher"][m], ref["p_fisher"][m], rtol=1e-12, atol=0)
+    gpu_ctx.set_quantitative_phenotype(d["y"])
+    gpu_ctx.set_covariates(None)
+    gq = gpu_ctx.quantitative_batch(d["paths"])
+    rq = oracle.quantitative_batch(d["bits"], d["n_cols"], d["y"], P)
+    H.assert_quant_equal(gq, rq)
+    assert (rq["filtered"] == 0).sum() > 100
+
+
+def test_long_fisher_tables_at_c5_width(gpu_ctx, oracle, monkeypatch):
+    """2x2 tables over 50,000 haplotypes: ~850 steps of the recurrence per table, up to several thousand for the skewed
+    ones.  Default quotient (N * rcp(D)) within 1e-12 of the oracle; STOAT_GPU_FISHER=exact bit-identical."""
+    rng = np.random.default_rng(50)
+    n = 25000
+    tables = []
+    for i in range(60):
+        f = rng.uniform(0.02, 0.98)
+        shift = rng.choice([0.0, 0.0, 0.01, 0.03])
+        a = rng.binomial(n, f)
+        b = rng.binomial(n, min(f + shift, 0.995))
+        tables.append(([n - a, a], [n - b, b]))
+    is_case = np.array([0] * (n // 2) + [1] * (n // 2), np.uint8)
+    dense, snarls = H.matrix_realising_tables(tables, is_case)
+    got, ref = binary_both(gpu_ctx, oracle, dense, snarls, is_case)
+    H.assert_binary_equal(got, ref)
+    m = ref["fisher_code"] == 0
+    assert m.sum() > 30
+    np.testing.assert_allclose(got["p_fisher"][m], ref["p_fisher"][m], rtol=1e-12, atol=0)
+    monkeypatch.setenv("STOAT_GPU_FISHER", "exact")
+    got, ref = binary_both(gpu_ctx, oracle, dense, snarls, is_case)
+    np.testing.assert_array_equal(got["p_fisher"][m], ref["p_fisher"][m])
+
+
+def test_partitions_at_c5_width_quantitative(gpu_ctx, oracle):
+    """Two-, three- and four-path snarls at 50,000 haplotypes: K3M runs in haplotype slices, the other shapes on whatever
+    the width still allows (K3 / the general kernel)."""
+    rng = np.random.default_rng(51)
+    n = 25000
+    dense, snarls = H.partition_problem(rng, 24, n, max_paths=4)
+    y = rng.normal(size=n) * 2 + 5
+    y = y + dense[snarls[0][0][0]].reshape(n, 2).sum(1)
+    got, ref = quant_both(gpu_ctx, oracle, dense, snarls, y)
+    H.assert_quant_equal(got, ref)
+    assert (ref["filtered"] == 0).sum() > 10
+    is_case = (rng.random(n) < 0.5).astype(np.uint8)
+    gb, rb = binary_both(gpu_ctx, oracle, dense, snarls, is_case)
+    H.assert_binary_equal(gb, rb)
+
+
+@pytest.mark.parametrize("overlap", ["1", "4", "8"])
+def test_overlapped_run_many_snarls(gpu_ctx, oracle, monkeypatch, overlap):
+    """>= 65,536 snarls: the run is cut into chunks whose Fisher lists run beside the next chunk's count pass; the result
+    must not depend on the number of chunks."""
+    from stoat_b200 import synth
+
+    monkeypatch.setenv("STOAT_GPU_OVERLAP", overlap)
+    d = synth.numpy_dataset(70000, 48, seed=12, frac_missing_edge=0.02)
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    gpu_ctx.set_matrix(d["bits"], d["n_rows"], d["n_cols"])
+    gpu_ctx.set_binary_phenotype(d["is_case"])
+    got = gpu_ctx.binary_batch(d["paths"])
+    ref = oracle.binary_batch(d["bits"], d["n_cols"], d["is_case"], P)
+    H.assert_binary_equal(got, ref)
+    # resident mode, twice in a row without reading anything back in between (the runs only enqueue)
+    gpu_ctx.stage_paths(d["paths"])
+    gpu_ctx.binary_run_staged()
+    gpu_ctx.binary_run_staged()
+    again = gpu_ctx.binary_fetch()
+    for k in got:
+        np.testing.assert_array_equal(got[k], again[k], err_msg=k)
+    t = gpu_ctx.timing()
+    assert t["n_fisher"] > 0
+    m = gpu_ctx.mean_timing(2)
+    assert m["table_ms"] > 0 and m["stats_ms"] > 0
+
+
+def test_chunked_upload_matches_single_copy(gpu_ctx, oracle, monkeypatch):
+    """set_matrix sends the reference-layout bytes up in chunks of whole rows (copy of chunk k + 1 beside the repack of
+    chunk k); rows must come out the same whatever the chunk size, also when rows are not byte aligned (n_cols % 8 != 0)."""
+    rng = np.random.default_rng(5)
+    for n_cols in (402, 4098):
+        n_rows = 1000
+        dense = rng.random((n_rows, n_cols)) < 0.5
+        bits = oracle.pack_matrix(dense)
+        monkeypatch.delenv("STOAT_GPU_UPLOAD_CHUNK_ROWS", raising=False)
+        gpu_ctx.set_matrix(bits, n_rows, n_cols)
+        want = [gpu_ctx.read_row(r).copy() for r in range(0, n_rows, 37)] + [gpu_ctx.read_row(n_rows - 1).copy()]
+        monkeypatch.setenv("STOAT_GPU_UPLOAD_CHUNK_ROWS", "128")  # 8 chunks, the last one short
+        gpu_ctx.set_matrix(bits, n_rows, n_cols)
+        got = [gpu_ctx.read_row(r).copy() for r in range(0, n_rows, 37)] + [gpu_ctx.read_row(n_rows - 1).copy()]
+        for a, b in zip(got, want):
+            np.testing.assert_array_equal(a, b)
+        for r in (0, 127, 128, 129, 511, 512, 999):
+            row = np.unpackbits(gpu_ctx.read_row(r), bitorder="little")
+            np.testing.assert_array_equal(row[:n_cols].astype(bool), dense[r])
