@@ -826,7 +826,7 @@ static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int ph
     else
         CK(cudaMemcpyAsync(ctx->d_counters.p, x->counters_host, 4, cudaMemcpyHostToDevice, ctx->stream));
     // filtered snarls keep NaN / NA outputs (the moments path writes them in K4, which visits every snarl)
-    if (S && phase != 1 && !quant_fast_path(ctx->pitch, x->max_stage_rows, ctx->k1_variant, uint32_t(ctx->n_covar))) {
+    if (S && phase != 1 && !quant_fast_path(ctx->pitch, ctx->n_cols, x->max_stage_rows, ctx->k1_variant, uint32_t(ctx->n_covar))) {
         CK(cudaMemsetAsync(ctx->q_p.p, 0xFF, S * 8, ctx->stream));
         CK(cudaMemsetAsync(ctx->q_r2.p, 0xFF, S * 8, ctx->stream));
         CK(cudaMemsetAsync(ctx->q_beta.p, 0xFF, S * 8, ctx->stream));

@@ -126,7 +126,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                                      double* tail_t, double* tail_x, uint32_t* tail_df,  // [n_snarls] K4 -> K4b hand-over
                                      uint64_t stage_gen = 0,         // identifies the staged paths (rec / blob)
                                      uint64_t* lean_key = nullptr);  // in/out: what lean_rec holds (nullptr: rebuild every step)
-bool quant_fast_path(uint64_t pitch, uint32_t max_stage_rows, int variant, uint32_t n_covar);  // K4 initialises the outputs
+bool quant_fast_path(uint64_t pitch, uint64_t n_hap, uint32_t max_stage_rows, int variant, uint32_t n_covar);  // K4 initialises the outputs
 size_t quant_yslices_bytes(uint64_t pitch);  // K3M's phenotype slice table
 // slices of the haplotype range the two-path kernels (K3M / K3R) use: sizes the partial-sum buffers (0: neither runs)
 uint32_t quant_lean_slices(uint64_t pitch, uint64_t n_hap, uint32_t stage_rows);

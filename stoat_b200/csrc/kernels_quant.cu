@@ -754,6 +754,19 @@ __global__ void __launch_bounds__(kTailWarps * 32) student_tail_kernel(const dou
 
 #include "quant_general.cuh"
 
+// Rows too wide for K3's shared-memory phenotype table (16 x pitch / 4 doubles: 200 KB at 50,000 haplotypes): what K3M
+// and its siblings left on the slow list goes to the general kernel instead of K3.
+__global__ void slow_list_to_general_kernel(const uint32_t* __restrict__ slow_list, const uint32_t* __restrict__ slow_count,
+                                            QuantMoments* __restrict__ mom, uint32_t* __restrict__ g_list,
+                                            uint32_t* __restrict__ g_count) {
+    const uint32_t n = *slow_count;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t s = slow_list[i];
+        mom[s].state = 0;
+        g_list[atomicAdd(g_count, 1u)] = s;
+    }
+}
+
 
 // =================================================================================================
 // host side
@@ -854,9 +867,11 @@ static bool k3m_plan(uint32_t pitch, uint64_t n_hap, K3MPlan& pl) {
     return true;
 }
 // true: launch_quantitative_impl takes the moments path, whose K4 initialises the outputs itself
-bool quant_fast_path(uint64_t pitch, uint32_t max_stage_rows, int variant, uint32_t n_covar) {
+bool quant_fast_path(uint64_t pitch, uint64_t n_hap, uint32_t max_stage_rows, int variant, uint32_t n_covar) {
     K3Config cfg{};
-    return variant == 0 && n_covar == 0 && choose_k3_config(uint32_t(pitch), max_stage_rows, cfg);
+    K3MPlan pm;
+    return variant == 0 && n_covar == 0 &&
+           (choose_k3_config(uint32_t(pitch), max_stage_rows, cfg) || k3m_plan(uint32_t(pitch), n_hap, pm));
 }
 size_t quant_yslices_bytes(uint64_t pitch) { return size_t((pitch / 16 + 3) / 4) * 2048; }
 // slices of the haplotype range the two-path kernel uses (sizes the partial-sum buffers); 0: neither K3M nor K3R
@@ -898,8 +913,13 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
     const uint32_t pitch = uint32_t(m.pitch);
     const uint32_t n_samples = uint32_t(m.n_cols / 2);
     K3Config cfg{};
-    // counters[0] already holds the number of snarls prep sent to the general list
-    const bool fast = (variant == 0) && (n_covar == 0) && choose_k3_config(pitch, max_stage_rows, cfg);
+    // counters[0] already holds the number of snarls prep sent to the general list.  K3 needs the permuted phenotype in
+    // shared memory (32 x pitch bytes); where that does not fit (> ~37,000 haplotypes) the moments path still runs on
+    // K3M, whose slices bound its shared memory, and the snarls K3M leaves over take the general kernel.
+    const bool k3_ok = choose_k3_config(pitch, max_stage_rows, cfg);
+    K3MPlan pm_probe;
+    const bool k3m_ok = part_i && part_d && slow_list && lean_rec && yslices && yc && k3m_plan(pitch, m.n_cols, pm_probe);
+    const bool fast = (variant == 0) && (n_covar == 0) && (k3_ok || k3m_ok);
     cudaError_t e;
     GParams g{};
     g.rows = m.rows;
@@ -931,7 +951,7 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         p.mom = mom;
         p.g_list = b.big_list;
         p.g_count = b.counters;
-        {
+        if (k3_ok) {
             static thread_local int k3_dev = -1;
             static thread_local uint32_t k3_smem = 0;
             int dev_now = 0;
@@ -1072,10 +1092,14 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             }
             p.list = slow_list;
             p.list_count = b.counters + 3;
-            dosage_moments_tma_kernel<<<unsigned(num_sms), cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
+            if (k3_ok)
+                dosage_moments_tma_kernel<<<unsigned(num_sms), cfg.n_warps * 32, cfg.smem_bytes, st>>>(p);
+            else
+                slow_list_to_general_kernel<<<unsigned(num_sms), 256, 0, st>>>(slow_list, b.counters + 3, mom, b.big_list,
+                                                                              b.counters);
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             if (launches) *launches += 1;
-        } else if (part_i && part_d && slow_list && k3r_plan(pitch, cfg.stage_rows, pl)) {
+        } else if (k3_ok && part_i && part_d && slow_list && k3r_plan(pitch, cfg.stage_rows, pl)) {
             // K3R over every snarl (two-path snarls -> partial sums), then K3 over what it left on the slow list
             K3RParams q{};
             q.k = p;
