@@ -60,7 +60,11 @@ struct QuantState {
 }  // namespace
 
 constexpr int kMaxRunChunks = 8;  // chunks of an overlapped binary run (stoat_gpu_binary_run_staged)
-constexpr int kDefaultRunChunks = 4;  // chunks of the overlapped binary run (measured: profiles/r2_*)
+// Chunks of the binary run by default.  Measured on B200 at C3 with the 64-register count pass and the branch-free Fisher loop
+// (profiles/r2a_sweep_c3.json): 1 chunk 1.57 ms, 2 / 4 / 8 chunks 1.80 / 1.90 / 2.10 ms (4 chunks with 8 Fisher blocks per
+// SM: 1.64 ms).  Both kernels fit one SM now, but both are bound by the SM's issue slots (K1 by its shared-memory loads and
+// popcounts, the Fisher list by the FP64 pipe), so running them side by side only stretches both: back to back stays.
+constexpr int kDefaultRunChunks = 1;
 constexpr int kRunRing = 64;      // staged runs whose events are kept for stoat_gpu_mean_timing
 
 // extra per-context state that does not need to be visible to the kernel translation units
@@ -687,10 +691,10 @@ int stoat_gpu_binary_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* 
     CtxExtra* x = extra_of(ctx);
     const uint64_t S = ctx->batch.n_snarls;
     // The count pass (K1) is HBM bound and leaves the FP64 pipe idle, the Fisher work list (K2b) is the opposite, so the
-    // run is cut into chunks of snarls with K1 of chunk c + 1 (main stream) overlapping K2a / K2b of chunk c (second
-    // stream).  For the two to share an SM the count pass runs in its 64-register build (416 threads x 64 registers +
-    // four 128-thread Fisher blocks fit the register file; the 105-register build and eight Fisher blocks did not, which
-    // is why this lost to the back-to-back order in round 1).  STOAT_GPU_OVERLAP=<chunks>, 1 = back to back.
+    // run CAN be cut into chunks of snarls with K1 of chunk c + 1 (main stream) overlapping K2a / K2b of chunk c (second
+    // stream): STOAT_GPU_OVERLAP=<chunks>.  For the two to share an SM the count pass then runs in its 64-register build
+    // (416 threads x 64 registers + four 128-thread Fisher blocks fit the register file).  See kDefaultRunChunks for
+    // what that measures.
     int n_chunks = 1;
     if (S >= 65536) {
         n_chunks = kDefaultRunChunks;
