@@ -716,7 +716,8 @@ def main():
     stream = torch.cuda.ExternalStream(ctx.stream, device=env.dev)
     host_cache = {}
     line = trait_record(env, args, ctx, d, args.trait, stream, host_cache)
-    nested = args.traits == "all" and args.trait == "binary" and args.config == "c3" and not args.custom and not sample_sharded
+    nested = args.traits == "all" and args.trait == "binary" and not args.custom and not sample_sharded
+    nested_eqtl = nested and args.config == "c3"
     traits = {}
     if nested:
         q = trait_record(env, args, ctx, d, "quantitative", stream, host_cache, with_clocks=False)
@@ -726,7 +727,7 @@ def main():
     ctx.close()
     del d
     torch.cuda.empty_cache()
-    if nested:
+    if nested_eqtl:
         import bench_eqtl
 
         eargs = parse_args(["--trait", "eqtl", "--gpus", str(args.gpus), "--steps", str(min(args.steps, 3)), "--warmup", "3",

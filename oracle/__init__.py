@@ -95,6 +95,13 @@ def _declare(L):
     L.orc_quantitative_batch.argtypes = [u8p, C.c_uint64, f64p, f64p, C.c_uint64, C.c_uint64, u64p, u64p, u32p,
                                          C.c_uint64, C.c_uint64, C.c_double,
                                          u32p, u8p, u32p, f64p, f64p, f64p, f64p, u8p, C.c_int]
+    L.orc_binary_covar_batch.restype = C.c_double
+    L.orc_binary_covar_batch.argtypes = [u8p, C.c_uint64, u8p, f64p, C.c_uint64, C.c_int, C.c_uint64, u64p, u64p, u32p,
+                                         C.c_uint64, C.c_uint64, C.c_double,
+                                         u32p, u8p, u32p, f64p, f64p, f64p, u8p, C.c_int]
+    L.orc_logistic_regression.restype = None
+    L.orc_logistic_regression.argtypes = [f64p, C.c_uint64, C.c_uint64, u8p, f64p, C.c_uint64, C.c_int,
+                                          f64p, f64p, f64p, u8p]
     L.orc_eqtl_batch.restype = C.c_double
     L.orc_eqtl_batch.argtypes = [u8p, C.c_uint64, f64p, C.c_uint64, u64p, u32p, f64p, C.c_uint64,
                                  C.c_uint64, u64p, u64p, u32p, C.c_uint64, C.c_uint64, C.c_double,
@@ -271,6 +278,24 @@ def linear_regression(df, y, covar=None):
     return dict(p=p.value, beta=b.value, se=se.value, r2=r2.value, code=code.value)
 
 
+def logistic_regression(df, y, covar=None, use_covariates=False):
+    """-> dict(p, beta, se, code), LogisticRegression::logistic_regression (src/stats_test.cpp:49-176).
+    use_covariates=False is the reference as written (its covariate block shadows its own variables, :59-62)."""
+    df = np.ascontiguousarray(df, dtype=np.float64)
+    y = np.ascontiguousarray(y, dtype=np.uint8)
+    n, nv = df.shape
+    if covar is None or np.size(covar) == 0:
+        cov_p, ncov = C.POINTER(C.c_double)(), 0
+    else:
+        covar = np.ascontiguousarray(covar, dtype=np.float64)
+        cov_p, ncov = _p(covar, C.c_double), covar.shape[1]
+    p, b, se = (np.zeros(1) for _ in range(3))
+    code = np.zeros(1, np.uint8)
+    lib().orc_logistic_regression(_p(df, C.c_double), n, nv, _p(y, C.c_uint8), cov_p, ncov, int(bool(use_covariates)),
+                                  _p(p, C.c_double), _p(b, C.c_double), _p(se, C.c_double), _p(code, C.c_uint8))
+    return dict(p=float(p[0]), beta=float(b[0]), se=float(se[0]), code=int(code[0]))
+
+
 def xtx_inverse(xtx):
     a = np.asfortranarray(xtx, dtype=np.float64)
     out = np.zeros_like(a, order="F")
@@ -324,6 +349,30 @@ def quantitative_batch(bits, n_cols, y, paths: Paths, covar=None, min_ind=3, min
         _p(out["allele_paths"], C.c_uint32), _p(out["filtered"], C.c_uint8), _p(out["n_used"], C.c_uint32),
         _p(out["p_value"], C.c_double), _p(out["r2"], C.c_double), _p(out["beta"], C.c_double),
         _p(out["se"], C.c_double), _p(out["code"], C.c_uint8), n_threads)
+    out["seconds"] = secs
+    return out
+
+
+def binary_covar_batch(bits, n_cols, is_case, paths: Paths, covar=None, use_covariates=False, min_ind=3, min_hap=5,
+                       maf=0.05, n_threads=0):
+    """BinaryCovarSnarlAnalyzer (src/snarl_analyzer.cpp:392-428): quantitative table + logistic regression per snarl."""
+    S, P = paths.n_snarls, paths.n_paths
+    bits = np.ascontiguousarray(bits, dtype=np.uint8)
+    is_case = np.ascontiguousarray(is_case, dtype=np.uint8)
+    if covar is None or np.size(covar) == 0:
+        cov_p, ncov = C.POINTER(C.c_double)(), 0
+    else:
+        covar = np.ascontiguousarray(covar, dtype=np.float64)
+        cov_p, ncov = _p(covar, C.c_double), covar.shape[1]
+    out = dict(allele_paths=np.zeros(P, np.uint32), filtered=np.zeros(S, np.uint8), n_used=np.zeros(S, np.uint32),
+               p_value=np.zeros(S), beta=np.zeros(S), se=np.zeros(S), code=np.zeros(S, np.uint8))
+    secs = lib().orc_binary_covar_batch(
+        _p(bits, C.c_uint8), n_cols, _p(is_case, C.c_uint8), cov_p, ncov, int(bool(use_covariates)), S,
+        _p(paths.snarl_path_off, C.c_uint64), _p(paths.path_edge_off, C.c_uint64), _p(paths.edge_row, C.c_uint32),
+        min_ind, min_hap, maf,
+        _p(out["allele_paths"], C.c_uint32), _p(out["filtered"], C.c_uint8), _p(out["n_used"], C.c_uint32),
+        _p(out["p_value"], C.c_double), _p(out["beta"], C.c_double), _p(out["se"], C.c_double),
+        _p(out["code"], C.c_uint8), n_threads)
     out["seconds"] = secs
     return out
 

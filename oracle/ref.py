@@ -39,6 +39,7 @@ def lib() -> C.CDLL:
                               f64p, C.c_uint64, f64p, C.c_uint64, u64p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_double,
                               C.c_int, C.c_char_p, u64p]
         L.ref_linear_regression.argtypes = [f64p, C.c_uint64, C.c_uint64, f64p, f64p, C.c_uint64, C.c_char_p, C.c_uint64]
+        L.ref_logistic_regression.argtypes = [f64p, C.c_uint64, C.c_uint64, u8p, f64p, C.c_uint64, C.c_char_p, C.c_uint64]
         L.ref_fisher_khi2.argtypes = [u64p, u64p, C.c_uint64, C.c_char_p, C.c_uint64]
         L.ref_chi2_2x2.argtypes = [C.c_uint64] * 4 + [C.c_char_p, C.c_uint64]
         L.ref_fisher_2x2.argtypes = [C.c_uint64] * 4 + [C.c_char_p, C.c_uint64]
@@ -86,6 +87,16 @@ def linear_regression(df, y, covar=None):
     y = np.ascontiguousarray(y, np.float64)
     cv = None if covar is None else np.ascontiguousarray(covar, np.float64)
     s = _str(lib().ref_linear_regression, _p(df, C.c_double), df.shape[0], df.shape[1], _p(y, C.c_double),
+             _p(cv, C.c_double), 0 if cv is None else cv.shape[1])
+    return tuple(s.split("\t"))
+
+
+def logistic_regression(df, y, covar=None):
+    """-> (p, beta, se) strings: LogisticRegression::logistic_regression (src/stats_test.cpp:49-176)."""
+    df = np.ascontiguousarray(df, np.float64)
+    y = np.ascontiguousarray(y, np.uint8)
+    cv = None if covar is None else np.ascontiguousarray(covar, np.float64)
+    s = _str(lib().ref_logistic_regression, _p(df, C.c_double), df.shape[0], df.shape[1], _p(y, C.c_uint8),
              _p(cv, C.c_double), 0 if cv is None else cv.shape[1])
     return tuple(s.split("\t"))
 
@@ -156,7 +167,7 @@ def run(trait: str, bits, n_rows, n_cols, snarl_path_off, nodes: dict, *, is_cas
         gene_pos=None, snarl_pos=None, window=0, min_ind=3, min_hap=5, maf=0.05, n_threads=0, tsv_path=None, parse=True):
     """Run the reference's own analyzer loop.  -> dict(seconds, n_filtered, rows: {snarl index: [row dicts]})."""
     L = lib()
-    t = {"binary": 0, "quantitative": 1, "eqtl": 2}[trait]
+    t = {"binary": 0, "quantitative": 1, "eqtl": 2, "binary_covar": 3}[trait]
     bits = np.ascontiguousarray(bits, np.uint8)
     need = (int(n_rows) * int(n_cols) + 7) // 8
     assert bits.size >= need

@@ -120,7 +120,8 @@ int put(const std::string& s, char* buf, uint64_t len) {
 
 extern "C" {
 
-// trait: 0 binary (chi2 + Fisher), 1 quantitative (OLS), 2 eQTL (OLS per gene of the window)
+// trait: 0 binary (chi2 + Fisher), 1 quantitative (OLS), 2 eQTL (OLS per gene of the window), 3 binary with covariates
+// (logistic regression)
 // edge_desc [n_rows][4] = {id1, rev1, id2, rev2}; snarl_pos [n_snarls][2] or NULL; thr = {min_individuals, min_haplotypes}
 double ref_run(int trait, const uint8_t* bits, uint64_t n_rows, uint64_t n_cols, const uint64_t* edge_desc, uint64_t n_snarls,
                const uint64_t* snarl_path_off, const uint64_t* path_node_off, const uint64_t* node_id, const uint8_t* node_rev,
@@ -149,6 +150,13 @@ double ref_run(int trait, const uint8_t* bits, uint64_t n_rows, uint64_t n_cols,
                                                 regression_dir);
         return run_loop(an, snarls, n_threads, tsv_path, n_filtered);
     }
+    if (trait == 3) {  // BinaryCovarSnarlAnalyzer (src/snarl_analyzer.cpp:392-428): logistic regression
+        std::vector<bool> pheno(n_samples);
+        for (uint64_t i = 0; i < n_samples; ++i) pheno[i] = is_case[i] != 0;
+        stoat_vcf::BinaryCovarSnarlAnalyzer an(c.chr_to_snarls, m, c.samples, cov, maf, table_threshold, pheno, min_ind, min_hap,
+                                               regression_dir);
+        return run_loop(an, snarls, n_threads, tsv_path, n_filtered);
+    }
     if (trait == 2) {
         std::unordered_map<std::string, std::vector<stoat_vcf::Qtl_data>> eqtl;
         auto& genes = eqtl[kChr];
@@ -174,6 +182,18 @@ int ref_linear_regression(const double* df_rowmajor, uint64_t n, uint64_t nv, co
     stoat::LinearRegression lr;
     const auto [p, beta, se, r2] = lr.linear_regression(df, yy, covar_rows(covar, n, nc));
     return put(p + "\t" + beta + "\t" + se + "\t" + r2, buf, len);
+}
+
+// LogisticRegression::logistic_regression (src/stats_test.cpp:49-176) -> "p\tbeta\tse"
+int ref_logistic_regression(const double* df_rowmajor, uint64_t n, uint64_t nv, const uint8_t* y, const double* covar, uint64_t nc,
+                            char* buf, uint64_t len) {
+    std::vector<std::vector<double>> df(n);
+    for (uint64_t i = 0; i < n; ++i) df[i].assign(df_rowmajor + i * nv, df_rowmajor + (i + 1) * nv);
+    std::vector<bool> yy(n);
+    for (uint64_t i = 0; i < n; ++i) yy[i] = y[i] != 0;
+    stoat::LogisticRegression lr;
+    const auto [p, beta, se] = lr.logistic_regression(df, yy, covar_rows(covar, n, nc));
+    return put(p + "\t" + beta + "\t" + se, buf, len);
 }
 
 // FisherKhi2::fisher_khi2 (src/stats_test.cpp:362-380) -> "chi2\tfisher"

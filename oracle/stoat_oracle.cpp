@@ -611,6 +611,160 @@ OlsResult linear_regression(const Table& df, const std::vector<double>& y_in, co
     return {pval, beta[1], se1, r2, P_VALUE};  // :487-489: FIRST dosage column only
 }
 
+// ----------------------------------------------------------------------------------------------
+// Logistic regression — LogisticRegression::logistic_regression, src/stats_test.cpp:49-176
+// (constants src/stats_test.hpp:109-112: 100 iterations, tolerance 1e-6, L2 1e-4, epsilon 1e-8)
+// ----------------------------------------------------------------------------------------------
+struct LogitResult {
+    double p, beta, se;
+    uint8_t code;  // P_VALUE, P_NA (LDLT failure or no convergence: "NA" triple, :107,120), P_UNDEF (no dosage column)
+};
+
+// Eigen MatrixXd::inverse() of a dynamic-size matrix = PartialPivLU::inverse() (deps/eigen/Eigen/src/LU/InverseImpl.h,
+// compute_inverse<..., Dynamic>): row-pivoted LU, then the solve of the identity.
+Mat lu_inverse(const Mat& A) {
+    const int n = A.n;
+    Mat lu(A), inv(n);
+    std::vector<int> perm(n);
+    for (int i = 0; i < n; ++i) perm[i] = i;
+    for (int k = 0; k < n; ++k) {
+        int piv = k;
+        double best = std::fabs(lu(k, k));
+        for (int i = k + 1; i < n; ++i)
+            if (std::fabs(lu(i, k)) > best) {
+                best = std::fabs(lu(i, k));
+                piv = i;
+            }
+        if (piv != k) {
+            for (int j = 0; j < n; ++j) std::swap(lu(k, j), lu(piv, j));
+            std::swap(perm[k], perm[piv]);
+        }
+        if (lu(k, k) != 0.0)
+            for (int i = k + 1; i < n; ++i) lu(i, k) /= lu(k, k);
+        for (int j = k + 1; j < n; ++j)
+            for (int i = k + 1; i < n; ++i) lu(i, j) -= lu(i, k) * lu(k, j);
+    }
+    std::vector<double> b(n);
+    for (int c = 0; c < n; ++c) {
+        for (int i = 0; i < n; ++i) b[i] = (perm[i] == c) ? 1.0 : 0.0;
+        for (int i = 0; i < n; ++i)
+            for (int j = 0; j < i; ++j) b[i] -= lu(i, j) * b[j];
+        for (int i = n - 1; i >= 0; --i) {
+            for (int j = i + 1; j < n; ++j) b[i] -= lu(i, j) * b[j];
+            b[i] /= lu(i, i);
+        }
+        for (int i = 0; i < n; ++i) inv(i, c) = b[i];
+    }
+    return inv;
+}
+
+// adjusted_holm — src/utils.cpp:61-87
+std::vector<double> adjusted_holm(const std::vector<double>& p_values) {
+    const int m = int(p_values.size());
+    std::vector<std::pair<double, int>> indexed;
+    for (int i = 0; i < m; ++i) indexed.emplace_back(p_values[i], i);
+    std::sort(indexed.begin(), indexed.end());
+    std::vector<double> adjusted(m), reordered(m);
+    double prev = 0.0;
+    for (int i = 0; i < m; ++i) {
+        double raw = (m - i) * indexed[i].first;
+        raw = std::min(raw, 1.0);
+        adjusted[i] = std::max(prev, raw);
+        prev = adjusted[i];
+    }
+    for (int i = 0; i < m; ++i) reordered[indexed[i].second] = adjusted[i];
+    return reordered;
+}
+
+// `use_covariates` = false is the reference as written: the block at :59-62 declares NEW locals that shadow
+// num_covariates / num_features, so the design is [1, dosage columns] whatever covariates are passed.  true is what the
+// code evidently meant (covariate columns appended, taken by filtered row position like the linear model, and left out
+// of the Wald tests, :148-153).
+LogitResult logistic_regression(const Table& df, const std::vector<uint8_t>& y_in, const double* covar, uint64_t n_covar,
+                                bool use_covariates) {
+    const double nan = std::numeric_limits<double>::quiet_NaN();
+    const size_t n = df.size();
+    const size_t nv = df[0].size();
+    if (nv == 0) return {nan, nan, nan, P_UNDEF};  // the reference reads p_values[0] of an empty vector (:165)
+    const size_t nc = (use_covariates && covar) ? size_t(n_covar) : 0;
+    const int p = int(nv + nc + 1);
+    const int max_iterations = 100;
+    const double tolerance = 1e-6, l2_penalty = 1e-4, epsilon = 1e-8;
+    std::vector<double> X(n * size_t(p)), y(n);
+    for (size_t i = 0; i < n; ++i) {  // :68-83
+        X[i * p] = 1.0;
+        size_t col = 1;
+        for (size_t j = 0; j < nv; ++j) X[i * p + col++] = df[i][j];
+        for (size_t j = 0; j < nc; ++j) X[i * p + col++] = covar[i * n_covar + j];
+        y[i] = y_in[i] ? 1.0 : 0.0;
+    }
+    auto sigmoid = [](double x) { return 1.0 / (1.0 + std::exp(-x)); };
+    auto clampd = [](double x, double lo, double hi) { return std::max(lo, std::min(hi, x)); };
+    std::vector<double> beta(p, 0.0), beta_old(p, 0.0), prob(n), w(n);
+    auto weights_and_hessian = [&](Mat& H) {  // :91-103 and :124-137
+        for (size_t i = 0; i < n; ++i) {
+            double z = 0.0;
+            for (int a = 0; a < p; ++a) z += X[i * p + a] * beta[a];
+            prob[i] = sigmoid(z);
+            w[i] = clampd(prob[i] * (1.0 - prob[i]), epsilon, 1.0);
+        }
+        for (size_t i = 0; i < n; ++i) {
+            const double sw = std::sqrt(w[i]);  // X_weighted.row(i) *= sqrt(w)
+            for (int a = 0; a < p; ++a) {
+                const double xa = X[i * p + a] * sw;
+                for (int b = 0; b <= a; ++b) H(a, b) += xa * (X[i * p + b] * sw);
+            }
+        }
+        for (int a = 0; a < p; ++a) {
+            for (int b = a + 1; b < p; ++b) H(a, b) = H(b, a);
+            H(a, a) += l2_penalty;
+        }
+    };
+    bool converged = false;
+    for (int iter = 0; iter < max_iterations; ++iter) {
+        Mat H(p);
+        weights_and_hessian(H);
+        std::vector<double> g(p, 0.0);
+        for (size_t i = 0; i < n; ++i)
+            for (int a = 0; a < p; ++a) g[a] += X[i * p + a] * (y[i] - prob[i]);
+        for (int a = 0; a < p; ++a) g[a] -= l2_penalty * beta[a];  // :105
+        Ldlt f(H);                                                // :107
+        for (double d : f.D)
+            if (std::isnan(d)) return {nan, nan, nan, P_NA};  // NumericalIssue: only reachable through NaNs here
+        f.solve(g);
+        double nrm = 0.0;
+        for (int a = 0; a < p; ++a) {
+            beta[a] += g[a];
+            const double d = beta[a] - beta_old[a];
+            nrm += d * d;
+        }
+        if (std::sqrt(nrm) < tolerance) {  // :113
+            converged = true;
+            break;
+        }
+        beta_old = beta;
+    }
+    if (!converged) return {nan, nan, nan, P_NA};  // :120
+    Mat H(p);
+    weights_and_hessian(H);
+    const Mat cov = lu_inverse(H);  // :138
+    std::vector<double> se(p), pv;
+    for (int a = 0; a < p; ++a) se[a] = std::sqrt(cov(a, a));
+    for (size_t i = 1; i < size_t(p) - nc; ++i) {  // :148-151
+        const double z = beta[i] / se[i];
+        pv.push_back(2.0 * (1.0 - normal_cdf(std::fabs(z))));
+    }
+    double p_adj = pv[0], b_adj = beta[1], se_adj = se[1];
+    if (pv.size() > 1) {  // :169-175
+        const std::vector<double> adj = adjusted_holm(pv);
+        const size_t k = size_t(std::min_element(adj.begin(), adj.end()) - adj.begin());
+        p_adj = adj[k];
+        b_adj = beta[k + 1];
+        se_adj = se[k + 1];
+    }
+    return {p_adj, b_adj, se_adj, P_VALUE};
+}
+
 struct QuantSnarl {
     bool filtered;
     uint32_t n_used;
@@ -868,6 +1022,54 @@ double orc_quantitative_batch(const uint8_t* bits, uint64_t n_cols, const double
     }
     const auto t1 = std::chrono::high_resolution_clock::now();
     return std::chrono::duration<double>(t1 - t0).count();
+}
+
+// BinaryCovarSnarlAnalyzer::analyze_and_write_snarl — src/snarl_analyzer.cpp:392-428: the quantitative table built
+// against the binary phenotype, the same column surgery, then the logistic regression.
+double orc_binary_covar_batch(const uint8_t* bits, uint64_t n_cols, const uint8_t* is_case, const double* covar,
+                              uint64_t n_covar, int use_covariates, uint64_t n_snarls, const uint64_t* snarl_path_off,
+                              const uint64_t* path_edge_off, const uint32_t* edge_row, uint64_t min_ind,
+                              uint64_t min_hap, double maf, uint32_t* allele_paths, uint8_t* filtered_out,
+                              uint32_t* n_used_out, double* p_out, double* beta_out, double* se_out, uint8_t* code_out,
+                              int n_threads) {
+    const uint64_t n_samples = n_cols / 2;
+#ifdef _OPENMP
+    if (n_threads > 0) omp_set_num_threads(n_threads);
+#endif
+    const auto t0 = std::chrono::high_resolution_clock::now();
+#pragma omp parallel for schedule(static)
+    for (int64_t s = 0; s < int64_t(n_snarls); ++s) {
+        PathsView pv{path_edge_off, edge_row, snarl_path_off[s], snarl_path_off[s + 1] - snarl_path_off[s]};
+        Table df;
+        std::vector<uint64_t> used;
+        bool filtered = true;
+        quantitative_table_for_snarl(bits, n_samples, pv, allele_paths + pv.first_path, min_ind, min_hap, maf, df, used,
+                                     filtered);
+        filtered_out[s] = filtered ? 1 : 0;
+        n_used_out[s] = uint32_t(used.size());
+        const double nan = std::numeric_limits<double>::quiet_NaN();
+        p_out[s] = beta_out[s] = se_out[s] = nan;
+        code_out[s] = P_NA;
+        if (!filtered) {
+            std::vector<uint8_t> yf;
+            yf.reserve(used.size());
+            for (uint64_t i : used) yf.push_back(is_case[i]);
+            const LogitResult o = logistic_regression(df, yf, covar, n_covar, use_covariates != 0);
+            p_out[s] = o.p; beta_out[s] = o.beta; se_out[s] = o.se; code_out[s] = o.code;
+        }
+    }
+    const auto t1 = std::chrono::high_resolution_clock::now();
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+// logistic_regression on an explicit table (row-major n x nv), y[n] 0/1, covar row-major [>= n][n_covar]
+void orc_logistic_regression(const double* df_rowmajor, uint64_t n, uint64_t nv, const uint8_t* y, const double* covar,
+                             uint64_t n_covar, int use_covariates, double* p, double* beta, double* se, uint8_t* code) {
+    Table df(n, std::vector<double>(nv));
+    for (uint64_t r = 0; r < n; ++r)
+        for (uint64_t c = 0; c < nv; ++c) df[r][c] = df_rowmajor[r * nv + c];
+    const LogitResult o = logistic_regression(df, std::vector<uint8_t>(y, y + n), covar, n_covar, use_covariates != 0);
+    *p = o.p; *beta = o.beta; *se = o.se; *code = o.code;
 }
 
 // eQTL — EQTLSnarlAnalyzer::analyze_and_write_snarl, src/snarl_analyzer.cpp:493-539.

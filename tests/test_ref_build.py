@@ -208,3 +208,82 @@ def test_reference_eqtl_analyzer_vs_oracle(oracle):
                     assert _close(row[col], oracle.set_precision(res[key][k])), (s, k, col, row, res[key][k])
                 n_rows_checked += 1
         assert n_rows_checked > 100
+
+
+# ---------------------------------------------------------------------------------------------------
+# logistic regression with covariates: LogisticRegression + BinaryCovarSnarlAnalyzer
+# ---------------------------------------------------------------------------------------------------
+def _logit_strings(oracle, got):
+    if got["code"] == 1:
+        return ["NA", "NA", "NA"]
+    return [oracle.set_precision(got[q]) for q in ("p", "beta", "se")]
+
+
+def test_oracle_logistic_regression_matches_reference_eigen(oracle):
+    """LogisticRegression::logistic_regression (src/stats_test.cpp:49-176: IRLS, L2 1e-4, Wald z, Holm over the dosage
+    columns) vs the oracle's restatement; covariates are passed and — as in the reference — have no effect."""
+    rng = np.random.default_rng(11)
+    n_checked = n_multi = n_na = 0
+    for trial in range(160):
+        n = int(rng.integers(12, 200))
+        k = int(rng.integers(1, 4))
+        df = rng.choice([0.0, 1.0 / 3.0, 0.5, 1.0], size=(n, k), p=[0.5, 0.05, 0.25, 0.2])
+        eff = rng.normal(scale=2.0)
+        y = (rng.random(n) < 1.0 / (1.0 + np.exp(-(eff * df[:, 0] - 0.3)))).astype(np.uint8)
+        if trial % 9 == 4:
+            y = (df[:, 0] > 0.4).astype(np.uint8)       # perfect separation: large betas held by the L2 term
+        if trial % 13 == 6:
+            y[:] = 1                                    # constant phenotype
+        covar = rng.normal(size=(n, 2)) if trial % 2 == 0 else None
+        want = ref.logistic_regression(df, y, covar)
+        got = oracle.logistic_regression(df, y, covar)
+        got_s = _logit_strings(oracle, got)
+        assert all(_close(a, b) for a, b in zip(got_s, want)), (trial, n, k, got_s, want)
+        with_cov = oracle.logistic_regression(df, y, covar, use_covariates=False)
+        assert with_cov == got or (np.isnan(got["p"]) and np.isnan(with_cov["p"]))
+        n_checked += 1
+        n_multi += k > 1
+        n_na += want[0] == "NA"
+    assert n_checked == 160 and n_multi > 60
+
+
+def _check_binary_covar(oracle, bits, n_rows, n_cols, P, nodes, is_case, covar, threads):
+    res = oracle.binary_covar_batch(bits, n_cols, is_case, P, covar=covar)
+    out = ref.run("binary_covar", bits, n_rows, n_cols, P.snarl_path_off, nodes, is_case=is_case, covar=covar, n_threads=threads)
+    spo = P.snarl_path_off.astype(np.int64)
+    kept = np.flatnonzero((res["filtered"] == 0) & (res["code"] != 5))  # code 5: the reference reads out of bounds
+    undef = set(np.flatnonzero((res["filtered"] == 0) & (res["code"] == 5)).tolist())
+    assert sorted(set(out["rows"]) - undef) == list(kept), "filter decisions differ"
+    for s in kept:
+        (row,) = out["rows"][int(s)]
+        assert row["ALLELE_PATHS"] == ",".join(str(v) for v in res["allele_paths"][spo[s]:spo[s + 1]]), (s, row)
+        want = ["NA"] * 3 if res["code"][s] == 1 else [oracle.set_precision(res[k][s]) for k in ("p_value", "beta", "se")]
+        for col, w in zip(("P", "BETA", "SE"), want):
+            assert _close(row[col], w), (s, col, row, w)
+    return kept.size
+
+
+def test_reference_binary_covar_analyzer_vs_oracle(oracle):
+    from stoat_b200 import synth
+
+    d = synth.numpy_dataset(400, 150, seed=6, frac_missing_edge=0.03)
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    nodes = ref.nodes_from_structure(d["structure"])
+    covar = np.random.default_rng(4).normal(size=(150, 3))
+    assert _check_binary_covar(oracle, d["bits"], d["n_rows"], d["n_cols"], P, nodes, d["is_case"], covar, threads=4) > 200
+    assert _check_binary_covar(oracle, d["bits"], d["n_rows"], d["n_cols"], P, nodes, d["is_case"], None, threads=1) > 200
+    rng = np.random.default_rng(17)
+    n_samples = 60
+    dense, snarls = H.partition_problem(rng, 150, n_samples)
+    spo, peo, er = H.csr_from_lists(snarls)
+    bits = oracle.pack_matrix(dense)
+    P = oracle.Paths(spo, peo, er)
+    nodes = ref.nodes_from_csr(spo, peo, er, dense.shape[0])
+    is_case = (rng.random(n_samples) < 0.5).astype(np.uint8)
+    assert _check_binary_covar(oracle, bits, dense.shape[0], 2 * n_samples, P, nodes, is_case, None, threads=2) > 30
+    dense, snarls = H.random_snarl_problem(rng, 150, n_samples, 40)
+    spo, peo, er = H.csr_from_lists(snarls)
+    bits = oracle.pack_matrix(dense)
+    P = oracle.Paths(spo, peo, er)
+    nodes = ref.nodes_from_csr(spo, peo, er, 40)
+    _check_binary_covar(oracle, bits, 40, 2 * n_samples, P, nodes, is_case, None, threads=2)
