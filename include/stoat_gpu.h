@@ -123,6 +123,21 @@ typedef struct stoat_gpu_quant_out {
     uint8_t* code;          /* [n_snarls] STOAT_P_VALUE or STOAT_P_UNDEF                     */
 } stoat_gpu_quant_out;
 
+/* outputs of the binary analyzer with covariates: BinaryCovarSnarlAnalyzer::analyze_and_write_snarl
+ * (src/snarl_analyzer.cpp:392-428) -> LogisticRegression::logistic_regression
+ * (src/stats_test.cpp:49-176): the dosage table of the quantitative analyzer against the binary
+ * phenotype, IRLS with an L2 penalty of 1e-4, Wald test, Holm over the dosage columns.       */
+typedef struct stoat_gpu_binary_covar_out {
+    uint32_t* allele_paths; /* [n_paths]                                                     */
+    uint8_t* filtered;      /* [n_snarls] filtration_quantitative_table (:542-579)          */
+    uint32_t* n_used;       /* [n_snarls]                                                    */
+    double* p_value;        /* [n_snarls] smallest Holm-adjusted Wald p over the dosage columns */
+    double* beta;           /* [n_snarls] coefficient of that column                         */
+    double* se;             /* [n_snarls]                                                    */
+    uint8_t* code;          /* [n_snarls] STOAT_P_VALUE, STOAT_P_NA ("NA" triple: LDLT failure or
+                               no convergence in 100 iterations, :107,120) or STOAT_P_UNDEF  */
+} stoat_gpu_binary_covar_out;
+
 /* eQTL: EQTLSnarlAnalyzer::analyze_and_write_snarl (src/snarl_analyzer.cpp:493-539): one OLS
  * per (snarl, gene in window).  Gene windows are resolved on the host (found_gene_snarl,
  * :471-491) into a CSR of gene indices per snarl; pair k of the output is
@@ -199,6 +214,16 @@ STOAT_GPU_API int stoat_gpu_binary_batch(stoat_gpu_ctx* ctx, const stoat_gpu_pat
                            const stoat_gpu_thresholds* thr, stoat_gpu_binary_out* out);
 STOAT_GPU_API int stoat_gpu_quantitative_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
                                  const stoat_gpu_thresholds* thr, stoat_gpu_quant_out* out);
+/* Binary trait with covariates (logistic regression).  Needs set_binary_phenotype.  use_covariates = 0 reproduces the
+ * reference as written: its covariate block declares new locals that shadow num_covariates / num_features
+ * (src/stats_test.cpp:59-62), so the covariates never enter the design.  use_covariates = 1 appends the columns of
+ * set_covariates to the design (by filtered row position, as the linear model does) and leaves them out of the Wald
+ * tests (:148-153) — what the code evidently meant; no reference output exists for it.                           */
+STOAT_GPU_API int stoat_gpu_binary_covar_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
+                                 const stoat_gpu_thresholds* thr, int use_covariates,
+                                 stoat_gpu_binary_covar_out* out);
+STOAT_GPU_API int stoat_gpu_binary_covar_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int use_covariates);
+STOAT_GPU_API int stoat_gpu_binary_covar_fetch(stoat_gpu_ctx* ctx, stoat_gpu_binary_covar_out* out);
 STOAT_GPU_API int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths,
                          const stoat_gpu_eqtl_genes* genes, const stoat_gpu_thresholds* thr,
                          stoat_gpu_eqtl_out* out);

@@ -35,6 +35,11 @@ class QuantOut(C.Structure):
                 ("beta", f64p), ("se", f64p), ("code", u8p)]
 
 
+class BinaryCovarOut(C.Structure):
+    _fields_ = [("allele_paths", u32p), ("filtered", u8p), ("n_used", u32p), ("p_value", f64p), ("beta", f64p),
+                ("se", f64p), ("code", u8p)]
+
+
 class EqtlGenes(C.Structure):
     _fields_ = [("n_genes", C.c_uint64), ("expression", f64p), ("snarl_gene_off", u64p), ("gene_idx", u32p)]
 
@@ -67,6 +72,10 @@ SIGNATURES = {
     "stoat_gpu_set_covariates": (C.c_int, [CTX, C.c_void_p, C.c_uint64, C.c_uint64]),
     "stoat_gpu_binary_batch": (C.c_int, [CTX, C.POINTER(PathsC), C.POINTER(Thresholds), C.POINTER(BinaryOut)]),
     "stoat_gpu_quantitative_batch": (C.c_int, [CTX, C.POINTER(PathsC), C.POINTER(Thresholds), C.POINTER(QuantOut)]),
+    "stoat_gpu_binary_covar_batch": (C.c_int, [CTX, C.POINTER(PathsC), C.POINTER(Thresholds), C.c_int,
+                                               C.POINTER(BinaryCovarOut)]),
+    "stoat_gpu_binary_covar_run_staged": (C.c_int, [CTX, C.POINTER(Thresholds), C.c_int]),
+    "stoat_gpu_binary_covar_fetch": (C.c_int, [CTX, C.POINTER(BinaryCovarOut)]),
     "stoat_gpu_eqtl_batch": (C.c_int, [CTX, C.POINTER(PathsC), C.POINTER(EqtlGenes), C.POINTER(Thresholds),
                                        C.POINTER(EqtlOut)]),
     "stoat_gpu_eqtl_dense_summary": (C.c_int, [CTX, C.POINTER(PathsC), C.POINTER(EqtlGenes), C.POINTER(Thresholds),

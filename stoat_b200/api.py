@@ -203,6 +203,40 @@ class Context:
         self._check(self._lib.stoat_gpu_quantitative_batch(self._ctx, C.byref(pc), C.byref(thr), C.byref(oc)))
         return o
 
+    # ---- binary trait with covariates: logistic regression (BinaryCovarSnarlAnalyzer, src/snarl_analyzer.cpp:392-428) ---
+    @staticmethod
+    def _covar_arrays(S: int, P: int) -> dict:
+        return dict(allele_paths=np.zeros(P, np.uint32), filtered=np.zeros(S, np.uint8),
+                    n_used=np.zeros(S, np.uint32), p_value=np.zeros(S), beta=np.zeros(S), se=np.zeros(S),
+                    code=np.zeros(S, np.uint8))
+
+    @staticmethod
+    def _covar_c(o: dict) -> L.BinaryCovarOut:
+        return L.BinaryCovarOut(o["allele_paths"].ctypes.data_as(L.u32p), o["filtered"].ctypes.data_as(L.u8p),
+                                o["n_used"].ctypes.data_as(L.u32p), o["p_value"].ctypes.data_as(L.f64p),
+                                o["beta"].ctypes.data_as(L.f64p), o["se"].ctypes.data_as(L.f64p),
+                                o["code"].ctypes.data_as(L.u8p))
+
+    def binary_covar_batch(self, paths: SnarlPaths, use_covariates=False, min_ind=3, min_hap=5, maf=0.05,
+                           out: dict | None = None) -> dict:
+        """use_covariates=False is the reference as written (its covariates never reach the design, stats_test.cpp:59-62)."""
+        o = out if out is not None else self._covar_arrays(paths.n_snarls, paths.n_paths)
+        pc, thr, oc = paths.as_c(), self._thr(min_ind, min_hap, maf), self._covar_c(o)
+        self._check(self._lib.stoat_gpu_binary_covar_batch(self._ctx, C.byref(pc), C.byref(thr), int(bool(use_covariates)),
+                                                           C.byref(oc)))
+        return o
+
+    def binary_covar_run_staged(self, use_covariates=False, min_ind=3, min_hap=5, maf=0.05):
+        thr = self._thr(min_ind, min_hap, maf)
+        self._check(self._lib.stoat_gpu_binary_covar_run_staged(self._ctx, C.byref(thr), int(bool(use_covariates))))
+
+    def binary_covar_fetch(self, out: dict | None = None) -> dict:
+        S, P = self._staged
+        o = out if out is not None else self._covar_arrays(S, P)
+        oc = self._covar_c(o)
+        self._check(self._lib.stoat_gpu_binary_covar_fetch(self._ctx, C.byref(oc)))
+        return o
+
     # ---- eQTL: one OLS per (snarl, gene of its window) ----------------------------------------------
     def _genes_c(self, expression, snarl_gene_off, gene_idx):
         expr = np.ascontiguousarray(expression, dtype=np.float64)

@@ -57,6 +57,12 @@ struct QuantState {
     uint64_t lean_key = 0;  // what lean_rec holds: staging generation + participating kernels (launch_quantitative_impl)
 };
 
+struct LogitState {  // logistic regression (binary trait with covariates): its own result buffers
+    DevBuf counts, list, n_list, allele, filtered, n_used, p, beta, se, code;
+    bool have_result = false;
+    uint32_t n_general = 0;
+};
+
 }  // namespace
 
 constexpr int kMaxRunChunks = 8;  // chunks of an overlapped binary run (stoat_gpu_binary_run_staged)
@@ -70,6 +76,7 @@ constexpr int kRunRing = 64;      // staged runs whose events are kept for stoat
 // extra per-context state that does not need to be visible to the kernel translation units
 struct CtxExtra {
     QuantState q;
+    LogitState lg;
     uint32_t max_stage_rows = 0;
     uint64_t stage_gen = 0;  // bumped by every stage_paths
     uint32_t counters_host[4] = {0, 0, 0, 0};
@@ -140,6 +147,7 @@ static void invalidate_derived(stoat_gpu_ctx* ctx) {
     ctx->have_binary_counts = ctx->have_binary_result = ctx->have_quant_result = false;
     extra_of(ctx)->q.have_partials = false;
     extra_of(ctx)->q.lean_key = 0;
+    extra_of(ctx)->lg.have_result = false;
 }
 
 extern "C" {
@@ -231,6 +239,9 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     x->q.tail_df.release();
     x->q.tail_x.release();
     x->bh.release();
+    for (DevBuf* b : {&x->lg.counts, &x->lg.list, &x->lg.n_list, &x->lg.allele, &x->lg.filtered, &x->lg.n_used, &x->lg.p,
+                      &x->lg.beta, &x->lg.se, &x->lg.code})
+        b->release();
     for (auto& ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : x->chunk_done)
@@ -575,6 +586,7 @@ int stoat_gpu_stage_paths(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths) {
     ctx->have_batch = false;
     ctx->have_binary_counts = ctx->have_binary_result = ctx->have_quant_result = ctx->have_eqtl_summary = false;
     extra_of(ctx)->q.have_partials = false;
+    extra_of(ctx)->lg.have_result = false;
     ++x->stage_gen;  // lean records of the previous staging are stale
     CK(ctx->d_snarl_path_off.reserve((S + 1) * 8));
     CK(ctx->d_path_edge_off.reserve((P + 1) * 8));
@@ -926,6 +938,96 @@ int stoat_gpu_quantitative_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* path
     rc = stoat_gpu_quantitative_run_staged(ctx, thr);
     if (rc) return rc;
     rc = stoat_gpu_quantitative_fetch(ctx, out);
+    ctx->timing.h2d_ms = h2d;
+    if (ctx->batch.n_snarls) ctx->timing.launches += 1;  // prep
+    return rc;
+}
+
+// ---- binary trait with covariates: logistic regression ---------------------------------------------------
+// BinaryCovarSnarlAnalyzer::analyze_and_write_snarl (src/snarl_analyzer.cpp:392-428)
+int stoat_gpu_binary_covar_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int use_covariates) {
+    if (!ctx || !thr) return fail(ctx, STOAT_GPU_ERR_ARG, "binary_covar: NULL argument");
+    if (!ctx->have_batch) return fail(ctx, STOAT_GPU_ERR_STATE, "binary_covar: no staged batch");
+    if (!ctx->have_binary) return fail(ctx, STOAT_GPU_ERR_STATE, "binary_covar: no binary phenotype");
+    if (use_covariates && ctx->n_covar && ctx->n_samples_covar * 2 < ctx->n_cols)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "binary_covar: fewer covariate rows than samples");
+    CK(cudaSetDevice(ctx->device));
+    CtxExtra* x = extra_of(ctx);
+    LogitState& lg = x->lg;
+    const BatchDev& b = ctx->batch;
+    const uint64_t S = b.n_snarls;
+    CK(lg.counts.reserve(std::max<uint64_t>(S * sizeof(LogitCounts), 16)));
+    CK(lg.list.reserve(std::max<uint64_t>(S * 4, 16)));
+    CK(lg.n_list.reserve(16));
+    CK(lg.allele.reserve(std::max<uint64_t>(b.n_paths * 4, 16)));
+    CK(lg.filtered.reserve(std::max<uint64_t>(S, 16)));
+    CK(lg.n_used.reserve(std::max<uint64_t>(S * 4, 16)));
+    CK(lg.p.reserve(std::max<uint64_t>(S * 8, 16)));
+    CK(lg.beta.reserve(std::max<uint64_t>(S * 8, 16)));
+    CK(lg.se.reserve(std::max<uint64_t>(S * 8, 16)));
+    CK(lg.code.reserve(std::max<uint64_t>(S, 16)));
+    if (int frc = finalize_timing(ctx)) return frc;
+    ctx->timing.launches = 0;
+    LogitOut out{lg.allele.as<uint32_t>(), lg.filtered.as<uint8_t>(), lg.n_used.as<uint32_t>(), lg.p.as<double>(),
+                 lg.beta.as<double>(),     lg.se.as<double>(),        lg.code.as<uint8_t>()};
+    const bool honour = use_covariates && ctx->n_covar > 0;
+    // STOAT_GPU_LOGIT=general sends every snarl through the general kernel (tests compare the two paths)
+    const char* mode = std::getenv("STOAT_GPU_LOGIT");
+    const bool all_general = honour || ctx->n_cols >= (uint64_t(1) << 32) || (mode && std::string(mode) == "general");
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    CK(cudaMemsetAsync(lg.n_list.p, 0, 4, ctx->stream));
+    if (!all_general)
+        CK(launch_logit_fast(matrix_view(ctx), ctx->case_mask.as<uint8_t>(), b, *thr, lg.counts.as<LogitCounts>(),
+                             lg.list.as<uint32_t>(), lg.n_list.as<uint32_t>(), out, ctx->num_sms, ctx->stream,
+                             &ctx->timing.launches));
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    if (S) {
+        CK(launch_logit_general(matrix_view(ctx), ctx->is_case_dev.as<uint8_t>(), honour ? ctx->covar.as<double>() : nullptr,
+                                uint32_t(ctx->n_covar), b, *thr, out, all_general ? nullptr : lg.list.as<uint32_t>(),
+                                lg.n_list.as<uint32_t>(), S, ctx->num_sms, ctx->stream));
+        ctx->timing.launches += 1;
+    }
+    CK(cudaEventRecord(ctx->ev[4], ctx->stream));
+    lg.have_result = true;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_binary_covar_fetch(stoat_gpu_ctx* ctx, stoat_gpu_binary_covar_out* out) {
+    if (!ctx || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "binary_covar_fetch: NULL argument");
+    CtxExtra* x = extra_of(ctx);
+    LogitState& lg = x->lg;
+    if (!lg.have_result) return fail(ctx, STOAT_GPU_ERR_STATE, "binary_covar_fetch: nothing to fetch");
+    CK(cudaSetDevice(ctx->device));
+    const uint64_t S = ctx->batch.n_snarls, P = ctx->batch.n_paths;
+    const cudaMemcpyKind k = cudaMemcpyDeviceToHost;
+    CK(cudaEventRecord(ctx->ev[6], ctx->stream));
+    if (P && out->allele_paths) CK(cudaMemcpyAsync(out->allele_paths, lg.allele.p, P * 4, k, ctx->stream));
+    if (S && out->filtered) CK(cudaMemcpyAsync(out->filtered, lg.filtered.p, S, k, ctx->stream));
+    if (S && out->n_used) CK(cudaMemcpyAsync(out->n_used, lg.n_used.p, S * 4, k, ctx->stream));
+    if (S && out->p_value) CK(cudaMemcpyAsync(out->p_value, lg.p.p, S * 8, k, ctx->stream));
+    if (S && out->beta) CK(cudaMemcpyAsync(out->beta, lg.beta.p, S * 8, k, ctx->stream));
+    if (S && out->se) CK(cudaMemcpyAsync(out->se, lg.se.p, S * 8, k, ctx->stream));
+    if (S && out->code) CK(cudaMemcpyAsync(out->code, lg.code.p, S, k, ctx->stream));
+    CK(cudaMemcpyAsync(&lg.n_general, lg.n_list.p, 4, k, ctx->stream));
+    CK(cudaEventRecord(ctx->ev[7], ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaEventElapsedTime(&ctx->timing.table_ms, ctx->ev[2], ctx->ev[3]));  // class counts + IRLS on the counts
+    CK(cudaEventElapsedTime(&ctx->timing.stats_ms, ctx->ev[3], ctx->ev[4]));  // general kernel
+    CK(cudaEventElapsedTime(&ctx->timing.d2h_ms, ctx->ev[6], ctx->ev[7]));
+    ctx->timing.n_general = S ? lg.n_general : 0;
+    ctx->timing.n_fisher = 0;
+    return STOAT_GPU_OK;
+}
+
+int stoat_gpu_binary_covar_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const stoat_gpu_thresholds* thr,
+                                 int use_covariates, stoat_gpu_binary_covar_out* out) {
+    if (!ctx || !paths || !thr || !out) return fail(ctx, STOAT_GPU_ERR_ARG, "binary_covar_batch: NULL argument");
+    int rc = stoat_gpu_stage_paths(ctx, paths);
+    if (rc) return rc;
+    const float h2d = ctx->timing.h2d_ms;
+    rc = stoat_gpu_binary_covar_run_staged(ctx, thr, use_covariates);
+    if (rc) return rc;
+    rc = stoat_gpu_binary_covar_fetch(ctx, out);
     ctx->timing.h2d_ms = h2d;
     if (ctx->batch.n_snarls) ctx->timing.launches += 1;  // prep
     return rc;

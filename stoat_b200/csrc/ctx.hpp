@@ -130,6 +130,26 @@ bool quant_fast_path(uint64_t pitch, uint64_t n_hap, uint32_t max_stage_rows, in
 size_t quant_yslices_bytes(uint64_t pitch);  // K3M's phenotype slice table
 // slices of the haplotype range the two-path kernels (K3M / K3R) use: sizes the partial-sum buffers (0: neither runs)
 uint32_t quant_lean_slices(uint64_t pitch, uint64_t n_hap, uint32_t stage_rows);
+// logistic regression (kernels_logit.cu: class-count fast path; kernels_quant.cu: the general kernel's logistic mode)
+struct LogitCounts {  // per two-path snarl: haplotypes per path, samples per dosage class, and the cases among them
+    uint32_t al0, al1, used, full0, half, third, tthird, c_used, c_full0, c_half, c_third, c_tthird;
+};
+struct LogitOut {
+    uint32_t* allele_paths;
+    uint8_t* filtered;
+    uint32_t* n_used;
+    double* p;
+    double* beta;
+    double* se;
+    uint8_t* code;
+};
+cudaError_t launch_logit_fast(const MatrixDev& m, const uint8_t* case_mask, const BatchDev& b,
+                              const stoat_gpu_thresholds& thr, LogitCounts* counts, uint32_t* general_list,
+                              uint32_t* n_general, LogitOut out, int num_sms, cudaStream_t st, uint32_t* launches);
+// snarls list[0 .. *n_list_dev) (list == nullptr: every snarl of the batch); n_max bounds the grid
+cudaError_t launch_logit_general(const MatrixDev& m, const uint8_t* is_case, const double* covar, uint32_t n_covar,
+                                 const BatchDev& b, const stoat_gpu_thresholds& thr, LogitOut out, const uint32_t* list,
+                                 const uint32_t* n_list_dev, uint64_t n_max, int num_sms, cudaStream_t st);
 cudaError_t launch_centre_permute(const double* y, uint32_t n, double mean, uint32_t n_words, double* yc, double* ys,
                                   cudaStream_t st);
 size_t quant_moments_bytes(uint64_t n_snarls);

@@ -23,6 +23,10 @@ struct PVal {
     uint8_t code;
 };
 
+// boost::math::cdf(normal_distribution<>(0, 1), z) = erfc(-z / sqrt 2) / 2 (src/stats_test.cpp:22-25); the logistic
+// regression's Wald test then forms 2 (1 - cdf), a multiple of 2^-52 (:151-152)
+__device__ inline double normal_cdf_like_reference(double z) { return 0.5 * erfc(-z / 1.4142135623730951); }
+
 // ------------------------------------------------------------------------------------------------
 // Regularized upper incomplete gamma Q(a, x) for a = df/2, df a positive integer — finite sums:
 //   Q(n, x)     = e^-x * sum_{k<n} x^k / k!

@@ -1210,6 +1210,31 @@ cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, ui
     return launch_quant_general(g, n_snarls * g.gene_split, num_sms, st);
 }
 
+// BinaryCovarSnarlAnalyzer (src/snarl_analyzer.cpp:392-428) on the general path: the table against the binary phenotype,
+// then the logistic regression of quant_general.cuh.  covar == nullptr reproduces the reference (covariates ignored).
+cudaError_t launch_logit_general(const MatrixDev& m, const uint8_t* is_case, const double* covar, uint32_t n_covar,
+                                 const BatchDev& b, const stoat_gpu_thresholds& thr, LogitOut out, const uint32_t* list,
+                                 const uint32_t* n_list_dev, uint64_t n_max, int num_sms, cudaStream_t st) {
+    if (n_max == 0) return cudaSuccess;
+    GParams g{};
+    g.rows = m.rows;
+    g.pitch = uint32_t(m.pitch);
+    g.n_hap = uint32_t(m.n_cols);
+    g.n_samples = uint32_t(m.n_cols / 2);
+    g.y = nullptr;
+    g.is_case = is_case;
+    g.covar = covar;
+    g.n_covar = covar ? n_covar : 0;
+    g.b = b;
+    g.thr = thr;
+    g.out = QuantOut{out.allele_paths, out.filtered, out.n_used, out.p, nullptr, out.beta, out.se, out.code};
+    g.list = list;
+    g.n_list_dev = list ? n_list_dev : nullptr;
+    g.n_list_host = n_max;
+    g.gene_split = 1;
+    return launch_quant_general(g, n_max, num_sms, st);
+}
+
 // per-snarl reduction of a dense chunk: smallest p, its gene, number of genes with p < p_threshold
 // (the device-side stand-in for writing 4e9 TSV rows; mirrors --table-threshold, src/snarl_analyzer.cpp:524-527)
 __global__ void __launch_bounds__(128) eqtl_summary_kernel(const double* __restrict__ p, const uint8_t* __restrict__ code,

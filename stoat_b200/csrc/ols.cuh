@@ -151,6 +151,53 @@ __device__ inline bool xtx_inverse(const SmallMat<N>& XtX, int n, SmallMat<N>& i
     return false;
 }
 
+// Diagonal of the inverse of a general n x n matrix by row-pivoted LU and n unit-vector solves: what Eigen's
+// MatrixXd::inverse() does for a dynamic-size matrix (PartialPivLU), used by the logistic regression for the covariance
+// (src/stats_test.cpp:138-139).
+template <int N>
+__device__ inline void lu_inverse_diag(const SmallMat<N>& A, int n, double* diag) {
+    SmallMat<N> lu = A;
+    int perm[N];
+    for (int i = 0; i < n; ++i) perm[i] = i;
+    for (int k = 0; k < n; ++k) {
+        int piv = k;
+        double best = fabs(lu(k, k));
+        for (int i = k + 1; i < n; ++i) {
+            const double v = fabs(lu(i, k));
+            if (v > best) {
+                best = v;
+                piv = i;
+            }
+        }
+        if (piv != k) {
+            for (int j = 0; j < n; ++j) {
+                const double t = lu(k, j);
+                lu(k, j) = lu(piv, j);
+                lu(piv, j) = t;
+            }
+            const int t = perm[k];
+            perm[k] = perm[piv];
+            perm[piv] = t;
+        }
+        const double d = lu(k, k);
+        if (d != 0.0)
+            for (int i = k + 1; i < n; ++i) lu(i, k) /= d;
+        for (int j = k + 1; j < n; ++j)
+            for (int i = k + 1; i < n; ++i) lu(i, j) -= lu(i, k) * lu(k, j);
+    }
+    double b[N];
+    for (int c = 0; c < n; ++c) {
+        for (int i = 0; i < n; ++i) b[i] = (perm[i] == c) ? 1.0 : 0.0;
+        for (int i = 0; i < n; ++i)
+            for (int j = 0; j < i; ++j) b[i] -= lu(i, j) * b[j];
+        for (int i = n - 1; i >= c; --i) {  // rows below c of column c are not needed for the diagonal
+            for (int j = i + 1; j < n; ++j) b[i] -= lu(i, j) * b[j];
+            b[i] /= lu(i, i);
+        }
+        diag[c] = b[c];
+    }
+}
+
 struct OlsOut {
     double p, r2, beta, se;
 };

@@ -39,6 +39,9 @@ struct GParams {
     uint64_t item_base;  // per-item outputs are written at (item - item_base): chunked dense scans
     bool items_by_slot;  // dense scan over a LIST of snarls: the items of list entry i are [i * n_genes, (i + 1) * n_genes)
     uint32_t gene_split;  // items_by_slot: a list entry is worked by gene_split warps, each a contiguous share of the genes
+    // logistic regression (BinaryCovarSnarlAnalyzer, src/snarl_analyzer.cpp:392-428): the same table against the binary
+    // phenotype.  is_case != nullptr selects it; the outputs are p / beta / se (r2 is left NaN).
+    const uint8_t* is_case;  // [n_samples] 0 / 1
 };
 
 constexpr int kGWarps = 4;
@@ -55,6 +58,7 @@ struct GScratch {
     uint8_t fmult[kMaxPathsG];
     uint8_t merged[kMaxPathsG];
     uint8_t same[kMaxPathsG];
+    double wv[32], rv[32];            // logistic: sqrt(weight) and y - p of the current 32 samples
 };
 
 // word `w` (32 haplotypes) of the presence vector of path `pth` (identify_path, src/snarl_analyzer.cpp:315-356)
@@ -184,7 +188,8 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         }
         for (uint64_t k = k0 + lane; k < k1; k += 32) {
             const uint64_t o = k - g.item_base;
-            g.out.p[o] = g.out.r2[o] = g.out.beta[o] = g.out.se[o] = nan;
+            g.out.p[o] = g.out.beta[o] = g.out.se[o] = nan;
+            if (g.out.r2) g.out.r2[o] = nan;
             g.out.code[o] = code;
         }
     };
@@ -350,8 +355,160 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         for (uint32_t c = 0; c < g.n_covar; ++c)
             // covariate rows are taken by position in the FILTERED table (stats_test.cpp:450-452)
             sc.tile[lane][1 + k_reg + c] = used ? g.covar[size_t(rank) * g.n_covar + c] : 0.0;
-        sc.tile[lane][kMaxFeat] = (used && i < g.n_samples) ? y[i] : 0.0;
+        sc.tile[lane][kMaxFeat] = (used && i < g.n_samples) ? (g.is_case ? (g.is_case[i] ? 1.0 : 0.0) : y[i]) : 0.0;
     };
+    if (g.is_case) {
+        // ---- LogisticRegression::logistic_regression (src/stats_test.cpp:49-176) ----------------------
+        // IRLS: every pass sweeps the samples once for the Hessian X^T W X + l2 I and the gradient X^T (y - p) - l2 beta
+        // at the current beta (lanes own the entries, as in sweep B); lane 0 then takes the Newton step (pivoted LDLT,
+        // :107-111).  After the step that meets the tolerance (:113) one more pass gives the Hessian whose inverse is the
+        // covariance (:124-139).
+        constexpr double kTol = 1e-6, kL2 = 1e-4, kEps = 1e-8;  // src/stats_test.hpp:109-112
+        constexpr int kMaxIter = 100;
+        const uint32_t n_tri = p * (p + 1) / 2;
+        const uint32_t n_ent = n_tri + p;
+        double* beta_old = sc.inv;  // free here: no (X^T X)^-1 in this mode
+        if (lane < p) {
+            sc.beta[lane] = 0.0;
+            beta_old[lane] = 0.0;
+        }
+        __syncwarp();
+        int steps = 0;
+        int state = 0;  // 0: iterate, 1: converged (this pass is the covariance pass), 2: done
+        while (state != 2) {
+            double accv[6] = {0, 0, 0, 0, 0, 0};
+            rank_base = 0;
+            for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+                const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
+                const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+                __syncwarp();
+                build_tile(blk, used_ballot, nullptr);
+                rank_base += __popc(used_ballot);
+                {
+                    double z = 0.0;
+                    for (uint32_t r = 0; r < p; ++r) z = fma(sc.tile[lane][r], sc.beta[r], z);
+                    const double pr = 1.0 / (1.0 + exp(-z));                 // :27-29
+                    const double w = fmax(kEps, fmin(1.0, pr * (1.0 - pr)));  // :93
+                    const bool used = (used_ballot >> lane) & 1u;
+                    sc.wv[lane] = used ? sqrt(w) : 0.0;                       // X_weighted.row(i) *= sqrt(w), :97-98
+                    sc.rv[lane] = used ? sc.tile[lane][kMaxFeat] - pr : 0.0;
+                }
+                __syncwarp();
+#pragma unroll
+                for (int q = 0; q < 6; ++q) {
+                    const uint32_t e = lane + 32u * q;
+                    if (e >= n_ent) continue;
+                    double a2 = 0.0;
+                    if (e < n_tri) {
+                        for (uint32_t i = 0; i < 32; ++i)
+                            a2 = fma(sc.tile[i][er[q]] * sc.wv[i], sc.tile[i][ec[q]] * sc.wv[i], a2);
+                    } else {
+                        const uint32_t r = e - n_tri;
+                        for (uint32_t i = 0; i < 32; ++i) a2 = fma(sc.tile[i][r], sc.rv[i], a2);
+                    }
+                    accv[q] += a2;
+                }
+                __syncwarp();
+            }
+            double* flat = &sc.tile[0][0];
+#pragma unroll
+            for (int q = 0; q < 6; ++q)
+                if (lane + 32u * q < n_ent) flat[lane + 32u * q] = accv[q];
+            __syncwarp();
+            if (lane == 0) {
+                SmallMat<kMaxFeat> Hm;
+                uint32_t e = 0;
+                for (uint32_t r = 0; r < p; ++r)
+                    for (uint32_t c = 0; c <= r; ++c, ++e) {
+                        Hm(r, c) = flat[e];
+                        Hm(c, r) = flat[e];
+                    }
+                for (uint32_t r = 0; r < p; ++r) Hm(r, r) += kL2;  // :101
+                uint8_t code = kPValue;
+                double out_p = nan, out_b = nan, out_se = nan;
+                if (state == 1) {
+                    double diag[kMaxFeat];
+                    lu_inverse_diag<kMaxFeat>(Hm, int(p), diag);  // hessian.inverse(), :138
+                    double pv[kMaxFeat];
+                    const uint32_t n_tests = k_reg;  // covariate columns are not tested (:150)
+                    for (uint32_t i = 0; i < n_tests; ++i) {
+                        const double zs = sc.beta[1 + i] / sqrt(diag[1 + i]);
+                        pv[i] = 2.0 * (1.0 - normal_cdf_like_reference(fabs(zs)));  // :151-152
+                    }
+                    uint32_t best = 0;
+                    out_p = pv[0];
+                    if (n_tests > 1) {  // adjusted_holm (src/utils.cpp:61-87) + the smallest adjusted value (:169-175)
+                        uint8_t ord[kMaxFeat];
+                        for (uint32_t i = 0; i < n_tests; ++i) {
+                            uint32_t j = i;
+                            while (j > 0 && pv[ord[j - 1]] > pv[i]) {
+                                ord[j] = ord[j - 1];
+                                --j;
+                            }
+                            ord[j] = uint8_t(i);
+                        }
+                        double prev = 0.0, best_v = 0.0;
+                        bool have = false;
+                        for (uint32_t i = 0; i < n_tests; ++i) {
+                            const double raw = fmin(double(n_tests - i) * pv[ord[i]], 1.0);
+                            const double adj = fmax(prev, raw);
+                            prev = adj;
+                            // std::min_element over the ORIGINAL order: the first index holding the minimum
+                            if (!have || adj < best_v || (adj == best_v && ord[i] < best)) {
+                                best_v = adj;
+                                best = ord[i];
+                                have = true;
+                            }
+                        }
+                        out_p = best_v;
+                    }
+                    out_b = sc.beta[1 + best];
+                    out_se = sqrt(diag[1 + best]);
+                    state = 2;
+                } else {
+                    double gvec[kMaxFeat];
+                    for (uint32_t r = 0; r < p; ++r) gvec[r] = flat[n_tri + r] - kL2 * sc.beta[r];  // :105
+                    int tr[kMaxFeat];
+                    ldlt_factor<kMaxFeat>(Hm, int(p), tr);
+                    bool bad = false;
+                    for (uint32_t r = 0; r < p; ++r) bad |= isnan(Hm(r, r));
+                    if (bad) {
+                        code = kPNa;  // ldlt.info() != Success, :107
+                        state = 2;
+                    } else {
+                        ldlt_solve<kMaxFeat>(Hm, int(p), tr, gvec);
+                        double nrm = 0.0;
+                        for (uint32_t r = 0; r < p; ++r) {
+                            sc.beta[r] += gvec[r];
+                            const double d = sc.beta[r] - beta_old[r];
+                            nrm = fma(d, d, nrm);
+                        }
+                        ++steps;
+                        if (sqrt(nrm) < kTol) {
+                            state = 1;
+                        } else if (steps >= kMaxIter) {
+                            code = kPNa;  // not converged, :120
+                            state = 2;
+                        } else {
+                            for (uint32_t r = 0; r < p; ++r) beta_old[r] = sc.beta[r];
+                        }
+                    }
+                }
+                if (state == 2) {
+                    const uint64_t oi = s - g.item_base;
+                    g.out.p[oi] = out_p;
+                    if (g.out.r2) g.out.r2[oi] = nan;
+                    g.out.beta[oi] = out_b;
+                    g.out.se[oi] = out_se;
+                    g.out.code[oi] = code;
+                }
+            }
+            state = __shfl_sync(0xffffffffu, state, 0);
+            steps = __shfl_sync(0xffffffffu, steps, 0);
+            __syncwarp();
+        }
+        return;
+    }
     for (uint64_t item = k0; item < k1; ++item) {
         const bool first = (item == k0);
         const double* y = g.y;
