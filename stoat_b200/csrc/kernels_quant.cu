@@ -997,10 +997,14 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             if ((e = cudaMemsetAsync(b.counters + 3, 0, 8, st)) != cudaSuccess) return e;
             // three-path snarls: K3M3 when one CTA row covers the haplotype range and the step is not sample-sharded
             // (K3M3 writes moments, not partial sums); their records live behind the two-path records
-            const bool three = phase == 0 && pm.n_slices == 1 && env_int("STOAT_GPU_K3M3", 1) != 0;
+            // beyond one slice (> 12,288 haplotypes) their slice table stays in global memory
+            const bool wide_table = pm.n_slices > 1;
+            const uint32_t smem_small = wide_table ? 0u : pm.smem_bytes;
+            q.table_in_global = wide_table ? 1u : 0u;
+            const bool three = phase == 0 && env_int("STOAT_GPU_K3M3", 1) != 0;
             uint4* rec3 = three ? lean_rec + b.n_snarls : nullptr;
             // ... and two-path snarls with dosages of 1/3, 2/3 (K3M2x), under the same conditions: [S][2] more records
-            const bool thirds = phase == 0 && pm.n_slices == 1 && env_int("STOAT_GPU_K3M2X", 1) != 0;
+            const bool thirds = phase == 0 && env_int("STOAT_GPU_K3M2X", 1) != 0;
             q.rec2x = thirds ? lean_rec + 3 * b.n_snarls : nullptr;
             q.count2x = b.counters + 6;
             q.count2x_dyn = b.counters + 4;
@@ -1041,7 +1045,13 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             uint64_t ctas = uint64_t(num_sms) * uint64_t(occ) / pm.n_slices;
             if (ctas < 1) ctas = 1;
             if (ctas > (n_tiles + kMmaWarps - 1) / kMmaWarps) ctas = (n_tiles + kMmaWarps - 1) / kMmaWarps;
-            dosage_moments_mma_kernel<<<dim3(unsigned(ctas), pm.n_slices), kMmaWarps * 32, pm.smem_bytes, st>>>(q);
+            {
+                // With several haplotype slices a snarl's thirds may show in one slice only, so K3M does not append to the
+                // thirds list itself (the slices would race on the snarl's state): K4 sends such a snarl to the general list
+                K3MParams q_main = q;
+                if (wide_table) q_main.rec2x = nullptr;
+                dosage_moments_mma_kernel<<<dim3(unsigned(ctas), pm.n_slices), kMmaWarps * 32, pm.smem_bytes, st>>>(q_main);
+            }
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             if (ev_table_done && (e = cudaEventRecord(ev_table_done, st)) != cudaSuccess) return e;
             if (launches) *launches += 1;
@@ -1049,44 +1059,44 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             if (three) {
                 static thread_local int dev3 = -1, occ3 = 1;
                 static thread_local uint32_t smem3 = 0;
-                if (dev_now != dev3 || pm.smem_bytes != smem3) {
+                if (dev_now != dev3 || smem_small != smem3) {
                     e = cudaFuncSetAttribute(dosage_moments_mma3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             int(pm.smem_bytes));
+                                             int(smem_small));
                     if (e != cudaSuccess) return e;
                     int o = 1;
                     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, dosage_moments_mma3_kernel, kMmaWarps * 32,
-                                                                      pm.smem_bytes) != cudaSuccess || o < 1)
+                                                                      smem_small) != cudaSuccess || o < 1)
                         o = 1;
                     dev3 = dev_now;
-                    smem3 = pm.smem_bytes;
+                    smem3 = smem_small;
                     occ3 = o;
                 }
                 const uint64_t tiles3 = (b.n_snarls + kMma3Tile - 1) / kMma3Tile;
                 uint64_t ctas3 = uint64_t(num_sms) * uint64_t(occ3);
                 if (ctas3 > (tiles3 + kMmaWarps - 1) / kMmaWarps) ctas3 = (tiles3 + kMmaWarps - 1) / kMmaWarps;
-                dosage_moments_mma3_kernel<<<unsigned(ctas3), kMmaWarps * 32, pm.smem_bytes, st>>>(q, rec3, b.counters + 5);
+                dosage_moments_mma3_kernel<<<unsigned(ctas3), kMmaWarps * 32, smem_small, st>>>(q, rec3, b.counters + 5);
                 if ((e = cudaGetLastError()) != cudaSuccess) return e;
                 if (launches) *launches += 1;
             }
             if (thirds) {
                 static thread_local int dev2 = -1, occ2 = 1;
                 static thread_local uint32_t smem2 = 0;
-                if (dev_now != dev2 || pm.smem_bytes != smem2) {
+                if (dev_now != dev2 || smem_small != smem2) {
                     e = cudaFuncSetAttribute(dosage_moments_mma2x_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             int(pm.smem_bytes));
+                                             int(smem_small));
                     if (e != cudaSuccess) return e;
                     int o = 1;
                     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, dosage_moments_mma2x_kernel, kMmaWarps * 32,
-                                                                      pm.smem_bytes) != cudaSuccess || o < 1)
+                                                                      smem_small) != cudaSuccess || o < 1)
                         o = 1;
                     dev2 = dev_now;
-                    smem2 = pm.smem_bytes;
+                    smem2 = smem_small;
                     occ2 = o;
                 }
                 const uint64_t tiles2 = (b.n_snarls + kMma3Tile - 1) / kMma3Tile;
                 uint64_t ctas2 = uint64_t(num_sms) * uint64_t(occ2);
                 if (ctas2 > (tiles2 + kMmaWarps - 1) / kMmaWarps) ctas2 = (tiles2 + kMmaWarps - 1) / kMmaWarps;
-                dosage_moments_mma2x_kernel<<<unsigned(ctas2), kMmaWarps * 32, pm.smem_bytes, st>>>(q);
+                dosage_moments_mma2x_kernel<<<unsigned(ctas2), kMmaWarps * 32, smem_small, st>>>(q);
                 if ((e = cudaGetLastError()) != cudaSuccess) return e;
                 if (launches) *launches += 1;
             }

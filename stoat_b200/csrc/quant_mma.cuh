@@ -52,6 +52,8 @@ struct K3MParams {
     uint4* rec2x;        // nullptr: snarls with non-dyadic dosages are marked for the general path instead
     uint32_t* count2x;      // records lean_rec_kernel listed (fixed for a staging)
     uint32_t* count2x_dyn;  // records K3M appended behind them during this step
+    uint32_t table_in_global;  // K3M3 / K3M2x: the slice table does not fit shared memory (> 24 rounds = 12,288 haplotypes),
+                               // the B fragments are read from global memory (L1 / L2 resident: 2 KB per round)
 };
 
 // rec / path program -> lean record (one thread per snarl; 48 B in, 16 B out)
@@ -487,13 +489,13 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma3_kernel(
     const uint32_t n3 = *count3;
     if (n3 == 0u) return;
     const uint32_t r_len = q.n_rounds;
-    {
+    if (!q.table_in_global) {
         const uint4* src = reinterpret_cast<const uint4*>(q.yslices);
         uint4* dst = reinterpret_cast<uint4*>(ysl);
         for (uint32_t i = tid; i < r_len * 128u; i += blockDim.x) dst[i] = __ldg(src + i);
     }
     __syncthreads();
-    const uint8_t* bfrag_lane = ysl + lane * 8;
+    const uint8_t* bfrag_lane = (q.table_in_global ? q.yslices : ysl) + lane * 8;
     const uint32_t n_tiles = (n3 + kMma3Tile - 1) / kMma3Tile;
     const uint32_t stride = gridDim.x * kMmaWarps;
     const double sc0 = __hiloint2double(int((1023u - 7u * (2u * t + 1u)) << 20), 0);
@@ -753,13 +755,13 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma2x_kernel
     __shared__ double2 exact_tab[16];  // lean_exact_filtered
     if (tid < 16) exact_tab[tid] = exact_tab_entry(tid);
     const uint32_t r_len = q.n_rounds;
-    {
+    if (!q.table_in_global) {
         const uint4* src = reinterpret_cast<const uint4*>(q.yslices);
         uint4* dst = reinterpret_cast<uint4*>(ysl);
         for (uint32_t i = tid; i < r_len * 128u; i += blockDim.x) dst[i] = __ldg(src + i);
     }
     __syncthreads();
-    const uint8_t* bfrag_lane = ysl + lane * 8;
+    const uint8_t* bfrag_lane = (q.table_in_global ? q.yslices : ysl) + lane * 8;
     const uint32_t n_tiles = (n2 + kMma3Tile - 1) / kMma3Tile;
     const uint32_t stride = gridDim.x * kMmaWarps;
     const double sc0 = __hiloint2double(int((1023u - 7u * (2u * t + 1u)) << 20), 0);
