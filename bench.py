@@ -464,10 +464,17 @@ def parity_spot_check(env, ctx, d, trait, n_check, res, col_sharded):
     is_case, y = d["is_case"], d["y"]
     n_cols = d["n_cols"]
     if col_sharded and env.world > 1:
-        parts = [torch.empty_like(pre) for _ in range(env.world)]
-        env.dist.all_gather(parts, pre.contiguous())
-        pre = torch.cat(parts, dim=1)
-        n_cols = d["n_cols"] * env.world
+        # the ranks' column slices differ in width (the last one is what is left): pad to the widest, gather, trim
+        widths = [torch.zeros(1, dtype=torch.int64, device=pre.device) for _ in range(env.world)]
+        env.dist.all_gather(widths, torch.tensor([row_bytes], dtype=torch.int64, device=pre.device))
+        widths = [int(w.item()) for w in widths]
+        wmax = max(widths)
+        mine = torch.zeros((r1, wmax), dtype=pre.dtype, device=pre.device)
+        mine[:, :row_bytes] = pre
+        parts = [torch.empty_like(mine) for _ in range(env.world)]
+        env.dist.all_gather(parts, mine)
+        pre = torch.cat([p_[:, :w] for p_, w in zip(parts, widths)], dim=1)
+        n_cols = 8 * sum(widths)
         is_case, y = d["is_case_all"], d["y_all"]
     if env.rank != 0:
         return None
