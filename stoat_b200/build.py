@@ -19,7 +19,7 @@ NVCC_FLAGS = [
     "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
     "--expt-relaxed-constexpr",
-]
+] + os.environ.get("STOAT_NVCC_EXTRA", "").split()
 
 
 def nvcc() -> str:

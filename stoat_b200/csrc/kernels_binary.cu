@@ -757,6 +757,210 @@ __global__ void __launch_bounds__(128, 8) fisher_exact_kernel(const uint4* __res
     }
 }
 
+// K2b, block form (default).  The serial kernel above issues ~34 instructions per step of the recurrence, 13 of them on the
+// FP64 pipe (the quotient alone is MUFU + 4 DFMA + DMUL), and a table has three events that run divergent code.  Here a lane
+// advances its table M steps at a time without a division and without a per-step decision:
+//     N_j, D_j   the carried integer products of the serial form (exact)
+//     PN_j = (cur / bias) * N_1 ... N_j,   PD_j = D_1 ... D_j            =>  term_j = bias * PN_j / PD_j
+//     A_j  = A_{j-1} * D_j + PN_j                                         =>  sum of the block's terms = bias * A_M / PD_M
+// (Horner over the common denominator: M steps cost 4 DADD + 2 DMUL + 1 DFMA each and ONE reciprocal.)  Which running sum
+// a term belongs to is the reference's own test `cur_prob < kExactTestBias` (src/stats_test.cpp:315), here PN_j < PD_j on
+// the bit patterns; the terms below the bias are summed a second time (T_j), so the block adds bias * (A - T) / PD to cprob
+// and bias * T / PD to tprob.  The sequence of terms is unimodal, so that test is also what separates the reference's first
+// loop (towards and past the centre, :306-321) from its second (:326-337): the two become ONE pass over the far side with no
+// hand-over event, followed by the near side (:339-357).  A side ends when its last term no longer changes tprob
+// (:333, :351: here term < tprob * 2^-53 at the end of a block — at most M - 1 terms, each below an ulp of tprob, are
+// added beyond the reference's stopping point) or when the column is used up (:306 `cur12 > 0.5`); steps past the end of
+// the column multiply by N = 0 and add exact zeros.  A block whose products leave the double range
+// sends the table through the serial routine of device_math.cuh.  Not bit-identical to the reference (sums are associated
+// differently, ~1e-15 relative); STOAT_GPU_FISHER=exact is.  Ties within kExactTestEpsilon2 = 9.1e-13 of the observed
+// table's probability fall on the reference's side: the block form's error is three orders below that margin.
+__device__ unsigned long long g_fisher_dbg[4];  // STOAT_GPU_FISHER_DEBUG: fallbacks, lane-blocks, tables, far-side blocks
+template <int M>
+__global__ void __launch_bounds__(128, 8) fisher_block_kernel(const uint4* __restrict__ tab,
+                                                              const uint32_t* __restrict__ idx,
+                                                              uint32_t* __restrict__ counters,  // [0] n_work, [1] next
+                                                              double* __restrict__ p_fisher,
+                                                              uint8_t* __restrict__ fisher_code) {
+    constexpr double kEps2 = 9.094947017729282e-13;
+    constexpr double kBias = 1.0339757656912846e-25;
+    constexpr double kStart = (1 - kEps2) * kBias;
+    constexpr double kInvBias = 1.0 / kBias;
+    const long long kBiasBits = __double_as_longlong(kBias);
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t n_work = counters[0];
+    bool active = false, drained = false, far = false;
+    uint32_t snarl = 0, a11 = 0, a12 = 0, a21 = 0, a22 = 0;
+    int rem = 0;
+    double N = 0, sN = 0, D = 1, sD = 0, cur = 0, tprob = 1, cprob = 0, two = 0;
+    // cur, tprob and cprob are kept as (true value) * pd0, pd0 = 2^-E.  E stays 0 unless the terms of the far side climb
+    // above 2^128 (a table whose p-value is below ~1e-60): then all three are scaled down by 2^256 at the end of a block, so
+    // that the climb towards the centre can go on to the reference's overflow point (cur_prob > DBL_MAX -> "0", :312-314) in
+    // block form instead of overflowing the block products 250 orders early.  The result tprob / (cprob + tprob) and the
+    // tests against the bias (PN_0 = cur / bias, PD_0 = pd0) do not depend on the scale.
+    double pd0 = 1.0;
+    // One side of the table: numerator factors n1, n2 count down, denominator factors d1, d2 count up.  The carried products
+    // and their increments are scaled by k = 2^-ilogb(first denominator) — exact, and the same k on both, so every quotient
+    // N_j / D_j is unchanged while the block products PD = prod D_j k stay near 1 for any M and any table size.
+    auto start_side = [&](uint32_t n1, uint32_t n2, uint32_t d1, uint32_t d2) {
+        const double d_first = __dmul_rn(double(d1) + 1.0, double(d2) + 1.0);
+        const double k = __hiloint2double((2046 - (__double2hiint(d_first) >> 20)) << 20, 0);  // 2^-ilogb(d_first)
+        N = __dmul_rn(__dmul_rn(double(n1), double(n2)), k);
+        sN = __dmul_rn(double(n1) + double(n2) - 1.0, k);
+        D = __dmul_rn(__dmul_rn(double(d1), double(d2)), k);
+        sD = __dmul_rn(double(d1) + double(d2) + 1.0, k);
+        two = __dadd_rn(k, k);
+        cur = __dmul_rn(kStart, pd0);
+        rem = int(n1);
+    };
+    auto finish = [&](double v, uint8_t code) {
+        p_fisher[snarl] = v;
+        fisher_code[snarl] = code;
+        active = false;
+    };
+    for (;;) {
+        // ---- refill the idle lanes from the work list ----------------------------------------------------------
+        const uint32_t need = __ballot_sync(0xffffffffu, !active && !drained);
+        if (need) {
+            const int leader = __ffs(need) - 1;
+            uint32_t base = 0;
+            if (int(lane) == leader) base = atomicAdd(&counters[1], uint32_t(__popc(need)));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!active && !drained) {
+                const uint32_t w = base + __popc(need & ((1u << lane) - 1u));
+                if (w < n_work) {
+                    const uint4 t = tab[w];
+                    snarl = idx[w];
+                    if ((t.x | t.y | t.z | t.w) >> 26) {  // products would leave the exact-integer range
+                        fisher_big_table(t, snarl, p_fisher, fisher_code);
+                    } else {
+                        a11 = t.x; a12 = t.y; a21 = t.z; a22 = t.w;
+                        uint32_t u;
+                        if (a12 > a21) { u = a12; a12 = a21; a21 = u; }  // stats_test.cpp:280-284
+                        if (a11 > a22) { u = a11; a11 = a22; a22 = u; }  // :286-290
+                        if (uint64_t(a11) * a22 > uint64_t(a12) * a21) {  // :292-299
+                            u = a11; a11 = a12; a12 = u;
+                            u = a21; a21 = a22; a22 = u;
+                        }
+                        if (a12 == 0) {  // the first loop does not run (:306), cprob == 0 (:322-324)
+                            p_fisher[snarl] = 1.0;
+                            fisher_code[snarl] = kPOne;
+                        } else {
+#ifdef STOAT_FISHER_DEBUG
+                            atomicAdd(&g_fisher_dbg[2], 1ull);
+#endif
+                            pd0 = 1.0;
+                            start_side(a12, a21, a11, a22);
+                            tprob = kStart; cprob = 0.0;
+                            far = true;
+                            active = true;
+                        }
+                    }
+                } else {
+                    drained = true;
+                }
+            }
+            if (__any_sync(0xffffffffu, !active && !drained)) continue;  // a lane drew a table that was done at once
+        }
+        if (!__any_sync(0xffffffffu, active)) break;
+        if (!active) {  // parked: a lane whose list ran dry iterates on harmless values
+            N = 0; sN = 0; D = 1; sD = 0; two = 0; cur = 0; tprob = 1; cprob = 0; rem = 0x3FFFFFFF; far = false; pd0 = 1.0;
+        }
+        // ---- M steps of the recurrence, every lane in the same straight-line code ----------------------------------
+        const double cur0 = cur;
+        double PN = __dmul_rn(cur, kInvBias), PD = pd0, A = 0.0, T = 0.0;
+#pragma unroll
+        for (int j = 0; j < M; ++j) {
+            D = __dadd_rn(D, sD);
+            sD = __dadd_rn(sD, two);
+            PN = __dmul_rn(PN, N);
+            N = __dsub_rn(N, sN);
+            sN = __dsub_rn(sN, two);
+            PD = __dmul_rn(PD, D);
+            A = fma(A, D, PN);
+            // term_j < bias: the positive doubles compare like their bit patterns (a -0 past the end of the column counts as below)
+            const bool below = __double_as_longlong(PN) < __double_as_longlong(PD);
+            T = fma(T, D, below ? PN : 0.0);
+        }
+        rem -= M;
+#ifdef STOAT_FISHER_DEBUG
+        if (active) { atomicAdd(&g_fisher_dbg[1], 1ull); if (far) atomicAdd(&g_fisher_dbg[3], 1ull); }
+#endif
+        const double sc = __dmul_rn(fast_rcp(PD), __dmul_rn(kBias, pd0));
+        const double t_add = __dmul_rn(T, sc), c_add = __dmul_rn(__dsub_rn(A, T), sc);
+        cur = __dmul_rn(PN, sc);
+        tprob = __dadd_rn(tprob, t_add);
+        cprob = __dadd_rn(cprob, c_add);
+        // end of the side: the last term is below the bias AND no longer counts in tprob, or the column is used up
+        const double still = __dmul_rn(tprob, 1.1102230246251565e-16);
+        const long long cb = __double_as_longlong(cur);
+        const bool end_side = (cb < __double_as_longlong(__dmul_rn(kBias, pd0)) && cb < __double_as_longlong(still)) || rem <= 0;
+        const double ovf = __dmul_rn(DBL_MAX, pd0);  // DBL_MAX on the scale of cur / tprob / cprob
+        const bool nonfinite = __double2hiint(cprob) >= 0x7FF00000 || __double2hiint(tprob) >= 0x7FF00000 ||
+                               __double2hiint(cur) >= 0x7FF00000;
+        const bool over = c_add > ovf || cur > ovf;          // a term of this block may have passed DBL_MAX
+        const bool large = __double2hiint(cur) >= 0x47F00000;  // scaled cur >= 2^128
+        bool ev = (end_side || nonfinite || over || large) && active;
+        if (!__any_sync(0xffffffffu, ev)) continue;
+        // ---- events --------------------------------------------------------------------------------------------------
+        if (ev) {
+            bool passed = over && cur > ovf;  // the block's last term is beyond DBL_MAX
+            if (!nonfinite && over && !passed) {
+                // The block's sum passed DBL_MAX, its last term did not: whether a single term did (:312) is decided by
+                // stepping through this one block again, term by term, from the state it started in (the carried products
+                // are recovered exactly from the end state: they are integers times k).
+                constexpr double h = double(M) * double(M - 1) / 2.0;
+                double sn = __dadd_rn(sN, __dmul_rn(double(M), two)), sd = __dsub_rn(sD, __dmul_rn(double(M), two));
+                double nn = __dsub_rn(__dadd_rn(N, __dmul_rn(double(M), sn)), __dmul_rn(h, two));
+                double dd = __dsub_rn(__dsub_rn(D, __dmul_rn(double(M), sd)), __dmul_rn(h, two));
+                double c = cur0;
+                for (int j = 0; j < M && j < rem + M; ++j) {
+                    dd = __dadd_rn(dd, sd);
+                    sd = __dadd_rn(sd, two);
+                    c = __dmul_rn(c, __ddiv_rn(nn, dd));
+                    nn = __dsub_rn(nn, sn);
+                    sn = __dsub_rn(sn, two);
+                    if (c > ovf) {
+                        passed = true;
+                        break;
+                    }
+                }
+            }
+            if (nonfinite) {
+                // the block products themselves left the double range (a climb of more than 2^800 within one block)
+#ifdef STOAT_FISHER_DEBUG
+                atomicAdd(&g_fisher_dbg[0], 1ull);
+#endif
+                fisher_big_table(make_uint4(a11, a12, a21, a22), snarl, p_fisher, fisher_code);
+                active = false;
+            } else if (passed) {
+                finish(0.0, kPZero);  // :312-314: cur_prob > DBL_MAX
+            } else if (!end_side) {
+                // still climbing with large scaled values: scale down by 2^256 (at most three times: the bias stays a normal
+                // number) and go on
+                if (large && pd0 > 1e-200) {
+                    const double dn = 8.636168555094445e-78;  // 2^-256
+                    cur = __dmul_rn(cur, dn);
+                    tprob = __dmul_rn(tprob, dn);
+                    cprob = __dmul_rn(cprob, dn);
+                    pd0 = __dmul_rn(pd0, dn);
+                }
+            } else if (far) {
+                if (cprob == 0) {
+                    finish(1.0, kPOne);  // :322-324: no table is more probable than the observed one
+                } else if (a11 == 0) {
+                    finish(__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue);  // :339, :359
+                } else {  // :339-344
+                    start_side(a11, a22, a12, a21);
+                    far = false;
+                }
+            } else {
+                finish(__ddiv_rn(tprob, __dadd_rn(cprob, tprob)), kPValue);  // :352-354, :359
+            }
+        }
+    }
+}
+
 // statistics of the snarls [s_begin, s_begin + s_count); the Fisher work list of the range lives at fisher_tab / fisher_idx
 // + s_begin (at most one table per snarl) with its own pair of counters
 cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const stoat_gpu_thresholds& thr,
@@ -782,6 +986,33 @@ cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const
     const unsigned fblocks = unsigned(want < uint64_t(num_sms) * per_sm ? want : uint64_t(num_sms) * per_sm);
     // STOAT_GPU_FISHER=exact: the quotient by __ddiv_rn, bit-identical to the reference's recurrence (15 % slower)
     const char* fv = std::getenv("STOAT_GPU_FISHER");
+    const bool serial_form = fv && (fv[0] == 'e' || fv[0] == 's');  // exact | serial: one step of the recurrence at a time
+    if (!serial_form) {
+        int per_sm_b = per_sm;
+        const unsigned bb = unsigned(want < uint64_t(num_sms) * per_sm_b ? want : uint64_t(num_sms) * per_sm_b);
+        // steps per block: 32 measured best on B200 (C3, stats_ms incl. K2a: 8 / 16 / 24 / 32 steps 0.59 / 0.47 / 0.41 / 0.39 ms,
+        // the serial form 0.76 ms; profiles/r2g_sweep_fisher_block.json); STOAT_GPU_FISHER=8|16 select the others
+        if (fv && fv[0] == '1' && fv[1] == '6')
+            fisher_block_kernel<16><<<bb, 128, 0, st>>>(fisher_tab + s_begin, fisher_idx + s_begin, fisher_counters, p_fisher,
+                                                        fisher_code);
+        else if (fv && fv[0] == '8')
+            fisher_block_kernel<8><<<bb, 128, 0, st>>>(fisher_tab + s_begin, fisher_idx + s_begin, fisher_counters, p_fisher,
+                                                       fisher_code);
+        else
+            fisher_block_kernel<32><<<bb, 128, 0, st>>>(fisher_tab + s_begin, fisher_idx + s_begin, fisher_counters, p_fisher,
+                                                        fisher_code);
+#ifdef STOAT_FISHER_DEBUG
+        {
+            unsigned long long h[4];
+            cudaStreamSynchronize(st);
+            cudaMemcpyFromSymbol(h, g_fisher_dbg, sizeof(h));
+            std::fprintf(stderr, "[fisher dbg] fallbacks %llu lane-blocks %llu tables %llu far-blocks %llu\n", h[0], h[1], h[2], h[3]);
+            unsigned long long z[4] = {0, 0, 0, 0};
+            cudaMemcpyToSymbol(g_fisher_dbg, z, sizeof(z));
+        }
+#endif
+        return cudaGetLastError();
+    }
     if (fv && fv[0] == 'e')
         fisher_exact_kernel<false><<<fblocks, 128, 0, st>>>(fisher_tab + s_begin, fisher_idx + s_begin, fisher_counters,
                                                             p_fisher, fisher_code);
