@@ -5,14 +5,21 @@
 //   shim_selftest golden <binary_table_vcf.golden.tsv> <binary_phenotype.tsv> <out.tsv>
 //       every golden row of the reference's expected output becomes a snarl whose paths are walked by exactly the
 //       haplotypes its GROUP_PATHS column counts; the written TSV must equal the golden file row for row.
+//   shim_selftest bench <n_snarls> <n_samples> <devices, e.g. 0 or 0,1> <out.json>
+//       a C3-shaped chunk (biallelic snarls, random matrix bytes) through GpuBinarySnarlAnalyzer: seconds per stage
+//       (flatten / matrix upload + repack / batch / format / write) and the same rows written the reference's way
+//       (an ostringstream per value, std::endl per row: src/utils.cpp:5-15, src/writer.cpp:23-35) for comparison.
 //   shim_selftest synth <seed> <n_snarls> <n_samples> <out_dir>
 //       random haplotype walks; writes binary.tsv / quantitative.tsv / quantitative_covar.tsv / eqtl.tsv and dumps the
 //       problem (matrix bytes, CSR, phenotypes, expression, gene windows) as raw arrays for the Python side to feed
 //       the oracle.
+#include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <iomanip>
 #include <iostream>
 #include <sstream>
 
@@ -192,6 +199,28 @@ int run_synth(uint64_t seed, size_t n_snarls, size_t n_samples, const std::strin
         a.analyze_and_write_chunk(snarls, "chr7", out);
     }
     {
+        // logistic regression (BinaryCovarSnarlAnalyzer); covariates passed and, as in the reference, without effect
+        GpuBinaryCovarSnarlAnalyzer a(matrix, is_case, covar, 3, 5, 0.05);
+        std::ofstream out(dir + "/binary_covar.tsv");
+        a.write_header(out);
+        a.analyze_and_write_chunk(snarls, "chr7", out);
+    }
+    {
+        // the same chunk cut over several contexts on several host threads (STOAT_SHIM_DEVICES, default "0,0,0": three
+        // contexts on GPU 0, so the path also runs on a one-GPU box); the rows must equal binary.tsv
+        std::vector<int> devs;
+        const char* e = std::getenv("STOAT_SHIM_DEVICES");
+        for (const std::string& d : split(e ? e : "0,0,0", ',')) devs.push_back(std::atoi(d.c_str()));
+        GpuBinarySnarlAnalyzer a(matrix, is_case, 3, 5, 0.05, devs);
+        std::ofstream out(dir + "/binary_multi.tsv");
+        a.write_header(out);
+        a.analyze_and_write_chunk(snarls, "chr7", out);
+        GpuQuantitativeSnarlAnalyzer q(matrix, y, no_covar, 3, 5, 0.05, devs);
+        std::ofstream outq(dir + "/quantitative_multi.tsv");
+        q.write_header(outq);
+        q.analyze_and_write_chunk(snarls, "chr7", outq);
+    }
+    {
         GpuEQTLSnarlAnalyzer a(matrix, eqtl_map, no_covar, window, 3, 5, 0.05);
         std::ofstream out(dir + "/eqtl.tsv");
         a.write_header(out);
@@ -229,11 +258,119 @@ int run_synth(uint64_t seed, size_t n_snarls, size_t n_samples, const std::strin
     return 0;
 }
 
+
+// ---- bench ---------------------------------------------------------------------------------------------------------------
+// EdgeBySampleMatrix keeps its storage protected; a derived class may fill it (what make_edge_matrix does bit by bit)
+struct FilledMatrix : EdgeBySampleMatrix {
+    FilledMatrix(const std::vector<std::string>& names, size_t rows, size_t cols) : EdgeBySampleMatrix(names, rows, cols) {}
+    void fill(Rng& rng, const std::vector<Edge_t>& edges) {
+        uint64_t* w = reinterpret_cast<uint64_t*>(matrix_1D.data());
+        for (size_t i = 0; i < matrix_1D.size() / 8; ++i) w[i] = rng.next();
+        row_header.reserve(edges.size());
+        for (size_t r = 0; r < edges.size(); ++r) row_header.emplace(edges[r], r);
+    }
+};
+
+double wall() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+std::string reference_set_precision(double value) {  // the reference's own way, src/utils.cpp:5-15
+    std::ostringstream oss;
+    if (std::abs(value) < 1e-1 && value != 0.0) oss << std::scientific << std::setprecision(4);
+    else oss << std::defaultfloat << std::setprecision(4);
+    oss << value;
+    return oss.str();
+}
+
+int run_bench(size_t n_snarls, size_t n_samples, const std::string& devices, const char* out_json) {
+    Rng rng{7};
+    const size_t H = 2 * n_samples;
+    std::vector<std::string> names(n_samples);
+    std::vector<Snarl_data_t> snarls(n_snarls);
+    std::vector<Edge_t> edges;
+    edges.reserve(4 * n_snarls);
+    size_t node = 10;
+    for (size_t s = 0; s < n_snarls; ++s) {
+        Snarl_data_t& sd = snarls[s];
+        const size_t a = node++, b = node++, c = node++, d = node++;
+        sd.snarl_ids = {d, a};
+        sd.start_positions = 100 * s + 17;
+        sd.end_positions = sd.start_positions + 1;
+        sd.depth = 1;
+        sd.type_variants = {"1", "1"};
+        sd.snarl_paths.push_back(make_path({a, b, d}));
+        sd.snarl_paths.push_back(make_path({a, c, d}));
+        edges.emplace_back(Node_traversal_t(a, false), Node_traversal_t(b, false));
+        edges.emplace_back(Node_traversal_t(b, false), Node_traversal_t(d, false));
+        edges.emplace_back(Node_traversal_t(a, false), Node_traversal_t(c, false));
+        edges.emplace_back(Node_traversal_t(c, false), Node_traversal_t(d, false));
+    }
+    FilledMatrix matrix(names, edges.size(), H);
+    matrix.fill(rng, edges);
+    std::vector<bool> is_case(n_samples);
+    for (size_t i = 0; i < n_samples; ++i) is_case[i] = i >= n_samples / 2;
+    std::vector<int> devs;
+    for (const std::string& d : split(devices, ',')) devs.push_back(std::atoi(d.c_str()));
+    GpuBinarySnarlAnalyzer an(matrix, is_case, 3, 5, 0.05, devs);
+    const std::string tsv = "/tmp/shim_bench.tsv";
+    GpuSnarlAnalyzer::StageSeconds st;
+    double chunk_s = 0;
+    size_t filtered = 0;
+    for (int rep = 0; rep < 2; ++rep) {  // the second pass is the measured one (allocations, page faults)
+        std::ofstream out(tsv);
+        an.write_header(out);
+        const double t0 = wall();
+        filtered = an.analyze_and_write_chunk(snarls, "chr1", out);
+        out.flush();
+        chunk_s = wall() - t0;
+        st = an.last_stage_seconds();
+    }
+    // the same rows the reference's way: set_precision through an ostringstream per value, std::endl per row
+    size_t n_rows = 0;
+    {
+        std::ifstream in(tsv);
+        std::string line;
+        while (std::getline(in, line)) ++n_rows;
+        n_rows -= 1;
+    }
+    std::vector<double> pf(n_rows), pc(n_rows);
+    for (size_t i = 0; i < n_rows; ++i) {
+        pf[i] = std::exp(-40.0 * rng.uniform());
+        pc[i] = std::exp(-40.0 * rng.uniform());
+    }
+    const double t1 = wall();
+    {
+        std::ofstream out("/tmp/shim_bench_reference_style.tsv");
+        for (size_t i = 0; i < n_rows; ++i) {
+            const Snarl_data_t& sd = snarls[i];
+            out << "chr1" << "\t" << sd.start_positions << "\t" << sd.end_positions << "\t"
+                << std::to_string(sd.snarl_ids.first) + "_" + std::to_string(sd.snarl_ids.second) << "\t"
+                << type_variants_string(sd) << "\t" << reference_set_precision(pf[i]) << "\t" << reference_set_precision(pc[i])
+                << "\t" << "1234:1250,1266:1250" << "\t" << sd.depth << std::endl;
+        }
+    }
+    const double ref_style_s = wall() - t1;
+    std::ofstream js(out_json);
+    js << "{\"workload\": \"" << n_snarls << " biallelic snarls x " << H << " haplotypes, binary, through GpuBinarySnarlAnalyzer\", "
+       << "\"devices\": \"" << devices << "\", \"rows_written\": " << n_rows << ", \"filtered\": " << filtered
+       << ", \"chunk_seconds\": " << chunk_s << ", \"stage_seconds\": {\"flatten\": " << st.flatten << ", \"set_matrix\": "
+       << st.set_matrix << ", \"phenotype\": " << st.phenotype << ", \"batch\": " << st.batch << ", \"format\": " << st.format
+       << ", \"write\": " << st.write << "}, \"path_tests_per_second\": " << double(2 * n_snarls) / chunk_s
+       << ", \"reference_style_writer_seconds\": " << ref_style_s
+       << ", \"reference_style_note\": \"the same number of rows with an ostringstream per value and std::endl per row "
+          "(src/utils.cpp:5-15, src/writer.cpp:23-35), one thread\"}\n";
+    std::printf("bench: %zu snarls, %zu rows, chunk %.3f s (flatten %.3f, set_matrix %.3f, batch %.3f, format %.3f, write %.3f); "
+                "reference-style writer %.3f s\n", n_snarls, n_rows, chunk_s, st.flatten, st.set_matrix, st.batch, st.format,
+                st.write, ref_style_s);
+    return 0;
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
     try {
         if (argc == 5 && std::strcmp(argv[1], "golden") == 0) return run_golden(argv[2], argv[3], argv[4]);
+        if (argc == 6 && std::strcmp(argv[1], "bench") == 0)
+            return run_bench(std::strtoull(argv[2], nullptr, 10), std::strtoull(argv[3], nullptr, 10), argv[4], argv[5]);
         if (argc == 6 && std::strcmp(argv[1], "synth") == 0)
             return run_synth(std::strtoull(argv[2], nullptr, 10), std::strtoull(argv[3], nullptr, 10),
                              std::strtoull(argv[4], nullptr, 10), argv[5]);

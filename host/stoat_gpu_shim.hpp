@@ -160,7 +160,10 @@ struct FlatPaths {
     std::vector<uint32_t> edge_row;
     stoat_gpu_paths view() const;
 };
-FlatPaths flatten_snarl_paths(const std::vector<Snarl_data_t>& snarls, const EdgeBySampleMatrix& edge_matrix);
+FlatPaths flatten_snarl_paths(const Snarl_data_t* snarls, size_t n_snarls, const EdgeBySampleMatrix& edge_matrix);
+inline FlatPaths flatten_snarl_paths(const std::vector<Snarl_data_t>& snarls, const EdgeBySampleMatrix& edge_matrix) {
+    return flatten_snarl_paths(snarls.data(), snarls.size(), edge_matrix);
+}
 
 // the reference's output strings
 std::string set_precision(double value, uint8_t code = STOAT_P_VALUE);                          // src/utils.cpp:5-15
@@ -168,12 +171,29 @@ std::string format_group_paths(const uint32_t* g0, const uint32_t* g1, size_t n)
 std::string type_variants_string(const Snarl_data_t& s);                                         // src/snarl_analyzer.cpp:363-370
 std::vector<size_t> found_gene_snarl(const std::vector<Qtl_data_t>& genes, size_t start, size_t end, size_t window);  // :471-491
 
-// Owner of one stoat_gpu_ctx; common state of the three analyzers (what SnarlAnalyzer holds by reference,
-// src/snarl_analyzer.hpp:75-92).  One instance per host thread and per GPU.
+// A column of values as the reference prints them, formatted on the device in one call (stoat_gpu_format_values):
+// text(i) is what set_precision(values[i], codes[i]) returns.  The rows of a chunk are assembled from such columns
+// into ONE buffer and written with one ostream::write — the reference formats every value through its own ostringstream
+// and flushes the file after every row (src/writer.cpp:34,49,85), which is what caps its OpenMP scaling.
+class TextColumn {
+public:
+    void format(stoat_gpu_ctx* ctx, const double* values, const uint8_t* codes, size_t n);
+    void append_to(std::string& row, size_t i) const { row.append(slots.data() + 16 * i, lengths[i]); }
+
+private:
+    std::vector<char> slots;
+    std::vector<uint8_t> lengths;
+};
+
+// Owner of the stoat_gpu_ctx handles; common state of the analyzers (what SnarlAnalyzer holds by reference,
+// src/snarl_analyzer.hpp:75-92).  With one device the chunk is one batch call.  With several (`devices`), the chunk's snarl
+// vector is cut into contiguous ranges balanced by path count, one host thread per device uploads the matrix, tests its
+// range and formats its rows, and the fragments are written in snarl order: the snarl-sharded mode of SURVEY §8e behind
+// the single-process C++ host (no collective; the reference's unit of parallelism is the snarl, :165-172).
 class GpuSnarlAnalyzer {
 public:
     GpuSnarlAnalyzer(const EdgeBySampleMatrix& edge_matrix, size_t min_individuals, size_t min_haplotypes,
-                     double maf_threshold, int device = 0);
+                     double maf_threshold, const std::vector<int>& devices);
     virtual ~GpuSnarlAnalyzer();
     GpuSnarlAnalyzer(const GpuSnarlAnalyzer&) = delete;
     GpuSnarlAnalyzer& operator=(const GpuSnarlAnalyzer&) = delete;
@@ -184,29 +204,64 @@ public:
     size_t analyze_and_write_chunk(const std::vector<Snarl_data_t>& snarls, const std::string& chr, std::ostream& outf);
     virtual void write_header(std::ostream& outf) const = 0;
     stoat_gpu_timing last_timing() const;
+    // wall-clock seconds of the last chunk's stages (slowest device): flatten, matrix upload + repack, phenotype,
+    // batch call (H2D CSR, kernels, D2H), formatting + row assembly, the ostream write
+    struct StageSeconds {
+        double flatten = 0, set_matrix = 0, phenotype = 0, batch = 0, format = 0, write = 0;
+    };
+    StageSeconds last_stage_seconds() const { return stages; }
+    size_t n_devices() const { return ctxs.size(); }
 
 protected:
-    virtual void upload_phenotype() = 0;
-    virtual size_t run(const std::vector<Snarl_data_t>& snarls, const FlatPaths& flat, const std::string& chr,
-                       std::ostream& outf) = 0;
-    void check(int rc, const char* what) const;  // throws std::runtime_error(last_error)
+    virtual void upload_phenotype(stoat_gpu_ctx* ctx) = 0;
+    // test snarls[0 .. n) on ctx and append their rows to `rows`; returns the number of filtered snarls
+    virtual size_t run(stoat_gpu_ctx* ctx, const Snarl_data_t* snarls, size_t n, const FlatPaths& flat, const std::string& chr,
+                       std::string& rows, StageSeconds& t) = 0;
+    static void check(stoat_gpu_ctx* ctx, int rc, const char* what);  // throws std::runtime_error(last_error)
 
     const EdgeBySampleMatrix& edge_matrix;
     stoat_gpu_thresholds thr;
-    stoat_gpu_ctx* ctx = nullptr;
+    std::vector<stoat_gpu_ctx*> ctxs;
+    StageSeconds stages;
 };
 
 // BinarySnarlAnalyzer (src/snarl_analyzer.cpp:358-390): chi2 + Fisher per snarl
 class GpuBinarySnarlAnalyzer : public GpuSnarlAnalyzer {
 public:
     GpuBinarySnarlAnalyzer(const EdgeBySampleMatrix& edge_matrix, const std::vector<bool>& binary_phenotype,
-                           size_t min_individuals, size_t min_haplotypes, double maf_threshold, int device = 0);
+                           size_t min_individuals, size_t min_haplotypes, double maf_threshold, int device = 0)
+        : GpuBinarySnarlAnalyzer(edge_matrix, binary_phenotype, min_individuals, min_haplotypes, maf_threshold,
+                                 std::vector<int>{device}) {}
+    GpuBinarySnarlAnalyzer(const EdgeBySampleMatrix& edge_matrix, const std::vector<bool>& binary_phenotype,
+                           size_t min_individuals, size_t min_haplotypes, double maf_threshold,
+                           const std::vector<int>& devices);
     void write_header(std::ostream& outf) const override;  // src/writer.cpp:7-9
 
 protected:
-    void upload_phenotype() override;
-    size_t run(const std::vector<Snarl_data_t>&, const FlatPaths&, const std::string&, std::ostream&) override;
+    void upload_phenotype(stoat_gpu_ctx* ctx) override;
+    size_t run(stoat_gpu_ctx*, const Snarl_data_t*, size_t, const FlatPaths&, const std::string&, std::string&,
+               StageSeconds&) override;
     const std::vector<bool>& binary_phenotype;  // false = control (g0), true = case (g1), src/arg_parser.cpp:20-95
+};
+
+// BinaryCovarSnarlAnalyzer (src/snarl_analyzer.cpp:392-428): logistic regression of the binary phenotype on path dosage.
+// The reference never puts its covariates into the design (src/stats_test.cpp:59-62 shadows its own variables);
+// use_covariates = false reproduces that, true appends them (stoat_gpu_binary_covar_batch).
+class GpuBinaryCovarSnarlAnalyzer : public GpuSnarlAnalyzer {
+public:
+    GpuBinaryCovarSnarlAnalyzer(const EdgeBySampleMatrix& edge_matrix, const std::vector<bool>& binary_phenotype,
+                                const std::vector<std::vector<double>>& covariate, size_t min_individuals,
+                                size_t min_haplotypes, double maf_threshold, const std::vector<int>& devices = {0},
+                                bool use_covariates = false);
+    void write_header(std::ostream& outf) const override;  // src/writer.cpp:11-13
+
+protected:
+    void upload_phenotype(stoat_gpu_ctx* ctx) override;
+    size_t run(stoat_gpu_ctx*, const Snarl_data_t*, size_t, const FlatPaths&, const std::string&, std::string&,
+               StageSeconds&) override;
+    const std::vector<bool>& binary_phenotype;
+    const std::vector<std::vector<double>>& covariate;
+    bool use_covariates;
 };
 
 // QuantitativeSnarlAnalyzer (src/snarl_analyzer.cpp:431-467): OLS of the phenotype on path dosage (+ covariates)
@@ -214,12 +269,18 @@ class GpuQuantitativeSnarlAnalyzer : public GpuSnarlAnalyzer {
 public:
     GpuQuantitativeSnarlAnalyzer(const EdgeBySampleMatrix& edge_matrix, const std::vector<double>& quantitative_phenotype,
                                  const std::vector<std::vector<double>>& covariate, size_t min_individuals,
-                                 size_t min_haplotypes, double maf_threshold, int device = 0);
+                                 size_t min_haplotypes, double maf_threshold, int device = 0)
+        : GpuQuantitativeSnarlAnalyzer(edge_matrix, quantitative_phenotype, covariate, min_individuals, min_haplotypes,
+                                       maf_threshold, std::vector<int>{device}) {}
+    GpuQuantitativeSnarlAnalyzer(const EdgeBySampleMatrix& edge_matrix, const std::vector<double>& quantitative_phenotype,
+                                 const std::vector<std::vector<double>>& covariate, size_t min_individuals,
+                                 size_t min_haplotypes, double maf_threshold, const std::vector<int>& devices);
     void write_header(std::ostream& outf) const override;  // src/writer.cpp:15-17
 
 protected:
-    void upload_phenotype() override;
-    size_t run(const std::vector<Snarl_data_t>&, const FlatPaths&, const std::string&, std::ostream&) override;
+    void upload_phenotype(stoat_gpu_ctx* ctx) override;
+    size_t run(stoat_gpu_ctx*, const Snarl_data_t*, size_t, const FlatPaths&, const std::string&, std::string&,
+               StageSeconds&) override;
     const std::vector<double>& quantitative_phenotype;
     const std::vector<std::vector<double>>& covariate;  // [sample][covariate]; empty = none
 };
@@ -234,8 +295,9 @@ public:
     void write_header(std::ostream& outf) const override;  // src/writer.cpp:19-21
 
 protected:
-    void upload_phenotype() override;
-    size_t run(const std::vector<Snarl_data_t>&, const FlatPaths&, const std::string&, std::ostream&) override;
+    void upload_phenotype(stoat_gpu_ctx* ctx) override;
+    size_t run(stoat_gpu_ctx*, const Snarl_data_t*, size_t, const FlatPaths&, const std::string&, std::string&,
+               StageSeconds&) override;
     const std::unordered_map<std::string, std::vector<Qtl_data_t>>& eqtl_map;
     const std::vector<std::vector<double>>& covariate;
     size_t windows_gene_threshold;

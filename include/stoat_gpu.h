@@ -302,6 +302,14 @@ STOAT_GPU_API uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx);
 /* read back one repacked row (tests of K0)                                                  */
 STOAT_GPU_API int stoat_gpu_read_row(stoat_gpu_ctx* ctx, uint64_t row, uint8_t* out, uint64_t out_bytes);
 
+/* ---- the value columns of the TSV rows as text ------------------------------------------------
+ * The reference formats every value through an ostringstream (stoat::set_precision, src/utils.cpp:5-15) and flushes the
+ * file per row (src/writer.cpp:34,49,85).  This call formats a whole column on the device: slot i = slots + 16 * i holds
+ * the text of (values[i], codes[i]) — exactly what stoat_gpu_format_value returns for it — NUL padded, lengths[i] its
+ * length.  codes may be NULL (all STOAT_P_VALUE).  Host buffers.                                                    */
+STOAT_GPU_API int stoat_gpu_format_values(stoat_gpu_ctx* ctx, const double* values, const uint8_t* codes, uint64_t n,
+                                          char* slots, uint8_t* lengths);
+
 /* ---- host formatting helper (pure C, no device): reference strings -------------------- */
 /* set_precision (src/utils.cpp:5-15) + the literal strings selected by `code`.  Returns the
  * number of characters written (excluding the NUL), or -1 if buf is too small.             */

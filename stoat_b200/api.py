@@ -135,6 +135,18 @@ class Context:
         self._check(self._lib.stoat_gpu_bh_adjust(self._ctx, _ptr(a), a.size, _ptr(out)))
         return out
 
+    def format_values(self, values, codes=None) -> list[str]:
+        """The value column as the reference prints it (set_precision + the literal strings of the codes), formatted on the
+        device (include/stoat_gpu.h: stoat_gpu_format_values)."""
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        c = None if codes is None else np.ascontiguousarray(codes, dtype=np.uint8)
+        slots = np.zeros((v.size, 16), np.uint8)
+        lens = np.zeros(v.size, np.uint8)
+        self._check(self._lib.stoat_gpu_format_values(self._ctx, _ptr(v), None if c is None else _ptr(c), v.size, _ptr(slots),
+                                                      _ptr(lens)))
+        raw = slots.tobytes()
+        return [raw[16 * i:16 * i + int(lens[i])].decode() for i in range(v.size)]
+
     @property
     def row_pitch(self) -> int:
         return int(self._lib.stoat_gpu_row_pitch(self._ctx))

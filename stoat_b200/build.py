@@ -54,7 +54,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(out)
         if p.returncode:
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
-    link = [nvcc(), "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"]
+    link = [nvcc(), "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart", "-lpthread"]
     subprocess.check_call(link)
     return LIB
 
@@ -70,7 +70,7 @@ def build_host(force: bool = False) -> str:
     if not force and os.path.exists(SHIM_TEST) and all(os.path.getmtime(d) <= os.path.getmtime(SHIM_TEST) for d in deps):
         return SHIM_TEST
     cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-Wextra"] + srcs + ["-o", SHIM_TEST, "-L" + HERE, "-lstoat_gpu",
-                                                                      "-Wl,-rpath," + HERE, "-Wl,-rpath,$ORIGIN/../stoat_b200"]
+                                                                      "-Wl,-rpath," + HERE, "-Wl,-rpath,$ORIGIN/../stoat_b200", "-pthread"]
     subprocess.check_call(cmd)
     return SHIM_TEST
 

@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <thread>
 #include <vector>
 
 #include "ctx.hpp"
@@ -65,6 +66,28 @@ struct LogitState {  // logistic regression (binary trait with covariates): its 
 
 }  // namespace
 
+constexpr int kHostRing = 3;
+constexpr uint64_t kHostRingBytes = 64ull << 20;
+// memcpy by a few threads: one core moves ~10 GB/s, the PCIe link 55
+static void parallel_memcpy(uint8_t* dst, const uint8_t* src, uint64_t n) {
+    static const unsigned n_threads = [] {
+        unsigned hw = std::thread::hardware_concurrency();
+        if (const char* e = std::getenv("STOAT_GPU_UPLOAD_THREADS")) hw = unsigned(std::max(1, std::atoi(e))) * 2;
+        return std::max(1u, std::min(6u, hw / 2));
+    }();
+    if (n_threads == 1 || n < (4ull << 20)) {
+        std::memcpy(dst, src, n);
+        return;
+    }
+    const uint64_t per = ((n + n_threads - 1) / n_threads + 4095) & ~uint64_t(4095);
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < n_threads; ++t) {
+        const uint64_t a = std::min(n, per * t), b = std::min(n, per * (t + 1));
+        if (b > a) th.emplace_back([=] { std::memcpy(dst + a, src + a, b - a); });
+    }
+    std::memcpy(dst, src, std::min(n, per));
+    for (std::thread& t : th) t.join();
+}
 constexpr int kMaxRunChunks = 8;  // chunks of an overlapped binary run (stoat_gpu_binary_run_staged)
 // Chunks of the binary run by default.  Measured on B200 at C3 with the 64-register count pass and the branch-free Fisher loop
 // (profiles/r2a_sweep_c3.json): 1 chunk 1.57 ms, 2 / 4 / 8 chunks 1.80 / 1.90 / 2.10 ms (4 chunks with 8 Fisher blocks per
@@ -83,6 +106,10 @@ struct CtxExtra {
     uint32_t readback[2] = {0, 0};
     uint32_t fisher_readback[2 * kMaxRunChunks] = {};
     DevBuf bh;  // scratch of stoat_gpu_bh_adjust
+    void* host_ring[kHostRing] = {};  // pinned staging of a pageable matrix upload (set_matrix_common)
+    cudaEvent_t host_ring_free[kHostRing] = {};
+    DevBuf fmt;  // scratch of stoat_gpu_format_values
+    std::vector<uint8_t> fmt_unsure;
     cudaEvent_t chunk_done[kMaxRunChunks] = {};
     // Events of the last kRunRing staged runs: [0] start, [1] end of the count / moments pass, [2] start and [3] end of the
     // statistics.  A run only enqueues work; its timing (and the counters that come back with it) is read when somebody asks
@@ -239,6 +266,11 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     x->q.tail_df.release();
     x->q.tail_x.release();
     x->bh.release();
+    x->fmt.release();
+    for (int i = 0; i < kHostRing; ++i) {
+        if (x->host_ring[i]) cudaFreeHost(x->host_ring[i]);
+        if (x->host_ring_free[i]) cudaEventDestroy(x->host_ring_free[i]);
+    }
     for (DevBuf* b : {&x->lg.counts, &x->lg.list, &x->lg.n_list, &x->lg.allele, &x->lg.filtered, &x->lg.n_used, &x->lg.p,
                       &x->lg.beta, &x->lg.se, &x->lg.code})
         b->release();
@@ -284,8 +316,26 @@ static int set_matrix_common(stoat_gpu_ctx* ctx, const uint8_t* bits, bool on_de
         // (copy stream) overlaps the repack of chunk k (main stream), and the staging never holds more than two chunks.
         // A chunk starts at a multiple of 128 rows, so its first bit sits on a 16-byte boundary of the bit stream and the
         // repack kernel can address the staging buffer as if it were the whole matrix (base pointer shifted back).
-        uint64_t chunk_bytes = 256ull << 20;
+        // A pageable source (the reference's std::vector<uint8_t>, src/matrix.hpp:53) would make every cudaMemcpyAsync a
+        // synchronous, single-threaded staged copy (measured 11 GB/s on the B200 box against 55 GB/s from pinned memory):
+        // such a source goes through a ring of three pinned 64 MB buffers that a few host threads fill while the previous
+        // buffer is on the wire.
+        bool pageable = false;
+        {
+            cudaPointerAttributes at{};
+            if (n_rows && cudaPointerGetAttributes(&at, bits) == cudaSuccess) pageable = at.type == cudaMemoryTypeUnregistered;
+            (void)cudaGetLastError();
+            if (const char* e = std::getenv("STOAT_GPU_UPLOAD_RING")) pageable = pageable && std::atoi(e) != 0;
+        }
+        uint64_t chunk_bytes = pageable ? kHostRingBytes : (256ull << 20);
         if (const char* e = std::getenv("STOAT_GPU_UPLOAD_CHUNK_MB")) chunk_bytes = std::max<uint64_t>(1, uint64_t(std::atoll(e))) << 20;
+        if (pageable) {
+            chunk_bytes = std::min<uint64_t>(chunk_bytes, kHostRingBytes);
+            for (int i = 0; i < kHostRing; ++i) {
+                if (!x->host_ring[i]) CK(cudaHostAlloc(&x->host_ring[i], kHostRingBytes + 64, cudaHostAllocDefault));
+                if (!x->host_ring_free[i]) CK(cudaEventCreateWithFlags(&x->host_ring_free[i], cudaEventDisableTiming));
+            }
+        }
         uint64_t rows_per = std::max<uint64_t>(128, (chunk_bytes * 8 / n_cols) / 128 * 128);
         if (const char* e = std::getenv("STOAT_GPU_UPLOAD_CHUNK_ROWS"))  // tests: many chunks of a small matrix
             rows_per = std::max<uint64_t>(128, (uint64_t(std::atoll(e)) + 127) / 128 * 128);
@@ -299,7 +349,15 @@ static int set_matrix_common(stoat_gpu_ctx* ctx, const uint8_t* bits, bool on_de
             if (k < 2) CK(st.reserve(std::min(raw_bytes, (rows_per * n_cols + 7) / 8) + 64));
             if (k >= 2) CK(cudaStreamWaitEvent(ctx->copy_stream, x->chunk_done[k & 1], 0));  // the buffer's previous repack
             else CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev[0], 0));
-            CK(cudaMemcpyAsync(st.p, bits + b0, b1 - b0, cudaMemcpyHostToDevice, ctx->copy_stream));
+            const uint8_t* src = bits + b0;
+            if (pageable) {
+                uint8_t* pin = static_cast<uint8_t*>(x->host_ring[k % kHostRing]);
+                if (k >= uint64_t(kHostRing)) CK(cudaEventSynchronize(x->host_ring_free[k % kHostRing]));  // its last copy left
+                parallel_memcpy(pin, src, b1 - b0);
+                src = pin;
+            }
+            CK(cudaMemcpyAsync(st.p, src, b1 - b0, cudaMemcpyHostToDevice, ctx->copy_stream));
+            if (pageable) CK(cudaEventRecord(x->host_ring_free[k % kHostRing], ctx->copy_stream));
             CK(cudaEventRecord(x->chunk_done[2 + (k & 1)], ctx->copy_stream));
             CK(cudaStreamWaitEvent(ctx->stream, x->chunk_done[2 + (k & 1)], 0));
             CK(launch_repack_rows(st.as<uint8_t>() - b0, raw_bytes, r0, r1, n_cols, pitch, ctx->rows.as<uint8_t>(),
@@ -1317,6 +1375,42 @@ int stoat_gpu_eqtl_dense_summary(stoat_gpu_ctx* ctx, const stoat_gpu_paths* path
     if ((rc = eqtl_prepare_expression(ctx, genes->n_genes))) return rc;
     if ((rc = stoat_gpu_eqtl_dense_run_staged(ctx, thr, p_threshold))) return rc;
     return stoat_gpu_eqtl_summary_fetch(ctx, out);
+}
+
+// Text of a value column — stoat::set_precision (src/utils.cpp:5-15) and the literal strings of `codes`, formatted on the
+// device (kernels_post.cu); the few values whose decimal rounding FP64 cannot decide are redone here with the C library,
+// so slot i always holds exactly what stoat_gpu_format_value(values[i], codes[i]) would write.
+int stoat_gpu_format_values(stoat_gpu_ctx* ctx, const double* values, const uint8_t* codes, uint64_t n, char* slots,
+                            uint8_t* lengths) {
+    if (!ctx) return STOAT_GPU_ERR_ARG;
+    if (n == 0) return STOAT_GPU_OK;
+    if (!values || !slots || !lengths) return fail(ctx, STOAT_GPU_ERR_ARG, "format_values: NULL argument");
+    CK(cudaSetDevice(ctx->device));
+    CtxExtra* x = extra_of(ctx);
+    // scratch: slots [n][16] (16-byte stores) | values [n] f64 | codes [n] | lengths [n] | unsure [n]
+    const size_t off_slots = 0, off_values = size_t(n) * 16, off_codes = off_values + size_t(n) * 8, off_len = off_codes + n,
+                 off_unsure = off_len + n;
+    CK(x->fmt.reserve(off_unsure + n + 64));
+    uint8_t* base = x->fmt.as<uint8_t>();
+    CK(cudaMemcpyAsync(base + off_values, values, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    if (codes) CK(cudaMemcpyAsync(base + off_codes, codes, n, cudaMemcpyHostToDevice, ctx->stream));
+    CK(launch_format_values(reinterpret_cast<const double*>(base + off_values), codes ? base + off_codes : nullptr, n,
+                            reinterpret_cast<char*>(base + off_slots), base + off_len, base + off_unsure, ctx->stream));
+    x->fmt_unsure.resize(n);
+    CK(cudaMemcpyAsync(slots, base + off_slots, n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(lengths, base + off_len, n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(x->fmt_unsure.data(), base + off_unsure, n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (uint64_t i = 0; i < n; ++i)
+        if (x->fmt_unsure[i]) {
+            char buf[32];
+            const int l = stoat_gpu_format_value(values[i], codes ? codes[i] : uint8_t(STOAT_P_VALUE), buf, sizeof buf);
+            if (l < 0 || l > 15) return fail(ctx, STOAT_GPU_ERR_ARG, "format_values: value does not fit a slot");
+            std::memset(slots + i * 16, 0, 16);
+            std::memcpy(slots + i * 16, buf, size_t(l));
+            lengths[i] = uint8_t(l);
+        }
+    return STOAT_GPU_OK;
 }
 
 // set_precision (src/utils.cpp:5-15): iostream scientific / defaultfloat at precision 4 are "%.4e" / "%.4g"

@@ -103,6 +103,9 @@ cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const
 size_t bh_temp_bytes(uint64_t n);
 cudaError_t launch_bh_adjust(const double* p, uint64_t n, double* out, uint64_t* keys_sorted, uint32_t* idx_in,
                              uint32_t* idx_sorted, double* a, double* b, void* temp, size_t temp_bytes, cudaStream_t st);
+// text of the value columns (kernels_post.cu): slots [n][16] NUL padded, len [n], unsure [n] (1: format on the host)
+cudaError_t launch_format_values(const double* v, const uint8_t* code, uint64_t n, char* slots, uint8_t* len,
+                                 uint8_t* unsure, cudaStream_t st);
 // quantitative
 struct QuantMoments;  // kernels_quant.cu
 struct QuantOut {

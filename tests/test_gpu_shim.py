@@ -116,3 +116,45 @@ def test_synthetic_chunk_all_analyzers(selftest, oracle, tmp_path):
     assert len(got) == len(want) > 20
     for g, w in zip(got, want):
         assert g[:6] == w[:6] and g[10:] == w[10:] and all(_close(a, b) for a, b in zip(g[6:10], w[6:10])), (g, w)
+
+    # logistic regression (GpuBinaryCovarSnarlAnalyzer): covariates passed, without effect, as in the reference
+    ref = oracle.binary_covar_batch(bits, n_cols, is_case, P, covar=covar)
+    want = []
+    for s in range(S):
+        if ref["filtered"][s]:
+            continue
+        ap = ",".join(str(v) for v in ref["allele_paths"][spo[s]:spo[s + 1]])
+        vals = ["NA"] * 3 if ref["code"][s] == 1 else [fmt(ref[k][s], 0) for k in ("p_value", "beta", "se")]
+        want.append(prefix(s) + vals + [ap, info[s][4]])
+    got = _rows(os.path.join(d, "binary_covar.tsv"))
+    assert len(got) == len(want) > 20
+    for g, w in zip(got, want):
+        assert g[:5] == w[:5] and g[8:] == w[8:] and all(_close(a, b) for a, b in zip(g[5:8], w[5:8])), (g, w)
+
+    # the chunk cut over three contexts on three host threads: the same file
+    assert open(os.path.join(d, "binary_multi.tsv")).read() == open(os.path.join(d, "binary.tsv")).read()
+    assert open(os.path.join(d, "quantitative_multi.tsv")).read() == open(os.path.join(d, "quantitative.tsv")).read()
+
+
+def test_device_formatted_columns_equal_the_c_library(gpu_ctx):
+    """stoat_gpu_format_values (device) against stoat_gpu_format_value (snprintf "%.4e" / "%.4g", the reference's
+    set_precision): every string identical, over magnitudes from denormals to 1e308, exact decimal ties and the codes."""
+    from stoat_b200 import format_value
+
+    rng = np.random.default_rng(3)
+    v = np.concatenate([
+        10.0 ** rng.uniform(-320, 300, 200000) * rng.choice([-1.0, 1.0], 200000, p=[0.2, 0.8]),
+        rng.uniform(0, 1, 100000), rng.uniform(0.09, 0.11, 20000), rng.normal(size=50000) * 100,
+        np.round(rng.uniform(0, 1e5, 20000)),                       # integers: "%g" drops the zeros, switches at 1e4
+        np.array([0.0, -0.0, 1.0, 0.1, 0.09999999999999999, 0.1 - 1e-17, 9.9995e-5, 9.99949999e-5, 0.099995, 0.99995,
+                  9999.5, 9999.4999, 99995.0, 1e-300, 5e-324, 1.7976931348623157e308, np.inf, -np.inf, np.nan,
+                  0.5, 0.25, 0.125, 0.0625, 0.03125, 0.015625, 1.00005, 1.00015, 123450.0, 1234.5, 12.345, 1.2345e-3]),
+        (np.arange(1, 20001) * 2 + 1) / 2.0 * 1e-4,                 # k + 0.5 in the 5th digit: rounding boundaries
+    ])
+    codes = np.zeros(v.size, np.uint8)
+    codes[:40] = np.tile(np.array([0, 1, 2, 3, 4], np.uint8), 8)
+    got = gpu_ctx.format_values(v, codes)
+    bad = [(float(x), int(c), g, format_value(float(x), int(c))) for x, c, g in zip(v, codes, got)
+           if g != format_value(float(x), int(c))]
+    assert not bad, f"{len(bad)} of {v.size} strings differ, first: {bad[:5]}"
+    assert gpu_ctx.format_values(np.array([0.0123456]), None) == ["1.2346e-02"]
