@@ -56,7 +56,7 @@ def parse_args(argv=None):
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c3", choices=sorted(CONFIGS))
-    ap.add_argument("--sharding", default="snarl", choices=["snarl", "sample"])
+    ap.add_argument("--sharding", default="snarl", choices=["snarl", "sample", "gene"])
     ap.add_argument("--snarls", type=int, default=0, help="snarls per GPU (default: the config's)")
     ap.add_argument("--samples", type=int, default=0, help="samples (haplotypes = 2x; default: the config's)")
     ap.add_argument("--seed", type=int, default=42, help="generator seed of rank 0 (rank r draws seed + r)")

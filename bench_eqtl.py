@@ -27,7 +27,10 @@ def config_dict(args, n_gpus):
         "workload": f"C4 synthetic {args.snarls} biallelic snarls x {args.samples} samples x {args.genes} genes, "
                     f"dense eQTL scan (one OLS per pair), per GPU",
         "snarls_per_gpu": args.snarls, "samples": args.samples, "genes": args.genes,
-        "sharding": "snarl-sharded, no collective" if n_gpus > 1 else "single GPU",
+        "sharding": ("single GPU" if n_gpus <= 1 else
+                     f"gene-sharded: {n_gpus} ranks scan the same snarls against {args.genes} / {n_gpus} genes each, per-snarl "
+                     f"summaries merged by one all-reduce per step" if getattr(args, "sharding", "snarl") == "gene" else
+                     "snarl-sharded, no collective"),
         "l2": "the expression matrix (0.8 GB) and the dosage codes (0.25 GB) exceed the 126 MB L2; gene groups of ~48 MB "
               "are L2 resident by design, every step streams the rest from HBM, no flush needed",
         "p_threshold": args.p_threshold, "thresholds": {"min_individuals": 3, "min_haplotypes": 5, "maf": 0.05},
@@ -160,22 +163,39 @@ def dgemm_peak_tflops(torch, dev, n=8192, reps=5):
     return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
-def parity_spot_check(ctx_summary, d, expr_dev, args, n_check, n_threads):
-    """The first `n_check` snarls of the TIMED scan x every gene through the CPU oracle (one OLS per pair, as the
-    reference), against the device's per-snarl summary: min p (1e-9 relative), its gene, the count below the threshold."""
+def parity_spot_check(ctx_summary, d, expr_dev, args, n_check, n_threads, gene0=0):
+    """`n_check` snarls SAMPLED at a fixed stride over the timed scan x every gene through the CPU oracle (one OLS per pair,
+    as the reference: n_check x G = 10^6 rows at C4), against the device's per-snarl summary: min p (1e-9
+    relative), its gene, the count below the threshold."""
     import time
 
     import oracle
 
     st = d["structure"]
-    n = min(n_check, d["paths"].n_snarls)
-    r1 = int(st.row0[n - 1] + st.n_rows_of[n - 1])
+    S = d["paths"].n_snarls
+    n = min(n_check, S)
+    sel = np.unique(np.linspace(0, S - 1, n).astype(np.int64))
+    n = sel.size
     row_bytes = d["n_cols"] // 8
-    bits = d["bits_dev"][: r1 * row_bytes].cpu().numpy()
-    expr = expr_dev.cpu().numpy()
     p = d["paths"]
-    P1, E1 = int(p.snarl_path_off[n]), int(p.path_edge_off[int(p.snarl_path_off[n])])
-    sub = oracle.Paths(p.snarl_path_off[: n + 1].copy(), p.path_edge_off[: P1 + 1].copy(), p.edge_row[:E1].copy())
+    spo_all, peo_all = np.asarray(p.snarl_path_off, np.int64), np.asarray(p.path_edge_off, np.int64)
+    torch = __import__("torch")
+    # the sampled snarls' rows (private and contiguous per snarl in this generator), compacted; edge rows renumbered
+    row_idx, spo, peo, er, base = [], [0], [0], [], 0
+    for s_ in sel:
+        r0, nr = int(st.row0[s_]), int(st.n_rows_of[s_])
+        row_idx.append(np.arange(r0, r0 + nr))
+        for pth in range(spo_all[s_], spo_all[s_ + 1]):
+            rows = np.asarray(p.edge_row[peo_all[pth]:peo_all[pth + 1]], np.int64)
+            er.extend(np.where(rows == 0xFFFFFFFF, 0xFFFFFFFF, rows - r0 + base).tolist())
+            peo.append(len(er))
+        spo.append(len(peo) - 1)
+        base += nr
+    row_idx = torch.as_tensor(np.concatenate(row_idx), device=d["bits_dev"].device)
+    bits = d["bits_dev"].view(-1, row_bytes)[row_idx].contiguous().cpu().numpy().reshape(-1)
+    expr = expr_dev.cpu().numpy()
+    sub = oracle.Paths(np.array(spo, np.uint64), np.array(peo, np.uint64), np.array(er, np.uint32))
+    ctx_summary = {k: np.asarray(v)[sel] for k, v in ctx_summary.items()}
     t0 = time.time()
     ref = oracle.eqtl_batch(bits, d["n_cols"], expr, sub, n_threads=n_threads)
     G, thr, rtol = expr.shape[0], args.p_threshold, 1e-9
@@ -183,7 +203,7 @@ def parity_spot_check(ctx_summary, d, expr_dev, args, n_check, n_threads):
     ok = ref["code"].reshape(n, G) == 0
     bad = []
     for s in range(n):
-        mp, ag, nb = ctx_summary["min_p"][s], int(ctx_summary["argmin_gene"][s]), int(ctx_summary["n_below"][s])
+        mp, ag, nb = ctx_summary["min_p"][s], int(ctx_summary["argmin_gene"][s]) - gene0, int(ctx_summary["n_below"][s])
         if ref["filtered"][s] or not ok[s].any():
             if not (np.isnan(mp) and nb == 0):
                 bad.append((s, "filtered"))
@@ -199,6 +219,7 @@ def parity_spot_check(ctx_summary, d, expr_dev, args, n_check, n_threads):
         elif not lo <= nb <= hi:
             bad.append((s, "n_below", nb, lo, hi))
     out = {"checked_snarls": int(n), "checked_pair_tests": int(n * G), "mismatches": len(bad),
+           "sampling": "snarls at a fixed stride over the whole timed batch, every gene",
            "against": "oracle port (oracle/stoat_oracle.cpp), one OLS per (snarl, gene) on the timed matrix's own rows and "
                       "the timed expression matrix; min p 1e-9 relative, its gene, count below the threshold",
            "seconds": round(time.time() - t0, 2)}
@@ -217,19 +238,48 @@ def measure(args, env, ClockSampler, n_threads, with_clocks=True):
     barrier = env.barrier
 
     S, n, G = args.snarls, args.samples, args.genes
-    d = synth.torch_dataset(S, n, dev, seed=42 + rank, **BIALLELIC)
+    # snarl-sharded (default): every rank its own snarl shard against every gene (weak scaling, no exchange).
+    # gene-sharded (--sharding gene, SURVEY §8e "split genes (columns of Y) across GPUs"): every rank the SAME snarls
+    # against G / world genes (strong scaling); the per-snarl summaries are merged with one small all-reduce per step.
+    gene_sharded = getattr(args, "sharding", "snarl") == "gene" and world > 1
+    d = synth.torch_dataset(S, n, dev, seed=42 + (0 if gene_sharded else rank), **BIALLELIC)
     gen = torch.Generator(device=dev)
     gen.manual_seed(7)
     base = torch.rand((G, 1), device=dev, generator=gen, dtype=torch.float64) * 8
     expr = base * (1 + (torch.rand((G, n), device=dev, generator=gen, dtype=torch.float64) * 2 - 1))
+    gene0 = 0
+    if gene_sharded:
+        if G % world:
+            raise SystemExit("bench.py --trait eqtl --sharding gene: the gene count must be a multiple of the GPU count")
+        per = (G + world - 1) // world
+        gene0 = min(G, rank * per)
+        expr = expr[gene0:min(G, gene0 + per)].contiguous()
+    G_local = expr.shape[0]
     # 10 % of the genes depend on a snarl's dosage (simulate_test_dataset.py:75-88): add the alt-path dosage of snarl g
     peak = dgemm_peak_tflops(torch, dev) if rank == 0 else None
     ctx = stoat_b200.Context(local)
     ctx.set_matrix_dev(d["bits_dev"].data_ptr(), d["n_rows"], d["n_cols"])
     ctx.stage_paths(d["paths"])
-    ctx.set_expression_dev(expr.data_ptr(), G)
+    ctx.set_expression_dev(expr.data_ptr(), G_local)
     stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
-    run_scan = lambda: ctx.eqtl_dense_run_staged(p_threshold=args.p_threshold)  # noqa: E731
+    merged = {}
+
+    def run_scan():
+        ctx.eqtl_dense_run_staged(p_threshold=args.p_threshold)
+        if gene_sharded:
+            # merge of the per-snarl summaries: min p (and whose gene it is) and the count, S x 16 bytes per rank
+            sm = ctx.eqtl_summary_fetch()
+            mp = torch.as_tensor(np.nan_to_num(sm["min_p"], nan=np.inf), device=dev)
+            ag = torch.as_tensor(sm["argmin_gene"].astype(np.int64) + gene0, device=dev)
+            nb = torch.as_tensor(sm["n_below"].astype(np.int64), device=dev)
+            best = mp.clone()
+            dist.all_reduce(best, op=dist.ReduceOp.MIN)
+            cand = torch.where(mp == best, ag, torch.full_like(ag, 1 << 40))
+            dist.all_reduce(cand, op=dist.ReduceOp.MIN)  # ties: the smallest gene index, as a single scan would report
+            dist.all_reduce(nb, op=dist.ReduceOp.SUM)
+            merged["min_p"] = torch.where(torch.isinf(best), torch.full_like(best, float("nan")), best).cpu().numpy()
+            merged["argmin_gene"] = cand.cpu().numpy()
+            merged["n_below"] = nb.cpu().numpy()
     for _ in range(max(args.warmup, 3)):
         run_scan()
     barrier()
@@ -255,15 +305,23 @@ def measure(args, env, ClockSampler, n_threads, with_clocks=True):
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         dist.all_reduce(lsum, op=dist.ReduceOp.SUM)
     elapsed_ms = float(tmax.item())
-    value = world * S * G * args.steps / (elapsed_ms * 1e-3)
+    value = (1 if gene_sharded else world) * S * G * args.steps / (elapsed_ms * 1e-3)
     summary = ctx.eqtl_summary_fetch()
     n_dense = int(S - n_general - int(np.isnan(summary["min_p"]).sum()))
     parity = None
-    if rank == 0 and not getattr(args, "no_parity", False):
-        parity = parity_spot_check(summary, d, expr, args, 8, n_threads)
+    if not getattr(args, "no_parity", False):
+        if gene_sharded:
+            # the MERGED summary against the oracle over every gene: gather the ranks' expression slices on rank 0
+            parts = [torch.empty_like(expr) for _ in range(world)]
+            dist.all_gather(parts, expr)
+            if rank == 0:
+                parity = parity_spot_check(merged, d, torch.cat(parts, dim=0), args, 50, n_threads)
+            del parts
+        elif rank == 0:
+            parity = parity_spot_check(summary, d, expr, args, 50, n_threads)
 
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and not gene_sharded:
         host_bits = torch.empty(d["bits_dev"].numel(), dtype=torch.uint8, pin_memory=True)
         host_bits.copy_(d["bits_dev"])
         host_expr = torch.empty((G, n), dtype=torch.float64, pin_memory=True)
@@ -298,7 +356,7 @@ def measure(args, env, ClockSampler, n_threads, with_clocks=True):
     line = None
     if rank == 0:
         k_ms = float(np.mean(e1_ms))
-        flops = 2.0 * n * n_dense * G
+        flops = 2.0 * n * n_dense * G_local
         achieved = flops / (k_ms * 1e-3) / 1e12
         roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                     "traffic": None, "kernel": "eqtl_dense_dmma (E1: DMMA.8x8x4 contraction + per-pair OLS epilogue)",
@@ -309,7 +367,8 @@ def measure(args, env, ClockSampler, n_threads, with_clocks=True):
                     "other_kernels_ms": {"E0 dosage codes + E2 finish + general-path rest": float(np.mean(rest_ms))}}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f64 (2-bit dosage codes x f64 expression, DMMA)",
+                "scaling": "strong" if gene_sharded else "weak", "vs_baseline": None,
+                "dtype": "f64 (2-bit dosage codes x f64 expression, DMMA)",
                 "data": "synthetic (seed 42, drawn on device)", "config": config_dict(args, world), "clocks": clocks,
                 "e2e": e2e, "gpu_launches": int(lsum.item()), "roofline": roofline, "parity": parity}
         if world == 1 and not args.no_cpu_baseline:

@@ -43,6 +43,16 @@ void dump(const std::string& path, const std::vector<T>& v) {
     f.write(reinterpret_cast<const char*>(v.data()), std::streamsize(v.size() * sizeof(T)));
 }
 
+// a snarl record to be filled in: the reference's Snarl_data_t has no default constructor (src/snarl_data_t.hpp:98-118)
+Snarl_data_t blank_snarl() {
+#ifdef STOAT_GPU_SHIM_USE_REFERENCE_TYPES
+    return Snarl_data_t(handlegraph::net_handle_t(), std::pair<size_t, size_t>(0, 0), std::vector<Path_traversal_t>(), 0, 0,
+                        std::vector<std::string>(), 0);
+#else
+    return Snarl_data_t();
+#endif
+}
+
 Path_traversal_t make_path(std::initializer_list<size_t> nodes) {
     Path_traversal_t p;
     for (size_t n : nodes) p.add_node_traversal_t(Node_traversal_t(n, false));
@@ -85,7 +95,7 @@ int run_golden(const char* golden_tsv, const char* pheno_tsv, const char* out_ts
         const auto c = split(line, '\t');
         if (c.size() < 9) continue;
         chr = c[0];
-        Snarl_data_t s;
+        Snarl_data_t s = blank_snarl();
         s.start_positions = std::stoull(c[1]);
         s.end_positions = std::stoull(c[2]);
         const auto ids = split(c[3], '_');
@@ -135,7 +145,7 @@ int run_synth(uint64_t seed, size_t n_snarls, size_t n_samples, const std::strin
     std::vector<Snarl_data_t> snarls;
     size_t node = 10;
     for (size_t s = 0; s < n_snarls; ++s) {
-        Snarl_data_t sd;
+        Snarl_data_t sd = blank_snarl();
         const size_t a = node++, d = node++;
         sd.snarl_ids = {d, a};
         sd.start_positions = 1000 * s + 17;
@@ -285,7 +295,7 @@ int run_bench(size_t n_snarls, size_t n_samples, const std::string& devices, con
     Rng rng{7};
     const size_t H = 2 * n_samples;
     std::vector<std::string> names(n_samples);
-    std::vector<Snarl_data_t> snarls(n_snarls);
+    std::vector<Snarl_data_t> snarls(n_snarls, blank_snarl());
     std::vector<Edge_t> edges;
     edges.reserve(4 * n_snarls);
     size_t node = 10;

@@ -275,6 +275,16 @@ STOAT_GPU_API int stoat_gpu_quantitative_partials_dev(stoat_gpu_ctx* ctx, uint32
                                                       double** doubles_dev, uint64_t* n_doubles);
 STOAT_GPU_API int stoat_gpu_quantitative_solve_staged(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr);
 
+/* The two calls a sample-sharded run uses to finish the snarls quantitative_solve_staged deferred: every rank gathers the
+ * local-column slices of the rows those snarls use (device buffer owned by the context, row i = rows[i], `pitch` bytes each),
+ * the slices are exchanged with ncclAllGather and joined at their byte offsets (column ranges start at multiples of 128
+ * haplotypes = 16 bytes), and the joined rows become the matrix of a second context that runs the ordinary batch call.    */
+STOAT_GPU_API int stoat_gpu_gather_rows_dev(stoat_gpu_ctx* ctx, const uint32_t* rows, uint64_t n, uint8_t** out_dev,
+                                            uint64_t* pitch);
+/* rows already in the device layout: src_pitch bytes per row (a multiple of 16, >= n_cols / 8), bits beyond n_cols zero  */
+STOAT_GPU_API int stoat_gpu_set_matrix_pitched_dev(stoat_gpu_ctx* ctx, const uint8_t* rows_dev, uint64_t n_rows,
+                                                   uint64_t n_cols, uint64_t src_pitch);
+
 /* ---- introspection --------------------------------------------------------------------- */
 /* The staged run calls (stoat_gpu_*_run_staged) only ENQUEUE work on the context's stream; this call waits for the
  * last one and reports its CUDA-event durations and counters.                                                   */

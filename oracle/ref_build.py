@@ -62,5 +62,49 @@ def build(force: bool = False) -> str | None:
     return LIB
 
 
+# ---------------------------------------------------------------------------------------------------
+# The C++ host shim compiled the way a maintainer would compile it INSIDE the reference tree (INTEGRATION.md §2):
+# -DSTOAT_GPU_SHIM_USE_REFERENCE_TYPES, i.e. against stoat::Snarl_data_t / Edge_t / Path_traversal_t and
+# stoat_vcf::EdgeBySampleMatrix themselves, linked with the reference's own matrix.cpp / snarl_data_t.cpp objects
+# (libstoat_ref.so) and libstoat_gpu.so.  The only change to the reference is §2(a) of INTEGRATION.md — three accessors in
+# class EdgeBySampleMatrix — applied here to a COPY of src/matrix.hpp written to oracle/_ref/patched/ (a build output,
+# git-ignored; the shim finds it first on the include path, the reference's own sources keep including theirs).
+# ---------------------------------------------------------------------------------------------------
+ROOT = os.path.dirname(HERE)
+SHIM_REFTYPES = os.path.join(OUT, "shim_reftypes_selftest")
+ACCESSORS = """
+    // --- INTEGRATION.md section 2(a): what the GPU shim reads -------------------------------------
+    const std::vector<uint8_t>& data() const { return matrix_1D; }
+    size_t cols() const { return cols_; }
+    size_t rows() const { return row_header.size(); }
+"""
+
+
+def build_shim_reftypes(force: bool = False) -> str | None:
+    gpu_lib = os.path.join(ROOT, "stoat_b200", "libstoat_gpu.so")
+    if not available() or not os.path.exists(LIB) or not os.path.exists(gpu_lib):
+        return SHIM_REFTYPES if os.path.exists(SHIM_REFTYPES) else None
+    srcs = [os.path.join(ROOT, "host", f) for f in ("shim_selftest.cpp", "stoat_gpu_shim.cpp")]
+    deps = srcs + [os.path.join(ROOT, "host", "stoat_gpu_shim.hpp"), LIB, gpu_lib, os.path.abspath(__file__)]
+    if not force and os.path.exists(SHIM_REFTYPES) and all(os.path.getmtime(d) <= os.path.getmtime(SHIM_REFTYPES) for d in deps):
+        return SHIM_REFTYPES
+    patched = os.path.join(OUT, "patched")
+    os.makedirs(patched, exist_ok=True)
+    text = open(os.path.join(REF, "src", "matrix.hpp")).read()
+    anchor = "protected:"
+    if text.count(anchor) != 1:
+        raise RuntimeError("oracle/_ref: src/matrix.hpp no longer has exactly one `protected:` — revisit INTEGRATION.md 2(a)")
+    with open(os.path.join(patched, "matrix.hpp"), "w") as f:
+        f.write(text.replace(anchor, ACCESSORS + "\n" + anchor))
+    inc = ["-I" + patched, "-I" + os.path.join(HERE, "ref_stubs"), "-I" + os.path.join(REF, "src"),
+           "-I" + os.path.join(REF, "deps", "eigen"), "-I" + os.path.join(REF, "deps", "libhandlegraph", "src", "include")]
+    cmd = ["g++", "-std=c++17", "-O2", "-w", "-fopenmp", "-DSTOAT_GPU_SHIM_USE_REFERENCE_TYPES"] + inc + srcs + \
+          ["-o", SHIM_REFTYPES, "-L" + OUT, "-lstoat_ref", "-L" + os.path.dirname(gpu_lib), "-lstoat_gpu", "-pthread",
+           "-Wl,-rpath,$ORIGIN", "-Wl,-rpath,$ORIGIN/../../stoat_b200"]
+    subprocess.check_call(cmd)
+    return SHIM_REFTYPES
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv))
+    print(build_shim_reftypes(force="--force" in sys.argv))

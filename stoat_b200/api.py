@@ -113,6 +113,17 @@ class Context:
         self._check(self._lib.stoat_gpu_set_matrix_dev(self._ctx, C.c_void_p(dev_ptr), n_rows, n_cols))
         self.n_rows, self.n_cols = n_rows, n_cols
 
+    def set_matrix_pitched_dev(self, dev_ptr: int, n_rows: int, n_cols: int, src_pitch: int):
+        """rows already in the device layout (src_pitch bytes each, zero beyond n_cols): no repack"""
+        self._check(self._lib.stoat_gpu_set_matrix_pitched_dev(self._ctx, C.c_void_p(dev_ptr), n_rows, n_cols, src_pitch))
+
+    def gather_rows_dev(self, rows) -> tuple[int, int]:
+        """(device pointer, pitch) of a context-owned buffer holding rows[i] of the local matrix, in that order"""
+        r = np.ascontiguousarray(rows, dtype=np.uint32)
+        ptr, pitch = C.c_void_p(), C.c_uint64()
+        self._check(self._lib.stoat_gpu_gather_rows_dev(self._ctx, _ptr(r), r.size, C.byref(ptr), C.byref(pitch)))
+        return int(ptr.value or 0), int(pitch.value)
+
     def set_binary_phenotype(self, is_case: np.ndarray):
         a = np.ascontiguousarray(is_case, dtype=np.uint8)
         self._check(self._lib.stoat_gpu_set_binary_phenotype(self._ctx, _ptr(a), a.size))

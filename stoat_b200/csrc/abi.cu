@@ -109,6 +109,7 @@ struct CtxExtra {
     void* host_ring[kHostRing] = {};  // pinned staging of a pageable matrix upload (set_matrix_common)
     cudaEvent_t host_ring_free[kHostRing] = {};
     DevBuf fmt;  // scratch of stoat_gpu_format_values
+    DevBuf gather_idx, gather_out;  // stoat_gpu_gather_rows_dev
     std::vector<uint8_t> fmt_unsure;
     cudaEvent_t chunk_done[kMaxRunChunks] = {};
     // Events of the last kRunRing staged runs: [0] start, [1] end of the count / moments pass, [2] start and [3] end of the
@@ -267,6 +268,8 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     x->q.tail_x.release();
     x->bh.release();
     x->fmt.release();
+    x->gather_idx.release();
+    x->gather_out.release();
     for (int i = 0; i < kHostRing; ++i) {
         if (x->host_ring[i]) cudaFreeHost(x->host_ring[i]);
         if (x->host_ring_free[i]) cudaEventDestroy(x->host_ring_free[i]);
@@ -484,6 +487,60 @@ int stoat_gpu_bh_adjust(stoat_gpu_ctx* ctx, const double* p, uint64_t n, double*
 
 uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx) { return ctx ? ctx->pitch : 0; }
 uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx) { return ctx ? reinterpret_cast<uint64_t>(ctx->stream) : 0; }
+
+// Rows of this context's (pitched, local-column) matrix gathered into a context-owned device buffer: what a rank of a
+// sample-sharded run contributes to the re-assembly of the snarls it deferred.  The buffer stays valid until the next call.
+int stoat_gpu_gather_rows_dev(stoat_gpu_ctx* ctx, const uint32_t* rows, uint64_t n, uint8_t** out_dev, uint64_t* pitch) {
+    if (!ctx || !out_dev || !pitch || (n && !rows)) return fail(ctx, STOAT_GPU_ERR_ARG, "gather_rows_dev: NULL argument");
+    if (!ctx->have_matrix) return fail(ctx, STOAT_GPU_ERR_STATE, "gather_rows_dev: no matrix");
+    for (uint64_t i = 0; i < n; ++i)
+        if (rows[i] >= ctx->n_rows) return fail(ctx, STOAT_GPU_ERR_ARG, "gather_rows_dev: row out of range");
+    CK(cudaSetDevice(ctx->device));
+    CtxExtra* x = extra_of(ctx);
+    CK(x->gather_idx.reserve(std::max<uint64_t>(n * 4, 16)));
+    CK(x->gather_out.reserve(std::max<uint64_t>(n * ctx->pitch, 16)));
+    if (n) {
+        CK(cudaMemcpyAsync(x->gather_idx.p, rows, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CK(launch_gather_rows(ctx->rows.as<uint8_t>(), ctx->pitch, x->gather_idx.as<uint32_t>(), n, x->gather_out.as<uint8_t>(),
+                              ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    *out_dev = x->gather_out.as<uint8_t>();
+    *pitch = ctx->pitch;
+    return STOAT_GPU_OK;
+}
+
+// The matrix from rows that are already in the device layout (src_pitch >= ceil(n_cols / 8) bytes per row, a multiple of 16,
+// every bit beyond n_cols zero): no repack pass.
+int stoat_gpu_set_matrix_pitched_dev(stoat_gpu_ctx* ctx, const uint8_t* rows_dev, uint64_t n_rows, uint64_t n_cols,
+                                     uint64_t src_pitch) {
+    if (!ctx) return STOAT_GPU_ERR_ARG;
+    if (n_cols == 0 || (n_cols & 1)) return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_pitched_dev: n_cols must be even and > 0");
+    if (n_cols >= (1ull << 32) || n_rows >= 0xFFFFFFFFull)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_pitched_dev: dimensions exceed 32-bit row / column indices");
+    if (n_rows && !rows_dev) return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_pitched_dev: rows is NULL");
+    if (src_pitch * 8 < n_cols || (src_pitch & 15)) return fail(ctx, STOAT_GPU_ERR_ARG, "set_matrix_pitched_dev: bad pitch");
+    CK(cudaSetDevice(ctx->device));
+    if (int rc = finalize_timing(ctx)) return rc;
+    const uint64_t pitch = pitch_for(n_cols);
+    ctx->have_matrix = false;
+    invalidate_derived(ctx);
+    CK(ctx->rows.reserve(std::max<uint64_t>(n_rows * pitch, 16)));
+    ctx->timing = stoat_gpu_timing{};
+    if (n_rows) {
+        CK(cudaMemsetAsync(ctx->rows.p, 0, n_rows * pitch, ctx->stream));
+        CK(cudaMemcpy2DAsync(ctx->rows.p, pitch, rows_dev, src_pitch, std::min(pitch, src_pitch), n_rows,
+                             cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->n_rows = n_rows;
+    ctx->n_cols = n_cols;
+    ctx->pitch = pitch;
+    ctx->have_matrix = true;
+    if (ctx->have_binary && ctx->n_samples_binary * 2 != n_cols) ctx->have_binary = false;
+    if (ctx->have_quant && ctx->n_samples_quant * 2 != n_cols) ctx->have_quant = false;
+    return STOAT_GPU_OK;
+}
 
 int stoat_gpu_read_row(stoat_gpu_ctx* ctx, uint64_t row, uint8_t* out, uint64_t out_bytes) {
     if (!ctx || !out) return STOAT_GPU_ERR_ARG;

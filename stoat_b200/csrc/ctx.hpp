@@ -86,6 +86,8 @@ cudaError_t launch_repack_rows(const uint8_t* raw, uint64_t raw_bytes, uint64_t 
                                uint64_t n_cols, uint64_t pitch, uint8_t* out, cudaStream_t st);
 cudaError_t launch_scatter_bits(const uint32_t* row, const uint32_t* col, uint64_t n_pairs, uint64_t n_rows, uint64_t n_cols,
                                 uint64_t pitch, uint8_t* out, uint32_t* bad, int num_sms, cudaStream_t st);
+cudaError_t launch_gather_rows(const uint8_t* rows, uint64_t pitch, const uint32_t* idx, uint64_t n, uint8_t* out,
+                               cudaStream_t st);
 cudaError_t launch_build_case_mask(const uint8_t* is_case, uint64_t n_samples, uint64_t pitch, uint8_t* mask,
                                    cudaStream_t st);
 // binary

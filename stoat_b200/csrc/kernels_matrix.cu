@@ -118,4 +118,21 @@ cudaError_t launch_scatter_bits(const uint32_t* row, const uint32_t* col, uint64
     return cudaGetLastError();
 }
 
+
+// rows[i] of the pitched matrix -> out[i] (same pitch): the row slices a sample-sharded run exchanges for the snarls its
+// summed two-path partials cannot finish (stoat_b200/shard.py).  One block per row, 16-byte copies.
+__global__ void __launch_bounds__(128) gather_rows_kernel(const uint8_t* __restrict__ rows, uint64_t pitch,
+                                                          const uint32_t* __restrict__ idx, uint8_t* __restrict__ out) {
+    const uint4* src = reinterpret_cast<const uint4*>(rows + uint64_t(idx[blockIdx.x]) * pitch);
+    uint4* dst = reinterpret_cast<uint4*>(out + uint64_t(blockIdx.x) * pitch);
+    for (uint32_t c = threadIdx.x; c < pitch / 16; c += blockDim.x) dst[c] = src[c];
+}
+
+cudaError_t launch_gather_rows(const uint8_t* rows, uint64_t pitch, const uint32_t* idx, uint64_t n, uint8_t* out,
+                               cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    gather_rows_kernel<<<unsigned(n), 128, 0, st>>>(rows, pitch, idx, out);
+    return cudaGetLastError();
+}
+
 }  // namespace stoat

@@ -38,6 +38,21 @@ def test_golden_binary_tsv_byte_for_byte(selftest, tmp_path):
     assert not bad, f"{len(bad)} rows differ, first: {bad[0]}"
 
 
+def test_golden_through_the_reference_types_build(tmp_path):
+    """The same golden file through the shim compiled against the REFERENCE'S OWN Snarl_data_t / Edge_t /
+    EdgeBySampleMatrix (oracle/_ref/shim_reftypes_selftest, built by oracle/ref_build.py with the INTEGRATION.md §2a
+    accessors): the build a maintainer would make."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "shim_reftypes_selftest")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/shim_reftypes_selftest not built (needs /root/reference at build time)")
+    out = tmp_path / "binary.tsv"
+    golden = os.path.join(H.GOLDEN, "binary_table_vcf.golden.tsv")
+    r = subprocess.run([exe, "golden", golden, os.path.join(H.GOLDEN, "binary_phenotype.tsv"), str(out)],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert open(out).read() == open(golden).read()
+
+
 def _rows(path):
     with open(path) as f:
         return [ln.rstrip("\n").split("\t") for ln in f][1:]

@@ -287,3 +287,23 @@ def test_reference_binary_covar_analyzer_vs_oracle(oracle):
     P = oracle.Paths(spo, peo, er)
     nodes = ref.nodes_from_csr(spo, peo, er, 40)
     _check_binary_covar(oracle, bits, 40, 2 * n_samples, P, nodes, is_case, None, threads=2)
+
+
+def test_shim_builds_against_reference_types():
+    """host/stoat_gpu_shim.cpp compiled with -DSTOAT_GPU_SHIM_USE_REFERENCE_TYPES against the reference's own headers (plus the
+    three accessors of INTEGRATION.md §2a, patched into a copy of src/matrix.hpp at build time) and linked with the
+    reference's matrix.cpp / snarl_data_t.cpp objects: the mode a maintainer compiles.  Running it needs a GPU
+    (tests/test_gpu_shim.py); here: it builds, and it binds both libraries."""
+    import subprocess
+
+    from oracle import ref_build
+
+    exe = ref_build.build_shim_reftypes()
+    if exe is None:
+        pytest.skip("libstoat_gpu.so or oracle/_ref not built")
+    assert os.path.exists(exe)
+    needed = subprocess.run(["readelf", "-d", exe], capture_output=True, text=True).stdout
+    assert "libstoat_ref.so" in needed and "libstoat_gpu.so" in needed
+    syms = subprocess.run(["nm", "-C", "--undefined-only", exe], capture_output=True, text=True).stdout
+    assert "stoat_vcf::EdgeBySampleMatrix::find_edge" in syms and "stoat_vcf::EdgeBySampleMatrix::push_matrix" in syms
+    assert "stoat_gpu_binary_batch" in syms
