@@ -282,44 +282,107 @@ def gather_deferred_rows(local_bits: np.ndarray, n_rows: int, local_cols: int, p
     return bits, int(rows.size), SnarlPaths(sub.snarl_path_off, sub.path_edge_off, er2)
 
 
+def _ranges(starts: np.ndarray, lengths: np.ndarray) -> np.ndarray:
+    """concatenation of arange(starts[i], starts[i] + lengths[i]) without a Python loop"""
+    total = int(lengths.sum())
+    if total == 0:
+        return np.zeros(0, np.int64)
+    ends = np.cumsum(lengths)
+    out = np.ones(total, np.int64)
+    first = ends - lengths
+    nz = lengths > 0
+    out[first[nz]] = starts[nz] - np.concatenate([[0], (starts + lengths)[nz][:-1] - 1])
+    return np.cumsum(out)
+
+
 def select_snarls(paths: SnarlPaths, idx: np.ndarray) -> SnarlPaths:
-    """The CSR of the snarls `idx` (in that order)."""
+    """The CSR of the snarls `idx` (in that order); vectorised (1M snarls x a few per cent deferred is 70k snarls)."""
     spo = np.asarray(paths.snarl_path_off, dtype=np.int64)
     peo = np.asarray(paths.path_edge_off, dtype=np.int64)
     er = np.asarray(paths.edge_row, dtype=np.uint32)
+    idx = np.asarray(idx, dtype=np.int64)
     n_paths = spo[idx + 1] - spo[idx]
     new_spo = np.concatenate([[0], np.cumsum(n_paths)]).astype(np.uint64)
-    path_ids = np.concatenate([np.arange(spo[s], spo[s + 1]) for s in idx]) if len(idx) else np.zeros(0, np.int64)
+    path_ids = _ranges(spo[idx], n_paths)
     n_edges = peo[path_ids + 1] - peo[path_ids]
     new_peo = np.concatenate([[0], np.cumsum(n_edges)]).astype(np.uint64)
-    edges = np.concatenate([er[peo[p]:peo[p + 1]] for p in path_ids]) if len(path_ids) else np.zeros(0, np.uint32)
+    edges = er[_ranges(peo[path_ids], n_edges)] if path_ids.size else np.zeros(0, np.uint32)
     return SnarlPaths(new_spo, new_peo, edges.astype(np.uint32))
 
 
 def merge_deferred(result: dict, todo: np.ndarray, replay: dict, paths: SnarlPaths) -> dict:
     """Write the replayed snarls' rows over the deferred ones (per-snarl arrays by snarl, allele_paths by path)."""
     spo = np.asarray(paths.snarl_path_off, dtype=np.int64)
+    todo = np.asarray(todo, dtype=np.int64)
     out = {k: np.array(v, copy=True) for k, v in result.items()}
     for k, v in replay.items():
+        if k not in out:
+            continue
         if k == "allele_paths":
-            pos = 0
-            for s in todo:
-                n = int(spo[s + 1] - spo[s])
-                out[k][spo[s]:spo[s] + n] = v[pos:pos + n]
-                pos += n
+            out[k][_ranges(spo[todo], spo[todo + 1] - spo[todo])] = v
         else:
             out[k][todo] = v
     return out
 
 
+def remap_rows(sub: SnarlPaths) -> tuple[np.ndarray, SnarlPaths]:
+    """(distinct matrix rows of `sub`, `sub` with edge_row pointing into that list)"""
+    er = np.asarray(sub.edge_row, dtype=np.uint32)
+    ok = er != MISSING_EDGE
+    rows, inv = np.unique(er[ok], return_inverse=True)
+    er2 = er.copy()
+    er2[ok] = inv.astype(np.uint32)
+    return rows.astype(np.uint32), SnarlPaths(sub.snarl_path_off, sub.path_edge_off, er2)
+
+
+def replay_deferred_on_device(shard_ctxs, col_ranges, paths: SnarlPaths, todo: np.ndarray, y, thresholds, replay_ctx,
+                              allgather_dev=None) -> dict:
+    """The snarls a sample-sharded solve deferred, finished WITHOUT leaving the device: every shard gathers its column
+    slices of the rows those snarls use (stoat_gpu_gather_rows_dev), the slices are exchanged (`allgather_dev`: NCCL
+    all-gather of one byte tensor per rank in a distributed run; None when `shard_ctxs` already holds every shard, as in
+    a single-process run over several contexts), joined at their byte offsets into whole rows and handed to `replay_ctx`
+    (a second context: the shard's own matrix and staging stay as they are) for the ordinary batch call."""
+    import torch
+
+    mi, mh, maf = thresholds
+    sub = select_snarls(paths, todo)
+    rows, sub = remap_rows(sub)
+    dev = torch.device("cuda", replay_ctx.device)
+    n_cols = sum(c1 - c0 for c0, c1 in col_ranges)
+    full_pitch = (n_cols + 255) // 256 * 32
+    parts = []
+    for ctx in shard_ctxs:
+        ptr, pitch = ctx.gather_rows_dev(rows)
+        t = torch.as_tensor(_DevU8(ptr, rows.size * pitch), device=torch.device("cuda", ctx.device)).view(rows.size, pitch)
+        parts.append(t)
+    if allgather_dev is not None:
+        parts = allgather_dev(parts[0])
+    full = torch.zeros((rows.size, full_pitch), dtype=torch.uint8, device=dev)
+    for (c0, c1), t in zip(col_ranges, parts):
+        if c1 <= c0:
+            continue
+        nb = (c1 - c0 + 7) // 8
+        full[:, c0 // 8:c0 // 8 + nb] = t[:, :nb].to(dev)
+    torch.cuda.synchronize(dev)
+    replay_ctx.set_matrix_pitched_dev(full.data_ptr(), int(rows.size), n_cols, full_pitch)
+    replay_ctx.set_quantitative_phenotype(np.asarray(y, dtype=np.float64))
+    return replay_ctx.quantitative_batch(sub, mi, mh, maf)
+
+
+class _DevU8:
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
 def run_quantitative_sample_sharded(ctx, bits, n_rows: int, n_cols: int, paths: SnarlPaths, y, rank: int, world: int,
-                                    group=None, thresholds=(3, 5, 0.05)) -> dict:
+                                    group=None, thresholds=(3, 5, 0.05), replay_ctx=None) -> dict:
     """One rank's part of a sample-sharded quantitative run (every rank returns the full result).
 
     moments of the local columns (K3M: per snarl 7 class counts + 3 phenotype sums) -> ONE all-reduce -> filters and OLS
     on the sums (K4).  Snarls that need more than the two-path sums (other shapes, rank-deficient or near-perfect
-    fits: a few per cent) come back deferred; their rows are re-assembled from all ranks' column slices and replayed
-    through the ordinary batch call, replicated."""
+    fits: a few per cent) come back deferred; the column slices of their rows are all-gathered over NCCL (device buffers,
+    no pickling, no host copy of the matrix), joined on the device and replayed through the ordinary batch call on a second
+    context, replicated on every rank.  `ctx` keeps its shard (matrix, phenotype slice, staging)."""
     import torch.distributed as dist
 
     ranges = plan_column_shards(n_cols, world)
@@ -341,16 +404,78 @@ def run_quantitative_sample_sharded(ctx, bits, n_rows: int, n_cols: int, paths: 
     todo = deferred_snarls(res)
     if todo.size == 0:
         return res
+    from .api import Context
 
-    def allgather(obj):
+    def allgather_dev(mine):
+        """one byte tensor [rows, local pitch] per rank; pitches differ by rank, so pad to the widest"""
+        import torch
+
         if world == 1:
-            return [obj]
-        out = [None] * world
-        dist.all_gather_object(out, obj, group=group)
+            return [mine]
+        w = torch.tensor([mine.shape[1]], dtype=torch.int64, device=mine.device)
+        ws = [torch.zeros_like(w) for _ in range(world)]
+        dist.all_gather(ws, w, group=group)
+        wmax = max(int(v.item()) for v in ws)
+        padded = torch.zeros((mine.shape[0], wmax), dtype=torch.uint8, device=mine.device)
+        padded[:, :mine.shape[1]] = mine
+        out = [torch.empty_like(padded) for _ in range(world)]
+        dist.all_gather(out, padded, group=group)
         return out
 
-    full_bits, full_rows, sub = gather_deferred_rows(local, n_rows, c1 - c0, paths, todo, ranges, allgather)
-    ctx.set_matrix(full_bits, full_rows, n_cols)
-    ctx.set_quantitative_phenotype(yy)
-    replay = ctx.quantitative_batch(sub, mi, mh, maf)
+    own = replay_ctx is None
+    rctx = Context(ctx.device) if own else replay_ctx
+    try:
+        replay = replay_deferred_on_device([ctx], ranges, paths, todo, yy, thresholds, rctx, allgather_dev)
+    finally:
+        if own:
+            rctx.close()
+    return merge_deferred(res, todo, replay, paths)
+
+
+def run_quantitative_sample_sharded_local(ctxs, bits, n_rows: int, n_cols: int, paths: SnarlPaths, y,
+                                          thresholds=(3, 5, 0.05), replay_ctx=None) -> dict:
+    """The same run inside ONE process over len(ctxs) contexts (on one GPU or several): shard i holds the column range i.
+    The all-reduce becomes a sum over the contexts' partial buffers, the exchange of deferred rows a list.  This is what a
+    single-GPU test box can run; the arithmetic and every library call are those of the distributed driver."""
+    import torch
+
+    from .api import Context
+
+    world = len(ctxs)
+    ranges = plan_column_shards(n_cols, world)
+    mi, mh, maf = thresholds
+    yy = np.asarray(y, dtype=np.float64)
+    mean, s1, s2, vmax = phenotype_summary(yy)
+    views = []
+    for ctx, (c0, c1) in zip(ctxs, ranges):
+        if c1 <= c0:
+            raise ValueError("sample-sharded run needs at least 128 columns per shard")
+        ctx.set_matrix(split_columns(bits, n_rows, n_cols, c0, c1), n_rows, c1 - c0)
+        ctx.set_quantitative_phenotype_shard(yy[c0 // 2:c1 // 2], mean, s1, s2, vmax)
+        ctx.stage_paths(paths)
+        ctx.quantitative_moments_staged(mi, mh, maf)
+        pi, ni, pd, nd = ctx.quantitative_partials_dev()
+        dev = torch.device("cuda", ctx.device)
+        views.append((torch.as_tensor(_DevU32(pi, ni), device=dev), torch.as_tensor(_DevF64(pd, nd), device=dev)))
+    if len({v[0].numel() for v in views}) != 1:
+        raise ValueError("the shards use different numbers of haplotype slices: give every shard <= 12,288 haplotypes")
+    tot_i = sum(v[0].to(views[0][0].device) for v in views)
+    tot_d = sum(v[1].to(views[0][1].device) for v in views)
+    for vi, vd in views:
+        vi.copy_(tot_i.to(vi.device))
+        vd.copy_(tot_d.to(vd.device))
+    for ctx in ctxs:
+        torch.cuda.synchronize(ctx.device)
+    ctxs[0].quantitative_solve_staged(mi, mh, maf)
+    res = ctxs[0].quantitative_fetch()
+    todo = deferred_snarls(res)
+    if todo.size == 0:
+        return res
+    own = replay_ctx is None
+    rctx = Context(ctxs[0].device) if own else replay_ctx
+    try:
+        replay = replay_deferred_on_device(ctxs, ranges, paths, todo, yy, thresholds, rctx)
+    finally:
+        if own:
+            rctx.close()
     return merge_deferred(res, todo, replay, paths)

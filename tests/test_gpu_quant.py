@@ -206,6 +206,49 @@ def test_sample_sharded_phases_single_gpu(gpu_ctx, oracle):
     assert set(np.flatnonzero(n_paths != 2)) <= set(todo) and todo.size < d["paths"].n_snarls // 4
 
 
+@pytest.mark.parametrize("n_shards", [2, 3])
+def test_sample_sharded_column_split_on_one_gpu(gpu_ctx, oracle, n_shards):
+    """The sample-sharded run with REAL column shards on a one-GPU box: n_shards contexts each hold a column range, the
+    all-reduce is a sum over their partial buffers, the deferred snarls (three paths, thirds, missing edges: ~10 %) are
+    finished on the device from the shards' gathered row slices (stoat_gpu_gather_rows_dev -> joined rows ->
+    stoat_gpu_set_matrix_pitched_dev on a second context).  Same library calls as the NCCL driver."""
+    import stoat_b200
+    from stoat_b200 import shard, synth
+
+    d = synth.numpy_dataset(3000, 640, seed=21, frac_missing_edge=0.02)
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    ref = oracle.quantitative_batch(d["bits"], d["n_cols"], d["y"], P)
+    ctxs = [gpu_ctx] + [stoat_b200.Context(0) for _ in range(n_shards - 1)]
+    try:
+        got = shard.run_quantitative_sample_sharded_local(ctxs, d["bits"], d["n_rows"], d["n_cols"], d["paths"], d["y"])
+    finally:
+        for c in ctxs[1:]:
+            c.close()
+    H.assert_quant_equal(got, ref)
+    assert (ref["filtered"] == 0).sum() > 1000
+    # the shard contexts keep their state: shard 0 still holds its column range
+    assert gpu_ctx.row_pitch == (shard.plan_column_shards(d["n_cols"], n_shards)[0][1] + 255) // 256 * 32
+
+
+def test_select_snarls_vectorised_equals_loops():
+    from stoat_b200 import shard, synth
+
+    d = synth.numpy_dataset(500, 20, seed=3, frac_missing_edge=0.05)
+    p = d["paths"]
+    idx = np.array([7, 3, 499, 0, 250, 251])
+    sub = shard.select_snarls(p, idx)
+    spo, peo = p.snarl_path_off.astype(np.int64), p.path_edge_off.astype(np.int64)
+    want_er, want_peo, want_spo = [], [0], [0]
+    for s_ in idx:
+        for q in range(spo[s_], spo[s_ + 1]):
+            want_er.extend(p.edge_row[peo[q]:peo[q + 1]].tolist())
+            want_peo.append(len(want_er))
+        want_spo.append(len(want_peo) - 1)
+    np.testing.assert_array_equal(sub.snarl_path_off, np.array(want_spo, np.uint64))
+    np.testing.assert_array_equal(sub.path_edge_off, np.array(want_peo, np.uint64))
+    np.testing.assert_array_equal(sub.edge_row, np.array(want_er, np.uint32))
+
+
 def _three_path_problem(rng, n_snarls, n_samples, frac_missing):
     """Three-path snarls, 1 or 2 checked edges per path.  Every 11th snarl has a path nobody takes (the reference makes
     no column for it), every 13th two paths over the SAME rows (identical columns, which the reference merges), every
