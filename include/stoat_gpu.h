@@ -285,6 +285,11 @@ STOAT_GPU_API int stoat_gpu_gather_rows_dev(stoat_gpu_ctx* ctx, const uint32_t* 
 STOAT_GPU_API int stoat_gpu_set_matrix_pitched_dev(stoat_gpu_ctx* ctx, const uint8_t* rows_dev, uint64_t n_rows,
                                                    uint64_t n_cols, uint64_t src_pitch);
 
+/* Test hook: C [128][n_b_rows] (int32) = A [128][k] * B [n_b_rows][k]^T (int8) through the tcgen05 kernel of the dense eQTL
+ * scan (n_b_rows a multiple of 256, k a multiple of 128).  Exercises the operand images, descriptors and tensor memory. */
+STOAT_GPU_API int stoat_gpu_debug_umma_probe(stoat_gpu_ctx* ctx, const int8_t* a, const int8_t* b, uint32_t n_b_rows,
+                                             uint32_t k, int32_t* c);
+
 /* ---- introspection --------------------------------------------------------------------- */
 /* The staged run calls (stoat_gpu_*_run_staged) only ENQUEUE work on the context's stream; this call waits for the
  * last one and reports its CUDA-event durations and counters.                                                   */

@@ -74,6 +74,7 @@ SIGNATURES = {
     "stoat_gpu_quantitative_batch": (C.c_int, [CTX, C.POINTER(PathsC), C.POINTER(Thresholds), C.POINTER(QuantOut)]),
     "stoat_gpu_gather_rows_dev": (C.c_int, [CTX, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
     "stoat_gpu_set_matrix_pitched_dev": (C.c_int, [CTX, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64]),
+    "stoat_gpu_debug_umma_probe": (C.c_int, [CTX, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]),
     "stoat_gpu_format_values": (C.c_int, [CTX, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "stoat_gpu_binary_covar_batch": (C.c_int, [CTX, C.POINTER(PathsC), C.POINTER(Thresholds), C.c_int,
                                                C.POINTER(BinaryCovarOut)]),

@@ -146,6 +146,14 @@ class Context:
         self._check(self._lib.stoat_gpu_bh_adjust(self._ctx, _ptr(a), a.size, _ptr(out)))
         return out
 
+    def debug_umma_probe(self, a, b) -> np.ndarray:
+        """int32 C [128][rows of b] = a [128][k] @ b[rows][k].T through the tcgen05 kernel of the dense eQTL scan (tests)"""
+        a = np.ascontiguousarray(a, dtype=np.int8)
+        b = np.ascontiguousarray(b, dtype=np.int8)
+        c = np.zeros((128, b.shape[0]), np.int32)
+        self._check(self._lib.stoat_gpu_debug_umma_probe(self._ctx, _ptr(a), _ptr(b), b.shape[0], a.shape[1], _ptr(c)))
+        return c
+
     def format_values(self, values, codes=None) -> list[str]:
         """The value column as the reference prints it (set_precision + the literal strings of the codes), formatted on the
         device (include/stoat_gpu.h: stoat_gpu_format_values)."""

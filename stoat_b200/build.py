@@ -12,8 +12,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libstoat_gpu.so")
-SOURCES = ["abi.cu", "kernels_matrix.cu", "kernels_binary.cu", "kernels_quant.cu", "kernels_eqtl.cu", "kernels_post.cu", "kernels_logit.cu"]
-HEADERS = ["ctx.hpp", "ptx.cuh", "device_math.cuh", "ols.cuh", "stage_pipeline.cuh", "quant_general.cuh", "quant_lean.cuh", "quant_reg.cuh", "quant_mma.cuh", "dosage_masks.cuh", "eqtl_dense.hpp", os.path.join("..", "..", "include", "stoat_gpu.h")]
+SOURCES = ["abi.cu", "kernels_matrix.cu", "kernels_binary.cu", "kernels_quant.cu", "kernels_eqtl.cu", "kernels_post.cu", "kernels_logit.cu", "kernels_eqtl_umma.cu"]
+HEADERS = ["ctx.hpp", "ptx.cuh", "device_math.cuh", "ols.cuh", "stage_pipeline.cuh", "quant_general.cuh", "quant_lean.cuh", "quant_reg.cuh", "quant_mma.cuh", "dosage_masks.cuh", "eqtl_dense.hpp", "eqtl_pair.cuh", os.path.join("..", "..", "include", "stoat_gpu.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",

@@ -108,6 +108,7 @@ struct CtxExtra {
     DevBuf bh;  // scratch of stoat_gpu_bh_adjust
     void* host_ring[kHostRing] = {};  // pinned staging of a pageable matrix upload (set_matrix_common)
     cudaEvent_t host_ring_free[kHostRing] = {};
+    DevBuf um_scale, um_b, um_a, um_probe;  // tcgen05 eQTL: gene scales, B / A operand images, probe scratch
     DevBuf fmt;  // scratch of stoat_gpu_format_values
     DevBuf gather_idx, gather_out;  // stoat_gpu_gather_rows_dev
     std::vector<uint8_t> fmt_unsure;
@@ -235,7 +236,8 @@ int stoat_gpu_create(stoat_gpu_ctx** out, int device) {
     const char* k1 = std::getenv("STOAT_GPU_K1");
     ctx->k1_variant = (k1 && std::strcmp(k1, "ldg") == 0) ? 1 : 0;
     const char* eq = std::getenv("STOAT_GPU_EQTL");
-    ctx->eqtl_variant = (eq && std::strcmp(eq, "general") == 0) ? 1 : 0;
+    // 0: tcgen05 int8 contraction (default); 2: the FP64 DMMA contraction (STOAT_GPU_EQTL=dmma); 1: general kernel only
+    ctx->eqtl_variant = (eq && std::strcmp(eq, "general") == 0) ? 1 : (eq && std::strcmp(eq, "dmma") == 0) ? 2 : 0;
     *out = ctx;
     return STOAT_GPU_OK;
 }
@@ -268,6 +270,7 @@ void stoat_gpu_destroy(stoat_gpu_ctx* ctx) {
     x->q.tail_x.release();
     x->bh.release();
     x->fmt.release();
+    for (DevBuf* b : {&x->um_scale, &x->um_b, &x->um_a, &x->um_probe}) b->release();
     x->gather_idx.release();
     x->gather_out.release();
     for (int i = 0; i < kHostRing; ++i) {
@@ -1266,6 +1269,15 @@ static int eqtl_prepare_expression(stoat_gpu_ctx* ctx, uint64_t G) {
     CK(ctx->e_tot2.reserve(std::max<uint64_t>(G * 8, 16)));
     CK(launch_eqtl_centre(ctx->e_expr.as<double>(), uint32_t(G), uint32_t(n), uint32_t(n_pad), ctx->e_yc.as<double>(),
                           ctx->e_tot.as<double>(), ctx->e_tot2.as<double>(), ctx->stream));
+    if (ctx->eqtl_variant == 0) {
+        // the limbs of the centred expression as the shared-memory images of the tcgen05 kernel's B tiles (once per matrix)
+        CtxExtra* x = extra_of(ctx);
+        const uint64_t g_tiles = (G + kUmTileG - 1) / kUmTileG, n_kb = n_pad / kUmKB;
+        CK(x->um_scale.reserve(std::max<uint64_t>(G * 8, 16)));
+        CK(x->um_b.reserve(std::max<uint64_t>(g_tiles * n_kb * kUmBBytes, 16)));
+        CK(launch_eqtl_umma_prepare_expression(ctx->e_yc.as<double>(), uint32_t(G), uint32_t(n_pad), x->um_scale.as<double>(),
+                                               x->um_b.as<uint8_t>(), ctx->stream));
+    }
     ctx->e_n_genes = G;
     extra_of(ctx)->expr_cols = ctx->n_cols;
     ctx->have_expression = true;
@@ -1361,7 +1373,18 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     e.min_p = ctx->e_min_p.as<double>();
     e.argmin = ctx->e_argmin.as<uint32_t>();
     e.n_below = ctx->e_nbelow.as<uint32_t>();
-    const bool allow_dense = ctx->eqtl_variant == 0 && ctx->n_covar == 0;
+    const bool allow_dense = ctx->eqtl_variant != 1 && ctx->n_covar == 0;
+    const bool use_umma = ctx->eqtl_variant == 0 && n < 65536;
+    EqtlUmma um{};
+    if (allow_dense && use_umma) {
+        CtxExtra* x = extra_of(ctx);
+        um.n_kb = e.n_pad / kUmKB;
+        CK(x->um_a.reserve(std::max<uint64_t>((e.s_pad / kUmTileS) * uint64_t(um.n_kb) * kUmABytes, 16)));
+        um.a_img = x->um_a.as<uint8_t>();
+        um.b_img = x->um_b.as<uint8_t>();
+        um.scale = x->um_scale.as<double>();
+        um.probe_out = nullptr;
+    }
 
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     CK(cudaMemsetAsync(e.fb_count, 0, 8, ctx->stream));  // general-path list length, dense slot count
@@ -1369,7 +1392,12 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     uint32_t launches = 1;
     CK(cudaEventRecord(ctx->ev[5], ctx->stream));
     if (allow_dense && S) {
-        CK(launch_eqtl_dense(e, ctx->num_sms, ctx->stream));
+        if (use_umma) {
+            CK(launch_eqtl_dense_umma(e, um, ctx->stream));
+            ++launches;  // the expansion of the dosage codes into the A image
+        } else {
+            CK(launch_eqtl_dense(e, ctx->num_sms, ctx->stream));
+        }
         CK(cudaEventRecord(ctx->ev[6], ctx->stream));
         CK(launch_eqtl_dense_finish(e, ctx->stream));
         launches += 2;
@@ -1402,6 +1430,48 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     ctx->timing.launches = launches;
     ctx->timing.n_general = n_fb;
     ctx->have_eqtl_summary = true;
+    return STOAT_GPU_OK;
+}
+
+// Test hook of the tcgen05 kernel's mechanics (operand images, descriptors, TMEM round trip): C = A * B^T for int8
+// A [128][K], B [n_b_rows][K] (n_b_rows a multiple of 256, K of 128), C int32 [128][n_b_rows], through the SAME kernel the
+// scan uses (its epilogue dumps the raw accumulators).  Host buffers.
+int stoat_gpu_debug_umma_probe(stoat_gpu_ctx* ctx, const int8_t* a, const int8_t* b, uint32_t n_b_rows, uint32_t k,
+                               int32_t* c) {
+    if (!ctx || !a || !b || !c) return fail(ctx, STOAT_GPU_ERR_ARG, "umma_probe: NULL argument");
+    if (n_b_rows == 0 || n_b_rows % kUmTileN || k == 0 || k % kUmKB) return fail(ctx, STOAT_GPU_ERR_ARG, "umma_probe: bad shape");
+    CK(cudaSetDevice(ctx->device));
+    CtxExtra* x = extra_of(ctx);
+    const uint32_t n_kb = k / kUmKB, n_gt = n_b_rows / kUmTileN;
+    std::vector<uint8_t> ai(size_t(n_kb) * kUmABytes), bi(size_t(n_gt) * n_kb * kUmBBytes);
+    auto swz = [](uint32_t r, uint32_t kk) { return r * 128u + ((((kk >> 4) ^ (r & 7u)) << 4) | (kk & 15u)); };
+    for (uint32_t r = 0; r < uint32_t(kUmTileS); ++r)
+        for (uint32_t kk = 0; kk < k; ++kk) ai[size_t(kk / kUmKB) * kUmABytes + swz(r, kk % kUmKB)] = uint8_t(a[size_t(r) * k + kk]);
+    for (uint32_t r = 0; r < n_b_rows; ++r)
+        for (uint32_t kk = 0; kk < k; ++kk)
+            bi[(size_t(r / kUmTileN) * n_kb + kk / kUmKB) * kUmBBytes + swz(r % kUmTileN, kk % kUmKB)] = uint8_t(b[size_t(r) * k + kk]);
+    const size_t c_bytes = size_t(kUmTileS) * n_b_rows * 4;
+    CK(x->um_probe.reserve(ai.size() + bi.size() + c_bytes + 64));
+    uint8_t* d_a = x->um_probe.as<uint8_t>();
+    uint8_t* d_b = d_a + ai.size();
+    int32_t* d_c = reinterpret_cast<int32_t*>(d_b + bi.size());
+    CK(cudaMemcpyAsync(d_a, ai.data(), ai.size(), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_b, bi.data(), bi.size(), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemsetAsync(d_c, 0xFF, c_bytes, ctx->stream));
+    EqtlDense e{};
+    e.n_genes = n_b_rows / 8;
+    e.genes_per_group = e.n_genes;
+    e.n_groups = 1;
+    e.s_pad = kUmTileS;
+    e.n_snarls = kUmTileS;
+    EqtlUmma um{};
+    um.a_img = d_a;
+    um.b_img = d_b;
+    um.n_kb = n_kb;
+    um.probe_out = d_c;
+    CK(launch_eqtl_dense_umma(e, um, ctx->stream));
+    CK(cudaMemcpyAsync(c, d_c, c_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
     return STOAT_GPU_OK;
 }
 

@@ -48,6 +48,25 @@ struct EqtlDense {
     uint32_t* n_below;
 };
 
+// ---- tcgen05 int8 form (kernels_eqtl_umma.cu) ---------------------------------------------------------------------------
+constexpr int kUmTileS = 128;               // slots per CTA tile = UMMA M
+constexpr int kUmTileG = 32;                // genes per gene tile
+constexpr int kUmTileN = kUmTileG * 8;      // limb columns per gene tile = UMMA N
+constexpr int kUmKB = 128;                  // samples (bytes of a K-major int8 row) per pipeline stage
+constexpr int kUmABytes = kUmTileS * kUmKB; // 16,384: image of a stage's A tile
+constexpr int kUmBBytes = kUmTileN * kUmKB; // 32,768: image of a stage's B tile
+struct EqtlUmma {
+    uint8_t* a_img;        // [slot tiles][n_kb][16 KB]   2 d as int8, shared-memory image (K-major, 128-byte swizzle)
+    const uint8_t* b_img;  // [gene tiles][n_kb][32 KB]   limbs of the centred expression, same
+    const double* scale;   // [n_genes]
+    uint32_t n_kb;         // n_pad / 128
+    int32_t* probe_out;    // tests: raw accumulators [128][gene tiles * 32][8] of slot tile 0 instead of the statistics
+};
+cudaError_t launch_eqtl_umma_prepare_expression(const double* yc, uint32_t n_genes, uint32_t n_pad, double* scale,
+                                                uint8_t* b_img, cudaStream_t st);
+cudaError_t launch_eqtl_dense_umma(const EqtlDense& e, const EqtlUmma& u, cudaStream_t st);
+size_t eqtl_umma_smem_bytes();
+
 cudaError_t launch_eqtl_centre(const double* y, uint32_t n_genes, uint32_t n, uint32_t n_pad, double* yc, double* tot,
                                double* tot2, cudaStream_t st);
 cudaError_t launch_eqtl_dosage_codes(const MatrixDev& m, const BatchDev& b, const stoat_gpu_thresholds& thr, bool allow_dense,
