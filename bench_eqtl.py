@@ -31,8 +31,8 @@ def config_dict(args, n_gpus):
                      f"gene-sharded: {n_gpus} ranks scan the same snarls against {args.genes} / {n_gpus} genes each, per-snarl "
                      f"summaries merged by one all-reduce per step" if getattr(args, "sharding", "snarl") == "gene" else
                      "snarl-sharded, no collective"),
-        "l2": "the expression matrix (0.8 GB) and the dosage codes (0.25 GB) exceed the 126 MB L2; gene groups of ~48 MB "
-              "are L2 resident by design, every step streams the rest from HBM, no flush needed",
+        "l2": "the operand images (expression limbs 0.8 GB, dosage 0.9 GB) exceed the 126 MB L2; a gene group (~10 MB) and a "
+              "panel of slot tiles are L2 resident by design, every step streams the rest from HBM, no flush needed",
         "p_threshold": args.p_threshold, "thresholds": {"min_individuals": 3, "min_haplotypes": 5, "maf": 0.05},
     }
 
@@ -163,6 +163,29 @@ def dgemm_peak_tflops(torch, dev, n=8192, reps=5):
     return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
+def int8_peak_tops(torch, dev, n=8192, reps=5):
+    """int8 x int8 -> int32 GEMM through torch._int_mm (cuBLASLt), CUDA events, best of `reps`: the int8 tensor-core roofline
+    of this box in TOP/s (2 ops per multiply-add).  None when the build has no int8 matmul."""
+    try:
+        a = torch.randint(-64, 64, (n, n), device=dev, dtype=torch.int8)
+        b = torch.randint(-64, 64, (n, n), device=dev, dtype=torch.int8)
+        for _ in range(2):
+            torch._int_mm(a, b)
+        torch.cuda.synchronize()
+        best = float("inf")
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch._int_mm(a, b)
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        del a, b
+        return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+    except Exception:
+        return None
+
+
 def parity_spot_check(ctx_summary, d, expr_dev, args, n_check, n_threads, gene0=0):
     """`n_check` snarls SAMPLED at a fixed stride over the timed scan x every gene through the CPU oracle (one OLS per pair,
     as the reference: n_check x G = 10^6 rows at C4), against the device's per-snarl summary: min p (1e-9
@@ -257,6 +280,8 @@ def measure(args, env, ClockSampler, n_threads, with_clocks=True):
     G_local = expr.shape[0]
     # 10 % of the genes depend on a snarl's dosage (simulate_test_dataset.py:75-88): add the alt-path dosage of snarl g
     peak = dgemm_peak_tflops(torch, dev) if rank == 0 else None
+    umma = os.environ.get("STOAT_GPU_EQTL", "") not in ("dmma", "general")
+    peak_i8 = int8_peak_tops(torch, dev) if (rank == 0 and umma) else None
     ctx = stoat_b200.Context(local)
     ctx.set_matrix_dev(d["bits_dev"].data_ptr(), d["n_rows"], d["n_cols"])
     ctx.stage_paths(d["paths"])
@@ -357,18 +382,43 @@ def measure(args, env, ClockSampler, n_threads, with_clocks=True):
     if rank == 0:
         k_ms = float(np.mean(e1_ms))
         flops = 2.0 * n * n_dense * G_local
-        achieved = flops / (k_ms * 1e-3) / 1e12
-        roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                    "traffic": None, "kernel": "eqtl_dense_dmma (E1: DMMA.8x8x4 contraction + per-pair OLS epilogue)",
-                    "algorithmic_flops_per_launch": flops, "kernel_ms": k_ms,
-                    "peak_source": "FP64 GEMM measured live in this run: torch.matmul f64 8192^3 (cuBLAS DGEMM), best of 5, "
-                                   "CUDA events; MEASURED_PEAKS.json carries no FP64 figure",
-                    "snarls_on_tensor_path": n_dense, "snarls_on_general_path": int(n_general),
-                    "other_kernels_ms": {"E0 dosage codes + E2 finish + general-path rest": float(np.mean(rest_ms))}}
+        if umma:
+            # the exact int8 form: 2 d (int8) against the 8 signed 7-bit limbs of the centred expression, INT32 accumulators in
+            # tensor memory.  Algorithmic ops = 8 limb columns per gene; the FP64-equivalent rate is what the FP64 form would need.
+            ops = 8.0 * flops
+            achieved = ops / (k_ms * 1e-3) / 1e12
+            nominal = 4500.0  # dense int8 = dense fp8 on B200 (NVIDIA's 9 POPS figure is 2:4 sparse)
+            pk = peak_i8 if peak_i8 else nominal
+            roofline = {"bound": "tensor", "achieved": achieved, "peak": pk, "unit": "TFLOP/s", "frac": achieved / pk,
+                        "traffic": None,
+                        "kernel": "eqtl_dense_umma (EU1: tcgen05.mma kind::i8, M 128 x N 256 x K 32, accumulators in TMEM, per-pair "
+                                  "OLS epilogue from tcgen05.ld) incl. the expansion of the dosage codes into the A operand",
+                        "ops": "int8 multiply-adds x 2 (TOP/s reported under the contract's TFLOP/s unit)",
+                        "algorithmic_flops_per_launch": ops, "kernel_ms": k_ms,
+                        "peak_source": ("int8 GEMM measured live in this run: torch._int_mm 8192^3 (cuBLASLt), best of 5, CUDA "
+                                        "events" if peak_i8 else "nominal dense int8 rate of B200 (torch._int_mm unavailable)") +
+                                       "; MEASURED_PEAKS.json carries no int8 figure",
+                        "fp64_equivalent": {"tflops": flops / (k_ms * 1e-3) / 1e12, "dgemm_peak_tflops": peak,
+                                            "note": "2 n S G flops, what the FP64 (DMMA) form of the same contraction executes; "
+                                                    "STOAT_GPU_EQTL=dmma runs that form (0.87 of cuBLAS DGEMM, 1.17 s per scan)"},
+                        "limiter": "L2 -> SM operand traffic (48 KB per 4 MMAs: 171 int8 ops per byte against the ~600 the tensor "
+                                   "rate would need), see DESIGN.md",
+                        "snarls_on_tensor_path": n_dense, "snarls_on_general_path": int(n_general),
+                        "other_kernels_ms": {"E0 dosage codes + E2 finish + general-path rest": float(np.mean(rest_ms))}}
+        else:
+            achieved = flops / (k_ms * 1e-3) / 1e12
+            roofline = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                        "traffic": None, "kernel": "eqtl_dense_dmma (E1: DMMA.8x8x4 contraction + per-pair OLS epilogue)",
+                        "algorithmic_flops_per_launch": flops, "kernel_ms": k_ms,
+                        "peak_source": "FP64 GEMM measured live in this run: torch.matmul f64 8192^3 (cuBLAS DGEMM), best of 5, "
+                                       "CUDA events; MEASURED_PEAKS.json carries no FP64 figure",
+                        "snarls_on_tensor_path": n_dense, "snarls_on_general_path": int(n_general),
+                        "other_kernels_ms": {"E0 dosage codes + E2 finish + general-path rest": float(np.mean(rest_ms))}}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
                 "scaling": "strong" if gene_sharded else "weak", "vs_baseline": None,
-                "dtype": "f64 (2-bit dosage codes x f64 expression, DMMA)",
+                "dtype": ("int8 x int8 -> int32 exact contraction (2-bit dosage codes x 8 limbs of the f64 expression, tcgen05), f64 "
+                          "statistics" if umma else "f64 (2-bit dosage codes x f64 expression, DMMA)"),
                 "data": "synthetic (seed 42, drawn on device)", "config": config_dict(args, world), "clocks": clocks,
                 "e2e": e2e, "gpu_launches": int(lsum.item()), "roofline": roofline, "parity": parity}
         if world == 1 and not args.no_cpu_baseline:

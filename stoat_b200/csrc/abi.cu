@@ -1347,7 +1347,10 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     e.s_pad = (S + kEqTileS - 1) / kEqTileS * kEqTileS;
     // a gene group's rows of yc (~48 MB) stay L2 resident while every snarl tile passes over them
     const uint64_t row_bytes = uint64_t(e.n_pad) * 8;
-    uint64_t gpg = std::max<uint64_t>(1, (uint64_t(48) << 20) / row_bytes / kEqTileG) * kEqTileG;
+    // (the tcgen05 form streams 16 KB of A per 32 KB of B and keeps a panel of A images resident too: smaller groups,
+    // measured at C4: 256 / 576 / 1152 / 2304 genes per group 397 / 487 / 518 / 533 ms)
+    const bool umma_form = ctx->eqtl_variant == 0 && n < 65536;
+    uint64_t gpg = std::max<uint64_t>(1, (uint64_t(umma_form ? 10 : 48) << 20) / row_bytes / kEqTileG) * kEqTileG;
     if (const char* v = std::getenv("STOAT_GPU_EQTL_GROUP")) gpg = std::max<uint64_t>(1, uint64_t(std::atoll(v)) / kEqTileG) * kEqTileG;
     e.genes_per_group = uint32_t(std::min<uint64_t>(gpg, (G + kEqTileG - 1) / kEqTileG * kEqTileG));
     e.n_groups = uint32_t((G + e.genes_per_group - 1) / e.genes_per_group);
@@ -1384,6 +1387,12 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
         um.b_img = x->um_b.as<uint8_t>();
         um.scale = x->um_scale.as<double>();
         um.probe_out = nullptr;
+        um.panel = 64;
+        um.split = 0;   // measured at C4: one copy per operand image 211 ms, 24 copies of 2 KB + rotated K order 239 ms
+        um.rotate = 0;
+        if (const char* v = std::getenv("STOAT_GPU_EQTL_SPLIT")) um.split = uint32_t(std::atoi(v));
+        if (const char* v = std::getenv("STOAT_GPU_EQTL_ROTATE")) um.rotate = uint32_t(std::atoi(v));
+        if (const char* v = std::getenv("STOAT_GPU_EQTL_PANEL")) um.panel = uint32_t(std::max(1, std::atoi(v)));
     }
 
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));

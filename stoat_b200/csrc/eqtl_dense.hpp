@@ -60,6 +60,8 @@ struct EqtlUmma {
     const uint8_t* b_img;  // [gene tiles][n_kb][32 KB]   limbs of the centred expression, same
     const double* scale;   // [n_genes]
     uint32_t n_kb;         // n_pad / 128
+    uint32_t split, rotate; // producer: 24 copies of 2 KB per stage instead of two; K blocks rotated by the slot tile
+    uint32_t panel;        // slot tiles per panel of the CTA order (0 / 1: slot tile fastest over the whole grid)
     int32_t* probe_out;    // tests: raw accumulators [128][gene tiles * 32][8] of slot tile 0 instead of the statistics
 };
 cudaError_t launch_eqtl_umma_prepare_expression(const double* yc, uint32_t n_genes, uint32_t n_pad, double* scale,

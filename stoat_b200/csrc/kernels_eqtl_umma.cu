@@ -131,6 +131,7 @@ __global__ void __launch_bounds__(256) eqtl_expand_codes_kernel(const uint8_t* _
 // =================================================================================================
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync_um(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols)
                  : "memory");
@@ -159,6 +160,18 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, int32_t (&v)[8]) {
                  : "r"(taddr));
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+// 32 consecutive columns (four genes' limbs)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, int32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, "
+        "%18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+          "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+          "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
 // shared-memory operand descriptor: K-major rows of 128 bytes, 128-byte swizzle, 8-row groups 1024 bytes apart
 // (cute::UMMA::SmemDescriptor: start >> 4 at [0,14), LBO >> 4 at [16,30) = 1, SBO >> 4 at [32,46) = 64, version 1 at
 // [46,48), layout SWIZZLE_128B = 2 at [61,64)); advancing K by 32 int8 inside the swizzle atom = + 32 bytes = + 2
@@ -182,6 +195,7 @@ struct UmSmem {
     uint32_t tmem_base, pad_;
     EqConst k;
     EqtlRec rec[kUmTileS];
+    double gconst[2][kUmTileG][3];  // per gene of the tile in flight: sum yc, sum yc^2, limb scale (one buffer per accumulator)
 };
 constexpr size_t kUmStageOff = (sizeof(UmSmem) + 1023) / 1024 * 1024;
 size_t eqtl_umma_smem_bytes() { return kUmStageOff + size_t(kUmStages) * kUmStageBytes + 1024; }
@@ -193,10 +207,18 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
     UmSmem& sm = *reinterpret_cast<UmSmem*>(base);
     uint8_t* stages = base + kUmStageOff;
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint64_t s0 = uint64_t(blockIdx.x) * kUmTileS;
+    // CTA order: panels of `panel` slot tiles; inside a panel the slot tile runs fastest, then the gene group.  The ~148 CTAs in
+    // flight are then `panel` slot tiles x a few gene groups: their A images (panel x 655 KB at C4) and B groups stay L2 resident
+    // while the panel passes over every gene group, instead of 148 different A tiles competing with one B group.
+    const uint32_t n_st = uint32_t(e.s_pad / kUmTileS), panel = u.panel ? u.panel : 1u;
+    const uint32_t per_panel = panel * e.n_groups;
+    const uint32_t pn = blockIdx.x / per_panel, in_p = blockIdx.x % per_panel;
+    const uint32_t rows_here = min(panel, n_st - pn * panel);  // the last panel may be short
+    const uint32_t slot_tile = pn * panel + in_p % rows_here, grp = in_p / rows_here;
+    if (grp >= e.n_groups) return;
+    const uint64_t s0 = uint64_t(slot_tile) * kUmTileS;
     const uint32_t n_dense = u.probe_out ? uint32_t(kUmTileS) : *e.dense_count;
     if (s0 >= n_dense) return;  // whole CTA: nothing allocated yet
-    const uint32_t grp = blockIdx.y;
     const uint32_t g_begin = grp * e.genes_per_group;
     const uint32_t g_end = min(e.n_genes, g_begin + e.genes_per_group);
     const uint32_t n_gt = (g_end - g_begin + kUmTileG - 1) / kUmTileG;
@@ -226,17 +248,29 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
     const uint32_t tmem = sm.tmem_base;
 
     if (warp == 4) {
-        // ---------------- producer
-        if (lane == 0) {
-            uint32_t it = 0;
-            for (uint32_t gt = 0; gt < n_gt; ++gt) {
-                const uint8_t* b_src = u.b_img + (uint64_t(g_begin / kUmTileG + gt) * n_kb) * kUmBBytes;
-                const uint8_t* a_src = u.a_img + (uint64_t(blockIdx.x) * n_kb) * kUmABytes;
-                for (uint32_t kb = 0; kb < n_kb; ++kb, ++it) {
-                    const uint32_t st = it % kUmStages, round = it / kUmStages;
-                    if (round) mbar_wait(&sm.empty[st], (round - 1) & 1);
-                    uint8_t* dst = stages + size_t(st) * kUmStageBytes;
-                    mbar_arrive_expect_tx(&sm.full[st], kUmStageBytes);
+        // ---------------- producer (the whole warp: lane 0 keeps the barriers, every lane copies a slice of the stage)
+        // The 128-sample blocks are taken in an order rotated by the CTA's slot tile: the sum is exact in any order, and the
+        // CTAs that share a gene group then ask the L2 for different blocks of it at any one time instead of all for the same.
+        uint32_t it = 0;
+        const uint32_t rot = u.rotate ? (slot_tile * 7u) % n_kb : 0u;
+        const uint32_t piece = 2048;  // 24 lanes copy 2 KB each: 8 pieces of the A image, 16 of the B image
+        for (uint32_t gt = 0; gt < n_gt; ++gt) {
+            const uint8_t* b_src = u.b_img + (uint64_t(g_begin / kUmTileG + gt) * n_kb) * kUmBBytes;
+            const uint8_t* a_src = u.a_img + (uint64_t(slot_tile) * n_kb) * kUmABytes;
+            for (uint32_t kq = 0; kq < n_kb; ++kq, ++it) {
+                const uint32_t kb = kq + rot < n_kb ? kq + rot : kq + rot - n_kb;
+                const uint32_t st = it % kUmStages, round = it / kUmStages;
+                if (round) mbar_wait(&sm.empty[st], (round - 1) & 1);
+                uint8_t* dst = stages + size_t(st) * kUmStageBytes;
+                if (lane == 0) mbar_arrive_expect_tx(&sm.full[st], kUmStageBytes);
+                __syncwarp();
+                if (u.split) {
+                    if (lane >= uint32_t(kUmStageBytes) / piece) continue;
+                    const uint32_t off = lane * piece;  // A image [0, 16 KB), B image [16 KB, 48 KB): pieces do not straddle
+                    const uint8_t* src = off < uint32_t(kUmABytes) ? a_src + uint64_t(kb) * kUmABytes + off
+                                                                   : b_src + uint64_t(kb) * kUmBBytes + (off - kUmABytes);
+                    tma_bulk_g2s(dst + off, src, piece, &sm.full[st]);
+                } else if (lane == 0) {
                     tma_bulk_g2s(dst, a_src + uint64_t(kb) * kUmABytes, kUmABytes, &sm.full[st]);
                     tma_bulk_g2s(dst + kUmABytes, b_src + uint64_t(kb) * kUmBBytes, kUmBBytes, &sm.full[st]);
                 }
@@ -266,36 +300,88 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
         }
     } else {
         // ---------------- epilogue: thread = slot (TMEM lane), all gene tiles of the group
+        // The per-pair tail of linear_regression for X = [1, d] (stats_test.cpp:455-489, as eq_pair_stat in eqtl_pair.cuh) with
+        // the slot's record in registers and the gene's constants in shared memory: with four warps per SM nothing hides a
+        // dependent global load per pair.  Ranking is by t^2 = b1^2 / (inv11 * rss / df) (one division, no square root); the
+        // exact Student-t tail only for pairs beyond the normal-tail bound of the threshold.
         const uint32_t sl = tid;  // 0 .. 127
-        const EqtlRec* r = &sm.rec[sl];
-        double bk = -1.0;
+        const EqtlRec rr = sm.rec[sl];
+        const bool live = rr.state == 1;
+        const double n_used = double(rr.n_used);
+        int df_res = int(rr.n_used) - 2 + 1;  // stats_test.cpp:467 (sic)
+        if (df_res < 1) df_res = 1;
+        const double dfd = double(df_res), z2 = sm.k.z_threshold * sm.k.z_threshold;
+        const bool z_all = !(sm.k.z_threshold > 0.0);  // a threshold of 1 or more: every |t| has to be looked at
+        double bk2 = -1.0;
         uint32_t bg = 0xFFFFFFFFu, cnt = 0;
         for (uint32_t gt = 0; gt < n_gt; ++gt) {
             const uint32_t acc = gt & 1;
+            const uint32_t g_tile = g_begin + gt * kUmTileG;
+            if (!u.probe_out && lane < 8) {  // this warp stages the constants of genes [8 warp, 8 warp + 8)
+                const uint32_t gl = warp * 8 + lane, g = min(g_tile + gl, e.n_genes - 1);
+                sm.gconst[acc][gl][0] = e.tot[g];
+                sm.gconst[acc][gl][1] = e.tot2[g];
+                sm.gconst[acc][gl][2] = u.scale[g];
+            }
+            named_bar_sync_um(1, 128);
             mbar_wait(&sm.tfull[acc], (gt >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem + ((warp * 32u) << 16) + acc * kUmTileN;
-            const uint32_t g_tile = g_begin + gt * kUmTileG;
 #pragma unroll 1
-            for (uint32_t gl = 0; gl < uint32_t(kUmTileG); ++gl) {
-                int32_t c[8];
-                tmem_ld8(taddr + gl * 8, c);  // warp-collective: every lane takes part, whatever its slot's state
-                const uint32_t g = g_tile + gl;
+            for (uint32_t gb = 0; gb < uint32_t(kUmTileG) / 4; ++gb) {
+                int32_t c[32];
+                tmem_ld32(taddr + gb * 32, c);  // warp-collective: every lane takes part, whatever its slot's state
                 if (u.probe_out) {
 #pragma unroll
-                    for (int l = 0; l < 8; ++l) u.probe_out[(uint64_t(sl) * n_gt * kUmTileG + gt * kUmTileG + gl) * 8 + l] = c[l];
+                    for (int l = 0; l < 32; ++l)
+                        u.probe_out[(uint64_t(sl) * n_gt * kUmTileG + gt * kUmTileG + gb * 4) * 8 + l] = c[l];
                     continue;
                 }
-                if (g < g_end && r->state == 1) {
+                if (!live) continue;
+                double sy[4], syy[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    sy[j] = sm.gconst[acc][gb * 4 + j][0];
+                    syy[j] = sm.gconst[acc][gb * 4 + j][1];
+                }
+                for (uint32_t q = 0; q < rr.n_unused; ++q) {  // samples on no path are not rows of the table
+                    const uint32_t iu = rr.unused[q];
+                    double y[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)  // four independent loads in flight
+                        y[j] = e.yc[uint64_t(min(g_tile + gb * 4 + j, e.n_genes - 1)) * e.n_pad + iu];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        sy[j] -= y[j];
+                        syy[j] = fma(-y[j], y[j], syy[j]);
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t g = g_tile + gb * 4 + j;
+                    if (g >= g_end) continue;
                     double v = 0.0;
 #pragma unroll
-                    for (int l = 7; l >= 0; --l) v = (v + double(c[l])) * 0.0078125;  // Horner over the limbs, 128^-1 exact
-                    const double sdy = 0.5 * u.scale[g] * v;
-                    const double key = eq_pair_stat(&sm.k, r, s0 + sl, g, sdy);  // < 0: also below the threshold
-                    const double ak = fabs(key) - 1.0;
-                    cnt += key < 0.0 ? 1u : 0u;
-                    if (ak > bk || (ak == bk && g < bg)) {
-                        bk = ak;
+                    for (int l = 7; l >= 0; --l) v = (v + double(c[8 * j + l])) * 0.0078125;  // Horner over the limbs
+                    const double sdy = 0.5 * sm.gconst[acc][gb * 4 + j][2] * v;
+                    const double b0 = rr.inv00 * sy[j] + rr.inv01 * sdy, b1 = rr.inv01 * sy[j] + rr.inv11 * sdy;
+                    const double bxy = b0 * sy[j] + b1 * sdy;
+                    const double bxxb = b0 * (n_used * b0 + rr.sd * b1) + b1 * (rr.sd * b0 + rr.sdd * b1);
+                    double rss = syy[j] - 2.0 * bxy + bxxb;
+                    const double tss = syy[j] - sy[j] * sy[j] / n_used;
+                    if (!(rss > 1e-6 * tss))
+                        rss = eq_rss_explicit(e.yc + uint64_t(g) * e.n_pad, e.dcode + (s0 + sl) * 16, e.s_pad, e.n_samples, &sm.rec[sl],
+                                              b0, b1);
+                    const double den = rr.inv11 * (rss / dfd);
+                    const double t2 = (b1 * b1) / den;
+                    const bool fin = den > 0.0 && t2 < __longlong_as_double(0x7ff0000000000000LL);  // t finite (:480-482)
+                    const double k2 = fin ? t2 : 0.0;
+                    bool below;
+                    if (fin) below = (z_all || k2 > z2) && 2.0 * student_t_upper_tail(dfd, sqrt(k2)) < sm.k.p_threshold;
+                    else below = 1.0 < sm.k.p_threshold;
+                    cnt += below ? 1u : 0u;
+                    if (k2 > bk2 || (k2 == bk2 && g < bg)) {
+                        bk2 = k2;
                         bg = g;
                     }
                 }
@@ -305,7 +391,7 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
         }
         if (!u.probe_out) {
             const uint64_t o = uint64_t(grp) * e.s_pad + s0 + sl;
-            e.part_key[o] = bk;
+            e.part_key[o] = bk2 < 0.0 ? -1.0 : sqrt(bk2);  // |t| of the best gene, as the FP64 kernel reports it
             e.part_gene[o] = bg;
             e.part_cnt[o] = cnt;
         }
@@ -340,8 +426,9 @@ cudaError_t launch_eqtl_dense_umma(const EqtlDense& e, const EqtlUmma& u, cudaSt
     const int smem = int(eqtl_umma_smem_bytes());
     err = cudaFuncSetAttribute(eqtl_dense_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (err != cudaSuccess) return err;
-    dim3 grid(unsigned(e.s_pad / kUmTileS), e.n_groups);
-    eqtl_dense_umma_kernel<<<grid, kUmThreads, smem, st>>>(e, u);
+    const uint64_t n_st = e.s_pad / kUmTileS, panel = u.panel ? u.panel : 1;
+    const uint64_t n_panels = (n_st + panel - 1) / panel;
+    eqtl_dense_umma_kernel<<<unsigned(n_panels * panel * e.n_groups), kUmThreads, smem, st>>>(e, u);
     return cudaGetLastError();
 }
 
