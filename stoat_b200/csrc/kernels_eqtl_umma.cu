@@ -172,6 +172,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, int32_t (&v)[32]) {
         : "r"(taddr));
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+// 1 / d to ~1 ulp (MUFU.RCP64H seed + two Newton steps), d positive and finite; anything else gives a value the caller's
+// `den > 0 && t2 < inf` test rejects or accepts correctly (0 -> inf, inf -> 0, NaN -> NaN)
+__device__ __forceinline__ double um_rcp(double d) {
+    double x;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(d));
+    double e = fma(-d, x, 1.0);
+    x = fma(x, e, x);
+    e = fma(-d, x, 1.0);
+    return fma(x, e, x);
+}
 // shared-memory operand descriptor: K-major rows of 128 bytes, 128-byte swizzle, 8-row groups 1024 bytes apart
 // (cute::UMMA::SmemDescriptor: start >> 4 at [0,14), LBO >> 4 at [16,30) = 1, SBO >> 4 at [32,46) = 64, version 1 at
 // [46,48), layout SWIZZLE_128B = 2 at [61,64)); advancing K by 32 int8 inside the swizzle atom = + 32 bytes = + 2
@@ -188,7 +198,10 @@ constexpr uint32_t kUmIdesc = (2u << 4) | (1u << 7) | (1u << 10) | (uint32_t(kUm
 // =================================================================================================
 constexpr int kUmStages = 4;
 constexpr int kUmStageBytes = kUmABytes + kUmBBytes;  // 49,152
-constexpr int kUmThreads = 192;                       // warps 0-3 epilogue, 4 producer, 5 MMA
+constexpr int kUmEpiWarps = 8;                        // two warps per TMEM lane quarter, each takes half of a tile's genes
+constexpr int kUmEpiThreads = kUmEpiWarps * 32;
+constexpr int kUmProducerWarp = kUmEpiWarps, kUmMmaWarp = kUmEpiWarps + 1;
+constexpr int kUmThreads = (kUmEpiWarps + 2) * 32;    // warps 0-7 epilogue, 8 producer, 9 MMA
 
 struct UmSmem {
     uint64_t full[kUmStages], empty[kUmStages], tfull[2], tempty[2];
@@ -196,6 +209,8 @@ struct UmSmem {
     EqConst k;
     EqtlRec rec[kUmTileS];
     double gconst[2][kUmTileG][3];  // per gene of the tile in flight: sum yc, sum yc^2, limb scale (one buffer per accumulator)
+    double half_key[kUmTileS];      // the upper gene half's best t^2 / gene / count per slot, merged by the lower half's thread
+    uint32_t half_gene[kUmTileS], half_cnt[kUmTileS];
 };
 constexpr size_t kUmStageOff = (sizeof(UmSmem) + 1023) / 1024 * 1024;
 size_t eqtl_umma_smem_bytes() { return kUmStageOff + size_t(kUmStages) * kUmStageBytes + 1024; }
@@ -231,7 +246,7 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&sm.tfull[i], 1);
-            mbar_init(&sm.tempty[i], 128);
+            mbar_init(&sm.tempty[i], kUmEpiThreads);
         }
         mbar_fence_init();
         sm.k = EqConst{e.yc, e.tot, e.tot2, e.dcode, e.s_pad, e.n_pad, e.n_samples, e.p_threshold, e.z_threshold};
@@ -241,13 +256,13 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
             const bool live = s0 + i / (sizeof(EqtlRec) / 16) < n_dense;
             reinterpret_cast<uint4*>(sm.rec)[i] = live ? reinterpret_cast<const uint4*>(e.rec + s0)[i] : make_uint4(0, 0, 0, 0);
         }
-    if (warp == 5) tmem_alloc(&sm.tmem_base, 512);  // two accumulators of 256 columns: the whole tensor memory of the SM
+    if (warp == kUmMmaWarp) tmem_alloc(&sm.tmem_base, 512);  // two accumulators of 256 columns: the whole tensor memory of the SM
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = sm.tmem_base;
 
-    if (warp == 4) {
+    if (warp == kUmProducerWarp) {
         // ---------------- producer (the whole warp: lane 0 keeps the barriers, every lane copies a slice of the stage)
         // The 128-sample blocks are taken in an order rotated by the CTA's slot tile: the sum is exact in any order, and the
         // CTAs that share a gene group then ask the L2 for different blocks of it at any one time instead of all for the same.
@@ -276,7 +291,7 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
                 }
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == kUmMmaWarp) {
         // ---------------- MMA issuer (one thread)
         if (lane == 0) {
             uint32_t it = 0;
@@ -304,7 +319,8 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
         // the slot's record in registers and the gene's constants in shared memory: with four warps per SM nothing hides a
         // dependent global load per pair.  Ranking is by t^2 = b1^2 / (inv11 * rss / df) (one division, no square root); the
         // exact Student-t tail only for pairs beyond the normal-tail bound of the threshold.
-        const uint32_t sl = tid;  // 0 .. 127
+        const uint32_t sl = tid & 127u;       // slot = TMEM lane; a warp reaches the lanes 32 (warp % 4) .. + 31
+        const uint32_t ghalf = tid >> 7;      // 0: genes 0-15 of every tile, 1: genes 16-31
         const EqtlRec rr = sm.rec[sl];
         const bool live = rr.state == 1;
         const double n_used = double(rr.n_used);
@@ -312,76 +328,107 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
         if (df_res < 1) df_res = 1;
         const double dfd = double(df_res), z2 = sm.k.z_threshold * sm.k.z_threshold;
         const bool z_all = !(sm.k.z_threshold > 0.0);  // a threshold of 1 or more: every |t| has to be looked at
+        const double inf = __longlong_as_double(0x7ff0000000000000LL), inv_n = 1.0 / n_used;
         double bk2 = -1.0;
         uint32_t bg = 0xFFFFFFFFu, cnt = 0;
         for (uint32_t gt = 0; gt < n_gt; ++gt) {
             const uint32_t acc = gt & 1;
             const uint32_t g_tile = g_begin + gt * kUmTileG;
-            if (!u.probe_out && lane < 8) {  // this warp stages the constants of genes [8 warp, 8 warp + 8)
-                const uint32_t gl = warp * 8 + lane, g = min(g_tile + gl, e.n_genes - 1);
+            if (!u.probe_out && lane < 4) {  // this warp stages the constants of genes [4 warp, 4 warp + 4)
+                const uint32_t gl = warp * 4 + lane, g = min(g_tile + gl, e.n_genes - 1);
                 sm.gconst[acc][gl][0] = e.tot[g];
                 sm.gconst[acc][gl][1] = e.tot2[g];
                 sm.gconst[acc][gl][2] = u.scale[g];
             }
-            named_bar_sync_um(1, 128);
+            named_bar_sync_um(1, kUmEpiThreads);
             mbar_wait(&sm.tfull[acc], (gt >> 1) & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem + ((warp * 32u) << 16) + acc * kUmTileN;
+            const uint32_t taddr = tmem + (((warp & 3u) * 32u) << 16) + acc * kUmTileN + ghalf * (kUmTileN / 2);
 #pragma unroll 1
-            for (uint32_t gb = 0; gb < uint32_t(kUmTileG) / 4; ++gb) {
+            for (uint32_t gb = 0; gb < uint32_t(kUmTileG) / 8; ++gb) {
                 int32_t c[32];
                 tmem_ld32(taddr + gb * 32, c);  // warp-collective: every lane takes part, whatever its slot's state
+                const uint32_t gl0 = ghalf * (kUmTileG / 2) + gb * 4;  // first of the four genes, within the tile
                 if (u.probe_out) {
 #pragma unroll
-                    for (int l = 0; l < 32; ++l)
-                        u.probe_out[(uint64_t(sl) * n_gt * kUmTileG + gt * kUmTileG + gb * 4) * 8 + l] = c[l];
+                    for (int l = 0; l < 32; ++l) u.probe_out[(uint64_t(sl) * n_gt * kUmTileG + gt * kUmTileG + gl0) * 8 + l] = c[l];
                     continue;
                 }
                 if (!live) continue;
-                double sy[4], syy[4];
+                double sy[4], syy[4], sdy[4], b0[4], b1[4], rss[4], k2[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    sy[j] = sm.gconst[acc][gb * 4 + j][0];
-                    syy[j] = sm.gconst[acc][gb * 4 + j][1];
+                    sy[j] = sm.gconst[acc][gl0 + j][0];
+                    syy[j] = sm.gconst[acc][gl0 + j][1];
                 }
                 for (uint32_t q = 0; q < rr.n_unused; ++q) {  // samples on no path are not rows of the table
                     const uint32_t iu = rr.unused[q];
                     double y[4];
 #pragma unroll
                     for (int j = 0; j < 4; ++j)  // four independent loads in flight
-                        y[j] = e.yc[uint64_t(min(g_tile + gb * 4 + j, e.n_genes - 1)) * e.n_pad + iu];
+                        y[j] = e.yc[uint64_t(min(g_tile + gl0 + j, e.n_genes - 1)) * e.n_pad + iu];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         sy[j] -= y[j];
                         syy[j] = fma(-y[j], y[j], syy[j]);
                     }
                 }
+                // the four genes in lock step, stage by stage: four independent dependency chains for the FP64 pipe
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const uint32_t g = g_tile + gb * 4 + j;
-                    if (g >= g_end) continue;
+                    // sum_l C_l 128^-(l+1): every product is exact (a power of two times an integer below 2^21), smallest first
                     double v = 0.0;
 #pragma unroll
-                    for (int l = 7; l >= 0; --l) v = (v + double(c[8 * j + l])) * 0.0078125;  // Horner over the limbs
-                    const double sdy = 0.5 * sm.gconst[acc][gb * 4 + j][2] * v;
-                    const double b0 = rr.inv00 * sy[j] + rr.inv01 * sdy, b1 = rr.inv01 * sy[j] + rr.inv11 * sdy;
-                    const double bxy = b0 * sy[j] + b1 * sdy;
-                    const double bxxb = b0 * (n_used * b0 + rr.sd * b1) + b1 * (rr.sd * b0 + rr.sdd * b1);
-                    double rss = syy[j] - 2.0 * bxy + bxxb;
-                    const double tss = syy[j] - sy[j] * sy[j] / n_used;
-                    if (!(rss > 1e-6 * tss))
-                        rss = eq_rss_explicit(e.yc + uint64_t(g) * e.n_pad, e.dcode + (s0 + sl) * 16, e.s_pad, e.n_samples, &sm.rec[sl],
-                                              b0, b1);
-                    const double den = rr.inv11 * (rss / dfd);
-                    const double t2 = (b1 * b1) / den;
-                    const bool fin = den > 0.0 && t2 < __longlong_as_double(0x7ff0000000000000LL);  // t finite (:480-482)
-                    const double k2 = fin ? t2 : 0.0;
-                    bool below;
-                    if (fin) below = (z_all || k2 > z2) && 2.0 * student_t_upper_tail(dfd, sqrt(k2)) < sm.k.p_threshold;
-                    else below = 1.0 < sm.k.p_threshold;
-                    cnt += below ? 1u : 0u;
-                    if (k2 > bk2 || (k2 == bk2 && g < bg)) {
-                        bk2 = k2;
+                    for (int l = 7; l >= 0; --l) v = fma(double(c[8 * j + l]), __hiloint2double((1023 - 7 * (l + 1)) << 20, 0), v);
+                    sdy[j] = 0.5 * sm.gconst[acc][gl0 + j][2] * v;
+                }
+                bool redo = false;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    b0[j] = rr.inv00 * sy[j] + rr.inv01 * sdy[j];
+                    b1[j] = rr.inv01 * sy[j] + rr.inv11 * sdy[j];
+                    const double bxy = b0[j] * sy[j] + b1[j] * sdy[j];
+                    const double bxxb = b0[j] * (n_used * b0[j] + rr.sd * b1[j]) + b1[j] * (rr.sd * b0[j] + rr.sdd * b1[j]);
+                    rss[j] = syy[j] - 2.0 * bxy + bxxb;
+                    const double tss = syy[j] - sy[j] * sy[j] * inv_n;  // only decides which form of rss is taken
+                    if (!(rss[j] > 1e-6 * tss)) {
+                        rss[j] = -1.0;  // marker: the moment expansion has lost its digits (near-perfect fit)
+                        redo = true;
+                    }
+                }
+                if (redo) {
+#pragma unroll 1
+                    for (int j = 0; j < 4; ++j)
+                        if (rss[j] == -1.0 && g_tile + gl0 + j < g_end)
+                            rss[j] = eq_rss_explicit(e.yc + uint64_t(g_tile + gl0 + j) * e.n_pad, e.dcode + (s0 + sl) * 16, e.s_pad,
+                                                     e.n_samples, &sm.rec[sl], b0[j], b1[j]);
+                }
+                bool look = z_all;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const double den = rr.inv11 * (rss[j] / dfd);
+                    const double t2 = (b1[j] * b1[j]) * um_rcp(den);  // ~1 ulp; |t| is reported to 1e-9
+                    const bool valid = g_tile + gl0 + j < g_end;
+                    const bool fin = den > 0.0 && t2 < inf;  // t finite (:480-482), else p = 1
+                    k2[j] = !valid ? -2.0 : fin ? t2 : -0.5;  // -0.5: invalid t, ranks as t = 0
+                    look = look || k2[j] > z2 || (k2[j] == -0.5 && 1.0 < sm.k.p_threshold);
+                }
+                if (look) {  // rare at a genome-wide threshold: the exact Student-t tail decides
+#pragma unroll 1
+                    for (int j = 0; j < 4; ++j) {
+                        if (k2[j] == -2.0) continue;
+                        bool below;
+                        if (k2[j] >= 0.0) below = (z_all || k2[j] > z2) && 2.0 * student_t_upper_tail(dfd, sqrt(k2[j])) < sm.k.p_threshold;
+                        else below = 1.0 < sm.k.p_threshold;
+                        cnt += below ? 1u : 0u;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const double kk = k2[j] == -0.5 ? 0.0 : k2[j];  // (-2: not a gene, never the best)
+                    const uint32_t g = g_tile + gl0 + j;
+                    if (kk > bk2 || (kk == bk2 && kk >= 0.0 && g < bg)) {
+                        bk2 = kk;
                         bg = g;
                     }
                 }
@@ -390,15 +437,31 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
             mbar_arrive(&sm.tempty[acc]);
         }
         if (!u.probe_out) {
-            const uint64_t o = uint64_t(grp) * e.s_pad + s0 + sl;
-            e.part_key[o] = bk2 < 0.0 ? -1.0 : sqrt(bk2);  // |t| of the best gene, as the FP64 kernel reports it
-            e.part_gene[o] = bg;
-            e.part_cnt[o] = cnt;
+            // the two gene halves of a slot: the upper one hands over through shared memory
+            if (ghalf == 1) {
+                sm.half_key[sl] = bk2;
+                sm.half_gene[sl] = bg;
+                sm.half_cnt[sl] = cnt;
+            }
+            named_bar_sync_um(1, kUmEpiThreads);
+            if (ghalf == 0) {
+                const double ok = sm.half_key[sl];
+                const uint32_t og = sm.half_gene[sl];
+                cnt += sm.half_cnt[sl];
+                if (ok > bk2 || (ok == bk2 && og < bg)) {
+                    bk2 = ok;
+                    bg = og;
+                }
+                const uint64_t o = uint64_t(grp) * e.s_pad + s0 + sl;
+                e.part_key[o] = bk2 < 0.0 ? -1.0 : sqrt(bk2);  // |t| of the best gene, as the FP64 kernel reports it
+                e.part_gene[o] = bg;
+                e.part_cnt[o] = cnt;
+            }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 5) tmem_dealloc(tmem, 512);
+    if (warp == kUmMmaWarp) tmem_dealloc(tmem, 512);
 }
 
 cudaError_t launch_eqtl_umma_prepare_expression(const double* yc, uint32_t n_genes, uint32_t n_pad, double* scale,
