@@ -196,9 +196,12 @@ constexpr uint32_t kUmIdesc = (2u << 4) | (1u << 7) | (1u << 10) | (uint32_t(kUm
 // =================================================================================================
 // EU1
 // =================================================================================================
+#ifndef STOAT_UM_EPI_WARPS
+#define STOAT_UM_EPI_WARPS 8
+#endif
 constexpr int kUmStages = 4;
 constexpr int kUmStageBytes = kUmABytes + kUmBBytes;  // 49,152
-constexpr int kUmEpiWarps = 8;                        // two warps per TMEM lane quarter, each takes half of a tile's genes
+constexpr int kUmEpiWarps = STOAT_UM_EPI_WARPS;                        // two warps per TMEM lane quarter, each takes half of a tile's genes
 constexpr int kUmEpiThreads = kUmEpiWarps * 32;
 constexpr int kUmProducerWarp = kUmEpiWarps, kUmMmaWarp = kUmEpiWarps + 1;
 constexpr int kUmThreads = (kUmEpiWarps + 2) * 32;    // warps 0-7 epilogue, 8 producer, 9 MMA
@@ -209,8 +212,9 @@ struct UmSmem {
     EqConst k;
     EqtlRec rec[kUmTileS];
     double gconst[2][kUmTileG][3];  // per gene of the tile in flight: sum yc, sum yc^2, limb scale (one buffer per accumulator)
-    double half_key[kUmTileS];      // the upper gene half's best t^2 / gene / count per slot, merged by the lower half's thread
-    uint32_t half_gene[kUmTileS], half_cnt[kUmTileS];
+    // the other gene parts' best t^2 / gene / count per slot, merged by part 0's thread
+    double half_key[kUmEpiWarps / 4][kUmTileS];
+    uint32_t half_gene[kUmEpiWarps / 4][kUmTileS], half_cnt[kUmEpiWarps / 4][kUmTileS];
 };
 constexpr size_t kUmStageOff = (sizeof(UmSmem) + 1023) / 1024 * 1024;
 size_t eqtl_umma_smem_bytes() { return kUmStageOff + size_t(kUmStages) * kUmStageBytes + 1024; }
@@ -320,7 +324,8 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
         // dependent global load per pair.  Ranking is by t^2 = b1^2 / (inv11 * rss / df) (one division, no square root); the
         // exact Student-t tail only for pairs beyond the normal-tail bound of the threshold.
         const uint32_t sl = tid & 127u;       // slot = TMEM lane; a warp reaches the lanes 32 (warp % 4) .. + 31
-        const uint32_t ghalf = tid >> 7;      // 0: genes 0-15 of every tile, 1: genes 16-31
+        const uint32_t ghalf = tid >> 7;      // which part of a tile's genes (kUmEpiWarps / 4 parts)
+        constexpr uint32_t kParts = kUmEpiWarps / 4, kPartGenes = kUmTileG / kParts;
         const EqtlRec rr = sm.rec[sl];
         const bool live = rr.state == 1;
         const double n_used = double(rr.n_used);
@@ -334,8 +339,8 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
         for (uint32_t gt = 0; gt < n_gt; ++gt) {
             const uint32_t acc = gt & 1;
             const uint32_t g_tile = g_begin + gt * kUmTileG;
-            if (!u.probe_out && lane < 4) {  // this warp stages the constants of genes [4 warp, 4 warp + 4)
-                const uint32_t gl = warp * 4 + lane, g = min(g_tile + gl, e.n_genes - 1);
+            if (!u.probe_out && lane < uint32_t(kUmTileG) / kUmEpiWarps) {  // this warp stages the constants of its share of the genes
+                const uint32_t gl = warp * (kUmTileG / kUmEpiWarps) + lane, g = min(g_tile + gl, e.n_genes - 1);
                 sm.gconst[acc][gl][0] = e.tot[g];
                 sm.gconst[acc][gl][1] = e.tot2[g];
                 sm.gconst[acc][gl][2] = u.scale[g];
@@ -343,12 +348,12 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
             named_bar_sync_um(1, kUmEpiThreads);
             mbar_wait(&sm.tfull[acc], (gt >> 1) & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem + (((warp & 3u) * 32u) << 16) + acc * kUmTileN + ghalf * (kUmTileN / 2);
+            const uint32_t taddr = tmem + (((warp & 3u) * 32u) << 16) + acc * kUmTileN + ghalf * (kPartGenes * 8);
 #pragma unroll 1
-            for (uint32_t gb = 0; gb < uint32_t(kUmTileG) / 8; ++gb) {
+            for (uint32_t gb = 0; gb < kPartGenes / 4; ++gb) {
                 int32_t c[32];
                 tmem_ld32(taddr + gb * 32, c);  // warp-collective: every lane takes part, whatever its slot's state
-                const uint32_t gl0 = ghalf * (kUmTileG / 2) + gb * 4;  // first of the four genes, within the tile
+                const uint32_t gl0 = ghalf * kPartGenes + gb * 4;  // first of the four genes, within the tile
                 if (u.probe_out) {
 #pragma unroll
                     for (int l = 0; l < 32; ++l) u.probe_out[(uint64_t(sl) * n_gt * kUmTileG + gt * kUmTileG + gl0) * 8 + l] = c[l];
@@ -438,19 +443,21 @@ __global__ void __launch_bounds__(kUmThreads, 1) eqtl_dense_umma_kernel(const Eq
         }
         if (!u.probe_out) {
             // the two gene halves of a slot: the upper one hands over through shared memory
-            if (ghalf == 1) {
-                sm.half_key[sl] = bk2;
-                sm.half_gene[sl] = bg;
-                sm.half_cnt[sl] = cnt;
+            if (ghalf != 0) {
+                sm.half_key[ghalf][sl] = bk2;
+                sm.half_gene[ghalf][sl] = bg;
+                sm.half_cnt[ghalf][sl] = cnt;
             }
             named_bar_sync_um(1, kUmEpiThreads);
             if (ghalf == 0) {
-                const double ok = sm.half_key[sl];
-                const uint32_t og = sm.half_gene[sl];
-                cnt += sm.half_cnt[sl];
-                if (ok > bk2 || (ok == bk2 && og < bg)) {
-                    bk2 = ok;
-                    bg = og;
+                for (uint32_t h = 1; h < kParts; ++h) {
+                    const double ok = sm.half_key[h][sl];
+                    const uint32_t og = sm.half_gene[h][sl];
+                    cnt += sm.half_cnt[h][sl];
+                    if (ok > bk2 || (ok == bk2 && og < bg)) {
+                        bk2 = ok;
+                        bg = og;
+                    }
                 }
                 const uint64_t o = uint64_t(grp) * e.s_pad + s0 + sl;
                 e.part_key[o] = bk2 < 0.0 ? -1.0 : sqrt(bk2);  // |t| of the best gene, as the FP64 kernel reports it
