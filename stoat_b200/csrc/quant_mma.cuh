@@ -172,10 +172,11 @@ __device__ __forceinline__ void mma_word_step(const K3MParams& q, MmaLaneSums& z
     const K3Params& p = q.k;
     const uint2 bm0 = *reinterpret_cast<const uint2*>(bfrag);
     const uint2 bm1 = *reinterpret_cast<const uint2*>(bfrag + 256);
-    uint32_t r[2][4];
+    uint32_t r[2][4], used[2];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
         const LeanMasks m = lean_masks(a[h], b[h]);
+        used[h] = m.used;
         z.cA[h] += __popc(a[h]) | (__popc(b[h]) << 16);
         z.cB[h] += __popc(m.used) | (__popc(m.full0) << 16);
         z.cC[h] += __popc(m.half);
@@ -192,8 +193,7 @@ __device__ __forceinline__ void mma_word_step(const K3MParams& q, MmaLaneSums& z
     const uint32_t valid = valid_word(word, p.n_hap) & 0x55555555u;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-        const uint32_t x = a[h] | b[h];
-        uint32_t un = ~(x | (x >> 1)) & valid & z.live[h];
+        uint32_t un = ~used[h] & valid & z.live[h];
         if (un != 0u) {
             z.saw_unused = true;
             while (un) {
