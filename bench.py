@@ -513,6 +513,12 @@ def trait_record(env, args, ctx, d, trait, stream, host_cache, with_clocks=True)
     sample_sharded = args.sharding == "sample" and world > 1
     if trait == "binary":
         ctx.set_binary_phenotype(d["is_case"])
+    elif sample_sharded:
+        from stoat_b200 import shard as shard_mod
+
+        # the local slice + the WHOLE phenotype's mean / centred sums / max |y - mean| (the centring and the fixed-point scale of
+        # the integer contraction must be global)
+        ctx.set_quantitative_phenotype_shard(d["y"], *shard_mod.phenotype_summary(d["y_all"]))
     else:
         ctx.set_quantitative_phenotype(d["y"])
     ctx.stage_paths(paths)
@@ -520,27 +526,50 @@ def trait_record(env, args, ctx, d, trait, stream, host_cache, with_clocks=True)
     ar_ms, k1_ms_own, k2_ms_own = [], [], []
     ar_bytes = 0
     if sample_sharded:
-        if trait != "binary":
-            raise SystemExit("bench.py --sharding sample measures the binary trait (the quantitative phases: scripts/multi_gpu_check.py)")
         from stoat_b200 import shard as shard_mod
 
-        ctx.binary_counts_staged()
-        ptr, n_words = ctx.binary_counts_dev()  # the buffer only grows: the pointer stays valid for every step below
-        counts_t = torch.as_tensor(shard_mod._DevU32(ptr, n_words), device=env.dev)  # int32 view (same sums)
-        ar_bytes = n_words * 4
         evs = []
+        if trait == "binary":
+            ctx.binary_counts_staged()
+            ptr, n_words = ctx.binary_counts_dev()  # the buffer only grows: the pointer stays valid for every step below
+            counts_t = torch.as_tensor(shard_mod._DevU32(ptr, n_words), device=env.dev)  # int32 view (same sums)
+            ar_bytes = n_words * 4
+            ar_what = "ncclAllReduce(sum, u32, in place) of g0|g1"
 
-        def run():
-            with torch.cuda.stream(stream):
-                a, b, c, e = (torch.cuda.Event(enable_timing=True) for _ in range(4))
-                a.record(stream)
-                ctx.binary_counts_staged()
-                b.record(stream)
-                env.dist.all_reduce(counts_t, op=env.dist.ReduceOp.SUM)
-                c.record(stream)
-                ctx.binary_stats_staged()
-                e.record(stream)
-                evs.append((a, b, c, e))
+            def run():
+                with torch.cuda.stream(stream):
+                    a, b, c, e = (torch.cuda.Event(enable_timing=True) for _ in range(4))
+                    a.record(stream)
+                    ctx.binary_counts_staged()
+                    b.record(stream)
+                    env.dist.all_reduce(counts_t, op=env.dist.ReduceOp.SUM)
+                    c.record(stream)
+                    ctx.binary_stats_staged()
+                    e.record(stream)
+                    evs.append((a, b, c, e))
+        else:
+            # moments of the local columns (K3M: 7 class counts + 3 sums per snarl and haplotype slice) | ONE exchange: the two
+            # partial buffers all-reduced in place | filters + OLS on the sums (K4, replicated).  Snarls that need more than the
+            # two-path sums come back deferred; they are finished after the timed loop (shard.replay_deferred_on_device).
+            ctx.quantitative_moments_staged()
+            pi, ni, pd, nd = ctx.quantitative_partials_dev()
+            part_i = torch.as_tensor(shard_mod._DevU32(pi, ni), device=env.dev)
+            part_d = torch.as_tensor(shard_mod._DevF64(pd, nd), device=env.dev)
+            ar_bytes = ni * 4 + nd * 8
+            ar_what = "ncclAllReduce(sum, in place) of K3M's partials: u32 class counts [slices][7][S] and f64 sums [slices][3][S]"
+
+            def run():
+                with torch.cuda.stream(stream):
+                    a, b, c, e = (torch.cuda.Event(enable_timing=True) for _ in range(4))
+                    a.record(stream)
+                    ctx.quantitative_moments_staged()
+                    b.record(stream)
+                    env.dist.all_reduce(part_i, op=env.dist.ReduceOp.SUM)
+                    env.dist.all_reduce(part_d, op=env.dist.ReduceOp.SUM)
+                    c.record(stream)
+                    ctx.quantitative_solve_staged()
+                    e.record(stream)
+                    evs.append((a, b, c, e))
     else:
         run = ctx.binary_run_staged if trait == "binary" else ctx.quantitative_run_staged
 
@@ -566,7 +595,7 @@ def trait_record(env, args, ctx, d, trait, stream, host_cache, with_clocks=True)
             ar_ms.append(b.elapsed_time(c))
             k2_ms_own.append(c.elapsed_time(e))
         k1, k2 = float(np.mean(k1_ms_own)), float(np.mean(k2_ms_own))
-        launches = 3 * steps  # K1, K2a, K2b (the collective is NCCL's kernel, not counted)
+        launches = (3 if trait == "binary" else 4) * steps  # K1, K2a, K2b | lean records, K3M, K4a, K4b (NCCL's kernels not counted)
         t_last = {"n_general": 0, "n_fisher": 0}
         value = P * steps / (elapsed_ms * 1e-3)  # the ranks share ONE batch
     else:
@@ -577,6 +606,38 @@ def trait_record(env, args, ctx, d, trait, stream, host_cache, with_clocks=True)
         value = world * P * steps / (elapsed_ms * 1e-3)
     launches = int(env.sum_over_ranks(launches))
     res = ctx.binary_fetch() if trait == "binary" else ctx.quantitative_fetch()  # results of the last timed step
+    deferred = None
+    if sample_sharded and trait == "quantitative":
+        # outside the timed loop: the deferred snarls (three paths, thirds, ...) from the ranks' gathered row slices, on the device
+        import stoat_b200
+        from stoat_b200 import shard as shard_mod
+
+        todo = shard_mod.deferred_snarls(res)
+        deferred = int(todo.size)
+        if todo.size:
+            H = 2 * args.samples
+            per = ((H + world - 1) // world + 127) // 128 * 128  # the column ranges main() dealt out
+            ranges = [(min(H, r * per), min(H, (r + 1) * per)) for r in range(world)]
+
+            def allgather_dev(mine):
+                w = torch.tensor([mine.shape[1]], dtype=torch.int64, device=mine.device)
+                ws = [torch.zeros_like(w) for _ in range(world)]
+                env.dist.all_gather(ws, w)
+                wmax = max(int(v.item()) for v in ws)
+                padded = torch.zeros((mine.shape[0], wmax), dtype=torch.uint8, device=mine.device)
+                padded[:, :mine.shape[1]] = mine
+                out = [torch.empty_like(padded) for _ in range(world)]
+                env.dist.all_gather(out, padded)
+                return out
+
+            t0 = time.time()
+            rctx = stoat_b200.Context(env.local)
+            try:
+                replay = shard_mod.replay_deferred_on_device([ctx], ranges, paths, todo, d["y_all"], (3, 5, 0.05), rctx, allgather_dev)
+            finally:
+                rctx.close()
+            res = shard_mod.merge_deferred(res, todo, replay, paths)
+            deferred = {"snarls": deferred, "replay_seconds": round(time.time() - t0, 2)}
 
     # ---- parity spot check on the timed data ---------------------------------------------------------
     parity = None
@@ -672,9 +733,11 @@ def trait_record(env, args, ctx, d, trait, stream, host_cache, with_clocks=True)
            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "parity": parity}
     if sample_sharded:
         ar = float(np.mean(ar_ms))
-        rec["collective"] = {"op": "ncclAllReduce(sum, u32, in place) of g0|g1", "bytes": int(ar_bytes), "ms": ar,
+        rec["collective"] = {"op": ar_what, "bytes": int(ar_bytes), "ms": ar,
                              "share_of_step": ar / step_ms, "busbw_gbs": 2 * (world - 1) / world * ar_bytes / (ar * 1e-3) / 1e9,
                              "k1_ms_local_columns": k1, "k2_ms_replicated": k2}
+        if deferred is not None:
+            rec["collective"]["deferred"] = deferred
     if world == 1 and not args.no_cpu_baseline:
         import oracle
 
