@@ -230,25 +230,6 @@ def test_sample_sharded_column_split_on_one_gpu(gpu_ctx, oracle, n_shards):
     assert gpu_ctx.row_pitch == (shard.plan_column_shards(d["n_cols"], n_shards)[0][1] + 255) // 256 * 32
 
 
-def test_select_snarls_vectorised_equals_loops():
-    from stoat_b200 import shard, synth
-
-    d = synth.numpy_dataset(500, 20, seed=3, frac_missing_edge=0.05)
-    p = d["paths"]
-    idx = np.array([7, 3, 499, 0, 250, 251])
-    sub = shard.select_snarls(p, idx)
-    spo, peo = p.snarl_path_off.astype(np.int64), p.path_edge_off.astype(np.int64)
-    want_er, want_peo, want_spo = [], [0], [0]
-    for s_ in idx:
-        for q in range(spo[s_], spo[s_ + 1]):
-            want_er.extend(p.edge_row[peo[q]:peo[q + 1]].tolist())
-            want_peo.append(len(want_er))
-        want_spo.append(len(want_peo) - 1)
-    np.testing.assert_array_equal(sub.snarl_path_off, np.array(want_spo, np.uint64))
-    np.testing.assert_array_equal(sub.path_edge_off, np.array(want_peo, np.uint64))
-    np.testing.assert_array_equal(sub.edge_row, np.array(want_er, np.uint32))
-
-
 def _three_path_problem(rng, n_snarls, n_samples, frac_missing):
     """Three-path snarls, 1 or 2 checked edges per path.  Every 11th snarl has a path nobody takes (the reference makes
     no column for it), every 13th two paths over the SAME rows (identical columns, which the reference merges), every

@@ -186,3 +186,42 @@ def test_phenotype_summary_matches_library_definition():
     spo, peo = full.snarl_path_off.astype(np.int64), full.path_edge_off.astype(np.int64)
     assert sel.n_snarls == 2 and sel.n_paths == (spo[6] - spo[5]) + (spo[2] - spo[1])
     np.testing.assert_array_equal(sel.edge_row[: peo[spo[6]] - peo[spo[5]]], full.edge_row[peo[spo[5]]:peo[spo[6]]])
+
+
+def test_select_snarls_vectorised_equals_loops():
+    from stoat_b200 import shard, synth
+
+    d = synth.numpy_dataset(500, 20, seed=3, frac_missing_edge=0.05)
+    p = d["paths"]
+    idx = np.array([7, 3, 499, 0, 250, 251])
+    sub = shard.select_snarls(p, idx)
+    spo, peo = p.snarl_path_off.astype(np.int64), p.path_edge_off.astype(np.int64)
+    want_er, want_peo, want_spo = [], [0], [0]
+    for s_ in idx:
+        for q in range(spo[s_], spo[s_ + 1]):
+            want_er.extend(p.edge_row[peo[q]:peo[q + 1]].tolist())
+            want_peo.append(len(want_er))
+        want_spo.append(len(want_peo) - 1)
+    np.testing.assert_array_equal(sub.snarl_path_off, np.array(want_spo, np.uint64))
+    np.testing.assert_array_equal(sub.path_edge_off, np.array(want_peo, np.uint64))
+    np.testing.assert_array_equal(sub.edge_row, np.array(want_er, np.uint32))
+
+
+def test_merge_deferred_vectorised():
+    from stoat_b200 import shard, synth
+
+    d = synth.numpy_dataset(60, 20, seed=4)
+    p = d["paths"]
+    spo = p.snarl_path_off.astype(np.int64)
+    res = dict(allele_paths=np.zeros(p.n_paths, np.uint32), p_value=np.zeros(p.n_snarls), code=np.full(p.n_snarls, 7, np.uint8))
+    todo = np.array([3, 10, 59])
+    n_paths = int((spo[todo + 1] - spo[todo]).sum())
+    replay = dict(allele_paths=np.arange(1, n_paths + 1, dtype=np.uint32), p_value=np.array([0.1, 0.2, 0.3]), code=np.zeros(3, np.uint8))
+    out = shard.merge_deferred(res, todo, replay, p)
+    assert out["p_value"][10] == 0.2 and out["code"][59] == 0 and out["code"][0] == 7
+    pos = 0
+    for s_ in todo:
+        n = int(spo[s_ + 1] - spo[s_])
+        np.testing.assert_array_equal(out["allele_paths"][spo[s_]:spo[s_] + n], replay["allele_paths"][pos:pos + n])
+        pos += n
+    assert out["allele_paths"].sum() == replay["allele_paths"].sum()
