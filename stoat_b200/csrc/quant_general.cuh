@@ -45,6 +45,10 @@ struct GParams {
 };
 
 constexpr int kGWarps = 4;
+constexpr int kSmallCols = 8;  // kept columns up to which sweep A keeps lane-private column sums
+constexpr int kSmallP = 6;     // features up to which the moment sweeps keep lane-private accumulators (registers, no tile)
+constexpr int kSmallTri = kSmallP * (kSmallP + 1) / 2;
+constexpr int kSmallEnt = kSmallTri + kSmallP + 2;
 struct GScratch {
     double tile[32][kMaxFeat + 1];    // X rows of the current 32 samples, last column = y
     double inv[kMaxFeat * kMaxFeat];  // (X^T X)^-1 of the snarl, column-major with leading dimension p
@@ -59,6 +63,8 @@ struct GScratch {
     uint8_t merged[kMaxPathsG];
     uint8_t same[kMaxPathsG];
     double wv[32], rv[32];            // logistic: sqrt(weight) and y - p of the current 32 samples
+    uint32_t erow[kMaxPathsG][4];     // matrix rows of the kept columns' checked edges (<= 4 cached, else read through the CSR)
+    uint8_t ecode[kMaxPathsG];        // 0: no checked edge (every haplotype), 1..4: cached rows, 0xFE: more than four edges
 };
 
 // word `w` (32 haplotypes) of the presence vector of path `pth` (identify_path, src/snarl_analyzer.cpp:315-356)
@@ -79,12 +85,34 @@ struct GSnarl {  // warp-uniform state of the snarl being processed
     uint32_t np, nk, n_words, n_blocks;
 };
 
-// presence words of every kept column for superblock sb (lane = word)
+// word `w` of kept column c from the cached rows: the loads of a column's edges are independent (ANDed at the end)
+__device__ __forceinline__ uint32_t g_cached_word(const GParams& g, const GScratch& sc, const GSnarl& sn, uint32_t c, uint32_t w) {
+    const uint32_t code = sc.ecode[c];
+    if (code == 0xFEu) return g_path_word(g, sn.p0 + sc.kept[c], w);
+    if (code == 0u) return valid_word(w, g.n_hap);
+    uint32_t v[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+        v[e] = (uint32_t(e) < code) ? __ldg(reinterpret_cast<const uint32_t*>(g.rows + size_t(sc.erow[c][e]) * g.pitch) + w) : 0xFFFFFFFFu;
+    return (v[0] & v[1]) & (v[2] & v[3]);
+}
+
+// presence words of every kept column for superblock sb (lane = word).  Four columns at a time so that their row loads are
+// in flight together: with the CSR walked per word (path_edge_off -> edge_row -> row, four dependent global loads per column,
+// superblock and sweep) one snarl on this kernel cost ~1 ms at 5,000 samples.
 __device__ __forceinline__ void g_load_superblock(const GParams& g, GScratch& sc, const GSnarl& sn, uint32_t sb,
                                                   uint32_t lane) {
     __syncwarp();
     const uint32_t w = sb * 32 + lane;
-    for (uint32_t c = 0; c < sn.nk; ++c) sc.pw[c][lane] = (w < sn.n_words) ? g_path_word(g, sn.p0 + sc.kept[c], w) : 0u;
+    const bool in = w < sn.n_words;
+    for (uint32_t c0 = 0; c0 < sn.nk; c0 += 4) {
+        uint32_t v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = (in && c0 + j < sn.nk) ? g_cached_word(g, sc, sn, c0 + j, w) : 0u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (c0 + j < sn.nk) sc.pw[c0 + j][lane] = v[j];
+    }
     __syncwarp();
 }
 
@@ -202,7 +230,27 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
     __syncwarp();
     for (uint32_t j = 0; j < sn.np; ++j) {
         uint32_t c = 0;
-        for (uint32_t w = lane; w < sn.n_words; w += 32) c += __popc(g_path_word(g, sn.p0 + j, w));
+        const uint64_t ea = g.b.path_edge_off[sn.p0 + j], ez = g.b.path_edge_off[sn.p0 + j + 1];
+        if (ez - ea <= 4) {  // the CSR is read once per path, the row words of a pass are independent loads
+            uint32_t rw[4] = {0, 0, 0, 0};
+            bool missing = false;
+            for (uint64_t e = ea; e < ez; ++e) {
+                rw[e - ea] = g.b.edge_row[e];
+                missing |= rw[e - ea] == kMissingQ;
+            }
+            const uint32_t ne = uint32_t(ez - ea);
+            if (!missing)
+                for (uint32_t w = lane; w < sn.n_words; w += 32) {
+                    uint32_t v[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        v[e] = (uint32_t(e) < ne) ? __ldg(reinterpret_cast<const uint32_t*>(g.rows + size_t(rw[e]) * g.pitch) + w)
+                                                  : valid_word(w, g.n_hap);
+                    c += __popc((v[0] & v[1]) & (v[2] & v[3]));
+                }
+        } else {
+            for (uint32_t w = lane; w < sn.n_words; w += 32) c += __popc(g_path_word(g, sn.p0 + j, w));
+        }
         c = __reduce_add_sync(0xffffffffu, c);
         if (lane == 0) g.out.allele_paths[sn.p0 + j] = c;
         if (c > 0) {
@@ -212,16 +260,36 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
     }
     __syncwarp();
     const uint32_t nk = sn.nk;
+    for (uint32_t c = lane; c < nk; c += 32) {  // the kept columns' edge rows, read from the CSR once
+        const uint64_t pth = sn.p0 + sc.kept[c];
+        const uint64_t a = g.b.path_edge_off[pth], z = g.b.path_edge_off[pth + 1];
+        uint8_t code = uint8_t(z - a <= 4 ? (z - a) : 0xFEu);
+        if (code != 0xFEu)
+            for (uint64_t e = a; e < z; ++e) sc.erow[c][e - a] = g.b.edge_row[e];  // a kept column has no missing edge
+        sc.ecode[c] = code;
+    }
+    __syncwarp();
     // ---- sweep A: used rows and column sums --------------------------------------------------------
     uint32_t n_used = 0;
     bool nondyadic = false;
     double colsum0 = 0.0, colsum1 = 0.0;  // lane c owns column c (and c + 32)
+    double cs_lane[kSmallCols];
+#pragma unroll
+    for (int c = 0; c < kSmallCols; ++c) cs_lane[c] = 0.0;
     for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
         const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
         const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
         n_used += __popc(used_ballot);
         nondyadic |= __any_sync(0xffffffffu, rs >= 3 && (rs & (rs - 1)) != 0);
         const double rsum = double(rs);
+        if (nk <= uint32_t(kSmallCols)) {  // the usual table: every lane keeps its own partial column sums, one reduction at the end
+#pragma unroll
+            for (int c = 0; c < kSmallCols; ++c) {
+                const uint32_t k = (uint32_t(c) < nk) ? sc.cnt[lane][c] : 0u;
+                cs_lane[c] += (k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;  // quantitative_table.cpp:93
+            }
+            continue;
+        }
         for (uint32_t c = 0; c < nk; ++c) {
             const uint32_t k = sc.cnt[lane][c];
             const double d = (k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;  // quantitative_table.cpp:93
@@ -230,6 +298,13 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                 if (c < 32) colsum0 += sum;
                 else colsum1 += sum;
             }
+        }
+    }
+    if (nk <= uint32_t(kSmallCols)) {
+#pragma unroll
+        for (int c = 0; c < kSmallCols; ++c) {
+            const double tot = warp_sum(cs_lane[c]);  // dyadic terms: exact in any order (else the replay below decides)
+            if (lane == uint32_t(c)) colsum0 = tot;
         }
     }
     // remove_empty_columns is a no-op here (empty paths were never added); filtration (:549)
@@ -277,30 +352,27 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         if (sc.merged[a]) continue;
         uint32_t mult = 1;
         if (nk >= 3 && a + 1 < nk) {
-            bool same0 = (a + 1 + lane < nk) && !sc.merged[a + 1 + lane];
-            bool same1 = (a + 33 + lane < nk) && !sc.merged[a + 33 + lane];
-            if (__any_sync(0xffffffffu, same0 || same1)) {
-                for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
-                    g_load_block(g, sc, sn, blk, lane);
-                    __syncwarp();
-                    for (uint32_t i = 0; i < 32; ++i) {
-                        const uint8_t ka = sc.cnt[i][a];
-                        if (same0 && sc.cnt[i][a + 1 + lane] != ka) same0 = false;
-                        if (same1 && sc.cnt[i][a + 33 + lane] != ka) same1 = false;
-                    }
-                    __syncwarp();
-                    if (!__any_sync(0xffffffffu, same0 || same1)) break;
+            // candidates b > a that may equal column a; lane = sample, one vote per candidate and block
+            uint64_t cand = 0;
+            for (uint32_t b2 = a + 1; b2 < nk; ++b2)
+                if (!sc.merged[b2]) cand |= 1ull << b2;
+            for (uint32_t blk = 0; blk < sn.n_blocks && cand; ++blk) {
+                g_load_block(g, sc, sn, blk, lane);
+                __syncwarp();
+                const uint8_t ka = sc.cnt[lane][a];
+                uint64_t c2 = cand;
+                while (c2) {
+                    const int b2 = __ffsll((long long)c2) - 1;
+                    c2 &= c2 - 1;
+                    if (__any_sync(0xffffffffu, sc.cnt[lane][b2] != ka)) cand &= ~(1ull << b2);
                 }
+                __syncwarp();
             }
-            if (a + 1 + lane < nk) sc.same[a + 1 + lane] = same0 ? 1 : 0;
-            if (a + 33 + lane < nk) sc.same[a + 33 + lane] = same1 ? 1 : 0;
-            __syncwarp();
             if (lane == 0)
                 for (uint32_t b2 = a + 1; b2 < nk; ++b2)
-                    if (sc.same[b2]) sc.merged[b2] = 1;
+                    if ((cand >> b2) & 1ull) sc.merged[b2] = 1;
+            mult += uint32_t(__popcll(cand));
             __syncwarp();
-            for (uint32_t b2 = a + 1; b2 < nk; ++b2)
-                if (sc.same[b2]) ++mult;
         }
         if (lane == 0) {
             sc.fcol[nf] = uint8_t(a);
@@ -357,6 +429,37 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
             sc.tile[lane][1 + k_reg + c] = used ? g.covar[size_t(rank) * g.n_covar + c] : 0.0;
         sc.tile[lane][kMaxFeat] = (used && i < g.n_samples) ? (g.is_case ? (g.is_case[i] ? 1.0 : 0.0) : y[i]) : 0.0;
     };
+    // the same row in REGISTERS (lane = sample), for designs of up to kSmallP features: the moment sweeps then keep
+    // lane-private accumulators and reduce once per sweep, instead of 32-step loops over a shared-memory tile per block
+    const bool small_p = p <= uint32_t(kSmallP);
+    auto build_row = [&](uint32_t blk, uint32_t used_ballot, const double* y, double (&x)[kSmallP], double& yv) -> bool {
+        const bool used = (used_ballot >> lane) & 1u;
+        const uint32_t i = blk * 32 + lane;
+        const uint32_t rank = rank_base + __popc(used_ballot & ((1u << lane) - 1u));
+        const double rsum = double(sc.rs[lane]);
+#pragma unroll
+        for (int r = 0; r < kSmallP; ++r) x[r] = 0.0;
+        x[0] = used ? 1.0 : 0.0;
+#pragma unroll
+        for (int a = 0; a < kSmallP - 1; ++a)
+            if (uint32_t(a) < k_reg) {
+                const uint32_t k = sc.cnt[lane][sc.fcol[a]];
+                const double d = (used && k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;
+                double v = d;
+                for (uint32_t m = 1; m < sc.fmult[a]; ++m) v = __dadd_rn(v, d);
+                x[1 + a] = v;
+            }
+#pragma unroll
+        for (int c = 0; c < kSmallP - 2; ++c)
+            if (uint32_t(c) < g.n_covar && 1 + k_reg + uint32_t(c) < uint32_t(kSmallP)) {
+                const double cv = used ? g.covar[size_t(rank) * g.n_covar + c] : 0.0;  // by FILTERED row position (:450-452)
+#pragma unroll
+                for (int r = 2; r < kSmallP; ++r)
+                    if (uint32_t(r) == 1 + k_reg + uint32_t(c)) x[r] = cv;
+            }
+        yv = (used && i < g.n_samples) ? (g.is_case ? (g.is_case[i] ? 1.0 : 0.0) : y[i]) : 0.0;
+        return used;
+    };
     if (g.is_case) {
         // ---- LogisticRegression::logistic_regression (src/stats_test.cpp:49-176) ----------------------
         // IRLS: every pass sweeps the samples once for the Hessian X^T W X + l2 I and the gradient X^T (y - p) - l2 beta
@@ -376,8 +479,50 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         int steps = 0;
         int state = 0;  // 0: iterate, 1: converged (this pass is the covariance pass), 2: done
         while (state != 2) {
-            double accv[6] = {0, 0, 0, 0, 0, 0};
+            double* flat = &sc.tile[0][0];
             rank_base = 0;
+            if (small_p) {
+                double acc[kSmallTri + kSmallP];
+#pragma unroll
+                for (int e = 0; e < kSmallTri + kSmallP; ++e) acc[e] = 0.0;
+                double bta[kSmallP];
+#pragma unroll
+                for (int r = 0; r < kSmallP; ++r) bta[r] = (uint32_t(r) < p) ? sc.beta[r] : 0.0;
+                for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+                    const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
+                    const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+                    double x[kSmallP], yv;
+                    const bool used = build_row(blk, used_ballot, nullptr, x, yv);
+                    rank_base += __popc(used_ballot);
+                    double z = 0.0;
+#pragma unroll
+                    for (int r = 0; r < kSmallP; ++r) z = fma(x[r], bta[r], z);
+                    const double pr = 1.0 / (1.0 + exp(-z));                 // :27-29
+                    const double w = fmax(kEps, fmin(1.0, pr * (1.0 - pr)));  // :93
+                    const double sw = used ? sqrt(w) : 0.0;                   // X_weighted.row(i) *= sqrt(w), :97-98
+                    const double rv = used ? yv - pr : 0.0;
+                    int e = 0;
+#pragma unroll
+                    for (int r = 0; r < kSmallP; ++r) {
+#pragma unroll
+                        for (int c = 0; c <= r; ++c, ++e) acc[e] = fma(x[r] * sw, x[c] * sw, acc[e]);
+                        acc[kSmallTri + r] = fma(x[r], rv, acc[kSmallTri + r]);
+                    }
+                }
+#pragma unroll
+                for (int e = 0; e < kSmallTri + kSmallP; ++e) {
+                    const double v = warp_sum(acc[e]);
+                    if (lane == 0) {
+                        if (e < kSmallTri) {
+                            if (uint32_t(e) < n_tri) flat[e] = v;
+                        } else if (uint32_t(e - kSmallTri) < p) {
+                            flat[n_tri + (e - kSmallTri)] = v;
+                        }
+                    }
+                }
+                __syncwarp();
+            } else {
+            double accv[6] = {0, 0, 0, 0, 0, 0};
             for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
                 const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
                 const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
@@ -410,11 +555,11 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                 }
                 __syncwarp();
             }
-            double* flat = &sc.tile[0][0];
 #pragma unroll
             for (int q = 0; q < 6; ++q)
                 if (lane + 32u * q < n_ent) flat[lane + 32u * q] = accv[q];
             __syncwarp();
+            }
             if (lane == 0) {
                 SmallMat<kMaxFeat> Hm;
                 uint32_t e = 0;
@@ -517,8 +662,48 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
             y = g.y + gene * uint64_t(g.n_samples);  // retain_indices(expression, index_filtered), :510-511
         }
         // ---- sweep B: X^T X (first item only), X^T y, y'y, sum y ------------------------------------
-        double accv[6] = {0, 0, 0, 0, 0, 0};
+        double* flat = &sc.tile[0][0];
         rank_base = 0;
+        if (small_p) {
+            double acc[kSmallEnt];
+#pragma unroll
+            for (int e = 0; e < kSmallEnt; ++e) acc[e] = 0.0;
+            for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+                const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
+                const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+                double x[kSmallP], yv;
+                build_row(blk, used_ballot, y, x, yv);
+                rank_base += __popc(used_ballot);
+                int e = 0;
+#pragma unroll
+                for (int r = 0; r < kSmallP; ++r) {
+                    if (first) {
+#pragma unroll
+                        for (int c = 0; c <= r; ++c) acc[e + c] = fma(x[r], x[c], acc[e + c]);
+                    }
+                    e += r + 1;
+                    acc[kSmallTri + r] = fma(x[r], yv, acc[kSmallTri + r]);
+                }
+                acc[kSmallTri + kSmallP] = fma(yv, yv, acc[kSmallTri + kSmallP]);
+                acc[kSmallTri + kSmallP + 1] += yv;
+            }
+#pragma unroll
+            for (int e = 0; e < kSmallEnt; ++e) {
+                if (e < kSmallTri && !first) continue;
+                const double v = warp_sum(acc[e]);
+                if (lane == 0) {
+                    if (e < kSmallTri) {
+                        if (uint32_t(e) < n_tri) flat[e] = v;
+                    } else if (e < kSmallTri + kSmallP) {
+                        if (uint32_t(e - kSmallTri) < p) flat[n_tri + (e - kSmallTri)] = v;
+                    } else {
+                        flat[n_tri + p + (e - kSmallTri - kSmallP)] = v;
+                    }
+                }
+            }
+            __syncwarp();
+        } else {
+        double accv[6] = {0, 0, 0, 0, 0, 0};
         for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
             const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
             const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
@@ -546,11 +731,11 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
             __syncwarp();
         }
         // ---- solve on lane 0: gather the entries through shared memory (reuse the tile) --------------
-        double* flat = &sc.tile[0][0];
 #pragma unroll
         for (int q = 0; q < 6; ++q)
             if (lane + 32u * q < n_ent) flat[lane + 32u * q] = accv[q];
         __syncwarp();
+        }
         double sum_y = 0.0;
         if (lane == 0) {
             if (first) {
@@ -578,6 +763,27 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         // ---- sweep C: residuals (stats_test.cpp:459-465) ----------------------------------------------
         double rss = 0.0, tss = 0.0;
         rank_base = 0;
+        if (small_p) {
+            double bta[kSmallP];
+#pragma unroll
+            for (int r = 0; r < kSmallP; ++r) bta[r] = (uint32_t(r) < p) ? sc.beta[r] : 0.0;
+            for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+                const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
+                const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+                double x[kSmallP], yv;
+                const bool used = build_row(blk, used_ballot, y, x, yv);
+                rank_base += __popc(used_ballot);
+                if (used) {
+                    double pred = 0.0;
+#pragma unroll
+                    for (int r = 0; r < kSmallP; ++r) pred = fma(x[r], bta[r], pred);
+                    const double res = yv - pred;
+                    rss = fma(res, res, rss);
+                    const double dm = yv - y_mean;
+                    tss = fma(dm, dm, tss);
+                }
+            }
+        } else {
         for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
             const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
             const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
@@ -595,6 +801,7 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                 tss = fma(dm, dm, tss);
             }
             __syncwarp();
+        }
         }
         rss = warp_sum(rss);
         tss = warp_sum(tss);
