@@ -1,5 +1,2 @@
-timeout 120 python scripts/umma_probe.py 2>&1 | tail -1
-timeout 600 python -m pytest tests/test_gpu_eqtl.py -x -q 2>&1 | tail -3
-timeout 600 python bench.py --trait eqtl --steps 3 --warmup 3 --no-cpu-baseline --no-e2e 2>/dev/null | grep '^{' | python -c "
-import json,sys
-d=json.loads(sys.stdin.read()); print(round(d['ms_per_step'],1), 'ms', d['parity']['mismatches'], d['parity'].get('first_mismatch'), d['roofline']['frac'])"
+ncu --set full --import-source on --clock-control none -k regex:quant_general -s 30 -c 1 -f -o gpurun_out/prof_k3g python scripts/k3g_cliff.py 5000 > /dev/null 2>&1
+ls -la gpurun_out/prof_k3g.ncu-rep
