@@ -174,3 +174,53 @@ def test_chunked_upload_matches_single_copy(gpu_ctx, oracle, monkeypatch):
         for r in (0, 127, 128, 129, 511, 512, 999):
             row = np.unpackbits(gpu_ctx.read_row(r), bitorder="little")
             np.testing.assert_array_equal(row[:n_cols].astype(bool), dense[r])
+
+
+@pytest.mark.parametrize("n_samples", [25000, 33000])
+def test_logistic_at_c5_width_and_beyond(gpu_ctx, oracle, n_samples):
+    """The logistic path at 50,000 haplotypes and at 66,000 (class-count reductions no longer packed two per word; the
+    general kernel's sweeps over ~1,000 sample blocks).  Tolerance 1e-8 instead of 1e-9: at convergence the Newton step is
+    H^-1 times the rounding noise of the gradient sum, and the reference's (and the oracle's) sequential sum over 33,000
+    samples ordered controls-first passes through partial sums of ~8,000, so its own beta is defined to ~5e-12 absolute only
+    (numpy's pairwise sum, the oracle and the GPU's two exact-count formulations differ by that much; the two GPU paths agree
+    with each other to 1e-14)."""
+    import test_gpu_logit
+    from stoat_b200 import synth
+
+    d = synth.numpy_dataset(120, n_samples, seed=14, frac_missing_edge=0.03)
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    gpu_ctx.set_matrix(d["bits"], d["n_rows"], d["n_cols"])
+    gpu_ctx.set_binary_phenotype(d["is_case"])
+    gpu_ctx.set_covariates(None)
+    got = gpu_ctx.binary_covar_batch(d["paths"])
+    ref = oracle.binary_covar_batch(d["bits"], d["n_cols"], d["is_case"], P)
+    assert test_gpu_logit.assert_logit_equal(got, ref, rtol=1e-8) > 50
+
+
+def test_dense_eqtl_tcgen05_at_c5_width(oracle):
+    """The int8 tcgen05 contraction at 25,000 samples (196 blocks of 128 samples per gene tile, INT32 sums up to 3.2e6) and
+    with a gene count that is not a multiple of the 32-gene tile."""
+    import stoat_b200
+    from stoat_b200 import synth
+
+    n = 25000
+    d = synth.numpy_dataset(150, n, seed=15, frac_three=0.0, frac_node0=0.0)
+    P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
+    rng = np.random.default_rng(15)
+    G = 37
+    expr = rng.uniform(0, 8, size=(G, 1)) * (1.0 + rng.uniform(-1, 1, size=(G, n)))
+    expr[3] += 0.2 * d["dense"][d["structure"].row0[5]].reshape(n, 2).sum(1) if "dense" in d else 0.0
+    ref = oracle.eqtl_batch(d["bits"], d["n_cols"], expr, P)
+    with stoat_b200.Context(0) as ctx:
+        ctx.set_matrix(d["bits"], d["n_rows"], d["n_cols"])
+        got = ctx.eqtl_dense_summary(d["paths"], expr, p_threshold=1e-2)
+        assert ctx.timing()["n_general"] <= 4
+    pv = np.where(ref["code"].reshape(-1, G) == 0, ref["p_value"].reshape(-1, G), np.inf)
+    rows = np.flatnonzero((ref["filtered"] == 0) & np.isfinite(pv.min(axis=1)))
+    assert rows.size > 100
+    want = pv[rows].min(axis=1)
+    np.testing.assert_allclose(got["min_p"][rows], want, rtol=1e-9, atol=1e-300)
+    near = np.abs(pv[rows] - 1e-2) <= 1e-11
+    lo, hi = ((pv[rows] < 1e-2) & ~near).sum(axis=1), ((pv[rows] < 1e-2) | near).sum(axis=1)
+    assert np.all((lo <= got["n_below"][rows]) & (got["n_below"][rows] <= hi))
+    assert np.isnan(got["min_p"][ref["filtered"] == 1]).all()
