@@ -1,20 +1,10 @@
-python - <<'PY' 2>/dev/null
-import sys, os, numpy as np
-sys.path.insert(0,'tests'); sys.path.insert(0,'.')
-import oracle, stoat_b200
-from stoat_b200 import synth
-d = synth.numpy_dataset(120, 33000, seed=14, frac_missing_edge=0.03)
-P = oracle.Paths(d["paths"].snarl_path_off, d["paths"].path_edge_off, d["paths"].edge_row)
-ref = oracle.binary_covar_batch(d["bits"], d["n_cols"], d["is_case"], P)
-m=(ref["filtered"]==0)&(ref["code"]==0)
-npaths=np.diff(d["paths"].snarl_path_off.astype(np.int64))
-for mode in ("", "general"):
-    if mode: os.environ["STOAT_GPU_LOGIT"]=mode
-    with stoat_b200.Context(0) as ctx:
-        ctx.set_matrix(d["bits"], d["n_rows"], d["n_cols"]); ctx.set_binary_phenotype(d["is_case"])
-        got = ctx.binary_covar_batch(d["paths"])
-    for k in ("beta","se","p_value"):
-        a,b=got[k],ref[k]; e=np.where(m,np.abs(a-b),0); rel=e/np.maximum(np.abs(b),1e-300)
-        idx=np.argsort(-rel)[:3]
-        print(mode or "fast", k, [(int(i), int(npaths[i]), float(a[i]), float(b[i]), float(rel[i])) for i in idx])
-PY
+mkdir -p gpurun_out
+{
+for n in 5000 25000; do
+  STOAT_GPU_K3G_TEAM=0 timeout 300 python scripts/k3g_cliff.py $n
+  timeout 300 python scripts/k3g_cliff.py $n
+done
+} > gpurun_out/r2o_cliff.txt 2>&1
+cat gpurun_out/r2o_cliff.txt
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/r2o_pytest.txt 2>&1
+tail -5 gpurun_out/r2o_pytest.txt

@@ -83,7 +83,43 @@ __device__ __forceinline__ uint32_t g_path_word(const GParams& g, uint64_t pth, 
 struct GSnarl {  // warp-uniform state of the snarl being processed
     uint64_t p0;
     uint32_t np, nk, n_words, n_blocks;
+    uint32_t b0, b1;   // the sample blocks this warp sweeps: all of them, or its share of a team's
+    uint32_t cur_sb;   // superblock whose presence words sit in sc.pw (0xFFFFFFFF: none)
 };
+
+// A TEAM of warps on one snarl (quant_general_team_kernel: the CTA is the team).  Every warp of the team runs the whole
+// routine with its own scratch and takes the same decisions; only the sweeps over the samples are shared out, each warp
+// taking a contiguous range of the 32-sample blocks, and every sum of a sweep is all-reduced through `buf` in a fixed
+// order, so that all warps continue from bit-identical totals.  size == 1: one warp per snarl, no CTA barrier is executed.
+constexpr int kGTeamWarps = 8;
+struct GTeam {
+    uint32_t rank, size;
+    double* buf;  // [size][32]
+};
+__device__ __forceinline__ void team_sync(const GTeam& tm) {
+    if (tm.size > 1) __syncthreads();
+}
+// element-wise over the lanes: lane l of every warp returns the sum over the team of its lane-l values
+__device__ __forceinline__ double team_sum(const GTeam& tm, double v, uint32_t lane) {
+    if (tm.size == 1) return v;
+    tm.buf[tm.rank * 32 + lane] = v;
+    __syncthreads();
+    double r = 0.0;
+    for (uint32_t t = 0; t < tm.size; ++t) r += tm.buf[t * 32 + lane];
+    __syncthreads();
+    return r;
+}
+__device__ __forceinline__ uint64_t team_and64(const GTeam& tm, uint64_t v, uint32_t lane) {
+    if (tm.size == 1) return v;
+    if (lane == 0) tm.buf[tm.rank * 32] = __longlong_as_double((long long)v);
+    __syncthreads();
+    uint64_t r = ~0ull;
+    for (uint32_t t = 0; t < tm.size; ++t) r &= uint64_t(__double_as_longlong(tm.buf[t * 32]));
+    __syncthreads();
+    return r;
+}
+// the sample blocks of this warp, in order
+#define G_FOR_BLOCKS(blk) for (uint32_t blk = sn.b0; blk < sn.b1; ++blk)
 
 // word `w` of kept column c from the cached rows: the loads of a column's edges are independent (ANDed at the end)
 __device__ __forceinline__ uint32_t g_cached_word(const GParams& g, const GScratch& sc, const GSnarl& sn, uint32_t c, uint32_t w) {
@@ -117,9 +153,12 @@ __device__ __forceinline__ void g_load_superblock(const GParams& g, GScratch& sc
 }
 
 // counts of the 32 samples of block blk (lane = sample) for every kept column -> sc.cnt / sc.rs; returns the row sum
-__device__ __forceinline__ uint32_t g_load_block(const GParams& g, GScratch& sc, const GSnarl& sn, uint32_t blk,
+__device__ __forceinline__ uint32_t g_load_block(const GParams& g, GScratch& sc, GSnarl& sn, uint32_t blk,
                                                  uint32_t lane) {
-    if ((blk & 15u) == 0) g_load_superblock(g, sc, sn, blk >> 4, lane);
+    if ((blk >> 4) != sn.cur_sb) {
+        g_load_superblock(g, sc, sn, blk >> 4, lane);
+        sn.cur_sb = blk >> 4;
+    }
     const uint32_t i = blk * 32 + lane;
     const uint32_t wl = (blk & 15u) * 2 + (lane >> 4);
     const uint32_t sh = (lane & 15) * 2;
@@ -134,10 +173,42 @@ __device__ __forceinline__ uint32_t g_load_block(const GParams& g, GScratch& sc,
     return rs;
 }
 
+// the same for tables of up to kSmallCols kept columns, in REGISTERS: count of column c in bits [4c, 4c + 4) of `packed`
+// (a count is 0..2), no round trip through sc.cnt / sc.rs
+__device__ __forceinline__ uint32_t g_load_block_small(const GParams& g, GScratch& sc, GSnarl& sn, uint32_t blk, uint32_t lane,
+                                                       uint32_t& packed) {
+    if ((blk >> 4) != sn.cur_sb) {
+        g_load_superblock(g, sc, sn, blk >> 4, lane);
+        sn.cur_sb = blk >> 4;
+    }
+    const uint32_t i = blk * 32 + lane;
+    const uint32_t wl = (blk & 15u) * 2 + (lane >> 4);
+    const uint32_t sh = (lane & 15) * 2;
+    uint32_t rs = 0;
+    packed = 0;
+    if (i < g.n_samples) {
+#pragma unroll
+        for (int c = 0; c < kSmallCols; ++c)
+            if (uint32_t(c) < sn.nk) {
+                const uint32_t k = __popc((sc.pw[c][wl] >> sh) & 3u);
+                packed |= k << (4 * c);
+                rs += k;
+            }
+    }
+    return rs;
+}
+
+// count / row_sum as the reference divides it (quantitative_table.cpp:93), without a division per column: a sample has two
+// haplotypes, so a count is 0, 1 or 2, and k * rn(1 / rs) IS rn(k / rs) for those k (a product with 0, 1 or 2 is exact).
+// One reciprocal per sample, then a product per column, no branches (0 for an unused sample: its counts are all 0).
+__device__ __forceinline__ double g_row_rcp(uint32_t rs) {
+    return __drcp_rn(double(rs ? rs : 1u));
+}
+
 // exact replay of filtration_quantitative_table's accumulation order (src/snarl_analyzer.cpp:558-576) for the rare
 // non-dyadic snarl whose filter comparison is within rounding of a threshold: `total` is one running sum over
 // (row, column); column sums accumulate down the rows.  Lane c owns column c (and c + 32); lane 0 owns the total.
-__device__ void g_exact_sums(const GParams& g, GScratch& sc, const GSnarl& sn, uint32_t lane, double& total) {
+__device__ void g_exact_sums(const GParams& g, GScratch& sc, GSnarl& sn, uint32_t lane, double& total) {
     double colsum0 = 0.0, colsum1 = 0.0, t = 0.0;
     for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
         const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
@@ -186,7 +257,8 @@ __device__ void g_exact_sums(const GParams& g, GScratch& sc, const GSnarl& sn, u
     __syncwarp();
 }
 
-__device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64_t slot, uint32_t part, uint32_t lane) {
+__device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64_t slot, uint32_t part, uint32_t lane,
+                              const GTeam& tm) {
     GSnarl sn;
     sn.p0 = g.b.snarl_path_off[s];
     const uint64_t p1 = g.b.snarl_path_off[s + 1];
@@ -194,6 +266,12 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
     sn.n_words = g.pitch / 4;
     sn.n_blocks = (g.n_samples + 31) / 32;
     sn.nk = 0;
+    sn.cur_sb = 0xFFFFFFFFu;
+    {
+        const uint32_t per = (sn.n_blocks + tm.size - 1) / tm.size;
+        sn.b0 = tm.rank * per < sn.n_blocks ? tm.rank * per : sn.n_blocks;
+        sn.b1 = sn.b0 + per < sn.n_blocks ? sn.b0 + per : sn.n_blocks;
+    }
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
     // items (regressions) of this snarl: one for the quantitative analyzer, one per gene of the window for eQTL
     uint64_t k0 = s, k1 = s + 1, gene_base = 0;
@@ -209,12 +287,13 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         }
         gene_base = dense_row * uint64_t(g.n_genes);
     }
+    const bool writer = tm.rank == 0;  // one warp of the team writes the results
     auto finish_none = [&](bool filtered, uint32_t n_used, uint8_t code) {
-        if (lane == 0) {
+        if (lane == 0 && writer) {
             g.out.filtered[s] = filtered ? 1 : 0;
             g.out.n_used[s] = n_used;
         }
-        for (uint64_t k = k0 + lane; k < k1; k += 32) {
+        for (uint64_t k = k0 + lane; k < k1 && writer; k += 32) {
             const uint64_t o = k - g.item_base;
             g.out.p[o] = g.out.beta[o] = g.out.se[o] = nan;
             if (g.out.r2) g.out.r2[o] = nan;
@@ -222,12 +301,14 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         }
     };
     if (sn.np > uint32_t(kMaxPathsG)) {  // over the device limit: reported, never mangled
-        for (uint32_t j = lane; j < sn.np; j += 32) g.out.allele_paths[sn.p0 + j] = 0;
+        for (uint32_t j = lane; j < sn.np && writer; j += 32) g.out.allele_paths[sn.p0 + j] = 0;
         finish_none(true, 0, kPOverLimit);
         return;
     }
     // ---- allele_paths and the kept columns (quantitative_table.cpp:37-58) --------------------------
     __syncwarp();
+    const uint32_t w_first = tm.rank * 32 + lane, w_step = tm.size * 32;
+    double ap0 = 0.0, ap1 = 0.0;  // lane j owns the count of path j (and j + 32)
     for (uint32_t j = 0; j < sn.np; ++j) {
         uint32_t c = 0;
         const uint64_t ea = g.b.path_edge_off[sn.p0 + j], ez = g.b.path_edge_off[sn.p0 + j + 1];
@@ -240,7 +321,7 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
             }
             const uint32_t ne = uint32_t(ez - ea);
             if (!missing)
-                for (uint32_t w = lane; w < sn.n_words; w += 32) {
+                for (uint32_t w = w_first; w < sn.n_words; w += w_step) {
                     uint32_t v[4];
 #pragma unroll
                     for (int e = 0; e < 4; ++e)
@@ -249,10 +330,16 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                     c += __popc((v[0] & v[1]) & (v[2] & v[3]));
                 }
         } else {
-            for (uint32_t w = lane; w < sn.n_words; w += 32) c += __popc(g_path_word(g, sn.p0 + j, w));
+            for (uint32_t w = w_first; w < sn.n_words; w += w_step) c += __popc(g_path_word(g, sn.p0 + j, w));
         }
         c = __reduce_add_sync(0xffffffffu, c);
-        if (lane == 0) g.out.allele_paths[sn.p0 + j] = c;
+        if (lane == (j & 31u)) (j < 32 ? ap0 : ap1) = double(c);
+    }
+    ap0 = team_sum(tm, ap0, lane);
+    if (sn.np > 32) ap1 = team_sum(tm, ap1, lane);
+    for (uint32_t j = 0; j < sn.np; ++j) {
+        const uint32_t c = uint32_t(__shfl_sync(0xffffffffu, j < 32 ? ap0 : ap1, j & 31u));
+        if (lane == 0 && writer) g.out.allele_paths[sn.p0 + j] = c;
         if (c > 0) {
             if (lane == 0) sc.kept[sn.nk] = uint8_t(j);
             ++sn.nk;
@@ -276,20 +363,24 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
     double cs_lane[kSmallCols];
 #pragma unroll
     for (int c = 0; c < kSmallCols; ++c) cs_lane[c] = 0.0;
-    for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+    const bool fastk = nk <= uint32_t(kSmallCols);  // counts of a block in registers (g_load_block_small)
+    G_FOR_BLOCKS(blk) {
+        if (fastk) {  // the usual table: every lane keeps its own partial column sums, one reduction at the end
+            uint32_t packed;
+            const uint32_t rs = g_load_block_small(g, sc, sn, blk, lane, packed);
+            n_used += __popc(__ballot_sync(0xffffffffu, rs > 0));
+            nondyadic |= __any_sync(0xffffffffu, (rs & (rs - 1)) != 0);
+            const double rinv = g_row_rcp(rs);
+#pragma unroll
+            for (int c = 0; c < kSmallCols; ++c)  // (columns >= nk hold 0; the product is exact, so the fma adds what the reference adds)
+                cs_lane[c] = fma(double((packed >> (4 * c)) & 15u), rinv, cs_lane[c]);
+            continue;
+        }
         const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
         const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
         n_used += __popc(used_ballot);
         nondyadic |= __any_sync(0xffffffffu, rs >= 3 && (rs & (rs - 1)) != 0);
         const double rsum = double(rs);
-        if (nk <= uint32_t(kSmallCols)) {  // the usual table: every lane keeps its own partial column sums, one reduction at the end
-#pragma unroll
-            for (int c = 0; c < kSmallCols; ++c) {
-                const uint32_t k = (uint32_t(c) < nk) ? sc.cnt[lane][c] : 0u;
-                cs_lane[c] += (k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;  // quantitative_table.cpp:93
-            }
-            continue;
-        }
         for (uint32_t c = 0; c < nk; ++c) {
             const uint32_t k = sc.cnt[lane][c];
             const double d = (k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;  // quantitative_table.cpp:93
@@ -306,6 +397,22 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
             const double tot = warp_sum(cs_lane[c]);  // dyadic terms: exact in any order (else the replay below decides)
             if (lane == uint32_t(c)) colsum0 = tot;
         }
+    }
+    uint32_t rank0 = 0;  // used samples in the blocks before this warp's: covariate rows go by FILTERED position
+    if (tm.size > 1) {
+        colsum0 = team_sum(tm, colsum0, lane);
+        if (nk > 32) colsum1 = team_sum(tm, colsum1, lane);
+        tm.buf[tm.rank * 32 + lane] = lane == 0 ? double(n_used) : (lane == 1 && nondyadic ? 1.0 : 0.0);
+        __syncthreads();
+        double tot_used = 0.0, tot_nd = 0.0;
+        for (uint32_t t = 0; t < tm.size; ++t) {
+            if (t == tm.rank) rank0 = uint32_t(tot_used);
+            tot_used += tm.buf[t * 32];
+            tot_nd += tm.buf[t * 32 + 1];
+        }
+        __syncthreads();
+        n_used = uint32_t(tot_used);
+        nondyadic = tot_nd > 0.0;
     }
     // remove_empty_columns is a no-op here (empty paths were never added); filtration (:549)
     if (n_used == 0 || nk < 2 || uint64_t(n_used) < g.thr.min_individuals) {
@@ -356,7 +463,7 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
             uint64_t cand = 0;
             for (uint32_t b2 = a + 1; b2 < nk; ++b2)
                 if (!sc.merged[b2]) cand |= 1ull << b2;
-            for (uint32_t blk = 0; blk < sn.n_blocks && cand; ++blk) {
+            for (uint32_t blk = sn.b0; blk < sn.b1 && cand; ++blk) {
                 g_load_block(g, sc, sn, blk, lane);
                 __syncwarp();
                 const uint8_t ka = sc.cnt[lane][a];
@@ -368,6 +475,7 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                 }
                 __syncwarp();
             }
+            cand = team_and64(tm, cand, lane);
             if (lane == 0)
                 for (uint32_t b2 = a + 1; b2 < nk; ++b2)
                     if ((cand >> b2) & 1ull) sc.merged[b2] = 1;
@@ -391,7 +499,7 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         finish_none(false, n_used, kPOverLimit);
         return;
     }
-    if (lane == 0) {
+    if (lane == 0 && writer) {
         g.out.filtered[s] = 0;
         g.out.n_used[s] = n_used;
     }
@@ -399,16 +507,17 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
     // entries e of [packed lower triangle of X^T X | X^T y | y'y | sum y] are owned by lanes (e % 32)
     const uint32_t n_tri = p * (p + 1) / 2;
     const uint32_t n_ent = n_tri + p + 2;
+    const bool small_p = p <= uint32_t(kSmallP);
     uint32_t er[6], ec[6];  // ceil((136 + 16 + 2) / 32) = 5
 #pragma unroll
     for (int q = 0; q < 6; ++q) {
         const uint32_t e = lane + 32u * q;
         uint32_t r = 0;
-        while ((r + 1) * (r + 2) / 2 <= e) ++r;
+        while (!small_p && (r + 1) * (r + 2) / 2 <= e) ++r;  // (the register sweeps of small designs do not use them)
         er[q] = r;
         ec[q] = e - r * (r + 1) / 2;
     }
-    uint32_t rank_base = 0;
+    uint32_t rank_base = rank0;
     auto build_tile = [&](uint32_t blk, uint32_t used_ballot, const double* y) {
         // lane = sample: write its X row (zeros when unused)
         const bool used = (used_ballot >> lane) & 1u;
@@ -431,24 +540,48 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
     };
     // the same row in REGISTERS (lane = sample), for designs of up to kSmallP features: the moment sweeps then keep
     // lane-private accumulators and reduce once per sweep, instead of 32-step loops over a shared-memory tile per block
-    const bool small_p = p <= uint32_t(kSmallP);
-    auto build_row = [&](uint32_t blk, uint32_t used_ballot, const double* y, double (&x)[kSmallP], double& yv) -> bool {
-        const bool used = (used_ballot >> lane) & 1u;
-        const uint32_t i = blk * 32 + lane;
-        const uint32_t rank = rank_base + __popc(used_ballot & ((1u << lane) - 1u));
-        const double rsum = double(sc.rs[lane]);
+    // column maps of the small design in registers; `fastk`: the block's counts come packed in a register as well
+    uint32_t fc[kSmallP - 1], fm[kSmallP - 1], fmask[kSmallP - 1];
+    bool has_mult = false;
 #pragma unroll
-        for (int r = 0; r < kSmallP; ++r) x[r] = 0.0;
+    for (int a = 0; a < kSmallP - 1; ++a) {
+        const bool on = small_p && uint32_t(a) < k_reg;
+        fc[a] = on ? sc.fcol[a] : 0u;
+        fm[a] = on ? sc.fmult[a] : 1u;
+        fmask[a] = on ? 15u : 0u;  // columns the design does not have read as count 0
+        has_mult |= fm[a] > 1;
+    }
+    // value of sample blk * 32 + lane: the phenotype, or the case flag of the logistic mode
+    auto load_y = [&](uint32_t blk, const double* y) -> double {
+        const uint32_t i = blk * 32 + lane;
+        if (blk >= sn.b1 || i >= g.n_samples) return 0.0;
+        return g.is_case ? (g.is_case[i] ? 1.0 : 0.0) : y[i];
+    };
+    // one block of the small design: counts (registers when fastk), the row in registers, y from the value loaded one
+    // block ahead (`y_next` in, refilled for blk + 1 before the arithmetic of this block so that the load is hidden)
+    auto build_row = [&](uint32_t blk, const double* y, double& y_next, double (&x)[kSmallP], double& yv) -> bool {
+        uint32_t packed = 0;
+        const uint32_t rs = fastk ? g_load_block_small(g, sc, sn, blk, lane, packed) : g_load_block(g, sc, sn, blk, lane);
+        const double y_cur = y_next;
+        y_next = load_y(blk + 1, y);
+        const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+        const bool used = rs > 0;
+        const uint32_t rank = rank_base + __popc(used_ballot & ((1u << lane) - 1u));
+        rank_base += __popc(used_ballot);
+        const double rinv = g_row_rcp(rs > 255 ? 255 : rs);  // (the clamp as sc.rs holds it)
         x[0] = used ? 1.0 : 0.0;
 #pragma unroll
-        for (int a = 0; a < kSmallP - 1; ++a)
-            if (uint32_t(a) < k_reg) {
-                const uint32_t k = sc.cnt[lane][sc.fcol[a]];
-                const double d = (used && k > 0) ? __ddiv_rn(double(k), rsum) : 0.0;
-                double v = d;
-                for (uint32_t m = 1; m < sc.fmult[a]; ++m) v = __dadd_rn(v, d);
-                x[1 + a] = v;
+        for (int a = 0; a < kSmallP - 1; ++a) {
+            const uint32_t k = (fastk ? (packed >> (4 * fc[a])) : uint32_t(sc.cnt[lane][fc[a]])) & fmask[a];
+            x[1 + a] = double(k) * rinv;  // k / row_sum (0 for an unused sample)
+        }
+        if (has_mult) {  // merged columns are sums of identical columns (:653-658): d + d + ... as the reference adds them
+#pragma unroll
+            for (int a = 0; a < kSmallP - 1; ++a) {
+                const double d = x[1 + a];
+                for (uint32_t m = 1; m < fm[a]; ++m) x[1 + a] = __dadd_rn(x[1 + a], d);
             }
+        }
 #pragma unroll
         for (int c = 0; c < kSmallP - 2; ++c)
             if (uint32_t(c) < g.n_covar && 1 + k_reg + uint32_t(c) < uint32_t(kSmallP)) {
@@ -457,7 +590,7 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                 for (int r = 2; r < kSmallP; ++r)
                     if (uint32_t(r) == 1 + k_reg + uint32_t(c)) x[r] = cv;
             }
-        yv = (used && i < g.n_samples) ? (g.is_case ? (g.is_case[i] ? 1.0 : 0.0) : y[i]) : 0.0;
+        yv = used ? y_cur : 0.0;
         return used;
     };
     if (g.is_case) {
@@ -480,7 +613,7 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         int state = 0;  // 0: iterate, 1: converged (this pass is the covariance pass), 2: done
         while (state != 2) {
             double* flat = &sc.tile[0][0];
-            rank_base = 0;
+            rank_base = rank0;
             if (small_p) {
                 double acc[kSmallTri + kSmallP];
 #pragma unroll
@@ -488,12 +621,10 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                 double bta[kSmallP];
 #pragma unroll
                 for (int r = 0; r < kSmallP; ++r) bta[r] = (uint32_t(r) < p) ? sc.beta[r] : 0.0;
-                for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
-                    const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
-                    const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+                double y_next = load_y(sn.b0, nullptr);
+                G_FOR_BLOCKS(blk) {
                     double x[kSmallP], yv;
-                    const bool used = build_row(blk, used_ballot, nullptr, x, yv);
-                    rank_base += __popc(used_ballot);
+                    const bool used = build_row(blk, nullptr, y_next, x, yv);
                     double z = 0.0;
 #pragma unroll
                     for (int r = 0; r < kSmallP; ++r) z = fma(x[r], bta[r], z);
@@ -510,20 +641,22 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                     }
                 }
 #pragma unroll
+                double mine = 0.0;  // lane e takes entry e (27 of them), one team reduction for all
+#pragma unroll
                 for (int e = 0; e < kSmallTri + kSmallP; ++e) {
                     const double v = warp_sum(acc[e]);
-                    if (lane == 0) {
-                        if (e < kSmallTri) {
-                            if (uint32_t(e) < n_tri) flat[e] = v;
-                        } else if (uint32_t(e - kSmallTri) < p) {
-                            flat[n_tri + (e - kSmallTri)] = v;
-                        }
-                    }
+                    if (lane == uint32_t(e)) mine = v;
+                }
+                mine = team_sum(tm, mine, lane);
+                if (lane < uint32_t(kSmallTri)) {
+                    if (lane < n_tri) flat[lane] = mine;
+                } else if (lane < uint32_t(kSmallTri + kSmallP) && lane - kSmallTri < p) {
+                    flat[n_tri + (lane - kSmallTri)] = mine;
                 }
                 __syncwarp();
             } else {
             double accv[6] = {0, 0, 0, 0, 0, 0};
-            for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+            G_FOR_BLOCKS(blk) {
                 const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
                 const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
                 __syncwarp();
@@ -557,7 +690,10 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
             }
 #pragma unroll
             for (int q = 0; q < 6; ++q)
-                if (lane + 32u * q < n_ent) flat[lane + 32u * q] = accv[q];
+                if (32u * q < n_ent) {  // warp-uniform condition: the team reduction holds a barrier
+                    const double v = team_sum(tm, accv[q], lane);
+                    if (lane + 32u * q < n_ent) flat[lane + 32u * q] = v;
+                }
             __syncwarp();
             }
             if (lane == 0) {
@@ -639,7 +775,7 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                         }
                     }
                 }
-                if (state == 2) {
+                if (state == 2 && writer) {
                     const uint64_t oi = s - g.item_base;
                     g.out.p[oi] = out_p;
                     if (g.out.r2) g.out.r2[oi] = nan;
@@ -663,17 +799,15 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         }
         // ---- sweep B: X^T X (first item only), X^T y, y'y, sum y ------------------------------------
         double* flat = &sc.tile[0][0];
-        rank_base = 0;
+        rank_base = rank0;
         if (small_p) {
             double acc[kSmallEnt];
 #pragma unroll
             for (int e = 0; e < kSmallEnt; ++e) acc[e] = 0.0;
-            for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
-                const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
-                const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+            double y_next = load_y(sn.b0, y);
+            G_FOR_BLOCKS(blk) {
                 double x[kSmallP], yv;
-                build_row(blk, used_ballot, y, x, yv);
-                rank_base += __popc(used_ballot);
+                build_row(blk, y, y_next, x, yv);
                 int e = 0;
 #pragma unroll
                 for (int r = 0; r < kSmallP; ++r) {
@@ -688,23 +822,25 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                 acc[kSmallTri + kSmallP + 1] += yv;
             }
 #pragma unroll
+            double mine = 0.0;  // lane e takes entry e (29 of them), one team reduction for all
+#pragma unroll
             for (int e = 0; e < kSmallEnt; ++e) {
                 if (e < kSmallTri && !first) continue;
                 const double v = warp_sum(acc[e]);
-                if (lane == 0) {
-                    if (e < kSmallTri) {
-                        if (uint32_t(e) < n_tri) flat[e] = v;
-                    } else if (e < kSmallTri + kSmallP) {
-                        if (uint32_t(e - kSmallTri) < p) flat[n_tri + (e - kSmallTri)] = v;
-                    } else {
-                        flat[n_tri + p + (e - kSmallTri - kSmallP)] = v;
-                    }
-                }
+                if (lane == uint32_t(e)) mine = v;
+            }
+            mine = team_sum(tm, mine, lane);
+            if (lane < uint32_t(kSmallTri)) {
+                if (first && lane < n_tri) flat[lane] = mine;
+            } else if (lane < uint32_t(kSmallTri + kSmallP)) {
+                if (lane - kSmallTri < p) flat[n_tri + (lane - kSmallTri)] = mine;
+            } else if (lane < uint32_t(kSmallEnt)) {
+                flat[n_tri + p + (lane - kSmallTri - kSmallP)] = mine;
             }
             __syncwarp();
         } else {
         double accv[6] = {0, 0, 0, 0, 0, 0};
-        for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+        G_FOR_BLOCKS(blk) {
             const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
             const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
             __syncwarp();
@@ -733,7 +869,10 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         // ---- solve on lane 0: gather the entries through shared memory (reuse the tile) --------------
 #pragma unroll
         for (int q = 0; q < 6; ++q)
-            if (lane + 32u * q < n_ent) flat[lane + 32u * q] = accv[q];
+            if (32u * q < n_ent) {  // warp-uniform condition: the team reduction holds a barrier
+                const double v = team_sum(tm, accv[q], lane);
+                if (lane + 32u * q < n_ent && (first || lane + 32u * q >= n_tri)) flat[lane + 32u * q] = v;
+            }
         __syncwarp();
         }
         double sum_y = 0.0;
@@ -762,17 +901,15 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         const double y_mean = sum_y / double(n_used);
         // ---- sweep C: residuals (stats_test.cpp:459-465) ----------------------------------------------
         double rss = 0.0, tss = 0.0;
-        rank_base = 0;
+        rank_base = rank0;
         if (small_p) {
             double bta[kSmallP];
 #pragma unroll
             for (int r = 0; r < kSmallP; ++r) bta[r] = (uint32_t(r) < p) ? sc.beta[r] : 0.0;
-            for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
-                const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
-                const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
+            double y_next = load_y(sn.b0, y);
+            G_FOR_BLOCKS(blk) {
                 double x[kSmallP], yv;
-                const bool used = build_row(blk, used_ballot, y, x, yv);
-                rank_base += __popc(used_ballot);
+                const bool used = build_row(blk, y, y_next, x, yv);
                 if (used) {
                     double pred = 0.0;
 #pragma unroll
@@ -784,7 +921,7 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
                 }
             }
         } else {
-        for (uint32_t blk = 0; blk < sn.n_blocks; ++blk) {
+        G_FOR_BLOCKS(blk) {
             const uint32_t rs = g_load_block(g, sc, sn, blk, lane);
             const uint32_t used_ballot = __ballot_sync(0xffffffffu, rs > 0);
             __syncwarp();
@@ -805,7 +942,12 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         }
         rss = warp_sum(rss);
         tss = warp_sum(tss);
-        if (lane == 0) {
+        if (tm.size > 1) {
+            const double aux = team_sum(tm, lane == 0 ? rss : (lane == 1 ? tss : 0.0), lane);
+            rss = __shfl_sync(0xffffffffu, aux, 0);
+            tss = __shfl_sync(0xffffffffu, aux, 1);
+        }
+        if (lane == 0 && writer) {
             const OlsOut o = ols_statistics(sc.beta[1], sc.inv[1 + p], rss, tss, n_used, int(p));
             const uint64_t oi = item - g.item_base;
             g.out.p[oi] = o.p;
@@ -818,18 +960,44 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
     }
 }
 
-__global__ void __launch_bounds__(kGWarps * 32) quant_general_kernel(const GParams g) {
+// n > kGTeamWarps-wide teams pay off only while there are fewer snarls than the grid has warp slots
+__device__ __forceinline__ bool g_team_mode(const GParams& g, uint64_t n, uint32_t team_limit) {
+    return team_limit > 0 && n <= team_limit;
+}
+
+__global__ void __launch_bounds__(kGWarps * 32) quant_general_kernel(const GParams g, uint32_t team_limit) {
     extern __shared__ __align__(16) uint8_t g_smem[];
     GScratch* scratch = reinterpret_cast<GScratch*>(g_smem);
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint64_t gw = uint64_t(blockIdx.x) * kGWarps + warp;
     const uint64_t n_warps = uint64_t(gridDim.x) * kGWarps;
     const uint64_t split = (g.items_by_slot && g.gene_split > 1) ? g.gene_split : 1;
-    const uint64_t n = ((g.list && g.n_list_dev) ? uint64_t(*g.n_list_dev) : g.n_list_host) * split;
+    const uint64_t n_list = (g.list && g.n_list_dev) ? uint64_t(*g.n_list_dev) : g.n_list_host;
+    if (g_team_mode(g, n_list, team_limit)) return;  // quant_general_team_kernel has them
+    const uint64_t n = n_list * split;
+    const GTeam tm{0u, 1u, nullptr};
     for (uint64_t i = gw; i < n; i += n_warps) {
         const uint64_t entry = i / split;
         const uint64_t s = g.list ? g.list[entry] : g.s_begin + entry;
-        quant_general(g, scratch[warp], s, entry, uint32_t(i - entry * split), lane);
+        quant_general(g, scratch[warp], s, entry, uint32_t(i - entry * split), lane, tm);
+    }
+}
+
+// The short list (a handful of stray snarls behind the integer-MMA kernels, a small batch): one CTA of kGTeamWarps warps
+// per snarl.  A lone warp is latency bound (~0.7 ms for one snarl at 5,000 samples, 3.4 ms at 25,000), so the step
+// waited on a single warp; here the sample sweeps of the snarl are spread over the team.
+__global__ void __launch_bounds__(kGTeamWarps * 32) quant_general_team_kernel(const GParams g, uint32_t team_limit) {
+    extern __shared__ __align__(16) uint8_t g_smem[];
+    GScratch* scratch = reinterpret_cast<GScratch*>(g_smem);
+    double* buf = reinterpret_cast<double*>(g_smem + sizeof(GScratch) * kGTeamWarps);
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t n_list = (g.list && g.n_list_dev) ? uint64_t(*g.n_list_dev) : g.n_list_host;
+    if (!g_team_mode(g, n_list, team_limit)) return;
+    const GTeam tm{warp, uint32_t(kGTeamWarps), buf};
+    for (uint64_t entry = blockIdx.x; entry < n_list; entry += gridDim.x) {
+        const uint64_t s = g.list ? g.list[entry] : g.s_begin + entry;
+        quant_general(g, scratch[warp], s, entry, 0u, lane, tm);
+        __syncthreads();
     }
 }
 
@@ -837,9 +1005,27 @@ inline cudaError_t launch_quant_general(const GParams& g, uint64_t max_items, in
     const int smem = int(sizeof(GScratch) * kGWarps);
     cudaError_t e = cudaFuncSetAttribute(quant_general_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
+    // teams while they finish sooner than one warp per snarl would: ceil(n / SMs) / 8 against ceil(n / (12 SMs))
+    static const bool no_team = [] {
+        const char* v = getenv("STOAT_GPU_K3G_TEAM");
+        return v && v[0] == '0';
+    }();
+    const bool team_ok = !no_team && !(g.items_by_slot && g.gene_split > 1);
+    const uint32_t team_limit = team_ok ? uint32_t(num_sms) * 6u : 0u;
+    const bool count_on_device = g.list && g.n_list_dev;
+    if (team_ok && (count_on_device || g.n_list_host <= team_limit)) {
+        const int tsmem = int(sizeof(GScratch) * kGTeamWarps + sizeof(double) * kGTeamWarps * 32);
+        e = cudaFuncSetAttribute(quant_general_team_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tsmem);
+        if (e != cudaSuccess) return e;
+        const uint64_t n_max = max_items < uint64_t(num_sms) ? max_items : uint64_t(num_sms);  // one resident team per SM
+        quant_general_team_kernel<<<unsigned(n_max ? n_max : 1), kGTeamWarps * 32, tsmem, st>>>(g, team_limit);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        if (!count_on_device) return cudaSuccess;
+    }
     const uint64_t want = (max_items + kGWarps - 1) / kGWarps;
     const uint64_t cap = uint64_t(num_sms) * 3;  // 3 CTAs of ~70 KB shared memory per SM
     const unsigned grid = unsigned(want < cap ? (want ? want : 1) : cap);
-    quant_general_kernel<<<grid, kGWarps * 32, smem, st>>>(g);
+    quant_general_kernel<<<grid, kGWarps * 32, smem, st>>>(g, team_limit);
     return cudaGetLastError();
 }
