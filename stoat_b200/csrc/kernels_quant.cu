@@ -19,6 +19,7 @@
 // are re-done by K3G on the raw phenotype with an explicit residual pass, as the reference does (:460-463).
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
 #include "ctx.hpp"
 #include "dosage_masks.cuh"
@@ -1021,11 +1022,52 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                 if (lean_key) *lean_key = key;
                 if (launches) *launches += 1;
             }
+            // K3M variant: the register kernel, or the cp.async ring kernel (STOAT_GPU_K3M_RING=<warps>x<stages>, one CTA per
+            // SM).  Measured at C3 on one box: register kernel 1.26 ms; ring 8x2 1.42, 10x2 1.34, 11x2 1.23, 6x3 1.90, 7x3
+            // 1.65 ms - the time follows the number of warps, not the way the rows arrive: K3M is bound by the issue rate of
+            // its ~138 instructions per word step (the bare access patterns reach 5.4-6.8 TB/s, scripts/micro/k3m_pattern.cu)
+            const int ring_cfg = [] {
+                const char* v = std::getenv("STOAT_GPU_K3M_RING");
+                if (!v || !std::strcmp(v, "0")) return 0;
+                if (!std::strcmp(v, "8x2")) return 82;
+                if (!std::strcmp(v, "10x2")) return 102;
+                if (!std::strcmp(v, "11x2")) return 112;
+                if (!std::strcmp(v, "6x3")) return 63;
+                if (!std::strcmp(v, "7x3")) return 73;
+                return 0;
+            }();
+            const uint64_t n_tiles = (b.n_snarls + kMmaTile - 1) / kMmaTile;
+            int dev_now = 0;
+            cudaGetDevice(&dev_now);
+            K3MParams q_main = q;
+            // With several haplotype slices a snarl's thirds may show in one slice only, so K3M does not append to the
+            // thirds list itself (the slices would race on the snarl's state): K4 sends such a snarl to the general list
+            if (wide_table) q_main.rec2x = nullptr;
+            auto launch_ring = [&](auto kernel, int warps, int stages) -> cudaError_t {
+                const uint32_t smem = pm.smem_bytes + uint32_t(warps * stages) * kRingStageBytes;
+                static thread_local int ring_dev = -1;
+                static thread_local uint32_t ring_smem = 0;
+                if (dev_now != ring_dev || smem != ring_smem) {
+                    cudaError_t e2 = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+                    if (e2 != cudaSuccess) return e2;
+                    ring_dev = dev_now;
+                    ring_smem = smem;
+                }
+                uint64_t ctas = uint64_t(num_sms) / pm.n_slices;
+                if (ctas < 1) ctas = 1;
+                if (ctas > (n_tiles + warps - 1) / warps) ctas = (n_tiles + warps - 1) / warps;
+                kernel<<<dim3(unsigned(ctas), pm.n_slices), warps * 32, smem, st>>>(q_main);
+                return cudaGetLastError();
+            };
+            if (ring_cfg == 82) e = launch_ring(dosage_moments_mma_ring_kernel<8, 2>, 8, 2);
+            else if (ring_cfg == 102) e = launch_ring(dosage_moments_mma_ring_kernel<10, 2>, 10, 2);
+            else if (ring_cfg == 112) e = launch_ring(dosage_moments_mma_ring_kernel<11, 2>, 11, 2);
+            else if (ring_cfg == 63) e = launch_ring(dosage_moments_mma_ring_kernel<6, 3>, 6, 3);
+            else if (ring_cfg == 73) e = launch_ring(dosage_moments_mma_ring_kernel<7, 3>, 7, 3);
+            else {
             // attribute + occupancy query once per (device, shared-memory size): they are driver calls, not free per step
             static thread_local int cached_dev = -1, cached_occ = 1;
             static thread_local uint32_t cached_smem = 0;
-            int dev_now = 0;
-            cudaGetDevice(&dev_now);
             if (dev_now != cached_dev || pm.smem_bytes != cached_smem) {
                 e = cudaFuncSetAttribute(dosage_moments_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          int(pm.smem_bytes));
@@ -1041,17 +1083,13 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
             int occ = cached_occ;
             const int occ_env = env_int("STOAT_GPU_K3M_CTAS", 0);
             if (occ_env >= 1 && occ_env < occ) occ = occ_env;
-            const uint64_t n_tiles = (b.n_snarls + kMmaTile - 1) / kMmaTile;
             uint64_t ctas = uint64_t(num_sms) * uint64_t(occ) / pm.n_slices;
             if (ctas < 1) ctas = 1;
             if (ctas > (n_tiles + kMmaWarps - 1) / kMmaWarps) ctas = (n_tiles + kMmaWarps - 1) / kMmaWarps;
-            {
-                // With several haplotype slices a snarl's thirds may show in one slice only, so K3M does not append to the
-                // thirds list itself (the slices would race on the snarl's state): K4 sends such a snarl to the general list
-                K3MParams q_main = q;
-                if (wide_table) q_main.rec2x = nullptr;
-                dosage_moments_mma_kernel<<<dim3(unsigned(ctas), pm.n_slices), kMmaWarps * 32, pm.smem_bytes, st>>>(q_main);
+            dosage_moments_mma_kernel<<<dim3(unsigned(ctas), pm.n_slices), kMmaWarps * 32, pm.smem_bytes, st>>>(q_main);
+            e = cudaGetLastError();
             }
+            if (e != cudaSuccess) return e;
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             if (ev_table_done && (e = cudaEventRecord(ev_table_done, st)) != cudaSuccess) return e;
             if (launches) *launches += 1;

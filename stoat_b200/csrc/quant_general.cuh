@@ -552,14 +552,15 @@ __device__ void quant_general(const GParams& g, GScratch& sc, uint64_t s, uint64
         has_mult |= fm[a] > 1;
     }
     // value of sample blk * 32 + lane: the phenotype, or the case flag of the logistic mode
-    auto load_y = [&](uint32_t blk, const double* y) -> double {
+    auto load_y = [&](uint32_t blk, const double* y) __attribute__((always_inline)) -> double {
         const uint32_t i = blk * 32 + lane;
         if (blk >= sn.b1 || i >= g.n_samples) return 0.0;
         return g.is_case ? (g.is_case[i] ? 1.0 : 0.0) : y[i];
     };
     // one block of the small design: counts (registers when fastk), the row in registers, y from the value loaded one
     // block ahead (`y_next` in, refilled for blk + 1 before the arithmetic of this block so that the load is hidden)
-    auto build_row = [&](uint32_t blk, const double* y, double& y_next, double (&x)[kSmallP], double& yv) -> bool {
+    auto build_row = [&](uint32_t blk, const double* y, double& y_next, double (&x)[kSmallP], double& yv)
+                         __attribute__((always_inline)) -> bool {
         uint32_t packed = 0;
         const uint32_t rs = fastk ? g_load_block_small(g, sc, sn, blk, lane, packed) : g_load_block(g, sc, sn, blk, lane);
         const double y_cur = y_next;

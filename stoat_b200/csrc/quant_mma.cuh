@@ -268,6 +268,65 @@ __device__ __forceinline__ void mma_compute_round(const K3MParams& q, MmaLaneSum
     }
 }
 
+// tile epilogue shared by the two K3M kernels: the 4 lanes of a group hold the pieces of the same two snarls
+__device__ __forceinline__ void mma_tile_epilogue(const K3MParams& q, MmaLaneSums& z, const uint4 (&lr)[2], uint64_t tile,
+                                                  uint32_t slice, uint32_t g, uint32_t t, double sc0, double sc1) {
+    const K3Params& p = q.k;
+    double xs[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        xs[h] = double(z.c[2 * h]) * sc0 + double(z.c[2 * h + 1]) * sc1;
+#pragma unroll
+        for (int o = 1; o <= 2; o <<= 1) {
+            z.cA[h] += __shfl_xor_sync(0xffffffffu, z.cA[h], o);
+            z.cB[h] += __shfl_xor_sync(0xffffffffu, z.cB[h], o);
+            z.cC[h] += __shfl_xor_sync(0xffffffffu, z.cC[h], o);
+            z.nd[h] |= __shfl_xor_sync(0xffffffffu, z.nd[h], o);
+            xs[h] += __shfl_xor_sync(0xffffffffu, xs[h], o);
+        }
+    }
+    if (__any_sync(0xffffffffu, z.saw_unused)) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int o = 1; o <= 2; o <<= 1) {
+                z.su[h] += __shfl_xor_sync(0xffffffffu, z.su[h], o);
+                z.suu[h] += __shfl_xor_sync(0xffffffffu, z.suu[h], o);
+            }
+    }
+    if (t == 0) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint64_t s = tile * kMmaTile + g + 8u * h;
+            if (s >= p.n_snarls) continue;
+            if (z.live[h] && z.nd[h] != 0u && q.rec2x != nullptr) {
+                // a sample on three path-haplotypes (overlapping paths): dosages of 1/3, 2/3 -> the 2x kernel
+                mma_push_thirds(q.rec2x, q.count2x, q.count2x_dyn, p.mom, uint32_t(s), lr[h]);
+            } else if (z.live[h]) {
+                uint32_t* pi = q.part.i + size_t(slice) * 7 * q.part.stride + s;
+                double* pd = q.part.d + size_t(slice) * 3 * q.part.stride + s;
+                pi[0] = z.cA[h] & 0xFFFFu;
+                pi[q.part.stride] = z.cA[h] >> 16;
+                pi[2 * q.part.stride] = z.cB[h] & 0xFFFFu;
+                pi[3 * q.part.stride] = z.cB[h] >> 16;
+                pi[4 * q.part.stride] = z.cC[h];
+                pi[5 * q.part.stride] = 0u;
+                pi[6 * q.part.stride] = z.nd[h] ? kLeanReplayMark : 0u;  // K4 sends the snarl to the general path
+                pd[0] = 0.5 * q.y_scale * xs[h];  // d = (2d) / 2
+                pd[q.part.stride] = z.su[h];
+                pd[2 * q.part.stride] = z.suu[h];
+                if (slice == 0) p.mom[s].state = 2;  // K4 builds the moments from the partial sums
+            } else if (slice == 0) {
+                p.mom[s].state = 0;
+                if (lr[h].y != 0u) {  // no paths at all: prep already put the snarl on the general list
+                    const uint32_t slot = atomicAdd(q.slow_count, 1u);
+                    q.slow_list[slot] = uint32_t(s);
+                }
+            }
+        }
+    }
+}
+
 // =================================================================================================
 // K3M kernel.  grid = (CTAs, haplotype slices); every WARP owns tiles of 16 consecutive snarls (no barrier, no shared
 // state between warps but the read-only slice table).  dynamic shared memory: the slice table of this haplotype slice.
@@ -328,60 +387,130 @@ __global__ void __launch_bounds__(kMmaWarps * 32, 2) dosage_moments_mma_kernel(c
             mma_load_round(q, lr, z.live, (c + 2 < r_len) ? (r_first + c + 2) * 4 + t : 0xFFFFFFF0u, ra);
             if (c + 1 < r_len) mma_compute_round(q, z, rb, (r_first + c + 1) * 4 + t, bfrag_lane + size_t(c + 1) * 2048);
         }
-        // ---- tile epilogue: the 4 lanes of a group hold the pieces of the same two snarls -------------------------
-        double xs[2];
+        mma_tile_epilogue(q, z, lr, tile, slice, g, t, sc0, sc1);
+        lr[0] = lr_next[0];
+        lr[1] = lr_next[1];
+    }
+}
+
+// =================================================================================================
+// K3M, ring variant (the default): the same tiles, class counts and MMAs, but the rows arrive through a per-warp
+// shared-memory ring filled with cp.async instead of through registers.
+//   * a copy instruction of the warp moves 128 contiguous bytes (a whole L2 line) of 4 rows (8 lanes x 16 B per row); a
+//     stage is 128 B of each of the tile's 64 rows = 8 KB; S stages per warp.  Nothing in flight lives in registers, so
+//     the loop holds one round (32 registers) instead of two rounds in flight + the one being worked on.
+//   * within a stage row r = h * 32 + g * 4 + k of the tile sits at r * 128, its 16-byte chunk c at (c ^ 4 (g & 1)) * 16:
+//     the quarter-warp of an LDS.128 (g in {2q, 2q + 1}, t = 0..3) then touches all 32 banks once.
+//   * lane (g, t) reads chunks t and 4 + t of its 8 rows back as the two rounds 2m, 2m + 1 of macro step m: the chunk
+//     numbering, the B fragments and the arithmetic are those of the register kernel, bit for bit.
+// Measured on the bare access pattern (scripts/micro/k3m_pattern.cu, 5.1 GB, no arithmetic): 64 B x 8 rows through
+// registers 5.4-6.1 TB/s with 16 warps per SM, this ring 6.7-6.8 TB/s with 8.
+// =================================================================================================
+constexpr int kRingStageBytes = 64 * 128;
+
+template <int WARPS, int S>
+__global__ void __launch_bounds__(WARPS * 32, 1) dosage_moments_mma_ring_kernel(const K3MParams q) {
+    extern __shared__ __align__(128) uint8_t ysl[];
+    const K3Params& p = q.k;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const uint32_t slice = blockIdx.y;
+    const uint32_t r_first = slice * q.rounds_per_slice;
+    const uint32_t r_len = min(q.rounds_per_slice, q.n_rounds - r_first);
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(q.yslices + size_t(r_first) * 2048);
+        uint4* dst = reinterpret_cast<uint4*>(ysl);
+        for (uint32_t i = tid; i < r_len * 128u; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    const uint8_t* bfrag_lane = ysl + lane * 8;
+    uint8_t* ring = ysl + size_t(q.rounds_per_slice) * 2048 + size_t(warp) * S * kRingStageBytes;
+    const uint32_t ring_s = uint32_t(__cvta_generic_to_shared(ring));
+    // copy mapping: instruction i of a stage moves the rows of snarl (h = i >> 3, g = i & 7); this lane takes row k = sub
+    const uint32_t sub = lane >> 3, c8 = lane & 7;
+    // read mapping: this lane's 8 rows, chunk t (+ 4 for the odd round), swizzled by g & 1
+    const uint32_t rd_chunk = (t ^ ((g & 1u) << 2)) * 16;
+
+    const uint64_t n_tiles = (p.n_snarls + kMmaTile - 1) / kMmaTile;
+    const uint64_t stride = uint64_t(gridDim.x) * WARPS;
+    const double sc0 = __hiloint2double(int((1023u - 7u * (2u * t + 1u)) << 20), 0);
+    const double sc1 = __hiloint2double(int((1023u - 7u * (2u * t + 2u)) << 20), 0);
+    const uint32_t n_macro = (r_len + 1) / 2;
+    const uint32_t chunk_end = (r_first + r_len) * 4 < p.pitch / 16 ? (r_first + r_len) * 4 : p.pitch / 16;
+
+    uint64_t tile = uint64_t(blockIdx.x) * WARPS + warp;
+    uint4 lr[2], lr_next[2];
+    auto load_recs = [&](uint64_t tl, uint4 (&dst)[2]) {
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            xs[h] = double(z.c[2 * h]) * sc0 + double(z.c[2 * h + 1]) * sc1;
-#pragma unroll
-            for (int o = 1; o <= 2; o <<= 1) {
-                z.cA[h] += __shfl_xor_sync(0xffffffffu, z.cA[h], o);
-                z.cB[h] += __shfl_xor_sync(0xffffffffu, z.cB[h], o);
-                z.cC[h] += __shfl_xor_sync(0xffffffffu, z.cC[h], o);
-                z.nd[h] |= __shfl_xor_sync(0xffffffffu, z.nd[h], o);
-                xs[h] += __shfl_xor_sync(0xffffffffu, xs[h], o);
-            }
+            const uint64_t s = tl * kMmaTile + g + 8u * h;
+            dst[h] = (tl < n_tiles && s < p.n_snarls) ? __ldg(q.lean_rec + s) : make_uint4(kLeanNo, 0u, 0u, 0u);
         }
-        if (__any_sync(0xffffffffu, z.saw_unused)) {
+    };
+    load_recs(tile, lr);
+    for (; tile < n_tiles; tile += stride) {
+        load_recs(tile + stride, lr_next);
+        MmaLaneSums z;
 #pragma unroll
-            for (int h = 0; h < 2; ++h)
-#pragma unroll
-                for (int o = 1; o <= 2; o <<= 1) {
-                    z.su[h] += __shfl_xor_sync(0xffffffffu, z.su[h], o);
-                    z.suu[h] += __shfl_xor_sync(0xffffffffu, z.suu[h], o);
-                }
+        for (int h = 0; h < 2; ++h) {
+            z.cA[h] = z.cB[h] = z.cC[h] = z.nd[h] = 0u;
+            z.su[h] = z.suu[h] = 0.0;
+            z.live[h] = (lr[h].x != kLeanNo) ? 0xFFFFFFFFu : 0u;
         }
-        if (t == 0) {
+        z.c[0] = z.c[1] = z.c[2] = z.c[3] = 0;
+        z.saw_unused = false;
+        // rows this lane copies: component t of the record of the lane it is fetched from equals that lane's k = sub
+        uint32_t rid[16];
+        {
+            uint32_t comp[2];
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const uint64_t s = tile * kMmaTile + g + 8u * h;
-                if (s >= p.n_snarls) continue;
-                if (z.live[h] && z.nd[h] != 0u && q.rec2x != nullptr) {
-                    // a sample on three path-haplotypes (overlapping paths): dosages of 1/3, 2/3 -> the 2x kernel
-                    mma_push_thirds(q.rec2x, q.count2x, q.count2x_dyn, p.mom, uint32_t(s), lr[h]);
-                } else if (z.live[h]) {
-                    uint32_t* pi = q.part.i + size_t(slice) * 7 * q.part.stride + s;
-                    double* pd = q.part.d + size_t(slice) * 3 * q.part.stride + s;
-                    pi[0] = z.cA[h] & 0xFFFFu;
-                    pi[q.part.stride] = z.cA[h] >> 16;
-                    pi[2 * q.part.stride] = z.cB[h] & 0xFFFFu;
-                    pi[3 * q.part.stride] = z.cB[h] >> 16;
-                    pi[4 * q.part.stride] = z.cC[h];
-                    pi[5 * q.part.stride] = 0u;
-                    pi[6 * q.part.stride] = z.nd[h] ? kLeanReplayMark : 0u;  // K4 sends the snarl to the general path
-                    pd[0] = 0.5 * q.y_scale * xs[h];  // d = (2d) / 2
-                    pd[q.part.stride] = z.su[h];
-                    pd[2 * q.part.stride] = z.suu[h];
-                    if (slice == 0) p.mom[s].state = 2;  // K4 builds the moments from the partial sums
-                } else if (slice == 0) {
-                    p.mom[s].state = 0;
-                    if (lr[h].y != 0u) {  // no paths at all: prep already put the snarl on the general list
-                        const uint32_t slot = atomicAdd(q.slow_count, 1u);
-                        q.slow_list[slot] = uint32_t(s);
-                    }
+                const uint32_t v = t == 0 ? lr[h].x : t == 1 ? lr[h].y : t == 2 ? lr[h].z : lr[h].w;
+                comp[h] = z.live[h] ? v : kLeanNo;
+            }
+#pragma unroll
+            for (int i = 0; i < 16; ++i) rid[i] = __shfl_sync(0xffffffffu, comp[i >> 3], (i & 7) * 4 + sub);
+        }
+        auto issue = [&](uint32_t m) {
+            if (m < n_macro) {
+                const uint32_t chunk = (r_first + 2 * m) * 4 + c8;  // 16-byte chunk of the row this lane copies
+                const bool in = chunk < chunk_end;
+                const uint32_t dst0 = ring_s + (m % S) * kRingStageBytes + sub * 128 + c8 * 16;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const bool ok = in && rid[i] != kLeanNo;
+                    const uint8_t* src = p.rows + (ok ? size_t(rid[i]) * p.pitch + size_t(chunk) * 16 : size_t(0));
+                    // row i * 4 + sub; g = i & 7 -> swizzle bit i & 1
+                    const uint32_t dst = (dst0 + i * 512) ^ ((uint32_t(i) & 1u) << 6);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(ok ? 16u : 0u)
+                                 : "memory");
                 }
             }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+#pragma unroll
+        for (int m = 0; m < S - 1; ++m) issue(m);
+        for (uint32_t m = 0; m < n_macro; ++m) {
+            issue(m + S - 1);
+            asm volatile("cp.async.wait_group %0;" ::"n"(S - 1) : "memory");
+            __syncwarp();
+            const uint8_t* st = ring + (m % S) * kRingStageBytes + g * 512;
+#pragma unroll
+            for (int sr = 0; sr < 2; ++sr) {
+                const uint32_t round = 2 * m + sr;
+                if (round < r_len) {
+                    MmaRound d;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            d.v[h][k] = *reinterpret_cast<const uint4*>(st + h * 4096 + k * 128 + (rd_chunk ^ (sr * 64u)));
+                    mma_compute_round(q, z, d, (r_first + round) * 4 + t, bfrag_lane + size_t(round) * 2048);
+                }
+            }
+            __syncwarp();
         }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        mma_tile_epilogue(q, z, lr, tile, slice, g, t, sc0, sc1);
         lr[0] = lr_next[0];
         lr[1] = lr_next[1];
     }

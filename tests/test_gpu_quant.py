@@ -167,6 +167,24 @@ def test_two_path_integer_contraction(gpu_ctx, oracle, seed, n_samples, frac_mis
     assert (ref["filtered"] == 0).sum() > 20
 
 
+@pytest.mark.parametrize("ring", ["8x2", "11x2", "6x3"])
+@pytest.mark.parametrize("n_samples,frac_missing,overlap", [(1300, 0.45, 0), (500, 0.02, 7), (7000, 0.01, 0)])
+def test_two_path_contraction_ring_variant(gpu_ctx, oracle, monkeypatch, ring, n_samples, frac_missing, overlap):
+    """The cp.async ring variant of K3M (STOAT_GPU_K3M_RING, rows through a per-warp shared-memory ring instead of
+    registers) does the register kernel's arithmetic in its order: parity with the oracle AND bit-identical results,
+    at one and at two haplotype slices (14,000 haplotypes), odd numbers of rounds included."""
+    rng = np.random.default_rng(77)
+    dense, snarls = _two_path_problem(rng, 96 if n_samples >= 7000 else 330, n_samples, frac_missing, overlap)
+    y = rng.normal(size=n_samples) * 2.5 - 40.0
+    y = y + 0.8 * dense[snarls[1][0][0]].reshape(n_samples, 2).sum(1)
+    base, ref = run_both(gpu_ctx, oracle, dense, snarls, y, min_ind=2, min_hap=2, maf=0.01)
+    monkeypatch.setenv("STOAT_GPU_K3M_RING", ring)
+    got, _ = run_both(gpu_ctx, oracle, dense, snarls, y, min_ind=2, min_hap=2, maf=0.01)
+    H.assert_quant_equal(got, ref)
+    for k in ("p_value", "beta", "se", "r2", "n_used", "filtered", "allele_paths"):
+        np.testing.assert_array_equal(got[k], base[k], err_msg=k)
+
+
 def test_two_path_integer_contraction_phenotype_range(gpu_ctx, oracle):
     """The slice split uses ONE fixed-point scale for the whole phenotype: a heavy-tailed phenotype (values from 1e-7 to
     1e5) must still give 1e-9 parity, and a constant phenotype (all slices zero) the reference's degenerate rows."""
