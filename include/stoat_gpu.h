@@ -312,6 +312,18 @@ STOAT_GPU_API int stoat_gpu_set_matrix_pairs(stoat_gpu_ctx* ctx, const uint32_t*
  * values).  p must be finite and >= 0: the caller drops the rows the reference's string_to_pvalue would not parse.  Host
  * buffers; n < 2^31.                                                                                                  */
 STOAT_GPU_API int stoat_gpu_bh_adjust(stoat_gpu_ctx* ctx, const double* p, uint64_t n, double* p_adjusted);
+/* The same adjustment WITHOUT ANY ALLOCATION.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The scratch of the sort and the scan lives in a file-scope device array of the library (64 MiB, held by
+ * every GPU that loads the library until the process exits), so n <= STOAT_GPU_BH_STATIC_MAX_N; a larger n is rejected
+ * with STOAT_GPU_ERR_ARG and a message.  p and p_adjusted may be host OR device pointers (unified addressing decides);
+ * the values are validated on the device (finite and >= 0, else STOAT_GPU_ERR_ARG and p_adjusted is left untouched).
+ * Calls neither cudaMalloc nor cudaFree nor an allocating library routine.  The array is shared by every call and every
+ * context of the process on that GPU: calls that overlap on the GPU race on it (this call synchronises its stream before
+ * it returns, so calls made one after the other from one thread are safe).  Results are bit-identical to
+ * stoat_gpu_bh_adjust.                                                                                               */
+#define STOAT_GPU_BH_STATIC_MAX_N 1048576
+STOAT_GPU_API int stoat_gpu_bh_adjust_static(stoat_gpu_ctx* ctx, const double* p, uint64_t n, double* p_adjusted);
 /* bytes per repacked row on the device: ceil(n_cols / 256) * 32 (whole 32-byte sectors)         */
 STOAT_GPU_API uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx);
 /* read back one repacked row (tests of K0)                                                  */

@@ -106,6 +106,7 @@ SIGNATURES = {
     "stoat_gpu_stream": (C.c_uint64, [CTX]),
     "stoat_gpu_set_matrix_pairs": (C.c_int, [CTX, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64]),
     "stoat_gpu_bh_adjust": (C.c_int, [CTX, C.c_void_p, C.c_uint64, C.c_void_p]),
+    "stoat_gpu_bh_adjust_static": (C.c_int, [CTX, C.c_void_p, C.c_uint64, C.c_void_p]),
     "stoat_gpu_row_pitch": (C.c_uint64, [CTX]),
     "stoat_gpu_read_row": (C.c_int, [CTX, C.c_uint64, C.c_void_p, C.c_uint64]),
     "stoat_gpu_format_value": (C.c_int, [C.c_double, C.c_uint8, C.c_char_p, C.c_size_t]),

@@ -146,6 +146,20 @@ class Context:
         self._check(self._lib.stoat_gpu_bh_adjust(self._ctx, _ptr(a), a.size, _ptr(out)))
         return out
 
+    BH_STATIC_MAX_N = 1 << 20  # STOAT_GPU_BH_STATIC_MAX_N of include/stoat_gpu.h
+
+    def bh_adjust_static(self, p) -> np.ndarray:
+        """As bh_adjust through stoat_gpu_bh_adjust_static: scratch in a static device array of the library, no allocation
+        on the device; at most BH_STATIC_MAX_N p-values.  Calls that overlap on the GPU race on the shared scratch."""
+        a = np.ascontiguousarray(p, dtype=np.float64)
+        out = np.empty_like(a)
+        self._check(self._lib.stoat_gpu_bh_adjust_static(self._ctx, _ptr(a), a.size, _ptr(out)))
+        return out
+
+    def bh_adjust_static_dev(self, p_dev: int, n: int, out_dev: int) -> None:
+        """The same with device pointers of the caller (nothing crosses PCIe but the validity flag)."""
+        self._check(self._lib.stoat_gpu_bh_adjust_static(self._ctx, C.c_void_p(int(p_dev)), int(n), C.c_void_p(int(out_dev))))
+
     def debug_umma_probe(self, a, b) -> np.ndarray:
         """int32 C [128][rows of b] = a [128][k] @ b[rows][k].T through the tcgen05 kernel of the dense eQTL scan (tests)"""
         a = np.ascontiguousarray(a, dtype=np.int8)

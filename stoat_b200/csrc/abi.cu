@@ -488,6 +488,24 @@ int stoat_gpu_bh_adjust(stoat_gpu_ctx* ctx, const double* p, uint64_t n, double*
     return STOAT_GPU_OK;
 }
 
+// No counterpart in the reference (see include/stoat_gpu.h): Benjamini-Hochberg with the scratch in a file-scope device
+// array of kernels_post.cu.  Nothing here allocates: no DevBuf::reserve, no cudaMalloc / cudaFree, CUB is given its storage.
+int stoat_gpu_bh_adjust_static(stoat_gpu_ctx* ctx, const double* p, uint64_t n, double* p_adjusted) {
+    if (!ctx) return STOAT_GPU_ERR_ARG;
+    if (n == 0) return STOAT_GPU_OK;  // src/post_processing.cpp:9
+    if (!p || !p_adjusted) return fail(ctx, STOAT_GPU_ERR_ARG, "bh_adjust_static: NULL argument");
+    if (n > bh_static_max_n())
+        return fail(ctx, STOAT_GPU_ERR_ARG,
+                    "bh_adjust_static: n = " + std::to_string(n) + " exceeds the static scratch (STOAT_GPU_BH_STATIC_MAX_N = " +
+                        std::to_string(bh_static_max_n()) + " p-values); use stoat_gpu_bh_adjust");
+    CK(cudaSetDevice(ctx->device));
+    uint32_t bad = 0;
+    CK(launch_bh_adjust_static(ctx->device, p, n, p_adjusted, &bad, ctx->stream));
+    if (bad)
+        return fail(ctx, STOAT_GPU_ERR_ARG, "bh_adjust_static: p-values must be finite and >= 0 (drop the NA rows first)");
+    return STOAT_GPU_OK;
+}
+
 uint64_t stoat_gpu_row_pitch(const stoat_gpu_ctx* ctx) { return ctx ? ctx->pitch : 0; }
 uint64_t stoat_gpu_stream(const stoat_gpu_ctx* ctx) { return ctx ? reinterpret_cast<uint64_t>(ctx->stream) : 0; }
 

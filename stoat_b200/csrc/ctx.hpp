@@ -105,6 +105,9 @@ cudaError_t launch_binary_stats(const BatchDev& b, const uint32_t* counts, const
 size_t bh_temp_bytes(uint64_t n);
 cudaError_t launch_bh_adjust(const double* p, uint64_t n, double* out, uint64_t* keys_sorted, uint32_t* idx_in,
                              uint32_t* idx_sorted, double* a, double* b, void* temp, size_t temp_bytes, cudaStream_t st);
+// the same with its scratch in a file-scope device array (no allocation; stoat_gpu_bh_adjust_static)
+uint64_t bh_static_max_n();
+cudaError_t launch_bh_adjust_static(int device, const double* p, uint64_t n, double* out, uint32_t* bad, cudaStream_t st);
 // text of the value columns (kernels_post.cu): slots [n][16] NUL padded, len [n], unsure [n] (1: format on the host)
 cudaError_t launch_format_values(const double* v, const uint8_t* code, uint64_t n, char* slots, uint8_t* len,
                                  uint8_t* unsure, cudaStream_t st);

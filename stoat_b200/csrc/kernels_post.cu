@@ -8,6 +8,8 @@
 // The sort and the scan are CUB device primitives (library code): this is post-processing, not the hot path.
 #include <cub/cub.cuh>
 
+#include <mutex>
+
 #include "ctx.hpp"
 #include "device_math.cuh"
 
@@ -62,6 +64,82 @@ cudaError_t launch_bh_adjust(const double* p, uint64_t n, double* out, uint64_t*
     if (e != cudaSuccess) return e;
     bh_scatter_kernel<<<blocks, 256, 0, st>>>(b, idx_sorted, n, out);
     return cudaGetLastError();
+}
+
+// ---- Benjamini-Hochberg without any allocation (stoat_gpu_bh_adjust_static) ---------------------------------------
+// The same kernels as launch_bh_adjust with their scratch (sort keys, index pairs, the two scan arrays, CUB's temporary
+// storage, one flag word) in a file-scope device array instead of a context-owned cudaMalloc block, for callers that
+// cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the
+// library holds kBhStaticBytes (64 MiB) until the process exits.  The array is shared by every call and every context of
+// the process on that GPU and keeps the contents of the last call: calls that overlap on the GPU race on it.
+constexpr uint64_t kBhStaticMaxN = uint64_t(STOAT_GPU_BH_STATIC_MAX_N);
+constexpr size_t kBhStaticFixed = size_t(kBhStaticMaxN) * (5 * 8 + 2 * 4);  // p | out | keys | a | b | idx_in | idx_sorted
+constexpr size_t kBhStaticTemp = size_t(16) << 20;                           // CUB temporary storage (checked at set-up)
+constexpr size_t kBhStaticBytes = kBhStaticFixed + kBhStaticTemp;
+static __device__ __align__(256) uint8_t g_bh_static_scratch[kBhStaticBytes];
+
+// 1 in *flag when some p[i] is negative, NaN or infinite (the host check of stoat_gpu_bh_adjust, done where the data is)
+__global__ void __launch_bounds__(256) bh_check_kernel(const double* __restrict__ p, uint64_t n, uint32_t* flag) {
+    const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n && (!(p[i] >= 0.0) || isinf(p[i]))) atomicOr(flag, 1u);
+}
+
+// Device address of the array on `device`, resolved once per device with that device current.  In host code the array's
+// NAME is only a host-side stand-in for the symbol: a kernel must be given the address cudaGetSymbolAddress returns.
+static cudaError_t bh_static_base(int device, uint8_t** base) {
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static uint8_t* addr[kMaxDev] = {};
+    if (device < 0 || device >= kMaxDev) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[device]) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (cur != device) return cudaErrorInvalidDevice;  // the caller makes the device current first
+        void* ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_bh_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (bh_temp_bytes(kBhStaticMaxN) > kBhStaticTemp) return cudaErrorMemoryAllocation;  // CUB wants more than reserved
+        addr[device] = static_cast<uint8_t*>(ptr);
+    }
+    *base = addr[device];
+    return cudaSuccess;
+}
+
+uint64_t bh_static_max_n() { return kBhStaticMaxN; }
+
+// p / out: host or device pointers of the caller (unified addressing tells which), n <= kBhStaticMaxN.  *bad = 1 when the
+// input held a value the reference's string_to_pvalue would not have produced (nothing is written to out then).
+cudaError_t launch_bh_adjust_static(int device, const double* p, uint64_t n, double* out, uint32_t* bad, cudaStream_t st) {
+    *bad = 0;
+    if (n == 0) return cudaSuccess;
+    if (n > kBhStaticMaxN) return cudaErrorInvalidValue;
+    uint8_t* base = nullptr;
+    cudaError_t e = bh_static_base(device, &base);
+    if (e != cudaSuccess) return e;
+    double* d_p = reinterpret_cast<double*>(base);
+    double* d_out = d_p + kBhStaticMaxN;
+    uint64_t* d_keys = reinterpret_cast<uint64_t*>(d_out + kBhStaticMaxN);
+    double* d_a = reinterpret_cast<double*>(d_keys + kBhStaticMaxN);
+    double* d_b = d_a + kBhStaticMaxN;
+    uint32_t* d_i0 = reinterpret_cast<uint32_t*>(d_b + kBhStaticMaxN);
+    uint32_t* d_i1 = d_i0 + kBhStaticMaxN;
+    uint8_t* d_temp = base + kBhStaticFixed;
+    // the flag word sits at the end of the temporary storage (bh_temp_bytes leaves 256 spare bytes) and must start at 0:
+    // the array keeps whatever the last call left in it
+    uint32_t* d_flag = reinterpret_cast<uint32_t*>(d_temp + kBhStaticTemp - 256);
+    if ((e = cudaMemsetAsync(d_flag, 0, 4, st)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyAsync(d_p, p, n * 8, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    bh_check_kernel<<<unsigned((n + 255) / 256), 256, 0, st>>>(d_p, n, d_flag);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if ((e = cudaMemcpyAsync(bad, d_flag, 4, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+    if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
+    if (*bad) return cudaSuccess;
+    e = launch_bh_adjust(d_p, n, d_out, d_keys, d_i0, d_i1, d_a, d_b, d_temp, kBhStaticTemp - 256, st);
+    if (e != cudaSuccess) return e;
+    if ((e = cudaMemcpyAsync(out, d_out, n * 8, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    return cudaStreamSynchronize(st);
 }
 
 
