@@ -70,6 +70,8 @@ def parse_args(argv=None):
     ap.add_argument("--traits", default="all", choices=["all", "headline"],
                     help="all: the C3 binary headline also carries the quantitative and eQTL records")
     ap.add_argument("--genes", type=int, default=20_000, help="eqtl: genes (C4: 200k snarls x 5k samples x 20k genes)")
+    ap.add_argument("--ncov", type=int, default=0,
+                    help="quantitative / eqtl: covariates (SURVEY §8d 'then ncov = 3'; every snarl then takes the general kernel)")
     ap.add_argument("--p-threshold", type=float, default=1e-5, help="eqtl: significance threshold of the scan summary")
     args = ap.parse_args(argv)
     args.custom = bool(args.snarls or args.samples)
@@ -96,7 +98,18 @@ def config_dict(args, n_gpus, trait):
         "snarls_per_gpu": args.snarls, "haplotypes": 2 * args.samples, "sharding": shard,
         "l2": f"inputs ({mat_gb:.1f} GB matrix) exceed the 126 MB L2: every step streams from HBM, no flush needed",
         "thresholds": {"min_individuals": 3, "min_haplotypes": 5, "maf": 0.05},
+        "covariates": (f"{args.ncov} covariates: every snarl on the general kernel (K3G); the integer-MMA kernel the roofline "
+                       "object names does not run" if (getattr(args, "ncov", 0) and trait == "quantitative") else "none"),
     }
+
+
+def bench_covariates(args, n_samples):
+    """Seeded covariate matrix of a --ncov run [n_samples][ncov] (None without)."""
+    if not getattr(args, "ncov", 0):
+        return None
+    import numpy as np
+
+    return np.random.default_rng(11).normal(size=(n_samples, args.ncov))
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -445,7 +458,7 @@ class Env:
             self.dist.destroy_process_group()
 
 
-def parity_spot_check(env, ctx, d, trait, n_check, res, col_sharded):
+def parity_spot_check(env, ctx, d, trait, n_check, res, col_sharded, covar=None):
     """The first `n_check` snarls of the TIMED batch through the CPU oracle: their matrix rows come back from the device
     copy the kernels read (reference layout, byte-aligned rows), the results are the ones the timed configuration produced.
     Sample-sharded runs gather every rank's column slice of those rows first.  -> dict for the JSON line (rank 0)."""
@@ -488,7 +501,7 @@ def parity_spot_check(env, ctx, d, trait, n_check, res, col_sharded):
         got = {k: (v[:P1] if k in ("g0", "g1") else v[:n]) for k, v in res.items()}
         check = helpers.assert_binary_equal
     else:
-        ref = oracle.quantitative_batch(bits, n_cols, y, sub, n_threads=host_threads())
+        ref = oracle.quantitative_batch(bits, n_cols, y, sub, covar=covar, n_threads=host_threads())
         got = {k: (v[:P1] if k == "allele_paths" else v[:n]) for k, v in res.items()}
         check = helpers.assert_quant_equal
     try:
@@ -521,6 +534,8 @@ def trait_record(env, args, ctx, d, trait, stream, host_cache, with_clocks=True)
         ctx.set_quantitative_phenotype_shard(d["y"], *shard_mod.phenotype_summary(d["y_all"]))
     else:
         ctx.set_quantitative_phenotype(d["y"])
+    covar = bench_covariates(args, len(d["y"])) if (trait == "quantitative" and not sample_sharded) else None
+    ctx.set_covariates(covar)
     ctx.stage_paths(paths)
     steps, warm = args.steps, max(args.warmup, 3)
     ar_ms, k1_ms_own, k2_ms_own = [], [], []
@@ -642,7 +657,7 @@ def trait_record(env, args, ctx, d, trait, stream, host_cache, with_clocks=True)
     # ---- parity spot check on the timed data ---------------------------------------------------------
     parity = None
     if not args.no_parity:
-        parity = parity_spot_check(env, ctx, d, trait, args.parity_snarls, res, sample_sharded)
+        parity = parity_spot_check(env, ctx, d, trait, args.parity_snarls, res, sample_sharded, covar=covar)
 
     # ---- end to end: host buffers through the drop-in calls ----------------------------------------
     e2e = None

@@ -34,6 +34,8 @@ def config_dict(args, n_gpus):
         "l2": "the operand images (expression limbs 0.8 GB, dosage 0.9 GB) exceed the 126 MB L2; a gene group (~10 MB) and a "
               "panel of slot tiles are L2 resident by design, every step streams the rest from HBM, no flush needed",
         "p_threshold": args.p_threshold, "thresholds": {"min_individuals": 3, "min_haplotypes": 5, "maf": 0.05},
+        "covariates": (f"{args.ncov} covariates: every snarl on the general kernel (K3G); the tensor-core kernel the roofline "
+                       "object names does not run" if getattr(args, "ncov", 0) else "none"),
     }
 
 
@@ -186,7 +188,7 @@ def int8_peak_tops(torch, dev, n=8192, reps=5):
         return None
 
 
-def parity_spot_check(ctx_summary, d, expr_dev, args, n_check, n_threads, gene0=0):
+def parity_spot_check(ctx_summary, d, expr_dev, args, n_check, n_threads, gene0=0, covar=None):
     """`n_check` snarls SAMPLED at a fixed stride over the timed scan x every gene through the CPU oracle (one OLS per pair,
     as the reference: n_check x G = 10^6 rows at C4), against the device's per-snarl summary: min p (1e-9
     relative), its gene, the count below the threshold."""
@@ -220,7 +222,7 @@ def parity_spot_check(ctx_summary, d, expr_dev, args, n_check, n_threads, gene0=
     sub = oracle.Paths(np.array(spo, np.uint64), np.array(peo, np.uint64), np.array(er, np.uint32))
     ctx_summary = {k: np.asarray(v)[sel] for k, v in ctx_summary.items()}
     t0 = time.time()
-    ref = oracle.eqtl_batch(bits, d["n_cols"], expr, sub, n_threads=n_threads)
+    ref = oracle.eqtl_batch(bits, d["n_cols"], expr, sub, covar=covar, n_threads=n_threads)
     G, thr, rtol = expr.shape[0], args.p_threshold, 1e-9
     pv = ref["p_value"].reshape(n, G)
     ok = ref["code"].reshape(n, G) == 0
@@ -286,6 +288,12 @@ def measure(args, env, ClockSampler, n_threads, with_clocks=True):
     ctx.set_matrix_dev(d["bits_dev"].data_ptr(), d["n_rows"], d["n_cols"])
     ctx.stage_paths(d["paths"])
     ctx.set_expression_dev(expr.data_ptr(), G_local)
+    # SURVEY §8d "no covariates, then ncov = 3": with covariates every snarl takes the general kernel (K3G: the table and
+    # (X'X)^-1 once per snarl, then two sweeps over the samples per gene) - there is no tensor-core form of it, see DESIGN §9
+    covar = None
+    if getattr(args, "ncov", 0):
+        covar = np.random.default_rng(11).normal(size=(n, args.ncov))
+    ctx.set_covariates(covar)
     stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
     merged = {}
 
@@ -340,10 +348,10 @@ def measure(args, env, ClockSampler, n_threads, with_clocks=True):
             parts = [torch.empty_like(expr) for _ in range(world)]
             dist.all_gather(parts, expr)
             if rank == 0:
-                parity = parity_spot_check(merged, d, torch.cat(parts, dim=0), args, 50, n_threads)
+                parity = parity_spot_check(merged, d, torch.cat(parts, dim=0), args, 50, n_threads, covar=covar)
             del parts
         elif rank == 0:
-            parity = parity_spot_check(summary, d, expr, args, 50, n_threads)
+            parity = parity_spot_check(summary, d, expr, args, 50, n_threads, covar=covar)
 
     e2e = None
     if not args.no_e2e and not gene_sharded:

@@ -1,7 +1,6 @@
 mkdir -p gpurun_out
-for cfg in c3 c5; do
-for ov in 1 2 3 4 6 8; do
-  STOAT_GPU_OVERLAP=$ov timeout 300 python bench.py --config $cfg --no-cpu-baseline --no-e2e --traits headline --steps 30 --warmup 3 > gpurun_out/r2q_overlap_${cfg}_$ov.json 2>gpurun_out/r2q_overlap.err
-  python -c "import json;d=json.load(open('gpurun_out/r2q_overlap_${cfg}_$ov.json'));r=d['roofline'];print('$cfg overlap $ov', round(d['ms_per_step'],4), d['parity']['mismatches'], round(r['kernel_ms'],3), r['other_kernels_ms'])"
-done
+timeout 900 python -m pytest tests/test_gpu_quant.py -m gpu -x -q 2>&1 | tail -5
+for q in 1 3 5; do
+timeout 600 python bench.py --trait quantitative --ncov $q --traits headline --steps 10 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/r2q_quant_ncov$q.json 2> gpurun_out/r2q_quant_ncov.err
+python -c "import json;d=json.load(open('gpurun_out/r2q_quant_ncov$q.json'));print('quant ncov$q', d['value'], d['ms_per_step'], d['parity']['mismatches'], d['roofline']['kernel_ms'], list(d['roofline']['other_kernels_ms'].values())[0], d['roofline'].get('snarls_off_fast_path'))"; tail -3 gpurun_out/r2q_quant_ncov.err
 done

@@ -53,6 +53,7 @@ MatrixDev matrix_view(const stoat_gpu_ctx* ctx) {
 
 struct QuantState {
     DevBuf yc, ys, mom, part_i, part_d, slow, yslices, lean_rec, tail_t, tail_x, tail_df;
+    DevBuf cov_mom, cov_prefix;  // covariate runs (quant_covar.cuh): per-snarl moments, prefix sums of the covariate rows
     double sy_all = 0.0, syy_all = 0.0, y_scale = 1.0;
     bool have_partials = false;
     uint64_t lean_key = 0;  // what lean_rec holds: staging generation + participating kernels (launch_quantitative_impl)
@@ -690,6 +691,29 @@ int stoat_gpu_set_covariates(stoat_gpu_ctx* ctx, const double* covar, uint64_t n
     CK(ctx->covar.reserve(n_samples * n_covar * 8));
     CK(cudaMemcpyAsync(ctx->covar.p, covar, n_samples * n_covar * 8, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    if (quant_covar_fast(uint32_t(n_covar))) {
+        // The reference pairs covariate row r with the r-th row of the filtered table (stats_test.cpp:450-452), so 1'C and
+        // C'C of a snarl are sums over the FIRST n_used covariate rows: prefix[r] = those sums over rows [0, r), running
+        // down the rows as the reference's own accumulation does.  Layout per r: sum c_j (Q), then sum c_j c_k, j <= k.
+        const uint64_t Q = n_covar, per = Q + Q * (Q + 1) / 2;
+        std::vector<double> pre((n_samples + 1) * per + n_samples * Q, 0.0);  // + the covariates by column, for K3C
+        for (uint64_t r = 0; r < n_samples; ++r) {
+            const double* row = covar + r * Q;
+            const double* in = pre.data() + r * per;
+            double* o = pre.data() + (r + 1) * per;
+            uint64_t e = Q;
+            for (uint64_t j = 0; j < Q; ++j) {
+                o[j] = in[j] + row[j];
+                for (uint64_t k = j; k < Q; ++k, ++e) o[e] = in[e] + row[j] * row[k];
+            }
+        }
+        double* by_col = pre.data() + (n_samples + 1) * per;
+        for (uint64_t r = 0; r < n_samples; ++r)
+            for (uint64_t j = 0; j < Q; ++j) by_col[j * n_samples + r] = covar[r * Q + j];
+        CtxExtra* x = extra_of(ctx);
+        CK(x->q.cov_prefix.reserve(pre.size() * 8));
+        CK(cudaMemcpy(x->q.cov_prefix.p, pre.data(), pre.size() * 8, cudaMemcpyHostToDevice));
+    }
     ctx->n_covar = n_covar;
     ctx->n_samples_covar = n_samples;
     return STOAT_GPU_OK;
@@ -954,6 +978,8 @@ static int quant_reserve(stoat_gpu_ctx* ctx) {
     CK(x->q.tail_t.reserve(std::max<uint64_t>(b.n_snarls * 8, 16)));
     CK(x->q.tail_df.reserve(std::max<uint64_t>(b.n_snarls * 4, 16)));
     CK(x->q.tail_x.reserve(std::max<uint64_t>(b.n_snarls * 16, 16)));  // [2][S]: argument, starting state
+    if (ctx->n_covar && quant_covar_fast(uint32_t(ctx->n_covar)))
+        CK(x->q.cov_mom.reserve(std::max<size_t>(quant_covar_moments_bytes(b.n_snarls), 16)));
     return STOAT_GPU_OK;
 }
 
@@ -1003,7 +1029,10 @@ static int quant_run(stoat_gpu_ctx* ctx, const stoat_gpu_thresholds* thr, int ph
                                 x->q.yslices.as<uint8_t>(),
                                 x->q.yc.as<double>(), x->q.y_scale, ctx->num_sms, ctx->k1_variant, ctx->stream,
                                 &ctx->timing.launches, ev[1], phase, x->q.tail_t.as<double>(),
-                                x->q.tail_x.as<double>(), x->q.tail_df.as<uint32_t>(), x->stage_gen, &x->q.lean_key));
+                                x->q.tail_x.as<double>(), x->q.tail_df.as<uint32_t>(), x->stage_gen, &x->q.lean_key,
+                                (ctx->n_covar && quant_covar_fast(uint32_t(ctx->n_covar))) ? x->q.cov_mom.p : nullptr,
+                                (ctx->n_covar && quant_covar_fast(uint32_t(ctx->n_covar))) ? x->q.cov_prefix.as<double>() : nullptr,
+                                uint32_t(ctx->n_samples_covar)));
     if (phase == 2) CK(cudaEventRecord(ev[1], ctx->stream));
     CK(cudaEventRecord(ev[3], ctx->stream));
     ++x->run_seq;

@@ -133,7 +133,14 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                                      int phase,  // 0: whole step; 1: moments only; 2: solve only (sample-sharded)
                                      double* tail_t, double* tail_x, uint32_t* tail_df,  // [n_snarls] K4 -> K4b hand-over
                                      uint64_t stage_gen = 0,         // identifies the staged paths (rec / blob)
-                                     uint64_t* lean_key = nullptr);  // in/out: what lean_rec holds (nullptr: rebuild every step)
+                                     uint64_t* lean_key = nullptr,   // in/out: what lean_rec holds (nullptr: rebuild every step)
+                                     void* cov_mom = nullptr,        // covariate runs: [n_snarls] moments (quant_covar_moments_bytes)
+                                     const double* cov_prefix = nullptr,  // ... the prefix sums of the covariate rows
+                                                                          // [cov_rows + 1][Q + Q (Q + 1) / 2], then the
+                                                                          // covariates by column [Q][cov_rows]
+                                     uint32_t cov_rows = 0);
+size_t quant_covar_moments_bytes(uint64_t n_snarls);
+bool quant_covar_fast(uint32_t n_covar);  // the covariate run takes K3C / K4C (quant_covar.cuh) instead of K3G for every snarl
 bool quant_fast_path(uint64_t pitch, uint64_t n_hap, uint32_t max_stage_rows, int variant, uint32_t n_covar);  // K4 initialises the outputs
 size_t quant_yslices_bytes(uint64_t pitch);  // K3M's phenotype slice table
 // slices of the haplotype range the two-path kernels (K3M / K3R) use: sizes the partial-sum buffers (0: neither runs)

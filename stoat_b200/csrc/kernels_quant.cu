@@ -900,6 +900,8 @@ static cudaError_t launch_student_tail(const double* tail_t, const double* tail_
 
 // scratch owned by the caller: mom [n_snarls], ys permuted, sums; K3R: part_i [slices][7][S], part_d [slices][3][S],
 // slow_list [S]; counters[3] = length of the slow list
+#include "quant_covar.cuh"
+
 cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, const double* ys_perm,
                                      double sy_all, double syy_all, const double* covar, uint32_t n_covar,
                                      const BatchDev& b, uint32_t max_stage_rows, const stoat_gpu_thresholds& thr,
@@ -907,7 +909,8 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
                                      uint32_t* slow_list, uint4* lean_rec, const uint8_t* yslices, const double* yc,
                                      double y_scale, int num_sms, int variant, cudaStream_t st, uint32_t* launches,
                                      cudaEvent_t ev_table_done, int phase, double* tail_t, double* tail_x,
-                                     uint32_t* tail_df, uint64_t stage_gen, uint64_t* lean_key) {
+                                     uint32_t* tail_df, uint64_t stage_gen, uint64_t* lean_key, void* cov_mom,
+                                     const double* cov_prefix, uint32_t cov_rows) {
     // phase 0: the whole step.  Sample-sharded runs split it around the all-reduce of the partial sums:
     // phase 1 = lean records + K3M only, phase 2 = K4 on the summed partials with everything else deferred to the host.
     if (b.n_snarls == 0) return cudaSuccess;
@@ -1190,6 +1193,38 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         return cudaSuccess;
     }
     if (phase != 0) return cudaErrorNotSupported;  // covariates / K3M unavailable: no sample-sharded moments path
+    if (variant == 0 && n_covar && cov_mom && cov_prefix && cov_rows >= n_samples && yc && tail_t && quant_covar_fast(n_covar)) {
+        // covariates: K3C (one sweep per snarl) + K4C (solve) + K4b (tails), the general kernel on what they hand back.
+        // The list is this path's own: it starts empty (prep's entries are shapes K3C turns away itself).
+        CovParams c{};
+        c.rows = m.rows;
+        c.pitch = pitch;
+        c.n_hap = uint32_t(m.n_cols);
+        c.n_samples = n_samples;
+        c.n_covar = n_covar;
+        c.yc = yc;
+        c.cov_rows = cov_rows;
+        c.covar_t = cov_prefix + size_t(cov_rows + 1) * (n_covar + n_covar * (n_covar + 1) / 2);  // behind the prefix table
+        c.prefix = cov_prefix;
+        c.b = b;
+        c.thr = thr;
+        c.out = out;
+        c.mom = static_cast<CovMoments*>(cov_mom);
+        c.g_list = b.big_list;
+        c.g_count = b.counters;
+        if ((e = cudaMemsetAsync(b.counters, 0, 4, st)) != cudaSuccess) return e;
+        if ((e = launch_covar_moments(c, num_sms, st)) != cudaSuccess) return e;
+        if (ev_table_done && (e = cudaEventRecord(ev_table_done, st)) != cudaSuccess) return e;
+        const SolveArgs sa{out, b.big_list, b.counters, 0u, tail_t, tail_x, tail_df, b.n_snarls};
+        covar_solve_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(c, sa);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if ((e = launch_student_tail(tail_t, tail_x, tail_df, b, out.p, num_sms, st)) != cudaSuccess) return e;
+        g.list = b.big_list;
+        g.n_list_dev = b.counters;
+        if ((e = launch_quant_general(g, b.n_snarls, num_sms, st)) != cudaSuccess) return e;
+        if (launches) *launches += 5;
+        return cudaSuccess;
+    }
     g.list = nullptr;
     g.n_list_dev = nullptr;
     g.n_list_host = b.n_snarls;

@@ -71,6 +71,55 @@ def test_covariates_and_position_quirk(gpu_ctx, oracle):
     H.assert_quant_equal(got2, ref2)
 
 
+@pytest.mark.parametrize("ncov", [1, 3, 5])
+@pytest.mark.parametrize("kind,n_samples,max_paths", [("partition", 700, 2), ("partition", 1300, 4), ("partition", 5000, 3),
+                                                      ("random", 333, 4), ("synth", 1000, 0)])
+def test_covariates_sweep_kernels(gpu_ctx, oracle, monkeypatch, ncov, kind, n_samples, max_paths):
+    """K3C / K4C (csrc/quant_covar.cuh): with covariates a snarl of <= 4 paths takes one sweep over its samples (covariate
+    rows by FILTERED position, stats_test.cpp:450-452; 1'C and C'C from prefix tables) instead of the general kernel.
+    Parity with the oracle, and with the general kernel on the same input (STOAT_GPU_COVAR_FAST=0); shapes the sweep does
+    not cover (identical columns, empty paths, > 2 checked edges, thirds next to a threshold) come back through the list."""
+    from stoat_b200 import SnarlPaths, synth
+
+    rng = np.random.default_rng(100 + ncov + n_samples)
+    if kind == "partition":
+        dense, snarls = H.partition_problem(rng, 150 if n_samples < 5000 else 40, n_samples, max_paths=max_paths,
+                                            p_missing_hap=0.05)
+    elif kind == "random":
+        dense, snarls = H.random_snarl_problem(rng, 250, n_samples, 60, max_paths=max_paths, max_edges=3)
+    else:
+        d = synth.numpy_dataset(600, n_samples, seed=9, frac_three=0.2, frac_node0=0.1, frac_missing_edge=0.02)
+    covar = rng.normal(size=(n_samples, ncov)) * rng.uniform(0.5, 20.0, size=ncov) + rng.normal(size=ncov)
+    y = rng.normal(size=n_samples) * 2.0 + 7.0 + 0.5 * covar[:, 0]
+    if kind == "synth":
+        bits, n_rows, n_cols, P = d["bits"], d["n_rows"], d["n_cols"], d["paths"]
+        spo, peo, er = P.snarl_path_off, P.path_edge_off, P.edge_row
+    else:
+        y = y + dense[snarls[0][0][0]].reshape(n_samples, 2).sum(1)
+        bits, (n_rows, n_cols) = oracle.pack_matrix(dense), dense.shape
+        spo, peo, er = H.csr_from_lists(snarls)
+    thr = dict(min_ind=2, min_hap=2, maf=0.01)
+    ref = oracle.quantitative_batch(bits, n_cols, y, oracle.Paths(spo, peo, er), covar=covar, **thr)
+    gpu_ctx.set_matrix(bits, n_rows, n_cols)
+    gpu_ctx.set_quantitative_phenotype(y)
+    gpu_ctx.set_covariates(covar)
+    try:
+        got = gpu_ctx.quantitative_batch(SnarlPaths(spo, peo, er), **thr)
+        n_general = gpu_ctx.timing()["n_general"]
+        monkeypatch.setenv("STOAT_GPU_COVAR_FAST", "0")
+        gpu_ctx.set_covariates(covar)
+        slow = gpu_ctx.quantitative_batch(SnarlPaths(spo, peo, er), **thr)
+    finally:
+        gpu_ctx.set_covariates(None)
+    H.assert_quant_equal(got, ref)
+    H.assert_quant_equal(slow, ref)
+    H.assert_quant_equal(got, slow)
+    kept = int(((ref["filtered"] == 0) & (ref["code"] == 0)).sum())
+    assert kept > 20
+    if kind == "partition" and 1 + (max_paths - 1) + ncov <= 8:
+        assert n_general <= max(4, len(spo) // 10), n_general  # the sweep kernels did the work
+
+
 def test_merges_undefined_and_rank_deficient(gpu_ctx, oracle):
     n = 40
     H2 = 2 * n
