@@ -110,7 +110,7 @@ def main():
     os.makedirs(PROF, exist_ok=True)
     for t in ("binary", "quant", "eqtl"):
         launches(tag, t)
-    for name in ("k1", "fisher", "stats", "k3", "k3m", "k3m3", "k3m2x", "k4", "k4b", "general", "eqtl", "k3c"):
+    for name in ("k1", "fisher", "stats", "k3", "k3m", "k3m3", "k3m2x", "k4", "k4b", "general", "eqtl", "k3c", "e3c"):
         vals = full(tag, name)
         if name == "k3m" and vals:
             raw = ncu_csv(os.path.join(OUT, "prof_k3m.ncu-rep"), "raw")

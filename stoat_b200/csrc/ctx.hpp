@@ -173,7 +173,11 @@ cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, ui
                                 const uint64_t* snarl_gene_off, const uint32_t* gene_idx, const double* covar,
                                 uint32_t n_covar, const BatchDev& b, uint64_t s_begin, uint64_t n_snarls,
                                 uint64_t item_base, const stoat_gpu_thresholds& thr, QuantOut out, int num_sms,
-                                cudaStream_t st, const uint32_t* list = nullptr);
+                                cudaStream_t st, const uint32_t* list = nullptr,
+                                // covariate runs (quant_covar.cuh): prefix tables + column-major covariates, their row
+                                // count, a scratch byte per snarl of the call; nullptr: every snarl on the general kernel
+                                const double* cov_prefix = nullptr, uint32_t cov_rows = 0, uint8_t* cov_flag = nullptr,
+                                uint64_t max_items_per_snarl = 0);
 cudaError_t launch_eqtl_summary(const double* p, const uint8_t* code, const uint8_t* filtered, uint64_t s_begin,
                                 uint64_t n_snarls, uint32_t n_genes, double p_threshold, double* min_p,
                                 uint32_t* argmin, uint32_t* n_below, cudaStream_t st, const uint32_t* list = nullptr);

@@ -1262,8 +1262,38 @@ cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, ui
                                 const uint64_t* snarl_gene_off, const uint32_t* gene_idx, const double* covar,
                                 uint32_t n_covar, const BatchDev& b, uint64_t s_begin, uint64_t n_snarls,
                                 uint64_t item_base, const stoat_gpu_thresholds& thr, QuantOut out, int num_sms,
-                                cudaStream_t st, const uint32_t* list) {
+                                cudaStream_t st, const uint32_t* list, const double* cov_prefix, uint32_t cov_rows,
+                                uint8_t* cov_flag, uint64_t max_items_per_snarl) {
     if (n_snarls == 0) return cudaSuccess;
+    // covariates: the sweep kernels of quant_covar.cuh first; they flag the entries the general kernel must take
+    const bool cov_fast = n_covar && covar && cov_prefix && cov_flag && cov_rows >= uint32_t(m.n_cols / 2) &&
+                          quant_covar_fast(n_covar);
+    if (cov_fast) {
+        CovEqtlParams q{};
+        q.c.rows = m.rows;
+        q.c.pitch = uint32_t(m.pitch);
+        q.c.n_hap = uint32_t(m.n_cols);
+        q.c.n_samples = uint32_t(m.n_cols / 2);
+        q.c.n_covar = n_covar;
+        q.c.cov_rows = cov_rows;
+        q.c.covar_t = cov_prefix + size_t(cov_rows + 1) * (n_covar + n_covar * (n_covar + 1) / 2);
+        q.c.b = b;
+        q.c.thr = thr;
+        q.c.out = out;
+        q.prefix = cov_prefix;
+        q.expression = expression;
+        q.n_genes = n_genes;
+        q.snarl_gene_off = snarl_gene_off;
+        q.gene_idx = gene_idx;
+        q.list = list;
+        q.s_begin = s_begin;
+        q.n_entries = n_snarls;
+        q.item_base = item_base;
+        q.flag = cov_flag;
+        cudaError_t e = cudaMemsetAsync(cov_flag, 0, n_snarls, st);
+        if (e != cudaSuccess) return e;
+        if ((e = launch_eqtl_covar(q, max_items_per_snarl ? max_items_per_snarl : n_genes, num_sms, st)) != cudaSuccess) return e;
+    }
     GParams g{};
     g.rows = m.rows;
     g.pitch = uint32_t(m.pitch);
@@ -1285,6 +1315,7 @@ cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, ui
     g.item_base = item_base;
     g.items_by_slot = list != nullptr;
     g.gene_split = 1;
+    g.only_flagged = cov_fast ? cov_flag : nullptr;
     if (list) {  // few snarls, many genes each: give every snarl enough warps to fill the machine
         const uint64_t target = uint64_t(num_sms) * 3 * kGWarps * 2;
         const uint64_t want = (target + n_snarls - 1) / n_snarls, most = (uint64_t(n_genes) + 7) / 8;

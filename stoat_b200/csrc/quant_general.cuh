@@ -42,6 +42,7 @@ struct GParams {
     // logistic regression (BinaryCovarSnarlAnalyzer, src/snarl_analyzer.cpp:392-428): the same table against the binary
     // phenotype.  is_case != nullptr selects it; the outputs are p / beta / se (r2 is left NaN).
     const uint8_t* is_case;  // [n_samples] 0 / 1
+    const uint8_t* only_flagged;  // != nullptr: only the list entries e with only_flagged[e] != 0 (the rest was done elsewhere)
 };
 
 constexpr int kGWarps = 4;
@@ -979,6 +980,7 @@ __global__ void __launch_bounds__(kGWarps * 32) quant_general_kernel(const GPara
     const GTeam tm{0u, 1u, nullptr};
     for (uint64_t i = gw; i < n; i += n_warps) {
         const uint64_t entry = i / split;
+        if (g.only_flagged && !g.only_flagged[entry]) continue;
         const uint64_t s = g.list ? g.list[entry] : g.s_begin + entry;
         quant_general(g, scratch[warp], s, entry, uint32_t(i - entry * split), lane, tm);
     }
@@ -996,6 +998,7 @@ __global__ void __launch_bounds__(kGTeamWarps * 32) quant_general_team_kernel(co
     if (!g_team_mode(g, n_list, team_limit)) return;
     const GTeam tm{warp, uint32_t(kGTeamWarps), buf};
     for (uint64_t entry = blockIdx.x; entry < n_list; entry += gridDim.x) {
+        if (g.only_flagged && !g.only_flagged[entry]) continue;  // (CTA-uniform)
         const uint64_t s = g.list ? g.list[entry] : g.s_begin + entry;
         quant_general(g, scratch[warp], s, entry, 0u, lane, tm);
         __syncthreads();

@@ -219,3 +219,45 @@ def test_dense_with_covariates_takes_general_path(gpu_ctx, oracle):
     gpu_ctx.set_covariates(None)
     ref = oracle.eqtl_batch(d["bits"], d["n_cols"], expr, P, covar=covar)
     _check_summary(got, ref, P.n_snarls, 6, 1e-2)
+
+
+@pytest.mark.parametrize("ncov", [1, 3, 5])
+@pytest.mark.parametrize("kind,n_samples,n_genes,max_paths", [("partition", 333, 13, 2), ("partition", 1200, 70, 4),
+                                                              ("random", 150, 9, 4), ("windows", 700, 30, 3)])
+def test_covariates_sweep_kernels(gpu_ctx, oracle, monkeypatch, ncov, kind, n_samples, n_genes, max_paths):
+    """E3C (csrc/quant_covar.cuh): with covariates a snarl of <= 4 paths takes one sweep for its design and one per batch of
+    genes instead of the general kernel's three sweeps per gene.  Every pair against the oracle and against the general
+    kernel on the same input (STOAT_GPU_COVAR_FAST=0); gene windows (CSR) and dense; more genes than one batch; shapes
+    the sweep does not take (random problems: empty paths, identical columns, > 2 edges) come back through the flags."""
+    rng = np.random.default_rng(7 * ncov + n_samples)
+    if kind == "random":
+        dense, snarls = H.random_snarl_problem(rng, 120, n_samples, 40, max_paths=max_paths, max_edges=3)
+    else:
+        dense, snarls = H.partition_problem(rng, 60, n_samples, max_paths=max_paths, p_missing_hap=0.05)
+    base = rng.uniform(0, 8, size=(n_genes, 1))
+    expr = base * (1.0 + rng.uniform(-1, 1, size=(n_genes, n_samples)))
+    for g in range(0, n_genes, 4):
+        s = int(rng.integers(0, len(snarls)))
+        if snarls[s][0]:
+            expr[g] += 1.5 * dense[snarls[s][0][0]].reshape(n_samples, 2).sum(1)
+    covar = rng.normal(size=(n_samples, ncov)) * rng.uniform(0.5, 20.0, size=ncov) + rng.normal(size=ncov)
+    expr[1] += 0.3 * covar[:, 0]
+    off = idx = None
+    if kind == "windows":
+        counts = rng.integers(0, 12, size=len(snarls))
+        off = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint64)
+        idx = np.concatenate([rng.choice(n_genes, size=c, replace=False) for c in counts] + [np.zeros(0, int)]).astype(np.uint32)
+    thr = dict(min_ind=2, min_hap=2, maf=0.01)
+    got, ref = _run(gpu_ctx, oracle, dense, snarls, expr, off, idx, covar=covar, **thr)
+    monkeypatch.setenv("STOAT_GPU_COVAR_FAST", "0")
+    slow, _ = _run(gpu_ctx, oracle, dense, snarls, expr, off, idx, covar=covar, **thr)
+    # a coefficient that is small against its standard error comes out of a cancellation (inv(X'X) X'y over terms of the
+    # size of sum y): it is compared with 1e-9 |beta| + 1e-10 se — its uncertainty is se, its rounding noise ~1e-12 se
+    # (scripts/fuzz_parity.py arbitrates such rows with an 80-bit regression: the CUDA value is the nearer one)
+    for a_, b_ in ((slow, ref), (got, ref), (got, slow)):
+        m = b_["code"] == 0
+        fix = m & (np.abs(a_["beta"] - b_["beta"]) <= 1e-9 * np.abs(b_["beta"]) + 1e-10 * b_["se"])
+        a2 = dict(a_)
+        a2["beta"] = np.where(fix, b_["beta"], a_["beta"])
+        _assert_pairs_equal(a2, b_)
+    assert (ref["code"] == 0).sum() > 50
