@@ -19,12 +19,15 @@
 // than 2 checked edges on a path, an empty path (missing edge, no carrier), identical columns (the reference merges them,
 // :620-674), a filter comparison within 1e-9 of its threshold with thirds in the table (K3G replays the reference's
 // order of additions), a rank-deficient X'X (pseudo-inverse branch, not shift invariant), a near-perfect fit
-// (rss <= 1e-6 tss: the expansion has lost its digits), more than kCovFeat features.
+// (rss <= 1e-4 tss: the expansion has lost its digits), more than kCovFeat features.
 #pragma once
 
 constexpr int kCovMaxD = 3;   // regression dosage columns (paths - 1)
 constexpr int kCovMaxQ = 5;   // covariates
 constexpr int kCovFeat = 8;   // features 1 + D + Q the solver takes
+// rss from the moment expansion is trusted above this fraction of tss; below it the general kernel takes explicit
+// residuals.  (1e-6, K4a's guard, let one pair in 29,040 randomised runs through at 1.3e-9: 5 samples, 1 - R^2 = 2e-6.)
+constexpr double kCovRssGuard = 1e-4;
 constexpr uint32_t kCovRowAll = 0xFFFFFFFEu;  // a path without checked edges: every haplotype
 
 // per snarl, K3C -> K4C.  v[]: s1d[3] | sdd[6] (lower triangle) | sdy[3] | sy | syy | scy[Q] | sdc[3][Q]
@@ -340,7 +343,7 @@ __global__ void __launch_bounds__(128) covar_solve_kernel(const CovParams c, con
     const double syy = m.v[kCovOffSyy], sy = m.v[kCovOffSy];
     const double rss = syy - 2.0 * bxy + bxxb;
     const double tss = syy - sy * sy / double(n_used);
-    if (!(rss > 1e-6 * tss)) {  // near-perfect fit: explicit residuals on the general path
+    if (!(rss > kCovRssGuard * tss)) {  // near-perfect fit: explicit residuals on the general path
         solve_hand_on(a, s);
         return;
     }
@@ -384,7 +387,7 @@ inline cudaError_t launch_covar_moments(const CovParams& c, int num_sms, cudaStr
 // then one sweep per batch of GB genes for X'y_g and y_g'y_g (the expression rows are read contiguously, lane <-> sample)
 // and lane g finishes gene g.  The phenotype is shifted by the mean of the gene's first 32 samples before it is squared
 // (OLS with an intercept is shift invariant; the raw moments would cancel).  Shapes K3C turns away, a rank-deficient
-// design and any pair whose rss is within 1e-6 of tss flag the whole snarl for the general kernel (flag[entry] = 1).
+// design and any pair whose rss is below 1e-4 tss flag the whole snarl for the general kernel (flag[entry] = 1).
 // =================================================================================================
 struct CovEqtlParams {
     CovParams c;                 // rows, covariates, thresholds, out (per-pair arrays), b; yc / prefix / mom unused
@@ -682,7 +685,7 @@ __device__ __forceinline__ void cov_eqtl_snarl(const CovEqtlParams& q, const dou
             }
             const double rss = my_syy - 2.0 * bxy + bxxb;
             const double tss = my_syy - xty[0] * xty[0] / double(n_used);
-            if (!(rss > 1e-6 * tss)) {
+            if (!(rss > kCovRssGuard * tss)) {
                 bad = true;  // near-perfect fit: explicit residuals, on the general path
             } else {
                 const OlsOut o = ols_statistics(beta[1], wsm[P * P + P + 1], rss, tss, n_used, P);
