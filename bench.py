@@ -808,6 +808,17 @@ def main():
         q = trait_record(env, args, ctx, d, "quantitative", stream, host_cache, with_clocks=False)
         if rank == 0:
             traits["quantitative"] = q
+        if nested_eqtl and not args.ncov:
+            # SURVEY §8d "then ncov = 3": the same batch with 3 covariates (sweep kernels K3C / K4C); device-resident
+            # timing and parity only, the end-to-end and CPU legs are those of the record above
+            import copy
+
+            cargs = copy.copy(args)
+            cargs.ncov, cargs.no_e2e, cargs.no_cpu_baseline = 3, True, True
+            qc = trait_record(env, cargs, ctx, d, "quantitative", stream, host_cache, with_clocks=False)
+            if rank == 0:
+                qc["roofline"] = None  # (the record's roofline object describes K3M, which does not run with covariates)
+                traits["quantitative_3_covariates"] = qc
     host_cache.clear()
     ctx.close()
     del d
@@ -822,6 +833,15 @@ def main():
         e = bench_eqtl.measure(eargs, env, ClockSampler, host_threads(), with_clocks=False)
         if rank == 0:
             traits["eqtl"] = e
+        if not args.ncov:
+            # ... and the eQTL scan with 3 covariates (E3C), on 2,000 snarls x 2,000 genes of the same generators
+            cargs = parse_args(["--trait", "eqtl", "--gpus", str(args.gpus), "--steps", "3", "--warmup", "3", "--ncov", "3",
+                                "--snarls", "2000", "--genes", "2000", "--no-cpu-baseline", "--no-e2e"] +
+                               (["--no-parity"] if args.no_parity else []))
+            ec = bench_eqtl.measure(cargs, env, ClockSampler, host_threads(), with_clocks=False)
+            if rank == 0:
+                ec["roofline"] = None  # (describes the tensor-core kernel, which does not run with covariates)
+                traits["eqtl_3_covariates"] = ec
     if rank == 0:
         if traits:
             line["traits"] = traits
