@@ -386,7 +386,10 @@ inline cudaError_t launch_covar_moments(const CovParams& c, int num_sms, cudaStr
 // 0, the filters and (X'X)^-1 — once per snarl, as the reference should have done (it re-inverts per gene, :510-520) —
 // then one sweep per batch of GB genes for X'y_g and y_g'y_g (the expression rows are read contiguously, lane <-> sample)
 // and lane g finishes gene g.  The phenotype is shifted by the mean of the gene's first 32 samples before it is squared
-// (OLS with an intercept is shift invariant; the raw moments would cancel).  Shapes K3C turns away, a rank-deficient
+// (OLS with an intercept is shift invariant; the raw moments would cancel).  Tried and dropped: the expression values staged
+// once per CTA in shared memory for its 8 snarls (cp.async double buffering with CTA barriers: 57 ms; a 4-stage TMA ring with
+// full / empty mbarriers and no CTA barrier: 50 ms, against 44 ms for this form on 2,000 x 2,000 x 5,000) — the expression
+// loads are not what a pair waits for; the per-block chain shuffle -> ballot -> rank -> covariate loads is.  Shapes K3C turns away, a rank-deficient
 // design and any pair whose rss is below 1e-4 tss flag the whole snarl for the general kernel (flag[entry] = 1).
 // =================================================================================================
 struct CovEqtlParams {
@@ -455,24 +458,14 @@ __device__ __forceinline__ uint32_t cov_for_blocks(const CovParams& c, const uin
     return rank_run;  // n_used
 }
 
-template <int NP, int Q, int GB>
-__device__ __forceinline__ void cov_eqtl_snarl(const CovEqtlParams& q, const double* lut, double* wsm, uint64_t entry,
-                                               uint64_t s, uint32_t part, uint64_t p0, const uint32_t (&r0)[kCovMaxD + 1],
-                                               const uint32_t (&r1)[kCovMaxD + 1], uint32_t lane) {
+// The design of one snarl (one sweep, then lane 0: filters, X'X, inverse into wsm = [X'X (P x P) | inverse (P x P)]).
+// -> 0: regress, 1: filtered, 2: the general kernel takes the snarl; allele_paths are written here.
+template <int NP, int Q>
+__device__ __forceinline__ int cov_eqtl_design(const CovEqtlParams& q, const double* lut, double* wsm, uint64_t s, uint64_t p0,
+                                               const uint32_t (&r0)[kCovMaxD + 1], const uint32_t (&r1)[kCovMaxD + 1],
+                                               uint32_t lane, uint32_t& n_used_out) {
     constexpr int D = NP - 1, kTri = D * (D + 1) / 2, P = 1 + D + Q;
     const CovParams& c = q.c;
-    const double nan = __longlong_as_double(0x7ff8000000000000LL);
-    // ---- the items (genes) of this warp ------------------------------------------------------------------------------
-    const uint64_t dense_row = q.list ? entry : s;  // as quant_general.cuh numbers the items of a dense scan
-    uint64_t k0 = q.snarl_gene_off ? q.snarl_gene_off[s] : dense_row * uint64_t(q.n_genes);
-    uint64_t k1 = q.snarl_gene_off ? q.snarl_gene_off[s + 1] : (dense_row + 1) * uint64_t(q.n_genes);
-    const uint64_t gene_base = dense_row * uint64_t(q.n_genes);
-    {
-        const uint64_t share = (k1 - k0 + q.chunks - 1) / q.chunks;
-        const uint64_t lo = k0 + uint64_t(part) * share;
-        k1 = lo + share < k1 ? lo + share : k1;
-        k0 = lo < k1 ? lo : k1;
-    }
     // ---- the design: one sweep --------------------------------------------------------------------------------------
     double s1d[D], sdd[kTri], sdc[D][Q];
 #pragma unroll
@@ -517,10 +510,8 @@ __device__ __forceinline__ void cov_eqtl_snarl(const CovEqtlParams& q, const dou
         identical = (same & ((1u << (NP * (NP - 1) / 2)) - 1u)) != 0u;
     }
     rs_seen = __reduce_or_sync(0xffffffffu, rs_seen);
-    if (empty_path || identical) {
-        if (lane == 0) q.flag[entry] = 1;
-        return;
-    }
+    n_used_out = n_used;
+    if (empty_path || identical) return 2;
 #pragma unroll
     for (int a = 0; a < D; ++a) {
         s1d[a] = warp_sum(s1d[a]);
@@ -582,6 +573,63 @@ __device__ __forceinline__ void cov_eqtl_snarl(const CovEqtlParams& q, const dou
     }
     status = __shfl_sync(0xffffffffu, status, 0);
     __syncwarp();
+    return status;
+}
+
+// One gene of a snarl from its X'y (lane-private): beta, rss by the moment expansion, statistics, stored at item oi.
+// -> false: the expansion has lost its digits (the general kernel takes explicit residuals).
+template <int P>
+__device__ __forceinline__ bool cov_eqtl_finish(const CovParams& c, const double* wsm, const double (&xty)[P], double my_syy,
+                                                uint32_t n_used, uint64_t oi) {
+    double beta[P];
+#pragma unroll
+    for (int i = 0; i < P; ++i) {
+        double b = 0.0;
+#pragma unroll
+        for (int j = 0; j < P; ++j) b += wsm[P * P + i * P + j] * xty[j];
+        beta[i] = b;
+    }
+    double bxy = 0.0, bxxb = 0.0;
+#pragma unroll
+    for (int i = 0; i < P; ++i) {
+        bxy += beta[i] * xty[i];
+        double r = 0.0;
+#pragma unroll
+        for (int j = 0; j < P; ++j) r += wsm[i * P + j] * beta[j];
+        bxxb += beta[i] * r;
+    }
+    const double rss = my_syy - 2.0 * bxy + bxxb;
+    const double tss = my_syy - xty[0] * xty[0] / double(n_used);
+    if (!(rss > kCovRssGuard * tss)) return false;  // near-perfect fit: explicit residuals, on the general path
+    const OlsOut o = ols_statistics(beta[1], wsm[P * P + P + 1], rss, tss, n_used, P);
+    c.out.p[oi] = o.p;
+    c.out.r2[oi] = o.r2;
+    c.out.beta[oi] = o.beta;
+    c.out.se[oi] = o.se;
+    c.out.code[oi] = kPValue;
+    return true;
+}
+
+template <int NP, int Q, int GB>
+__device__ __forceinline__ void cov_eqtl_snarl(const CovEqtlParams& q, const double* lut, double* wsm, uint64_t entry,
+                                               uint64_t s, uint32_t part, uint64_t p0, const uint32_t (&r0)[kCovMaxD + 1],
+                                               const uint32_t (&r1)[kCovMaxD + 1], uint32_t lane) {
+    constexpr int D = NP - 1, kTri = D * (D + 1) / 2, P = 1 + D + Q;
+    const CovParams& c = q.c;
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    // ---- the items (genes) of this warp ------------------------------------------------------------------------------
+    const uint64_t dense_row = q.list ? entry : s;  // as quant_general.cuh numbers the items of a dense scan
+    uint64_t k0 = q.snarl_gene_off ? q.snarl_gene_off[s] : dense_row * uint64_t(q.n_genes);
+    uint64_t k1 = q.snarl_gene_off ? q.snarl_gene_off[s + 1] : (dense_row + 1) * uint64_t(q.n_genes);
+    const uint64_t gene_base = dense_row * uint64_t(q.n_genes);
+    {
+        const uint64_t share = (k1 - k0 + q.chunks - 1) / q.chunks;
+        const uint64_t lo = k0 + uint64_t(part) * share;
+        k1 = lo + share < k1 ? lo + share : k1;
+        k0 = lo < k1 ? lo : k1;
+    }
+    uint32_t n_used = 0;
+    int status = cov_eqtl_design<NP, Q>(q, lut, wsm, s, p0, r0, r1, lane, n_used);
     if (status == 2) {
         if (lane == 0) q.flag[entry] = 1;
         return;
@@ -665,38 +713,7 @@ __device__ __forceinline__ void cov_eqtl_snarl(const CovEqtlParams& q, const dou
             }
         }
         bool bad = false;
-        if (lane < uint32_t(GB) && kb + lane < k1) {
-            double beta[P];
-#pragma unroll
-            for (int i = 0; i < P; ++i) {
-                double b = 0.0;
-#pragma unroll
-                for (int j = 0; j < P; ++j) b += wsm[P * P + i * P + j] * xty[j];
-                beta[i] = b;
-            }
-            double bxy = 0.0, bxxb = 0.0;
-#pragma unroll
-            for (int i = 0; i < P; ++i) {
-                bxy += beta[i] * xty[i];
-                double r = 0.0;
-#pragma unroll
-                for (int j = 0; j < P; ++j) r += wsm[i * P + j] * beta[j];
-                bxxb += beta[i] * r;
-            }
-            const double rss = my_syy - 2.0 * bxy + bxxb;
-            const double tss = my_syy - xty[0] * xty[0] / double(n_used);
-            if (!(rss > kCovRssGuard * tss)) {
-                bad = true;  // near-perfect fit: explicit residuals, on the general path
-            } else {
-                const OlsOut o = ols_statistics(beta[1], wsm[P * P + P + 1], rss, tss, n_used, P);
-                const uint64_t oi = kb + lane - q.item_base;
-                c.out.p[oi] = o.p;
-                c.out.r2[oi] = o.r2;
-                c.out.beta[oi] = o.beta;
-                c.out.se[oi] = o.se;
-                c.out.code[oi] = kPValue;
-            }
-        }
+        if (lane < uint32_t(GB) && kb + lane < k1) bad = !cov_eqtl_finish<P>(c, wsm, xty, my_syy, n_used, kb + lane - q.item_base);
         if (__any_sync(0xffffffffu, bad)) {
             redo = true;
             break;
@@ -785,3 +802,4 @@ inline cudaError_t launch_eqtl_covar(CovEqtlParams& q, uint64_t max_items_per_en
         default: return cudaErrorInvalidValue;
     }
 }
+
