@@ -1222,7 +1222,8 @@ cudaError_t launch_quantitative_impl(const MatrixDev& m, const double* y_raw, co
         g.list = b.big_list;
         g.n_list_dev = b.counters;
         if ((e = launch_quant_general(g, b.n_snarls, num_sms, st)) != cudaSuccess) return e;
-        if (launches) *launches += 5;
+        // K3C instances (2-, 3-, 4-path snarls while 1 + D + Q <= 8), K4C, K4b, the general kernel's two launches
+        if (launches) *launches += 1 + (3 + n_covar <= uint32_t(kCovFeat)) + (4 + n_covar <= uint32_t(kCovFeat)) + 1 + 1 + 2;
         return cudaSuccess;
     }
     g.list = nullptr;
