@@ -1,5 +1,3 @@
 mkdir -p gpurun_out
-for v in 0 1 2 4 8; do
-STOAT_GPU_E3C_PREFETCH=$v timeout 200 python bench.py --trait eqtl --ncov 3 --snarls 2000 --genes 2000 --steps 3 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/r2s_eqtl_ncov3.json 2> gpurun_out/r2s_eqtl_ncov3.err
-python -c "import json;d=json.load(open('gpurun_out/r2s_eqtl_ncov3.json'));print('eqtl ncov3 prefetch $v', d['value'], d['ms_per_step'], d['parity']['mismatches'])"; tail -3 gpurun_out/r2s_eqtl_ncov3.err
-done
+timeout 600 python -m pytest tests/test_gpu_eqtl.py tests/test_gpu_shim.py tests/test_gpu_vs_reference.py -m gpu -x -q 2>&1 | tail -6
+timeout 600 python scripts/bench_eqtl_windows.py 100000 5000 2000 5 2>&1 | tail -4 | tee gpurun_out/r2s_eqtl_windows.txt

@@ -1267,7 +1267,7 @@ int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const
     ctx->have_quant_result = false;  // the pair outputs live in the quantitative result buffers
     if ((rc = eqtl_reserve_pairs(ctx, n_pairs))) return rc;
     const uint64_t S = ctx->batch.n_snarls, P = ctx->batch.n_paths;
-    const bool cov_fast = ctx->n_covar && quant_covar_fast(uint32_t(ctx->n_covar));
+    const bool cov_fast = quant_covar_fast(ctx->n_covar ? uint32_t(ctx->n_covar) : 1u);  // (also without covariates: Q = 0)
     if (cov_fast) CK(extra_of(ctx)->q.cov_flag.reserve(std::max<uint64_t>(S, 16)));
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     CK(launch_eqtl_general(matrix_view(ctx), ctx->e_expr.as<double>(), uint32_t(genes->n_genes),
@@ -1275,8 +1275,8 @@ int stoat_gpu_eqtl_batch(stoat_gpu_ctx* ctx, const stoat_gpu_paths* paths, const
                            genes->snarl_gene_off ? ctx->e_gene_idx.as<uint32_t>() : nullptr,
                            ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar), ctx->batch, 0, S, 0,
                            *thr, eqtl_out_view(ctx), ctx->num_sms, ctx->stream, nullptr,
-                           cov_fast ? extra_of(ctx)->q.cov_prefix.as<double>() : nullptr, uint32_t(ctx->n_samples_covar),
-                           cov_fast ? extra_of(ctx)->q.cov_flag.as<uint8_t>() : nullptr, 0));
+                           (cov_fast && ctx->n_covar) ? extra_of(ctx)->q.cov_prefix.as<double>() : nullptr,
+                           uint32_t(ctx->n_samples_covar), cov_fast ? extra_of(ctx)->q.cov_flag.as<uint8_t>() : nullptr, 0));
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
     const cudaMemcpyKind k = cudaMemcpyDeviceToHost;
     CK(cudaEventRecord(ctx->ev[6], ctx->stream));
@@ -1472,14 +1472,14 @@ int stoat_gpu_eqtl_dense_run_staged(stoat_gpu_ctx* ctx, const stoat_gpu_threshol
     if (n_fb) {
         const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(n_fb, (uint64_t(1) << 24) / G + 1));
         if (int rc = eqtl_reserve_pairs(ctx, chunk * G)) return rc;
-        const bool cov_fast = ctx->n_covar && quant_covar_fast(uint32_t(ctx->n_covar));
+        const bool cov_fast = quant_covar_fast(ctx->n_covar ? uint32_t(ctx->n_covar) : 1u);
         if (cov_fast) CK(extra_of(ctx)->q.cov_flag.reserve(std::max<uint64_t>(chunk, 16)));
         for (uint64_t i0 = 0; i0 < n_fb; i0 += chunk) {
             const uint64_t ns = std::min<uint64_t>(chunk, n_fb - i0);
             CK(launch_eqtl_general(matrix_view(ctx), ctx->e_expr.as<double>(), uint32_t(G), nullptr, nullptr,
                                    ctx->n_covar ? ctx->covar.as<double>() : nullptr, uint32_t(ctx->n_covar), b, 0, ns, 0,
                                    *thr, eqtl_out_view(ctx), ctx->num_sms, ctx->stream, e.fb_list + i0,
-                                   cov_fast ? extra_of(ctx)->q.cov_prefix.as<double>() : nullptr,
+                                   (cov_fast && ctx->n_covar) ? extra_of(ctx)->q.cov_prefix.as<double>() : nullptr,
                                    uint32_t(ctx->n_samples_covar), cov_fast ? extra_of(ctx)->q.cov_flag.as<uint8_t>() : nullptr, G));
             CK(launch_eqtl_summary(ctx->q_p.as<double>(), ctx->q_code.as<uint8_t>(), ctx->filtered.as<uint8_t>(), 0, ns,
                                    uint32_t(G), p_threshold, e.min_p, e.argmin, e.n_below, ctx->stream, e.fb_list + i0));

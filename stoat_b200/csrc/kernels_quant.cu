@@ -1267,8 +1267,10 @@ cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, ui
                                 uint8_t* cov_flag, uint64_t max_items_per_snarl) {
     if (n_snarls == 0) return cudaSuccess;
     // covariates: the sweep kernels of quant_covar.cuh first; they flag the entries the general kernel must take
-    const bool cov_fast = n_covar && covar && cov_prefix && cov_flag && cov_rows >= uint32_t(m.n_cols / 2) &&
-                          quant_covar_fast(n_covar);
+    // (without covariates the same kernels run with Q = 0: the gene windows of eqtl_batch and the shapes a dense scan
+    // leaves over; the dense scan itself is the tensor-core path's)
+    const bool cov_fast = cov_flag && quant_covar_fast(n_covar ? n_covar : 1u) &&
+                          (n_covar == 0 || (covar && cov_prefix && cov_rows >= uint32_t(m.n_cols / 2)));
     if (cov_fast) {
         CovEqtlParams q{};
         q.c.rows = m.rows;
@@ -1277,7 +1279,7 @@ cudaError_t launch_eqtl_general(const MatrixDev& m, const double* expression, ui
         q.c.n_samples = uint32_t(m.n_cols / 2);
         q.c.n_covar = n_covar;
         q.c.cov_rows = cov_rows;
-        q.c.covar_t = cov_prefix + size_t(cov_rows + 1) * (n_covar + n_covar * (n_covar + 1) / 2);
+        q.c.covar_t = n_covar ? cov_prefix + size_t(cov_rows + 1) * (n_covar + n_covar * (n_covar + 1) / 2) : nullptr;
         q.c.b = b;
         q.c.thr = thr;
         q.c.out = out;

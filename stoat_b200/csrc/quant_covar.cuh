@@ -380,7 +380,7 @@ inline cudaError_t launch_covar_moments(const CovParams& c, int num_sms, cudaStr
 }
 
 // =================================================================================================
-// E3C: the eQTL regressions WITH COVARIATES off the general kernel (EQTLSnarlAnalyzer::analyze_and_write_snarl,
+// E3C: the eQTL regressions of gene windows, and of any scan WITH COVARIATES, off the general kernel (EQTLSnarlAnalyzer::analyze_and_write_snarl,
 // src/snarl_analyzer.cpp:493-539, one OLS per gene of the snarl's window on the same table).
 // A warp takes (snarl, share of its genes): one sweep over the samples for the design's own moments (as K3C) and, on lane
 // 0, the filters and (X'X)^-1 — once per snarl, as the reference should have done (it re-inverts per gene, :510-520) —
@@ -467,7 +467,8 @@ __device__ __forceinline__ int cov_eqtl_design(const CovEqtlParams& q, const dou
     constexpr int D = NP - 1, kTri = D * (D + 1) / 2, P = 1 + D + Q;
     const CovParams& c = q.c;
     // ---- the design: one sweep --------------------------------------------------------------------------------------
-    double s1d[D], sdd[kTri], sdc[D][Q];
+    constexpr int QA = Q > 0 ? Q : 1;  // (Q = 0: the same kernels without covariates)
+    double s1d[D], sdd[kTri], sdc[D][QA];
 #pragma unroll
     for (int a = 0; a < D; ++a) {
         s1d[a] = 0.0;
@@ -483,7 +484,7 @@ __device__ __forceinline__ int cov_eqtl_design(const CovEqtlParams& q, const dou
     const uint32_t n_used = cov_for_blocks<NP, Q>(c, r0, r1, lane, al, same,
         [&](uint32_t, bool us, uint32_t rs, const uint32_t (&k)[NP], uint32_t rank) {
             rs_seen |= 1u << rs;
-            double cv[Q];
+            double cv[QA];
 #pragma unroll
             for (int j = 0; j < Q; ++j) cv[j] = us ? __ldg(c.covar_t + size_t(j) * c.cov_rows + rank) : 0.0;
             int e = 0;
@@ -614,7 +615,7 @@ template <int NP, int Q, int GB>
 __device__ __forceinline__ void cov_eqtl_snarl(const CovEqtlParams& q, const double* lut, double* wsm, uint64_t entry,
                                                uint64_t s, uint32_t part, uint64_t p0, const uint32_t (&r0)[kCovMaxD + 1],
                                                const uint32_t (&r1)[kCovMaxD + 1], uint32_t lane) {
-    constexpr int D = NP - 1, kTri = D * (D + 1) / 2, P = 1 + D + Q;
+    constexpr int D = NP - 1, kTri = D * (D + 1) / 2, P = 1 + D + Q, QA = Q > 0 ? Q : 1;
     const CovParams& c = q.c;
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
     // ---- the items (genes) of this warp ------------------------------------------------------------------------------
@@ -659,7 +660,7 @@ __device__ __forceinline__ void cov_eqtl_snarl(const CovEqtlParams& q, const dou
             const double v = lane < c.n_samples ? __ldg(yrow[g] + lane) : 0.0;
             shift[g] = warp_sum(v) / double(c.n_samples < 32u ? c.n_samples : 32u);
         }
-        double sy[GB], syy[GB], sdy[GB][D], scy[GB][Q];
+        double sy[GB], syy[GB], sdy[GB][D], scy[GB][QA];
 #pragma unroll
         for (int g = 0; g < GB; ++g) {
             sy[g] = syy[g] = 0.0;
@@ -674,7 +675,7 @@ __device__ __forceinline__ void cov_eqtl_snarl(const CovEqtlParams& q, const dou
         uint32_t same2 = 0;
         cov_for_blocks<NP, Q>(c, r0, r1, lane, al2, same2,
             [&](uint32_t i, bool us, uint32_t rs, const uint32_t (&k)[NP], uint32_t rank) {
-                double cv[Q], d[D];
+                double cv[QA], d[D];
 #pragma unroll
                 for (int j = 0; j < Q; ++j) cv[j] = us ? __ldg(c.covar_t + size_t(j) * c.cov_rows + rank) : 0.0;
 #pragma unroll
@@ -794,6 +795,7 @@ inline cudaError_t launch_eqtl_covar(CovEqtlParams& q, uint64_t max_items_per_en
     const uint64_t ctas = (n_work + kCovEqtlWarps - 1) / kCovEqtlWarps;
     const unsigned grid = unsigned(ctas < cap ? ctas : cap);
     switch (q.c.n_covar) {
+        case 0: return launch_eqtl_covar_q<0>(q, grid, st);
         case 1: return launch_eqtl_covar_q<1>(q, grid, st);
         case 2: return launch_eqtl_covar_q<2>(q, grid, st);
         case 3: return launch_eqtl_covar_q<3>(q, grid, st);
