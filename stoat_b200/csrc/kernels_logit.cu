@@ -37,6 +37,14 @@ __device__ __forceinline__ uint4 ldg_nc_v4(const uint8_t* p) {
     return v;
 }
 
+// three paths of at most two checked edges each: logit_three_path_kernel (L3) takes the snarl
+__device__ __forceinline__ bool logit_three_shape(const BatchDev& b, uint64_t p0, uint64_t p1) {
+    if (p1 - p0 != 3) return false;
+    for (int j = 0; j < 3; ++j)
+        if (b.path_edge_off[p0 + j + 1] - b.path_edge_off[p0 + j] > 2) return false;
+    return true;
+}
+
 struct Acc12 {
     uint32_t al0 = 0, al1 = 0, used = 0, full0 = 0, half = 0, third = 0, tthird = 0;
     uint32_t c_used = 0, c_full0 = 0, c_half = 0, c_third = 0, c_tthird = 0;
@@ -83,7 +91,7 @@ __global__ void __launch_bounds__(256) logit_class_counts_kernel(const uint8_t* 
         if (general) {
             if (lane == 0) {
                 out[s].al0 = kLogitGeneral;
-                general_list[atomicAdd(n_general, 1u)] = uint32_t(s);
+                if (!logit_three_shape(b, p0, p1)) general_list[atomicAdd(n_general, 1u)] = uint32_t(s);  // else L3 has it
             }
             continue;
         }
@@ -275,6 +283,208 @@ __global__ void __launch_bounds__(128) logit_irls_kernel(const LogitCounts* __re
     out.code[s] = r.code;
 }
 
+// ---- L3: three-path snarls ---------------------------------------------------------------------------------------------
+// With every sample on one or two path-haplotypes the rows of X = [1, d0, d1] (path 2 is the column the reference drops,
+// snarl_analyzer.cpp:676-684) take SIX values — (1,0) (0,1) (0,0) for a sample on one path, (1/2,1/2) (1/2,0) (0,1/2) for one
+// haplotype on each of two — so the regression is a function of 6 class x phenotype counts, as the two-path one is of 5.
+// A warp per snarl: the class masks word by word, popcounts of (class) and (class & case), then lane 0 applies the filters
+// and runs the IRLS over the six weighted points (the reference's operations per point), Wald tests of both columns, Holm.
+// Anything else — a sample on three or more path-haplotypes, an empty or missing path, identical columns (the reference
+// merges them) — goes to the general kernel.  (The general kernel alone took 40 of the 46 ms of a C3 step for these 5 % of
+// the snarls.)
+namespace {
+
+struct Logit3 {
+    double p, beta, se;
+    uint8_t code;
+};
+
+__device__ Logit3 logit_irls_classes3(const uint32_t (&n0)[6], const uint32_t (&n1)[6]) {
+    constexpr double kTol = 1e-6, kL2 = 1e-4, kEps = 1e-8;  // src/stats_test.hpp:109-112
+    constexpr int kMaxIter = 100;
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    const double d0[6] = {1.0, 0.0, 0.0, 0.5, 0.5, 0.0}, d1[6] = {0.0, 1.0, 0.0, 0.5, 0.0, 0.5};
+    double bt[3] = {0.0, 0.0, 0.0}, old[3] = {0.0, 0.0, 0.0};
+    bool converged = false;
+    for (int pass = 0; pass <= kMaxIter; ++pass) {
+        double h[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};  // lower triangle (0,0) (1,0) (1,1) (2,0) (2,1) (2,2)
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+            const uint32_t nt = n0[c] + n1[c];
+            if (!nt) continue;
+            const double z = fma(d1[c], bt[2], fma(d0[c], bt[1], bt[0]));
+            const double pr = 1.0 / (1.0 + exp(-z));                  // :27-29
+            const double w = fmax(kEps, fmin(1.0, pr * (1.0 - pr)));   // :93
+            const double sw = sqrt(w), x1 = d0[c] * sw, x2 = d1[c] * sw;  // :97-98
+            const double cnt = double(nt);
+            h[0] = fma(cnt, sw * sw, h[0]);
+            h[1] = fma(cnt, x1 * sw, h[1]);
+            h[2] = fma(cnt, x1 * x1, h[2]);
+            h[3] = fma(cnt, x2 * sw, h[3]);
+            h[4] = fma(cnt, x2 * x1, h[4]);
+            h[5] = fma(cnt, x2 * x2, h[5]);
+            const double r = fma(double(n1[c]), 1.0 - pr, double(n0[c]) * (0.0 - pr));  // sum of (y - p) over the class
+            g[0] += r;
+            g[1] = fma(d0[c], r, g[1]);
+            g[2] = fma(d1[c], r, g[2]);
+        }
+        SmallMat<3> H;
+        H(0, 0) = h[0] + kL2;
+        H(1, 0) = H(0, 1) = h[1];
+        H(1, 1) = h[2] + kL2;
+        H(2, 0) = H(0, 2) = h[3];
+        H(2, 1) = H(1, 2) = h[4];
+        H(2, 2) = h[5] + kL2;
+        if (converged) {
+            double diag[3];
+            lu_inverse_diag<3>(H, 3, diag);  // :138-139
+            double pv[2];
+            for (int i = 0; i < 2; ++i) pv[i] = 2.0 * (1.0 - normal_cdf_like_reference(fabs(bt[1 + i] / sqrt(diag[1 + i]))));  // :151-152
+            // adjusted_holm (src/utils.cpp:61-87) + the smallest adjusted value, first index on ties (:169-175)
+            const int lo = pv[1] < pv[0] ? 1 : 0, hi = 1 - lo;  // stable order: ties keep index 0 first
+            double adj[2];
+            adj[lo] = fmin(2.0 * pv[lo], 1.0);
+            adj[hi] = fmax(adj[lo], fmin(pv[hi], 1.0));
+            const int best = adj[1] < adj[0] ? 1 : 0;
+            return {adj[best], bt[1 + best], sqrt(diag[1 + best]), kPValue};
+        }
+        if (pass == kMaxIter) break;
+        double st[3] = {g[0] - kL2 * bt[0], g[1] - kL2 * bt[1], g[2] - kL2 * bt[2]};  // :105
+        int tr[3];
+        ldlt_factor<3>(H, 3, tr);
+        if (isnan(H(0, 0)) || isnan(H(1, 1)) || isnan(H(2, 2))) return {nan, nan, nan, kPNa};  // :107
+        ldlt_solve<3>(H, 3, tr, st);
+        double nrm = 0.0;
+        for (int r = 0; r < 3; ++r) {
+            bt[r] += st[r];
+            const double e = bt[r] - old[r];
+            nrm = fma(e, e, nrm);
+        }
+        if (sqrt(nrm) < kTol) {  // :113
+            converged = true;
+        } else {
+            for (int r = 0; r < 3; ++r) old[r] = bt[r];
+        }
+    }
+    return {nan, nan, nan, kPNa};  // :120
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(256) logit_three_path_kernel(const uint8_t* __restrict__ rows, uint32_t pitch, uint32_t n_hap,
+                                                               const uint8_t* __restrict__ case_mask, const BatchDev b,
+                                                               const stoat_gpu_thresholds thr, LogitOut out,
+                                                               uint32_t* __restrict__ general_list,
+                                                               uint32_t* __restrict__ n_general) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t warp = (uint64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    const uint64_t n_warps = (uint64_t(gridDim.x) * blockDim.x) >> 5;
+    const uint32_t n_words = pitch / 4, M = 0x55555555u;
+    const double nan = __longlong_as_double(0x7ff8000000000000LL);
+    for (uint64_t s = warp; s < b.n_snarls; s += n_warps) {
+        const uint64_t p0 = b.snarl_path_off[s], p1 = b.snarl_path_off[s + 1];
+        if (!logit_three_shape(b, p0, p1)) continue;
+        // lane j < 3: the rows of path j (kLogitAll: no checked edge, every haplotype)
+        uint32_t my_r0 = 0xFFFFFFFEu, my_r1 = 0xFFFFFFFEu;
+        bool missing = false;
+        if (lane < 3) {
+            const uint64_t a = b.path_edge_off[p0 + lane], z = b.path_edge_off[p0 + lane + 1];
+            if (z > a) {
+                my_r0 = b.edge_row[a];
+                my_r1 = z - a == 2 ? b.edge_row[a + 1] : my_r0;
+                missing = my_r0 == kMissingL || my_r1 == kMissingL;
+            }
+        }
+        if (__any_sync(0xffffffffu, missing)) {  // an empty path: the table has two columns, the general kernel builds it
+            if (lane == 0) general_list[atomicAdd(n_general, 1u)] = uint32_t(s);
+            continue;
+        }
+        uint32_t r0[3], r1[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            r0[j] = __shfl_sync(0xffffffffu, my_r0, j);
+            r1[j] = __shfl_sync(0xffffffffu, my_r1, j);
+        }
+        uint32_t al[3] = {0, 0, 0}, cnt[6] = {0, 0, 0, 0, 0, 0}, cas[6] = {0, 0, 0, 0, 0, 0}, bad = 0, differ = 0;
+        for (uint32_t w = lane; w < n_words; w += 32) {
+            const uint32_t cm = *reinterpret_cast<const uint32_t*>(case_mask + size_t(w) * 4);
+            uint32_t c1[3], any[3], f[3];
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                uint32_t pw;
+                if (r0[j] == 0xFFFFFFFEu) {
+                    pw = valid_word(w, n_hap);
+                } else {
+                    pw = __ldg(reinterpret_cast<const uint32_t*>(rows + size_t(r0[j]) * pitch) + w) &
+                         __ldg(reinterpret_cast<const uint32_t*>(rows + size_t(r1[j]) * pitch) + w);
+                }
+                al[j] += __popc(pw);
+                const uint32_t sft = pw >> 1;
+                c1[j] = (pw ^ sft) & M;
+                any[j] = (pw | sft) & M;
+                f[j] = pw - (sft & M);  // 2-bit count fields
+            }
+            differ |= (f[0] != f[1] ? 1u : 0u) | (f[0] != f[2] ? 2u : 0u) | (f[1] != f[2] ? 4u : 0u);
+            uint32_t cls[6];
+            cls[0] = any[0] & ~any[1] & ~any[2];
+            cls[1] = any[1] & ~any[0] & ~any[2];
+            cls[2] = any[2] & ~any[0] & ~any[1];
+            cls[3] = c1[0] & c1[1] & ~any[2];
+            cls[4] = c1[0] & c1[2] & ~any[1];
+            cls[5] = c1[1] & c1[2] & ~any[0];
+            uint32_t covered = 0;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+                cnt[c] += __popc(cls[c]);
+                cas[c] += __popc(cls[c] & cm);
+                covered |= cls[c];
+            }
+            bad |= (any[0] | any[1] | any[2]) & ~covered;  // a sample on three or more path-haplotypes
+        }
+#pragma unroll
+        for (int j = 0; j < 3; ++j) al[j] = __reduce_add_sync(0xffffffffu, al[j]);
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+            cnt[c] = __reduce_add_sync(0xffffffffu, cnt[c]);
+            cas[c] = __reduce_add_sync(0xffffffffu, cas[c]);
+        }
+        bad = __reduce_or_sync(0xffffffffu, bad);
+        differ = __reduce_or_sync(0xffffffffu, differ);
+        if (lane != 0) continue;
+        if (bad != 0u || differ != 7u || al[0] == 0 || al[1] == 0 || al[2] == 0) {
+            general_list[atomicAdd(n_general, 1u)] = uint32_t(s);  // thirds, identical columns, an empty column
+            continue;
+        }
+        const uint32_t n_used = cnt[0] + cnt[1] + cnt[2] + cnt[3] + cnt[4] + cnt[5];
+        // filtration_quantitative_table (src/snarl_analyzer.cpp:542-579): every sum is dyadic, hence exact
+        const double colsum[3] = {double(cnt[0]) + 0.5 * double(cnt[3] + cnt[4]), double(cnt[1]) + 0.5 * double(cnt[3] + cnt[5]),
+                                  double(cnt[2]) + 0.5 * double(cnt[4] + cnt[5])};
+        bool filtered = n_used == 0 || uint64_t(n_used) < thr.min_individuals;
+        if (!filtered) {
+            const double total = double(n_used);
+            int above = 0;
+            for (int j = 0; j < 3; ++j) {
+                const double fr = __ddiv_rn(colsum[j], total);
+                if (fmin(fr, __dsub_rn(1.0, fr)) > thr.maf_threshold) ++above;
+            }
+            filtered = total < double(thr.min_haplotypes) || above < 2;
+        }
+        for (int j = 0; j < 3; ++j) out.allele_paths[p0 + j] = al[j];
+        out.filtered[s] = filtered ? 1 : 0;
+        out.n_used[s] = n_used;
+        Logit3 r{nan, nan, nan, kPNa};
+        if (!filtered) {
+            uint32_t n0[6];
+            for (int c = 0; c < 6; ++c) n0[c] = cnt[c] - cas[c];
+            r = logit_irls_classes3(n0, cas);
+        }
+        out.p[s] = r.p;
+        out.beta[s] = r.beta;
+        out.se[s] = r.se;
+        out.code[s] = r.code;
+    }
+}
+
 cudaError_t launch_logit_fast(const MatrixDev& m, const uint8_t* case_mask, const BatchDev& b,
                               const stoat_gpu_thresholds& thr, LogitCounts* counts, uint32_t* general_list,
                               uint32_t* n_general, LogitOut out, int num_sms, cudaStream_t st, uint32_t* launches) {
@@ -287,6 +497,10 @@ cudaError_t launch_logit_fast(const MatrixDev& m, const uint8_t* case_mask, cons
     if (e != cudaSuccess) return e;
     logit_irls_kernel<<<unsigned((b.n_snarls + 127) / 128), 128, 0, st>>>(counts, b, thr, out, general_list, n_general);
     if (launches) *launches += 2;
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    logit_three_path_kernel<<<unsigned(std::min(want, cap)), 256, 0, st>>>(m.rows, uint32_t(m.pitch), uint32_t(m.n_cols), case_mask,
+                                                                           b, thr, out, general_list, n_general);
+    if (launches) *launches += 1;
     return cudaGetLastError();
 }
 

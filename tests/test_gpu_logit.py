@@ -58,6 +58,23 @@ def test_two_path_class_counts(gpu_ctx, oracle, seed, n_samples):
     assert gpu_ctx.timing()["n_general"] == 0
 
 
+@pytest.mark.parametrize("seed,n_samples,p_missing", [(21, 90, 0.05), (22, 700, 0.0), (23, 2500, 0.3), (24, 5000, 0.01)])
+def test_three_path_class_counts(gpu_ctx, oracle, monkeypatch, seed, n_samples, p_missing):
+    """L3 (logit_three_path_kernel): a three-path snarl whose samples sit on one or two path-haplotypes is a regression over
+    SIX weighted points (two dosage columns, Holm over their Wald tests).  Against the oracle and against the general
+    kernel on the same snarls; two-path snarls in the same batch keep their own kernel."""
+    rng = np.random.default_rng(seed)
+    dense, snarls = H.partition_problem(rng, 200 if n_samples < 5000 else 60, n_samples, max_paths=3, p_missing_hap=p_missing)
+    is_case = planted_phenotype(rng, dense, snarls, n_samples)
+    got, ref = run_both(gpu_ctx, oracle, dense, snarls, is_case, min_ind=2, min_hap=2, maf=0.01)
+    assert assert_logit_equal(got, ref) > 20
+    assert gpu_ctx.timing()["n_general"] <= len(snarls) // 20  # (an empty or a repeated column sends a snarl there)
+    assert sum(len(s_) == 3 for s_ in snarls) > 20
+    monkeypatch.setenv("STOAT_GPU_LOGIT", "general")
+    slow, _ = run_both(gpu_ctx, oracle, dense, snarls, is_case, min_ind=2, min_hap=2, maf=0.01)
+    assert_logit_equal(got, slow)
+
+
 @pytest.mark.parametrize("seed,n_samples", [(5, 80), (6, 700)])
 def test_many_paths_holm_general_kernel(gpu_ctx, oracle, seed, n_samples):
     rng = np.random.default_rng(seed)
