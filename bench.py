@@ -517,6 +517,58 @@ def parity_spot_check(env, ctx, d, trait, n_check, res, col_sharded, covar=None)
     return out
 
 
+def logit_record(env, args, ctx, d, stream):
+    """The binary trait WITH covariates (BinaryCovarSnarlAnalyzer: a logistic regression per snarl) on the
+    resident batch: device-resident timing of stoat_gpu_binary_covar_run_staged, parity of the first snarls against the
+    oracle.  As the reference does, the covariates have no effect on the fit (src/stats_test.cpp:59-62)."""
+    torch = env.torch
+    paths = d["paths"]
+    ctx.set_binary_phenotype(d["is_case"])
+    ctx.stage_paths(paths)
+    steps, warm = args.steps, max(args.warmup, 3)
+    for _ in range(warm):
+        ctx.binary_covar_run_staged()
+    env.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        ctx.binary_covar_run_staged()
+    e1.record(stream)
+    env.barrier()
+    elapsed_ms = env.max_over_ranks(e0.elapsed_time(e1))
+    res = ctx.binary_covar_fetch()
+    t = ctx.timing()
+    launches = int(env.sum_over_ranks(t["launches"] * steps))
+    if env.rank != 0:
+        return None
+    parity = None
+    if not args.no_parity:
+        import oracle
+
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import test_gpu_logit
+
+        k = min(paths.n_snarls, 5000)
+        st = d["structure"]
+        r1 = int(st.row0[k - 1] + st.n_rows_of[k - 1])
+        bits = d["bits_dev"][: r1 * (d["n_cols"] // 8)].cpu().numpy()
+        P1 = int(paths.snarl_path_off[k])
+        E1 = int(paths.path_edge_off[P1])
+        sub = oracle.Paths(paths.snarl_path_off[: k + 1].copy(), paths.path_edge_off[: P1 + 1].copy(), paths.edge_row[:E1].copy())
+        ref = oracle.binary_covar_batch(bits, d["n_cols"], d["is_case"], sub, n_threads=host_threads())
+        got = {kk: (v[:P1] if kk == "allele_paths" else v[:k]) for kk, v in res.items()}
+        try:
+            parity = {"checked_snarls": int(k), "fits": int(test_gpu_logit.assert_logit_equal(got, ref)), "mismatches": 0,
+                      "against": "oracle port: tables / flags bit-exact, beta / se / p 1e-9 relative"}
+        except AssertionError as e:
+            parity = {"checked_snarls": int(k), "mismatches": 1, "first_mismatch": str(e)[:300]}
+    return {"metric": "snarl-path tests/sec (binary with covariates: logistic regression)", "unit": UNIT,
+            "value": env.world * paths.n_paths * steps / (elapsed_ms * 1e-3), "ms_per_step": elapsed_ms / steps, "steps": steps,
+            "n_gpus": env.world, "dtype": "u32 popcounts + f64 IRLS", "gpu_launches": launches,
+            "kernels_ms": {"class counts (L1)": t["table_ms"], "IRLS (L2), three-path snarls (L3), general kernel": t["stats_ms"]},
+            "snarls_on_general_kernel": int(t["n_general"]), "parity": parity}
+
+
 def trait_record(env, args, ctx, d, trait, stream, host_cache, with_clocks=True):
     """Measure one presence-matrix trait (binary | quantitative) on the resident data set -> the record of the JSON line."""
     torch = env.torch
@@ -819,6 +871,9 @@ def main():
             if rank == 0:
                 qc["roofline"] = None  # (the record's roofline object describes K3M, which does not run with covariates)
                 traits["quantitative_3_covariates"] = qc
+            lr = logit_record(env, args, ctx, d, stream)
+            if rank == 0:
+                traits["binary_with_covariates_logistic"] = lr
     host_cache.clear()
     ctx.close()
     del d
