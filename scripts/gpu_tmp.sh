@@ -1,3 +1,4 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_logit.py tests/test_gpu_wide.py tests/test_gpu_shim.py -m gpu -x -q 2>&1 | tail -8
-timeout 300 python scripts/fuzz_parity.py 60 50000 > gpurun_out/r2s_fuzz3.txt 2>&1; tail -3 gpurun_out/r2s_fuzz3.txt | cut -c1-700
+K='regex:^(binary_|build_case|centre_|covar_|dosage_|eqtl_|fisher_|lean_rec|logit_|ols_solve|path_and|quant_general|repack_rows|student_tail)'
+timeout 250 ncu --metrics gpu__time_duration.sum --clock-control none -k "$K" -c 600 --csv --log-file gpurun_out/launches_binary.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e --no-parity > gpurun_out/ncu_l1.log 2>&1
+wc -l gpurun_out/launches_binary.csv
